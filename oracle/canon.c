@@ -1,0 +1,779 @@
+/* O-canon — CPU restatement of learn-comms' per-frame loop.  TEST INFRASTRUCTURE ONLY.
+ * See canon.h for the rules (never linked into the product).  Compile with
+ *   gcc -O2 -ffp-contract=off -fno-fast-math  (no FMA contraction: the reference's CMake sets no -march / -O,
+ *   enginee/CMakeLists.txt:68-80, so it executes plain SSE2 mul+add).
+ * All arithmetic is IEEE binary32 unless marked f64.  "table order" = ascending agent index.
+ */
+#include "canon.h"
+#include <float.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---------- glm restatement (glm @ d214fbaa, 0.9.9 API) ---------- */
+typedef struct { float x, y; } v2;
+static inline v2 V2(float x, float y) { v2 r = {x, y}; return r; }
+static inline v2 add2(v2 a, v2 b) { return V2(a.x + b.x, a.y + b.y); }
+static inline v2 sub2(v2 a, v2 b) { return V2(a.x - b.x, a.y - b.y); }
+static inline v2 mul2s(v2 a, float s) { return V2(a.x * s, a.y * s); }
+static inline v2 div2s(v2 a, float s) { return V2(a.x / s, a.y / s); }
+static inline float dot2(v2 a, v2 b) { return a.x * b.x + a.y * b.y; }       /* tmp.x + tmp.y */
+static inline float len2_2(v2 a) { return dot2(a, a); }                        /* gtx/norm length2 */
+static inline float len_2(v2 a) { return sqrtf(dot2(a, a)); }
+static inline v2 normalize2(v2 a) { return mul2s(a, 1.0f / sqrtf(dot2(a, a))); } /* v * inversesqrt(dot) */
+static inline float glm_min(float a, float b) { return (b < a) ? b : a; }
+static inline float glm_max(float a, float b) { return (a < b) ? b : a; }
+static inline float glm_clamp(float x, float lo, float hi) { return glm_min(glm_max(x, lo), hi); }
+/* vec3 with y == 0: dot = (x*x' + 0*0) + z*z' */
+static inline float dot3_xz(float ax, float az, float bx, float bz) { return (ax * bx + 0.0f * 0.0f) + az * bz; }
+
+/* ---------- RNG: Seeder.cpp:5-20; libstdc++ minstd_rand0 + uniform_real_distribution<float> ---------- */
+uint32_t canon_lcg_next(uint32_t x) { return (uint32_t)(((uint64_t)x * 16807u) % 2147483647u); }
+uint32_t canon_lcg_seed(uint64_t seed) {
+    /* linear_congruential_engine::seed(s): if (c % m == 0 && s % m == 0) x = 1 else x = s % m */
+    uint64_t x = seed % 2147483647u;
+    return x == 0 ? 1u : (uint32_t)x;
+}
+/* generate_canonical<float,24>: k = 1 call; sum = float(x - min); tmp = float(2147483646.0L);
+ * ret = sum / tmp, clamped below 1; then u * (b - a) + a   (bits/random.tcc) */
+float canon_uniform(uint32_t x, float a, float b) {
+    float sum = (float)(x - 1u);
+    float tmp = (float)2147483646.0L;
+    float ret = sum / tmp;
+    if (ret >= 1.0f) ret = nextafterf(1.0f, 0.0f);
+    return ret * (b - a) + a;
+}
+
+/* ---------- state ---------- */
+struct canon_sim {
+    int32_t n;
+    float r;
+    float max_duration;
+    uint32_t rng;
+    float m_cv[24], m_f[6];
+    int comm_enabled, use_grid;
+    int32_t n_walls;
+    canon_rect* walls;
+    /* Dynamics.h:2-11 (live subset), Agent.h:6-33, CommComp.h:13-17 */
+    v2 *pos, *vel, *vfh, *force;
+    v2 *goal, *local_goal, *facing;
+    float (*c)[3], (*c_buf)[3];
+    v2* f_buf;
+    float *goal_dist, *min_time;
+    int32_t* num_done;
+    uint8_t* counted;
+    uint32_t* lost;
+    /* demo.cpp:650-653 */
+    int32_t total_num_done;
+    float run_avg, M2, run_std;
+    float avg_velocity; /* physics.cpp:10 */
+    uint32_t frame;
+    int finished;
+    /* diagnostics */
+    int32_t *partner, *nbr_cnt;
+    int record_nbrs;
+    int64_t* nbr_ptr;
+    int32_t* nbr_idx;
+    int64_t nbr_cap, nbr_total;
+    int64_t overlap_pairs, coll_hits;
+    /* scratch */
+    v2* pos_new;
+    /* grid scratch */
+    int32_t *cell_start, *cell_items;
+    int32_t gcap;
+};
+
+#define PLAN_SIZE 1 /* wall-free scenes: GMP::plan_one yields plan = [final_goal] (GMP.cpp:91-110) */
+static inline int is_done(const canon_sim* s, int i) { return s->num_done[i] == PLAN_SIZE; } /* Agent.h:22-24 */
+
+canon_sim* canon_create(const canon_desc* d) {
+    canon_sim* s = (canon_sim*)calloc(1, sizeof(*s));
+    int n = d->n;
+    s->n = n;
+    s->r = d->radius;
+    s->max_duration = d->max_duration;
+    s->rng = d->rng_state;
+    s->comm_enabled = d->comm_enabled;
+    s->use_grid = d->use_grid;
+    if (d->m_cv) memcpy(s->m_cv, d->m_cv, sizeof(s->m_cv));
+    if (d->m_f) memcpy(s->m_f, d->m_f, sizeof(s->m_f));
+    s->n_walls = d->n_walls;
+    if (d->n_walls > 0) {
+        s->walls = (canon_rect*)malloc(sizeof(canon_rect) * (size_t)d->n_walls);
+        memcpy(s->walls, d->walls, sizeof(canon_rect) * (size_t)d->n_walls);
+    }
+#define AL(p, T) s->p = (T*)calloc((size_t)n + 1, sizeof(T))
+    AL(pos, v2); AL(vel, v2); AL(vfh, v2); AL(force, v2); AL(goal, v2); AL(local_goal, v2); AL(facing, v2);
+    AL(f_buf, v2); AL(goal_dist, float); AL(min_time, float); AL(num_done, int32_t); AL(counted, uint8_t);
+    AL(lost, uint32_t); AL(partner, int32_t); AL(nbr_cnt, int32_t); AL(pos_new, v2);
+#undef AL
+    s->c = calloc((size_t)n + 1, sizeof(float[3]));
+    s->c_buf = calloc((size_t)n + 1, sizeof(float[3]));
+    for (int i = 0; i < n; ++i) {
+        /* demo.cpp:563-581 create_robo; ai.cpp:107-127 ai::init; physics.cpp:15-21 prewarm (all zero) */
+        s->pos[i] = V2(d->pos[2 * i], d->pos[2 * i + 1]);
+        s->goal[i] = V2(d->goal[2 * i], d->goal[2 * i + 1]);
+        s->facing[i] = sub2(s->goal[i], s->pos[i]); /* un-normalised, demo.cpp:580 */
+        s->local_goal[i] = V2(0.f, 0.f);            /* ai.cpp:112 */
+        s->goal_dist[i] = len_2(sub2(s->goal[i], s->pos[i])); /* ai.cpp:116 */
+        float mt = -1.0f;                            /* ai.cpp:121-126 */
+        mt += len_2(sub2(s->goal[i], s->pos[i]));
+        s->min_time[i] = mt;
+    }
+    return s;
+}
+
+void canon_destroy(canon_sim* s) {
+    if (!s) return;
+    free(s->pos); free(s->vel); free(s->vfh); free(s->force); free(s->goal); free(s->local_goal);
+    free(s->facing); free(s->c); free(s->c_buf); free(s->f_buf); free(s->goal_dist); free(s->min_time);
+    free(s->num_done); free(s->counted); free(s->lost); free(s->partner); free(s->nbr_cnt);
+    free(s->nbr_ptr); free(s->nbr_idx); free(s->pos_new); free(s->cell_start); free(s->cell_items);
+    free(s->walls);
+    free(s);
+}
+
+/* ---------- S0: demo::run / update_runs (demo.cpp:655-702) ---------- */
+static void update_runs(canon_sim* s, float overhead) { /* demo.cpp:655-663 */
+    float ftotal = (float)(++s->total_num_done);
+    float delta = overhead - s->run_avg;
+    s->run_avg += delta / ftotal;
+    float delta2 = overhead - s->run_avg;
+    s->M2 += delta * delta2;
+    s->run_std = sqrtf(s->M2 / ftotal);
+}
+
+static int demo_run(canon_sim* s, uint32_t frame_count) { /* demo.cpp:665-702 */
+    int all_done = 1;
+    float dt = 1.f / 60.f;
+    float fake_time = dt * (float)frame_count;
+    for (int i = 0; i < s->n; ++i) {
+        if (!is_done(s, i)) {
+            all_done = 0;
+        } else if (!s->counted[i]) {
+            update_runs(s, fake_time - s->min_time[i]);
+            s->counted[i] = 1;
+        }
+    }
+    if (fake_time > s->max_duration) { /* demo.cpp:691-700 */
+        for (int i = 0; i < s->n; ++i) {
+            if (!is_done(s, i)) {
+                float finish_time = 2 * len_2(sub2(s->goal[i], s->pos[i])) + fake_time - s->min_time[i];
+                update_runs(s, finish_time);
+            }
+        }
+        all_done = 1;
+    }
+    return all_done;
+}
+
+/* ---------- S1: comm::run (comm.cpp:144-305, CommComp.h:18-38) ---------- */
+
+/* comm.cpp:201-220 select_nearest — returns the FARTHEST other agent (quirk Q1): running max of
+ * length2(pos_k.xz - pos_i.xz), strict '>', initialised to FLT_MIN, table order. */
+static int farthest_brute(const canon_sim* s, int i, const int32_t* cand, int ncand) {
+    v2 p_i = s->pos[i];
+    float max_dist2 = FLT_MIN;
+    int best = -1;
+    if (cand) {
+        for (int q = 0; q < ncand; ++q) {
+            int k = cand[q];
+            if (k == i) continue;
+            float dist2 = len2_2(sub2(s->pos[k], p_i));
+            if (dist2 > max_dist2) { max_dist2 = dist2; best = k; }
+        }
+    } else {
+        for (int k = 0; k < s->n; ++k) {
+            if (k == i) continue;
+            float dist2 = len2_2(sub2(s->pos[k], p_i));
+            if (dist2 > max_dist2) { max_dist2 = dist2; best = k; }
+        }
+    }
+    return best;
+}
+
+/* Exact pruning for large N (not in the reference, which is O(N^2)): the farthest point from any query is
+ * a convex-hull vertex; agents strictly inside (by margin delta) the polygon spanned by the K directional
+ * extreme agents can never win even under float rounding of length2 (margin argument in DESIGN.md).  The
+ * survivors are scanned in table order with the reference's own predicate, so the result equals brute force. */
+#define HULL_K 64
+static int hull_candidates(const canon_sim* s, int32_t* cand) {
+    int n = s->n;
+    double lox = 1e300, hix = -1e300, loy = 1e300, hiy = -1e300;
+    for (int i = 0; i < n; ++i) {
+        double x = s->pos[i].x, y = s->pos[i].y;
+        if (!(x == x) || !(y == y)) continue;
+        if (x < lox) lox = x; if (x > hix) hix = x;
+        if (y < loy) loy = y; if (y > hiy) hiy = y;
+    }
+    double cx = 0.5 * (lox + hix), cy = 0.5 * (loy + hiy);
+    double extent = fmax(hix - lox, hiy - loy);
+    double delta = 1e-5 * extent + 1e-4;
+    int ext[HULL_K];
+    for (int k = 0; k < HULL_K; ++k) {
+        double th = 2.0 * 3.14159265358979323846 * k / HULL_K, dx = cos(th), dy = sin(th), best = -1e300;
+        int bi = -1;
+        for (int i = 0; i < n; ++i) {
+            double v = (s->pos[i].x - cx) * dx + (s->pos[i].y - cy) * dy;
+            if (v > best) { best = v; bi = i; }
+        }
+        ext[k] = bi;
+    }
+    /* edges between consecutive distinct extremes (CCW) */
+    double ex[HULL_K], ey[HULL_K], enx[HULL_K], eny[HULL_K];
+    int ne = 0;
+    for (int k = 0; k < HULL_K; ++k) {
+        int a = ext[k], b = ext[(k + 1) % HULL_K];
+        if (a < 0 || b < 0 || a == b) continue;
+        double ax = s->pos[a].x, ay = s->pos[a].y, bx = s->pos[b].x, by = s->pos[b].y;
+        double ux = bx - ax, uy = by - ay, l = sqrt(ux * ux + uy * uy);
+        if (l == 0) continue;
+        ex[ne] = ax; ey[ne] = ay; enx[ne] = -uy / l; eny[ne] = ux / l; /* inward normal of a CCW polygon */
+        ++ne;
+    }
+    int nc = 0;
+    for (int i = 0; i < n; ++i) {
+        int inside = ne >= 3;
+        double x = s->pos[i].x, y = s->pos[i].y;
+        if (!(x == x) || !(y == y)) inside = 0;
+        for (int e = 0; e < ne && inside; ++e)
+            if ((x - ex[e]) * enx[e] + (y - ey[e]) * eny[e] < delta) inside = 0;
+        if (!inside) cand[nc++] = i;
+    }
+    return nc;
+}
+
+static void comm_run(canon_sim* s) { /* comm.cpp:267-305 */
+    int n = s->n;
+    int32_t* cand = NULL;
+    int ncand = 0;
+    if (s->use_grid && n > 2048) {
+        cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
+        ncand = hull_candidates(s, cand);
+    }
+    for (int i = 0; i < n; ++i) { /* pass 1, comm.cpp:268-286 */
+        int j = farthest_brute(s, i, cand, ncand);
+        s->partner[i] = j;
+        if (j < 0) { /* quirk Q3: the reference dereferences a null CommComp here (UB) */
+            fprintf(stderr, "canon: agent %d has no comm partner (reference UB, comm.cpp:273-285)\n", i);
+            abort();
+        }
+        v2 p_j = V2(s->pos[j].x, 0.f); /* vec3 -> vec2 keeps (x, y): quirk Q2, comm.cpp:276-277 */
+        v2 v_j = V2(s->vel[j].x, 0.f);
+        /* comm.cpp:144-192 x() with COSINE_REL + PROX + SOFTSIGN_GOAL */
+        v2 facing = s->facing[i];
+        v2 right = V2(facing.y, -facing.x); /* CommComp.h:38 */
+        v2 diff_v = sub2(v_j, s->vel[i]);
+        v2 rel_v = V2(right.x * diff_v.x + right.y * diff_v.y, facing.x * diff_v.x + facing.y * diff_v.y);
+        float mag_rv = len_2(rel_v);
+        if (mag_rv > 0) rel_v = div2s(rel_v, mag_rv);
+        v2 diff_p = sub2(p_j, s->pos[i]);
+        v2 rel_p = V2(right.x * diff_p.x + right.y * diff_p.y, facing.x * diff_p.x + facing.y * diff_p.y);
+        float mag_rp = len_2(rel_p);
+        if (mag_rp > 0) {
+            rel_p = div2s(rel_p, mag_rp);
+            mag_rp = 1 / mag_rp;
+        }
+        float g = s->goal_dist[i];
+        g /= 1 + g;
+        float x[8] = {s->c[j][0], s->c[j][1], s->c[j][2], rel_v.y, mag_rv, rel_p.y, mag_rp, g};
+        /* comm.cpp:285 M_cv * x_i, M_f * c_j.  Eigen 3.3 coeff-based lazy product, non-vectorised redux:
+         * pairwise tree ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)); depth 3: p0+(p1+p2).  Eigen is not vendored
+         * (lib/init.sh:58-59) so this order is restated from the 3.3 sources' redux_novec_unroller —
+         * "parity unpinned at this boundary" (SURVEY.md §8c). */
+        for (int r = 0; r < 3; ++r) {
+            const float* m = &s->m_cv[8 * r];
+            float p[8];
+            for (int q = 0; q < 8; ++q) p[q] = m[q] * x[q];
+            float cp = ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]));
+            s->c_buf[i][r] = cp / (1.f + fabsf(2.f * cp)) + 0.5f; /* CommComp.h:20-27 */
+        }
+        float fp[2];
+        for (int r = 0; r < 2; ++r) {
+            const float* m = &s->m_f[3 * r];
+            fp[r] = m[0] * s->c[j][0] + (m[1] * s->c[j][1] + m[2] * s->c[j][2]);
+        }
+        s->f_buf[i] = V2(glm_clamp(fp[0], -1.f, 1.f), glm_clamp(fp[1], -1.f, 1.f)); /* CommComp.h:30-32 */
+    }
+    free(cand);
+    for (int i = 0; i < n; ++i) { /* pass 2, comm.cpp:288-304 */
+        v2 facing = s->facing[i];
+        v2 right = V2(facing.y, -facing.x);
+        v2 fb = s->f_buf[i];
+        v2 diff = V2(right.x * fb.x + facing.x * fb.y, right.y * fb.x + facing.y * fb.y);
+        if (!is_done(s, i)) s->force[i] = add2(s->force[i], diff);
+        float speed = sqrtf(dot3_xz(s->vel[i].x, s->vel[i].y, s->vel[i].x, s->vel[i].y));
+        v2 to_lg = sub2(s->local_goal[i], s->pos[i]); /* a->start == synced position (Pool.cpp:86-88) */
+        if (speed > 0 && len_2(to_lg) > 0) s->facing[i] = normalize2(to_lg);
+        s->c[i][0] = s->c_buf[i][0]; s->c[i][1] = s->c_buf[i][1]; s->c[i][2] = s->c_buf[i][2]; /* swap() */
+        s->f_buf[i] = V2(0.f, 0.f);
+    }
+}
+
+/* ---------- uniform grid (search acceleration only; results identical to brute force) ---------- */
+typedef struct { float x0, y0, h; int nx, ny; } grid_t;
+static grid_t g_grid;
+
+static float max_speed(const canon_sim* s) {
+    float m = 0.f;
+    for (int i = 0; i < s->n; ++i) {
+        float v = len_2(s->vel[i]);
+        if (v > m) m = v;
+    }
+    return m;
+}
+
+static inline int cell_of(const grid_t* g, v2 p, int* cx, int* cy) {
+    int ix = (int)floorf((p.x - g->x0) / g->h), iy = (int)floorf((p.y - g->y0) / g->h);
+    if (ix < 0) ix = 0; if (ix >= g->nx) ix = g->nx - 1;
+    if (iy < 0) iy = 0; if (iy >= g->ny) iy = g->ny - 1;
+    *cx = ix; *cy = iy;
+    return iy * g->nx + ix;
+}
+
+static void grid_build(canon_sim* s, float cutoff) {
+    grid_t* g = &g_grid;
+    float lox = FLT_MAX, loy = FLT_MAX, hix = -FLT_MAX, hiy = -FLT_MAX;
+    for (int i = 0; i < s->n; ++i) {
+        v2 p = s->pos[i];
+        if (p.x < lox) lox = p.x; if (p.x > hix) hix = p.x;
+        if (p.y < loy) loy = p.y; if (p.y > hiy) hiy = p.y;
+    }
+    float ext = fmaxf(hix - lox, hiy - loy);
+    g->h = fmaxf(cutoff, ext / 2048.f);
+    g->x0 = lox; g->y0 = loy;
+    g->nx = (int)floorf((hix - lox) / g->h) + 1;
+    g->ny = (int)floorf((hiy - loy) / g->h) + 1;
+    int nc = g->nx * g->ny;
+    if (nc + 1 > s->gcap) {
+        free(s->cell_start);
+        s->cell_start = (int32_t*)malloc(sizeof(int32_t) * (size_t)(nc + 1));
+        s->gcap = nc + 1;
+    }
+    if (!s->cell_items) s->cell_items = (int32_t*)malloc(sizeof(int32_t) * (size_t)s->n);
+    memset(s->cell_start, 0, sizeof(int32_t) * (size_t)(nc + 1));
+    int cx, cy;
+    for (int i = 0; i < s->n; ++i) s->cell_start[cell_of(g, s->pos[i], &cx, &cy) + 1]++;
+    for (int c = 0; c < nc; ++c) s->cell_start[c + 1] += s->cell_start[c];
+    int32_t* fill = (int32_t*)malloc(sizeof(int32_t) * (size_t)nc);
+    memcpy(fill, s->cell_start, sizeof(int32_t) * (size_t)nc);
+    for (int i = 0; i < s->n; ++i) s->cell_items[fill[cell_of(g, s->pos[i], &cx, &cy)]++] = i; /* ascending id per cell */
+    free(fill);
+}
+
+/* ---------- S2: ai::update_agents + LMP::calc_sum_force (ai.cpp:132-174, LMP.cpp:13-158,244-335) ---------- */
+
+/* LMP.cpp:13-55 ttc / ttc_(Circ,Circ) + BoundVolume.cpp:102-122 Circ::intersect */
+static inline float ttc_circ_circ(v2 oi, v2 vi, v2 oj, v2 vj, float R) {
+    v2 d = sub2(vj, vi);
+    v2 m = sub2(oj, oi);
+    float a = dot2(d, d);
+    float b = dot2(m, d);
+    float c = dot2(m, m) - R * R;
+    float t;
+    if (c > 0.f && b > 0.f) return FLT_MAX;
+    float discrim = b * b - a * c;
+    if (discrim < 0.f) return FLT_MAX;
+    t = (-b - sqrtf(discrim)) / a;
+    if (t < 0.f) t = 0.f;
+    if (t < 0 || isnan(t)) return FLT_MAX; /* LMP.cpp:31-34 */
+    return t;
+}
+
+/* LMP.cpp:115-127 ttc_forces_ (f64 magnitude, quirk Q11) */
+static inline v2 ttc_forces_(double ttc, v2 dir) {
+    float len = len2_2(dir);
+    if (len > 0) dir = div2s(dir, sqrtf(len));
+    double t_h = 5.0;
+    double mag = 0;
+    if (ttc >= 0 && ttc <= t_h) mag = (t_h - ttc) / (ttc + 0.001);
+    mag = mag > 20 ? 20 : mag;
+    return V2((float)(mag * (double)dir.x), (float)(mag * (double)dir.y));
+}
+
+typedef struct { int32_t id; v2 f; } hit_t;
+static int hit_cmp(const void* a, const void* b) { return ((const hit_t*)a)->id - ((const hit_t*)b)->id; }
+
+static void record_nbr(canon_sim* s, int32_t j) {
+    if (s->nbr_total == s->nbr_cap) {
+        s->nbr_cap = s->nbr_cap ? s->nbr_cap * 2 : 1024;
+        s->nbr_idx = (int32_t*)realloc(s->nbr_idx, sizeof(int32_t) * (size_t)s->nbr_cap);
+    }
+    s->nbr_idx[s->nbr_total++] = j;
+}
+
+static void update_agents(canon_sim* s) {
+    int n = s->n;
+    float R = s->r + s->r;
+    int replanned = 0;
+    const int limit = 2;
+    hit_t* hits = NULL;
+    int hcap = 0;
+    s->overlap_pairs = 0;
+    s->nbr_total = 0;
+    if (s->record_nbrs && !s->nbr_ptr) s->nbr_ptr = (int64_t*)calloc((size_t)n + 1, sizeof(int64_t));
+    int stencil = 1;
+    if (s->use_grid) {
+        float cutoff = R + 10.f * max_speed(s) * 1.001f + 0.01f;
+        grid_build(s, cutoff);
+        stencil = (int)ceilf(cutoff / g_grid.h);
+    }
+    for (int i = 0; i < n; ++i) {
+        /* ai.cpp:153-168 */
+        s->goal_dist[i] = len_2(sub2(s->goal[i], s->pos[i]));
+        int next = s->num_done[i];
+        int visible_next = 0;
+        if (next < PLAN_SIZE) visible_next = 1; /* Cspace2d::line_of_sight over zero obstacles (PRM.cpp:169-173) */
+        s->lost[i] = visible_next ? 0 : s->lost[i] + 1;
+        int need_replan = (is_done(s, i) && s->goal_dist[i] > 1.f) ||
+                          (!is_done(s, i) && !visible_next && s->lost[i] >= 360);
+        if (replanned < limit && need_replan) {
+            s->num_done[i] = 0; /* GMP::plan_one: plan = [final_goal], num_done = 0 (GMP.cpp:91-110) */
+            ++replanned;
+            s->lost[i] = 0;
+        }
+        /* LMP::calc_sum_force, LMP.cpp:244-273; lookahead LMP.cpp:84-113 */
+        v2 o = s->pos[i];
+        int target = s->num_done[i];
+        if (target < PLAN_SIZE) {
+            int at_target = len2_2(sub2(o, s->goal[i])) < 1.f; /* ai::at_dist */
+            if (at_target) ++target;
+            if (target < PLAN_SIZE) s->local_goal[i] = s->goal[i];
+            s->num_done[i] = target;
+        } else {
+            s->local_goal[i] = s->goal[i];
+        }
+        s->rng = canon_lcg_next(s->rng); /* one draw, used for both components (LMP.cpp:261-263) */
+        float eps = canon_uniform(s->rng, -.01f, .01f);
+        v2 fuzzy = add2(s->local_goal[i], V2(eps, eps));
+        v2 diff = sub2(fuzzy, o);
+        v2 goal_vel = mul2s(div2s(diff, glm_max(1.0f, len_2(diff))), 1.0f);
+        v2 vi = s->vel[i];
+        v2 goal_F = mul2s(sub2(goal_vel, vi), 2.0f);
+        v2 ttc_F = V2(0.f, 0.f);
+        int cnt = 0;
+        if (s->record_nbrs) s->nbr_ptr[i] = s->nbr_total;
+#define PAIR(j)                                                                           \
+    do {                                                                                  \
+        v2 oj = s->pos[j], vj = s->vel[j];                                                \
+        v2 mm = sub2(oj, o);                                                              \
+        if (dot2(mm, mm) < R * R) s->overlap_pairs++; /* BoundVolume.cpp:203-207 */       \
+        double ttc = (double)ttc_circ_circ(o, vi, oj, vj, R);                             \
+        if (ttc > 5.0) break;                                                             \
+        float tf = (float)ttc;                                                            \
+        v2 dir = sub2(add2(o, V2(vi.x * tf, vi.y * tf)), add2(oj, V2(vj.x * tf, vj.y * tf))); \
+        fcontrib = ttc_forces_(tf, dir);                                                  \
+        hit = 1;                                                                          \
+    } while (0)
+        if (!s->use_grid) {
+            for (int j = 0; j < n; ++j) { /* LMP.cpp:288-304 */
+                if (j == i) continue;
+                v2 fcontrib; int hit = 0;
+                PAIR(j);
+                if (hit) { ttc_F = add2(ttc_F, fcontrib); ++cnt; if (s->record_nbrs) record_nbr(s, j); }
+            }
+        } else {
+            int cx, cy, nh = 0;
+            cell_of(&g_grid, o, &cx, &cy);
+            for (int yy = cy - stencil; yy <= cy + stencil; ++yy) {
+                if (yy < 0 || yy >= g_grid.ny) continue;
+                for (int xx = cx - stencil; xx <= cx + stencil; ++xx) {
+                    if (xx < 0 || xx >= g_grid.nx) continue;
+                    int c = yy * g_grid.nx + xx;
+                    for (int q = s->cell_start[c]; q < s->cell_start[c + 1]; ++q) {
+                        int j = s->cell_items[q];
+                        if (j == i) continue;
+                        v2 fcontrib; int hit = 0;
+                        PAIR(j);
+                        if (hit) {
+                            if (nh == hcap) { hcap = hcap ? 2 * hcap : 256; hits = (hit_t*)realloc(hits, sizeof(hit_t) * (size_t)hcap); }
+                            hits[nh].id = j; hits[nh].f = fcontrib; ++nh;
+                        }
+                    }
+                }
+            }
+            qsort(hits, (size_t)nh, sizeof(hit_t), hit_cmp); /* accumulate in table order */
+            for (int q = 0; q < nh; ++q) { ttc_F = add2(ttc_F, hits[q].f); if (s->record_nbrs) record_nbr(s, hits[q].id); }
+            cnt = nh;
+        }
+#undef PAIR
+        s->nbr_cnt[i] = cnt;
+        v2 f2d = add2(goal_F, ttc_F);
+        s->force[i] = add2(s->force[i], f2d); /* ai.cpp:172 */
+    }
+    if (s->record_nbrs) s->nbr_ptr[n] = s->nbr_total;
+    s->overlap_pairs /= 2;
+    free(hits);
+}
+
+/* ---------- S3: physics::simulate (physics.cpp:23-78), Jacobi collision pass ---------- */
+static inline void push_away(v2* pos, v2* vfh, v2 away) { /* physics.cpp:23-36 (acc is dead afterwards) */
+    float l2 = dot3_xz(away.x, away.y, away.x, away.y);
+    if (l2 > 0.f) {
+        float inv = 1.0f / sqrtf(l2);
+        pos->x += away.x + 0.001f * (away.x * inv);
+        pos->y += away.y + 0.001f * (away.y * inv);
+    }
+    float d = dot3_xz(away.x, away.y, vfh->x, vfh->y);
+    vfh->x += away.x * d;
+    vfh->y += away.y * d;
+}
+
+/* BVH.cpp:106-120 leaf predicate + normal; BoundVolume.cpp:203-211 */
+static inline int circ_circ_hit(v2 pq, v2 pb, float rq, float rb, v2* away) {
+    float r = rq + rb;
+    v2 diff = sub2(pq, pb);
+    if (!(len2_2(diff) < r * r)) return 0;
+    v2 on_q = add2(mul2s(normalize2(sub2(pb, pq)), rq), pq);    /* closest_circ_point(bv->_o, q) */
+    v2 on_bv = add2(mul2s(normalize2(sub2(on_q, pb)), rb), pb); /* closest_circ_point(on_q, bv_circ) */
+    *away = sub2(on_bv, on_q);
+    return 1;
+}
+
+static void physics_simulate(canon_sim* s, float dt) {
+    int n = s->n;
+    /* phase A: leap-frog + clamp + move (physics.cpp:41-51) */
+    for (int i = 0; i < n; ++i) {
+        v2 vbh = s->vfh[i];
+        v2 acc = V2(s->force[i].x / 1.f, s->force[i].y / 1.f);
+        v2 vfh = V2(vbh.x + dt * acc.x, vbh.y + dt * acc.y);
+        if (dot3_xz(vfh.x, vfh.y, vfh.x, vfh.y) > 1.f) {
+            float inv = 1.0f / sqrtf(dot3_xz(vfh.x, vfh.y, vfh.x, vfh.y));
+            vfh = V2(vfh.x * inv, vfh.y * inv);
+        }
+        s->vel[i] = V2(vfh.x / 2.f + vbh.x / 2.f, vfh.y / 2.f + vbh.y / 2.f);
+        s->pos_new[i] = V2(s->pos[i].x + vfh.x * dt, s->pos[i].y + vfh.y * dt);
+        s->vfh[i] = vfh;
+        s->force[i] = V2(0.f, 0.f);
+    }
+    /* phase B: every agent queries all others at their integrated (pre-push) positions, table order
+     * (the reference is Gauss-Seidel in hash-map order through a stale BVH: quirks Q4/Q8, gap measured vs O-ref) */
+    s->coll_hits = 0;
+    float r = s->r;
+    for (int i = 0; i < n; ++i) {
+        v2 p = s->pos_new[i], vfh = s->vfh[i];
+        v2 pq = p;
+        if (!s->use_grid) {
+            for (int j = 0; j < n; ++j) {
+                v2 away;
+                if (j == i) continue;
+                if (circ_circ_hit(pq, s->pos_new[j], r, r, &away)) { push_away(&p, &vfh, away); s->coll_hits++; }
+            }
+        } else {
+            int cx, cy, nh = 0;
+            hit_t hits[64];
+            cell_of(&g_grid, s->pos[i], &cx, &cy); /* grid of start-of-frame positions; moves <= dt */
+            for (int yy = cy - 1; yy <= cy + 1; ++yy) {
+                if (yy < 0 || yy >= g_grid.ny) continue;
+                for (int xx = cx - 1; xx <= cx + 1; ++xx) {
+                    if (xx < 0 || xx >= g_grid.nx) continue;
+                    int c = yy * g_grid.nx + xx;
+                    for (int q = s->cell_start[c]; q < s->cell_start[c + 1]; ++q) {
+                        int j = s->cell_items[q];
+                        v2 away;
+                        if (j == i) continue;
+                        if (circ_circ_hit(pq, s->pos_new[j], r, r, &away)) {
+                            if (nh == 64) { fprintf(stderr, "canon: >64 simultaneous collisions\n"); abort(); }
+                            hits[nh].id = j; hits[nh].f = away; ++nh;
+                        }
+                    }
+                }
+            }
+            qsort(hits, (size_t)nh, sizeof(hit_t), hit_cmp);
+            for (int q = 0; q < nh; ++q) { push_away(&p, &vfh, hits[q].f); s->coll_hits++; }
+        }
+        s->pos[i] = p;
+        s->vfh[i] = vfh;
+        if (!is_done(s, i)) { /* physics.cpp:72-76; vel_count is never incremented (quirk Q6) */
+            float v = (float)0;
+            s->avg_velocity = (s->avg_velocity * v + sqrtf(dot3_xz(s->vel[i].x, s->vel[i].y, s->vel[i].x, s->vel[i].y))) / (v + 1.f);
+        }
+    }
+}
+
+/* ---------- frame loop: main.cpp:98-150 ---------- */
+static void one_frame(canon_sim* s, int free_run) {
+    ++s->frame;
+    int all_done = 0;
+    if (!s->finished) all_done = demo_run(s, s->frame); /* S0 */
+    if (s->comm_enabled) comm_run(s);                   /* S1  (#ifndef NO_COMM) */
+    update_agents(s);                                   /* S2 */
+    physics_simulate(s, 1.f / 60.f);                    /* S3; S4 all_sync is the identity in SoA */
+    if (all_done) s->finished = 1;
+    (void)free_run;
+}
+
+int32_t canon_step(canon_sim* s, int32_t nframes) {
+    int32_t k = 0;
+    while (k < nframes && !s->finished) { one_frame(s, 0); ++k; }
+    return k;
+}
+int32_t canon_step_fixed(canon_sim* s, int32_t nframes) {
+    for (int32_t k = 0; k < nframes; ++k) one_frame(s, 1);
+    return nframes;
+}
+int32_t canon_finished(const canon_sim* s) { return s->finished; }
+uint32_t canon_frame(const canon_sim* s) { return s->frame; }
+
+/* ---------- accessors ---------- */
+void canon_get_state(const canon_sim* s, float* pos, float* vel, float* vfh, float* c, float* facing,
+                     float* local_goal, float* goal_dist, int32_t* num_done) {
+    for (int i = 0; i < s->n; ++i) {
+        if (pos) { pos[2 * i] = s->pos[i].x; pos[2 * i + 1] = s->pos[i].y; }
+        if (vel) { vel[2 * i] = s->vel[i].x; vel[2 * i + 1] = s->vel[i].y; }
+        if (vfh) { vfh[2 * i] = s->vfh[i].x; vfh[2 * i + 1] = s->vfh[i].y; }
+        if (c) { c[3 * i] = s->c[i][0]; c[3 * i + 1] = s->c[i][1]; c[3 * i + 2] = s->c[i][2]; }
+        if (facing) { facing[2 * i] = s->facing[i].x; facing[2 * i + 1] = s->facing[i].y; }
+        if (local_goal) { local_goal[2 * i] = s->local_goal[i].x; local_goal[2 * i + 1] = s->local_goal[i].y; }
+        if (goal_dist) goal_dist[i] = s->goal_dist[i];
+        if (num_done) num_done[i] = s->num_done[i];
+    }
+}
+void canon_set_state(canon_sim* s, const float* pos, const float* vel, const float* vfh, const float* c,
+                     const float* facing, const float* local_goal, const float* goal_dist,
+                     const int32_t* num_done) {
+    for (int i = 0; i < s->n; ++i) {
+        if (pos) s->pos[i] = V2(pos[2 * i], pos[2 * i + 1]);
+        if (vel) s->vel[i] = V2(vel[2 * i], vel[2 * i + 1]);
+        if (vfh) s->vfh[i] = V2(vfh[2 * i], vfh[2 * i + 1]);
+        if (c) { s->c[i][0] = c[3 * i]; s->c[i][1] = c[3 * i + 1]; s->c[i][2] = c[3 * i + 2]; }
+        if (facing) s->facing[i] = V2(facing[2 * i], facing[2 * i + 1]);
+        if (local_goal) s->local_goal[i] = V2(local_goal[2 * i], local_goal[2 * i + 1]);
+        if (goal_dist) s->goal_dist[i] = goal_dist[i];
+        if (num_done) s->num_done[i] = num_done[i];
+    }
+}
+void canon_get_rng(const canon_sim* s, uint32_t* state) { *state = s->rng; }
+void canon_set_rng(canon_sim* s, uint32_t state) { s->rng = state; }
+
+void canon_get_scores(const canon_sim* s, float* avg_velocity, float* group_time, float* run_avg,
+                      float* run_std, int32_t* total_num_done) {
+    if (avg_velocity) *avg_velocity = s->avg_velocity;
+    if (group_time) *group_time = s->run_avg + s->run_std * 3; /* comm.cpp:139 */
+    if (run_avg) *run_avg = s->run_avg;
+    if (run_std) *run_std = s->run_std;
+    if (total_num_done) *total_num_done = s->total_num_done;
+}
+void canon_get_partners(const canon_sim* s, int32_t* partner) { memcpy(partner, s->partner, sizeof(int32_t) * (size_t)s->n); }
+void canon_get_neighbor_counts(const canon_sim* s, int32_t* cnt) { memcpy(cnt, s->nbr_cnt, sizeof(int32_t) * (size_t)s->n); }
+int64_t canon_get_neighbor_lists(const canon_sim* s, int64_t* row_ptr, int32_t* idx) {
+    if (!s->nbr_ptr) return -1;
+    if (row_ptr) memcpy(row_ptr, s->nbr_ptr, sizeof(int64_t) * ((size_t)s->n + 1));
+    if (idx) memcpy(idx, s->nbr_idx, sizeof(int32_t) * (size_t)s->nbr_total);
+    return s->nbr_total;
+}
+int64_t canon_overlap_pairs(const canon_sim* s) { return s->overlap_pairs; }
+int64_t canon_collision_hits(const canon_sim* s) { return s->coll_hits; }
+void canon_record_neighbors(canon_sim* s, int32_t on) { s->record_nbrs = on; }
+
+/* ---------- scene catalogue, wall-free scenes only (demo.cpp:48-104,141-206,356-373) ---------- */
+static const float GLM_PI_F = 3.14159265358979323846264338327950288f; /* glm::pi<float>() */
+
+static v2 radial(unsigned i, unsigned num, float radius) { /* demo.cpp:48-54 */
+    float radian = (float)i / (float)num * 2.f * GLM_PI_F;
+    return V2(radius * cosf(radian), radius * sinf(radian));
+}
+typedef struct { v2 facing, head, spacing; unsigned cols, n; } regiment;
+static v2 right_face(regiment r) { /* demo.cpp:63-65: cross(vec3(facing,0), (0,0,1)).xy */
+    return V2(r.facing.y * 1.f - 0.f * 0.f, 0.f * 0.f - 1.f * r.facing.x);
+}
+static regiment center(regiment r) { /* demo.cpp:66-70 */
+    float half = (r.spacing.x * (float)(r.cols - 1)) / 2.f;
+    r.head = sub2(r.head, mul2s(right_face(r), half));
+    return r;
+}
+static v2 regimented(const regiment* regs, unsigned i) { /* demo.cpp:72-95 */
+    unsigned current = 0, last = regs[0].n, j = i;
+    while (j >= last) { j -= last; last = regs[++current].n; }
+    unsigned col = j % regs[current].cols, row = j / regs[current].cols;
+    float u = regs[current].spacing.x * (float)col, v = regs[current].spacing.y * (float)row;
+    v2 x = mul2s(right_face(regs[current]), u);
+    v2 y = mul2s(V2(-regs[current].facing.x, -regs[current].facing.y), v);
+    return add2(add2(x, y), regs[current].head);
+}
+static int sgnf(float v) { return (0.f < v) - (v < 0.f); }
+static v2 axial_goal(v2 pos) { /* demo.cpp:36-41 */
+    int axis = sgnf(fabsf(pos.x) - fabsf(pos.y));
+    axis = (axis == 0 ? 1 : axis);
+    float faxis = (float)axis;
+    return V2(-faxis * pos.x, faxis * pos.y);
+}
+
+int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration, int32_t cap) {
+    int32_t n = 0;
+    float md = 0.f;
+    switch (scene) {
+    case 0: n = 60; md = 45.f; break;
+    case 1: n = 90; md = 70.f; break;
+    case 4: n = 56; md = 40.f; break;
+    case 5: n = 56; md = 70.f; break;
+    case 12: n = 200; md = 30.f; break;
+    default: return 0; /* walled scenes: not restated yet */
+    }
+    if (n > cap) return -n;
+    *max_duration = md;
+    regiment regs[4];
+    if (scene == 4 || scene == 5) { /* demo.cpp:96-104 make_intersecting_bots(14, 7, 6.f) */
+        float d = 6.f;
+        regiment a = {{1, 0}, {-d, 0}, {1.f, 1.f}, 7, 14}, b = {{-1, 0}, {d, 0}, {1.f, 1.f}, 7, 14};
+        regiment c = {{0, 1}, {0, -d}, {1.f, 1.f}, 7, 14}, e = {{0, -1}, {0, d}, {1.f, 1.f}, 7, 14};
+        regs[0] = center(a); regs[1] = center(b); regs[2] = center(c); regs[3] = center(e);
+    }
+    for (int32_t i = 0; i < n; ++i) {
+        v2 p, g;
+        switch (scene) {
+        case 0: p = radial((unsigned)i, 60, 10.f); g = V2(-p.x, -p.y); break;
+        case 1: p = radial((unsigned)i, 90, 13.f); g = V2(-p.x, -p.y); break;
+        case 4: p = regimented(regs, (unsigned)i); g = axial_goal(p); break;
+        case 5: p = regimented(regs, (unsigned)i); g = V2(-p.x, -p.y); break;
+        default: { /* scene 12, demo.cpp:358-371: glm::vec2(inside(gen), inside(gen)); g++ evaluates the
+                      constructor arguments right to left, so the first draw lands in .y (checked against O-ref) */
+            uint32_t x = *rng_state;
+            x = canon_lcg_next(x); p.y = canon_uniform(x, -10.f, 10.f);
+            x = canon_lcg_next(x); p.x = canon_uniform(x, -10.f, 10.f);
+            x = canon_lcg_next(x); g.y = canon_uniform(x, -10.f, 10.f);
+            x = canon_lcg_next(x); g.x = canon_uniform(x, -10.f, 10.f);
+            *rng_state = x;
+        }
+        }
+        pos[2 * i] = p.x; pos[2 * i + 1] = p.y;
+        goal[2 * i] = g.x; goal[2 * i + 1] = g.y;
+    }
+    return n;
+}
+
+/* ---------- comms.config / comms.result (comm.cpp:74-142; pso_opt.py:17-41) ---------- */
+int32_t canon_read_config(const char* path, float* m_cv, float* m_f) {
+    FILE* f = fopen(path, "r");
+    if (!f) return -1;
+    char line[4096];
+    for (int row = 0; row < 5; ++row) {
+        if (!fgets(line, sizeof line, f)) { fclose(f); return -2; } /* reference: stof("") throws */
+        char* p = line;
+        int ncol = row < 3 ? 8 : 3;
+        for (int col = 0; col < ncol; ++col) {
+            /* std::getline(sl, item, ' ') + std::stof(item): single-space separated tokens */
+            char* e = p;
+            while (*e && *e != ' ' && *e != '\n') ++e;
+            char save = *e;
+            *e = 0;
+            char* endp;
+            float v = strtof(p, &endp);
+            if (endp == p) { fclose(f); return -3; }
+            if (row < 3) m_cv[8 * row + col] = v; else m_f[3 * (row - 3) + col] = v;
+            *e = save;
+            p = (*e == ' ') ? e + 1 : e;
+        }
+    }
+    fclose(f);
+    return 0;
+}
+
+int32_t canon_write_result(const char* path, float avg_velocity, float group_time) {
+    FILE* f = fopen(path, "w");
+    if (!f) return -1;
+    fprintf(f, "%g\n%g\n", (double)avg_velocity, (double)group_time); /* ostream << float: %g, precision 6 */
+    fclose(f);
+    return 0;
+}

@@ -1,0 +1,94 @@
+/* O-canon — CPU restatement of learn-comms' per-frame loop.  TEST INFRASTRUCTURE ONLY.
+ *
+ * This header and canon.c are the parity oracle for the CUDA path.  They are never linked
+ * into, imported by, or executed from the product library (liblearncomms.so); only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load them.
+ *
+ * The algorithm restated is the reference frame loop enginee/src/main.cpp:98-150 with
+ * canonical (ascending agent index) table order, 32-bit ids and a Jacobi collision pass
+ * (SURVEY.md §8c "O-canon").  Every function in canon.c cites the reference file:line it
+ * follows.  Parity status: the reference ships no tests or golden vectors
+ * (enginee/test/PURPOSE), so this oracle is pinned against the reference's own translation
+ * units compiled here (oracle/_ref, see oracle/ref/) — see DESIGN.md §Oracle for the measured
+ * O-canon vs O-ref gap.
+ */
+#ifndef LEARN_COMMS_ORACLE_CANON_H
+#define LEARN_COMMS_ORACLE_CANON_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct canon_sim canon_sim;
+
+/* axis-aligned rectangular wall (demo.cpp:515-537 create_wall; BoundVolume.h Rect) */
+typedef struct { float ox, oy, w, h; } canon_rect;
+
+typedef struct {
+    int32_t n;               /* robots */
+    const float* pos;        /* [n][2] initial (x,z) */
+    const float* goal;       /* [n][2] final_goal */
+    float radius;            /* 0.15 (demo.cpp:540,552) */
+    float max_duration;      /* Scene::max_duration */
+    uint32_t rng_state;      /* minstd_rand0 state BEFORE the first per-frame draw */
+    const float* m_cv;       /* [3][8] row-major  (comm.cpp:124-131) */
+    const float* m_f;        /* [2][3] row-major  (comm.cpp:112-121) */
+    int32_t comm_enabled;    /* 0 = nocomm_norender flavour (main.cpp:130-132) */
+    int32_t use_grid;        /* 0 = brute-force all pairs (reference), 1 = uniform-grid search (same result) */
+    int32_t n_walls;         /* static Rect obstacles (0 in wall-free scenes) */
+    const canon_rect* walls;
+} canon_desc;
+
+canon_sim* canon_create(const canon_desc* d);
+void canon_destroy(canon_sim* s);
+
+/* run `nframes` frames of main.cpp:98-150 (S0..S4).  Stops early once demo::run reported
+ * all_done (the frame in which it is reported still executes S1..S4, as in the reference).
+ * Returns the number of frames executed. */
+int32_t canon_step(canon_sim* s, int32_t nframes);
+/* run exactly nframes without the all_done latch ever stopping the dynamics (fixed-step benchmarks);
+ * scoring still latches at the first all_done. */
+int32_t canon_step_fixed(canon_sim* s, int32_t nframes);
+int32_t canon_finished(const canon_sim* s);
+uint32_t canon_frame(const canon_sim* s);
+
+/* state access (teacher forcing).  Arrays are [n][2] except c [n][3]; any pointer may be NULL. */
+void canon_get_state(const canon_sim* s, float* pos, float* vel, float* vel_forehalf, float* c,
+                     float* facing, float* local_goal, float* goal_dist, int32_t* num_done);
+void canon_set_state(canon_sim* s, const float* pos, const float* vel, const float* vel_forehalf,
+                     const float* c, const float* facing, const float* local_goal,
+                     const float* goal_dist, const int32_t* num_done);
+void canon_get_rng(const canon_sim* s, uint32_t* state);
+void canon_set_rng(canon_sim* s, uint32_t state);
+
+/* scores: comm.cpp:136-142 (avg_velocity, run_avg_time + 3*run_std_time) + demo.cpp:650-663 */
+void canon_get_scores(const canon_sim* s, float* avg_velocity, float* group_time, float* run_avg,
+                      float* run_std, int32_t* total_num_done);
+
+/* diagnostics of the LAST executed frame */
+void canon_get_partners(const canon_sim* s, int32_t* partner);               /* [n] comm.cpp:201-220 */
+void canon_get_neighbor_counts(const canon_sim* s, int32_t* cnt);            /* [n] |{j : ttc_ij <= 5}| */
+/* neighbour lists, CSR; returns total; pass idx=NULL to query the size */
+int64_t canon_get_neighbor_lists(const canon_sim* s, int64_t* row_ptr, int32_t* idx);
+int64_t canon_overlap_pairs(const canon_sim* s);   /* unordered pairs overlapping at frame start */
+int64_t canon_collision_hits(const canon_sim* s);  /* ordered (q,bv) hits in physics::simulate */
+void canon_record_neighbors(canon_sim* s, int32_t on);
+
+/* RNG restatement (Seeder.cpp:5-20 + libstdc++ minstd_rand0 / uniform_real_distribution<float>) */
+uint32_t canon_lcg_next(uint32_t x);
+uint32_t canon_lcg_seed(uint64_t seed);
+float canon_uniform(uint32_t x_after_draw, float a, float b);
+
+/* scene catalogue (demo.cpp:141-511): fills pos/goal for wall-free scenes; returns n (0 = unsupported).
+ * rng_state is advanced by construction-time draws (scene 12). */
+int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration,
+                    int32_t cap);
+
+/* config / result files (comm.cpp:74-142, pso_opt.py:17-41) */
+int32_t canon_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);
+int32_t canon_write_result(const char* path, float avg_velocity, float group_time);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
