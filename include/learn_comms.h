@@ -1,0 +1,130 @@
+/* learn_comms.h — C ABI of the B200-native learn-comms hot path (liblearncomms.so).
+ *
+ * The reference (daltonhildreth/learn-comms) has no FFI: the path is reached through the process-global
+ * system functions that enginee/src/main.cpp:98-150 calls every frame.  Each entry point below names the
+ * reference interface it replaces.  Plain pointers and sizes only; no exceptions cross this boundary;
+ * every function returns 0 on success or a negative lc_status, with lc_last_error() giving the text.
+ * A handle is confined to one host thread at a time; distinct handles may be used concurrently.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with LC_ERR_CUDA.
+ *
+ * Array conventions: agent arrays are in agent-id (creation) order; vec2 arrays are [n][2] = (x, z).
+ */
+#ifndef LEARN_COMMS_H
+#define LEARN_COMMS_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    LC_OK = 0,
+    LC_ERR_ARG = -1,      /* bad argument (reference: assert / exit(1), io.cpp:42-45) */
+    LC_ERR_CUDA = -2,     /* CUDA runtime error / no device */
+    LC_ERR_STATE = -3,    /* simulation reached a state the reference treats as UB (e.g. no comm partner, comm.cpp:273-285) */
+    LC_ERR_IO = -4,       /* config / result file error (comm.cpp:78,92) */
+    LC_ERR_CAPACITY = -5  /* an internal fixed-capacity buffer overflowed */
+} lc_status;
+
+/* flags for lc_desc.flags */
+#define LC_FLAG_NO_COMM 1u        /* nocomm_* executables: comm::run is compiled out (main.cpp:130-132) */
+#define LC_FLAG_FREE_RUN 2u       /* keep stepping the dynamics after demo::run reported all_done (fixed-step benchmarks) */
+#define LC_FLAG_DEBUG_LISTS 4u    /* record per-agent neighbour lists {j : ttc_ij <= 5} each frame (parity tests) */
+
+typedef struct lc_rect { float ox, oy, w, h; } lc_rect; /* BoundVolume.h Rect: origin (centre), width, height */
+
+/* Scene description: replaces demo::init + ai::init + physics::init/prewarm (demo.cpp:611-648, ai.cpp:24-129,
+ * physics.cpp:13-21).  All pointers are HOST pointers, copied during the call. */
+typedef struct lc_desc {
+    int32_t n;              /* robots, >= 2 (comm.cpp:273-285: n == 1 is UB in the reference) */
+    const float* pos;       /* [n][2] initial positions   (Scene::pos_of, demo.cpp:630-632) */
+    const float* goal;      /* [n][2] final goals         (Scene::goal_of, demo.cpp:572) */
+    float radius;           /* robot radius, reference 0.15 (demo.cpp:540,552) */
+    float max_duration;     /* Scene::max_duration, seconds of simulated time */
+    uint32_t rng_state;     /* minstd_rand0 state before the first per-frame draw (Seeder.cpp:15-18; LMP.cpp:261-263) */
+    const float* m_cv;      /* [3][8] row-major comm matrix M_cv (comm.cpp:124-131); NULL = zeros */
+    const float* m_f;       /* [2][3] row-major force matrix M_f (comm.cpp:112-121); NULL = zeros */
+    uint32_t flags;
+    int32_t device;         /* CUDA device ordinal */
+    int32_t n_walls;        /* reserved for walled scenes; must be 0 */
+    const lc_rect* walls;
+    int32_t stencil;        /* grid cells per interaction cutoff (0 = default 1): cell side = cutoff / stencil */
+} lc_desc;
+
+typedef struct lc_sim lc_sim;
+
+/* ---- single crowd: one simulation resident on one GPU ---- */
+int32_t lc_create(const lc_desc* desc, lc_sim** out);
+void lc_destroy(lc_sim* sim);
+/* comm::init's parameter load (comm.cpp:80-131) from memory */
+int32_t lc_set_weights(lc_sim* sim, const float* m_cv, const float* m_f);
+/* nframes iterations of the frame loop main.cpp:98-150: demo::run -> comm::run -> ai::update_agents ->
+ * physics::simulate -> POOL.all_sync.  Asynchronous; frames after all_done are no-ops unless LC_FLAG_FREE_RUN. */
+int32_t lc_step(lc_sim* sim, int32_t nframes);
+/* the whole while(!all_done) loop (main.cpp:98); returns the number of frames executed */
+int32_t lc_run_to_completion(lc_sim* sim, int32_t* frames);
+int32_t lc_sync(lc_sim* sim);
+int32_t lc_finished(lc_sim* sim, int32_t* finished, uint32_t* frame);
+
+/* state exchange with the host engine's component tables (Dynamics.h, Agent.h, CommComp.h); HOST pointers, any may be NULL.
+ * get = what POOL.all_sync publishes (Pool.cpp:69-91); set = teacher forcing / a host engine that owns the state. */
+int32_t lc_get_state(lc_sim* sim, float* pos, float* vel, float* vel_forehalf, float* c, float* facing,
+                     float* local_goal, float* goal_dist, int32_t* num_done);
+int32_t lc_set_state(lc_sim* sim, const float* pos, const float* vel, const float* vel_forehalf, const float* c,
+                     const float* facing, const float* local_goal, const float* goal_dist, const int32_t* num_done);
+int32_t lc_set_rng(lc_sim* sim, uint32_t rng_state);
+int32_t lc_get_rng(lc_sim* sim, uint32_t* rng_state);
+
+/* comm::terminate's two numbers (comm.cpp:136-142) + demo's running statistics (demo.cpp:650-663) */
+int32_t lc_get_scores(lc_sim* sim, float* avg_velocity, float* group_time, float* run_avg, float* run_std,
+                      int32_t* total_num_done);
+
+/* diagnostics of the last executed frame (parity tests) */
+int32_t lc_get_partners(lc_sim* sim, int32_t* partner);         /* [n] select_nearest result, comm.cpp:201-220 */
+int32_t lc_get_neighbor_counts(lc_sim* sim, int32_t* count);    /* [n] |{j : ttc_ij <= 5}|, LMP.cpp:297-300 */
+int32_t lc_get_neighbor_lists(lc_sim* sim, int32_t* idx, int32_t cap_per_agent); /* [n][cap], ascending id; needs LC_FLAG_DEBUG_LISTS */
+int32_t lc_get_counters(lc_sim* sim, int64_t* overlap_pairs, int64_t* collision_hits, int64_t* candidates);
+
+/* timing on the simulation's own stream (CUDA events) */
+int32_t lc_timer_start(lc_sim* sim);
+int32_t lc_timer_stop(lc_sim* sim, float* milliseconds);
+int64_t lc_kernel_launches(lc_sim* sim); /* kernels launched by this handle so far */
+
+/* ---- batched rollouts: many independent small scenarios / PSO particles in one launch ----
+ * replaces pso_opt.py:236-267 simulate_set/simulate (one comm_norender process per (particle, scene)). */
+typedef struct lc_batch lc_batch;
+typedef struct lc_batch_desc {
+    int32_t n_scenarios;
+    int32_t n_agents;         /* agents per scenario (<= 256), identical for all scenarios */
+    const float* pos;         /* [S][n][2] */
+    const float* goal;        /* [S][n][2] */
+    const float* m_cv;        /* [S][3][8] per-scenario comm matrices */
+    const float* m_f;         /* [S][2][3] */
+    const float* max_duration;/* [S] */
+    const uint32_t* rng_state;/* [S] */
+    float radius;
+    uint32_t flags;
+    int32_t device;
+} lc_batch_desc;
+int32_t lc_batch_create(const lc_batch_desc* desc, lc_batch** out);
+void lc_batch_destroy(lc_batch* b);
+/* run every scenario to completion (or max_frames); outputs are HOST arrays [S] (any may be NULL) */
+int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float* group_time, int32_t* n_done,
+                     int32_t* frames);
+int32_t lc_batch_get_state(lc_batch* b, float* pos, float* vel, float* c);
+int32_t lc_batch_timer(lc_batch* b, float* milliseconds); /* device time of the last lc_batch_run */
+
+/* ---- files: comm::init / comm::terminate formats (comm.cpp:74-142, pso_opt.py:17-41) ---- */
+int32_t lc_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);
+int32_t lc_write_result(const char* path, float avg_velocity, float group_time);
+
+/* ---- scene catalogue (demo.cpp:141-511), wall-free scenes; returns agent count or negative status ---- */
+int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
+                 uint32_t* rng_state_after);
+
+const char* lc_last_error(void);
+const char* lc_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

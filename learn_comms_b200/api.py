@@ -1,0 +1,295 @@
+"""ctypes binding of liblearncomms.so.  Mirrors the reference's system interface for the hot path:
+Sim.step() == one iteration of enginee/src/main.cpp:98-150; Sim.scores() == comm::terminate's two numbers."""
+import ctypes as C
+import os
+import numpy as np
+
+from . import build as _build
+
+FLAG_NO_COMM, FLAG_FREE_RUN, FLAG_DEBUG_LISTS = 1, 2, 4
+_LIB = None
+
+
+class LcError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"learn_comms error {code}: {msg}")
+        self.code = code
+
+
+class _Desc(C.Structure):
+    _fields_ = [("n", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p), ("radius", C.c_float),
+                ("max_duration", C.c_float), ("rng_state", C.c_uint32), ("m_cv", C.c_void_p), ("m_f", C.c_void_p),
+                ("flags", C.c_uint32), ("device", C.c_int32), ("n_walls", C.c_int32), ("walls", C.c_void_p),
+                ("stencil", C.c_int32)]
+
+
+class _BatchDesc(C.Structure):
+    _fields_ = [("n_scenarios", C.c_int32), ("n_agents", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p),
+                ("m_cv", C.c_void_p), ("m_f", C.c_void_p), ("max_duration", C.c_void_p), ("rng_state", C.c_void_p),
+                ("radius", C.c_float), ("flags", C.c_uint32), ("device", C.c_int32)]
+
+
+EXPORTS = [
+    "lc_create", "lc_destroy", "lc_set_weights", "lc_step", "lc_run_to_completion", "lc_sync", "lc_finished",
+    "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
+    "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
+    "lc_kernel_launches", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
+    "lc_batch_timer", "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
+]
+
+
+def lib():
+    """Load (building if stale) the CUDA library.  Raises if it cannot be built/loaded: no fallback."""
+    global _LIB
+    if _LIB is None:
+        path = _build.build()
+        L = C.CDLL(path)
+        vp, i32, u32, f32p = C.c_void_p, C.c_int32, C.c_uint32, C.POINTER(C.c_float)
+        L.lc_create.argtypes = [C.POINTER(_Desc), C.POINTER(vp)]
+        L.lc_destroy.argtypes = [vp]
+        L.lc_destroy.restype = None
+        L.lc_set_weights.argtypes = [vp, vp, vp]
+        L.lc_step.argtypes = [vp, i32]
+        L.lc_run_to_completion.argtypes = [vp, C.POINTER(i32)]
+        L.lc_sync.argtypes = [vp]
+        L.lc_finished.argtypes = [vp, C.POINTER(i32), C.POINTER(u32)]
+        L.lc_get_state.argtypes = [vp] + [vp] * 8
+        L.lc_set_state.argtypes = [vp] + [vp] * 8
+        L.lc_set_rng.argtypes = [vp, u32]
+        L.lc_get_rng.argtypes = [vp, C.POINTER(u32)]
+        L.lc_get_scores.argtypes = [vp, f32p, f32p, f32p, f32p, C.POINTER(i32)]
+        L.lc_get_partners.argtypes = [vp, vp]
+        L.lc_get_neighbor_counts.argtypes = [vp, vp]
+        L.lc_get_neighbor_lists.argtypes = [vp, vp, i32]
+        L.lc_get_counters.argtypes = [vp] + [C.POINTER(C.c_int64)] * 3
+        L.lc_timer_start.argtypes = [vp]
+        L.lc_timer_stop.argtypes = [vp, f32p]
+        L.lc_kernel_launches.argtypes = [vp]
+        L.lc_kernel_launches.restype = C.c_int64
+        L.lc_batch_create.argtypes = [C.POINTER(_BatchDesc), C.POINTER(vp)]
+        L.lc_batch_destroy.argtypes = [vp]
+        L.lc_batch_destroy.restype = None
+        L.lc_batch_run.argtypes = [vp, i32, vp, vp, vp, vp]
+        L.lc_batch_get_state.argtypes = [vp, vp, vp, vp]
+        L.lc_batch_timer.argtypes = [vp, f32p]
+        L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
+        L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
+        L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
+        L.lc_last_error.restype = C.c_char_p
+        L.lc_version.restype = C.c_char_p
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _ck(rc):
+    if rc != 0:
+        raise LcError(rc, lib().lc_last_error().decode())
+
+
+def scene(scene_id, seed=0):
+    """demo::init's scene catalogue (demo.cpp:141-511), wall-free scenes.  Returns pos, goal, max_duration, rng_state."""
+    pos = np.zeros((4096, 2), np.float32)
+    goal = np.zeros((4096, 2), np.float32)
+    md, rng = C.c_float(0), C.c_uint32(0)
+    n = lib().lc_scene(scene_id, seed, _p(pos), _p(goal), 4096, C.byref(md), C.byref(rng))
+    if n <= 0:
+        raise LcError(n, f"scene {scene_id} is not in the wall-free catalogue")
+    return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value)
+
+
+def read_config(path):
+    m_cv, m_f = np.zeros((3, 8), np.float32), np.zeros((2, 3), np.float32)
+    rc = lib().lc_read_config(os.fsencode(path), _p(m_cv), _p(m_f))
+    if rc:
+        raise LcError(rc, f"cannot parse {path} (comm.cpp:80-121 format: 5 lines x 8 floats)")
+    return m_cv, m_f
+
+
+def write_result(path, avg_velocity, group_time):
+    rc = lib().lc_write_result(os.fsencode(path), avg_velocity, group_time)
+    if rc:
+        raise LcError(rc, f"cannot write {path}")
+
+
+_STATE_KEYS = ("pos", "vel", "vfh", "c", "facing", "local_goal", "goal_dist", "num_done")
+
+
+class Sim:
+    """One crowd resident on one GPU.  step(k) runs k frames of main.cpp:98-150."""
+
+    def __init__(self, pos, goal, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15, comm=True,
+                 free_run=False, debug_lists=False, device=0, stencil=0):
+        self.n = int(pos.shape[0])
+        pos = np.ascontiguousarray(pos, np.float32)
+        goal = np.ascontiguousarray(goal, np.float32)
+        m_cv = None if m_cv is None else np.ascontiguousarray(m_cv, np.float32)
+        m_f = None if m_f is None else np.ascontiguousarray(m_f, np.float32)
+        flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0) | (FLAG_DEBUG_LISTS if debug_lists else 0)
+        d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0,
+                  None, stencil)
+        h = C.c_void_p()
+        self.h = None
+        _ck(lib().lc_create(C.byref(d), C.byref(h)))
+        self.h = h
+        self.list_cap = min(self.n - 1, 256) if debug_lists else 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().lc_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def set_weights(self, m_cv, m_f):
+        m_cv = np.ascontiguousarray(m_cv, np.float32)
+        m_f = np.ascontiguousarray(m_f, np.float32)
+        _ck(lib().lc_set_weights(self.h, _p(m_cv), _p(m_f)))
+
+    def step(self, n=1, sync=True):
+        _ck(lib().lc_step(self.h, n))
+        if sync:
+            _ck(lib().lc_sync(self.h))
+
+    def sync(self):
+        _ck(lib().lc_sync(self.h))
+
+    def run_to_completion(self):
+        k = C.c_int32(0)
+        _ck(lib().lc_run_to_completion(self.h, C.byref(k)))
+        return int(k.value)
+
+    @property
+    def finished(self):
+        f, k = C.c_int32(0), C.c_uint32(0)
+        _ck(lib().lc_finished(self.h, C.byref(f), C.byref(k)))
+        return bool(f.value)
+
+    @property
+    def frame(self):
+        f, k = C.c_int32(0), C.c_uint32(0)
+        _ck(lib().lc_finished(self.h, C.byref(f), C.byref(k)))
+        return int(k.value)
+
+    def state(self, keys=_STATE_KEYS, out=None):
+        n = self.n
+        shapes = dict(pos=(n, 2), vel=(n, 2), vfh=(n, 2), c=(n, 3), facing=(n, 2), local_goal=(n, 2), goal_dist=(n,),
+                      num_done=(n,))
+        out = {} if out is None else out
+        for k in keys:
+            if k not in out:
+                out[k] = np.zeros(shapes[k], np.int32 if k == "num_done" else np.float32)
+        _ck(lib().lc_get_state(self.h, *[_p(out.get(k)) if k in keys else None for k in _STATE_KEYS]))
+        return out
+
+    def set_state(self, **kw):
+        arrs = []
+        for k in _STATE_KEYS:
+            a = kw.get(k)
+            if a is not None:
+                a = np.ascontiguousarray(a, np.int32 if k == "num_done" else np.float32)
+            arrs.append(a)
+        _ck(lib().lc_set_state(self.h, *[_p(a) for a in arrs]))
+        _ck(lib().lc_sync(self.h))
+
+    @property
+    def rng(self):
+        v = C.c_uint32(0)
+        _ck(lib().lc_get_rng(self.h, C.byref(v)))
+        return int(v.value)
+
+    @rng.setter
+    def rng(self, v):
+        _ck(lib().lc_set_rng(self.h, v))
+
+    def scores(self):
+        a, g, u, s = C.c_float(), C.c_float(), C.c_float(), C.c_float()
+        k = C.c_int32()
+        _ck(lib().lc_get_scores(self.h, C.byref(a), C.byref(g), C.byref(u), C.byref(s), C.byref(k)))
+        return dict(avg_velocity=a.value, group_time=g.value, run_avg=u.value, run_std=s.value, n_done=k.value)
+
+    def partners(self):
+        p = np.zeros(self.n, np.int32)
+        _ck(lib().lc_get_partners(self.h, _p(p)))
+        return p
+
+    def neighbor_counts(self):
+        p = np.zeros(self.n, np.int32)
+        _ck(lib().lc_get_neighbor_counts(self.h, _p(p)))
+        return p
+
+    def neighbor_lists(self):
+        """CSR (row_ptr, idx) of {j : ttc_ij <= 5} for the last frame; needs debug_lists=True."""
+        cnt = self.neighbor_counts()
+        assert cnt.max(initial=0) <= self.list_cap, "neighbour list capacity exceeded"
+        dense = np.zeros((self.n, self.list_cap), np.int32)
+        _ck(lib().lc_get_neighbor_lists(self.h, _p(dense), self.list_cap))
+        ptr = np.zeros(self.n + 1, np.int64)
+        np.cumsum(cnt, out=ptr[1:])
+        idx = np.concatenate([dense[i, :cnt[i]] for i in range(self.n)]) if self.n else np.zeros(0, np.int32)
+        return ptr, idx.astype(np.int32)
+
+    def counters(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        _ck(lib().lc_get_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(overlap_pairs=a.value, collision_hits=b.value, candidates=c.value)
+
+    def timer_start(self):
+        _ck(lib().lc_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        _ck(lib().lc_timer_stop(self.h, C.byref(ms)))
+        return float(ms.value)
+
+    @property
+    def launches(self):
+        return int(lib().lc_kernel_launches(self.h))
+
+
+class Batch:
+    """Many independent small scenarios in one launch (pso_opt.py:236-267 simulate_set, in process)."""
+
+    def __init__(self, pos, goal, m_cv, m_f, max_duration, rng_state, radius=0.15, comm=True, device=0):
+        S, n = pos.shape[0], pos.shape[1]
+        self.S, self.n = int(S), int(n)
+        self._keep = [np.ascontiguousarray(pos, np.float32), np.ascontiguousarray(goal, np.float32),
+                      np.ascontiguousarray(m_cv, np.float32), np.ascontiguousarray(m_f, np.float32),
+                      np.ascontiguousarray(np.broadcast_to(np.asarray(max_duration, np.float32), (S,))),
+                      np.ascontiguousarray(np.broadcast_to(np.asarray(rng_state, np.uint32), (S,)))]
+        assert self._keep[2].shape == (S, 3, 8) and self._keep[3].shape == (S, 2, 3)
+        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, 0 if comm else FLAG_NO_COMM, device)
+        h = C.c_void_p()
+        self.h = None
+        _ck(lib().lc_batch_create(C.byref(d), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().lc_batch_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def run(self, max_frames=1 << 30):
+        S = self.S
+        out = dict(avg_velocity=np.zeros(S, np.float32), group_time=np.zeros(S, np.float32),
+                   n_done=np.zeros(S, np.int32), frames=np.zeros(S, np.int32))
+        _ck(lib().lc_batch_run(self.h, max_frames, _p(out["avg_velocity"]), _p(out["group_time"]), _p(out["n_done"]),
+                               _p(out["frames"])))
+        return out
+
+    def state(self):
+        pos = np.zeros((self.S, self.n, 2), np.float32)
+        vel = np.zeros((self.S, self.n, 2), np.float32)
+        c = np.zeros((self.S, self.n, 3), np.float32)
+        _ck(lib().lc_batch_get_state(self.h, _p(pos), _p(vel), _p(c)))
+        return dict(pos=pos, vel=vel, c=c)
+
+    def device_ms(self):
+        ms = C.c_float()
+        _ck(lib().lc_batch_timer(self.h, C.byref(ms)))
+        return float(ms.value)

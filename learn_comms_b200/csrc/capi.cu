@@ -1,0 +1,444 @@
+// C ABI of liblearncomms.so (include/learn_comms.h): handle management, host<->device plumbing, CUDA-graph
+// replay of the frame.  No compute happens on the host: every entry point that advances or reads the
+// simulation fails with LC_ERR_CUDA when no CUDA device is usable.
+#include "../../include/learn_comms.h"
+#include "crowd.cuh"
+#include "lc_math.cuh"
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(LC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+uint32_t lcg_pow(uint32_t a, uint64_t e) {
+    uint32_t r = 1;
+    while (e) {
+        if (e & 1) r = lcm::lcg_mul(r, a);
+        a = lcm::lcg_mul(a, a);
+        e >>= 1;
+    }
+    return r;
+}
+
+template <class T> cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, sizeof(T) * (count ? count : 1)); }
+
+}  // namespace
+
+struct lc_sim {
+    lc::Params hp{};
+    lc::Params* dP = nullptr;
+    lc::Buffers b{};
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaGraphExec_t gexec[2] = {nullptr, nullptr};  // 1 frame, GRAPH_BATCH frames
+    long long launches = 0;
+    int device = 0;
+    int n = 0;
+    uint32_t rng0 = 1;   // stream state before frame 1's first draw
+    // staging (device) for state exchange, pinned host mirror of Ctl
+    float* stage = nullptr;
+    size_t stage_floats = 0;
+    lc::Ctl* hctl = nullptr;
+    std::vector<void*> allocs;
+};
+
+static const int GRAPH_BATCH = 16;
+
+static int alloc_arrays(lc_sim* s, lc::AgentArrays& a, int n) {
+    CK(dalloc(&a.pv, n)); s->allocs.push_back(a.pv);
+    CK(dalloc(&a.vfh, n)); s->allocs.push_back(a.vfh);
+    CK(dalloc(&a.goal, n)); s->allocs.push_back(a.goal);
+    CK(dalloc(&a.lgoal, n)); s->allocs.push_back(a.lgoal);
+    CK(dalloc(&a.facing, n)); s->allocs.push_back(a.facing);
+    CK(dalloc(&a.c4, n)); s->allocs.push_back(a.c4);
+    CK(dalloc(&a.meta, n)); s->allocs.push_back(a.meta);
+    return 0;
+}
+
+static int build_graphs(lc_sim* s) {
+    for (int g = 0; g < 2; ++g) {
+        int frames = g == 0 ? 1 : GRAPH_BATCH;
+        cudaGraph_t graph;
+        CK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
+        for (int f = 0; f < frames; ++f) lc::launch_frame(s->dP, s->n, s->b, s->st, nullptr);
+        CK(cudaStreamEndCapture(s->st, &graph));
+        CK(cudaGraphInstantiate(&s->gexec[g], graph, 0));
+        CK(cudaGraphDestroy(graph));
+    }
+    return 0;
+}
+
+static int upload_params(lc_sim* s) {
+    CK(cudaMemcpyAsync(s->dP, &s->hp, sizeof(lc::Params), cudaMemcpyHostToDevice, s->st));
+    return 0;
+}
+
+static int read_ctl(lc_sim* s) {
+    CK(cudaMemcpyAsync(s->hctl, s->b.ctl, sizeof(lc::Ctl), cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return 0;
+}
+
+extern "C" {
+
+const char* lc_last_error(void) { return g_err.c_str(); }
+const char* lc_version(void) { return "learn_comms_b200 0.1 (sm_100a)"; }
+
+void lc_destroy(lc_sim* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->st) cudaStreamSynchronize(s->st);
+    for (auto& g : s->gexec) if (g) cudaGraphExecDestroy(g);
+    for (void* p : s->allocs) cudaFree(p);
+    if (s->dP) cudaFree(s->dP);
+    if (s->stage) cudaFree(s->stage);
+    if (s->hctl) cudaFreeHost(s->hctl);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->st) cudaStreamDestroy(s->st);
+    delete s;
+}
+
+int32_t lc_create(const lc_desc* d, lc_sim** out) {
+    if (!d || !out) return fail(LC_ERR_ARG, "lc_create: null argument");
+    *out = nullptr;
+    if (d->n < 2) return fail(LC_ERR_ARG, "lc_create: n must be >= 2 (the reference dereferences a null comm partner for n == 1, comm.cpp:273-285)");
+    if (!d->pos || !d->goal) return fail(LC_ERR_ARG, "lc_create: pos/goal are required");
+    if (d->n_walls != 0) return fail(LC_ERR_ARG, "lc_create: walled scenes are not supported yet");
+    if (!(d->radius > 0.f)) return fail(LC_ERR_ARG, "lc_create: radius must be positive");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(LC_ERR_CUDA, "lc_create: no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    if (d->device < 0 || d->device >= ndev) return fail(LC_ERR_ARG, "lc_create: device %d out of range", d->device);
+    CK(cudaSetDevice(d->device));
+    lc_sim* s = new lc_sim;
+    s->device = d->device;
+    const int n = s->n = d->n;
+    int rc = 0;
+    auto bail = [&](int code) { lc_destroy(s); return code; };
+#define CKB(x) do { rc = (x); if (rc) return bail(rc); } while (0)
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(LC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); return bail(LC_ERR_CUDA); } } while (0)
+    CKC(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
+    CKC(cudaEventCreate(&s->ev0));
+    CKC(cudaEventCreate(&s->ev1));
+    CKB(alloc_arrays(s, s->b.cur, n));
+    CKB(alloc_arrays(s, s->b.srt, n));
+    lc::Buffers& b = s->b;
+    CKC(dalloc(&b.posf, n)); s->allocs.push_back(b.posf);
+    CKC(dalloc(&b.cellrank, n)); s->allocs.push_back(b.cellrank);
+    CKC(dalloc(&b.cell_count, lc::CELL_CAP + 1)); s->allocs.push_back(b.cell_count);
+    CKC(dalloc(&b.cell_start, lc::CELL_CAP + 1)); s->allocs.push_back(b.cell_start);
+    CKC(dalloc(&b.slot_of_id, n)); s->allocs.push_back(b.slot_of_id);
+    CKC(dalloc(&b.cand, n)); s->allocs.push_back(b.cand);
+    CKC(dalloc(&b.near_cnt, n)); s->allocs.push_back(b.near_cnt);
+    CKC(dalloc(&b.near_idx, (size_t)n * lc::MAX_NEAR)); s->allocs.push_back(b.near_idx);
+    CKC(dalloc(&b.events, n)); s->allocs.push_back(b.events);
+    CKC(dalloc(&b.ev_by_id, n)); s->allocs.push_back(b.ev_by_id);
+    CKC(dalloc(&b.partner_id, n)); s->allocs.push_back(b.partner_id);
+    CKC(dalloc(&b.nbr_cnt, n)); s->allocs.push_back(b.nbr_cnt);
+    b.list_cap = 0;
+    b.nbr_list = nullptr;
+    if (d->flags & LC_FLAG_DEBUG_LISTS) {
+        b.list_cap = n - 1 < 256 ? n - 1 : 256;
+        CKC(dalloc(&b.nbr_list, (size_t)n * b.list_cap)); s->allocs.push_back(b.nbr_list);
+        CKC(cudaMemset(b.nbr_list, 0xff, sizeof(int) * (size_t)n * b.list_cap));
+    }
+    CKC(dalloc(&b.ctl, 1)); s->allocs.push_back(b.ctl);
+    CKC(cudaMemset(b.ctl, 0, sizeof(lc::Ctl)));
+    CKC(cudaMemset(b.partner_id, 0xff, sizeof(int) * n));
+    CKC(cudaMemset(b.nbr_cnt, 0, sizeof(int) * n));
+    CKC(cudaMemset(b.near_cnt, 0, sizeof(int) * n));
+    CKC(cudaMalloc((void**)&s->dP, sizeof(lc::Params)));
+    CKC(cudaMallocHost((void**)&s->hctl, sizeof(lc::Ctl)));
+    s->stage_floats = (size_t)n * 16;
+    CKC(cudaMalloc((void**)&s->stage, sizeof(float) * s->stage_floats));
+
+    lc::Params& P = s->hp;
+    P.n = n;
+    P.r = d->radius;
+    P.R = d->radius + d->radius;       // LMP.cpp:53 i._r + j._r
+    P.RR = P.R * P.R;                  // BoundVolume.cpp:106 _r * _r
+    {   // pairs that can overlap after this frame's move: both agents travel <= dt (|vel_forehalf| <= 1 after the clamp)
+        float reach = P.R + 2.f * (1.f / 60.f) * 1.01f + 0.002f;
+        P.near_c = reach * reach - P.RR;
+    }
+    P.max_duration = d->max_duration;
+    P.lcg_stride = lcg_pow(16807u, (uint64_t)n);
+    P.flags = d->flags;
+    P.stencil_req = d->stencil > 0 ? d->stencil : 1;
+    memset(P.m_cv, 0, sizeof P.m_cv);
+    memset(P.m_f, 0, sizeof P.m_f);
+    if (d->m_cv) memcpy(P.m_cv, d->m_cv, sizeof P.m_cv);
+    if (d->m_f) memcpy(P.m_f, d->m_f, sizeof P.m_f);
+    CKB(upload_params(s));
+    lc::upload_dirs();
+
+    // initial component values: demo.cpp:563-581 create_robo, ai.cpp:107-127 ai::init, physics.cpp:15-21 prewarm
+    {
+        std::vector<float> h((size_t)n * 9);
+        float* facing = h.data();           // [n][2]
+        float* gd = h.data() + 2 * (size_t)n;   // [n]
+        float* mt = h.data() + 3 * (size_t)n;   // [n]
+        for (int i = 0; i < n; ++i) {
+            float dx = d->goal[2 * i] - d->pos[2 * i], dy = d->goal[2 * i + 1] - d->pos[2 * i + 1];
+            facing[2 * i] = dx; facing[2 * i + 1] = dy;      // un-normalised (demo.cpp:580)
+            float len = sqrtf(dx * dx + dy * dy);            // glm::length (ai.cpp:116)
+            gd[i] = len;
+            float m = -1.0f;                                  // ai.cpp:121-126
+            m += len;
+            mt[i] = m;
+        }
+        float* dpos = s->stage;
+        float* dgoal = s->stage + 2 * (size_t)n;
+        float* dfacing = s->stage + 4 * (size_t)n;
+        float* dgd = s->stage + 6 * (size_t)n;
+        float* dmt = s->stage + 7 * (size_t)n;
+        CKC(cudaMemcpyAsync(dpos, d->pos, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+        CKC(cudaMemcpyAsync(dgoal, d->goal, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+        CKC(cudaMemcpyAsync(dfacing, facing, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+        CKC(cudaMemcpyAsync(dgd, gd, sizeof(float) * n, cudaMemcpyHostToDevice, s->st));
+        CKC(cudaMemcpyAsync(dmt, mt, sizeof(float) * n, cudaMemcpyHostToDevice, s->st));
+        lc::launch_set_state(s->dP, n, b, (const float2*)dpos, nullptr, nullptr, nullptr, (const float2*)dfacing, nullptr,
+                             dgd, nullptr, (const float2*)dgoal, dmt, 1, s->st, &s->launches);
+        CKC(cudaStreamSynchronize(s->st));  // h goes out of scope
+    }
+    s->rng0 = d->rng_state;
+    lc::launch_set_rng(s->dP, n, b, s->rng0, s->st, &s->launches);
+    lc::launch_init_reduce(s->dP, n, b, s->st, &s->launches);
+    CKC(cudaStreamSynchronize(s->st));
+    CKC(cudaGetLastError());
+    CKB(build_graphs(s));
+    *out = s;
+    return LC_OK;
+#undef CKB
+#undef CKC
+}
+
+}  // extern "C"
+
+#define SIM_ENTER(s)                                                   \
+    if (!(s)) return fail(LC_ERR_ARG, "%s: null handle", __func__);    \
+    CK(cudaSetDevice((s)->device))
+
+static int check_device_error(lc_sim* s) {
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    if (s->hctl->error) return fail(s->hctl->error, "device-side error %d at frame %u (non-finite state or an agent without comm partner)", s->hctl->error, s->hctl->frame);
+    return 0;
+}
+
+extern "C" {
+
+int32_t lc_set_weights(lc_sim* s, const float* m_cv, const float* m_f) {
+    SIM_ENTER(s);
+    if (m_cv) memcpy(s->hp.m_cv, m_cv, sizeof s->hp.m_cv);
+    if (m_f) memcpy(s->hp.m_f, m_f, sizeof s->hp.m_f);
+    CK(cudaStreamSynchronize(s->st));  // hp is the copy source; keep it stable
+    return upload_params(s);
+}
+
+int32_t lc_step(lc_sim* s, int32_t nframes) {
+    SIM_ENTER(s);
+    if (nframes < 0) return fail(LC_ERR_ARG, "lc_step: nframes < 0");
+    int left = nframes;
+    while (left >= GRAPH_BATCH) {
+        CK(cudaGraphLaunch(s->gexec[1], s->st));
+        left -= GRAPH_BATCH;
+        s->launches += 6 * GRAPH_BATCH;
+    }
+    while (left > 0) {
+        CK(cudaGraphLaunch(s->gexec[0], s->st));
+        --left;
+        s->launches += 6;
+    }
+    return LC_OK;
+}
+
+int32_t lc_sync(lc_sim* s) {
+    SIM_ENTER(s);
+    CK(cudaStreamSynchronize(s->st));
+    CK(cudaGetLastError());
+    return LC_OK;
+}
+
+int32_t lc_finished(lc_sim* s, int32_t* finished, uint32_t* frame) {
+    SIM_ENTER(s);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    if (finished) *finished = s->hctl->finished;
+    if (frame) *frame = s->hctl->frame;
+    return LC_OK;
+}
+
+int32_t lc_run_to_completion(lc_sim* s, int32_t* frames) {
+    SIM_ENTER(s);
+    // main.cpp:98 while (!all_done): frames after the all_done frame are device-side no-ops, so stepping in
+    // batches and polling the latch executes exactly the reference's frame count.
+    for (;;) {
+        int rc = lc_step(s, 4 * GRAPH_BATCH);
+        if (rc) return rc;
+        rc = check_device_error(s);
+        if (rc) return rc;
+        if (s->hctl->finished) break;
+    }
+    if (frames) *frames = (int32_t)s->hctl->frame;
+    return LC_OK;
+}
+
+int32_t lc_get_state(lc_sim* s, float* pos, float* vel, float* vfh, float* c, float* facing, float* lgoal,
+                     float* goal_dist, int32_t* num_done) {
+    SIM_ENTER(s);
+    const size_t n = (size_t)s->n;
+    float* st = s->stage;
+    float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
+    float* dc = st + 6 * n; float2* dfac = (float2*)(st + 9 * n); float2* dlg = (float2*)(st + 11 * n);
+    float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
+    lc::launch_get_state(s->dP, s->n, s->b, pos ? dpos : nullptr, vel ? dvel : nullptr, vfh ? dvfh : nullptr,
+                         c ? dc : nullptr, facing ? dfac : nullptr, lgoal ? dlg : nullptr, goal_dist ? dgd : nullptr,
+                         num_done ? dnd : nullptr, s->st, &s->launches);
+    if (pos) CK(cudaMemcpyAsync(pos, dpos, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+    if (vel) CK(cudaMemcpyAsync(vel, dvel, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+    if (vfh) CK(cudaMemcpyAsync(vfh, dvfh, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+    if (c) CK(cudaMemcpyAsync(c, dc, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, s->st));
+    if (facing) CK(cudaMemcpyAsync(facing, dfac, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+    if (lgoal) CK(cudaMemcpyAsync(lgoal, dlg, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+    if (goal_dist) CK(cudaMemcpyAsync(goal_dist, dgd, sizeof(float) * n, cudaMemcpyDeviceToHost, s->st));
+    if (num_done) CK(cudaMemcpyAsync(num_done, dnd, sizeof(int) * n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return LC_OK;
+}
+
+int32_t lc_set_state(lc_sim* s, const float* pos, const float* vel, const float* vfh, const float* c,
+                     const float* facing, const float* lgoal, const float* goal_dist, const int32_t* num_done) {
+    SIM_ENTER(s);
+    const size_t n = (size_t)s->n;
+    float* st = s->stage;
+    float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
+    float* dc = st + 6 * n; float2* dfac = (float2*)(st + 9 * n); float2* dlg = (float2*)(st + 11 * n);
+    float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
+    if (pos) CK(cudaMemcpyAsync(dpos, pos, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+    if (vel) CK(cudaMemcpyAsync(dvel, vel, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+    if (vfh) CK(cudaMemcpyAsync(dvfh, vfh, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+    if (c) CK(cudaMemcpyAsync(dc, c, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, s->st));
+    if (facing) CK(cudaMemcpyAsync(dfac, facing, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+    if (lgoal) CK(cudaMemcpyAsync(dlg, lgoal, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
+    if (goal_dist) CK(cudaMemcpyAsync(dgd, goal_dist, sizeof(float) * n, cudaMemcpyHostToDevice, s->st));
+    if (num_done) CK(cudaMemcpyAsync(dnd, num_done, sizeof(int) * n, cudaMemcpyHostToDevice, s->st));
+    lc::launch_set_state(s->dP, s->n, s->b, pos ? dpos : nullptr, vel ? dvel : nullptr, vfh ? dvfh : nullptr,
+                         c ? dc : nullptr, facing ? dfac : nullptr, lgoal ? dlg : nullptr, goal_dist ? dgd : nullptr,
+                         num_done ? dnd : nullptr, nullptr, nullptr, 0, s->st, &s->launches);
+    lc::launch_init_reduce(s->dP, s->n, s->b, s->st, &s->launches);
+    return LC_OK;
+}
+
+// stream state before the first draw of the NEXT frame; every frame consumes n draws (LMP.cpp:261-263)
+int32_t lc_get_rng(lc_sim* s, uint32_t* rng_state) {
+    SIM_ENTER(s);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    *rng_state = lcm::lcg_mul(s->rng0, lcg_pow(16807u, (uint64_t)s->hctl->frame * (uint64_t)s->n));
+    return LC_OK;
+}
+
+int32_t lc_set_rng(lc_sim* s, uint32_t rng_state) {
+    SIM_ENTER(s);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    // rng0 is defined relative to frame 0; rebase so that lc_get_rng stays consistent
+    uint64_t consumed = (uint64_t)s->hctl->frame * (uint64_t)s->n;
+    // inverse of 16807^consumed mod (2^31-1): a^(m-2) is the modular inverse (m prime)
+    uint32_t inv = lcg_pow(lcg_pow(16807u, consumed), 2147483647ull - 2ull);
+    s->rng0 = lcm::lcg_mul(rng_state, inv);
+    lc::launch_set_rng(s->dP, s->n, s->b, rng_state, s->st, &s->launches);
+    return LC_OK;
+}
+
+int32_t lc_get_scores(lc_sim* s, float* avg_velocity, float* group_time, float* run_avg, float* run_std,
+                      int32_t* total_num_done) {
+    SIM_ENTER(s);
+    lc::launch_finalize(s->dP, s->b, s->st, &s->launches);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    const lc::Ctl& c = *s->hctl;
+    if (avg_velocity) *avg_velocity = c.avg_velocity;
+    if (group_time) *group_time = c.run_avg + c.run_std * 3;  // comm.cpp:139
+    if (run_avg) *run_avg = c.run_avg;
+    if (run_std) *run_std = c.run_std;
+    if (total_num_done) *total_num_done = c.total_num_done;
+    if (c.error) return fail(c.error, "device-side error %d at frame %u", c.error, c.frame);
+    return LC_OK;
+}
+
+int32_t lc_get_partners(lc_sim* s, int32_t* partner) {
+    SIM_ENTER(s);
+    CK(cudaMemcpyAsync(partner, s->b.partner_id, sizeof(int) * (size_t)s->n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return LC_OK;
+}
+
+int32_t lc_get_neighbor_counts(lc_sim* s, int32_t* count) {
+    SIM_ENTER(s);
+    CK(cudaMemcpyAsync(count, s->b.nbr_cnt, sizeof(int) * (size_t)s->n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return LC_OK;
+}
+
+int32_t lc_get_neighbor_lists(lc_sim* s, int32_t* idx, int32_t cap) {
+    SIM_ENTER(s);
+    if (!s->b.nbr_list) return fail(LC_ERR_ARG, "lc_get_neighbor_lists: create the simulation with LC_FLAG_DEBUG_LISTS");
+    if (cap != s->b.list_cap) return fail(LC_ERR_ARG, "lc_get_neighbor_lists: cap_per_agent must be %d", s->b.list_cap);
+    CK(cudaMemcpyAsync(idx, s->b.nbr_list, sizeof(int) * (size_t)s->n * cap, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return LC_OK;
+}
+
+int32_t lc_get_counters(lc_sim* s, int64_t* overlap_pairs, int64_t* collision_hits, int64_t* candidates) {
+    SIM_ENTER(s);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    if (overlap_pairs) *overlap_pairs = (int64_t)(s->hctl->overlap2 / 2);
+    if (collision_hits) *collision_hits = (int64_t)s->hctl->coll_hits;
+    if (candidates) *candidates = s->hctl->n_cand;
+    return LC_OK;
+}
+
+int32_t lc_timer_start(lc_sim* s) {
+    SIM_ENTER(s);
+    CK(cudaEventRecord(s->ev0, s->st));
+    return LC_OK;
+}
+
+int32_t lc_timer_stop(lc_sim* s, float* ms) {
+    SIM_ENTER(s);
+    CK(cudaEventRecord(s->ev1, s->st));
+    CK(cudaEventSynchronize(s->ev1));
+    CK(cudaEventElapsedTime(ms, s->ev0, s->ev1));
+    return LC_OK;
+}
+
+int64_t lc_kernel_launches(lc_sim* s) { return s ? s->launches : 0; }
+
+}  // extern "C"

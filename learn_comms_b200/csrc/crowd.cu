@@ -1,0 +1,827 @@
+// Single-crowd frame kernels for sm_100a.  One frame of the reference loop (enginee/src/main.cpp:98-150)
+//   S0 demo::run -> S1 comm::run -> S2 ai::update_agents (LMP::calc_sum_force) -> S3 physics::simulate -> S4 all_sync
+// is six launches on one stream:
+//   k_frame_begin  S0 scoring + latch; derives this frame's grid from last frame's reductions      (1 block)
+//   k_bin          cell id + rank per agent (counting sort, phase 1); directional extremes          (n threads)
+//   k_scan_hull    exclusive scan of the cell histogram; candidate-pruning polygon                  (1 block)
+//   k_reorder      scatter the whole SoA state into cell order; replan gate; candidate compaction   (n threads)
+//   k_force        S1 + S2 + S3a fused: partner arg-max, message update, goal + TTC forces over the
+//                  3x3 (stencil) cells, leap-frog integrate; emits near-lists for the collision pass (n threads)
+//   k_collide      S3b collision push-out (Jacobi) + avg_velocity + next frame's reductions         (n threads)
+// FP32 CUDA cores only: the path is a gather / pair-test loop, not a dense contraction.
+#include "crowd.cuh"
+#include "lc_math.cuh"
+#include <math_constants.h>
+
+namespace lc {
+using namespace lcm;
+
+__constant__ float c_dirx[HULL_K];
+__constant__ float c_diry[HULL_K];
+
+// demo.cpp:655-663 update_runs (Welford, all float)
+__device__ __forceinline__ void update_runs(Ctl* ctl, float overhead) {
+    float ftotal = (float)(++ctl->total_num_done);
+    float delta = __fsub_rn(overhead, ctl->run_avg);
+    ctl->run_avg = __fadd_rn(ctl->run_avg, __fdiv_rn(delta, ftotal));
+    float delta2 = __fsub_rn(overhead, ctl->run_avg);
+    ctl->M2 = __fadd_rn(ctl->M2, __fmul_rn(delta, delta2));
+    ctl->run_std = __fsqrt_rn(__fdiv_rn(ctl->M2, ftotal));
+}
+
+// physics.cpp:72-76 with vel_count == 0 forever (quirk Q6): avg = (avg*0 + |vel|) / (0 + 1) per not-done agent in
+// table order, i.e. the speed of the last one unless a non-finite value poisoned the chain.
+__device__ __forceinline__ void fold_avg_velocity(Ctl* ctl) {
+    unsigned long long lv = ctl->lastvel;
+    if (lv != 0ull) {
+        float sp = __uint_as_float((uint32_t)(lv & 0xffffffffull));
+        int others = ctl->nonfinite - ((sp <= LC_FLT_MAX) ? 0 : 1);
+        bool poisoned = others > 0 || !(fabsf(ctl->avg_velocity) <= LC_FLT_MAX);
+        ctl->avg_velocity = poisoned ? CUDART_NAN_F : sp;
+        ctl->lastvel = 0ull;
+        ctl->nonfinite = 0;
+    }
+}
+
+__device__ void grid_from_reductions(const Params* P, Ctl* ctl) {
+    float minx = ord2f(ctl->minx), miny = ord2f(ctl->miny), maxx = ord2f(ctl->maxx), maxy = ord2f(ctl->maxy);
+    float vmax = __uint_as_float(ctl->vmax);
+    if (!(vmax <= 1.0e3f)) { vmax = 1.0e3f; if (!ctl->error) ctl->error = -3; }
+    if (!(maxx >= minx) || !(maxy >= miny) || !(maxx - minx <= 1e9f) || !(maxy - miny <= 1e9f)) {
+        minx = miny = 0.f; maxx = maxy = 1.f;
+        if (!ctl->error) ctl->error = -3;
+    }
+    // ttc <= 5 implies |m| <= R + 5*|dv| <= R + 10*vmax (LMP.cpp:297-300); slack covers float rounding
+    float cutoff = P->R + 10.f * vmax * 1.001f + 0.01f;
+    int st = P->stencil_req < 1 ? 1 : P->stencil_req;
+    float h = cutoff / (float)st;
+    float ext = fmaxf(maxx - minx, maxy - miny);
+    int nx, ny;
+    for (;;) {
+        nx = (int)floorf((maxx - minx) / h) + 1;
+        ny = (int)floorf((maxy - miny) / h) + 1;
+        if ((long long)nx * ny <= CELL_CAP && nx <= 65535 && ny <= 65535) break;
+        h *= 2.f;
+    }
+    ctl->x0 = minx; ctl->y0 = miny; ctl->h = h; ctl->nx = nx; ctl->ny = ny; ctl->ncells = nx * ny;
+    ctl->stencil = (int)ceilf(cutoff / h);
+    ctl->cx = 0.5f * (minx + maxx); ctl->cy = 0.5f * (miny + maxy);
+    ctl->delta = 1e-5f * ext + 1e-4f;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// S0: demo::run (demo.cpp:665-702)
+__global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    __shared__ int2 s_ev[EV_SORT_CAP];
+    __shared__ float s_ft[1024];
+    __shared__ int s_flag[1024];
+    const int tid = threadIdx.x;
+    const int n = P->n;
+    if (tid == 0) fold_avg_velocity(ctl);
+    __syncthreads();
+    const int was_finished = ctl->finished;
+    const int cnt = ctl->ev_count;
+    const int nnd = ctl->nnd_acc;
+    const uint32_t frame = ctl->frame + 1;
+    __syncthreads();
+    if (was_finished && !(P->flags & 2u)) {
+        if (tid == 0) ctl->halt = 1;
+        return;
+    }
+    const float fake_time = __fmul_rn(LC_DT, (float)frame);
+    if (!was_finished) {
+        // newly done agents, table order (demo.cpp:669-676)
+        if (cnt > 0 && cnt <= EV_SORT_CAP) {
+            int m = 1;
+            while (m < cnt) m <<= 1;
+            for (int i = tid; i < m; i += blockDim.x) s_ev[i] = i < cnt ? b.events[i] : make_int2(0x7fffffff, 0);
+            __syncthreads();
+            for (int k = 2; k <= m; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < m; i += blockDim.x) {
+                        int ixj = i ^ j;
+                        if (ixj > i) {
+                            int2 a = s_ev[i], c = s_ev[ixj];
+                            bool up = (i & k) == 0;
+                            if ((a.x > c.x) == up) { s_ev[i] = c; s_ev[ixj] = a; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            if (tid == 0)
+                for (int i = 0; i < cnt; ++i) update_runs(ctl, __fsub_rn(fake_time, __int_as_float(s_ev[i].y)));
+        } else if (cnt > EV_SORT_CAP) {
+            for (int i = tid; i < n; i += blockDim.x) b.ev_by_id[i] = CUDART_NAN_F;
+            __syncthreads();
+            for (int i = tid; i < cnt; i += blockDim.x) b.ev_by_id[b.events[i].x] = __int_as_float(b.events[i].y);
+            __syncthreads();
+            for (int base = 0; base < n; base += blockDim.x) {
+                int i = base + tid;
+                float v = i < n ? b.ev_by_id[i] : CUDART_NAN_F;
+                s_ft[tid] = v;
+                s_flag[tid] = (v == v);
+                __syncthreads();
+                if (tid == 0)
+                    for (int k = 0; k < blockDim.x; ++k)
+                        if (s_flag[k]) update_runs(ctl, __fsub_rn(fake_time, s_ft[k]));
+                __syncthreads();
+            }
+        }
+        __syncthreads();
+        bool all_done = nnd == 0;
+        if (fake_time > P->max_duration) {  // demo.cpp:691-700
+            for (int base = 0; base < n; base += blockDim.x) {
+                int id = base + tid;
+                int flag = 0;
+                float ft = 0.f;
+                if (id < n) {
+                    int s = b.slot_of_id[id];
+                    int4 mt = b.cur.meta[s];
+                    if (!(mt.y & 1)) {
+                        float2 g = b.cur.goal[s], p = b.posf[s];
+                        float l = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
+                        ft = __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
+                        flag = 1;
+                    }
+                }
+                s_ft[tid] = ft;
+                s_flag[tid] = flag;
+                __syncthreads();
+                if (tid == 0)
+                    for (int k = 0; k < blockDim.x; ++k)
+                        if (s_flag[k]) update_runs(ctl, s_ft[k]);
+                __syncthreads();
+            }
+            all_done = true;
+        }
+        if (tid == 0 && all_done) ctl->finished = 1;
+    }
+    if (tid == 0) {
+        ctl->frame = frame;
+        ctl->ev_count = 0;
+        ctl->n_not_done = nnd;
+        ctl->nnd_acc = 0;
+        grid_from_reductions(P, ctl);
+        ctl->minx = ctl->miny = 0xffffffffu;
+        ctl->maxx = ctl->maxy = 0u;
+        ctl->vmax = 0u;
+        ctl->n_cand = 0;
+        ctl->replan1 = ctl->replan2 = 0x7fffffff;
+        ctl->overlap2 = 0ull;
+        ctl->coll_hits = 0ull;
+    }
+    if (tid < HULL_K) ctl->ext[tid] = 0ull;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Uniform grid, phase 1: cell id + arrival rank per agent; directional extremes for candidate pruning.
+__device__ __forceinline__ int cell_of(const Ctl* ctl, float x, float y) {
+    int ix = (int)floorf((x - ctl->x0) / ctl->h), iy = (int)floorf((y - ctl->y0) / ctl->h);
+    ix = min(max(ix, 0), ctl->nx - 1);
+    iy = min(max(iy, 0), ctl->ny - 1);
+    return iy * ctl->nx + ix;
+}
+
+__global__ void __launch_bounds__(256) k_bin(const Params* __restrict__ P, Buffers b) {
+    const Ctl* ctl = b.ctl;
+    if (ctl->halt) return;
+    const int n = P->n;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float2 p = make_float2(0.f, 0.f);
+    if (i < n) {
+        p = b.posf[i];
+        int cell = cell_of(ctl, p.x, p.y);
+        int rank = atomicAdd(&b.cell_count[cell], 1);
+        b.cellrank[i] = make_int2(cell, rank);
+    }
+    if (P->flags & 1u) return;  // no comm: no partner search
+    const float rx = p.x - ctl->cx, ry = p.y - ctl->cy;
+    const bool ok = i < n && rx == rx && ry == ry;
+#pragma unroll
+    for (int k = 0; k < HULL_K; ++k) {
+        float v = rx * c_dirx[k] + ry * c_diry[k];
+        unsigned long long key = ok ? (((unsigned long long)f2ord(v) << 32) | (uint32_t)i) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+            key = other > key ? other : key;
+        }
+        if ((threadIdx.x & 31) == 0 && key != 0ull) atomicMax(&b.ctl->ext[k], key);
+    }
+}
+
+// Exclusive scan of the cell histogram (one block; ncells <= CELL_CAP) + the pruning polygon.
+__global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    if (ctl->halt) return;
+    __shared__ int s_warp[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nc = ctl->ncells;
+    const int ipt = (nc + 1023) / 1024;
+    const int lo = min(tid * ipt, nc), hi = min(lo + ipt, nc);
+    int sum = 0;
+    for (int k = lo; k < hi; ++k) sum += b.cell_count[k];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        s_warp[lane] = wi - w;
+    }
+    __syncthreads();
+    int run = s_warp[wid] + incl - sum;
+    for (int k = lo; k < hi; ++k) {
+        int c = b.cell_count[k];
+        b.cell_start[k] = run;
+        run += c;
+    }
+    if (tid == 1023) b.cell_start[nc] = run;
+    // polygon through consecutive distinct extreme agents (CCW); inward unit normals
+    if (tid == 0 && !(P->flags & 1u)) {
+        int ne = 0;
+        for (int k = 0; k < HULL_K; ++k) {
+            unsigned long long ka = ctl->ext[k], kb = ctl->ext[(k + 1) % HULL_K];
+            if (ka == 0ull || kb == 0ull) continue;
+            int a = (int)(ka & 0xffffffffull), c = (int)(kb & 0xffffffffull);
+            if (a == c) continue;
+            float2 pa = b.posf[a], pc = b.posf[c];
+            double ux = (double)pc.x - pa.x, uy = (double)pc.y - pa.y, l = sqrt(ux * ux + uy * uy);
+            if (!(l > 0.0)) continue;
+            ctl->ex[ne] = pa.x; ctl->ey[ne] = pa.y;
+            ctl->enx[ne] = (float)(-uy / l); ctl->eny[ne] = (float)(ux / l);
+            ++ne;
+        }
+        ctl->n_edges = ne;
+    }
+}
+
+// Uniform grid, phase 2: scatter the state into cell order (counting sort).  Also: the replan gate of
+// ai.cpp:151-168 (needs the two lowest ids that want a replan) and comm-partner candidate compaction.
+__global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    if (ctl->halt) return;
+    const int n = P->n;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int2 cr = b.cellrank[i];
+    const int s = b.cell_start[cr.x] + cr.y;
+    const float2 p = b.posf[i];
+    const float4 pv = b.cur.pv[i];
+    const int4 mt = b.cur.meta[i];
+    const float2 g = b.cur.goal[i];
+    b.srt.pv[s] = make_float4(p.x, p.y, pv.z, pv.w);
+    b.srt.vfh[s] = b.cur.vfh[i];
+    b.srt.goal[s] = g;
+    b.srt.lgoal[s] = b.cur.lgoal[i];
+    b.srt.facing[s] = b.cur.facing[i];
+    b.srt.c4[s] = b.cur.c4[i];
+    b.srt.meta[s] = mt;
+    b.slot_of_id[mt.x] = s;
+    // ai.cpp:154,161-163: need_replan = done && goal_dist > 1 (wall-free: the lost_frames clause cannot fire)
+    if (mt.y & 1) {
+        float gd = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
+        if (gd > 1.f) {
+            int old = atomicMin(&ctl->replan1, mt.x);
+            int loser = old < mt.x ? mt.x : old;
+            if (loser != 0x7fffffff) atomicMin(&ctl->replan2, loser);
+        }
+    }
+    if (!(P->flags & 1u)) {
+        // keep every agent that is not inside (by delta) the polygon of extreme agents: only those can be
+        // the arg-max of comm.cpp:201-220 for any query (proof in DESIGN.md)
+        const int ne = ctl->n_edges;
+        bool inside = ne >= 3;
+        const float delta = ctl->delta;
+        for (int e = 0; e < ne && inside; ++e) {
+            float d = (p.x - ctl->ex[e]) * ctl->enx[e] + (p.y - ctl->ey[e]) * ctl->eny[e];
+            if (!(d >= delta)) inside = false;
+        }
+        if (!inside) {
+            int k = atomicAdd(&ctl->n_cand, 1);
+            b.cand[k] = make_float4(p.x, p.y, __int_as_float(mt.x), __int_as_float(s));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// S1 + S2 + S3a fused, one thread per agent in cell order.
+
+// Visit every interacting neighbour {j : ttc_ij <= 5} of agent s in the (2*stencil+1)^2 cell block.  Cells of one
+// grid row are contiguous in the sorted arrays, so each row of the block is ONE contiguous slot range.
+template <bool FIRST, class F>
+__device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx,
+                                                float vy, float RR, float near_c, int& n_near, int& n_overlap, F&& f) {
+    const int st = ctl->stencil, nx = ctl->nx, ny = ctl->ny;
+    int ix = (int)floorf((px - ctl->x0) / ctl->h), iy = (int)floorf((py - ctl->y0) / ctl->h);
+    ix = min(max(ix, 0), nx - 1);
+    iy = min(max(iy, 0), ny - 1);
+    const int x_lo = max(ix - st, 0), x_hi = min(ix + st, nx - 1);
+    for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
+        const int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
+        for (int j = j0; j < j1; ++j) {
+            if (j == s) continue;
+            const float4 q = __ldg(&b.srt.pv[j]);
+            const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py);
+            const float dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
+            float t, c;
+            const bool hit = ttc_pair(mx, my, dvx, dvy, RR, t, c);
+            if (FIRST) {
+                if (c < near_c) {
+                    if (n_near < MAX_NEAR) b.near_idx[(size_t)s * MAX_NEAR + n_near] = j;
+                    ++n_near;
+                    if (c < 0.f) ++n_overlap;  // BoundVolume.cpp:203-207 on frame-start positions
+                }
+            }
+            if (hit) {
+                float fx, fy;
+                ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
+                f(j, fx, fy);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_force(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    if (ctl->halt) return;
+    const int n = P->n;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int not_done_after = 0;
+    if (s < n) {
+        const float4 me = b.srt.pv[s];
+        const float px = me.x, py = me.y, vx = me.z, vy = me.w;
+        int4 mt = b.srt.meta[s];
+        const int id = mt.x;
+        const float2 goal = b.srt.goal[s];
+        float2 lgoal = b.srt.lgoal[s];
+        float2 facing = b.srt.facing[s];
+        float4 c4 = b.srt.c4[s];
+        const bool done_before = mt.y & 1;
+        float forcex = 0.f, forcey = 0.f;
+
+        // ---- S1: comm::run (comm.cpp:267-305) ----
+        if (!(P->flags & 1u)) {
+            // comm.cpp:201-220 select_nearest == arg-max of squared distance (quirk Q1), strict '>', first in table order
+            const int nc = ctl->n_cand;
+            float best = LC_FLT_MIN;
+            int best_id = -1, best_slot = s;
+            for (int k = 0; k < nc; ++k) {
+                const float4 cd = __ldg(&b.cand[k]);
+                const int cid = __float_as_int(cd.z);
+                if (cid == id) continue;
+                const float dx = __fsub_rn(cd.x, px), dy = __fsub_rn(cd.y, py);
+                const float d2 = dot2(dx, dy, dx, dy);
+                if (d2 > best || (d2 == best && best_id >= 0 && cid < best_id)) {
+                    best = d2; best_id = cid; best_slot = __float_as_int(cd.w);
+                }
+            }
+            if (best_id < 0) atomicCAS(&ctl->error, 0, -3);  // comm.cpp:273-285: null partner is UB in the reference
+            b.partner_id[id] = best_id;
+            const float4 pj = __ldg(&b.srt.pv[best_slot]);
+            const float4 cj = __ldg(&b.srt.c4[best_slot]);
+            // comm.cpp:144-192 x(): COSINE_REL + PROX + SOFTSIGN_GOAL; partner (x, y) of a vec3 = (x, 0): quirk Q2
+            const float rightx = facing.y, righty = -facing.x;
+            const float dvx = __fsub_rn(pj.z, vx), dvy = __fsub_rn(0.f, vy);
+            float rvx = dot2(rightx, righty, dvx, dvy), rvy = dot2(facing.x, facing.y, dvx, dvy);
+            const float mag_rv = len2(rvx, rvy);
+            if (mag_rv > 0.f) { rvx = __fdiv_rn(rvx, mag_rv); rvy = __fdiv_rn(rvy, mag_rv); }
+            const float dpx = __fsub_rn(pj.x, px), dpy = __fsub_rn(0.f, py);
+            float rpx = dot2(rightx, righty, dpx, dpy), rpy = dot2(facing.x, facing.y, dpx, dpy);
+            float mag_rp = len2(rpx, rpy);
+            if (mag_rp > 0.f) {
+                rpx = __fdiv_rn(rpx, mag_rp); rpy = __fdiv_rn(rpy, mag_rp);
+                mag_rp = __fdiv_rn(1.f, mag_rp);
+            }
+            float g = c4.w;
+            g = __fdiv_rn(g, __fadd_rn(1.f, g));
+            const float x[8] = {cj.x, cj.y, cj.z, rvy, mag_rv, rpy, mag_rp, g};
+            float cn[3];
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {  // comm.cpp:285 M_cv * x (Eigen 3.3 unrolled redux order, see oracle/canon.c)
+                const float* m = &P->m_cv[8 * r];
+                float p0 = __fmul_rn(m[0], x[0]), p1 = __fmul_rn(m[1], x[1]), p2 = __fmul_rn(m[2], x[2]),
+                      p3 = __fmul_rn(m[3], x[3]), p4 = __fmul_rn(m[4], x[4]), p5 = __fmul_rn(m[5], x[5]),
+                      p6 = __fmul_rn(m[6], x[6]), p7 = __fmul_rn(m[7], x[7]);
+                float cp = __fadd_rn(__fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3)),
+                                     __fadd_rn(__fadd_rn(p4, p5), __fadd_rn(p6, p7)));
+                // CommComp.h:20-27 buf_in: x / (1 + |2x|) + 0.5
+                cn[r] = __fadd_rn(__fdiv_rn(cp, __fadd_rn(1.f, fabsf(__fmul_rn(2.f, cp)))), 0.5f);
+            }
+            float fb[2];
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                const float* m = &P->m_f[3 * r];
+                float fp = __fadd_rn(__fmul_rn(m[0], cj.x), __fadd_rn(__fmul_rn(m[1], cj.y), __fmul_rn(m[2], cj.z)));
+                fb[r] = glm_clamp(fp, -1.f, 1.f);  // CommComp.h:30-32
+            }
+            // pass 2, comm.cpp:288-304
+            const float diffx = __fadd_rn(__fmul_rn(rightx, fb[0]), __fmul_rn(facing.x, fb[1]));
+            const float diffy = __fadd_rn(__fmul_rn(righty, fb[0]), __fmul_rn(facing.y, fb[1]));
+            if (!done_before) { forcex = __fadd_rn(forcex, diffx); forcey = __fadd_rn(forcey, diffy); }
+            const float speed = __fsqrt_rn(dot3_xz(vx, vy, vx, vy));
+            const float tlx = __fsub_rn(lgoal.x, px), tly = __fsub_rn(lgoal.y, py);
+            if (speed > 0.f && len2(tlx, tly) > 0.f) {
+                const float inv = __fdiv_rn(1.0f, __fsqrt_rn(dot2(tlx, tly, tlx, tly)));
+                facing = make_float2(__fmul_rn(tlx, inv), __fmul_rn(tly, inv));
+            }
+            c4.x = cn[0]; c4.y = cn[1]; c4.z = cn[2];  // swap()
+        }
+
+        // ---- S2: ai::update_agents (ai.cpp:153-172) ----
+        const float gd = len2(__fsub_rn(goal.x, px), __fsub_rn(goal.y, py));
+        c4.w = gd;
+        int num_done = mt.y & 1;
+        if (num_done && gd > 1.f && (id == ctl->replan1 || id == ctl->replan2)) num_done = 0;  // GMP::plan_one
+        // LMP::lookahead (LMP.cpp:84-113) with plan = [final_goal]
+        if (num_done < 1) {
+            const float ox = __fsub_rn(px, goal.x), oy = __fsub_rn(py, goal.y);
+            if (dot2(ox, oy, ox, oy) < 1.f) num_done = 1; else lgoal = goal;
+        } else {
+            lgoal = goal;
+        }
+        if (num_done == 1 && !(mt.y & 2)) {  // will be counted by demo::run at the start of the next frame
+            mt.y |= 2;
+            int k = atomicAdd(&ctl->ev_count, 1);
+            b.events[k] = make_int2(id, mt.w);
+        }
+        mt.y = (mt.y & ~1) | num_done;
+        not_done_after = num_done == 0;
+        // LMP.cpp:261-273: one draw for both components
+        const float eps = lcg_uniform((uint32_t)mt.z, -.01f, .01f);
+        mt.z = (int)lcg_mul((uint32_t)mt.z, P->lcg_stride);
+        const float dgx = __fsub_rn(__fadd_rn(lgoal.x, eps), px), dgy = __fsub_rn(__fadd_rn(lgoal.y, eps), py);
+        const float dl = glm_max(1.0f, len2(dgx, dgy));
+        const float gvx = __fmul_rn(1.0f, __fdiv_rn(dgx, dl)), gvy = __fmul_rn(1.0f, __fdiv_rn(dgy, dl));
+        const float goalFx = __fmul_rn(2.0f, __fsub_rn(gvx, vx)), goalFy = __fmul_rn(2.0f, __fsub_rn(gvy, vy));
+
+        // LMP.cpp:288-304: TTC forces, summed in table (id) order
+        int hid[MAX_HITS];
+        float hfx[MAX_HITS], hfy[MAX_HITS];
+        int cnt = 0, n_near = 0, n_overlap = 0;
+        scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap,
+                              [&](int j, float fx, float fy) {
+                                  if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
+                                  ++cnt;
+                              });
+        float ttcFx = 0.f, ttcFy = 0.f;
+        int* lst = (P->flags & 4u) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
+        if (cnt <= MAX_HITS) {
+            int last = -1;
+            for (int k = 0; k < cnt; ++k) {
+                int bi = 0, bid = 0x7fffffff;
+                for (int q = 0; q < cnt; ++q) {
+                    int v = hid[q];
+                    if (v > last && v < bid) { bid = v; bi = q; }
+                }
+                ttcFx = __fadd_rn(ttcFx, hfx[bi]);
+                ttcFy = __fadd_rn(ttcFy, hfy[bi]);
+                last = bid;
+                if (lst && k < b.list_cap) lst[k] = bid;
+            }
+        } else {  // rare: more interacting neighbours than the register buffer holds — re-scan per neighbour
+            atomicAdd(&ctl->hit_overflow, 1);
+            int last = -1, dummy0 = 0, dummy1 = 0;
+            for (int k = 0; k < cnt; ++k) {
+                int bid = 0x7fffffff;
+                float bfx = 0.f, bfy = 0.f;
+                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1,
+                                       [&](int j, float fx, float fy) {
+                                           int v = __ldg(&b.srt.meta[j].x);
+                                           if (v > last && v < bid) { bid = v; bfx = fx; bfy = fy; }
+                                       });
+                ttcFx = __fadd_rn(ttcFx, bfx);
+                ttcFy = __fadd_rn(ttcFy, bfy);
+                last = bid;
+                if (lst && k < b.list_cap) lst[k] = bid;
+            }
+        }
+        b.nbr_cnt[id] = cnt;
+        if (n_near > MAX_NEAR) atomicAdd(&ctl->near_overflow, 1);
+        b.near_cnt[s] = n_near;
+        if (n_overlap) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
+        forcex = __fadd_rn(forcex, __fadd_rn(goalFx, ttcFx));  // ai.cpp:172
+        forcey = __fadd_rn(forcey, __fadd_rn(goalFy, ttcFy));
+
+        // ---- S3a: physics::simulate leap-frog (physics.cpp:41-51), mass == 1 ----
+        const float2 vbh = b.srt.vfh[s];
+        float hx = __fadd_rn(vbh.x, __fmul_rn(LC_DT, forcex)), hy = __fadd_rn(vbh.y, __fmul_rn(LC_DT, forcey));
+        const float h2 = dot3_xz(hx, hy, hx, hy);
+        if (h2 > 1.f) {
+            const float inv = __fdiv_rn(1.0f, __fsqrt_rn(h2));
+            hx = __fmul_rn(hx, inv); hy = __fmul_rn(hy, inv);
+        }
+        const float nvx = __fadd_rn(__fdiv_rn(hx, 2.f), __fdiv_rn(vbh.x, 2.f));
+        const float nvy = __fadd_rn(__fdiv_rn(hy, 2.f), __fdiv_rn(vbh.y, 2.f));
+        const float npx = __fadd_rn(px, __fmul_rn(hx, LC_DT)), npy = __fadd_rn(py, __fmul_rn(hy, LC_DT));
+        b.cur.pv[s] = make_float4(npx, npy, nvx, nvy);
+        b.cur.vfh[s] = make_float2(hx, hy);
+        b.cur.goal[s] = goal;
+        b.cur.lgoal[s] = lgoal;
+        b.cur.facing[s] = facing;
+        b.cur.c4[s] = c4;
+        b.cur.meta[s] = mt;
+    }
+    // demo.cpp:667-669: all_done of the next frame needs the number of agents that are not done after lookahead
+    unsigned ball = __ballot_sync(0xffffffffu, not_done_after);
+    if ((threadIdx.x & 31) == 0 && ball) atomicAdd(&ctl->nnd_acc, __popc(ball));
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// block-level reductions feeding the next frame's grid (bounding box of final positions, max speed)
+__device__ __forceinline__ void reduce_bbox_vmax(Ctl* ctl, bool valid, float x, float y, float speed) {
+    uint32_t mnx = valid ? f2ord(x) : 0xffffffffu, mxx = valid ? f2ord(x) : 0u;
+    uint32_t mny = valid ? f2ord(y) : 0xffffffffu, mxy = valid ? f2ord(y) : 0u;
+    uint32_t sp = valid ? __float_as_uint(speed) : 0u;  // speed >= 0 (or NaN, which sorts above everything)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
+        mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+        mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+        mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+        sp = max(sp, __shfl_xor_sync(0xffffffffu, sp, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(&ctl->minx, mnx); atomicMin(&ctl->miny, mny);
+        atomicMax(&ctl->maxx, mxx); atomicMax(&ctl->maxy, mxy);
+        atomicMax(&ctl->vmax, sp);
+    }
+}
+
+// S3b: collision push-out (physics.cpp:58-69 + BVH.cpp:106-120), Jacobi: every agent tests the others at their
+// integrated, not yet pushed positions; hits are applied in table (id) order.  Then physics.cpp:72-76.
+__global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    if (ctl->halt) return;
+    const int n = P->n;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = s < n;
+    float px = 0.f, py = 0.f, speed = 0.f;
+    if (valid) {
+        const float4 me = b.cur.pv[s];
+        px = me.x; py = me.y;
+        const float qx = me.x, qy = me.y;
+        const int4 mt = b.cur.meta[s];
+        int nn = b.near_cnt[s];
+        if (nn > 0) {
+            float2 h = b.cur.vfh[s];
+            int hid[MAX_NEAR];
+            float hax[MAX_NEAR], hay[MAX_NEAR];
+            int cnt = 0;
+            if (nn <= MAX_NEAR) {
+                for (int k = 0; k < nn; ++k) {
+                    const int j = b.near_idx[(size_t)s * MAX_NEAR + k];
+                    const float4 o = __ldg(&b.cur.pv[j]);
+                    float ax, ay;
+                    if (circ_circ_hit(qx, qy, o.x, o.y, P->r, P->RR, ax, ay)) {
+                        hid[cnt] = __ldg(&b.cur.meta[j].x); hax[cnt] = ax; hay[cnt] = ay; ++cnt;
+                    }
+                }
+                int last = -1;
+                for (int k = 0; k < cnt; ++k) {
+                    int bi = 0, bid = 0x7fffffff;
+                    for (int q = 0; q < cnt; ++q) {
+                        int v = hid[q];
+                        if (v > last && v < bid) { bid = v; bi = q; }
+                    }
+                    push_away(px, py, h.x, h.y, hax[bi], hay[bi]);
+                    last = bid;
+                }
+            } else {
+                // near-list overflow (more than MAX_NEAR agents within ~0.34 m): walk the cell block, one hit per pass
+                const int nx = ctl->nx, ny = ctl->ny;
+                const float4 old = b.srt.pv[s];  // frame-start position decides the cell block
+                int ix = min(max((int)floorf((old.x - ctl->x0) / ctl->h), 0), nx - 1);
+                int iy = min(max((int)floorf((old.y - ctl->y0) / ctl->h), 0), ny - 1);
+                int last = -1;
+                for (;;) {
+                    int bid = 0x7fffffff;
+                    float bax = 0.f, bay = 0.f;
+                    for (int yy = max(iy - 1, 0); yy <= min(iy + 1, ny - 1); ++yy) {
+                        const int j0 = b.cell_start[yy * nx + max(ix - 1, 0)], j1 = b.cell_start[yy * nx + min(ix + 1, nx - 1) + 1];
+                        for (int j = j0; j < j1; ++j) {
+                            if (j == s) continue;
+                            const float4 o = __ldg(&b.cur.pv[j]);
+                            float ax, ay;
+                            if (circ_circ_hit(qx, qy, o.x, o.y, P->r, P->RR, ax, ay)) {
+                                int v = __ldg(&b.cur.meta[j].x);
+                                if (v > last && v < bid) { bid = v; bax = ax; bay = ay; }
+                            }
+                        }
+                    }
+                    if (bid == 0x7fffffff) break;
+                    push_away(px, py, h.x, h.y, bax, bay);
+                    last = bid;
+                    ++cnt;
+                }
+            }
+            if (cnt) {
+                b.cur.vfh[s] = h;
+                atomicAdd(&ctl->coll_hits, (unsigned long long)cnt);
+            }
+        }
+        b.posf[s] = make_float2(px, py);
+        speed = __fsqrt_rn(dot3_xz(me.z, me.w, me.z, me.w));
+        if (!(mt.y & 1)) {  // physics.cpp:72-76
+            unsigned long long key = ((unsigned long long)(uint32_t)(mt.x + 1) << 32) | __float_as_uint(speed);
+            atomicMax(&ctl->lastvel, key);
+            // a non-finite speed anywhere but at the last agent poisons the running average (NaN * 0): counted here,
+            // resolved in fold_avg_velocity
+            if (!(speed <= LC_FLT_MAX)) atomicAdd(&ctl->nonfinite, 1);
+        }
+    }
+    const bool ok = valid && px == px && py == py;
+    reduce_bbox_vmax(ctl, ok, px, py, speed);
+}
+
+// reductions of an arbitrary state (after lc_create / lc_set_state)
+__global__ void __launch_bounds__(256) k_init_reduce(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    const int n = P->n;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = i < n;
+    float x = 0.f, y = 0.f, speed = 0.f;
+    int nd = 0;
+    if (valid) {
+        float2 p = b.posf[i];
+        float4 pv = b.cur.pv[i];
+        x = p.x; y = p.y;
+        speed = __fsqrt_rn(dot3_xz(pv.z, pv.w, pv.z, pv.w));
+        nd = !(b.cur.meta[i].y & 1);
+        b.slot_of_id[b.cur.meta[i].x] = i;
+    }
+    unsigned ball = __ballot_sync(0xffffffffu, nd);
+    if ((threadIdx.x & 31) == 0 && ball) atomicAdd(&ctl->nnd_acc, __popc(ball));
+    reduce_bbox_vmax(ctl, valid && x == x && y == y, x, y, speed);
+}
+
+__global__ void k_finalize(const Params* __restrict__ P, Buffers b) { fold_avg_velocity(b.ctl); }
+
+// state in id order for the host (POOL.all_sync view, Pool.cpp:69-91)
+__global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P, Buffers b, float2* pos, float2* vel,
+                                                    float2* vfh, float* c3, float2* facing, float2* lgoal,
+                                                    float* goal_dist, int* num_done) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P->n) return;
+    const int4 mt = b.cur.meta[s];
+    const int id = mt.x;
+    const float4 pv = b.cur.pv[s];
+    const float4 c4 = b.cur.c4[s];
+    if (pos) pos[id] = b.posf[s];
+    if (vel) vel[id] = make_float2(pv.z, pv.w);
+    if (vfh) vfh[id] = b.cur.vfh[s];
+    if (c3) { c3[3 * id] = c4.x; c3[3 * id + 1] = c4.y; c3[3 * id + 2] = c4.z; }
+    if (facing) facing[id] = b.cur.facing[s];
+    if (lgoal) lgoal[id] = b.cur.lgoal[s];
+    if (goal_dist) goal_dist[id] = c4.w;
+    if (num_done) num_done[id] = mt.y & 1;
+}
+
+// per-agent private LCG streams: agent id draws x0 * 16807^((frame-1)*n + id + 1) in frame `frame` (Seeder.cpp, LMP.cpp:261-263)
+__global__ void __launch_bounds__(256) k_set_rng(const Params* __restrict__ P, Buffers b, uint32_t base) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P->n) return;
+    int4 mt = b.cur.meta[s];
+    uint32_t e = (uint32_t)mt.x + 1u, a = 16807u, x = base;
+    while (e) {
+        if (e & 1u) x = lcg_mul(x, a);
+        a = lcg_mul(a, a);
+        e >>= 1;
+    }
+    mt.z = (int)x;
+    b.cur.meta[s] = mt;
+}
+
+// state upload in id order (slot == id): demo.cpp:563-581 create_robo / teacher forcing
+__global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P, Buffers b, const float2* pos,
+                                                    const float2* vel, const float2* vfh, const float* c3,
+                                                    const float2* facing, const float2* lgoal, const float* goal_dist,
+                                                    const int* num_done, const float2* goal, const float* min_time,
+                                                    int init) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P->n) return;
+    // bring the agent with id i to slot i
+    const int so = init ? i : b.slot_of_id[i];
+    float4 pv = init ? make_float4(0, 0, 0, 0) : b.srt.pv[so];      // srt holds a snapshot made by the caller
+    float2 p = init ? make_float2(0, 0) : make_float2(pv.x, pv.y);
+    float2 h = init ? make_float2(0, 0) : b.srt.vfh[so];
+    float2 g = init ? make_float2(0, 0) : b.srt.goal[so];
+    float2 lg = init ? make_float2(0, 0) : b.srt.lgoal[so];
+    float2 fc = init ? make_float2(0, 0) : b.srt.facing[so];
+    float4 c4 = init ? make_float4(0, 0, 0, 0) : b.srt.c4[so];
+    int4 mt = init ? make_int4(i, 0, 0, 0) : b.srt.meta[so];
+    if (pos) p = pos[i];
+    if (vel) { pv.z = vel[i].x; pv.w = vel[i].y; }
+    if (vfh) h = vfh[i];
+    if (c3) { c4.x = c3[3 * i]; c4.y = c3[3 * i + 1]; c4.z = c3[3 * i + 2]; }
+    if (facing) fc = facing[i];
+    if (lgoal) lg = lgoal[i];
+    if (goal_dist) c4.w = goal_dist[i];
+    if (num_done) mt.y = (mt.y & ~1) | (num_done[i] & 1);
+    if (goal) g = goal[i];
+    if (min_time) mt.w = __float_as_int(min_time[i]);
+    b.cur.pv[i] = make_float4(p.x, p.y, pv.z, pv.w);
+    b.posf[i] = p;
+    b.cur.vfh[i] = h;
+    b.cur.goal[i] = g;
+    b.cur.lgoal[i] = lg;
+    b.cur.facing[i] = fc;
+    b.cur.c4[i] = c4;
+    b.cur.meta[i] = mt;
+}
+
+// snapshot cur -> srt (posf folded into pv) so k_set_state can permute in place
+__global__ void __launch_bounds__(256) k_snapshot(const Params* __restrict__ P, Buffers b) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P->n) return;
+    float4 pv = b.cur.pv[i];
+    float2 p = b.posf[i];
+    b.srt.pv[i] = make_float4(p.x, p.y, pv.z, pv.w);
+    b.srt.vfh[i] = b.cur.vfh[i];
+    b.srt.goal[i] = b.cur.goal[i];
+    b.srt.lgoal[i] = b.cur.lgoal[i];
+    b.srt.facing[i] = b.cur.facing[i];
+    b.srt.c4[i] = b.cur.c4[i];
+    b.srt.meta[i] = b.cur.meta[i];
+}
+
+__global__ void k_reset_reductions(Buffers b) {
+    Ctl* ctl = b.ctl;
+    ctl->minx = ctl->miny = 0xffffffffu;
+    ctl->maxx = ctl->maxy = 0u;
+    ctl->vmax = 0u;
+    ctl->nnd_acc = 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+void upload_dirs() {
+    float dx[HULL_K], dy[HULL_K];
+    for (int k = 0; k < HULL_K; ++k) {
+        double th = 2.0 * 3.14159265358979323846 * k / HULL_K;
+        dx[k] = (float)cos(th);
+        dy[k] = (float)sin(th);
+    }
+    cudaMemcpyToSymbol(c_dirx, dx, sizeof dx);
+    cudaMemcpyToSymbol(c_diry, dy, sizeof dy);
+}
+
+void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
+    cudaMemsetAsync(b.cell_count, 0, sizeof(int) * (CELL_CAP + 1), st);
+    k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
+    k_bin<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    k_scan_hull<<<1, 1024, 0, st>>>(dP, b);
+    k_reorder<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    if (launches) *launches += 6;
+}
+
+void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
+    k_reset_reductions<<<1, 1, 0, st>>>(b);
+    k_init_reduce<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    if (launches) *launches += 2;
+}
+
+void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches) {
+    k_finalize<<<1, 1, 0, st>>>(dP, b);
+    if (launches) *launches += 1;
+}
+
+void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
+                      float2* facing, float2* lgoal, float* goal_dist, int* num_done, cudaStream_t st,
+                      long long* launches) {
+    k_get_state<<<cdiv(n, 256), 256, 0, st>>>(dP, b, pos, vel, vfh, c3, facing, lgoal, goal_dist, num_done);
+    if (launches) *launches += 1;
+}
+
+void launch_set_state(const Params* dP, int n, const Buffers& b, const float2* pos, const float2* vel,
+                      const float2* vfh, const float* c3, const float2* facing, const float2* lgoal,
+                      const float* goal_dist, const int* num_done, const float2* goal, const float* min_time, int init,
+                      cudaStream_t st, long long* launches) {
+    if (!init) {
+        k_snapshot<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+        if (launches) *launches += 1;
+    }
+    k_set_state<<<cdiv(n, 256), 256, 0, st>>>(dP, b, pos, vel, vfh, c3, facing, lgoal, goal_dist, num_done, goal,
+                                              min_time, init);
+    if (launches) *launches += 1;
+}
+
+void launch_set_rng(const Params* dP, int n, const Buffers& b, uint32_t base, cudaStream_t st, long long* launches) {
+    k_set_rng<<<cdiv(n, 256), 256, 0, st>>>(dP, b, base);
+    if (launches) *launches += 1;
+}
+
+}  // namespace lc

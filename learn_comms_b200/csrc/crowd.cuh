@@ -1,0 +1,106 @@
+// Single-crowd engine: data layout shared by crowd.cu (kernels) and capi.cu (C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace lc {
+
+constexpr int HULL_K = 16;        // directional extremes used to prune comm-partner candidates
+constexpr int MAX_HITS = 48;      // per-thread buffer of interacting neighbours (sorted by id before summation)
+constexpr int MAX_NEAR = 8;       // per-agent list of neighbours close enough to collide this frame
+constexpr int CELL_CAP = 1 << 18; // max grid cells (cell side grows beyond the cutoff if exceeded)
+constexpr int EV_SORT_CAP = 2048; // events sorted in shared memory; above this the per-id path is used
+
+// One copy of the per-agent state, structure of arrays.  All arrays have n elements.
+//   pv     (pos.x, pos.z, vel.x, vel.z)          Dynamics.h:4,6   — one 16-byte load per neighbour in the pair loop
+//   vfh    vel_forehalf.xz                       Dynamics.h:7
+//   goal   final_goal                            Agent.h:11
+//   lgoal  local_goal                            Agent.h:12
+//   facing CommComp::facing                      CommComp.h:17
+//   c4     (c[0], c[1], c[2], goal_dist)         CommComp.h:14, Agent.h:19
+//   meta   (id, flags, rng, min_time bits)       Agent.h:14,17-18; flags bit0 = num_done, bit1 = overhead_counted
+struct AgentArrays {
+    float4* pv;
+    float2* vfh;
+    float2* goal;
+    float2* lgoal;
+    float2* facing;
+    float4* c4;
+    int4* meta;
+};
+
+struct Ctl {
+    // frame / latch (main.cpp:98-150)
+    uint32_t frame;
+    int finished;   // demo::run returned all_done in some frame <= frame
+    int halt;       // frames after the all_done frame are no-ops
+    int error;      // lc_status of the first device-side error
+    // uniform grid of the current frame
+    float x0, y0, h;
+    int nx, ny, ncells, stencil;
+    // comm-partner candidate pruning
+    float cx, cy, delta;
+    unsigned long long ext[HULL_K];
+    int n_edges;
+    float ex[HULL_K], ey[HULL_K], enx[HULL_K], eny[HULL_K];
+    int n_cand;
+    // reductions over the final positions / velocities of the frame (consumed by the next frame_begin)
+    uint32_t minx, miny, maxx, maxy, vmax;
+    // scoring: demo.cpp:650-702, physics.cpp:72-76
+    int total_num_done;
+    float run_avg, M2, run_std, avg_velocity;
+    unsigned long long lastvel;  // ((id + 1) << 32) | speed bits of the highest-id not-done agent this frame
+    int nonfinite;               // some earlier not-done agent had a non-finite speed (sticky NaN of physics.cpp:75)
+    int n_not_done, nnd_acc;
+    int ev_count;
+    int replan1, replan2;        // ai.cpp:151-168: first two agents (table order) that need a replan
+    // counters (diagnostics)
+    unsigned long long overlap2, coll_hits;
+    int near_overflow, hit_overflow;
+};
+
+struct Params {
+    int n;
+    float r, R, RR, near_c;
+    float max_duration;
+    uint32_t lcg_stride;  // 16807^n mod (2^31-1): advances an agent's private stream by one frame
+    uint32_t flags;
+    int stencil_req;
+    float m_cv[24];
+    float m_f[6];
+};
+
+struct Buffers {
+    AgentArrays cur;   // state at frame start (arbitrary slot order) / K4 output (pre-push), new slot order
+    AgentArrays srt;   // frame-start state reordered by grid cell
+    float2* posf;      // final (post-push) positions, same order as cur
+    int2* cellrank;    // (cell, rank within cell) per agent, cur order
+    int* cell_count;   // [CELL_CAP + 1]
+    int* cell_start;   // [CELL_CAP + 1]
+    int* slot_of_id;   // inverse permutation
+    float4* cand;      // comm-partner candidates: (x, z, id bits, slot bits)
+    int* near_cnt;     // [n]
+    int* near_idx;     // [n][MAX_NEAR]
+    int2* events;      // (id, min_time bits) of agents that became done this frame
+    float* ev_by_id;   // [n] per-id event path (NaN = none)
+    int* partner_id;   // [n] by id (diagnostic)
+    int* nbr_cnt;      // [n] by id (diagnostic)
+    int* nbr_list;     // [n][list_cap] by id (LC_FLAG_DEBUG_LISTS)
+    int list_cap;
+    Ctl* ctl;
+};
+
+void upload_dirs();
+void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
+void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
+void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches);
+void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
+                      float2* facing, float2* lgoal, float* goal_dist, int* num_done, cudaStream_t st,
+                      long long* launches);
+void launch_set_state(const Params* dP, int n, const Buffers& b, const float2* pos, const float2* vel,
+                      const float2* vfh, const float* c3, const float2* facing, const float2* lgoal,
+                      const float* goal_dist, const int* num_done, const float2* goal, const float* min_time, int init,
+                      cudaStream_t st, long long* launches);
+void launch_set_rng(const Params* dP, int n, const Buffers& b, uint32_t base, cudaStream_t st, long long* launches);
+
+}  // namespace lc

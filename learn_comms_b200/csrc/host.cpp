@@ -1,0 +1,148 @@
+// Host-side pieces of the C ABI that never touch the GPU: the comms.config / comms.result file formats
+// (comm.cpp:74-142, pso_opt.py:17-41) and the wall-free part of the scene catalogue (demo.cpp:141-511).
+// Compiled with -ffp-contract=off: initial positions must be bit-identical to the reference's float math.
+#include "../../include/learn_comms.h"
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <functional>
+#include <sstream>
+#include <string>
+
+namespace {
+
+struct Vec2 {
+    float x, y;
+};
+inline Vec2 operator+(Vec2 a, Vec2 b) { return {a.x + b.x, a.y + b.y}; }
+inline Vec2 operator-(Vec2 a, Vec2 b) { return {a.x - b.x, a.y - b.y}; }
+inline Vec2 operator*(Vec2 a, float s) { return {a.x * s, a.y * s}; }
+inline Vec2 operator-(Vec2 a) { return {-a.x, -a.y}; }
+
+// libstdc++ std::minstd_rand0 + std::uniform_real_distribution<float> (Seeder.cpp:5-20), restated so the
+// catalogue does not depend on the C++ runtime's distribution algorithm staying the same.
+struct Lcg {
+    uint32_t x;
+    explicit Lcg(uint64_t seed) {
+        uint64_t s = seed % 2147483647ull;
+        x = s == 0 ? 1u : (uint32_t)s;
+    }
+    float uniform(float a, float b) {
+        x = (uint32_t)(((uint64_t)x * 16807ull) % 2147483647ull);
+        float ret = (float)(x - 1u) / 2147483648.0f;
+        if (ret >= 1.0f) ret = std::nextafter(1.0f, 0.0f);
+        return ret * (b - a) + a;
+    }
+};
+
+struct Regiment {  // demo.cpp:56-62
+    Vec2 facing, head, spacing;
+    unsigned cols, n;
+};
+Vec2 right_face(const Regiment& r) {  // cross((facing, 0), (0, 0, 1)).xy, demo.cpp:63-65
+    return {r.facing.y * 1.f - 0.f * 0.f, 0.f * 0.f - 1.f * r.facing.x};
+}
+Regiment centered(Regiment r) {  // demo.cpp:66-70
+    float half = (r.spacing.x * static_cast<float>(r.cols - 1)) / 2.f;
+    r.head = r.head - right_face(r) * half;
+    return r;
+}
+Vec2 regiment_pos(const Regiment* regs, unsigned i) {  // demo.cpp:77-94
+    unsigned k = 0, last = regs[0].n, j = i;
+    while (j >= last) {
+        j -= last;
+        last = regs[++k].n;
+    }
+    float u = regs[k].spacing.x * static_cast<float>(j % regs[k].cols);
+    float v = regs[k].spacing.y * static_cast<float>(j / regs[k].cols);
+    return right_face(regs[k]) * u + (-regs[k].facing) * v + regs[k].head;
+}
+Vec2 radial_pos(unsigned i, unsigned num, float radius) {  // demo.cpp:48-54
+    const float pi = 3.14159265358979323846264338327950288f;
+    float radian = static_cast<float>(i) / static_cast<float>(num) * 2.f * pi;
+    return Vec2{std::cos(radian), std::sin(radian)} * radius;
+}
+Vec2 axial_goal(Vec2 p) {  // demo.cpp:36-41
+    float d = std::fabs(p.x) - std::fabs(p.y);
+    int axis = (0.f < d) - (d < 0.f);
+    if (axis == 0) axis = 1;
+    float f = static_cast<float>(axis);
+    return {-f * p.x, f * p.y};
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
+                 uint32_t* rng_state_after) {
+    int32_t n;
+    float md;
+    switch (scene) {
+    case 0: n = 60; md = 45.f; break;   // demo.cpp:145-151
+    case 1: n = 90; md = 70.f; break;   // demo.cpp:153-159
+    case 4: n = 56; md = 40.f; break;   // demo.cpp:189-195
+    case 5: n = 56; md = 70.f; break;   // demo.cpp:197-203
+    case 12: n = 200; md = 30.f; break; // demo.cpp:356-373
+    default: return LC_ERR_ARG;         // walled scenes: SURVEY §8f-2, not built yet
+    }
+    if (cap < n || !pos || !goal) return LC_ERR_ARG;
+    Lcg rng(seed);
+    Regiment regs[4] = {centered({{1, 0}, {-6.f, 0}, {1.f, 1.f}, 7, 14}), centered({{-1, 0}, {6.f, 0}, {1.f, 1.f}, 7, 14}),
+                        centered({{0, 1}, {0, -6.f}, {1.f, 1.f}, 7, 14}), centered({{0, -1}, {0, 6.f}, {1.f, 1.f}, 7, 14})};
+    for (int32_t i = 0; i < n; ++i) {
+        Vec2 p{}, g{};
+        if (scene == 0) { p = radial_pos((unsigned)i, 60, 10.f); g = -p; }
+        else if (scene == 1) { p = radial_pos((unsigned)i, 90, 13.f); g = -p; }
+        else if (scene == 4) { p = regiment_pos(regs, (unsigned)i); g = axial_goal(p); }
+        else if (scene == 5) { p = regiment_pos(regs, (unsigned)i); g = -p; }
+        else {
+            // glm::vec2(inside(gen), inside(gen)): g++ evaluates the arguments right to left (verified with O-ref)
+            p.y = rng.uniform(-10.f, 10.f); p.x = rng.uniform(-10.f, 10.f);
+            g.y = rng.uniform(-10.f, 10.f); g.x = rng.uniform(-10.f, 10.f);
+        }
+        pos[2 * i] = p.x; pos[2 * i + 1] = p.y;
+        goal[2 * i] = g.x; goal[2 * i + 1] = g.y;
+    }
+    if (max_duration) *max_duration = md;
+    if (rng_state_after) *rng_state_after = rng.x;
+    return n;
+}
+
+// comm.cpp:80-121: 3 rows of 8 tokens (M_c | M_vy M_s M_py M_d M_g), then 2 rows whose first 3 tokens are M_f.
+// Tokens are separated by single spaces (std::getline(sl, item, ' ')) and parsed with std::stof.
+int32_t lc_read_config(const char* path, float* m_cv, float* m_f) {
+    if (!path || !m_cv || !m_f) return LC_ERR_ARG;
+    std::ifstream in(path);
+    if (!in) return LC_ERR_IO;  // the reference dereferences an empty optional here (comm.cpp:78)
+    std::string line;
+    for (int row = 0; row < 5; ++row) {
+        if (!std::getline(in, line)) line.clear();
+        std::stringstream sl(line);
+        std::string item;
+        const int ncol = row < 3 ? 8 : 3;
+        for (int col = 0; col < ncol; ++col) {
+            std::getline(sl, item, ' ');
+            float v;
+            try {
+                v = std::stof(item);
+            } catch (...) {
+                return LC_ERR_IO;  // reference: uncaught std::invalid_argument aborts the process
+            }
+            if (row < 3) m_cv[8 * row + col] = v; else m_f[3 * (row - 3) + col] = v;
+        }
+    }
+    return LC_OK;
+}
+
+// comm.cpp:136-142: default ostream formatting (6 significant digits), avg_velocity then mean + 3 sigma
+int32_t lc_write_result(const char* path, float avg_velocity, float group_time) {
+    if (!path) return LC_ERR_ARG;
+    std::ofstream out(path);
+    if (!out) return LC_ERR_IO;
+    out << avg_velocity << "\n" << group_time << "\n";
+    return out.good() ? LC_OK : LC_ERR_IO;
+}
+
+}  // extern "C"
