@@ -88,6 +88,10 @@ int32_t lc_get_counters(lc_sim* sim, int64_t* overlap_pairs, int64_t* collision_
 int32_t lc_timer_start(lc_sim* sim);
 int32_t lc_timer_stop(lc_sim* sim, float* milliseconds);
 int64_t lc_kernel_launches(lc_sim* sim); /* kernels launched by this handle so far */
+/* nframes frames launched kernel by kernel (no graph) with a CUDA event between launches; ms_per_kernel[6] receives
+ * the mean device time of k_frame_begin, k_bin, k_scan_hull, k_reorder, k_force, k_collide (roofline accounting) */
+#define LC_FRAME_KERNELS 6
+int32_t lc_step_profiled(lc_sim* sim, int32_t nframes, float* ms_per_kernel);
 
 /* ---- batched rollouts: many independent small scenarios / PSO particles in one launch ----
  * replaces pso_opt.py:236-267 simulate_set/simulate (one comm_norender process per (particle, scene)). */

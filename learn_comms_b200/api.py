@@ -33,7 +33,7 @@ EXPORTS = [
     "lc_create", "lc_destroy", "lc_set_weights", "lc_step", "lc_run_to_completion", "lc_sync", "lc_finished",
     "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
-    "lc_kernel_launches", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
+    "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
 ]
 
@@ -66,6 +66,7 @@ def lib():
         L.lc_timer_stop.argtypes = [vp, f32p]
         L.lc_kernel_launches.argtypes = [vp]
         L.lc_kernel_launches.restype = C.c_int64
+        L.lc_step_profiled.argtypes = [vp, i32, vp]
         L.lc_batch_create.argtypes = [C.POINTER(_BatchDesc), C.POINTER(vp)]
         L.lc_batch_destroy.argtypes = [vp]
         L.lc_batch_destroy.restype = None
@@ -244,6 +245,14 @@ class Sim:
         ms = C.c_float()
         _ck(lib().lc_timer_stop(self.h, C.byref(ms)))
         return float(ms.value)
+
+    KERNELS = ("k_frame_begin", "k_bin", "k_scan_hull", "k_reorder", "k_force", "k_collide")
+
+    def step_profiled(self, n=1):
+        """n frames launched kernel by kernel with CUDA events in between -> {kernel: mean ms per launch}."""
+        ms = np.zeros(len(self.KERNELS), np.float32)
+        _ck(lib().lc_step_profiled(self.h, n, _p(ms)))
+        return dict(zip(self.KERNELS, ms.tolist()))
 
     @property
     def launches(self):

@@ -267,12 +267,12 @@ int32_t lc_step(lc_sim* s, int32_t nframes) {
     while (left >= GRAPH_BATCH) {
         CK(cudaGraphLaunch(s->gexec[1], s->st));
         left -= GRAPH_BATCH;
-        s->launches += 6 * GRAPH_BATCH;
+        s->launches += lc::FRAME_KERNELS * GRAPH_BATCH;
     }
     while (left > 0) {
         CK(cudaGraphLaunch(s->gexec[0], s->st));
         --left;
-        s->launches += 6;
+        s->launches += lc::FRAME_KERNELS;
     }
     return LC_OK;
 }
@@ -440,5 +440,27 @@ int32_t lc_timer_stop(lc_sim* s, float* ms) {
 }
 
 int64_t lc_kernel_launches(lc_sim* s) { return s ? s->launches : 0; }
+
+int32_t lc_step_profiled(lc_sim* s, int32_t nframes, float* ms_per_kernel) {
+    SIM_ENTER(s);
+    if (nframes < 0 || !ms_per_kernel) return fail(LC_ERR_ARG, "lc_step_profiled: bad argument");
+    constexpr int K = lc::FRAME_KERNELS;
+    cudaEvent_t ev[K + 1];
+    for (auto& e : ev) CK(cudaEventCreate(&e));
+    double acc[K] = {0};
+    for (int f = 0; f < nframes; ++f) {
+        lc::launch_frame(s->dP, s->n, s->b, s->st, &s->launches, ev);
+        CK(cudaEventSynchronize(ev[K]));
+        for (int k = 0; k < K; ++k) {
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
+            acc[k] += ms;
+        }
+    }
+    for (int k = 0; k < K; ++k) ms_per_kernel[k] = nframes ? (float)(acc[k] / nframes) : 0.f;
+    for (auto& e : ev) cudaEventDestroy(e);
+    CK(cudaGetLastError());
+    return LC_OK;
+}
 
 }  // extern "C"

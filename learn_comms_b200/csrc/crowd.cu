@@ -777,15 +777,23 @@ void upload_dirs() {
     cudaMemcpyToSymbol(c_diry, dy, sizeof dy);
 }
 
-void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
+void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev) {
+    // ev (optional, FRAME_KERNELS + 1 events): per-kernel device timing for bench.py's roofline leg
     cudaMemsetAsync(b.cell_count, 0, sizeof(int) * (CELL_CAP + 1), st);
+    if (ev) cudaEventRecord(ev[0], st);
     k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
+    if (ev) cudaEventRecord(ev[1], st);
     k_bin<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    if (ev) cudaEventRecord(ev[2], st);
     k_scan_hull<<<1, 1024, 0, st>>>(dP, b);
+    if (ev) cudaEventRecord(ev[3], st);
     k_reorder<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    if (ev) cudaEventRecord(ev[4], st);
     k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    if (ev) cudaEventRecord(ev[5], st);
     k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
-    if (launches) *launches += 6;
+    if (ev) cudaEventRecord(ev[6], st);
+    if (launches) *launches += FRAME_KERNELS;
 }
 
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {

@@ -91,7 +91,9 @@ struct Buffers {
 };
 
 void upload_dirs();
-void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
+constexpr int FRAME_KERNELS = 6;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, force, collide
+void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
+                  cudaEvent_t* ev = nullptr);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,

@@ -1,0 +1,164 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI, liblearncomms.so) against O-canon on the same inputs.
+Integer outputs (neighbour lists {j : ttc_ij <= 5}, overlap-pair and collision-hit counts, comm partners, done flags)
+and — because the kernels use the oracle's operation order with FMA contraction off — all float state are compared
+BIT-EXACT (tolerance 0 ulp, stricter than the 4-ulp bound BASELINE.md allows)."""
+import numpy as np
+import pytest
+
+import _oracle
+import learn_comms_b200 as lcb
+from learn_comms_b200 import workloads as wl
+
+pytestmark = pytest.mark.gpu
+
+KEYS = ("pos", "vel", "vfh", "c", "facing", "local_goal", "goal_dist", "num_done")
+
+
+def assert_state_equal(g, o, tag):
+    for k in KEYS:
+        x, y = g[k], o[k]
+        same = np.array_equal(x, y, equal_nan=True) if x.dtype.kind == "f" else np.array_equal(x, y)
+        if not same:
+            d = np.abs(x.astype(np.float64) - y.astype(np.float64))
+            raise AssertionError(f"{tag}: {k} differs, max abs {np.nanmax(d):.3e}, {(d > 0).sum()} elements")
+
+
+def lockstep(pos, goal, md, rng, m_cv, m_f, frames, comm=True, grid=False, lists=True, check_every=1, stencil=0):
+    g = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=comm, debug_lists=lists, stencil=stencil)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=comm, grid=grid)
+    o.record_neighbors(lists)
+    f = 0
+    while f < frames and not o.finished:
+        k = min(check_every, frames - f)
+        g.step(k)
+        o.step(k)
+        f += k
+        assert_state_equal(g.state(), o.state(), f"frame {f}")
+        if comm:
+            assert np.array_equal(g.partners(), o.partners()), f"frame {f}: comm partners differ"
+        assert np.array_equal(g.neighbor_counts(), o.neighbor_counts()), f"frame {f}: neighbour counts differ"
+        if lists:
+            gp, gi = g.neighbor_lists()
+            op, oi = o.neighbor_lists()
+            assert np.array_equal(gp, op) and np.array_equal(gi, oi), f"frame {f}: neighbour lists differ"
+        cg = g.counters()
+        assert cg["overlap_pairs"] == o.overlap_pairs, f"frame {f}: overlap-pair count"
+        assert cg["collision_hits"] == o.collision_hits, f"frame {f}: collision-hit count"
+        assert g.rng == o.rng
+    return g, o
+
+
+@pytest.mark.parametrize("scene_id,wseed", [(0, None), (0, 1), (1, 5), (4, 2), (5, 7), (12, 3)])
+def test_scene_rollout_bit_exact(scene_id, wseed):
+    """Full rollouts of the reference's wall-free scenes to completion: per-frame state, lists and final scores."""
+    pos, goal, md, rng = lcb.scene(scene_id, 0)
+    m_cv, m_f = (None, None) if wseed is None else wl.weights(wseed)
+    g, o = lockstep(pos, goal, md, rng, m_cv, m_f, frames=10 ** 6, check_every=1 if scene_id in (0, 4) else 7)
+    assert g.finished and o.finished and g.frame == o.frame
+    gs, os_ = g.scores(), o.scores()
+    for k in gs:
+        assert gs[k] == os_[k] or (np.isnan(gs[k]) and np.isnan(os_[k])), (k, gs, os_)
+
+
+def test_run_to_completion_matches_stepping():
+    pos, goal, md, rng = lcb.scene(0, 0)
+    m_cv, m_f = wl.weights(11)
+    a = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    frames = a.run_to_completion()
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    k = o.step(10 ** 6)
+    assert frames == k == o.frame
+    assert a.scores() == o.scores()
+
+
+def test_nocomm_flavour():
+    """nocomm_norender (main.cpp:130-132): comm::run compiled out."""
+    pos, goal, md, rng = lcb.scene(4, 0)
+    lockstep(pos, goal, md, rng, None, None, frames=400, comm=False, check_every=5)
+
+
+def test_circle_1k_grid_vs_bruteforce_oracle():
+    """C2 (1 000 agents, r = 80): GPU uniform grid vs the oracle's brute-force all-pairs loop (LMP.cpp:288-304)."""
+    pos, goal, md, rng = wl.circle(1000, 80.0, seed=1)
+    m_cv, m_f = wl.weights(1, 0.1)
+    lockstep(pos, goal, md, rng, m_cv, m_f, frames=60, check_every=6)
+
+
+@pytest.mark.parametrize("stencil", [1, 2, 3])
+def test_stencil_variants_same_result(stencil):
+    """Cell side = cutoff / stencil: the result must not depend on the grid resolution."""
+    pos, goal, md, rng = wl.plaza(4000, 130.0, seed=9, goal_range=30.0)
+    m_cv, m_f = wl.weights(2)
+    lockstep(pos, goal, md, rng, m_cv, m_f, frames=40, check_every=8, stencil=stencil)
+
+
+def test_dense_crowd_collisions():
+    """Agents packed below contact distance: exercises the overlap predicate and push-out (physics.cpp:23-36,
+    BVH.cpp:106-120) with many simultaneous hits, and t = 0 / mag = 20 TTC forces."""
+    rs = np.random.RandomState(4)
+    n = 600
+    pos = rs.uniform(-3, 3, (n, 2)).astype(np.float32)
+    goal = rs.uniform(-3, 3, (n, 2)).astype(np.float32)
+    m_cv, m_f = wl.weights(8)
+    g, o = lockstep(pos, goal, 30.0, 1, m_cv, m_f, frames=30, check_every=1)
+    assert o.overlap_pairs > 0 or o.collision_hits > 0
+
+
+def test_teacher_forced_single_step():
+    """set_state -> one frame -> compare, from states sampled along an oracle trajectory."""
+    pos, goal, md, rng = lcb.scene(12, 0)
+    m_cv, m_f = wl.weights(21)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    g = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    for hop in (1, 50, 133, 200):
+        o.step(hop)
+        st = o.state()
+        g.set_state(**st)
+        g.rng = o.rng
+        o2 = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+        o2.set_state(**st)
+        o2.rng = o.rng
+        g.step(1)
+        o2.step(1)
+        assert_state_equal(g.state(), o2.state(), f"teacher-forced after {hop}")
+        assert np.array_equal(g.partners(), o2.partners())
+        assert np.array_equal(g.neighbor_counts(), o2.neighbor_counts())
+
+
+def test_corridor_grid_oracle_medium():
+    """C4 shape at 1/10 scale (10 000 agents) against the grid-accelerated oracle (itself checked against brute
+    force in the CPU suite)."""
+    pos, goal, md, rng = wl.corridor(cols=100, rows=50, gap=6.0, seed=4)
+    m_cv, m_f = wl.weights(4, 0.5)
+    lockstep(pos, goal, md, rng, m_cv, m_f, frames=24, grid=True, lists=True, check_every=8)
+
+
+def test_full_size_properties_plaza():
+    """C5 full size (1M agents): size-independent properties — determinism (two handles, same bits), permutation
+    invariance of the per-agent result w.r.t. slot order is implied by determinism after re-sorting, id bijection,
+    speed clamp |vel_forehalf| <= 1 up to push-out, and agreement with the grid oracle on a 3-frame prefix."""
+    pos, goal, md, rng = wl.plaza(1_000_000, 2000.0, seed=5)
+    m_cv, m_f = wl.weights(5, 0.5)
+    a = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, free_run=True)
+    b = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, free_run=True, stencil=2)
+    a.step(3)
+    b.step(3)
+    sa, sb = a.state(), b.state()
+    assert_state_equal(sa, sb, "stencil 1 vs 2 at 1M")
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, grid=True)
+    o.step(3, fixed=True)
+    assert_state_equal(sa, o.state(), "1M agents vs grid oracle, 3 frames")
+    assert np.array_equal(a.partners(), o.partners())
+    assert np.array_equal(a.neighbor_counts(), o.neighbor_counts())
+    a.step(60)
+    s = a.state()
+    assert np.isfinite(s["pos"]).all()
+    assert (np.hypot(s["vfh"][:, 0], s["vfh"][:, 1]) <= 1.0 + 1e-3).all()
+
+
+def test_error_paths():
+    pos, goal, md, rng = lcb.scene(0, 0)
+    with pytest.raises(lcb.LcError):
+        lcb.Sim(pos[:1], goal[:1])  # n == 1: reference UB (comm.cpp:273-285) -> LC_ERR_ARG
+    with pytest.raises(lcb.LcError):
+        lcb.Sim(pos, goal, device=99)
