@@ -279,7 +279,7 @@ def main():
                 "config": {"workload": name, "desc": WORKLOADS[name]["desc"], "agents": n * world, "frames_per_step": 1,
                            "parallelism": "single crowd, 1 GPU" if world == 1 else f"{world} independent crowds, one per GPU, no exchange",
                            "l2": "per-frame working set (2 x 88 B x agents + grid) exceeds the 126 MB L2 at 1M agents; no flush"},
-                "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+                "counters": sim.counters(), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()

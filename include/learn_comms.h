@@ -47,7 +47,7 @@ typedef struct lc_desc {
     int32_t device;         /* CUDA device ordinal */
     int32_t n_walls;        /* reserved for walled scenes; must be 0 */
     const lc_rect* walls;
-    int32_t stencil;        /* grid cells per interaction cutoff (0 = default 1): cell side = cutoff / stencil */
+    int32_t stencil;        /* grid cells per interaction cutoff (0 = default 2): cell side = cutoff / stencil */
 } lc_desc;
 
 typedef struct lc_sim lc_sim;
@@ -88,9 +88,9 @@ int32_t lc_get_counters(lc_sim* sim, int64_t* overlap_pairs, int64_t* collision_
 int32_t lc_timer_start(lc_sim* sim);
 int32_t lc_timer_stop(lc_sim* sim, float* milliseconds);
 int64_t lc_kernel_launches(lc_sim* sim); /* kernels launched by this handle so far */
-/* nframes frames launched kernel by kernel (no graph) with a CUDA event between launches; ms_per_kernel[6] receives
- * the mean device time of k_frame_begin, k_bin, k_scan_hull, k_reorder, k_force, k_collide (roofline accounting) */
-#define LC_FRAME_KERNELS 6
+/* nframes frames launched kernel by kernel (no graph) with a CUDA event between launches; ms_per_kernel[7] receives
+ * the mean device time of k_frame_begin, k_bin, k_scan_hull, k_reorder, k_refine, k_force, k_collide (roofline accounting) */
+#define LC_FRAME_KERNELS 7
 int32_t lc_step_profiled(lc_sim* sim, int32_t nframes, float* ms_per_kernel);
 
 /* ---- batched rollouts: many independent small scenarios / PSO particles in one launch ----

@@ -149,10 +149,15 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
     lc::Buffers& b = s->b;
     CKC(dalloc(&b.posf, n)); s->allocs.push_back(b.posf);
     CKC(dalloc(&b.cellrank, n)); s->allocs.push_back(b.cellrank);
-    CKC(dalloc(&b.cell_count, lc::CELL_CAP + 1)); s->allocs.push_back(b.cell_count);
-    CKC(dalloc(&b.cell_start, lc::CELL_CAP + 1)); s->allocs.push_back(b.cell_start);
+    CKC(dalloc(&b.cell_count, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_count);
+    CKC(dalloc(&b.cell_start, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_start);
+    CKC(dalloc(&b.tile_agg, lc::SCAN_TILES)); s->allocs.push_back(b.tile_agg);
+    CKC(cudaMemset(b.tile_agg, 0, sizeof(unsigned long long) * lc::SCAN_TILES));
     CKC(dalloc(&b.slot_of_id, n)); s->allocs.push_back(b.slot_of_id);
     CKC(dalloc(&b.cand, n)); s->allocs.push_back(b.cand);
+    CKC(dalloc(&b.cand2, lc::REFINE_MAX)); s->allocs.push_back(b.cand2);
+    CKC(dalloc(&b.blkred, (size_t)(n + 127) / 128)); s->allocs.push_back(b.blkred);
+    CKC(dalloc(&b.blkext, (size_t)((n + 1023) / 1024) * lc::HULL_K)); s->allocs.push_back(b.blkext);
     CKC(dalloc(&b.near_cnt, n)); s->allocs.push_back(b.near_cnt);
     CKC(dalloc(&b.near_idx, (size_t)n * lc::MAX_NEAR)); s->allocs.push_back(b.near_idx);
     CKC(dalloc(&b.events, n)); s->allocs.push_back(b.events);
@@ -184,11 +189,12 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
     {   // pairs that can overlap after this frame's move: both agents travel <= dt (|vel_forehalf| <= 1 after the clamp)
         float reach = P.R + 2.f * (1.f / 60.f) * 1.01f + 0.002f;
         P.near_c = reach * reach - P.RR;
+        P.near_reach = reach + 0.002f;
     }
     P.max_duration = d->max_duration;
     P.lcg_stride = lcg_pow(16807u, (uint64_t)n);
     P.flags = d->flags;
-    P.stencil_req = d->stencil > 0 ? d->stencil : 1;
+    P.stencil_req = d->stencil > 0 ? d->stencil : 2;
     memset(P.m_cv, 0, sizeof P.m_cv);
     memset(P.m_f, 0, sizeof P.m_f);
     if (d->m_cv) memcpy(P.m_cv, d->m_cv, sizeof P.m_cv);
@@ -421,7 +427,7 @@ int32_t lc_get_counters(lc_sim* s, int64_t* overlap_pairs, int64_t* collision_hi
     if (rc) return rc;
     if (overlap_pairs) *overlap_pairs = (int64_t)(s->hctl->overlap2 / 2);
     if (collision_hits) *collision_hits = (int64_t)s->hctl->coll_hits;
-    if (candidates) *candidates = s->hctl->n_cand;
+    if (candidates) *candidates = s->hctl->n_cand2;
     return LC_OK;
 }
 

@@ -5,10 +5,15 @@
 
 namespace lc {
 
-constexpr int HULL_K = 16;        // directional extremes used to prune comm-partner candidates
+constexpr int HULL_K = 16;        // directional extremes used to prune comm-partner candidates (stage 1, all agents)
+constexpr int HULL_K2 = 256;      // stage 2, over the stage-1 survivors only
+constexpr int REFINE_MAX = 1 << 16; // stage 2 is skipped when stage 1 leaves more than this many candidates
 constexpr int MAX_HITS = 48;      // per-thread buffer of interacting neighbours (sorted by id before summation)
 constexpr int MAX_NEAR = 8;       // per-agent list of neighbours close enough to collide this frame
 constexpr int CELL_CAP = 1 << 18; // max grid cells (cell side grows beyond the cutoff if exceeded)
+constexpr int SCAN_TILE = 4096;   // cells scanned per block of k_scan_hull
+constexpr int SCAN_TILES = CELL_CAP / SCAN_TILE + 1;  // tiles cover indices [0, ncells] inclusive
+constexpr int CELL_ALLOC = SCAN_TILES * SCAN_TILE;    // allocation of cell_count / cell_start
 constexpr int EV_SORT_CAP = 2048; // events sorted in shared memory; above this the per-id path is used
 
 // One copy of the per-agent state, structure of arrays.  All arrays have n elements.
@@ -29,6 +34,12 @@ struct AgentArrays {
     int4* meta;
 };
 
+// per-block partial reductions of k_collide / k_init_reduce (128-thread blocks), folded by the next k_frame_begin
+struct BlockRed {
+    uint32_t minx, miny, maxx, maxy, vmax, pad;
+    unsigned long long lastvel;
+};
+
 struct Ctl {
     // frame / latch (main.cpp:98-150)
     uint32_t frame;
@@ -44,6 +55,7 @@ struct Ctl {
     int n_edges;
     float ex[HULL_K], ey[HULL_K], enx[HULL_K], eny[HULL_K];
     int n_cand;
+    int n_cand2, cand_sel;   // list k_force scans: cand_sel ? cand2 : cand, n_cand2 entries
     // reductions over the final positions / velocities of the frame (consumed by the next frame_begin)
     uint32_t minx, miny, maxx, maxy, vmax;
     // scoring: demo.cpp:650-702, physics.cpp:72-76
@@ -52,6 +64,7 @@ struct Ctl {
     unsigned long long lastvel;  // ((id + 1) << 32) | speed bits of the highest-id not-done agent this frame
     int nonfinite;               // some earlier not-done agent had a non-finite speed (sticky NaN of physics.cpp:75)
     int n_not_done, nnd_acc;
+    int n_blkred;                // BlockRed entries waiting to be folded
     int ev_count;
     int replan1, replan2;        // ai.cpp:151-168: first two agents (table order) that need a replan
     // counters (diagnostics)
@@ -61,7 +74,7 @@ struct Ctl {
 
 struct Params {
     int n;
-    float r, R, RR, near_c;
+    float r, R, RR, near_c, near_reach;
     float max_duration;
     uint32_t lcg_stride;  // 16807^n mod (2^31-1): advances an agent's private stream by one frame
     uint32_t flags;
@@ -75,10 +88,14 @@ struct Buffers {
     AgentArrays srt;   // frame-start state reordered by grid cell
     float2* posf;      // final (post-push) positions, same order as cur
     int2* cellrank;    // (cell, rank within cell) per agent, cur order
-    int* cell_count;   // [CELL_CAP + 1]
-    int* cell_start;   // [CELL_CAP + 1]
+    int* cell_count;   // [CELL_ALLOC]
+    int* cell_start;   // [CELL_ALLOC]
+    unsigned long long* tile_agg; // [SCAN_TILES] (frame << 32) | tile total, published by k_scan_hull
     int* slot_of_id;   // inverse permutation
     float4* cand;      // comm-partner candidates: (x, z, id bits, slot bits)
+    BlockRed* blkred;  // [ceil(n / 128)]
+    unsigned long long* blkext; // [ceil(n / 1024)][HULL_K] per-block directional extremes of k_bin
+    float4* cand2;     // [REFINE_MAX] after the second pruning stage
     int* near_cnt;     // [n]
     int* near_idx;     // [n][MAX_NEAR]
     int2* events;      // (id, min_time bits) of agents that became done this frame
@@ -91,7 +108,7 @@ struct Buffers {
 };
 
 void upload_dirs();
-constexpr int FRAME_KERNELS = 6;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, force, collide
+constexpr int FRAME_KERNELS = 7;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, force, collide
 void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
                   cudaEvent_t* ev = nullptr);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);

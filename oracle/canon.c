@@ -416,6 +416,8 @@ static void update_agents(canon_sim* s) {
     int stencil = 1;
     if (s->use_grid) {
         float cutoff = R + 10.f * max_speed(s) * 1.001f + 0.01f;
+        /* the collision pass reuses this grid with a +-1 cell block: two agents each move <= dt per frame */
+        cutoff = fmaxf(cutoff, R + 2.f * (1.f / 60.f) * 1.01f + 0.004f);
         grid_build(s, cutoff);
         stencil = (int)ceilf(cutoff / g_grid.h);
     }

@@ -157,6 +157,28 @@ def test_oracle_grid_equals_bruteforce(seed):
         assert a.overlap_pairs == b.overlap_pairs and a.collision_hits == b.collision_hits
 
 
+def test_oracle_grid_equals_bruteforce_dense_from_rest():
+    """Packed crowd starting at rest: v_max = 0 makes the TTC cutoff (0.31 m) smaller than the contact reach of the
+    collision pass (0.3 + 2 dt); the grid must still find every pair that overlaps after the move."""
+    rs = np.random.RandomState(4)
+    n = 600
+    pos = rs.uniform(-3, 3, (n, 2)).astype(np.float32)
+    goal = rs.uniform(-3, 3, (n, 2)).astype(np.float32)
+    m_cv, m_f = wl.weights(8)
+    a = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=30.0, rng_state=1, grid=False)
+    b = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=30.0, rng_state=1, grid=True)
+    hits = 0
+    for f in range(12):
+        a.step(1)
+        b.step(1)
+        sa, sb = a.state(), b.state()
+        for k in sa:
+            assert np.array_equal(sa[k], sb[k], equal_nan=True), (f, k)
+        assert a.overlap_pairs == b.overlap_pairs and a.collision_hits == b.collision_hits
+        hits += a.collision_hits
+    assert hits > 0
+
+
 def test_neighbor_predicate_symmetry():
     """ttc(i,j) == ttc(j,i) bit for bit: neighbour lists are symmetric."""
     pos, goal, md, rng = _oracle.scene(12, 0)
