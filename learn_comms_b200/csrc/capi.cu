@@ -148,6 +148,8 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
     CKB(alloc_arrays(s, s->b.srt, n));
     lc::Buffers& b = s->b;
     CKC(dalloc(&b.posf, n)); s->allocs.push_back(b.posf);
+    CKC(dalloc(&b.srt_pq, (size_t)2 * ((n + 1) / 2))); s->allocs.push_back(b.srt_pq);
+    CKC(cudaMemset(b.srt_pq, 0, sizeof(float4) * 2 * ((size_t)(n + 1) / 2)));
     CKC(dalloc(&b.cellrank, n)); s->allocs.push_back(b.cellrank);
     CKC(dalloc(&b.cell_count, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_count);
     CKC(dalloc(&b.cell_start, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_start);

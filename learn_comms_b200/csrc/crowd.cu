@@ -370,6 +370,10 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     const int4 mt = b.cur.meta[i];
     const float2 g = b.cur.goal[i];
     b.srt.pv[s] = make_float4(p.x, p.y, pv.z, pv.w);
+    {   // pair-interleaved copy for the packed pair loop: slots (2k, 2k+1) -> (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
+        float* q = reinterpret_cast<float*>(b.srt_pq + 2 * (s >> 1)) + (s & 1);
+        q[0] = p.x; q[2] = p.y; q[4] = pv.z; q[6] = pv.w;
+    }
     b.srt.vfh[s] = b.cur.vfh[i];
     b.srt.goal[s] = g;
     b.srt.lgoal[s] = b.cur.lgoal[i];
@@ -479,37 +483,55 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
     ix = min(max(ix, 0), nx - 1);
     iy = min(max(iy, 0), ny - 1);
     const int x_lo = max(ix - st, 0), x_hi = min(ix + st, nx - 1);
+    const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
+    const float2 RR2 = make_float2(RR, RR);
+    const float4* __restrict__ pq = b.srt_pq;
+    // One candidate of a pair beyond the fast reject: LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame
+    // (same operations as lc_math.cuh ttc_pair), the near list of the collision pass, and the force on a hit.
+    auto slow = [&](int j, float bq, float c, float a, float disc) {
+        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f;
+        const bool near = FIRST && c < near_c;
+        if (miss && !near) return;
+        if (j == s) return;  // the self pair (m = dv = 0) always reaches this point
+        if (near) {
+            if (n_near < MAX_NEAR) b.near_idx[(size_t)s * MAX_NEAR + n_near] = j;
+            ++n_near;
+            if (c < 0.f) ++n_overlap;  // BoundVolume.cpp:203-207 on frame-start positions
+        }
+        if (miss) return;
+        float t = __fdiv_rn(__fsub_rn(-bq, __fsqrt_rn(disc)), a);
+        if (t < 0.f) t = 0.f;
+        if (!(t >= 0.f)) return;  // NaN -> FLT_MAX (LMP.cpp:31-34)
+        if (t > 5.0f) return;     // (double)ttc > 5.0 (LMP.cpp:297-300)
+        const float4 q = __ldg(&b.srt.pv[j]);
+        float fx, fy;
+        ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
+        f(j, fx, fy);
+    };
     for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
         const int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
-        const float4* __restrict__ pvs = b.srt.pv;
-        for (int j = j0; j < j1; ++j) {
-            const float4 q = __ldg(pvs + j);
-            const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py);
-            const float dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
-            // LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame (lc_math.cuh ttc_pair, split so that the
-            // common outcomes leave the loop body after the fewest instructions)
-            const float bq = dot2(mx, my, dvx, dvy);
-            const float c = __fsub_rn(dot2(mx, my, mx, my), RR);
-            if (bq > 0.f && c >= near_c) continue;  // separating and not in contact range: near_c > 0, so c > 0 && b > 0
-            const float a = dot2(dvx, dvy, dvx, dvy);
-            const float disc = __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c));
-            const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f;
-            const bool near = FIRST && c < near_c;
-            if (miss && !near) continue;
-            if (j == s) continue;  // the self pair (m = dv = 0) always reaches this point
-            if (near) {
-                if (n_near < MAX_NEAR) b.near_idx[(size_t)s * MAX_NEAR + n_near] = j;
-                ++n_near;
-                if (c < 0.f) ++n_overlap;  // BoundVolume.cpp:203-207 on frame-start positions
-            }
-            if (miss) continue;
-            float t = __fdiv_rn(__fsub_rn(-bq, __fsqrt_rn(disc)), a);
-            if (t < 0.f) t = 0.f;
-            if (!(t >= 0.f)) continue;  // NaN -> FLT_MAX (LMP.cpp:31-34)
-            if (t > 5.0f) continue;     // (double)ttc > 5.0 (LMP.cpp:297-300)
-            float fx, fy;
-            ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
-            f(j, fx, fy);
+        // two candidates per iteration: slots (2 jp, 2 jp + 1) are stored as (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
+        for (int jp = j0 >> 1; jp < ((j1 + 1) >> 1); ++jp) {
+            const float4 P4 = __ldg(pq + 2 * jp), V4 = __ldg(pq + 2 * jp + 1);
+            const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
+            const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
+            // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under -fmad=false, which would round once instead
+            // of twice: every sum that consumes a product is therefore a SCALAR __fadd_rn / __fsub_rn (never contracted);
+            // packed adds only ever consume loads or other sums.  tests/test_oracle_cpu.py checks the SASS for FFMA2.
+            const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
+            const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
+            const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
+            // fast reject: separating and not in contact range (near_c > 0, so this implies c > 0 && b > 0), or a
+            // slot of the pair that lies outside [j0, j1)
+            const bool skip0 = (bq.x > 0.f && c.x >= near_c) || 2 * jp < j0;
+            const bool skip1 = (bq.y > 0.f && c.y >= near_c) || 2 * jp + 1 >= j1;
+            if (skip0 && skip1) continue;
+            const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
+            const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
+            const float2 bb = mul2(bq, bq), ac = mul2(a, c);
+            const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
+            if (!skip0) slow(2 * jp, bq.x, c.x, a.x, disc.x);
+            if (!skip1) slow(2 * jp + 1, bq.y, c.y, a.y, disc.y);
         }
     }
 }
@@ -520,6 +542,53 @@ __global__ void __launch_bounds__(128) k_force(const Params* __restrict__ P, Buf
     const int n = P->n;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     int not_done_after = 0;
+    // Third pruning stage of the comm-partner candidates, per block: the 128 agents of a block are neighbours in cell
+    // order, so they share a small bounding box B.  Candidate k can be the arg-max of comm.cpp:201-220 for some query
+    // in B only if max_{q in B} |q - k|^2 is not below L = max_k' min_{q in B} |q - k'|^2 (1e-4 relative slack >> the
+    // float rounding of length2).  Survivors are staged in shared memory; typically a handful remain.
+    __shared__ float4 s_cand[CAND_SMEM];
+    __shared__ uint32_t s_bb[5];
+    __shared__ int s_nc;
+    const float4* __restrict__ cand = nullptr;
+    int ncand = 0;
+    if (!(P->flags & 1u)) {
+        const int nc = ctl->n_cand2;
+        const float4* __restrict__ gc = ctl->cand_sel ? b.cand2 : b.cand;
+        if (threadIdx.x == 0) { s_bb[0] = s_bb[1] = 0xffffffffu; s_bb[2] = s_bb[3] = 0u; s_bb[4] = 0u; s_nc = 0; }
+        __syncthreads();
+        const bool valid = s < n;
+        const float4 me0 = valid ? b.srt.pv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint32_t mnx = __reduce_min_sync(0xffffffffu, valid ? f2ord(me0.x) : 0xffffffffu);
+        const uint32_t mxx = __reduce_max_sync(0xffffffffu, valid ? f2ord(me0.x) : 0u);
+        const uint32_t mny = __reduce_min_sync(0xffffffffu, valid ? f2ord(me0.y) : 0xffffffffu);
+        const uint32_t mxy = __reduce_max_sync(0xffffffffu, valid ? f2ord(me0.y) : 0u);
+        if ((threadIdx.x & 31) == 0) {
+            atomicMin(&s_bb[0], mnx); atomicMin(&s_bb[1], mny); atomicMax(&s_bb[2], mxx); atomicMax(&s_bb[3], mxy);
+        }
+        __syncthreads();
+        const float bx0 = ord2f(s_bb[0]), by0 = ord2f(s_bb[1]), bx1 = ord2f(s_bb[2]), by1 = ord2f(s_bb[3]);
+        float lmax = 0.f;
+        for (int k = threadIdx.x; k < nc; k += blockDim.x) {
+            const float4 cd = __ldg(&gc[k]);
+            const float dx = fmaxf(fmaxf(bx0 - cd.x, cd.x - bx1), 0.f), dy = fmaxf(fmaxf(by0 - cd.y, cd.y - by1), 0.f);
+            const float d2 = dx * dx + dy * dy;
+            lmax = d2 > lmax || d2 != d2 ? d2 : lmax;  // NaN propagates: then nothing is pruned
+        }
+        atomicMax(&s_bb[4], __float_as_uint(lmax));  // d2 >= 0 (or NaN, whose bits sort above every finite value)
+        __syncthreads();
+        const float L = __uint_as_float(s_bb[4]);
+        for (int k = threadIdx.x; k < nc; k += blockDim.x) {
+            const float4 cd = __ldg(&gc[k]);
+            const float dx = fmaxf(fabsf(cd.x - bx0), fabsf(cd.x - bx1)), dy = fmaxf(fabsf(cd.y - by0), fabsf(cd.y - by1));
+            const float d2 = (dx * dx + dy * dy) * 1.0001f;
+            if (!(d2 < L)) {
+                const int q = atomicAdd(&s_nc, 1);
+                if (q < CAND_SMEM) s_cand[q] = cd;
+            }
+        }
+        __syncthreads();
+        if (s_nc <= CAND_SMEM) { cand = s_cand; ncand = s_nc; } else { cand = gc; ncand = nc; }
+    }
     if (s < n) {
         const float4 me = b.srt.pv[s];
         const float px = me.x, py = me.y, vx = me.z, vy = me.w;
@@ -535,12 +604,10 @@ __global__ void __launch_bounds__(128) k_force(const Params* __restrict__ P, Buf
         // ---- S1: comm::run (comm.cpp:267-305) ----
         if (!(P->flags & 1u)) {
             // comm.cpp:201-220 select_nearest == arg-max of squared distance (quirk Q1), strict '>', first in table order
-            const int nc = ctl->n_cand2;
-            const float4* __restrict__ cand = ctl->cand_sel ? b.cand2 : b.cand;
             float best = LC_FLT_MIN;
             int best_id = -1, best_slot = s;
-            for (int k = 0; k < nc; ++k) {
-                const float4 cd = __ldg(&cand[k]);
+            for (int k = 0; k < ncand; ++k) {
+                const float4 cd = cand[k];
                 const int cid = __float_as_int(cd.z);
                 if (cid == id) continue;
                 const float dx = __fsub_rn(cd.x, px), dy = __fsub_rn(cd.y, py);

@@ -7,6 +7,7 @@ namespace lc {
 
 constexpr int HULL_K = 16;        // directional extremes used to prune comm-partner candidates (stage 1, all agents)
 constexpr int HULL_K2 = 256;      // stage 2, over the stage-1 survivors only
+constexpr int CAND_SMEM = 128;     // per-block candidate list of k_force (stage 3); falls back to the global list beyond
 constexpr int REFINE_MAX = 1 << 16; // stage 2 is skipped when stage 1 leaves more than this many candidates
 constexpr int MAX_HITS = 48;      // per-thread buffer of interacting neighbours (sorted by id before summation)
 constexpr int MAX_NEAR = 8;       // per-agent list of neighbours close enough to collide this frame
@@ -86,6 +87,7 @@ struct Params {
 struct Buffers {
     AgentArrays cur;   // state at frame start (arbitrary slot order) / K4 output (pre-push), new slot order
     AgentArrays srt;   // frame-start state reordered by grid cell
+    float4* srt_pq;    // [2 * ceil(n/2)] pair-interleaved copy of srt.pv: (x0,x1,z0,z1), (vx0,vx1,vz0,vz1) per slot pair
     float2* posf;      // final (post-push) positions, same order as cur
     int2* cellrank;    // (cell, rank within cell) per agent, cur order
     int* cell_count;   // [CELL_ALLOC]

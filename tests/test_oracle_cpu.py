@@ -270,3 +270,17 @@ def test_no_device_fails_loudly():
     with pytest.raises(lcb.LcError) as e:
         lcb.Sim(pos, goal)
     assert e.value.code == -2
+
+
+def test_no_packed_fma_in_sass():
+    """ptxas contracts packed mul + add into FFMA2 even under -fmad=false (single rounding -> neighbour lists would
+    differ from the reference's SSE2 mul/add).  The kernels avoid the pattern; make sure no FFMA2 ever reappears."""
+    import shutil
+    from learn_comms_b200 import build
+    so = build.build()
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.check_output([cuobjdump, "-sass", so], text=True)
+    assert "FMUL2" in sass and "FADD2" in sass  # the packed pair loop is there
+    assert "FFMA2" not in sass
