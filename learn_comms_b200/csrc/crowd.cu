@@ -488,8 +488,8 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
     const float4* __restrict__ pq = b.srt_pq;
     // One candidate of a pair beyond the fast reject: LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame
     // (same operations as lc_math.cuh ttc_pair), the near list of the collision pass, and the force on a hit.
-    auto slow = [&](int j, float bq, float c, float a, float disc) {
-        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f;
+    auto slow = [&](int j, float bq, float c, float a, float disc, bool far) {
+        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
         const bool near = FIRST && c < near_c;
         if (miss && !near) return;
         if (j == s) return;  // the self pair (m = dv = 0) always reaches this point
@@ -508,11 +508,24 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
         f(j, fx, fy);
     };
+    // scalar version for the odd slot at either end of a row range
+    auto single = [&](int j) {
+        const float4 q = __ldg(&b.srt.pv[j]);
+        const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
+        const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
+        if (bq > 0.f && c >= near_c) return;
+        const float a = dot2(dvx, dvy, dvx, dvy);
+        slow(j, bq, c, a, __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c)), false);
+    };
     for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
-        const int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
-        // two candidates per iteration: slots (2 jp, 2 jp + 1) are stored as (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
-        for (int jp = j0 >> 1; jp < ((j1 + 1) >> 1); ++jp) {
-            const float4 P4 = __ldg(pq + 2 * jp), V4 = __ldg(pq + 2 * jp + 1);
+        int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
+        if (j0 >= j1) continue;
+        if (j0 & 1) single(j0++);
+        if ((j1 & 1) && j1 > j0) single(--j1);
+        // two candidates per iteration: slots (j, j + 1), j even, are stored as (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
+        const float4* __restrict__ pp = pq + j0;
+        for (int j = j0; j < j1; j += 2, pp += 2) {
+            const float4 P4 = __ldg(pp), V4 = __ldg(pp + 1);
             const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
             const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
             // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under -fmad=false, which would round once instead
@@ -521,22 +534,30 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
             const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
             const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
             const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
-            // fast reject: separating and not in contact range (near_c > 0, so this implies c > 0 && b > 0), or a
-            // slot of the pair that lies outside [j0, j1)
-            const bool skip0 = (bq.x > 0.f && c.x >= near_c) || 2 * jp < j0;
-            const bool skip1 = (bq.y > 0.f && c.y >= near_c) || 2 * jp + 1 >= j1;
+            // fast reject: separating and not in contact range (near_c > 0, so this implies c > 0 && b > 0)
+            const bool skip0 = bq.x > 0.f && c.x >= near_c;
+            const bool skip1 = bq.y > 0.f && c.y >= near_c;
             if (skip0 && skip1) continue;
             const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
             const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
             const float2 bb = mul2(bq, bq), ac = mul2(a, c);
             const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
-            if (!skip0) slow(2 * jp, bq.x, c.x, a.x, disc.x);
-            if (!skip1) slow(2 * jp + 1, bq.y, c.y, a.y, disc.y);
+            // Conservative "t > 5" filter, so that sqrt + division only run for near-certain neighbours.  With c >= 0 and
+            // b <= 0: t = (-b - sqrt(disc)) / a > 5  <=>  u = -b - 5a > sqrt(disc).  Requiring u > 0 and
+            // u^2 > disc + 1e-4 b^2 leaves u - sqrt(disc) > 5e-5 |b|, two orders of magnitude above the rounding error of
+            // the reference's float evaluation of t, so no pair with float ttc <= 5 is ever filtered.
+            const float2 a5 = mul2(a, make_float2(5.f, 5.f));
+            const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));  // scalar: keeps the SASS free of FFMA2
+            const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
+            const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+            const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+            if (!skip0) slow(j, bq.x, c.x, a.x, disc.x, far0);
+            if (!skip1) slow(j + 1, bq.y, c.y, a.y, disc.y, far1);
         }
     }
 }
 
-__global__ void __launch_bounds__(128) k_force(const Params* __restrict__ P, Buffers b) {
+__global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P, Buffers b) {
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int n = P->n;
@@ -592,8 +613,57 @@ __global__ void __launch_bounds__(128) k_force(const Params* __restrict__ P, Buf
     if (s < n) {
         const float4 me = b.srt.pv[s];
         const float px = me.x, py = me.y, vx = me.z, vy = me.w;
+        const int id = b.srt.meta[s].x;
+
+        // The pair loop runs first, while only (pos, vel, id) are live, so that it gets by with few registers; the
+        // rest of the agent's state is loaded after it.  Order of the float operations is unaffected.
+        // LMP.cpp:288-304: TTC forces, summed in table (id) order
+        int hid[MAX_HITS];
+        float hfx[MAX_HITS], hfy[MAX_HITS];
+        int cnt = 0, n_near = 0, n_overlap = 0;
+        scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap,
+                              [&](int j, float fx, float fy) {
+                                  if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
+                                  ++cnt;
+                              });
+        float ttcFx = 0.f, ttcFy = 0.f;
+        int* lst = (P->flags & 4u) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
+        if (cnt <= MAX_HITS) {
+            int last = -1;
+            for (int k = 0; k < cnt; ++k) {
+                int bi = 0, bid = 0x7fffffff;
+                for (int q = 0; q < cnt; ++q) {
+                    int v = hid[q];
+                    if (v > last && v < bid) { bid = v; bi = q; }
+                }
+                ttcFx = __fadd_rn(ttcFx, hfx[bi]);
+                ttcFy = __fadd_rn(ttcFy, hfy[bi]);
+                last = bid;
+                if (lst && k < b.list_cap) lst[k] = bid;
+            }
+        } else {  // rare: more interacting neighbours than the register buffer holds — re-scan per neighbour
+            atomicAdd(&ctl->hit_overflow, 1);
+            int last = -1, dummy0 = 0, dummy1 = 0;
+            for (int k = 0; k < cnt; ++k) {
+                int bid = 0x7fffffff;
+                float bfx = 0.f, bfy = 0.f;
+                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1,
+                                       [&](int j, float fx, float fy) {
+                                           int v = __ldg(&b.srt.meta[j].x);
+                                           if (v > last && v < bid) { bid = v; bfx = fx; bfy = fy; }
+                                       });
+                ttcFx = __fadd_rn(ttcFx, bfx);
+                ttcFy = __fadd_rn(ttcFy, bfy);
+                last = bid;
+                if (lst && k < b.list_cap) lst[k] = bid;
+            }
+        }
+        b.nbr_cnt[id] = cnt;
+        if (n_near > MAX_NEAR) atomicAdd(&ctl->near_overflow, 1);
+        b.near_cnt[s] = n_near;
+        if (n_overlap) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
+
         int4 mt = b.srt.meta[s];
-        const int id = mt.x;
         const float2 goal = b.srt.goal[s];
         float2 lgoal = b.srt.lgoal[s];
         float2 facing = b.srt.facing[s];
@@ -695,51 +765,6 @@ __global__ void __launch_bounds__(128) k_force(const Params* __restrict__ P, Buf
         const float gvx = __fmul_rn(1.0f, __fdiv_rn(dgx, dl)), gvy = __fmul_rn(1.0f, __fdiv_rn(dgy, dl));
         const float goalFx = __fmul_rn(2.0f, __fsub_rn(gvx, vx)), goalFy = __fmul_rn(2.0f, __fsub_rn(gvy, vy));
 
-        // LMP.cpp:288-304: TTC forces, summed in table (id) order
-        int hid[MAX_HITS];
-        float hfx[MAX_HITS], hfy[MAX_HITS];
-        int cnt = 0, n_near = 0, n_overlap = 0;
-        scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap,
-                              [&](int j, float fx, float fy) {
-                                  if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
-                                  ++cnt;
-                              });
-        float ttcFx = 0.f, ttcFy = 0.f;
-        int* lst = (P->flags & 4u) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
-        if (cnt <= MAX_HITS) {
-            int last = -1;
-            for (int k = 0; k < cnt; ++k) {
-                int bi = 0, bid = 0x7fffffff;
-                for (int q = 0; q < cnt; ++q) {
-                    int v = hid[q];
-                    if (v > last && v < bid) { bid = v; bi = q; }
-                }
-                ttcFx = __fadd_rn(ttcFx, hfx[bi]);
-                ttcFy = __fadd_rn(ttcFy, hfy[bi]);
-                last = bid;
-                if (lst && k < b.list_cap) lst[k] = bid;
-            }
-        } else {  // rare: more interacting neighbours than the register buffer holds — re-scan per neighbour
-            atomicAdd(&ctl->hit_overflow, 1);
-            int last = -1, dummy0 = 0, dummy1 = 0;
-            for (int k = 0; k < cnt; ++k) {
-                int bid = 0x7fffffff;
-                float bfx = 0.f, bfy = 0.f;
-                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1,
-                                       [&](int j, float fx, float fy) {
-                                           int v = __ldg(&b.srt.meta[j].x);
-                                           if (v > last && v < bid) { bid = v; bfx = fx; bfy = fy; }
-                                       });
-                ttcFx = __fadd_rn(ttcFx, bfx);
-                ttcFy = __fadd_rn(ttcFy, bfy);
-                last = bid;
-                if (lst && k < b.list_cap) lst[k] = bid;
-            }
-        }
-        b.nbr_cnt[id] = cnt;
-        if (n_near > MAX_NEAR) atomicAdd(&ctl->near_overflow, 1);
-        b.near_cnt[s] = n_near;
-        if (n_overlap) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
         forcex = __fadd_rn(forcex, __fadd_rn(goalFx, ttcFx));  // ai.cpp:172
         forcey = __fadd_rn(forcey, __fadd_rn(goalFy, ttcFy));
 
