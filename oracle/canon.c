@@ -77,6 +77,9 @@ struct canon_sim {
     int32_t* nbr_idx;
     int64_t nbr_cap, nbr_total;
     int64_t overlap_pairs, coll_hits;
+    /* table iteration order (default ascending index); reference = libstdc++ unordered_map order, quirk Q4 */
+    int32_t* order;
+    int gauss_seidel; /* physics pass sees already-processed agents at their integrated positions (reference, §3.4) */
     /* scratch */
     v2* pos_new;
     /* grid scratch */
@@ -108,6 +111,9 @@ canon_sim* canon_create(const canon_desc* d) {
     AL(f_buf, v2); AL(goal_dist, float); AL(min_time, float); AL(num_done, int32_t); AL(counted, uint8_t);
     AL(lost, uint32_t); AL(partner, int32_t); AL(nbr_cnt, int32_t); AL(pos_new, v2);
 #undef AL
+#define AL2(p) s->p = (int32_t*)calloc((size_t)n + 1, sizeof(int32_t))
+    AL2(order);
+    for (int i = 0; i < n; ++i) s->order[i] = i;
     s->c = calloc((size_t)n + 1, sizeof(float[3]));
     s->c_buf = calloc((size_t)n + 1, sizeof(float[3]));
     for (int i = 0; i < n; ++i) {
@@ -130,7 +136,7 @@ void canon_destroy(canon_sim* s) {
     free(s->facing); free(s->c); free(s->c_buf); free(s->f_buf); free(s->goal_dist); free(s->min_time);
     free(s->num_done); free(s->counted); free(s->lost); free(s->partner); free(s->nbr_cnt);
     free(s->nbr_ptr); free(s->nbr_idx); free(s->pos_new); free(s->cell_start); free(s->cell_items);
-    free(s->walls);
+    free(s->walls); free(s->order);
     free(s);
 }
 
@@ -148,7 +154,8 @@ static int demo_run(canon_sim* s, uint32_t frame_count) { /* demo.cpp:665-702 */
     int all_done = 1;
     float dt = 1.f / 60.f;
     float fake_time = dt * (float)frame_count;
-    for (int i = 0; i < s->n; ++i) {
+    for (int k = 0; k < s->n; ++k) {
+        int i = s->order[k];
         if (!is_done(s, i)) {
             all_done = 0;
         } else if (!s->counted[i]) {
@@ -157,7 +164,8 @@ static int demo_run(canon_sim* s, uint32_t frame_count) { /* demo.cpp:665-702 */
         }
     }
     if (fake_time > s->max_duration) { /* demo.cpp:691-700 */
-        for (int i = 0; i < s->n; ++i) {
+        for (int k = 0; k < s->n; ++k) {
+            int i = s->order[k];
             if (!is_done(s, i)) {
                 float finish_time = 2 * len_2(sub2(s->goal[i], s->pos[i])) + fake_time - s->min_time[i];
                 update_runs(s, finish_time);
@@ -184,7 +192,8 @@ static int farthest_brute(const canon_sim* s, int i, const int32_t* cand, int nc
             if (dist2 > max_dist2) { max_dist2 = dist2; best = k; }
         }
     } else {
-        for (int k = 0; k < s->n; ++k) {
+        for (int q = 0; q < s->n; ++q) {
+            int k = s->order[q];
             if (k == i) continue;
             float dist2 = len2_2(sub2(s->pos[k], p_i));
             if (dist2 > max_dist2) { max_dist2 = dist2; best = k; }
@@ -252,7 +261,8 @@ static void comm_run(canon_sim* s) { /* comm.cpp:267-305 */
         cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)n);
         ncand = hull_candidates(s, cand);
     }
-    for (int i = 0; i < n; ++i) { /* pass 1, comm.cpp:268-286 */
+    for (int oi = 0; oi < n; ++oi) { /* pass 1, comm.cpp:268-286 */
+        int i = s->order[oi];
         int j = farthest_brute(s, i, cand, ncand);
         s->partner[i] = j;
         if (j < 0) { /* quirk Q3: the reference dereferences a null CommComp here (UB) */
@@ -297,7 +307,8 @@ static void comm_run(canon_sim* s) { /* comm.cpp:267-305 */
         s->f_buf[i] = V2(glm_clamp(fp[0], -1.f, 1.f), glm_clamp(fp[1], -1.f, 1.f)); /* CommComp.h:30-32 */
     }
     free(cand);
-    for (int i = 0; i < n; ++i) { /* pass 2, comm.cpp:288-304 */
+    for (int oi = 0; oi < n; ++oi) { /* pass 2, comm.cpp:288-304 */
+        int i = s->order[oi];
         v2 facing = s->facing[i];
         v2 right = V2(facing.y, -facing.x);
         v2 fb = s->f_buf[i];
@@ -421,7 +432,8 @@ static void update_agents(canon_sim* s) {
         grid_build(s, cutoff);
         stencil = (int)ceilf(cutoff / g_grid.h);
     }
-    for (int i = 0; i < n; ++i) {
+    for (int oi = 0; oi < n; ++oi) {
+        int i = s->order[oi];
         /* ai.cpp:153-168 */
         s->goal_dist[i] = len_2(sub2(s->goal[i], s->pos[i]));
         int next = s->num_done[i];
@@ -469,7 +481,8 @@ static void update_agents(canon_sim* s) {
         hit = 1;                                                                          \
     } while (0)
         if (!s->use_grid) {
-            for (int j = 0; j < n; ++j) { /* LMP.cpp:288-304 */
+            for (int oj = 0; oj < n; ++oj) { /* LMP.cpp:288-304 */
+                int j = s->order[oj];
                 if (j == i) continue;
                 v2 fcontrib; int hit = 0;
                 PAIR(j);
@@ -553,14 +566,19 @@ static void physics_simulate(canon_sim* s, float dt) {
      * (the reference is Gauss-Seidel in hash-map order through a stale BVH: quirks Q4/Q8, gap measured vs O-ref) */
     s->coll_hits = 0;
     float r = s->r;
-    for (int i = 0; i < n; ++i) {
+    for (int oi = 0; oi < n; ++oi) {
+        int i = s->order[oi];
         v2 p = s->pos_new[i], vfh = s->vfh[i];
         v2 pq = p;
         if (!s->use_grid) {
-            for (int j = 0; j < n; ++j) {
+            for (int oj = 0; oj < n; ++oj) {
+                int j = s->order[oj];
                 v2 away;
                 if (j == i) continue;
-                if (circ_circ_hit(pq, s->pos_new[j], r, r, &away)) { push_away(&p, &vfh, away); s->coll_hits++; }
+                /* Gauss-Seidel (reference, physics.cpp:56 + BVH.cpp:109): agents later in the table still sit at their
+                 * frame-start position (s->pos[j] is only overwritten once j has been processed) */
+                v2 pj = (s->gauss_seidel && oj > oi) ? s->pos[j] : s->pos_new[j];
+                if (circ_circ_hit(pq, pj, r, r, &away)) { push_away(&p, &vfh, away); s->coll_hits++; }
             }
         } else {
             int cx, cy, nh = 0;
@@ -668,6 +686,15 @@ int64_t canon_get_neighbor_lists(const canon_sim* s, int64_t* row_ptr, int32_t* 
 int64_t canon_overlap_pairs(const canon_sim* s) { return s->overlap_pairs; }
 int64_t canon_collision_hits(const canon_sim* s) { return s->coll_hits; }
 void canon_record_neighbors(canon_sim* s, int32_t on) { s->record_nbrs = on; }
+/* table iteration order (a permutation of 0..n-1) for every loop the reference runs over a component table; brute-force
+ * mode only.  With the reference's own unordered_map order (dumped by oracle/_ref/oref) and gauss_seidel = 1 the
+ * restatement follows the reference operation for operation. */
+int32_t canon_set_order(canon_sim* s, const int32_t* order, int32_t gauss_seidel) {
+    if (s->use_grid) return -1;
+    if (order) memcpy(s->order, order, sizeof(int32_t) * (size_t)s->n);
+    s->gauss_seidel = gauss_seidel;
+    return 0;
+}
 
 /* ---------- scene catalogue, wall-free scenes only (demo.cpp:48-104,141-206,356-373) ---------- */
 static const float GLM_PI_F = 3.14159265358979323846264338327950288f; /* glm::pi<float>() */

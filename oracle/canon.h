@@ -73,6 +73,9 @@ int64_t canon_get_neighbor_lists(const canon_sim* s, int64_t* row_ptr, int32_t* 
 int64_t canon_overlap_pairs(const canon_sim* s);   /* unordered pairs overlapping at frame start */
 int64_t canon_collision_hits(const canon_sim* s);  /* ordered (q,bv) hits in physics::simulate */
 void canon_record_neighbors(canon_sim* s, int32_t on);
+/* iterate every component-table loop in `order` (permutation of 0..n-1; NULL keeps it) and, if gauss_seidel, let the
+ * collision pass see already-processed agents at their integrated positions (reference semantics) */
+int32_t canon_set_order(canon_sim* s, const int32_t* order, int32_t gauss_seidel);
 
 /* RNG restatement (Seeder.cpp:5-20 + libstdc++ minstd_rand0 / uniform_real_distribution<float>) */
 uint32_t canon_lcg_next(uint32_t x);

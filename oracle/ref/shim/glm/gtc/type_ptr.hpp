@@ -1,0 +1,3 @@
+// shim: see glm/shim_core.hpp
+#pragma once
+#include "../shim_core.hpp"

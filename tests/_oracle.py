@@ -51,6 +51,7 @@ def lib():
         L.canon_collision_hits.argtypes = [C.c_void_p]
         L.canon_collision_hits.restype = C.c_int64
         L.canon_record_neighbors.argtypes = [C.c_void_p, C.c_int32]
+        L.canon_set_order.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
         L.canon_lcg_next.argtypes = [C.c_uint32]
         L.canon_lcg_next.restype = C.c_uint32
         L.canon_lcg_seed.argtypes = [C.c_uint64]
@@ -155,6 +156,10 @@ class CanonSim:
         p = np.zeros(self.n, np.int32)
         lib().canon_get_neighbor_counts(self.h, _p(p))
         return p
+
+    def set_order(self, order=None, gauss_seidel=False):
+        o = None if order is None else np.ascontiguousarray(order, np.int32)
+        assert lib().canon_set_order(self.h, _p(o), 1 if gauss_seidel else 0) == 0
 
     def record_neighbors(self, on=True):
         lib().canon_record_neighbors(self.h, 1 if on else 0)

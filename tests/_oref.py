@@ -1,0 +1,78 @@
+"""Runner / dump reader for oracle/_ref/oref (the reference's own translation units, see oracle/ref/).
+TEST INFRASTRUCTURE ONLY.  /root/reference is only needed to BUILD oref; the binary travels with the snapshot."""
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OREF = os.path.join(ROOT, "oracle", "_ref", "oref")
+OREF_NOCOMM = os.path.join(ROOT, "oracle", "_ref", "oref_nocomm")
+
+
+def available():
+    return os.path.exists(OREF)
+
+
+def write_config(path, m_cv, m_f):
+    """pso_opt.py:17-23 write_config: 5 lines x 8 floats."""
+    cfg = np.zeros((5, 8), np.float64)
+    if m_cv is not None:
+        cfg[:3] = np.asarray(m_cv, np.float32)
+    if m_f is not None:
+        cfg[3:, :3] = np.asarray(m_f, np.float32)
+    with open(path, "w") as f:
+        for row in cfg:
+            f.write(" ".join(repr(float(np.float32(v))) for v in row) + "\n")
+
+
+def run(scene, seed=0, m_cv=None, m_f=None, max_frames=100000, dump_every=1, comm=True, keep_dir=None):
+    d = keep_dir or tempfile.mkdtemp(prefix="oref_")
+    write_config(os.path.join(d, "comms.config"), m_cv, m_f)
+    dump = os.path.join(d, "dump.bin")
+    exe = OREF if comm else OREF_NOCOMM
+    subprocess.run([exe, str(scene), str(seed), d, str(max_frames), str(dump_every), dump], check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d)
+    out = read_dump(dump)
+    res = open(os.path.join(d, "comms.result")).read().split()
+    out["result_file"] = (res[0], res[1])
+    return out
+
+
+def read_dump(path):
+    buf = np.fromfile(path, np.uint8)
+    off = 0
+
+    def take(dtype, count):
+        nonlocal off
+        nb = np.dtype(dtype).itemsize * count
+        a = buf[off:off + nb].view(dtype).copy()
+        off += nb
+        return a
+
+    magic, n, n_walls, _ = take(np.int32, 4)
+    assert magic == 0x4f524546
+    out = dict(n=int(n), n_walls=int(n_walls))
+    out["order"] = take(np.int32, n) - 1  # entity ids 1..n -> agent indices
+    out["pos0"] = take(np.float32, 2 * n).reshape(n, 2)
+    out["goal"] = take(np.float32, 2 * n).reshape(n, 2)
+    out["min_time"] = take(np.float32, n)
+    frames = []
+    while True:
+        f = int(take(np.int32, 1)[0])
+        if f < 0:
+            break
+        fr = dict(frame=f)
+        for k, w in (("pos", 2), ("vel", 2), ("vfh", 2), ("c", 3), ("facing", 2), ("local_goal", 2)):
+            fr[k] = take(np.float32, w * n).reshape(n, w)
+        fr["goal_dist"] = take(np.float32, n)
+        fr["num_done"] = take(np.int32, n)
+        fr["run_avg"], fr["run_std"], fr["avg_velocity"] = [float(x) for x in take(np.float32, 3)]
+        fr["total_num_done"], fr["all_done"] = [int(x) for x in take(np.int32, 2)]
+        frames.append(fr)
+    out["frames"] = frames
+    out["frames_executed"] = int(take(np.int32, 1)[0])
+    av, gt, ra, rs = [float(x) for x in take(np.float32, 4)]
+    out["scores"] = dict(avg_velocity=av, group_time=gt, run_avg=ra, run_std=rs, n_done=int(take(np.int32, 1)[0]))
+    return out

@@ -1,0 +1,111 @@
+"""Pins the oracle: O-canon, run in the reference's own table order with the Gauss-Seidel collision pass, against golden
+vectors produced by the REFERENCE'S OWN translation units (oracle/_ref/oref, built by oracle/ref/Makefile from
+/root/reference; fixtures by tools/make_golden.py).  Everything is compared bit for bit: per-frame component state
+(pos, vel, vel_forehalf, c, facing, local_goal, goal_dist, num_done), the Welford statistics and the final scores."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import _oracle
+import _oref
+
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+KEYS = ("pos", "vel", "vfh", "c", "facing", "local_goal", "goal_dist", "num_done")
+
+
+def canon_from_golden(g):
+    m_cv = g["m_cv"] if "m_cv" in g else None
+    m_f = g["m_f"] if "m_f" in g else None
+    pos, goal, md, rng = _oracle.scene(int(g["scene"]), int(g["seed"]))
+    assert np.array_equal(pos, g["pos0"]) and np.array_equal(goal, g["goal"]), "scene catalogue differs from demo.cpp"
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=bool(g["comm"]))
+    o.set_order(g["order"], gauss_seidel=True)
+    return o
+
+
+def test_fixtures_present():
+    assert len(GOLD) >= 7
+
+
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p)[:-4] for p in GOLD])
+def test_canon_matches_reference_golden(path):
+    g = np.load(path)
+    o = canon_from_golden(g)
+    comm = bool(g["comm"])
+    at = 0
+    for k, f in enumerate(g["frames"]):
+        o.step(int(f) - at)
+        at = int(f)
+        st = o.state()
+        # scene 12 (random layout) starts with overlapping agents: the reference's BVH misses some of those contacts
+        # (quirk Q8: approximate internal-node test on stale boxes), so pos / vel_forehalf of agents that have anybody
+        # within contact reach are excluded there; every other quantity of frame 1 is still compared for all agents.
+        free = np.ones(len(g["pos0"]), bool)
+        if int(g["scene"]) == 12:
+            d = g["pos0"][:, None, :] - g["pos0"][None, :, :]
+            d2 = (d * d).sum(-1) + np.eye(len(free)) * 1e9
+            free = d2.min(1) > 0.34 ** 2
+            assert free.sum() > 150
+        for key in KEYS:
+            if not comm and key in ("c", "facing"):
+                continue  # the nocomm flavour has no CommComp
+            m = free if key in ("pos", "vfh") else slice(None)
+            assert np.array_equal(st[key][m], g[key][k][m], equal_nan=True), f"{os.path.basename(path)} frame {f}: {key}"
+        sc = o.scores()
+        ra, rs, av, nd = g["progress"][k]
+        assert (np.float32(sc["run_avg"]), np.float32(sc["run_std"]), sc["n_done"]) == (np.float32(ra), np.float32(rs), int(nd))
+        assert np.float32(sc["avg_velocity"]) == np.float32(av)
+    if int(g["complete"]):
+        assert o.finished and o.frame == int(g["frames_executed"])
+        sc = o.scores()
+        got = np.array([sc[k] for k in ("avg_velocity", "group_time", "run_avg", "run_std")], np.float32)
+        assert np.array_equal(got, g["scores"]) and sc["n_done"] == int(g["n_done"])
+        # comms.result text (comm.cpp:136-142) — 6 significant digits
+        assert ("%g" % got[0], "%g" % got[1]) == tuple(str(x) for x in g["result_file"])
+
+
+def test_mintime_matches_reference():
+    g = np.load([p for p in GOLD if p.endswith("scene4_w2.npz")][0])
+    d = g["goal"] - g["pos0"]
+    mt = (np.float32(-1.0) + np.sqrt((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]).astype(np.float32))).astype(np.float32)
+    assert np.array_equal(mt, g["min_time"])  # ai.cpp:121-126
+
+
+@pytest.mark.skipif(not _oref.available(), reason="oracle/_ref/oref not built (needs /root/reference)")
+def test_live_reference_run_matches_canon():
+    """Same pin against a live run of the reference binary, with weights the fixtures do not cover."""
+    from learn_comms_b200 import workloads as wl
+    m_cv, m_f = wl.weights(31, 0.5)
+    r = _oref.run(4, 0, m_cv, m_f, dump_every=25)
+    pos, goal, md, rng = _oracle.scene(4, 0)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    o.set_order(r["order"], gauss_seidel=True)
+    at = 0
+    for fr in r["frames"]:
+        o.step(fr["frame"] - at)
+        at = fr["frame"]
+        st = o.state()
+        bad = [k for k in KEYS if not np.array_equal(st[k], fr[k], equal_nan=True)]
+        if bad:
+            # only a BVH contact (quirk Q8, tree-shaped false negatives) may separate the two: then positions differ first
+            assert o.collision_hits > 0 or "pos" in bad, (fr["frame"], bad)
+            return
+    assert o.scores() == r["scores"]
+
+
+@pytest.mark.skipif(not _oref.available(), reason="oracle/_ref/oref not built (needs /root/reference)")
+def test_canonical_order_score_gap_is_small():
+    """Deviation budget of the product's canonical (ascending id, Jacobi, exact leaf predicate) order vs the reference's
+    hash-map order: the rollouts are chaotic, so only the aggregate score is compared (measured gap)."""
+    from learn_comms_b200 import workloads as wl
+    gaps = []
+    for scene, ws in ((0, 1), (4, 2), (5, 7), (1, 5)):
+        m_cv, m_f = wl.weights(ws)
+        r = _oref.run(scene, 0, m_cv, m_f, dump_every=0)
+        pos, goal, md, rng = _oracle.scene(scene, 0)
+        o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+        o.step(10 ** 6)
+        gaps.append(abs(o.scores()["group_time"] - r["scores"]["group_time"]) / r["scores"]["group_time"])
+    assert max(gaps) < 0.25, gaps
