@@ -111,11 +111,24 @@ typedef struct lc_batch_desc {
 } lc_batch_desc;
 int32_t lc_batch_create(const lc_batch_desc* desc, lc_batch** out);
 void lc_batch_destroy(lc_batch* b);
-/* run every scenario to completion (or max_frames); outputs are HOST arrays [S] (any may be NULL) */
+/* Advance every unfinished scenario by up to max_frames frames of main.cpp:98-150 (pass INT32_MAX to run each to its own
+ * all_done, i.e. the whole `while (!all_done)` loop of every comm_norender process pso_opt.py would have spawned).
+ * Resumable: state stays on the device between calls.  Outputs are HOST arrays [S] (any may be NULL):
+ * comm::terminate's two numbers (comm.cpp:136-142), demo's total_num_done and the frames executed so far. */
 int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float* group_time, int32_t* n_done,
                      int32_t* frames);
-int32_t lc_batch_get_state(lc_batch* b, float* pos, float* vel, float* c);
-int32_t lc_batch_timer(lc_batch* b, float* milliseconds); /* device time of the last lc_batch_run */
+/* back to the initial state (frame 0) with new per-scenario parameters (NULL keeps the old ones): the next PSO iteration */
+int32_t lc_batch_reset(lc_batch* b, const float* m_cv /*[S][24]*/, const float* m_f /*[S][6]*/);
+int32_t lc_batch_finished(lc_batch* b, int32_t* n_finished);
+/* component tables of all scenarios, [S][n]... in the conventions of lc_get_state; HOST pointers, any may be NULL */
+int32_t lc_batch_get_state(lc_batch* b, float* pos, float* vel, float* vel_forehalf, float* c, float* facing,
+                           float* local_goal, float* goal_dist, int32_t* num_done);
+/* diagnostics (parity tests): partner / neighbour count [S][n] of the last executed frame; per-scenario totals over all
+ * executed frames of overlapping pairs at frame start, collision-pass hits and TTC pair evaluations */
+int32_t lc_batch_get_diag(lc_batch* b, int32_t* partner, int32_t* neighbor_count, int64_t* overlap_pairs,
+                          int64_t* collision_hits, int64_t* pair_tests);
+int32_t lc_batch_timer(lc_batch* b, float* milliseconds); /* device time of the last lc_batch_run (CUDA events) */
+int64_t lc_batch_kernel_launches(lc_batch* b);
 
 /* ---- files: comm::init / comm::terminate formats (comm.cpp:74-142, pso_opt.py:17-41) ---- */
 int32_t lc_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);

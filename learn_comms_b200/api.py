@@ -34,7 +34,8 @@ EXPORTS = [
     "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
-    "lc_batch_timer", "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
+    "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
 ]
 
 
@@ -71,8 +72,13 @@ def lib():
         L.lc_batch_destroy.argtypes = [vp]
         L.lc_batch_destroy.restype = None
         L.lc_batch_run.argtypes = [vp, i32, vp, vp, vp, vp]
-        L.lc_batch_get_state.argtypes = [vp, vp, vp, vp]
+        L.lc_batch_get_state.argtypes = [vp] + [vp] * 8
         L.lc_batch_timer.argtypes = [vp, f32p]
+        L.lc_batch_reset.argtypes = [vp, vp, vp]
+        L.lc_batch_finished.argtypes = [vp, C.POINTER(i32)]
+        L.lc_batch_get_diag.argtypes = [vp] + [vp] * 5
+        L.lc_batch_kernel_launches.argtypes = [vp]
+        L.lc_batch_kernel_launches.restype = C.c_int64
         L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
@@ -283,7 +289,8 @@ class Batch:
 
     __del__ = close
 
-    def run(self, max_frames=1 << 30):
+    def run(self, max_frames=(1 << 31) - 1):
+        """Advance every unfinished scenario by up to max_frames frames (default: each to its own all_done)."""
         S = self.S
         out = dict(avg_velocity=np.zeros(S, np.float32), group_time=np.zeros(S, np.float32),
                    n_done=np.zeros(S, np.int32), frames=np.zeros(S, np.int32))
@@ -291,14 +298,45 @@ class Batch:
                                _p(out["frames"])))
         return out
 
+    def reset(self, m_cv=None, m_f=None):
+        """Frame 0 again, optionally with new per-scenario parameters (the next PSO iteration)."""
+        if m_cv is not None:
+            m_cv = np.ascontiguousarray(m_cv, np.float32)
+            assert m_cv.shape == (self.S, 3, 8)
+        if m_f is not None:
+            m_f = np.ascontiguousarray(m_f, np.float32)
+            assert m_f.shape == (self.S, 2, 3)
+        _ck(lib().lc_batch_reset(self.h, _p(m_cv), _p(m_f)))
+
+    @property
+    def n_finished(self):
+        k = C.c_int32(0)
+        _ck(lib().lc_batch_finished(self.h, C.byref(k)))
+        return int(k.value)
+
     def state(self):
-        pos = np.zeros((self.S, self.n, 2), np.float32)
-        vel = np.zeros((self.S, self.n, 2), np.float32)
-        c = np.zeros((self.S, self.n, 3), np.float32)
-        _ck(lib().lc_batch_get_state(self.h, _p(pos), _p(vel), _p(c)))
-        return dict(pos=pos, vel=vel, c=c)
+        S, n = self.S, self.n
+        out = dict(pos=np.zeros((S, n, 2), np.float32), vel=np.zeros((S, n, 2), np.float32),
+                   vfh=np.zeros((S, n, 2), np.float32), c=np.zeros((S, n, 3), np.float32),
+                   facing=np.zeros((S, n, 2), np.float32), local_goal=np.zeros((S, n, 2), np.float32),
+                   goal_dist=np.zeros((S, n), np.float32), num_done=np.zeros((S, n), np.int32))
+        _ck(lib().lc_batch_get_state(self.h, *[_p(out[k]) for k in _STATE_KEYS]))
+        return out
+
+    def diag(self):
+        S, n = self.S, self.n
+        out = dict(partner=np.zeros((S, n), np.int32), neighbor_count=np.zeros((S, n), np.int32),
+                   overlap_pairs=np.zeros(S, np.int64), collision_hits=np.zeros(S, np.int64),
+                   pair_tests=np.zeros(S, np.int64))
+        _ck(lib().lc_batch_get_diag(self.h, *[_p(out[k]) for k in ("partner", "neighbor_count", "overlap_pairs",
+                                                                     "collision_hits", "pair_tests")]))
+        return out
 
     def device_ms(self):
         ms = C.c_float()
         _ck(lib().lc_batch_timer(self.h, C.byref(ms)))
         return float(ms.value)
+
+    @property
+    def launches(self):
+        return int(lib().lc_batch_kernel_launches(self.h))

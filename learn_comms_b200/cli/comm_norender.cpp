@@ -1,0 +1,111 @@
+// comm_norender / nocomm_norender — drop-in for the reference executables that pso_opt.py:245-267 launches:
+//     <build>/bin/comm_norender <scene> --seed <u64> --data <dir>
+// Same argument grammar as enginee/src/main.cpp:53-69 + io.cpp:63-125 (options --help, --record u, --data dir,
+// --split n, --seed u; one positional `scene`; misuse -> message + usage on stderr, exit 1), same files:
+// reads <project>data/<dir>/comms.config (comm.cpp:74-131), writes <project>data/<dir>/comms.result (comm.cpp:136-142).
+// The frame loop itself (main.cpp:98-150) runs on the GPU through the C ABI; there is no CPU fallback: without a CUDA
+// device the process exits 1 with the library's error text.  Build: tools/build_cli.sh (g++ + liblearncomms.so).
+// PROJECT_DIR: compile-time in the reference (CMake); here -DLC_PROJECT_DIR or the LEARN_COMMS_PROJECT_DIR variable.
+#include "../../include/learn_comms.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#ifndef LC_PROJECT_DIR
+#define LC_PROJECT_DIR "./"
+#endif
+
+static std::string g_usage;
+[[noreturn]] static void usage_error(const char* msg) {  // io.cpp:42-45
+    fprintf(stderr, "%s\n%s\n", msg, g_usage.c_str());
+    exit(EXIT_FAILURE);
+}
+[[noreturn]] static void lib_error(const char* what) {
+    fprintf(stderr, "%s: %s\n", what, lc_last_error());
+    exit(EXIT_FAILURE);
+}
+
+int main(int argc, char** argv) {
+    std::string data_dir;
+    unsigned long long seed = 0;
+    long scene = -1;
+    bool seen_scene = false, seen[5] = {false, false, false, false, false};
+    const char* names[5] = {"data", "help", "record", "seed", "split"};  // std::map order of the reference's usage line
+    const char* args[5] = {"dir", "", "u", "u", "n"};
+    g_usage = std::string("Usage: ") + argv[0];
+    for (int k = 0; k < 5; ++k) g_usage += std::string(" [--") + names[k] + (args[k][0] ? std::string(" ") + args[k] : "") + "]";
+    g_usage += " scene";
+    for (int i = 1; i < argc; ++i) {
+        std::string a(argv[i]);
+        int k = -1;
+        if (a.compare(0, 2, "--") == 0)
+            for (int q = 0; q < 5; ++q)
+                if (a.substr(2) == names[q]) k = q;
+        if (k >= 0) {
+            if (seen[k]) usage_error("no double options");
+            seen[k] = true;
+            if (k == 1) { printf("%s\n", g_usage.c_str()); return EXIT_SUCCESS; }
+            if (i + 1 >= argc) usage_error("no arg to read");
+            std::string v(argv[++i]);
+            if (v.find('-') != std::string::npos) usage_error("bad arg");
+            try {
+                if (k == 0) data_dir = v;
+                else if (k == 3) seed = std::stoull(v);
+                else (void)std::stoi(v);  // --record / --split: accepted and ignored (no renderer on this path)
+            } catch (...) { usage_error("bad arg"); }
+        } else {
+            if (seen_scene) usage_error("no further positionals");
+            if (a.find("--") != std::string::npos) usage_error("unknown option");
+            try { scene = std::stoi(a); } catch (...) { usage_error("bad arg"); }
+            seen_scene = true;
+        }
+    }
+    if (!seen_scene) usage_error("missing required positional");
+
+    const char* env = getenv("LEARN_COMMS_PROJECT_DIR");
+    std::string project = env ? env : LC_PROJECT_DIR;
+    if (!project.empty() && project.back() != '/') project += '/';
+    data_dir = project + "data/" + data_dir;  // main.cpp:68
+
+    // demo::init (scene catalogue) + Seeder::seed (main.cpp:69-70)
+    std::vector<float> pos(2 * 4096), goal(2 * 4096);
+    float max_duration = 0.f;
+    uint32_t rng = 0;
+    int n = lc_scene((uint32_t)scene, seed, pos.data(), goal.data(), 4096, &max_duration, &rng);
+    if (n <= 0) {
+        fprintf(stderr, "scene %ld is not available on the GPU path (wall-free scenes 0, 1, 4, 5, 12 only)\n", scene);
+        return EXIT_FAILURE;
+    }
+    float m_cv[24] = {0}, m_f[6] = {0};
+    uint32_t flags = 0;
+#ifdef NO_COMM
+    flags |= LC_FLAG_NO_COMM;  // main.cpp:130-132: comm::run compiled out; comm::init still runs but reads nothing
+#else
+    if (lc_read_config((data_dir + "/comms.config").c_str(), m_cv, m_f) != LC_OK) {
+        fprintf(stderr, "gg! Failed to open file %s/comms.config\n", data_dir.c_str());  // io.cpp:130
+        return EXIT_FAILURE;  // the reference dereferences an empty optional / throws from stof here
+    }
+#endif
+    lc_desc d;
+    memset(&d, 0, sizeof d);
+    d.n = n; d.pos = pos.data(); d.goal = goal.data(); d.radius = 0.15f; d.max_duration = max_duration;
+    d.rng_state = rng; d.m_cv = m_cv; d.m_f = m_f; d.flags = flags; d.device = 0;
+    lc_sim* sim = nullptr;
+    if (lc_create(&d, &sim) != LC_OK) lib_error("lc_create");
+    int32_t frames = 0;
+    if (lc_run_to_completion(sim, &frames) != LC_OK) lib_error("lc_run_to_completion");
+    float avg_velocity = 0.f, group_time = 0.f, run_avg = 0.f, run_std = 0.f;
+    int32_t total = 0;
+    int rc = lc_get_scores(sim, &avg_velocity, &group_time, &run_avg, &run_std, &total);
+    if (rc != LC_OK && rc != LC_ERR_STATE) lib_error("lc_get_scores");
+    fprintf(stderr, "\nFRAMES: %d\nNUM DONE: %d\n", frames, total);  // main.cpp:118-119, demo.cpp:686
+    printf("u:%f s:%f\n", run_avg, run_std);                           // last line of demo.cpp:662's log
+    if (lc_write_result((data_dir + "/comms.result").c_str(), avg_velocity, group_time) != LC_OK) {
+        fprintf(stderr, "cannot write %s/comms.result\n", data_dir.c_str());
+        return EXIT_FAILURE;
+    }
+    lc_destroy(sim);
+    return EXIT_SUCCESS;
+}

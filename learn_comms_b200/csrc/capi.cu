@@ -42,6 +42,16 @@ uint32_t lcg_pow(uint32_t a, uint64_t e) {
     return r;
 }
 
+}  // namespace
+
+// shared with batch.cu / domain.cu: one error text per host thread, whichever entry point failed last
+int lc_set_error(int code, const char* msg) {
+    g_err = msg;
+    return code;
+}
+
+namespace {
+
 template <class T> cudaError_t dalloc(T** p, size_t count) { return cudaMalloc((void**)p, sizeof(T) * (count ? count : 1)); }
 
 }  // namespace

@@ -1,0 +1,84 @@
+"""Host-side multi-GPU logic on CPU: scenario sharding and the score gather, world_size 2 over gloo (no GPU needed).
+The device work itself is replaced by a deterministic stand-in here; the -m gpu tests cover the kernels."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from learn_comms_b200 import pso
+
+
+def test_shard_range_partitions():
+    for n in (0, 1, 7, 64, 4096, 4099):
+        for world in (1, 2, 3, 8):
+            blocks = [pso.shard_range(n, r, world) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[r][1] == blocks[r + 1][0] for r in range(world - 1))
+            sizes = [hi - lo for lo, hi in blocks]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_config_split_and_files(tmp_path):
+    cfg = np.random.RandomState(0).uniform(-1, 1, pso.M_SHAPE)
+    m_cv, m_f = pso.split_config(cfg)
+    assert m_cv.shape == (3, 8) and m_f.shape == (2, 3)
+    assert np.array_equal(m_cv, cfg[:3].astype(np.float32)) and np.array_equal(m_f, cfg[3:, :3].astype(np.float32))
+    p = tmp_path / "comms.config"
+    with open(p, "w") as f:
+        pso.write_config(f, cfg)
+    lines = p.read_text().splitlines()
+    assert len(lines) == 5 and all(len(l.split(" ")) == 8 for l in lines)
+    # byte-compatible with the product's parser (== comm::init, comm.cpp:80-121)
+    import learn_comms_b200 as lcb
+    a, b = lcb.read_config(str(p))
+    assert np.array_equal(a, m_cv) and np.array_equal(b, m_f)
+    r = tmp_path / "comms.result"
+    r.write_text("0.5\nnan\n")
+    assert pso.read_result(str(r)) == 1e99
+    r.write_text("0.5\n12.25\n")
+    assert pso.read_result(str(r)) == 12.25
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n_items, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = pso.shard_range(n_items, rank, world)
+    idx = np.arange(lo, hi)
+    local = dict(avg_velocity=(idx * 0.5).astype(np.float32), group_time=(idx * 3 + 1).astype(np.float32),
+                 n_done=(idx % 64).astype(np.int32), frames=(idx + 600).astype(np.int32))
+    out = pso.gather_scores(local, n_items, rank, world, dist)
+    q.put((rank, {k: v.tolist() for k, v in out.items()}, {k: str(v.dtype) for k, v in out.items()}))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_items", [9, 64])
+def test_score_gather_world2_gloo(n_items):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_items, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    idx = np.arange(n_items)
+    for rank, out, dtypes in got:
+        assert out["avg_velocity"] == (idx * 0.5).astype(np.float32).tolist()
+        assert out["group_time"] == (idx * 3 + 1).astype(np.float32).tolist()
+        assert out["n_done"] == (idx % 64).tolist() and out["frames"] == (idx + 600).tolist()
+        assert dtypes["n_done"] == "int32" and dtypes["avg_velocity"] == "float32"
