@@ -3,7 +3,7 @@
 //
 // One thread block per scenario, one thread per agent (n <= 256).  The whole rollout — every frame of
 // main.cpp:98-150 until demo::run reports all_done — runs inside the block: the neighbour-visible state
-// (pos, vel, c) lives in shared memory (double-buffered, 64 B/agent), everything else in registers; global
+// (pos, vel, c) lives in shared memory (double-buffered, 80 B/agent), everything else in registers; global
 // memory is touched once at the start and once at the end.  Two __syncthreads per frame.  Blocks retire as their
 // scenario finishes (600-2700 frames), so the 148 SMs stay full until the tail.
 //
@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
     float4* s_pv1 = s_dyn + nt;       // integrated, not yet pushed (pos, vel): what the collision pass reads
     float4* s_c0 = s_dyn + 2 * nt;    // c, double-buffered by frame parity
     float4* s_c1 = s_dyn + 3 * nt;
-    int* s_near = reinterpret_cast<int*>(s_dyn + 4 * nt);  // [MAX_NEAR][nt]
+    float4* s_pq = s_dyn + 4 * nt;    // pair-interleaved copy of s_pv0: (x0,x1,z0,z1),(vx0,vx1,vz0,vz1) per agent pair
+    int* s_near = reinterpret_cast<int*>(s_dyn + 5 * nt);  // [MAX_NEAR][nt]
     __shared__ float s_w[32];                 // M_cv (24) | M_f (6)
     __shared__ float s_mt[MAX_N];             // min_time (constant per agent, Agent.h:17)
     __shared__ float s_ft[MAX_N];             // timeout finish times (demo.cpp:693-697)
@@ -116,10 +117,14 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
     float4 c4 = A.c4[g];
     int4 mt = A.meta[g];
     int last_cnt = 0;
+    float* const my_pq = reinterpret_cast<float*>(s_pq + 2 * (i >> 1)) + (i & 1);
     if (valid) {
         s_pv0[i] = me;
+        my_pq[0] = me.x; my_pq[2] = me.y; my_pq[4] = me.z; my_pq[6] = me.w;
         s_c0[i] = c4;
         s_mt[i] = __int_as_float(mt.z);
+    } else {
+        my_pq[0] = my_pq[2] = my_pq[4] = my_pq[6] = 0.f;  // padding of an odd last pair: finite, never selected
     }
     if (i < 24) s_w[i] = A.m_cv[(size_t)sc * 24 + i];
     if (i >= 24 && i < 30) s_w[i] = A.m_f[(size_t)sc * 6 + (i - 24)];
@@ -188,14 +193,14 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
             int bj = -1;
             float ttcFx = 0.f, ttcFy = 0.f;
             int cnt = 0, n_overlap = 0;
-            auto pair = [&](int j) {
+            // Phase 2 (rare): one pair that survived the packed filter, exact scalar arithmetic in the oracle's order
+            // (LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame), near list, force on a hit.
+            auto slow = [&](int j) {
                 const float4 q = pvA[j];
                 const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py);
                 const float dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
-                const float mm = dot2(mx, my, mx, my);
-                if (mm > best) { best = mm; bj = j; }
                 const float b = dot2(mx, my, dvx, dvy);
-                const float c = __fsub_rn(mm, K.RR);
+                const float c = __fsub_rn(dot2(mx, my, mx, my), K.RR);
                 if (c < K.near_c) {
                     if (n_near < MAX_NEAR) s_near[n_near * nt + i] = j;
                     ++n_near;
@@ -215,8 +220,52 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
                 ttcFy = __fadd_rn(ttcFy, fy);
                 ++cnt;
             };
-            for (int j = 0; j < i; ++j) pair(j);
-            for (int j = i + 1; j < n; ++j) pair(j);
+            // Phase 1: every lane walks the same j = 0..n-1 (uniform trip count, no divergence), two candidates per
+            // iteration from the pair-interleaved copy with packed FADD2 / FMUL2 (sums that consume products stay scalar:
+            // ptxas would contract them into FFMA2, see crowd.cu).  Survivors of the conservative filter are collected in
+            // a 32-bit mask per chunk and revisited in ascending j, so the force is still summed in table order.
+            const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
+            const float2 RR2 = make_float2(K.RR, K.RR);
+            for (int jb = 0; jb < n; jb += 32) {
+                unsigned m = 0u;
+                const int je = min(32, n - jb);
+                const float4* __restrict__ pp = s_pq + jb;
+#pragma unroll 2
+                for (int jj = 0; jj < je; jj += 2, pp += 2) {
+                    const float4 P4 = pp[0], V4 = pp[1];
+                    const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
+                    const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
+                    const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
+                    const float2 mm = make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y));
+                    const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
+                    const bool ok1 = jj + 1 < je;
+                    // comm.cpp:201-220: running max, strict '>', table order (the self pair has mm == 0 < FLT_MIN)
+                    if (mm.x > best) { best = mm.x; bj = jb + jj; }
+                    if (ok1 && mm.y > best) { best = mm.y; bj = jb + jj + 1; }
+                    const float2 c = sub2(mm, RR2);
+                    const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
+                    const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
+                    const float2 bb = mul2(bq, bq), ac = mul2(a, c);
+                    const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
+                    // conservative "t > 5" filter (same derivation as crowd.cu scan_neighbours / DESIGN.md)
+                    const float2 a5 = mul2(a, make_float2(5.f, 5.f));
+                    const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));
+                    const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
+                    const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+                    const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+                    const bool miss0 = (c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0;
+                    const bool miss1 = (c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1;
+                    const bool cand0 = !miss0 || c.x < K.near_c;
+                    const bool cand1 = ok1 && (!miss1 || c.y < K.near_c);
+                    m |= ((unsigned)cand0 | ((unsigned)cand1 << 1)) << jj;
+                }
+                if ((unsigned)(i - jb) < 32u) m &= ~(1u << (i - jb));  // the self pair (m = dv = 0) always survives
+                while (m) {
+                    const int j = jb + __ffs(m) - 1;
+                    m &= m - 1u;
+                    slow(j);
+                }
+            }
             last_cnt = cnt;
             overlap2 += (unsigned long long)n_overlap;
             pair_tests += (unsigned long long)(n - 1);
@@ -336,7 +385,10 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
             coll_hits += (unsigned long long)cnt;
         }
         me = make_float4(fx_, fy_, nvx, nvy);
-        if (valid) s_pv0[i] = me;  // read again only after the next B1 (or the final barrier)
+        if (valid) {  // read again only after the next B1 (or the final barrier)
+            s_pv0[i] = me;
+            my_pq[0] = me.x; my_pq[2] = me.y; my_pq[4] = me.z; my_pq[6] = me.w;
+        }
 
         // physics.cpp:72-76 inputs for the fold at the next B1
         const float speed = __fsqrt_rn(dot3_xz(nvx, nvy, nvx, nvy));
@@ -550,7 +602,7 @@ int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float
     BATCH_ENTER(b);
     if (max_frames < 0) return bfail(LC_ERR_ARG, "lc_batch_run: max_frames < 0");
     const int nt = (b->a.n + 31) & ~31;
-    const size_t smem = sizeof(float4) * 4 * nt + sizeof(int) * lcbatch::MAX_NEAR * nt;
+    const size_t smem = sizeof(float4) * 5 * nt + sizeof(int) * lcbatch::MAX_NEAR * nt;
     BCK(cudaEventRecord(b->ev0, b->st));
     lcbatch::k_batch_rollout<<<b->a.S, nt, smem, b->st>>>(b->a, b->k, max_frames);
     BCK(cudaEventRecord(b->ev1, b->st));
