@@ -326,6 +326,7 @@ def main():
     ap.add_argument("--stencil", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--replicas", action="store_true", help="N > 1: N independent crowds instead of one decomposed crowd")
     args = ap.parse_args()
     if WORKLOADS[args.workload]["kind"] == "pso":
         return run_batch_reference(args) if args.impl == "reference" else run_batch(args)
@@ -339,11 +340,19 @@ def main():
     rank, world, local, dist = dist_setup(args.gpus)
     W, K = max(args.warmup, 3), args.steps
     name = args.workload
-    # N > 1 (interim, round 1): every rank advances its own crowd of the named shape (different seed), no exchange
-    pos, goal, md, rng, m_cv, m_f = make_workload(name, seed_offset=rank)
+    # N > 1: ONE crowd of the named shape, decomposed into N x strips (one per GPU); boundary agents, comm-partner
+    # candidates and the global reductions travel through peer memory over NVLink inside the frame kernels (domain.cuh)
+    domain = world > 1 and not args.replicas
+    pos, goal, md, rng, m_cv, m_f = make_workload(name, seed_offset=0 if domain else rank)
     n = pos.shape[0]
-    sim = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, free_run=True, device=local, stencil=args.stencil)
-    sim.set_state(**walking_state(pos, goal))
+    if domain:
+        ws = walking_state(pos, goal)
+        sim = lcb.DomainSim(pos, goal, rank, world, m_cv, m_f, max_duration=md, rng_state=rng, free_run=True, device=local,
+                            stencil=args.stencil, vel=ws["vel"], vfh=ws["vfh"])
+        sim.connect_dist(dist)
+    else:
+        sim = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, free_run=True, device=local, stencil=args.stencil)
+        sim.set_state(**walking_state(pos, goal))
 
     def barrier():
         if dist is not None:
@@ -367,7 +376,10 @@ def main():
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    value = world * n * K / (ms * 1e-3)
+    n_total = n if domain else world * n   # agents advanced per step by the whole job
+    value = n_total * K / (ms * 1e-3)
+    n_local = sim.counts()[0] if domain else n
+    n_owned = int(sim.owned().sum()) if domain else n
 
     # roofline leg: per-kernel device time, CUDA events between the launches on the simulation's stream
     prof = sim.step_profiled(20)
@@ -377,7 +389,7 @@ def main():
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = ALG_BYTES_PER_AGENT_STEP * n / t_force / 1e9
+    achieved = ALG_BYTES_PER_AGENT_STEP * n_owned / t_force / 1e9  # this rank's own agents per k_force launch
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
@@ -389,7 +401,32 @@ def main():
 
     # e2e leg: host-resident component tables, pinned; set_state (H2D) -> one frame -> get_state (D2H) every step
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and domain:
+        # decomposed crowd: the state never leaves the GPUs between frames; the host-facing step is one frame plus the
+        # D2H read of the tables a host engine consumes every frame (pos, vel of the rank's own agents)
+        keys = ("pos", "vel")
+        out = sim.state(keys=keys)
+        pinned = {k: torch.from_numpy(out[k]).pin_memory() for k in keys}
+        views = {k: v.numpy() for k, v in pinned.items()}
+        d2h = sum(v.nbytes for v in views.values())
+        Ke = max(3, min(K, 50))
+        for _ in range(3):
+            sim.step(1, sync=False)
+            sim.state(keys=keys, out=views)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            sim.step(1, sync=False)
+            sim.state(keys=keys, out=views)
+        barrier()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        e2e = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h * world,
+               "steps": Ke, "ms_per_step": 1e3 * dt / Ke,
+               "api": "lc_step(1) + lc_get_state(pos, vel) per rank, pinned host tables; no per-frame H2D: the decomposed state is device-resident"}
+    elif not args.no_e2e:
         st = sim.state()
         pinned = {}
         for k, a in st.items():
@@ -414,7 +451,7 @@ def main():
             t = torch.tensor([dt], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e2e = {"value": world * n * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": h2d,
+        e2e = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": h2d * world,
                "steps": Ke, "ms_per_step": 1e3 * dt / Ke, "api": "lc_set_state + lc_step(1) + lc_get_state, pinned host tables"}
         del pinned_keep
 
@@ -425,10 +462,13 @@ def main():
 
     if rank == 0:
         line = {"metric": "agent_steps_per_sec", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak" if world > 1 else "strong", "vs_baseline": None,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak" if (world > 1 and not domain) else "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": name, "desc": WORKLOADS[name]["desc"], "agents": n * world, "frames_per_step": 1,
-                           "parallelism": "single crowd, 1 GPU" if world == 1 else f"{world} independent crowds, one per GPU, no exchange",
+                "config": {"workload": name, "desc": WORKLOADS[name]["desc"], "agents": n_total, "frames_per_step": 1,
+                           "parallelism": "single crowd, 1 GPU" if world == 1 else
+                           (f"one crowd in {world} x strips, one per GPU; halo / migration / candidate exchange through NVLink peer memory "
+                            f"inside the frame kernels (rank 0: {n_owned} own + {n_local - n_owned} ghost agents)" if domain
+                            else f"{world} independent crowds, one per GPU, no exchange"),
                            "l2": "per-frame working set (2 x 88 B x agents + grid) exceeds the 126 MB L2 at 1M agents; no flush"},
                 "counters": sim.counters(), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)

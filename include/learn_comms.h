@@ -93,6 +93,35 @@ int64_t lc_kernel_launches(lc_sim* sim); /* kernels launched by this handle so f
 #define LC_FRAME_KERNELS 7
 int32_t lc_step_profiled(lc_sim* sim, int32_t nframes, float* ms_per_kernel);
 
+/* ---- one crowd across several GPUs: spatial domain decomposition in x strips, one handle (rank) per GPU ----
+ * Replaces nothing in the reference (it is single-threaded, main.cpp:98-150); this is how BASELINE.json's 1M-agent
+ * plaza runs on 2/4/8 B200.  Every rank is created from the SAME global scene description and keeps the agents of its
+ * strip; each frame the kernels store boundary agents straight into the neighbours' mailboxes over NVLink (no host
+ * round trip).  All ranks must be stepped by the same number of frames.  Results are bit-identical to lc_create's. */
+typedef struct lc_domain_desc {
+    int32_t rank, world;        /* 2 <= world <= 8 */
+    const float* x_bounds;      /* [world + 1] strip boundaries (entries 1..world-1 are used); NULL = balanced quantiles of pos.x */
+    int32_t capacity;           /* local slot capacity (owned + ghost agents); 0 = 1.5 n/world + 2 halo_capacity */
+    int32_t halo_capacity;      /* records one neighbour may send per frame; 0 = max(65536, n/world/2) */
+    const float* vel;           /* optional [n][2] initial vel and vel_forehalf (developed-flow benchmarks); NULL = at rest */
+    const float* vel_forehalf;
+} lc_domain_desc;
+int32_t lc_dd_create(const lc_desc* global_desc, const lc_domain_desc* dom, lc_sim** out);
+/* wiring: every rank needs a device pointer to every other rank's mailbox.  Same process: lc_dd_mailbox + lc_dd_connect
+ * (enables peer access).  One process per GPU: lc_dd_ipc_handle (64-byte cudaIpcMemHandle_t, exchanged by the host's
+ * own means, e.g. torch.distributed.all_gather) + lc_dd_connect_ipc. */
+int32_t lc_dd_mailbox(lc_sim* sim, void** dev_ptr, uint64_t* bytes);
+int32_t lc_dd_connect(lc_sim* sim, int32_t peer_rank, void* peer_mailbox, int32_t peer_device);
+int32_t lc_dd_ipc_handle(lc_sim* sim, void* handle64);
+int32_t lc_dd_connect_ipc(lc_sim* sim, int32_t peer_rank, const void* handle64);
+/* lc_get_state on a rank returns global-size arrays with zeros for agents it does not own; owned[id] = 1 marks its own */
+int32_t lc_dd_get_owned(lc_sim* sim, int32_t* owned /*[n]*/);
+/* lc_get_scores on a rank: Welford statistics are complete on rank 0 (the scoring rank); avg_velocity is the value
+ * after the previous frame.  The last frame's physics.cpp:72-76 inputs are per-rank partials: the speed of the
+ * highest-id not-done agent is ((lastvel >> 32) - 1 = id, low 32 bits = speed) of the rank with the largest lastvel. */
+int32_t lc_dd_get_partials(lc_sim* sim, uint64_t* lastvel, int32_t* nonfinite, float* avg_velocity_before);
+int32_t lc_dd_counts(lc_sim* sim, int32_t* n_local /*owned + ghosts this frame*/, int32_t* capacity);
+
 /* ---- batched rollouts: many independent small scenarios / PSO particles in one launch ----
  * replaces pso_opt.py:236-267 simulate_set/simulate (one comm_norender process per (particle, scene)). */
 typedef struct lc_batch lc_batch;

@@ -23,6 +23,11 @@ class _Desc(C.Structure):
                 ("stencil", C.c_int32)]
 
 
+class _DomainDesc(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("x_bounds", C.c_void_p), ("capacity", C.c_int32),
+                ("halo_capacity", C.c_int32), ("vel", C.c_void_p), ("vel_forehalf", C.c_void_p)]
+
+
 class _BatchDesc(C.Structure):
     _fields_ = [("n_scenarios", C.c_int32), ("n_agents", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p),
                 ("m_cv", C.c_void_p), ("m_f", C.c_void_p), ("max_duration", C.c_void_p), ("rng_state", C.c_void_p),
@@ -35,6 +40,7 @@ EXPORTS = [
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
+    "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials",
     "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
 ]
 
@@ -68,6 +74,14 @@ def lib():
         L.lc_kernel_launches.argtypes = [vp]
         L.lc_kernel_launches.restype = C.c_int64
         L.lc_step_profiled.argtypes = [vp, i32, vp]
+        L.lc_dd_create.argtypes = [C.POINTER(_Desc), C.POINTER(_DomainDesc), C.POINTER(vp)]
+        L.lc_dd_mailbox.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
+        L.lc_dd_connect.argtypes = [vp, i32, vp, i32]
+        L.lc_dd_ipc_handle.argtypes = [vp, vp]
+        L.lc_dd_connect_ipc.argtypes = [vp, i32, vp]
+        L.lc_dd_get_owned.argtypes = [vp, vp]
+        L.lc_dd_counts.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
+        L.lc_dd_get_partials.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(i32), f32p]
         L.lc_batch_create.argtypes = [C.POINTER(_BatchDesc), C.POINTER(vp)]
         L.lc_batch_destroy.argtypes = [vp]
         L.lc_batch_destroy.restype = None
@@ -263,6 +277,141 @@ class Sim:
     @property
     def launches(self):
         return int(lib().lc_kernel_launches(self.h))
+
+
+class DomainSim(Sim):
+    """One rank (x strip) of a crowd that is spatially decomposed over several GPUs (lc_dd_*).  Every rank is built from
+    the same global arrays.  Ranks of one process are wired with connect_local(); one process per GPU (torchrun) with
+    connect_dist().  state() returns global-size arrays that are zero outside the rank's own agents plus `owned`."""
+
+    def __init__(self, pos, goal, rank, world, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15, comm=True,
+                 free_run=False, device=0, stencil=0, x_bounds=None, capacity=0, halo_capacity=0, vel=None, vfh=None):
+        self.n = int(pos.shape[0])
+        self.rank, self.world, self.device = int(rank), int(world), int(device)
+        pos = np.ascontiguousarray(pos, np.float32)
+        goal = np.ascontiguousarray(goal, np.float32)
+        m_cv = None if m_cv is None else np.ascontiguousarray(m_cv, np.float32)
+        m_f = None if m_f is None else np.ascontiguousarray(m_f, np.float32)
+        xb = None if x_bounds is None else np.ascontiguousarray(x_bounds, np.float32)
+        vel = None if vel is None else np.ascontiguousarray(vel, np.float32)
+        vfh = None if vfh is None else np.ascontiguousarray(vfh, np.float32)
+        flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0)
+        d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0, None, stencil)
+        dom = _DomainDesc(rank, world, _p(xb), capacity, halo_capacity, _p(vel), _p(vfh))
+        h = C.c_void_p()
+        self.h = None
+        _ck(lib().lc_dd_create(C.byref(d), C.byref(dom), C.byref(h)))
+        self.h = h
+        self.list_cap = 0
+
+    def mailbox(self):
+        ptr, nbytes = C.c_void_p(), C.c_uint64()
+        _ck(lib().lc_dd_mailbox(self.h, C.byref(ptr), C.byref(nbytes)))
+        return ptr, int(nbytes.value)
+
+    def owned(self):
+        o = np.zeros(self.n, np.int32)
+        _ck(lib().lc_dd_get_owned(self.h, _p(o)))
+        return o
+
+    def counts(self):
+        a, b = C.c_int32(), C.c_int32()
+        _ck(lib().lc_dd_counts(self.h, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def set_state(self, **kw):
+        raise LcError(-1, "set_state is not available for a domain-decomposed crowd")
+
+    def partials(self):
+        lv, nf, av = C.c_uint64(), C.c_int32(), C.c_float()
+        _ck(lib().lc_dd_get_partials(self.h, C.byref(lv), C.byref(nf), C.byref(av)))
+        return int(lv.value), int(nf.value), float(av.value)
+
+    @staticmethod
+    def merge_scores(rank0_scores, partials):
+        """comm::terminate's numbers of the whole crowd: Welford statistics from the scoring rank, avg_velocity
+        (physics.cpp:72-76: the speed of the last not-done agent in table order) from the ranks' partials."""
+        out = dict(rank0_scores)
+        key = max(p[0] for p in partials)
+        if key:
+            sp = np.array([key & 0xffffffff], np.uint32).view(np.float32)[0]
+            others = sum(p[1] for p in partials) - (0 if np.isfinite(sp) else 1)
+            poisoned = others > 0 or not np.isfinite(partials[0][2])
+            out["avg_velocity"] = float("nan") if poisoned else float(sp)
+        return out
+
+    @staticmethod
+    def merged_scores(sims):
+        return DomainSim.merge_scores(sims[0].scores(), [s.partials() for s in sims])
+
+    def scores_dist(self, dist):
+        """One process per GPU: every rank returns the whole crowd's scores."""
+        import torch
+        dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+        sc = self.scores()
+        lv, nf, av = self.partials()
+        keys = sorted(sc)
+        mine = torch.tensor([float(lv >> 32), float(lv & 0xffffffff), float(nf)] + [float(sc[k]) for k in keys],
+                            dtype=torch.float64, device=dev)
+        parts = [torch.zeros_like(mine) for _ in range(self.world)]
+        dist.all_gather(parts, mine)
+        parts = [p.cpu().numpy() for p in parts]
+        r0 = {k: (int(parts[0][3 + i]) if k == "n_done" else float(np.float32(parts[0][3 + i]))) for i, k in enumerate(keys)}
+        partials = [((int(p[0]) << 32) | int(p[1]), int(p[2]), float(np.float32(parts[0][3 + keys.index("avg_velocity")]))) for p in parts]
+        return DomainSim.merge_scores(r0, partials)
+
+    @staticmethod
+    def connect_local(sims):
+        """Ranks living in this process: hand every rank the device pointer of every other rank's mailbox."""
+        for a in sims:
+            for b in sims:
+                if a is not b:
+                    ptr, _ = b.mailbox()
+                    _ck(lib().lc_dd_connect(a.h, b.rank, ptr, b.device))
+
+    def connect_dist(self, dist):
+        """One process per GPU: all-gather the 64-byte CUDA IPC handles of the mailboxes over torch.distributed."""
+        import torch
+        mine = np.zeros(64, np.uint8)
+        _ck(lib().lc_dd_ipc_handle(self.h, _p(mine)))
+        dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+        t = torch.from_numpy(mine).to(dev)
+        parts = [torch.zeros_like(t) for _ in range(self.world)]
+        dist.all_gather(parts, t)
+        for r in range(self.world):
+            if r != self.rank:
+                hnd = np.ascontiguousarray(parts[r].cpu().numpy())
+                _ck(lib().lc_dd_connect_ipc(self.h, r, _p(hnd)))
+        dist.barrier()
+
+    @staticmethod
+    def step_all(sims, frames, chunk=16):
+        """Same-process ranks: enqueue `frames` frames on every rank, interleaved in chunks so that no stream's launch
+        queue fills up while its kernels wait for a peer whose work has not been enqueued yet."""
+        left = frames
+        while left > 0:
+            k = min(chunk, left)
+            for sm in sims:
+                sm.step(k, sync=False)
+            left -= k
+            for sm in sims:
+                sm.sync()
+
+    @staticmethod
+    def merged_state(sims):
+        """Global tables assembled from the owners' entries (same-process ranks)."""
+        out, seen = None, None
+        for sm in sims:
+            st = sm.state()
+            own = sm.owned().astype(bool)
+            if out is None:
+                out = {k: np.zeros_like(v) for k, v in st.items()}
+                seen = np.zeros(sm.n, np.int32)
+            seen += own
+            for k, v in st.items():
+                out[k][own] = v[own]
+        assert (seen == 1).all(), f"ownership is not a partition: {np.bincount(seen)}"
+        return out
 
 
 class Batch:

@@ -4,9 +4,12 @@
 #include "../../include/learn_comms.h"
 #include "crowd.cuh"
 #include "lc_math.cuh"
+#include <algorithm>
 #include <cmath>
+#include <cstddef>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -65,8 +68,16 @@ struct lc_sim {
     cudaGraphExec_t gexec[2] = {nullptr, nullptr};  // 1 frame, GRAPH_BATCH frames
     long long launches = 0;
     int device = 0;
-    int n = 0;
+    int n = 0;           // launch width: slot capacity of the local arrays (== n_ids for a single-GPU crowd)
+    int n_ids = 0;       // global id space: size of every id-indexed table and of the host-facing arrays
     uint32_t rng0 = 1;   // stream state before frame 1's first draw
+    // spatial domain decomposition (lc_dd_*): mailbox other ranks store into, device-side exchange state
+    int dd_rank = 0, dd_world = 1;
+    char* mailbox = nullptr;
+    lc::DomainLayout lay{};
+    lc::DomainDev* ddev = nullptr;
+    int* owned_dev = nullptr;
+    std::vector<void*> ipc_opened;
     // staging (device) for state exchange, pinned host mirror of Ctl
     float* stage = nullptr;
     size_t stage_floats = 0;
@@ -104,6 +115,12 @@ static int upload_params(lc_sim* s) {
     CK(cudaMemcpyAsync(s->dP, &s->hp, sizeof(lc::Params), cudaMemcpyHostToDevice, s->st));
     return 0;
 }
+// only the parameter matrices: Params::n is rewritten on the device every frame in domain mode
+static int upload_weights(lc_sim* s) {
+    const size_t off = offsetof(lc::Params, m_cv);
+    CK(cudaMemcpyAsync((char*)s->dP + off, (const char*)&s->hp + off, sizeof(lc::Params) - off, cudaMemcpyHostToDevice, s->st));
+    return 0;
+}
 
 static int read_ctl(lc_sim* s) {
     CK(cudaMemcpyAsync(s->hctl, s->b.ctl, sizeof(lc::Ctl), cudaMemcpyDeviceToHost, s->st));
@@ -121,7 +138,9 @@ void lc_destroy(lc_sim* s) {
     cudaSetDevice(s->device);
     if (s->st) cudaStreamSynchronize(s->st);
     for (auto& g : s->gexec) if (g) cudaGraphExecDestroy(g);
+    for (void* p : s->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void* p : s->allocs) cudaFree(p);
+    if (s->mailbox) cudaFree(s->mailbox);
     if (s->dP) cudaFree(s->dP);
     if (s->stage) cudaFree(s->stage);
     if (s->hctl) cudaFreeHost(s->hctl);
@@ -131,7 +150,10 @@ void lc_destroy(lc_sim* s) {
     delete s;
 }
 
-int32_t lc_create(const lc_desc* d, lc_sim** out) {
+}  // extern "C"
+
+// lc_create (dom == nullptr) and lc_dd_create share everything but the choice of the initially local agents
+static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out) {
     if (!d || !out) return fail(LC_ERR_ARG, "lc_create: null argument");
     *out = nullptr;
     if (d->n < 2) return fail(LC_ERR_ARG, "lc_create: n must be >= 2 (the reference dereferences a null comm partner for n == 1, comm.cpp:273-285)");
@@ -144,9 +166,54 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
         return fail(LC_ERR_CUDA, "lc_create: no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
     if (d->device < 0 || d->device >= ndev) return fail(LC_ERR_ARG, "lc_create: device %d out of range", d->device);
     CK(cudaSetDevice(d->device));
+    // ---- domain decomposition: strip bounds, the initially owned subset, capacities ----
+    const int n_ids = d->n;
+    const int world = dom ? dom->world : 1, rank = dom ? dom->rank : 0;
+    std::vector<int> ids;
+    std::vector<float> xb(lc::DD_MAX_WORLD + 1, 0.f);
+    float halo = 0.f;
+    int cap = n_ids, annex = 0, cap_halo = 0;
+    if (dom) {
+        if (world < 2 || world > lc::DD_MAX_WORLD || rank < 0 || rank >= world)
+            return fail(LC_ERR_ARG, "lc_dd_create: need 2 <= world <= %d and 0 <= rank < world", lc::DD_MAX_WORLD);
+        if (d->flags & LC_FLAG_DEBUG_LISTS) return fail(LC_ERR_ARG, "lc_dd_create: LC_FLAG_DEBUG_LISTS is single-GPU only");
+        const float R = d->radius + d->radius;
+        const float reach = R + 2.f * (1.f / 60.f) * 1.01f + 0.002f + 0.002f;
+        // |vel| <= 1.045 always (unit clamp, physics.cpp:45-48, then at most 9 % from push_away, physics.cpp:32-34);
+        // the band covers the TTC cutoff at 1.05 plus the collision reach.  k_frame_begin checks the live cutoff against it.
+        halo = R + 10.f * 1.05f * 1.001f + 0.01f + reach + 0.05f;
+        xb[0] = -3.0e38f; xb[world] = 3.0e38f;
+        if (dom->x_bounds) {
+            for (int r = 1; r < world; ++r) xb[r] = dom->x_bounds[r];
+        } else {  // balanced strips: cut at the n/world quantiles of the initial x coordinates (same on every rank)
+            std::vector<float> xs(n_ids);
+            for (int i = 0; i < n_ids; ++i) xs[i] = d->pos[2 * i];
+            std::sort(xs.begin(), xs.end());
+            for (int r = 1; r < world; ++r) {
+                const size_t k = (size_t)r * n_ids / world;
+                xb[r] = 0.5f * (xs[k - 1] + xs[k]);
+            }
+        }
+        for (int r = 1; r + 1 < world; ++r)
+            if (!(xb[r + 1] - xb[r] >= 1.05f * halo))
+                return fail(LC_ERR_ARG, "lc_dd_create: strip %d is %.2f m wide; strips must be wider than the %.2f m ghost band", r, xb[r + 1] - xb[r], halo);
+        for (int r = 1; r < world; ++r)
+            if (!(xb[r] > xb[r - 1])) return fail(LC_ERR_ARG, "lc_dd_create: x_bounds must increase");
+        for (int i = 0; i < n_ids; ++i) {
+            const float x = d->pos[2 * i];
+            if (x >= xb[rank] && x < xb[rank + 1]) ids.push_back(i);
+        }
+        cap_halo = dom->halo_capacity > 0 ? dom->halo_capacity : std::max(65536, n_ids / world / 2);
+        cap = dom->capacity > 0 ? dom->capacity : (int)std::min<long long>((long long)n_ids + 2 * cap_halo, (long long)(n_ids / world) * 3 / 2 + 2 * cap_halo + 4096);
+        if ((int)ids.size() > cap) return fail(LC_ERR_CAPACITY, "lc_dd_create: %d initial agents exceed the capacity %d", (int)ids.size(), cap);
+        annex = world * lc::DD_CAND_CAP;
+    }
     lc_sim* s = new lc_sim;
     s->device = d->device;
-    const int n = s->n = d->n;
+    s->n_ids = n_ids;
+    s->dd_rank = rank; s->dd_world = world;
+    const int n = s->n = cap;           // slot capacity == launch width
+    const int n_loc = dom ? (int)ids.size() : n_ids;
     int rc = 0;
     auto bail = [&](int code) { lc_destroy(s); return code; };
 #define CKB(x) do { rc = (x); if (rc) return bail(rc); } while (0)
@@ -155,7 +222,7 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
     CKC(cudaEventCreate(&s->ev0));
     CKC(cudaEventCreate(&s->ev1));
     CKB(alloc_arrays(s, s->b.cur, n));
-    CKB(alloc_arrays(s, s->b.srt, n));
+    CKB(alloc_arrays(s, s->b.srt, n + annex));  // annex: comm-partner payload of other ranks' candidates (k_dd_cand)
     lc::Buffers& b = s->b;
     CKC(dalloc(&b.posf, n)); s->allocs.push_back(b.posf);
     CKC(dalloc(&b.srt_pq, (size_t)2 * ((n + 1) / 2))); s->allocs.push_back(b.srt_pq);
@@ -165,36 +232,61 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
     CKC(dalloc(&b.cell_start, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_start);
     CKC(dalloc(&b.tile_agg, lc::SCAN_TILES)); s->allocs.push_back(b.tile_agg);
     CKC(cudaMemset(b.tile_agg, 0, sizeof(unsigned long long) * lc::SCAN_TILES));
-    CKC(dalloc(&b.slot_of_id, n)); s->allocs.push_back(b.slot_of_id);
-    CKC(dalloc(&b.cand, n)); s->allocs.push_back(b.cand);
-    CKC(dalloc(&b.cand2, lc::REFINE_MAX)); s->allocs.push_back(b.cand2);
+    CKC(dalloc(&b.slot_of_id, n_ids)); s->allocs.push_back(b.slot_of_id);
+    CKC(dalloc(&b.cand, n + annex)); s->allocs.push_back(b.cand);
+    CKC(dalloc(&b.cand2, lc::REFINE_MAX + annex)); s->allocs.push_back(b.cand2);
     CKC(dalloc(&b.blkred, (size_t)(n + 127) / 128)); s->allocs.push_back(b.blkred);
     CKC(dalloc(&b.blkext, (size_t)((n + 1023) / 1024) * lc::HULL_K)); s->allocs.push_back(b.blkext);
     CKC(dalloc(&b.near_cnt, n)); s->allocs.push_back(b.near_cnt);
     CKC(dalloc(&b.near_idx, (size_t)n * lc::MAX_NEAR)); s->allocs.push_back(b.near_idx);
-    CKC(dalloc(&b.events, n)); s->allocs.push_back(b.events);
-    CKC(dalloc(&b.ev_by_id, n)); s->allocs.push_back(b.ev_by_id);
-    CKC(dalloc(&b.partner_id, n)); s->allocs.push_back(b.partner_id);
-    CKC(dalloc(&b.nbr_cnt, n)); s->allocs.push_back(b.nbr_cnt);
+    CKC(dalloc(&b.events, (size_t)std::max(n, world * lc::DD_EV_CAP))); s->allocs.push_back(b.events);
+    CKC(dalloc(&b.ev_by_id, n_ids)); s->allocs.push_back(b.ev_by_id);
+    CKC(dalloc(&b.partner_id, n_ids)); s->allocs.push_back(b.partner_id);
+    CKC(dalloc(&b.nbr_cnt, n_ids)); s->allocs.push_back(b.nbr_cnt);
     b.list_cap = 0;
     b.nbr_list = nullptr;
     if (d->flags & LC_FLAG_DEBUG_LISTS) {
-        b.list_cap = n - 1 < 256 ? n - 1 : 256;
-        CKC(dalloc(&b.nbr_list, (size_t)n * b.list_cap)); s->allocs.push_back(b.nbr_list);
-        CKC(cudaMemset(b.nbr_list, 0xff, sizeof(int) * (size_t)n * b.list_cap));
+        b.list_cap = n_ids - 1 < 256 ? n_ids - 1 : 256;
+        CKC(dalloc(&b.nbr_list, (size_t)n_ids * b.list_cap)); s->allocs.push_back(b.nbr_list);
+        CKC(cudaMemset(b.nbr_list, 0xff, sizeof(int) * (size_t)n_ids * b.list_cap));
     }
     CKC(dalloc(&b.ctl, 1)); s->allocs.push_back(b.ctl);
     CKC(cudaMemset(b.ctl, 0, sizeof(lc::Ctl)));
-    CKC(cudaMemset(b.partner_id, 0xff, sizeof(int) * n));
-    CKC(cudaMemset(b.nbr_cnt, 0, sizeof(int) * n));
+    CKC(cudaMemset(b.partner_id, 0xff, sizeof(int) * n_ids));
+    CKC(cudaMemset(b.nbr_cnt, 0, sizeof(int) * n_ids));
     CKC(cudaMemset(b.near_cnt, 0, sizeof(int) * n));
     CKC(cudaMalloc((void**)&s->dP, sizeof(lc::Params)));
     CKC(cudaMallocHost((void**)&s->hctl, sizeof(lc::Ctl)));
-    s->stage_floats = (size_t)n * 16;
+    s->stage_floats = (size_t)n_ids * 16;
     CKC(cudaMalloc((void**)&s->stage, sizeof(float) * s->stage_floats));
+    b.dd = nullptr;
+    if (dom) {
+        s->lay = lc::domain_layout(world, n, cap_halo, n_ids);
+        CKC(cudaMalloc((void**)&s->mailbox, s->lay.total));
+        CKC(cudaMemset(s->mailbox, 0, s->lay.total));
+        CKC(cudaMemset(s->mailbox + s->lay.ev_by_id, 0xff, sizeof(float) * (size_t)n_ids));  // NaN = "no finish time"
+        CKC(dalloc(&s->ddev, 1)); s->allocs.push_back(s->ddev);
+        CKC(dalloc(&s->owned_dev, n_ids)); s->allocs.push_back(s->owned_dev);
+        lc::DomainDev hd{};
+        hd.lay = s->lay;
+        hd.mbox[rank] = s->mailbox;
+        hd.replan[0] = hd.replan[1] = 0x7fffffff;
+        {   // how long a rank waits for a peer's flag before it reports LC_ERR_CUDA instead of hanging the GPU
+            const char* e = getenv("LC_DD_TIMEOUT_MS");
+            const unsigned long long ms = e ? strtoull(e, nullptr, 10) : 10000ull;
+            hd.spin_timeout_ns = ms * 1000ull * 1000ull;
+        }
+        CKC(cudaMemcpy(s->ddev, &hd, sizeof hd, cudaMemcpyHostToDevice));
+        b.dd = s->ddev;
+    }
 
     lc::Params& P = s->hp;
-    P.n = n;
+    P.n = n_loc;
+    P.n_ids = n_ids;
+    P.cap = n;
+    P.dd_rank = rank; P.dd_world = world;
+    for (int r = 0; r <= lc::DD_MAX_WORLD; ++r) P.dd_xb[r] = xb[r];
+    P.dd_halo = halo;
     P.r = d->radius;
     P.R = d->radius + d->radius;       // LMP.cpp:53 i._r + j._r
     P.RR = P.R * P.R;                  // BoundVolume.cpp:106 _r * _r
@@ -204,7 +296,7 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
         P.near_reach = reach + 0.002f;
     }
     P.max_duration = d->max_duration;
-    P.lcg_stride = lcg_pow(16807u, (uint64_t)n);
+    P.lcg_stride = lcg_pow(16807u, (uint64_t)n_ids);
     P.flags = d->flags;
     P.stencil_req = d->stencil > 0 ? d->stencil : 2;
     memset(P.m_cv, 0, sizeof P.m_cv);
@@ -216,31 +308,46 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
 
     // initial component values: demo.cpp:563-581 create_robo, ai.cpp:107-127 ai::init, physics.cpp:15-21 prewarm
     {
-        std::vector<float> h((size_t)n * 9);
-        float* facing = h.data();           // [n][2]
-        float* gd = h.data() + 2 * (size_t)n;   // [n]
-        float* mt = h.data() + 3 * (size_t)n;   // [n]
-        for (int i = 0; i < n; ++i) {
+        const size_t m = (size_t)n_loc;
+        std::vector<float> h(m * 13 + 1);
+        float* hpos = h.data();             // [m][2]
+        float* hgoal = h.data() + 2 * m;    // [m][2]
+        float* facing = h.data() + 4 * m;   // [m][2]
+        float* gd = h.data() + 6 * m;       // [m]
+        float* mt = h.data() + 7 * m;       // [m]
+        float* hvel = h.data() + 8 * m;     // [m][2]  (domain mode: optional developed-flow start)
+        float* hvfh = h.data() + 10 * m;    // [m][2]
+        int* hid = reinterpret_cast<int*>(h.data() + 12 * m);  // [m]
+        const bool has_v = dom && dom->vel && dom->vel_forehalf;
+        for (size_t k = 0; k < m; ++k) {
+            const int i = dom ? ids[k] : (int)k;
+            hpos[2 * k] = d->pos[2 * i]; hpos[2 * k + 1] = d->pos[2 * i + 1];
+            hgoal[2 * k] = d->goal[2 * i]; hgoal[2 * k + 1] = d->goal[2 * i + 1];
             float dx = d->goal[2 * i] - d->pos[2 * i], dy = d->goal[2 * i + 1] - d->pos[2 * i + 1];
-            facing[2 * i] = dx; facing[2 * i + 1] = dy;      // un-normalised (demo.cpp:580)
+            facing[2 * k] = dx; facing[2 * k + 1] = dy;      // un-normalised (demo.cpp:580)
             float len = sqrtf(dx * dx + dy * dy);            // glm::length (ai.cpp:116)
-            gd[i] = len;
-            float m = -1.0f;                                  // ai.cpp:121-126
-            m += len;
-            mt[i] = m;
+            gd[k] = len;
+            float mn = -1.0f;                                 // ai.cpp:121-126
+            mn += len;
+            mt[k] = mn;
+            hid[k] = i;
+            if (has_v) {
+                hvel[2 * k] = dom->vel[2 * i]; hvel[2 * k + 1] = dom->vel[2 * i + 1];
+                hvfh[2 * k] = dom->vel_forehalf[2 * i]; hvfh[2 * k + 1] = dom->vel_forehalf[2 * i + 1];
+            }
         }
         float* dpos = s->stage;
-        float* dgoal = s->stage + 2 * (size_t)n;
-        float* dfacing = s->stage + 4 * (size_t)n;
-        float* dgd = s->stage + 6 * (size_t)n;
-        float* dmt = s->stage + 7 * (size_t)n;
-        CKC(cudaMemcpyAsync(dpos, d->pos, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
-        CKC(cudaMemcpyAsync(dgoal, d->goal, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
-        CKC(cudaMemcpyAsync(dfacing, facing, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
-        CKC(cudaMemcpyAsync(dgd, gd, sizeof(float) * n, cudaMemcpyHostToDevice, s->st));
-        CKC(cudaMemcpyAsync(dmt, mt, sizeof(float) * n, cudaMemcpyHostToDevice, s->st));
-        lc::launch_set_state(s->dP, n, b, (const float2*)dpos, nullptr, nullptr, nullptr, (const float2*)dfacing, nullptr,
-                             dgd, nullptr, (const float2*)dgoal, dmt, 1, s->st, &s->launches);
+        float* dgoal = s->stage + 2 * m;
+        float* dfacing = s->stage + 4 * m;
+        float* dgd = s->stage + 6 * m;
+        float* dmt = s->stage + 7 * m;
+        float* dvel = s->stage + 8 * m;
+        float* dvfh = s->stage + 10 * m;
+        int* did = reinterpret_cast<int*>(s->stage + 12 * m);
+        CKC(cudaMemcpyAsync(s->stage, h.data(), sizeof(float) * 13 * m, cudaMemcpyHostToDevice, s->st));
+        lc::launch_set_state(s->dP, n, b, (const float2*)dpos, has_v ? (const float2*)dvel : nullptr,
+                             has_v ? (const float2*)dvfh : nullptr, nullptr, (const float2*)dfacing, nullptr,
+                             dgd, nullptr, (const float2*)dgoal, dmt, 1, s->st, &s->launches, dom ? did : nullptr);
         CKC(cudaStreamSynchronize(s->st));  // h goes out of scope
     }
     s->rng0 = d->rng_state;
@@ -255,6 +362,12 @@ int32_t lc_create(const lc_desc* d, lc_sim** out) {
 #undef CKC
 }
 
+extern "C" {
+int32_t lc_create(const lc_desc* d, lc_sim** out) { return create_impl(d, nullptr, out); }
+int32_t lc_dd_create(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out) {
+    if (!dom) return fail(LC_ERR_ARG, "lc_dd_create: null domain description");
+    return create_impl(d, dom, out);
+}
 }  // extern "C"
 
 #define SIM_ENTER(s)                                                   \
@@ -275,7 +388,7 @@ int32_t lc_set_weights(lc_sim* s, const float* m_cv, const float* m_f) {
     if (m_cv) memcpy(s->hp.m_cv, m_cv, sizeof s->hp.m_cv);
     if (m_f) memcpy(s->hp.m_f, m_f, sizeof s->hp.m_f);
     CK(cudaStreamSynchronize(s->st));  // hp is the copy source; keep it stable
-    return upload_params(s);
+    return upload_weights(s);
 }
 
 int32_t lc_step(lc_sim* s, int32_t nframes) {
@@ -329,14 +442,18 @@ int32_t lc_run_to_completion(lc_sim* s, int32_t* frames) {
 int32_t lc_get_state(lc_sim* s, float* pos, float* vel, float* vfh, float* c, float* facing, float* lgoal,
                      float* goal_dist, int32_t* num_done) {
     SIM_ENTER(s);
-    const size_t n = (size_t)s->n;
+    const size_t n = (size_t)s->n_ids;
     float* st = s->stage;
     float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
     float* dc = st + 6 * n; float2* dfac = (float2*)(st + 9 * n); float2* dlg = (float2*)(st + 11 * n);
     float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
+    if (s->dd_world > 1) {  // domain mode: entries of agents owned by other ranks read as zero; lc_dd_get_owned tells which
+        CK(cudaMemsetAsync(st, 0, sizeof(float) * s->stage_floats, s->st));
+        CK(cudaMemsetAsync(s->owned_dev, 0, sizeof(int) * n, s->st));
+    }
     lc::launch_get_state(s->dP, s->n, s->b, pos ? dpos : nullptr, vel ? dvel : nullptr, vfh ? dvfh : nullptr,
                          c ? dc : nullptr, facing ? dfac : nullptr, lgoal ? dlg : nullptr, goal_dist ? dgd : nullptr,
-                         num_done ? dnd : nullptr, s->st, &s->launches);
+                         num_done ? dnd : nullptr, s->st, &s->launches, s->owned_dev);
     if (pos) CK(cudaMemcpyAsync(pos, dpos, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
     if (vel) CK(cudaMemcpyAsync(vel, dvel, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
     if (vfh) CK(cudaMemcpyAsync(vfh, dvfh, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
@@ -352,6 +469,7 @@ int32_t lc_get_state(lc_sim* s, float* pos, float* vel, float* vfh, float* c, fl
 int32_t lc_set_state(lc_sim* s, const float* pos, const float* vel, const float* vfh, const float* c,
                      const float* facing, const float* lgoal, const float* goal_dist, const int32_t* num_done) {
     SIM_ENTER(s);
+    if (s->dd_world > 1) return fail(LC_ERR_ARG, "lc_set_state: not available for a domain-decomposed crowd (pass the initial tables to lc_dd_create)");
     const size_t n = (size_t)s->n;
     float* st = s->stage;
     float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
@@ -377,7 +495,7 @@ int32_t lc_get_rng(lc_sim* s, uint32_t* rng_state) {
     SIM_ENTER(s);
     int rc = read_ctl(s);
     if (rc) return rc;
-    *rng_state = lcm::lcg_mul(s->rng0, lcg_pow(16807u, (uint64_t)s->hctl->frame * (uint64_t)s->n));
+    *rng_state = lcm::lcg_mul(s->rng0, lcg_pow(16807u, (uint64_t)s->hctl->frame * (uint64_t)s->n_ids));
     return LC_OK;
 }
 
@@ -386,7 +504,7 @@ int32_t lc_set_rng(lc_sim* s, uint32_t rng_state) {
     int rc = read_ctl(s);
     if (rc) return rc;
     // rng0 is defined relative to frame 0; rebase so that lc_get_rng stays consistent
-    uint64_t consumed = (uint64_t)s->hctl->frame * (uint64_t)s->n;
+    uint64_t consumed = (uint64_t)s->hctl->frame * (uint64_t)s->n_ids;
     // inverse of 16807^consumed mod (2^31-1): a^(m-2) is the modular inverse (m prime)
     uint32_t inv = lcg_pow(lcg_pow(16807u, consumed), 2147483647ull - 2ull);
     s->rng0 = lcm::lcg_mul(rng_state, inv);
@@ -412,14 +530,14 @@ int32_t lc_get_scores(lc_sim* s, float* avg_velocity, float* group_time, float* 
 
 int32_t lc_get_partners(lc_sim* s, int32_t* partner) {
     SIM_ENTER(s);
-    CK(cudaMemcpyAsync(partner, s->b.partner_id, sizeof(int) * (size_t)s->n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaMemcpyAsync(partner, s->b.partner_id, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }
 
 int32_t lc_get_neighbor_counts(lc_sim* s, int32_t* count) {
     SIM_ENTER(s);
-    CK(cudaMemcpyAsync(count, s->b.nbr_cnt, sizeof(int) * (size_t)s->n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaMemcpyAsync(count, s->b.nbr_cnt, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }
@@ -428,7 +546,7 @@ int32_t lc_get_neighbor_lists(lc_sim* s, int32_t* idx, int32_t cap) {
     SIM_ENTER(s);
     if (!s->b.nbr_list) return fail(LC_ERR_ARG, "lc_get_neighbor_lists: create the simulation with LC_FLAG_DEBUG_LISTS");
     if (cap != s->b.list_cap) return fail(LC_ERR_ARG, "lc_get_neighbor_lists: cap_per_agent must be %d", s->b.list_cap);
-    CK(cudaMemcpyAsync(idx, s->b.nbr_list, sizeof(int) * (size_t)s->n * cap, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaMemcpyAsync(idx, s->b.nbr_list, sizeof(int) * (size_t)s->n_ids * cap, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }
@@ -478,6 +596,92 @@ int32_t lc_step_profiled(lc_sim* s, int32_t nframes, float* ms_per_kernel) {
     for (int k = 0; k < K; ++k) ms_per_kernel[k] = nframes ? (float)(acc[k] / nframes) : 0.f;
     for (auto& e : ev) cudaEventDestroy(e);
     CK(cudaGetLastError());
+    return LC_OK;
+}
+
+
+// ---- spatial domain decomposition: wiring the ranks' mailboxes together ----
+int32_t lc_dd_mailbox(lc_sim* s, void** dev_ptr, uint64_t* bytes) {
+    SIM_ENTER(s);
+    if (!s->mailbox) return fail(LC_ERR_ARG, "lc_dd_mailbox: not a domain-decomposed crowd");
+    if (dev_ptr) *dev_ptr = s->mailbox;
+    if (bytes) *bytes = (uint64_t)s->lay.total;
+    return LC_OK;
+}
+
+int32_t lc_dd_ipc_handle(lc_sim* s, void* handle64) {
+    SIM_ENTER(s);
+    if (!s->mailbox || !handle64) return fail(LC_ERR_ARG, "lc_dd_ipc_handle: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, s->mailbox));
+    memcpy(handle64, &h, 64);
+    return LC_OK;
+}
+
+static int dd_set_peer(lc_sim* s, int peer_rank, void* ptr) {
+    if (peer_rank < 0 || peer_rank >= s->dd_world || peer_rank == s->dd_rank) return fail(LC_ERR_ARG, "lc_dd_connect: bad peer rank %d", peer_rank);
+    CK(cudaStreamSynchronize(s->st));
+    CK(cudaMemcpy((char*)s->ddev + offsetof(lc::DomainDev, mbox) + sizeof(char*) * peer_rank, &ptr, sizeof(char*), cudaMemcpyHostToDevice));
+    return LC_OK;
+}
+
+int32_t lc_dd_connect(lc_sim* s, int32_t peer_rank, void* peer_mailbox, int32_t peer_device) {
+    SIM_ENTER(s);
+    if (!s->mailbox || !peer_mailbox) return fail(LC_ERR_ARG, "lc_dd_connect: bad argument");
+    if (peer_device != s->device) {
+        int can = 0;
+        CK(cudaDeviceCanAccessPeer(&can, s->device, peer_device));
+        if (!can) return fail(LC_ERR_CUDA, "lc_dd_connect: device %d cannot access device %d (no NVLink / P2P path)", s->device, peer_device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) return fail(LC_ERR_CUDA, "cudaDeviceEnablePeerAccess failed: %s", cudaGetErrorString(e));
+    }
+    return dd_set_peer(s, peer_rank, peer_mailbox);
+}
+
+int32_t lc_dd_connect_ipc(lc_sim* s, int32_t peer_rank, const void* handle64) {
+    SIM_ENTER(s);
+    if (!s->mailbox || !handle64) return fail(LC_ERR_ARG, "lc_dd_connect_ipc: bad argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void* ptr = nullptr;
+    CK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    s->ipc_opened.push_back(ptr);
+    return dd_set_peer(s, peer_rank, ptr);
+}
+
+int32_t lc_dd_get_owned(lc_sim* s, int32_t* owned) {
+    SIM_ENTER(s);
+    if (!s->owned_dev || !owned) return fail(LC_ERR_ARG, "lc_dd_get_owned: bad argument");
+    const size_t n = (size_t)s->n_ids;
+    CK(cudaMemsetAsync(s->owned_dev, 0, sizeof(int) * n, s->st));
+    lc::launch_get_state(s->dP, s->n, s->b, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s->st,
+                         &s->launches, s->owned_dev);
+    CK(cudaMemcpyAsync(owned, s->owned_dev, sizeof(int) * n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return LC_OK;
+}
+
+int32_t lc_dd_get_partials(lc_sim* s, uint64_t* lastvel, int32_t* nonfinite, float* avg_velocity_before) {
+    SIM_ENTER(s);
+    if (s->dd_world <= 1) return fail(LC_ERR_ARG, "lc_dd_get_partials: not a domain-decomposed crowd");
+    lc::launch_finalize(s->dP, s->b, s->st, &s->launches);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    if (lastvel) *lastvel = (uint64_t)s->hctl->lastvel;
+    if (nonfinite) *nonfinite = s->hctl->nonfinite;
+    if (avg_velocity_before) *avg_velocity_before = s->hctl->avg_velocity;
+    return LC_OK;
+}
+
+int32_t lc_dd_counts(lc_sim* s, int32_t* n_local, int32_t* capacity) {
+    SIM_ENTER(s);
+    lc::Params hp;
+    CK(cudaMemcpyAsync(&hp, s->dP, sizeof hp, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    if (n_local) *n_local = hp.n;
+    if (capacity) *capacity = s->n;
     return LC_OK;
 }
 

@@ -115,7 +115,8 @@ __global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__
     __shared__ float s_ft[1024];
     __shared__ int s_flag[1024];
     const int tid = threadIdx.x;
-    const int n = P->n;
+    const int n = P->n_ids;  // everything below that walks "all agents" is indexed by global id
+    const bool dd = P->dd_world > 1;
     consume_block_reductions(ctl, b);
     if (tid == 0) fold_avg_velocity(ctl);
     __syncthreads();
@@ -169,7 +170,25 @@ __global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__
         }
         __syncthreads();
         bool all_done = nnd == 0;
-        if (fake_time > P->max_duration) {  // demo.cpp:691-700
+        if (fake_time > P->max_duration && dd) {
+            // domain mode: k_dd_pack of every rank scattered the finish times of its owned, not-done agents into the
+            // scoring rank's id-indexed table (NaN = none); fold them in id order there.  Other ranks only latch.
+            if (P->dd_rank == 0) {
+                float* tab = reinterpret_cast<float*>(b.dd->mbox[0] + b.dd->lay.ev_by_id);
+                for (int base = 0; base < n; base += blockDim.x) {
+                    const int id = base + tid;
+                    const float v = id < n ? tab[id] : CUDART_NAN_F;
+                    s_ft[tid] = v;
+                    s_flag[tid] = (v == v);
+                    __syncthreads();
+                    if (tid == 0)
+                        for (int k = 0; k < blockDim.x; ++k)
+                            if (s_flag[k]) update_runs(ctl, s_ft[k]);
+                    __syncthreads();
+                }
+            }
+            all_done = true;
+        } else if (fake_time > P->max_duration) {  // demo.cpp:691-700
             for (int base = 0; base < n; base += blockDim.x) {
                 int id = base + tid;
                 int flag = 0;
@@ -206,7 +225,11 @@ __global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
         ctl->n_cand = 0;
-        ctl->replan1 = ctl->replan2 = 0x7fffffff;
+        if (!dd) ctl->replan1 = ctl->replan2 = 0x7fffffff;  // domain mode: k_dd_wait merged the global gate
+        if (dd) {  // the ghost band was sized for the speed bound (domain.cuh); a wider cutoff would miss neighbours
+            const float vm = __uint_as_float(ctl->vmax);
+            if (!(P->R + 10.f * vm * 1.001f + 0.01f + P->near_reach <= P->dd_halo) && !ctl->error) ctl->error = -5;
+        }
         ctl->overlap2 = 0ull;
         ctl->coll_hits = 0ull;
     }
@@ -382,7 +405,7 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     b.srt.meta[s] = mt;
     b.slot_of_id[mt.x] = s;
     // ai.cpp:154,161-163: need_replan = done && goal_dist > 1 (wall-free: the lost_frames clause cannot fire)
-    if (mt.y & 1) {
+    if ((mt.y & 1) && P->dd_world <= 1) {
         float gd = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
         if (gd > 1.f) {
             int old = atomicMin(&ctl->replan1, mt.x);
@@ -390,7 +413,7 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
             if (loser != 0x7fffffff) atomicMin(&ctl->replan2, loser);
         }
     }
-    if (!(P->flags & 1u)) {
+    if (!(P->flags & 1u) && !(mt.y & META_GHOST)) {  // ghosts are published as candidates by their owner (k_dd_cand)
         // keep every agent that is not inside (by delta) the polygon of extreme agents: only those can be
         // the arg-max of comm.cpp:201-220 for any query (proof in DESIGN.md)
         const int ne = ctl->n_edges;
@@ -561,6 +584,7 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int n = P->n;
+    if ((int)(blockIdx.x * blockDim.x) >= n) return;  // domain mode launches for the capacity, not the count
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     int not_done_after = 0;
     // Third pruning stage of the comm-partner candidates, per block: the 128 agents of a block are neighbours in cell
@@ -627,7 +651,7 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
                                   ++cnt;
                               });
         float ttcFx = 0.f, ttcFy = 0.f;
-        int* lst = (P->flags & 4u) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
+        int* lst = ((P->flags & 4u) && !(b.srt.meta[s].y & META_GHOST)) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
         if (cnt <= MAX_HITS) {
             int last = -1;
             for (int k = 0; k < cnt; ++k) {
@@ -658,12 +682,14 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
                 if (lst && k < b.list_cap) lst[k] = bid;
             }
         }
-        b.nbr_cnt[id] = cnt;
+        int4 mt = b.srt.meta[s];
+        const bool owned = !(mt.y & META_GHOST);  // ghosts are advanced too (the collision pass needs their integrated
+                                                  // position) but never counted: their owner does that
+        if (owned) b.nbr_cnt[id] = cnt;
         if (n_near > MAX_NEAR) atomicAdd(&ctl->near_overflow, 1);
         b.near_cnt[s] = n_near;
-        if (n_overlap) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
+        if (n_overlap && owned) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
 
-        int4 mt = b.srt.meta[s];
         const float2 goal = b.srt.goal[s];
         float2 lgoal = b.srt.lgoal[s];
         float2 facing = b.srt.facing[s];
@@ -687,7 +713,7 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
                 }
             }
             if (best_id < 0) atomicCAS(&ctl->error, 0, -3);  // comm.cpp:273-285: null partner is UB in the reference
-            b.partner_id[id] = best_id;
+            if (owned) b.partner_id[id] = best_id;
             const float4 pj = __ldg(&b.srt.pv[best_slot]);
             const float4 cj = __ldg(&b.srt.c4[best_slot]);
             // comm.cpp:144-192 x(): COSINE_REL + PROX + SOFTSIGN_GOAL; partner (x, y) of a vec3 = (x, 0): quirk Q2
@@ -752,11 +778,13 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
         }
         if (num_done == 1 && !(mt.y & 2)) {  // will be counted by demo::run at the start of the next frame
             mt.y |= 2;
-            int k = atomicAdd(&ctl->ev_count, 1);
-            b.events[k] = make_int2(id, mt.w);
+            if (owned) {
+                int k = atomicAdd(&ctl->ev_count, 1);
+                b.events[k] = make_int2(id, mt.w);
+            }
         }
         mt.y = (mt.y & ~1) | num_done;
-        not_done_after = num_done == 0;
+        not_done_after = num_done == 0 && owned;
         // LMP.cpp:261-273: one draw for both components
         const float eps = lcg_uniform((uint32_t)mt.z, -.01f, .01f);
         mt.z = (int)lcg_mul((uint32_t)mt.z, P->lcg_stride);
@@ -894,12 +922,12 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
             }
             if (cnt) {
                 b.cur.vfh[s] = h;
-                atomicAdd(&ctl->coll_hits, (unsigned long long)cnt);
+                if (!(mt.y & META_GHOST)) atomicAdd(&ctl->coll_hits, (unsigned long long)cnt);
             }
         }
         b.posf[s] = make_float2(px, py);
         speed = __fsqrt_rn(dot3_xz(me.z, me.w, me.z, me.w));
-        if (!(mt.y & 1)) {  // physics.cpp:72-76
+        if (!(mt.y & 1) && !(mt.y & META_GHOST)) {  // physics.cpp:72-76
             lv_id = (uint32_t)(mt.x + 1);
             // a non-finite speed anywhere but at the last agent poisons the running average (NaN * 0): counted here,
             // resolved in fold_avg_velocity
@@ -940,11 +968,13 @@ __global__ void __launch_bounds__(1024) k_finalize(const Params* __restrict__ P,
 // state in id order for the host (POOL.all_sync view, Pool.cpp:69-91)
 __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P, Buffers b, float2* pos, float2* vel,
                                                     float2* vfh, float* c3, float2* facing, float2* lgoal,
-                                                    float* goal_dist, int* num_done) {
+                                                    float* goal_dist, int* num_done, int* owned) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
     const int4 mt = b.cur.meta[s];
+    if (mt.y & META_GHOST) return;  // the owner reports it
     const int id = mt.x;
+    if (owned) owned[id] = 1;
     const float4 pv = b.cur.pv[s];
     const float4 c4 = b.cur.c4[s];
     if (pos) pos[id] = b.posf[s];
@@ -977,7 +1007,7 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
                                                     const float2* vel, const float2* vfh, const float* c3,
                                                     const float2* facing, const float2* lgoal, const float* goal_dist,
                                                     const int* num_done, const float2* goal, const float* min_time,
-                                                    int init) {
+                                                    int init, const int* ids) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P->n) return;
     // bring the agent with id i to slot i
@@ -989,7 +1019,7 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
     float2 lg = init ? make_float2(0, 0) : b.srt.lgoal[so];
     float2 fc = init ? make_float2(0, 0) : b.srt.facing[so];
     float4 c4 = init ? make_float4(0, 0, 0, 0) : b.srt.c4[so];
-    int4 mt = init ? make_int4(i, 0, 0, 0) : b.srt.meta[so];
+    int4 mt = init ? make_int4(ids ? ids[i] : i, 0, 0, 0) : b.srt.meta[so];
     if (pos) p = pos[i];
     if (vel) { pv.z = vel[i].x; pv.w = vel[i].y; }
     if (vfh) h = vfh[i];
@@ -1037,8 +1067,30 @@ __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {
     }
 }
 
+#include "domain.cuh"
+
 // ---------------------------------------------------------------------------------------------------------
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids) {
+    DomainLayout L{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    L.cap_self = cap_self; L.cap_halo = cap_halo;
+    for (int p = 0; p < 2; ++p) {
+        L.blob[p] = take(sizeof(DomainBlob) * DD_MAX_WORLD);
+        L.flag[p] = take(sizeof(unsigned long long) * DD_MAX_WORLD);
+        L.cflag[p] = take(sizeof(unsigned long long) * DD_MAX_WORLD);
+        L.ncand[p] = take(sizeof(int) * DD_MAX_WORLD);
+        for (int r = 0; r < 3; ++r) L.region[p][r] = take(sizeof(float4) * DD_PLANES * (size_t)(r == 1 ? cap_self : cap_halo));
+        L.events[p] = take(sizeof(int2) * (size_t)DD_MAX_WORLD * DD_EV_CAP);
+        L.cand[p] = take(sizeof(float4) * 2 * (size_t)DD_MAX_WORLD * DD_CAND_CAP);
+    }
+    L.ev_by_id = take(sizeof(float) * (size_t)n_ids);
+    L.total = off;
+    (void)world;
+    return L;
+}
 
 void upload_dirs() {
     float dx[HULL_K], dy[HULL_K];
@@ -1059,10 +1111,19 @@ void upload_dirs() {
     cudaMemcpyToSymbol(c_dir2y, ey, sizeof ey);
 }
 
-void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev) {
+void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev) {
+    // n = launch width (the capacity in domain mode; kernels read the live count from Params::n on the device)
     // ev (optional, FRAME_KERNELS + 1 events): per-kernel device timing for bench.py's roofline leg
+    const bool dd = b.dd != nullptr;
     cudaMemsetAsync(b.cell_count, 0, sizeof(int) * CELL_ALLOC, st);
-    if (ev) cudaEventRecord(ev[0], st);
+    if (dd) {  // boundary exchange over peer memory (domain.cuh); its time is attributed to k_frame_begin's slot in `ev`
+        if (ev) cudaEventRecord(ev[0], st);
+        k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+        k_dd_publish<<<1, 1024, 0, st>>>(dP, b);
+        k_dd_wait<<<1, 1024, 0, st>>>(dP, b);
+        k_dd_unpack<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    }
+    if (ev && !dd) cudaEventRecord(ev[0], st);
     k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[1], st);
     k_bin<<<cdiv(n, 1024), 1024, 0, st>>>(dP, b);
@@ -1072,12 +1133,13 @@ void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, lo
     k_reorder<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[4], st);
     k_refine<<<1, 1024, 0, st>>>(dP, b);
+    if (dd) k_dd_cand<<<1, 1024, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[5], st);
     k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[6], st);
     k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[7], st);
-    if (launches) *launches += FRAME_KERNELS;
+    if (launches) *launches += FRAME_KERNELS + (dd ? DD_KERNELS : 0);
 }
 
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
@@ -1086,28 +1148,33 @@ void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t 
     if (launches) *launches += 2;
 }
 
+__global__ void __launch_bounds__(1024) k_consume_only(Buffers b) { consume_block_reductions(b.ctl, b); }
+
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches) {
-    k_finalize<<<1, 1024, 0, st>>>(dP, b);
+    // domain mode: avg_velocity of the last frame is a cross-rank quantity; only fold the block partials into Ctl
+    // (lc_dd_get_partials reads them, the host merges the ranks) and leave the rest to the next k_dd_publish
+    if (b.dd) k_consume_only<<<1, 1024, 0, st>>>(b);
+    else k_finalize<<<1, 1024, 0, st>>>(dP, b);
     if (launches) *launches += 1;
 }
 
 void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
                       float2* facing, float2* lgoal, float* goal_dist, int* num_done, cudaStream_t st,
-                      long long* launches) {
-    k_get_state<<<cdiv(n, 256), 256, 0, st>>>(dP, b, pos, vel, vfh, c3, facing, lgoal, goal_dist, num_done);
+                      long long* launches, int* owned) {
+    k_get_state<<<cdiv(n, 256), 256, 0, st>>>(dP, b, pos, vel, vfh, c3, facing, lgoal, goal_dist, num_done, owned);
     if (launches) *launches += 1;
 }
 
 void launch_set_state(const Params* dP, int n, const Buffers& b, const float2* pos, const float2* vel,
                       const float2* vfh, const float* c3, const float2* facing, const float2* lgoal,
                       const float* goal_dist, const int* num_done, const float2* goal, const float* min_time, int init,
-                      cudaStream_t st, long long* launches) {
+                      cudaStream_t st, long long* launches, const int* ids) {
     if (!init) {
         k_snapshot<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
         if (launches) *launches += 1;
     }
     k_set_state<<<cdiv(n, 256), 256, 0, st>>>(dP, b, pos, vel, vfh, c3, facing, lgoal, goal_dist, num_done, goal,
-                                              min_time, init);
+                                              min_time, init, ids);
     if (launches) *launches += 1;
 }
 

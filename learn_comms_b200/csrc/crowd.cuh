@@ -73,8 +73,19 @@ struct Ctl {
     int near_overflow, hit_overflow;
 };
 
+constexpr int DD_MAX_WORLD = 8;     // ranks of one spatially decomposed crowd (one B200 box)
+constexpr int DD_EV_CAP = 4096;      // done-events one rank can forward to the scoring rank per frame
+constexpr int DD_CAND_CAP = 4096;    // comm-partner candidates one rank can publish per frame
+constexpr int META_GHOST = 4;        // meta.y bit2: halo copy of an agent owned by a neighbouring rank
+
 struct Params {
-    int n;
+    int n;          // agents in the local arrays this frame; in domain mode (dd_world > 1) rewritten on the device every frame
+    int n_ids;      // size of the global id space (id-indexed tables, LCG stride); == n for a single-GPU crowd
+    int cap;        // capacity of the slot-indexed arrays (launch width); == n for a single-GPU crowd
+    // spatial domain decomposition in x strips: rank r owns xb[r] <= pos.x < xb[r+1]
+    int dd_rank, dd_world;
+    float dd_xb[DD_MAX_WORLD + 1];
+    float dd_halo;  // ghost band width: interaction cutoff at the speed bound + collision reach (domain.cuh)
     float r, R, RR, near_c, near_reach;
     float max_duration;
     uint32_t lcg_stride;  // 16807^n mod (2^31-1): advances an agent's private stream by one frame
@@ -107,21 +118,51 @@ struct Buffers {
     int* nbr_list;     // [n][list_cap] by id (LC_FLAG_DEBUG_LISTS)
     int list_cap;
     Ctl* ctl;
+    struct DomainDev* dd;  // device-side exchange state (domain.cuh); nullptr for a single-GPU crowd
 };
+
+// ---- spatial domain decomposition over NVLink peer memory (domain.cuh) ----
+// Agent record on the wire: 5 x 16 B planes (posf.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
+constexpr int DD_PLANES = 5;
+struct DomainBlob {               // one per (sender, parity), written into EVERY peer's mailbox
+    int n_sent[3];                // records the sender put into the regions of rank-1, itself, rank+1
+    uint32_t vmax;                // max speed bits over the sender's agents (interaction cutoff must be global)
+    int nnd;                      // owned agents that are not done (demo.cpp:667-669)
+    int nonfinite;
+    unsigned long long lastvel;   // physics.cpp:72-76: ((id + 1) << 32) | speed bits of the highest-id owned not-done agent
+    int replan[2];                // two lowest owned ids that need a replan (ai.cpp:151-168)
+    int n_events;                 // done-events forwarded to the scoring rank (rank 0)
+    int error;
+    int pad[2];
+};
+struct DomainLayout {             // byte offsets inside one rank's mailbox allocation; identical on every rank
+    size_t blob[2], flag[2], cflag[2], ncand[2], region[2][3], events[2], cand[2], ev_by_id, total;
+    int cap_self, cap_halo;
+};
+struct DomainDev {
+    char* mbox[DD_MAX_WORLD];     // mailbox base of every rank (own allocation + peer mappings)
+    DomainLayout lay;
+    int count[3];                 // records packed this frame for (rank-1, self, rank+1); cleared by k_dd_wait
+    int recv[3];                  // records waiting in this rank's regions (from the right, self, from the left)
+    int replan[2];
+    unsigned long long spin_timeout_ns;
+};
+DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 
 void upload_dirs();
 constexpr int FRAME_KERNELS = 7;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, force, collide
-void launch_frame(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
+constexpr int DD_KERNELS = 5;     // domain mode adds: dd_pack, dd_publish, dd_wait, dd_unpack (before frame_begin), dd_cand (after refine)
+void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
                   cudaEvent_t* ev = nullptr);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
                       float2* facing, float2* lgoal, float* goal_dist, int* num_done, cudaStream_t st,
-                      long long* launches);
+                      long long* launches, int* owned = nullptr);
 void launch_set_state(const Params* dP, int n, const Buffers& b, const float2* pos, const float2* vel,
                       const float2* vfh, const float* c3, const float2* facing, const float2* lgoal,
                       const float* goal_dist, const int* num_done, const float2* goal, const float* min_time, int init,
-                      cudaStream_t st, long long* launches);
+                      cudaStream_t st, long long* launches, const int* ids = nullptr);
 void launch_set_rng(const Params* dP, int n, const Buffers& b, uint32_t base, cudaStream_t st, long long* launches);
 
 }  // namespace lc
