@@ -109,7 +109,7 @@ __device__ void grid_from_reductions(const Params* P, Ctl* ctl) {
 
 // ---------------------------------------------------------------------------------------------------------
 // S0: demo::run (demo.cpp:665-702)
-__global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__ P, Buffers b) {
+__device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, const Buffers& b) {
     Ctl* ctl = b.ctl;
     __shared__ int2 s_ev[EV_SORT_CAP];
     __shared__ float s_ft[1024];
@@ -235,6 +235,8 @@ __global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__
     }
     if (tid < HULL_K) ctl->ext[tid] = 0ull;
 }
+
+__global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__ P, Buffers b) { frame_begin_body(P, b); }
 
 // ---------------------------------------------------------------------------------------------------------
 // Uniform grid, phase 1: cell id + arrival rank per agent; directional extremes for candidate pruning.
@@ -434,9 +436,9 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
 // tested against the polygon through THEIR HULL_K2 directional extremes.  Any convex polygon whose vertices are
 // agents lies inside the true hull, so the margin argument of stage 1 applies unchanged; only the
 // number of survivors depends on the polygon.  Typically leaves the hull vertices plus a few near-hull agents.
-__global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, Buffers b) {
+constexpr int REFINE_SMEM = 2048;  // candidates staged in shared memory (typical: a few hundred); beyond that they are read from global
+__device__ __forceinline__ void refine_body(const Params* __restrict__ P, const Buffers& b) {
     Ctl* ctl = b.ctl;
-    if (ctl->halt || (P->flags & 1u)) return;
     const int nc = ctl->n_cand;
     if (nc > REFINE_MAX || nc < 8) {  // degenerate outline (or tiny crowd): keep the stage-1 list
         if (threadIdx.x == 0) { ctl->cand_sel = 0; ctl->n_cand2 = nc; }
@@ -444,16 +446,22 @@ __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, B
     }
     __shared__ unsigned long long s_ext[HULL_K2];
     __shared__ float s_ex[HULL_K2], s_ey[HULL_K2], s_enx[HULL_K2], s_eny[HULL_K2];
+    __shared__ float2 s_cd[REFINE_SMEM];
     __shared__ int s_ne, s_out;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float cx = ctl->cx, cy = ctl->cy;
+    const bool staged = nc <= REFINE_SMEM;
     if (tid == 0) { s_ne = 0; s_out = 0; }
+    if (staged)
+        for (int c = tid; c < nc; c += blockDim.x) { const float4 cd = b.cand[c]; s_cd[c] = make_float2(cd.x, cd.y); }
+    __syncthreads();
     for (int k = wid; k < HULL_K2; k += 32) {
         const float dx = c_dir2x[k], dy = c_dir2y[k];
         unsigned long long key = 0ull;
         for (int c = lane; c < nc; c += 32) {
-            const float4 cd = b.cand[c];
-            const float v = (cd.x - cx) * dx + (cd.y - cy) * dy;
+            float2 q;
+            if (staged) q = s_cd[c]; else { const float4 cd = b.cand[c]; q = make_float2(cd.x, cd.y); }
+            const float v = (q.x - cx) * dx + (q.y - cy) * dy;
             const unsigned long long kk = ((unsigned long long)f2ord(v) << 32) | (uint32_t)c;
             key = kk > key ? kk : key;
         }
@@ -481,16 +489,30 @@ __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, B
     const int ne = s_ne;
     const float delta = ctl->delta;
     for (int c = tid; c < nc; c += blockDim.x) {
-        const float4 cd = b.cand[c];
+        float2 q;
+        if (staged) q = s_cd[c]; else { const float4 cd = b.cand[c]; q = make_float2(cd.x, cd.y); }
         bool inside = ne >= 3;
         for (int e = 0; e < ne && inside; ++e) {
-            const float d = (cd.x - s_ex[e]) * s_enx[e] + (cd.y - s_ey[e]) * s_eny[e];
+            const float d = (q.x - s_ex[e]) * s_enx[e] + (q.y - s_ey[e]) * s_eny[e];
             if (!(d >= delta)) inside = false;
         }
-        if (!inside) b.cand2[atomicAdd(&s_out, 1)] = cd;
+        if (!inside) b.cand2[atomicAdd(&s_out, 1)] = b.cand[c];
     }
     __syncthreads();
     if (tid == 0) { ctl->cand_sel = 1; ctl->n_cand2 = s_out; }
+}
+
+__device__ void dd_cand_body(const Params* __restrict__ P, const Buffers& b);
+
+// k_refine; in domain mode the same block then exchanges the survivors with the other ranks (domain.cuh)
+__global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, Buffers b) {
+    Ctl* ctl = b.ctl;
+    if (ctl->halt || (P->flags & 1u)) return;
+    refine_body(P, b);
+    if (b.dd) {
+        __syncthreads();
+        dd_cand_body(P, b);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1116,15 +1138,14 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     // ev (optional, FRAME_KERNELS + 1 events): per-kernel device timing for bench.py's roofline leg
     const bool dd = b.dd != nullptr;
     cudaMemsetAsync(b.cell_count, 0, sizeof(int) * CELL_ALLOC, st);
+    if (ev) cudaEventRecord(ev[0], st);
     if (dd) {  // boundary exchange over peer memory (domain.cuh); its time is attributed to k_frame_begin's slot in `ev`
-        if (ev) cudaEventRecord(ev[0], st);
         k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
-        k_dd_publish<<<1, 1024, 0, st>>>(dP, b);
-        k_dd_wait<<<1, 1024, 0, st>>>(dP, b);
-        k_dd_unpack<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+        k_dd_sync_begin<<<1, 1024, 0, st>>>(dP, b);   // publish + wait + merge + k_frame_begin's work
+        k_dd_unpack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    } else {
+        k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
     }
-    if (ev && !dd) cudaEventRecord(ev[0], st);
-    k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[1], st);
     k_bin<<<cdiv(n, 1024), 1024, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[2], st);
@@ -1132,14 +1153,13 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     if (ev) cudaEventRecord(ev[3], st);
     k_reorder<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[4], st);
-    k_refine<<<1, 1024, 0, st>>>(dP, b);
-    if (dd) k_dd_cand<<<1, 1024, 0, st>>>(dP, b);
+    k_refine<<<1, 1024, 0, st>>>(dP, b);            // + candidate all-gather in domain mode
     if (ev) cudaEventRecord(ev[5], st);
     k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[6], st);
     k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[7], st);
-    if (launches) *launches += FRAME_KERNELS + (dd ? DD_KERNELS : 0);
+    if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
 }
 
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {

@@ -127,6 +127,7 @@ constexpr int DD_PLANES = 5;
 struct DomainBlob {               // one per (sender, parity), written into EVERY peer's mailbox
     int n_sent[3];                // records the sender put into the regions of rank-1, itself, rank+1
     uint32_t vmax;                // max speed bits over the sender's agents (interaction cutoff must be global)
+    uint32_t bbox[4];             // order-encoded min x, min y, max x, max y of the sender's agents
     int nnd;                      // owned agents that are not done (demo.cpp:667-669)
     int nonfinite;
     unsigned long long lastvel;   // physics.cpp:72-76: ((id + 1) << 32) | speed bits of the highest-id owned not-done agent
@@ -135,6 +136,7 @@ struct DomainBlob {               // one per (sender, parity), written into EVER
     int error;
     int pad[2];
 };
+static_assert(sizeof(DomainBlob) % 8 == 0, "DomainBlob is copied word-wise");
 struct DomainLayout {             // byte offsets inside one rank's mailbox allocation; identical on every rank
     size_t blob[2], flag[2], cflag[2], ncand[2], region[2][3], events[2], cand[2], ev_by_id, total;
     int cap_self, cap_halo;
@@ -151,7 +153,7 @@ DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 
 void upload_dirs();
 constexpr int FRAME_KERNELS = 7;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, force, collide
-constexpr int DD_KERNELS = 5;     // domain mode adds: dd_pack, dd_publish, dd_wait, dd_unpack (before frame_begin), dd_cand (after refine)
+constexpr int DD_KERNELS = 2;     // domain mode: dd_pack, dd_sync_begin (replaces frame_begin), dd_unpack; the candidate exchange rides in k_refine
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
                   cudaEvent_t* ev = nullptr);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);

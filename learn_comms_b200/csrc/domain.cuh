@@ -147,10 +147,11 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
     }
 }
 
-__global__ void __launch_bounds__(1024) k_dd_publish(const Params* __restrict__ P, Buffers b) {
+// publish + wait + merge + S0 (k_frame_begin's work) in ONE single-block kernel: three launch gaps less per frame
+__global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
     Ctl* ctl = b.ctl;
     DomainDev* dd = b.dd;
-    if (!dd_active(P, ctl)) return;
+    if (!dd_active(P, ctl)) { frame_begin_body(P, b); return; }  // latches halt, like every later frame of a finished run
     const int me = P->dd_rank, w = P->dd_world, tid = threadIdx.x;
     const uint32_t frame = ctl->frame + 1u;
     const int par = frame & 1u;
@@ -161,6 +162,7 @@ __global__ void __launch_bounds__(1024) k_dd_publish(const Params* __restrict__ 
         if (ctl->ev_count > DD_EV_CAP && !ctl->error) ctl->error = -5;
         s_blob.n_sent[0] = dd->count[0]; s_blob.n_sent[1] = dd->count[1]; s_blob.n_sent[2] = dd->count[2];
         s_blob.vmax = ctl->vmax;
+        s_blob.bbox[0] = ctl->minx; s_blob.bbox[1] = ctl->miny; s_blob.bbox[2] = ctl->maxx; s_blob.bbox[3] = ctl->maxy;
         s_blob.nnd = ctl->nnd_acc;
         s_blob.nonfinite = ctl->nonfinite;
         s_blob.lastvel = ctl->lastvel;
@@ -181,15 +183,8 @@ __global__ void __launch_bounds__(1024) k_dd_publish(const Params* __restrict__ 
     __threadfence_system();
     __syncthreads();
     if (tid < w) dd_st_flag(reinterpret_cast<unsigned long long*>(dd->mbox[tid] + dd->lay.flag[par]) + me, (unsigned long long)frame);
-}
 
-__global__ void __launch_bounds__(1024) k_dd_wait(Params* P, Buffers b) {
-    Ctl* ctl = b.ctl;
-    DomainDev* dd = b.dd;
-    if (!dd_active(P, ctl)) return;
-    const int me = P->dd_rank, w = P->dd_world, tid = threadIdx.x;
-    const uint32_t frame = ctl->frame + 1u;
-    const int par = frame & 1u;
+    // ---- wait for every peer's blob of this frame and merge ----
     __shared__ int s_ok;
     __shared__ int s_evoff[DD_MAX_WORLD + 1];
     if (tid == 0) s_ok = 1;
@@ -204,7 +199,7 @@ __global__ void __launch_bounds__(1024) k_dd_wait(Params* P, Buffers b) {
     const DomainBlob* blobs = reinterpret_cast<const DomainBlob*>(dd->mbox[me] + dd->lay.blob[par]);
     if (tid == 0) {
         if (!s_ok && !ctl->error) ctl->error = -2;
-        uint32_t vmax = 0u;
+        uint32_t vmax = 0u, bb0 = 0xffffffffu, bb1 = 0xffffffffu, bb2 = 0u, bb3 = 0u;
         int nnd = 0, nonfinite = 0, err = ctl->error;
         unsigned long long lastvel = 0ull;
         int r1 = 0x7fffffff, r2 = 0x7fffffff;
@@ -212,6 +207,7 @@ __global__ void __launch_bounds__(1024) k_dd_wait(Params* P, Buffers b) {
         for (int q = 0; q < w; ++q) {
             const DomainBlob bl = blobs[q];
             vmax = max(vmax, bl.vmax);
+            bb0 = min(bb0, bl.bbox[0]); bb1 = min(bb1, bl.bbox[1]); bb2 = max(bb2, bl.bbox[2]); bb3 = max(bb3, bl.bbox[3]);
             nnd += bl.nnd;
             nonfinite += bl.nonfinite;
             lastvel = bl.lastvel > lastvel ? bl.lastvel : lastvel;
@@ -243,8 +239,16 @@ __global__ void __launch_bounds__(1024) k_dd_wait(Params* P, Buffers b) {
         ctl->replan1 = r1; ctl->replan2 = r2;
         ctl->ev_count = evoff;
         ctl->error = err;
-        ctl->minx = ctl->miny = 0xffffffffu;  // the bounding box of the new local set comes from k_dd_unpack
-        ctl->maxx = ctl->maxy = 0u;
+        // Grid extent of the new local set: every record routed here lies in the ghost-extended strip, and inside the
+        // crowd's global box in y.  (A box that is too small would still be correct — cell_of clamps, and clamping never
+        // increases a cell distance — a box that is too large only wastes cells.)
+        {
+            float gx0 = ord2f(bb0), gx1 = ord2f(bb2);
+            const float sx0 = P->dd_xb[me] - P->dd_halo - 0.25f, sx1 = P->dd_xb[me + 1] + P->dd_halo + 0.25f;
+            if (bb0 <= bb2) { gx0 = fmaxf(gx0, sx0); gx1 = fminf(gx1, sx1); if (!(gx1 >= gx0)) gx1 = gx0; }
+            ctl->minx = bb0 <= bb2 ? f2ord(gx0) : bb0; ctl->maxx = bb0 <= bb2 ? f2ord(gx1) : bb2;
+            ctl->miny = bb1; ctl->maxy = bb3;
+        }
         dd->replan[0] = dd->replan[1] = 0x7fffffff;
     }
     __syncthreads();
@@ -255,20 +259,21 @@ __global__ void __launch_bounds__(1024) k_dd_wait(Params* P, Buffers b) {
             for (int k = tid; k < cnt; k += blockDim.x) b.events[s_evoff[q] + k] = evsrc[(size_t)q * DD_EV_CAP + k];
         }
     }
+    __threadfence();
+    __syncthreads();
+    frame_begin_body(P, b);  // S0: scoring + latch + this frame's grid (demo.cpp:665-702), as on a single GPU
 }
 
-__global__ void __launch_bounds__(128) k_dd_unpack(const Params* __restrict__ P, Buffers b) {
+__global__ void __launch_bounds__(256) k_dd_unpack(const Params* __restrict__ P, Buffers b) {
     Ctl* ctl = b.ctl;
     DomainDev* dd = b.dd;
-    if (!dd_active(P, ctl)) return;
+    if (ctl->halt) return;
     const int n = P->n;
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t frame = ctl->frame + 1u;
+    const uint32_t frame = ctl->frame;  // k_dd_sync_begin already advanced it
     const int par = frame & 1u;
     const int n_l = dd->recv[2], n_self = dd->recv[1];
-    bool valid = k < n;
-    float x = 0.f, y = 0.f;
-    if (valid) {
+    if (k < n) {
         int reg, idx;
         if (k < n_self) { reg = 1; idx = k; }
         else if (k < n_self + n_l) { reg = 2; idx = k - n_self; }   // from the left neighbour
@@ -285,18 +290,15 @@ __global__ void __launch_bounds__(128) k_dd_unpack(const Params* __restrict__ P,
         b.cur.facing[k] = make_float2(r2.z, r2.w);
         b.cur.c4[k] = r3;
         b.cur.meta[k] = make_int4(__float_as_int(r4.x), __float_as_int(r4.y), __float_as_int(r4.z), __float_as_int(r4.w));
-        x = r0.x; y = r0.y;
     }
-    block_reduce_store(b, valid && x == x && y == y, x, y, 0.f, 0u);
 }
 
 // Comm-partner candidates are a global matter (comm.cpp:201-220 scans ALL agents).  Each rank's list after k_refine
 // holds the hull survivors of its own agents; publish them with the payload comm::x reads from the partner and
 // append everybody else's behind the local arrays ("annex" slots >= cap of srt.pv / srt.c4).
-__global__ void __launch_bounds__(1024) k_dd_cand(const Params* __restrict__ P, Buffers b) {
+__device__ void dd_cand_body(const Params* __restrict__ P, const Buffers& b) {
     Ctl* ctl = b.ctl;
     DomainDev* dd = b.dd;
-    if (ctl->halt || (P->flags & 1u)) return;
     const int me = P->dd_rank, w = P->dd_world, tid = threadIdx.x;
     const uint32_t frame = ctl->frame;  // k_frame_begin already advanced it
     const int par = frame & 1u;

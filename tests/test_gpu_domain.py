@@ -98,7 +98,9 @@ def test_domain_full_rollout_scores():
 
 def test_domain_nocomm_and_dense():
     """Packed crowd (collision pass across the strip boundary) without the comm system."""
-    pos, goal = _crowd(3000, 40.0, 14.0, seed=4, goal_range=30.0)
+    rs = np.random.RandomState(4)   # 0.25 m mean spacing < 2 r: hundreds of initial overlaps on both sides of the cut
+    pos = rs.uniform([-12, -4], [12, 4], (3000, 2)).astype(np.float32)
+    goal = (pos + rs.uniform(-30, 30, (3000, 2))).astype(np.float32)
     sims = _make(pos, goal, 100.0, 5, None, None, 2, comm=False)
     ref = lcb.Sim(pos, goal, None, None, max_duration=100.0, rng_state=5, comm=False)
     hits = 0
