@@ -398,12 +398,12 @@ int32_t lc_step(lc_sim* s, int32_t nframes) {
     while (left >= GRAPH_BATCH) {
         CK(cudaGraphLaunch(s->gexec[1], s->st));
         left -= GRAPH_BATCH;
-        s->launches += lc::FRAME_KERNELS * GRAPH_BATCH;
+        s->launches += (lc::FRAME_KERNELS + (s->ddev ? lc::DD_KERNELS : 0)) * GRAPH_BATCH;
     }
     while (left > 0) {
         CK(cudaGraphLaunch(s->gexec[0], s->st));
         --left;
-        s->launches += lc::FRAME_KERNELS;
+        s->launches += lc::FRAME_KERNELS + (s->ddev ? lc::DD_KERNELS : 0);
     }
     return LC_OK;
 }

@@ -17,6 +17,31 @@
 namespace lc {
 using namespace lcm;
 
+// Domain mode: the input of a frame is the set of records the ranks' k_dd_pack stored in this rank's mailbox (own
+// stayers, then what the left / right neighbour sent).  k_bin / k_scan_hull / k_reorder read them in place — no unpack copy.
+struct DDRec {
+    const float4* base;  // plane 0 of the region; plane p is at base + p * cap
+    int cap, idx;
+    __device__ __forceinline__ float4 plane(int p) const { return base[(size_t)p * cap + idx]; }
+};
+__device__ __forceinline__ DDRec dd_locate(const Params* P, const Buffers& b, int i) {
+    const DomainDev* dd = b.dd;
+    const int par = b.ctl->frame & 1u;  // k_dd_sync_begin already advanced the frame counter
+    const int n_self = dd->recv[1], n_l = dd->recv[2];
+    int reg;
+    DDRec r;
+    if (i < n_self) { reg = 1; r.idx = i; }
+    else if (i < n_self + n_l) { reg = 2; r.idx = i - n_self; }   // from the left neighbour
+    else { reg = 0; r.idx = i - n_self - n_l; }                    // from the right neighbour
+    r.cap = reg == 1 ? dd->lay.cap_self : dd->lay.cap_halo;
+    r.base = reinterpret_cast<const float4*>(dd->mbox[P->dd_rank] + dd->lay.region[par][reg]);
+    return r;
+}
+__device__ __forceinline__ float2 input_pos(const Params* P, const Buffers& b, int i) {
+    if (b.dd) { const float4 r0 = dd_locate(P, b, i).plane(0); return make_float2(r0.x, r0.y); }
+    return b.posf[i];
+}
+
 __constant__ float c_dirx[HULL_K];
 __constant__ float c_diry[HULL_K];
 __constant__ float c_dir2x[HULL_K2];
@@ -102,6 +127,7 @@ __device__ void grid_from_reductions(const Params* P, Ctl* ctl) {
         h *= 2.f;
     }
     ctl->x0 = minx; ctl->y0 = miny; ctl->h = h; ctl->nx = nx; ctl->ny = ny; ctl->ncells = nx * ny;
+    ctl->cutoff = cutoff;
     ctl->stencil = (int)ceilf(cutoff / h);
     ctl->cx = 0.5f * (minx + maxx); ctl->cy = 0.5f * (miny + maxy);
     ctl->delta = 1e-5f * ext + 1e-4f;
@@ -256,7 +282,7 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
     float2 p = make_float2(0.f, 0.f);
     int cell = -1;
     if (i < n) {
-        p = b.posf[i];
+        p = input_pos(P, b, i);
         cell = cell_of(ctl, p.x, p.y);
     }
     {   // Counting sort, phase 1.  The agents arrive in last frame's cell order, so equal cells form runs of
@@ -326,7 +352,7 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
                 if (ka == 0ull || kb == 0ull) continue;
                 int a = (int)(ka & 0xffffffffull), c = (int)(kb & 0xffffffffull);
                 if (a == c) continue;
-                float2 pa = b.posf[a], pc = b.posf[c];
+                float2 pa = input_pos(P, b, a), pc = input_pos(P, b, c);
                 double ux = (double)pc.x - pa.x, uy = (double)pc.y - pa.y, l = sqrt(ux * ux + uy * uy);
                 if (!(l > 0.0)) continue;
                 ctl->ex[ne] = pa.x; ctl->ey[ne] = pa.y;
@@ -390,20 +416,31 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     if (i >= n) return;
     const int2 cr = b.cellrank[i];
     const int s = b.cell_start[cr.x] + cr.y;
-    const float2 p = b.posf[i];
-    const float4 pv = b.cur.pv[i];
-    const int4 mt = b.cur.meta[i];
-    const float2 g = b.cur.goal[i];
+    float2 p, g;
+    float4 pv;
+    int4 mt;
+    if (b.dd) {  // records of k_dd_pack: (posf.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
+        const DDRec r = dd_locate(P, b, i);
+        const float4 r0 = r.plane(0), r1 = r.plane(1), r2 = r.plane(2), r4 = r.plane(4);
+        p = make_float2(r0.x, r0.y); pv = r0; g = make_float2(r1.z, r1.w);
+        mt = make_int4(__float_as_int(r4.x), __float_as_int(r4.y), __float_as_int(r4.z), __float_as_int(r4.w));
+        b.srt.vfh[s] = make_float2(r1.x, r1.y);
+        b.srt.lgoal[s] = make_float2(r2.x, r2.y);
+        b.srt.facing[s] = make_float2(r2.z, r2.w);
+        b.srt.c4[s] = r.plane(3);
+    } else {
+        p = b.posf[i]; pv = b.cur.pv[i]; mt = b.cur.meta[i]; g = b.cur.goal[i];
+        b.srt.vfh[s] = b.cur.vfh[i];
+        b.srt.lgoal[s] = b.cur.lgoal[i];
+        b.srt.facing[s] = b.cur.facing[i];
+        b.srt.c4[s] = b.cur.c4[i];
+    }
     b.srt.pv[s] = make_float4(p.x, p.y, pv.z, pv.w);
     {   // pair-interleaved copy for the packed pair loop: slots (2k, 2k+1) -> (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
         float* q = reinterpret_cast<float*>(b.srt_pq + 2 * (s >> 1)) + (s & 1);
         q[0] = p.x; q[2] = p.y; q[4] = pv.z; q[6] = pv.w;
     }
-    b.srt.vfh[s] = b.cur.vfh[i];
     b.srt.goal[s] = g;
-    b.srt.lgoal[s] = b.cur.lgoal[i];
-    b.srt.facing[s] = b.cur.facing[i];
-    b.srt.c4[s] = b.cur.c4[i];
     b.srt.meta[s] = mt;
     b.slot_of_id[mt.x] = s;
     // ai.cpp:154,161-163: need_replan = done && goal_dist > 1 (wall-free: the lost_frames clause cannot fire)
@@ -520,24 +557,29 @@ __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, B
 
 // Visit every interacting neighbour {j : ttc_ij <= 5} of agent s in the (2*stencil+1)^2 cell block.  Cells of one
 // grid row are contiguous in the sorted arrays, so each row of the block is ONE contiguous slot range.
+// `lst` (shared memory, [LIST_CAP][blockDim.x], or nullptr): survivors of the packed filter are only RECORDED while the
+// cell block is scanned and evaluated afterwards, all lanes of a warp working on their k-th survivor at the same time.
+// Evaluating them on the spot (sqrt, divisions, the f64 magnitude) ran at 13 of 32 lanes active and made up 39 % of the
+// kernel's instructions (profiles/prof_force_r1f_raw.csv).
 template <bool FIRST, class F>
 __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx,
-                                                float vy, float RR, float near_c, int& n_near, int& n_overlap, F&& f) {
+                                                float vy, float RR, float near_c, int& n_near, int& n_overlap, int* lst,
+                                                F&& f) {
     const int st = ctl->stencil, nx = ctl->nx, ny = ctl->ny;
     int ix = (int)floorf((px - ctl->x0) / ctl->h), iy = (int)floorf((py - ctl->y0) / ctl->h);
     ix = min(max(ix, 0), nx - 1);
     iy = min(max(iy, 0), ny - 1);
-    const int x_lo = max(ix - st, 0), x_hi = min(ix + st, nx - 1);
+    // Disc-shaped stencil: a row of cells whose nearest edge is gap_y away can only hold interaction partners within
+    // sqrt(cutoff^2 - gap_y^2) in x.  Inflated by 1e-3 so that float rounding here can never exclude a cell that cell_of
+    // (the same monotonic expression, applied to a position inside the disc) put an agent into.
+    const float cut = ctl->cutoff * 1.001f + 1e-3f, cut2 = cut * cut;
     const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
     const float2 RR2 = make_float2(RR, RR);
     const float4* __restrict__ pq = b.srt_pq;
     // One candidate of a pair beyond the fast reject: LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame
     // (same operations as lc_math.cuh ttc_pair), the near list of the collision pass, and the force on a hit.
-    auto slow = [&](int j, float bq, float c, float a, float disc, bool far) {
-        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
-        const bool near = FIRST && c < near_c;
-        if (miss && !near) return;
-        if (j == s) return;  // the self pair (m = dv = 0) always reaches this point
+    int nlst = 0;
+    auto evaluate = [&](int j, float bq, float c, float a, float disc, bool miss, bool near) {
         if (near) {
             if (n_near < MAX_NEAR) b.near_idx[(size_t)s * MAX_NEAR + n_near] = j;
             ++n_near;
@@ -553,6 +595,23 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
         f(j, fx, fy);
     };
+    // survivor j of the filter, recomputed from scratch (scalar operations == the packed lanes, bit for bit)
+    auto revisit = [&](int j) {
+        const float4 q = __ldg(&b.srt.pv[j]);
+        const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
+        const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
+        const float a = dot2(dvx, dvy, dvx, dvy);
+        const float disc = __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c));
+        evaluate(j, bq, c, a, disc, (c > 0.f && bq > 0.f) || disc < 0.f, FIRST && c < near_c);
+    };
+    auto slow = [&](int j, float bq, float c, float a, float disc, bool far) {
+        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
+        const bool near = FIRST && c < near_c;
+        if (miss && !near) return;
+        if (j == s) return;  // the self pair (m = dv = 0) always reaches this point
+        if (lst && nlst < LIST_CAP) { lst[nlst * blockDim.x + threadIdx.x] = j; ++nlst; return; }
+        evaluate(j, bq, c, a, disc, miss, near);
+    };
     // scalar version for the odd slot at either end of a row range
     auto single = [&](int j) {
         const float4 q = __ldg(&b.srt.pv[j]);
@@ -563,6 +622,13 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         slow(j, bq, c, a, __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c)), false);
     };
     for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
+        const float ylo = ctl->y0 + (float)yy * ctl->h;
+        const float gap = yy == iy ? 0.f : (yy > iy ? ylo - py : py - (ylo + ctl->h));
+        const float rem = cut2 - (gap > 0.f ? gap * gap : 0.f);
+        if (!(rem > 0.f)) continue;
+        const float reach = sqrtf(rem);
+        const int x_lo = min(max((int)floorf((px - reach - ctl->x0) / ctl->h), max(ix - st, 0)), ix);
+        const int x_hi = max(min((int)floorf((px + reach - ctl->x0) / ctl->h), min(ix + st, nx - 1)), ix);
         int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
         if (j0 >= j1) continue;
         if (j0 & 1) single(j0++);
@@ -600,6 +666,7 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
             if (!skip1) slow(j + 1, bq.y, c.y, a.y, disc.y, far1);
         }
     }
+    for (int k = 0; k < nlst; ++k) revisit(lst[k * blockDim.x + threadIdx.x]);
 }
 
 __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P, Buffers b) {
@@ -614,6 +681,7 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
     // in B only if max_{q in B} |q - k|^2 is not below L = max_k' min_{q in B} |q - k'|^2 (1e-4 relative slack >> the
     // float rounding of length2).  Survivors are staged in shared memory; typically a handful remain.
     __shared__ float4 s_cand[CAND_SMEM];
+    __shared__ int s_list[LIST_CAP * 128];
     __shared__ uint32_t s_bb[5];
     __shared__ int s_nc;
     const float4* __restrict__ cand = nullptr;
@@ -667,7 +735,7 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
         int hid[MAX_HITS];
         float hfx[MAX_HITS], hfy[MAX_HITS];
         int cnt = 0, n_near = 0, n_overlap = 0;
-        scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap,
+        scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, s_list,
                               [&](int j, float fx, float fy) {
                                   if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
                                   ++cnt;
@@ -693,7 +761,7 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
             for (int k = 0; k < cnt; ++k) {
                 int bid = 0x7fffffff;
                 float bfx = 0.f, bfy = 0.f;
-                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1,
+                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1, nullptr,
                                        [&](int j, float fx, float fy) {
                                            int v = __ldg(&b.srt.meta[j].x);
                                            if (v > last && v < bid) { bid = v; bfx = fx; bfy = fy; }
@@ -1142,7 +1210,6 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     if (dd) {  // boundary exchange over peer memory (domain.cuh); its time is attributed to k_frame_begin's slot in `ev`
         k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
         k_dd_sync_begin<<<1, 1024, 0, st>>>(dP, b);   // publish + wait + merge + k_frame_begin's work
-        k_dd_unpack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
     } else {
         k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
     }

@@ -6,9 +6,10 @@
 namespace lc {
 
 constexpr int HULL_K = 16;        // directional extremes used to prune comm-partner candidates (stage 1, all agents)
-constexpr int HULL_K2 = 256;      // stage 2, over the stage-1 survivors only
+constexpr int HULL_K2 = 64;       // stage 2, over the stage-1 survivors only (one block does it: 256 directions cost 20 us)
 constexpr int CAND_SMEM = 128;     // per-block candidate list of k_force (stage 3); falls back to the global list beyond
 constexpr int REFINE_MAX = 1 << 16; // stage 2 is skipped when stage 1 leaves more than this many candidates
+constexpr int LIST_CAP = 24;      // per-thread list (shared memory) of pair-filter survivors that k_force evaluates after the scan
 constexpr int MAX_HITS = 48;      // per-thread buffer of interacting neighbours (sorted by id before summation)
 constexpr int MAX_NEAR = 8;       // per-agent list of neighbours close enough to collide this frame
 constexpr int CELL_CAP = 1 << 18; // max grid cells (cell side grows beyond the cutoff if exceeded)
@@ -48,7 +49,7 @@ struct Ctl {
     int halt;       // frames after the all_done frame are no-ops
     int error;      // lc_status of the first device-side error
     // uniform grid of the current frame
-    float x0, y0, h;
+    float x0, y0, h, cutoff;
     int nx, ny, ncells, stencil;
     // comm-partner candidate pruning
     float cx, cy, delta;
@@ -153,7 +154,7 @@ DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 
 void upload_dirs();
 constexpr int FRAME_KERNELS = 7;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, force, collide
-constexpr int DD_KERNELS = 2;     // domain mode: dd_pack, dd_sync_begin (replaces frame_begin), dd_unpack; the candidate exchange rides in k_refine
+constexpr int DD_KERNELS = 1;     // domain mode: dd_pack + dd_sync_begin (replaces frame_begin); the candidate exchange rides in k_refine
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
                   cudaEvent_t* ev = nullptr);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);

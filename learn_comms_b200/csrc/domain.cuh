@@ -12,8 +12,9 @@
 //                 releases flag[rank] = f with a system-scope fence
 //   k_dd_wait     spins until every peer's flag reads f, merges the blobs into Ctl (GLOBAL max speed, not-done count,
 //                 replan gate, events on rank 0) and sets Params::n to the number of local records
-//   k_dd_unpack   records -> SoA arrays (owners and ghosts mixed; meta bit2 tells them apart), bounding box of the new local set
-//   k_frame_begin .. k_refine as for a single-GPU crowd (ghosts are binned and sorted like everybody else)
+//                 (k_dd_publish / k_dd_wait / k_frame_begin are ONE single-block kernel, k_dd_sync_begin)
+//   k_bin, k_scan_hull, k_reorder read the records in place (owners and ghosts mixed; meta bit2 tells them apart) and sort
+//                 them into cell order like a single-GPU crowd; there is no unpack copy
 //   k_dd_cand     publishes this rank's surviving comm-partner candidates (with the partner payload x() needs:
 //                 pos, vel.x, c) to every peer, waits for theirs and appends them (comm.cpp:201-220 is a GLOBAL arg-max)
 //   k_force, k_collide: ghosts are advanced too — the collision pass needs their integrated positions — but never
@@ -80,9 +81,10 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
     const int me = P->dd_rank;
     const uint32_t frame = ctl->frame + 1u;
     const int par = frame & 1u;
-    __shared__ int s_cnt[3], s_base[3];
-    if (threadIdx.x < 3) s_cnt[threadIdx.x] = 0;
-    __syncthreads();
+    // Slot allocation keeps the agents' order (ballot prefix inside the warp, warp totals, one global atomicAdd per block
+    // and destination): the records stay in last frame's cell order, which k_bin's run-aggregated counting relies on.
+    __shared__ int s_wcnt[3][8], s_base[3];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int role[3] = {0, 0, 0}, rank_in_blk[3] = {0, 0, 0};
     int4 mt = make_int4(0, 0, 0, 0);
     float2 p = make_float2(0.f, 0.f), g = make_float2(0.f, 0.f);
@@ -94,14 +96,23 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
             p = b.posf[i];
             g = b.cur.goal[i];
             dd_route(P, p.x, role);
-#pragma unroll
-            for (int k = 0; k < 3; ++k)
-                if (role[k]) rank_in_blk[k] = atomicAdd(&s_cnt[k], 1);
         }
     }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const unsigned m = __ballot_sync(0xffffffffu, role[k] != 0);
+        rank_in_blk[k] = __popc(m & ((1u << lane) - 1u));
+        if (lane == 0) s_wcnt[k][wid] = __popc(m);
+    }
     __syncthreads();
-    if (threadIdx.x < 3 && s_cnt[threadIdx.x]) s_base[threadIdx.x] = atomicAdd(&dd->count[threadIdx.x], s_cnt[threadIdx.x]);
+    if (threadIdx.x < 3) {
+        int tot = 0;
+        for (int w = 0; w < 8; ++w) { const int c = s_wcnt[threadIdx.x][w]; s_wcnt[threadIdx.x][w] = tot; tot += c; }
+        s_base[threadIdx.x] = tot ? atomicAdd(&dd->count[threadIdx.x], tot) : 0;
+    }
     __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 3; ++k) rank_in_blk[k] += s_wcnt[k][wid];
     if (!owned) return;
     const float4 pv = b.cur.pv[i];
     const float2 vfh = b.cur.vfh[i], lg = b.cur.lgoal[i], fc = b.cur.facing[i];
@@ -262,35 +273,6 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
     __threadfence();
     __syncthreads();
     frame_begin_body(P, b);  // S0: scoring + latch + this frame's grid (demo.cpp:665-702), as on a single GPU
-}
-
-__global__ void __launch_bounds__(256) k_dd_unpack(const Params* __restrict__ P, Buffers b) {
-    Ctl* ctl = b.ctl;
-    DomainDev* dd = b.dd;
-    if (ctl->halt) return;
-    const int n = P->n;
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t frame = ctl->frame;  // k_dd_sync_begin already advanced it
-    const int par = frame & 1u;
-    const int n_l = dd->recv[2], n_self = dd->recv[1];
-    if (k < n) {
-        int reg, idx;
-        if (k < n_self) { reg = 1; idx = k; }
-        else if (k < n_self + n_l) { reg = 2; idx = k - n_self; }   // from the left neighbour
-        else { reg = 0; idx = k - n_self - n_l; }                    // from the right neighbour
-        const int cap = reg == 1 ? dd->lay.cap_self : dd->lay.cap_halo;
-        const float4* src = reinterpret_cast<const float4*>(dd->mbox[P->dd_rank] + dd->lay.region[par][reg]);
-        const float4 r0 = src[idx], r1 = src[(size_t)cap + idx], r2 = src[(size_t)2 * cap + idx], r3 = src[(size_t)3 * cap + idx],
-                     r4 = src[(size_t)4 * cap + idx];
-        b.cur.pv[k] = r0;
-        b.posf[k] = make_float2(r0.x, r0.y);
-        b.cur.vfh[k] = make_float2(r1.x, r1.y);
-        b.cur.goal[k] = make_float2(r1.z, r1.w);
-        b.cur.lgoal[k] = make_float2(r2.x, r2.y);
-        b.cur.facing[k] = make_float2(r2.z, r2.w);
-        b.cur.c4[k] = r3;
-        b.cur.meta[k] = make_int4(__float_as_int(r4.x), __float_as_int(r4.y), __float_as_int(r4.z), __float_as_int(r4.w));
-    }
 }
 
 // Comm-partner candidates are a global matter (comm.cpp:201-220 scans ALL agents).  Each rank's list after k_refine

@@ -82,3 +82,21 @@ def test_score_gather_world2_gloo(n_items):
         assert out["group_time"] == (idx * 3 + 1).astype(np.float32).tolist()
         assert out["n_done"] == (idx % 64).tolist() and out["frames"] == (idx + 600).tolist()
         assert dtypes["n_done"] == "int32" and dtypes["avg_velocity"] == "float32"
+
+
+def test_domain_score_merge_is_pure_host_logic():
+    """physics.cpp:72-76 across ranks: the whole crowd's avg_velocity is the speed of the highest-id not-done agent over
+    all ranks (lastvel key = ((id + 1) << 32) | speed bits); non-finite speeds elsewhere poison it (NaN * 0)."""
+    import learn_comms_b200 as lcb
+    bits = lambda f: int(np.array([f], np.float32).view(np.uint32)[0])
+    r0 = dict(avg_velocity=0.25, group_time=3.0, run_avg=1.0, run_std=0.5, n_done=7)
+    key = lambda i, sp: ((i + 1) << 32) | bits(sp)
+    # nobody left that is not done: the previous frame's value stands
+    assert lcb.DomainSim.merge_scores(r0, [(0, 0, 0.25), (0, 0, 0.25)])["avg_velocity"] == 0.25
+    # highest id wins, whichever rank holds it
+    out = lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 0, 0.25), (key(99, 0.75), 0, 0.25), (key(50, 0.1), 0, 0.25)])
+    assert out["avg_velocity"] == 0.75 and out["group_time"] == 3.0 and out["n_done"] == 7
+    # a non-finite speed that is not the last one poisons the chain; the last one being infinite is kept as is
+    assert np.isnan(lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 1, 0.25), (key(99, 0.75), 0, 0.25)])["avg_velocity"])
+    assert np.isinf(lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 0, 0.25), (key(99, np.inf), 1, 0.25)])["avg_velocity"])
+    assert np.isnan(lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 0, np.nan), (key(99, 0.75), 0, np.nan)])["avg_velocity"])
