@@ -148,3 +148,30 @@ def test_batch_error_paths():
     with pytest.raises(lcb.LcError) as e:
         b.run(1)
     assert e.value.code == -3
+
+
+def test_batch_full_size_properties():
+    """BASELINE.json configs[2] at full size (4 096 scenarios x 64 agents): properties that need no oracle run —
+    determinism, invariance under sharding (what the multi-GPU path relies on), every scenario finishes within the
+    reference's 45 s limit (+1 frame), finite scores, and a 32-scenario sample against the oracle."""
+    pos, goal, m_cv, m_f, md, rng = wl.pso_batch(4096, 64, seed=3)
+    full = lcb.Batch(pos, goal, m_cv, m_f, md, rng)
+    a = full.run()
+    assert full.n_finished == 4096
+    full.reset()
+    b = full.run()
+    for k in a:
+        assert _eq(a[k], b[k]), f"not deterministic: {k}"
+    lo = lcb.Batch(pos[:1500], goal[:1500], m_cv[:1500], m_f[:1500], md[:1500], rng[:1500]).run()
+    hi = lcb.Batch(pos[1500:], goal[1500:], m_cv[1500:], m_f[1500:], md[1500:], rng[1500:]).run()
+    for k in a:
+        assert _eq(a[k], np.concatenate([lo[k], hi[k]])), f"sharding changes {k}"
+    assert a["frames"].max() <= 2701 and a["frames"].min() > 60
+    assert np.isfinite(a["group_time"]).all() and (a["n_done"] >= 64).all()
+    idx = np.arange(0, 4096, 128)
+    for s in idx:
+        o = _oracle.CanonSim(pos[s], goal[s], m_cv[s], m_f[s], max_duration=float(md[s]), rng_state=int(rng[s]))
+        o.step(10 ** 6)
+        sc = o.scores()
+        assert a["frames"][s] == o.frame and _score_eq(a["group_time"][s], np.float32(sc["group_time"])) \
+            and _score_eq(a["avg_velocity"][s], np.float32(sc["avg_velocity"])), s
