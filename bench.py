@@ -24,9 +24,11 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly ONE JSON line: NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) would land there too
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"
+# stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its "NCCL version ..." banner on fd 1),
+# so fd 1 is pointed at stderr for the whole run and the result line goes to a private duplicate of the real stdout.
+sys.stdout.flush()
+RESULT_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
 
 ALG_BYTES_PER_AGENT_STEP = 112  # 60 B compulsory read + 52 B compulsory write of live agent state
 WORKLOADS = {
@@ -34,6 +36,9 @@ WORKLOADS = {
     "plaza1m": dict(kind="plaza", n=1_000_000, side=2000.0, seed=5, wscale=0.1,
                     desc="open plaza 2000x2000 m, 1,000,000 agents (0.25/m^2), random goals, seed 5",
                     sample=dict(n=62_500, side=500.0)),
+    "plaza125k": dict(kind="plaza", n=125_000, side=707.1, seed=5, wscale=0.1,
+                      desc="1/8 of the plaza at the same density (development: the per-GPU load of the 8-GPU decomposition)",
+                      sample=dict(n=62_500, side=500.0)),
     "corridor100k": dict(kind="corridor", cols=500, rows=100, seed=4, wscale=0.1,
                          desc="bidirectional corridor, 2 x (500x100) lattice blocks = 100,000 agents, seed 4",
                          sample=dict(cols=125, rows=100)),
@@ -171,7 +176,7 @@ def run_reference(args):
             "config": {"workload": name, "desc": WORKLOADS[name]["desc"], "agents": n, "frames_per_step": 1},
             "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": "port", "sample": sample_text(name)},
             "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
 
 
 def pso_cpu_rate(n_scenarios, n_agents, seed, stride):
@@ -212,7 +217,7 @@ def run_batch_reference(args):
             "scenario_evals_per_sec": tot_evals / tot_dt,
             "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
 
 
 def run_batch(args):
@@ -313,7 +318,7 @@ def run_batch(args):
                            "parallelism": f"{world} GPU(s), contiguous scenario blocks, score gather only",
                            "l2": "no HBM working set: state is staged once into shared memory; nothing to flush"},
                 "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=RESULT_OUT, flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -407,28 +412,30 @@ def main():
     if not args.no_e2e and domain:
         # decomposed crowd: the state never leaves the GPUs between frames; the host-facing step is one frame plus the
         # D2H read of the tables a host engine consumes every frame (pos, vel of the rank's own agents)
-        keys = ("pos", "vel")
-        out = sim.state(keys=keys)
-        pinned = {k: torch.from_numpy(out[k]).pin_memory() for k in keys}
+        cap = sim.counts()[1]
+        pinned = dict(ids=torch.zeros(cap, dtype=torch.int32).pin_memory(), pos=torch.zeros((cap, 2)).pin_memory(),
+                      vel=torch.zeros((cap, 2)).pin_memory())
         views = {k: v.numpy() for k, v in pinned.items()}
-        d2h = sum(v.nbytes for v in views.values())
         Ke = max(3, min(K, 50))
         for _ in range(3):
             sim.step(1, sync=False)
-            sim.state(keys=keys, out=views)
+            _, k_own = sim.shard(out=views)
         barrier()
         t0 = time.perf_counter()
         for _ in range(Ke):
             sim.step(1, sync=False)
-            sim.state(keys=keys, out=views)
+            _, k_own = sim.shard(out=views)
         barrier()
         dt = time.perf_counter() - t0
+        d2h = torch.tensor([float(k_own * 20 + 4)], device="cuda")
+        dist.all_reduce(d2h)
         t = torch.tensor([dt], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
+        d2h = int(d2h.item()) // world
         e2e = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h * world,
                "steps": Ke, "ms_per_step": 1e3 * dt / Ke,
-               "api": "lc_step(1) + lc_get_state(pos, vel) per rank, pinned host tables; no per-frame H2D: the decomposed state is device-resident"}
+               "api": "lc_step(1) + lc_dd_get_shard (ids, pos, vel of the rank's own agents) per rank, pinned host tables; no per-frame H2D: the decomposed state is device-resident"}
     elif not args.no_e2e:
         st = sim.state()
         pinned = {}
@@ -474,7 +481,7 @@ def main():
                             else f"{world} independent crowds, one per GPU, no exchange"),
                            "l2": "per-frame working set (2 x 88 B x agents + grid) exceeds the 126 MB L2 at 1M agents; no flush"},
                 "counters": sim.counters(), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=RESULT_OUT, flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -116,6 +116,9 @@ int32_t lc_dd_ipc_handle(lc_sim* sim, void* handle64);
 int32_t lc_dd_connect_ipc(lc_sim* sim, int32_t peer_rank, const void* handle64);
 /* lc_get_state on a rank returns global-size arrays with zeros for agents it does not own; owned[id] = 1 marks its own */
 int32_t lc_dd_get_owned(lc_sim* sim, int32_t* owned /*[n]*/);
+/* the rank's own shard, compact: ids[k], pos[k][2], vel[k][2] for the *count agents it owns this frame (order arbitrary).
+ * What a host engine that consumes the tables every frame reads instead of the global-size lc_get_state arrays. */
+int32_t lc_dd_get_shard(lc_sim* sim, int32_t* ids, float* pos, float* vel, int32_t cap, int32_t* count);
 /* lc_get_scores on a rank: Welford statistics are complete on rank 0 (the scoring rank); avg_velocity is the value
  * after the previous frame.  The last frame's physics.cpp:72-76 inputs are per-rank partials: the speed of the
  * highest-id not-done agent is ((lastvel >> 32) - 1 = id, low 32 bits = speed) of the rank with the largest lastvel. */

@@ -40,7 +40,7 @@ EXPORTS = [
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
-    "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials",
+    "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
     "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
 ]
 
@@ -81,6 +81,7 @@ def lib():
         L.lc_dd_connect_ipc.argtypes = [vp, i32, vp]
         L.lc_dd_get_owned.argtypes = [vp, vp]
         L.lc_dd_counts.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
+        L.lc_dd_get_shard.argtypes = [vp, vp, vp, vp, i32, C.POINTER(i32)]
         L.lc_dd_get_partials.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(i32), f32p]
         L.lc_batch_create.argtypes = [C.POINTER(_BatchDesc), C.POINTER(vp)]
         L.lc_batch_destroy.argtypes = [vp]
@@ -321,6 +322,15 @@ class DomainSim(Sim):
 
     def set_state(self, **kw):
         raise LcError(-1, "set_state is not available for a domain-decomposed crowd")
+
+    def shard(self, out=None):
+        """(ids, pos, vel) of the agents this rank owns right now, compact; `out` = preallocated (pinned) arrays."""
+        cap = self.counts()[1] if out is None else out["ids"].shape[0]
+        if out is None:
+            out = dict(ids=np.zeros(cap, np.int32), pos=np.zeros((cap, 2), np.float32), vel=np.zeros((cap, 2), np.float32))
+        k = C.c_int32(0)
+        _ck(lib().lc_dd_get_shard(self.h, _p(out["ids"]), _p(out["pos"]), _p(out["vel"]), cap, C.byref(k)))
+        return out, int(k.value)
 
     def partials(self):
         lv, nf, av = C.c_uint64(), C.c_int32(), C.c_float()

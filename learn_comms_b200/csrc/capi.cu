@@ -257,7 +257,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(cudaMemset(b.near_cnt, 0, sizeof(int) * n));
     CKC(cudaMalloc((void**)&s->dP, sizeof(lc::Params)));
     CKC(cudaMallocHost((void**)&s->hctl, sizeof(lc::Ctl)));
-    s->stage_floats = (size_t)n_ids * 16;
+    s->stage_floats = std::max((size_t)n_ids * 16, (size_t)8 + 5 * (size_t)n);  // lc_get_state tables / lc_dd_get_shard
     CKC(cudaMalloc((void**)&s->stage, sizeof(float) * s->stage_floats));
     b.dd = nullptr;
     if (dom) {
@@ -659,6 +659,29 @@ int32_t lc_dd_get_owned(lc_sim* s, int32_t* owned) {
     lc::launch_get_state(s->dP, s->n, s->b, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s->st,
                          &s->launches, s->owned_dev);
     CK(cudaMemcpyAsync(owned, s->owned_dev, sizeof(int) * n, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    return LC_OK;
+}
+
+int32_t lc_dd_get_shard(lc_sim* s, int32_t* ids, float* pos, float* vel, int32_t cap, int32_t* count) {
+    SIM_ENTER(s);
+    if (s->dd_world <= 1 || !ids || !count) return fail(LC_ERR_ARG, "lc_dd_get_shard: bad argument");
+    // staging: [count | ids (cap) | pos (2 cap) | vel (2 cap)]; the rank never holds more than s->n agents
+    const size_t m = (size_t)s->n;
+    int* dcount = (int*)s->stage;
+    int* dids = dcount + 4;
+    float2* dpos = (float2*)(dids + m);
+    float2* dvel = dpos + m;
+    if ((4 + 5 * m) > s->stage_floats) return fail(LC_ERR_CAPACITY, "lc_dd_get_shard: staging too small");
+    CK(cudaMemsetAsync(dcount, 0, sizeof(int), s->st));
+    lc::launch_get_owned(s->dP, s->n, s->b, dids, dpos, dvel, dcount, s->st, &s->launches);
+    CK(cudaMemcpyAsync(count, dcount, sizeof(int), cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    const size_t k = (size_t)*count;
+    if ((int32_t)k > cap) return fail(LC_ERR_CAPACITY, "lc_dd_get_shard: %d owned agents, buffers hold %d", (int)k, cap);
+    CK(cudaMemcpyAsync(ids, dids, sizeof(int) * k, cudaMemcpyDeviceToHost, s->st));
+    if (pos) CK(cudaMemcpyAsync(pos, dpos, sizeof(float2) * k, cudaMemcpyDeviceToHost, s->st));
+    if (vel) CK(cudaMemcpyAsync(vel, dvel, sizeof(float2) * k, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }

@@ -344,19 +344,35 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
         }
         if (m) atomicMax(&s_ext[tid % HULL_K], m);
         __syncthreads();
-        // polygon through consecutive distinct extreme agents (CCW); inward unit normals
+        // polygon through consecutive distinct extreme agents (CCW); inward unit normals.  One thread per edge (the
+        // dependent position loads and the f64 sqrt used to sit in one thread's serial loop), thread 0 compacts.
+        __shared__ float s_e[HULL_K][4];
+        __shared__ int s_ev[HULL_K];
+        if (tid < HULL_K) {
+            const int k = tid;
+            int ok = 0;
+            const unsigned long long ka = s_ext[k], kb = s_ext[(k + 1) % HULL_K];
+            if (ka != 0ull && kb != 0ull) {
+                const int a = (int)(ka & 0xffffffffull), c = (int)(kb & 0xffffffffull);
+                if (a != c) {
+                    const float2 pa = input_pos(P, b, a), pc = input_pos(P, b, c);
+                    const double ux = (double)pc.x - pa.x, uy = (double)pc.y - pa.y, l = sqrt(ux * ux + uy * uy);
+                    if (l > 0.0) {
+                        s_e[k][0] = pa.x; s_e[k][1] = pa.y;
+                        s_e[k][2] = (float)(-uy / l); s_e[k][3] = (float)(ux / l);
+                        ok = 1;
+                    }
+                }
+            }
+            s_ev[k] = ok;
+        }
+        __syncthreads();
         if (tid == 0) {
             int ne = 0;
             for (int k = 0; k < HULL_K; ++k) {
-                unsigned long long ka = s_ext[k], kb = s_ext[(k + 1) % HULL_K];
-                if (ka == 0ull || kb == 0ull) continue;
-                int a = (int)(ka & 0xffffffffull), c = (int)(kb & 0xffffffffull);
-                if (a == c) continue;
-                float2 pa = input_pos(P, b, a), pc = input_pos(P, b, c);
-                double ux = (double)pc.x - pa.x, uy = (double)pc.y - pa.y, l = sqrt(ux * ux + uy * uy);
-                if (!(l > 0.0)) continue;
-                ctl->ex[ne] = pa.x; ctl->ey[ne] = pa.y;
-                ctl->enx[ne] = (float)(-uy / l); ctl->eny[ne] = (float)(ux / l);
+                if (!s_ev[k]) continue;
+                ctl->ex[ne] = s_e[k][0]; ctl->ey[ne] = s_e[k][1];
+                ctl->enx[ne] = s_e[k][2]; ctl->eny[ne] = s_e[k][3];
                 ++ne;
             }
             ctl->n_edges = ne;
@@ -1075,6 +1091,30 @@ __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P,
     if (lgoal) lgoal[id] = b.cur.lgoal[s];
     if (goal_dist) goal_dist[id] = c4.w;
     if (num_done) num_done[id] = mt.y & 1;
+}
+
+// domain mode, host-facing shard: (id, pos, vel) of the agents this rank owns, compacted (order arbitrary)
+__global__ void __launch_bounds__(256) k_get_owned(const Params* __restrict__ P, Buffers b, int* ids, float2* pos, float2* vel,
+                                                    int* count) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int4 mt = s < P->n ? b.cur.meta[s] : make_int4(0, META_GHOST, 0, 0);
+    const bool own = !(mt.y & META_GHOST);
+    const unsigned m = __ballot_sync(0xffffffffu, own);
+    int base = 0;
+    if ((threadIdx.x & 31) == 0 && m) base = atomicAdd(count, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (own) {
+        const int k = base + __popc(m & ((1u << (threadIdx.x & 31)) - 1u));
+        const float4 pv = b.cur.pv[s];
+        ids[k] = mt.x;
+        pos[k] = b.posf[s];
+        vel[k] = make_float2(pv.z, pv.w);
+    }
+}
+void launch_get_owned(const Params* dP, int n, const Buffers& b, int* ids, float2* pos, float2* vel, int* count,
+                      cudaStream_t st, long long* launches) {
+    k_get_owned<<<(n + 255) / 256, 256, 0, st>>>(dP, b, ids, pos, vel, count);
+    if (launches) *launches += 1;
 }
 
 // per-agent private LCG streams: agent id draws x0 * 16807^((frame-1)*n + id + 1) in frame `frame` (Seeder.cpp, LMP.cpp:261-263)

@@ -166,6 +166,8 @@ void launch_set_state(const Params* dP, int n, const Buffers& b, const float2* p
                       const float2* vfh, const float* c3, const float2* facing, const float2* lgoal,
                       const float* goal_dist, const int* num_done, const float2* goal, const float* min_time, int init,
                       cudaStream_t st, long long* launches, const int* ids = nullptr);
+void launch_get_owned(const Params* dP, int n, const Buffers& b, int* ids, float2* pos, float2* vel, int* count,
+                      cudaStream_t st, long long* launches);
 void launch_set_rng(const Params* dP, int n, const Buffers& b, uint32_t base, cudaStream_t st, long long* launches);
 
 }  // namespace lc

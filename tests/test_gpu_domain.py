@@ -63,9 +63,16 @@ def test_domain_lockstep_bit_exact(world):
     own1 = np.stack([s.owned() for s in sims])
     migrated = int((own0 != own1).any(0).sum())
     assert migrated > 0, "no agent changed owner: the test does not exercise migration"
+    full = ref.state()
+    seen = np.zeros(pos.shape[0], np.int32)
     for s in sims:
         n_loc, cap = s.counts()
         assert 0 < n_loc <= cap
+        sh, k = s.shard()   # the compact host-facing shard: ids, pos, vel of the rank's own agents
+        ids = sh["ids"][:k]
+        seen[ids] += 1
+        assert np.array_equal(sh["pos"][:k], full["pos"][ids]) and np.array_equal(sh["vel"][:k], full["vel"][ids])
+    assert (seen == 1).all()
     # diagnostics of the owners
     part = np.full(pos.shape[0], -2, np.int32)
     cnt = np.full(pos.shape[0], -2, np.int32)
