@@ -613,6 +613,7 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
     };
     // survivor j of the filter, recomputed from scratch (scalar operations == the packed lanes, bit for bit)
     auto revisit = [&](int j) {
+        if (j == s) return;
         const float4 q = __ldg(&b.srt.pv[j]);
         const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
         const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
@@ -620,22 +621,24 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         const float disc = __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c));
         evaluate(j, bq, c, a, disc, (c > 0.f && bq > 0.f) || disc < 0.f, FIRST && c < near_c);
     };
-    auto slow = [&](int j, float bq, float c, float a, float disc, bool far) {
-        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
-        const bool near = FIRST && c < near_c;
-        if (miss && !near) return;
-        if (j == s) return;  // the self pair (m = dv = 0) always reaches this point
-        if (lst && nlst < LIST_CAP) { lst[nlst * blockDim.x + threadIdx.x] = j; ++nlst; return; }
-        evaluate(j, bq, c, a, disc, miss, near);
+    // a survivor of the filter: remember it (evaluated after the scan), or evaluate on the spot when there is no list /
+    // the list is full.  The self pair (m = dv = 0: "in contact") always gets here once; revisit() drops it.
+    auto note = [&](int j) {
+        if (lst && nlst < LIST_CAP) { lst[nlst * blockDim.x + threadIdx.x] = j; ++nlst; }
+        else if (j != s) revisit(j);
     };
-    // scalar version for the odd slot at either end of a row range
+    // scalar version of the filter for the odd slot at either end of a row range
     auto single = [&](int j) {
         const float4 q = __ldg(&b.srt.pv[j]);
         const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
         const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
         if (bq > 0.f && c >= near_c) return;
         const float a = dot2(dvx, dvy, dvx, dvy);
-        slow(j, bq, c, a, __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c)), false);
+        const float bb = __fmul_rn(bq, bq), disc = __fsub_rn(bb, __fmul_rn(a, c));
+        const float u = __fsub_rn(-bq, __fmul_rn(a, 5.f));
+        const bool far = c >= 0.f && u > 0.f && __fmul_rn(u, u) > __fadd_rn(disc, __fmul_rn(bb, 1e-4f));
+        const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
+        if (!miss || (FIRST && c < near_c)) note(j);
     };
     for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
         const float ylo = ctl->y0 + (float)yy * ctl->h;
@@ -661,10 +664,6 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
             const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
             const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
             const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
-            // fast reject: separating and not in contact range (near_c > 0, so this implies c > 0 && b > 0)
-            const bool skip0 = bq.x > 0.f && c.x >= near_c;
-            const bool skip1 = bq.y > 0.f && c.y >= near_c;
-            if (skip0 && skip1) continue;
             const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
             const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
             const float2 bb = mul2(bq, bq), ac = mul2(a, c);
@@ -678,8 +677,17 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
             const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
             const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
             const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
-            if (!skip0) slow(j, bq.x, c.x, a.x, disc.x, far0);
-            if (!skip1) slow(j + 1, bq.y, c.y, a.y, disc.y, far1);
+            // Straight-line up to here on purpose: with 32 lanes x 2 candidates some lane always needs the whole filter,
+            // so "early outs" only added branches (the branchy version ran 77 instructions per iteration at 21 lanes).
+            // What survives is rare (~0.6 interacting neighbours per agent in the plaza): one predictable branch.
+            const bool miss0 = (c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0;
+            const bool miss1 = (c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1;
+            const bool cand0 = !miss0 || (FIRST && c.x < near_c);
+            const bool cand1 = !miss1 || (FIRST && c.y < near_c);
+            if (cand0 | cand1) {
+                if (cand0) note(j);
+                if (cand1) note(j + 1);
+            }
         }
     }
     for (int k = 0; k < nlst; ++k) revisit(lst[k * blockDim.x + threadIdx.x]);

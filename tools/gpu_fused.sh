@@ -1,14 +1,15 @@
 #!/bin/bash
 mkdir -p gpurun_out
 export LC_DD_TIMEOUT_MS=5000
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_fused.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_fused.log; tail -6 gpurun_out/pytest_fused.log
-for w in plaza1m plaza125k corridor100k circle1k; do
+timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_gpu_domain.py -m gpu -x -q > gpurun_out/pytest_fused.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_fused.log; tail -6 gpurun_out/pytest_fused.log
+for w in plaza1m plaza125k corridor100k; do
 python bench.py --no-cpu --no-e2e --workload $w > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err
 done
 python - <<'PY'
 import json
-for f in ('plaza1m','plaza125k','corridor100k','circle1k'):
+for f in ('plaza1m','plaza125k','corridor100k'):
     try:
         d=json.load(open(f'gpurun_out/bench_{f}.json')); print(f, '%.3e'%d['value'], '%.4f'%d['ms_per_step'], {k:round(v*1e3,1) for k,v in d['roofline']['kernel_ms'].items()})
     except Exception as e: print(f,'ERR',e)
 PY
+ncu --set full --clock-control none --import-source on -k k_force -s 30 -c 1 -o gpurun_out/prof_force_sl python bench.py --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_force_sl.log 2>&1
