@@ -251,6 +251,12 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
         ctl->n_cand = 0;
+        {   // k_bin's gate radius from last frame's directional extremes (0.1 m covers the agents' and the centre's motion)
+            float rho = CUDART_INF_F;
+            for (int k = 0; k < HULL_K; ++k) rho = fminf(rho, ctl->ext_val[k]);
+            rho -= 0.1f;
+            ctl->gate_rho2 = rho > 0.f ? rho * rho : -1.f;
+        }
         if (!dd) ctl->replan1 = ctl->replan2 = 0x7fffffff;  // domain mode: k_dd_wait merged the global gate
         if (dd) {  // the ghost band was sized for the speed bound (domain.cuh); a wider cutoff would miss neighbours
             const float vm = __uint_as_float(ctl->vmax);
@@ -303,15 +309,23 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
     // directional extremes of this block (stage-1 polygon for the comm-partner candidates); any maximiser is a valid vertex
     __shared__ unsigned long long s_key[32][HULL_K];
     const float rx = p.x - ctl->cx, ry = p.y - ctl->cy;
-    const bool ok = i < n && rx == rx && ry == ry;
+    // Gate: last frame's extreme in direction k had projection ext_val[k]; agents move a few cm per frame, so only agents
+    // at least min_k ext_val[k] - margin away from the centre can be this frame's extremes.  Warps whose agents are all
+    // inside that circle (3/4 of a square crowd) skip the 16 warp reductions.  If the guess is ever wrong the polygon just
+    // gets a vertex that is not extreme, or an edge less — any polygon through agents keeps the pruning exact.
+    const bool ok = i < n && rx == rx && ry == ry && (rx * rx + ry * ry >= ctl->gate_rho2);
+    if (__any_sync(0xffffffffu, ok)) {
 #pragma unroll
-    for (int k = 0; k < HULL_K; ++k) {
-        const float v = rx * c_dirx[k] + ry * c_diry[k];
-        const uint32_t ov = ok ? f2ord(v) : 0u;
-        const uint32_t best = __reduce_max_sync(0xffffffffu, ov);
-        const unsigned who = __ballot_sync(0xffffffffu, ov == best);
-        if (lane == (unsigned)(__ffs(who) - 1))
-            s_key[threadIdx.x >> 5][k] = best ? (((unsigned long long)best << 32) | (uint32_t)i) : 0ull;
+        for (int k = 0; k < HULL_K; ++k) {
+            const float v = rx * c_dirx[k] + ry * c_diry[k];
+            const uint32_t ov = ok ? f2ord(v) : 0u;
+            const uint32_t best = __reduce_max_sync(0xffffffffu, ov);
+            const unsigned who = __ballot_sync(0xffffffffu, ov == best);
+            if (lane == (unsigned)(__ffs(who) - 1))
+                s_key[threadIdx.x >> 5][k] = best ? (((unsigned long long)best << 32) | (uint32_t)i) : 0ull;
+        }
+    } else if (lane < HULL_K) {
+        s_key[threadIdx.x >> 5][lane] = 0ull;
     }
     __syncthreads();
     if (threadIdx.x < HULL_K) {
@@ -350,6 +364,7 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
         __shared__ int s_ev[HULL_K];
         if (tid < HULL_K) {
             const int k = tid;
+            ctl->ext_val[k] = s_ext[k] ? ord2f((uint32_t)(s_ext[k] >> 32)) : -CUDART_INF_F;  // next frame's k_bin gate
             int ok = 0;
             const unsigned long long ka = s_ext[k], kb = s_ext[(k + 1) % HULL_K];
             if (ka != 0ull && kb != 0ull) {
@@ -589,6 +604,7 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
     // sqrt(cutoff^2 - gap_y^2) in x.  Inflated by 1e-3 so that float rounding here can never exclude a cell that cell_of
     // (the same monotonic expression, applied to a position inside the disc) put an agent into.
     const float cut = ctl->cutoff * 1.001f + 1e-3f, cut2 = cut * cut;
+    const float inv_h = 1.f / ctl->h;
     const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
     const float2 RR2 = make_float2(RR, RR);
     const float4* __restrict__ pq = b.srt_pq;
@@ -645,9 +661,12 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         const float gap = yy == iy ? 0.f : (yy > iy ? ylo - py : py - (ylo + ctl->h));
         const float rem = cut2 - (gap > 0.f ? gap * gap : 0.f);
         if (!(rem > 0.f)) continue;
-        const float reach = sqrtf(rem);
-        const int x_lo = min(max((int)floorf((px - reach - ctl->x0) / ctl->h), max(ix - st, 0)), ix);
-        const int x_hi = max(min((int)floorf((px + reach - ctl->x0) / ctl->h), min(ix + st, nx - 1)), ix);
+        // approximate, but widened beyond every rounding: rsqrt is good to 2 ulp, the product with 1/h to < 1e-6 of its
+        // value, and the range only has to CONTAIN the cells cell_of() can have put a partner inside the disc into
+        const float reach = rem * rsqrtf(rem) * 1.0002f + 1e-4f;
+        const float xl = (px - reach - ctl->x0) * inv_h, xh = (px + reach - ctl->x0) * inv_h;
+        const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), max(ix - st, 0)), ix);
+        const int x_hi = max(min((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), min(ix + st, nx - 1)), ix);
         int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
         if (j0 >= j1) continue;
         if (j0 & 1) single(j0++);
@@ -816,16 +835,18 @@ __global__ void __launch_bounds__(128, 10) k_force(const Params* __restrict__ P,
             // comm.cpp:201-220 select_nearest == arg-max of squared distance (quirk Q1), strict '>', first in table order
             float best = LC_FLT_MIN;
             int best_id = -1, best_slot = s;
-            for (int k = 0; k < ncand; ++k) {
-                const float4 cd = cand[k];
+            auto consider = [&](const float4 cd) {
                 const int cid = __float_as_int(cd.z);
-                if (cid == id) continue;
+                if (cid == id) return;
                 const float dx = __fsub_rn(cd.x, px), dy = __fsub_rn(cd.y, py);
                 const float d2 = dot2(dx, dy, dx, dy);
                 if (d2 > best || (d2 == best && best_id >= 0 && cid < best_id)) {
                     best = d2; best_id = cid; best_slot = __float_as_int(cd.w);
                 }
-            }
+            };
+            // two loops so that the common case compiles to shared-memory loads instead of generic ones
+            if (cand == s_cand) for (int k = 0; k < ncand; ++k) consider(s_cand[k]);
+            else for (int k = 0; k < ncand; ++k) consider(__ldg(&cand[k]));
             if (best_id < 0) atomicCAS(&ctl->error, 0, -3);  // comm.cpp:273-285: null partner is UB in the reference
             if (owned) b.partner_id[id] = best_id;
             const float4 pj = __ldg(&b.srt.pv[best_slot]);
@@ -1202,6 +1223,7 @@ __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
         ctl->nnd_acc = 0;
+        for (int k = 0; k < HULL_K; ++k) ctl->ext_val[k] = -CUDART_INF_F;  // arbitrary new state: no gate next frame
     }
 }
 

@@ -54,6 +54,8 @@ struct Ctl {
     // comm-partner candidate pruning
     float cx, cy, delta;
     unsigned long long ext[HULL_K];
+    float ext_val[HULL_K];   // last frame's extreme projection per direction (k_scan_hull) -> gate of the next k_bin
+    float gate_rho2;
     int n_edges;
     float ex[HULL_K], ey[HULL_K], enx[HULL_K], eny[HULL_K];
     int n_cand;

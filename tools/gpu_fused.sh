@@ -12,4 +12,4 @@ for f in ('plaza1m','plaza125k','corridor100k'):
         d=json.load(open(f'gpurun_out/bench_{f}.json')); print(f, '%.3e'%d['value'], '%.4f'%d['ms_per_step'], {k:round(v*1e3,1) for k,v in d['roofline']['kernel_ms'].items()})
     except Exception as e: print(f,'ERR',e)
 PY
-ncu --set full --clock-control none --import-source on -k k_force -s 30 -c 1 -o gpurun_out/prof_force_sl python bench.py --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_force_sl.log 2>&1
+
