@@ -49,7 +49,7 @@ def lib():
     """Load (building if stale) the CUDA library.  Raises if it cannot be built/loaded: no fallback."""
     global _LIB
     if _LIB is None:
-        path = _build.build()
+        path = os.environ.get("LEARN_COMMS_LIB") or _build.build()  # override: A/B runs of differently built libraries
         L = C.CDLL(path)
         vp, i32, u32, f32p = C.c_void_p, C.c_int32, C.c_uint32, C.POINTER(C.c_float)
         L.lc_create.argtypes = [C.POINTER(_Desc), C.POINTER(vp)]
