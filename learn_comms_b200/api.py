@@ -267,7 +267,7 @@ class Sim:
         _ck(lib().lc_timer_stop(self.h, C.byref(ms)))
         return float(ms.value)
 
-    KERNELS = ("k_frame_begin", "k_bin", "k_scan_hull", "k_reorder", "k_refine", "k_force", "k_collide")
+    KERNELS = ("k_frame_begin", "k_bin", "k_scan_hull", "k_reorder", "k_refine", "k_pairs", "k_force", "k_collide")
 
     def step_profiled(self, n=1):
         """n frames launched kernel by kernel with CUDA events in between -> {kernel: mean ms per launch}."""

@@ -239,6 +239,9 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(dalloc(&b.blkext, (size_t)((n + 1023) / 1024) * lc::HULL_K)); s->allocs.push_back(b.blkext);
     CKC(dalloc(&b.near_cnt, n)); s->allocs.push_back(b.near_cnt);
     CKC(dalloc(&b.near_idx, (size_t)n * lc::MAX_NEAR)); s->allocs.push_back(b.near_idx);
+    CKC(dalloc(&b.pair_cnt, n)); s->allocs.push_back(b.pair_cnt);
+    CKC(dalloc(&b.pair_list, (size_t)n * lc::PAIR_CAP)); s->allocs.push_back(b.pair_list);
+    CKC(cudaMemset(b.pair_cnt, 0, sizeof(int) * n));
     CKC(dalloc(&b.events, (size_t)std::max(n, world * lc::DD_EV_CAP))); s->allocs.push_back(b.events);
     CKC(dalloc(&b.ev_by_id, n_ids)); s->allocs.push_back(b.ev_by_id);
     CKC(dalloc(&b.partner_id, n_ids)); s->allocs.push_back(b.partner_id);

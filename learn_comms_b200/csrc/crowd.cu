@@ -297,6 +297,7 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
     if (i < n) {
         p = input_pos(P, b, i);
         cell = cell_of(ctl, p.x, p.y);
+        b.pair_cnt[i] = 0;  // k_pairs' lists, indexed by this frame's slots
     }
     {   // Counting sort, phase 1.  The agents arrive in last frame's cell order, so equal cells form runs of
         // consecutive lanes: one atomicAdd per run instead of one per agent (same-address atomics serialise in L2).
@@ -593,16 +594,40 @@ __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, B
 // ---------------------------------------------------------------------------------------------------------
 // S1 + S2 + S3a fused, one thread per agent in cell order.
 
-// Visit every interacting neighbour {j : ttc_ij <= 5} of agent s in the (2*stencil+1)^2 cell block.  Cells of one
-// grid row are contiguous in the sorted arrays, so each row of the block is ONE contiguous slot range.
-// `lst` (shared memory, [LIST_CAP][blockDim.x], or nullptr): survivors of the packed filter are only RECORDED while the
-// cell block is scanned and evaluated afterwards, all lanes of a warp working on their k-th survivor at the same time.
-// Evaluating them on the spot (sqrt, divisions, the f64 magnitude) ran at 13 of 32 lanes active and made up 39 % of the
-// kernel's instructions (profiles/prof_force_r1f_raw.csv).
+// One pair (s, j), from scratch: LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame (same operations as
+// lc_math.cuh ttc_pair and, bit for bit, as the packed lanes of the filter below), the near list of the collision pass,
+// and the TTC force on a hit (LMP.cpp:288-304).
 template <bool FIRST, class F>
-__device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx,
-                                                float vy, float RR, float near_c, int& n_near, int& n_overlap, int* lst,
-                                                F&& f) {
+__device__ __forceinline__ void pair_eval(const Buffers& b, int s, int j, float px, float py, float vx, float vy, float RR,
+                                          float near_c, int& n_near, int& n_overlap, F&& f) {
+    const float4 q = __ldg(&b.srt.pv[j]);
+    const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
+    const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
+    const float a = dot2(dvx, dvy, dvx, dvy);
+    const float disc = __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c));
+    if (FIRST && c < near_c) {
+        if (n_near < MAX_NEAR) b.near_idx[(size_t)s * MAX_NEAR + n_near] = j;
+        ++n_near;
+        if (c < 0.f) ++n_overlap;  // BoundVolume.cpp:203-207 on frame-start positions
+    }
+    if ((c > 0.f && bq > 0.f) || disc < 0.f) return;
+    float t = __fdiv_rn(__fsub_rn(-bq, __fsqrt_rn(disc)), a);
+    if (t < 0.f) t = 0.f;
+    if (!(t >= 0.f)) return;  // NaN -> FLT_MAX (LMP.cpp:31-34)
+    if (t > 5.0f) return;     // (double)ttc > 5.0 (LMP.cpp:297-300)
+    float fx, fy;
+    ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
+    f(j, fx, fy);
+}
+
+// Pair filter over the cell block of agent s: note(j) for every j in the block that MAY interact with s (ttc <= 5) or
+// is within reach of the collision pass (FIRST).  Cells of one grid row are contiguous in the sorted arrays, so each
+// row of the block is ONE contiguous slot range.  HALF: only partners that come after s in slot order (the rest of
+// its own row and the rows above) — the filter is exactly symmetric in (s, j): m and dv only change sign, every
+// product and sum is the same float, so one test serves both agents (k_pairs).
+template <bool HALF, bool FIRST, class N>
+__device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
+                                           float RR, float near_c, N&& note) {
     const int st = ctl->stencil, nx = ctl->nx, ny = ctl->ny;
     int ix = (int)floorf((px - ctl->x0) / ctl->h), iy = (int)floorf((py - ctl->y0) / ctl->h);
     ix = min(max(ix, 0), nx - 1);
@@ -615,41 +640,6 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
     const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
     const float2 RR2 = make_float2(RR, RR);
     const float4* __restrict__ pq = b.srt_pq;
-    // One candidate of a pair beyond the fast reject: LMP.cpp:37-55 / BoundVolume.cpp:102-122 in the relative frame
-    // (same operations as lc_math.cuh ttc_pair), the near list of the collision pass, and the force on a hit.
-    int nlst = 0;
-    auto evaluate = [&](int j, float bq, float c, float a, float disc, bool miss, bool near) {
-        if (near) {
-            if (n_near < MAX_NEAR) b.near_idx[(size_t)s * MAX_NEAR + n_near] = j;
-            ++n_near;
-            if (c < 0.f) ++n_overlap;  // BoundVolume.cpp:203-207 on frame-start positions
-        }
-        if (miss) return;
-        float t = __fdiv_rn(__fsub_rn(-bq, __fsqrt_rn(disc)), a);
-        if (t < 0.f) t = 0.f;
-        if (!(t >= 0.f)) return;  // NaN -> FLT_MAX (LMP.cpp:31-34)
-        if (t > 5.0f) return;     // (double)ttc > 5.0 (LMP.cpp:297-300)
-        const float4 q = __ldg(&b.srt.pv[j]);
-        float fx, fy;
-        ttc_force(px, py, vx, vy, q.x, q.y, q.z, q.w, t, fx, fy);
-        f(j, fx, fy);
-    };
-    // survivor j of the filter, recomputed from scratch (scalar operations == the packed lanes, bit for bit)
-    auto revisit = [&](int j) {
-        if (j == s) return;
-        const float4 q = __ldg(&b.srt.pv[j]);
-        const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
-        const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
-        const float a = dot2(dvx, dvy, dvx, dvy);
-        const float disc = __fsub_rn(__fmul_rn(bq, bq), __fmul_rn(a, c));
-        evaluate(j, bq, c, a, disc, (c > 0.f && bq > 0.f) || disc < 0.f, FIRST && c < near_c);
-    };
-    // a survivor of the filter: remember it (evaluated after the scan), or evaluate on the spot when there is no list /
-    // the list is full.  The self pair (m = dv = 0: "in contact") always gets here once; revisit() drops it.
-    auto note = [&](int j) {
-        if (lst && nlst < LIST_CAP) { lst[nlst * blockDim.x + threadIdx.x] = j; ++nlst; }
-        else if (j != s) revisit(j);
-    };
     // scalar version of the filter for the odd slot at either end of a row range
     auto single = [&](int j) {
         const float4 q = __ldg(&b.srt.pv[j]);
@@ -663,7 +653,7 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
         if (!miss || (FIRST && c < near_c)) note(j);
     };
-    for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
+    for (int yy = HALF ? iy : max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
         const float ylo = ctl->y0 + (float)yy * ctl->h;
         const float gap = yy == iy ? 0.f : (yy > iy ? ylo - py : py - (ylo + ctl->h));
         const float rem = cut2 - (gap > 0.f ? gap * gap : 0.f);
@@ -674,7 +664,8 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
         const float xl = (px - reach - ctl->x0) * inv_h, xh = (px + reach - ctl->x0) * inv_h;
         const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), max(ix - st, 0)), ix);
         const int x_hi = max(min((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), min(ix + st, nx - 1)), ix);
-        int j0 = b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
+        // s lies in cell (ix, iy), x_lo <= ix <= x_hi: in its own row the partners after s start at slot s + 1
+        int j0 = (HALF && yy == iy) ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
         if (j0 >= j1) continue;
         if (j0 & 1) single(j0++);
         if ((j1 & 1) && j1 > j0) single(--j1);
@@ -716,7 +707,37 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
             }
         }
     }
-    for (int k = 0; k < nlst; ++k) revisit(lst[k * blockDim.x + threadIdx.x]);
+}
+
+// Every interacting neighbour of agent s, evaluated on the spot over its whole cell block.  The rare paths only: an
+// agent whose pair list overflowed, and the per-neighbour re-scan when the hit buffer overflowed.
+template <bool FIRST, class F>
+__device__ __noinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
+                                             float RR, float near_c, int& n_near, int& n_overlap, F&& f) {
+    scan_cells<false, FIRST>(b, ctl, s, px, py, vx, vy, RR, near_c, [&](int j) {
+        if (j != s) pair_eval<FIRST>(b, s, j, px, py, vx, vy, RR, near_c, n_near, n_overlap, f);
+    });
+}
+
+// S2a: pair filter, each unordered pair tested ONCE (by the agent that comes first in cell order) and recorded in the
+// pair lists of both; k_force evaluates the lists.  Halves the pair tests of a per-agent scan of the whole disc.
+#ifndef LC_PAIR_BLOCKS
+#define LC_PAIR_BLOCKS 12
+#endif
+__global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __restrict__ P, Buffers b) {
+    const Ctl* ctl = b.ctl;
+    if (ctl->halt) return;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P->n) return;
+    const float4 me = b.srt.pv[s];
+    const size_t stride = (size_t)P->cap;
+    scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [&](int j) {
+        // entries past PAIR_CAP are only counted: k_force then scans the whole disc for that agent
+        int k = atomicAdd(&b.pair_cnt[s], 1);
+        if (k < PAIR_CAP) b.pair_list[k * stride + s] = j;
+        k = atomicAdd(&b.pair_cnt[j], 1);
+        if (k < PAIR_CAP) b.pair_list[k * stride + j] = s;
+    });
 }
 
 #ifndef LC_FORCE_BLOCKS
@@ -734,7 +755,6 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
     // in B only if max_{q in B} |q - k|^2 is not below L = max_k' min_{q in B} |q - k'|^2 (1e-4 relative slack >> the
     // float rounding of length2).  Survivors are staged in shared memory; typically a handful remain.
     __shared__ float4 s_cand[CAND_SMEM];
-    __shared__ int s_list[LIST_CAP * 128];
     __shared__ uint32_t s_bb[5];
     __shared__ int s_nc;
     const float4* __restrict__ cand = nullptr;
@@ -790,11 +810,18 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         int hid[MAX_HITS];
         float hfx[MAX_HITS], hfy[MAX_HITS];
         int cnt = 0, n_near = 0, n_overlap = 0;
-        scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, s_list,
-                              [&](int j, float fx, float fy) {
-                                  if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
-                                  ++cnt;
-                              });
+        auto hit = [&](int j, float fx, float fy) {
+            if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
+            ++cnt;
+        };
+        const int np = b.pair_cnt[s];
+        if (np <= PAIR_CAP) {  // survivors of k_pairs' filter (in no particular order: hits and near list are sorted by id)
+            const size_t stride = (size_t)P->cap;
+            for (int k = 0; k < np; ++k)
+                pair_eval<true>(b, s, b.pair_list[k * stride + s], px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, hit);
+        } else {
+            scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, hit);
+        }
         float ttcFx = 0.f, ttcFy = 0.f;
         int* lst = ((P->flags & 4u) && !(b.srt.meta[s].y & META_GHOST)) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
         if (cnt <= MAX_HITS) {
@@ -816,7 +843,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             for (int k = 0; k < cnt; ++k) {
                 int bid = 0x7fffffff;
                 float bfx = 0.f, bfy = 0.f;
-                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1, nullptr,
+                scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1,
                                        [&](int j, float fx, float fy) {
                                            int v = __ldg(&b.srt.meta[j].x);
                                            if (v > last && v < bid) { bid = v; bfx = fx; bfy = fy; }
@@ -1304,10 +1331,12 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     if (ev) cudaEventRecord(ev[4], st);
     k_refine<<<1, 1024, 0, st>>>(dP, b);            // + candidate all-gather in domain mode
     if (ev) cudaEventRecord(ev[5], st);
-    k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    k_pairs<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[6], st);
-    k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[7], st);
+    k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    if (ev) cudaEventRecord(ev[8], st);
     if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
 }
 

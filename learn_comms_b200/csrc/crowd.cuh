@@ -9,7 +9,7 @@ constexpr int HULL_K = 16;        // directional extremes used to prune comm-par
 constexpr int HULL_K2 = 64;       // stage 2, over the stage-1 survivors only (one block does it: 256 directions cost 20 us)
 constexpr int CAND_SMEM = 128;     // per-block candidate list of k_force (stage 3); falls back to the global list beyond
 constexpr int REFINE_MAX = 1 << 16; // stage 2 is skipped when stage 1 leaves more than this many candidates
-constexpr int LIST_CAP = 24;      // per-thread list (shared memory) of pair-filter survivors that k_force evaluates after the scan
+constexpr int PAIR_CAP = 32;      // per-agent list of pair-filter survivors (k_pairs -> k_force); beyond it k_force scans the whole disc
 constexpr int MAX_HITS = 48;      // per-thread buffer of interacting neighbours (sorted by id before summation)
 constexpr int MAX_NEAR = 8;       // per-agent list of neighbours close enough to collide this frame
 constexpr int CELL_CAP = 1 << 18; // max grid cells (cell side grows beyond the cutoff if exceeded)
@@ -114,6 +114,8 @@ struct Buffers {
     float4* cand2;     // [REFINE_MAX] after the second pruning stage
     int* near_cnt;     // [n]
     int* near_idx;     // [n][MAX_NEAR]
+    int* pair_cnt;     // [n] by slot: filter survivors recorded for the agent this frame (may exceed PAIR_CAP)
+    int* pair_list;    // [PAIR_CAP][n] by slot: partner slots, entry k of all agents contiguous
     int2* events;      // (id, min_time bits) of agents that became done this frame
     float* ev_by_id;   // [n] per-id event path (NaN = none)
     int* partner_id;   // [n] by id (diagnostic)
@@ -155,7 +157,7 @@ struct DomainDev {
 DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 
 void upload_dirs();
-constexpr int FRAME_KERNELS = 7;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, force, collide
+constexpr int FRAME_KERNELS = 8;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, pairs, force, collide
 constexpr int DD_KERNELS = 1;     // domain mode: dd_pack + dd_sync_begin (replaces frame_begin); the candidate exchange rides in k_refine
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
                   cudaEvent_t* ev = nullptr);
