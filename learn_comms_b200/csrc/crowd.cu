@@ -712,7 +712,7 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
 // Every interacting neighbour of agent s, evaluated on the spot over its whole cell block.  The rare paths only: an
 // agent whose pair list overflowed, and the per-neighbour re-scan when the hit buffer overflowed.
 template <bool FIRST, class F>
-__device__ __noinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
+__device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
                                              float RR, float near_c, int& n_near, int& n_overlap, F&& f) {
     scan_cells<false, FIRST>(b, ctl, s, px, py, vx, vy, RR, near_c, [&](int j) {
         if (j != s) pair_eval<FIRST>(b, s, j, px, py, vx, vy, RR, near_c, n_near, n_overlap, f);
