@@ -65,6 +65,7 @@ struct lc_sim {
     lc::Buffers b{};
     cudaStream_t st = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    lc::SideStream side{nullptr, nullptr, nullptr};  // k_refine next to k_pairs (crowd.cuh)
     cudaGraphExec_t gexec[2] = {nullptr, nullptr};  // 1 frame, GRAPH_BATCH frames
     long long launches = 0;
     int device = 0;
@@ -103,7 +104,7 @@ static int build_graphs(lc_sim* s) {
         int frames = g == 0 ? 1 : GRAPH_BATCH;
         cudaGraph_t graph;
         CK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
-        for (int f = 0; f < frames; ++f) lc::launch_frame(s->dP, s->n, s->b, s->st, nullptr);
+        for (int f = 0; f < frames; ++f) lc::launch_frame(s->dP, s->n, s->b, s->st, nullptr, nullptr, &s->side);
         CK(cudaStreamEndCapture(s->st, &graph));
         CK(cudaGraphInstantiate(&s->gexec[g], graph, 0));
         CK(cudaGraphDestroy(graph));
@@ -138,6 +139,9 @@ void lc_destroy(lc_sim* s) {
     cudaSetDevice(s->device);
     if (s->st) cudaStreamSynchronize(s->st);
     for (auto& g : s->gexec) if (g) cudaGraphExecDestroy(g);
+    if (s->side.st) cudaStreamDestroy(s->side.st);
+    if (s->side.fork) cudaEventDestroy(s->side.fork);
+    if (s->side.join) cudaEventDestroy(s->side.join);
     for (void* p : s->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void* p : s->allocs) cudaFree(p);
     if (s->mailbox) cudaFree(s->mailbox);
@@ -221,6 +225,13 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking));
     CKC(cudaEventCreate(&s->ev0));
     CKC(cudaEventCreate(&s->ev1));
+    {
+        int lo = 0, hi = 0;
+        CKC(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CKC(cudaStreamCreateWithPriority(&s->side.st, cudaStreamNonBlocking, hi));  // one block: let it in ahead of k_pairs
+        CKC(cudaEventCreateWithFlags(&s->side.fork, cudaEventDisableTiming));
+        CKC(cudaEventCreateWithFlags(&s->side.join, cudaEventDisableTiming));
+    }
     CKB(alloc_arrays(s, s->b.cur, n));
     CKB(alloc_arrays(s, s->b.srt, n + annex));  // annex: comm-partner payload of other ranks' candidates (k_dd_cand)
     lc::Buffers& b = s->b;

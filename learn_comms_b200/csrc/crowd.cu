@@ -124,18 +124,21 @@ __device__ void grid_from_reductions(const Params* P, Ctl* ctl) {
     // when the crowd is (almost) at rest
     cutoff = fmaxf(cutoff, P->near_reach);
     int st = P->stencil_req < 1 ? 1 : P->stencil_req;
-    float h = cutoff / (float)st;
+    // Cells are CELL_XSUB times narrower in x than in y: a row of the cell block is one contiguous slot range whatever the
+    // cell width, so narrow cells trim the overshoot at both ends of every row without adding rows (= range setups).
+    float h = cutoff / (float)st, hx = h / (float)CELL_XSUB;
     float ext = fmaxf(maxx - minx, maxy - miny);
     int nx, ny;
     for (;;) {
-        nx = (int)floorf((maxx - minx) / h) + 1;
+        nx = (int)floorf((maxx - minx) / hx) + 1;
         ny = (int)floorf((maxy - miny) / h) + 1;
         if ((long long)nx * ny <= CELL_CAP && nx <= 65535 && ny <= 65535) break;
-        h *= 2.f;
+        if (hx < h) hx *= 2.f; else { h *= 2.f; hx = h; }
     }
-    ctl->x0 = minx; ctl->y0 = miny; ctl->h = h; ctl->nx = nx; ctl->ny = ny; ctl->ncells = nx * ny;
+    ctl->x0 = minx; ctl->y0 = miny; ctl->h = h; ctl->hx = hx; ctl->nx = nx; ctl->ny = ny; ctl->ncells = nx * ny;
     ctl->cutoff = cutoff;
     ctl->stencil = (int)ceilf(cutoff / h);
+    ctl->stencil_x = (int)ceilf(cutoff / hx);
     ctl->cx = 0.5f * (minx + maxx); ctl->cy = 0.5f * (miny + maxy);
     ctl->delta = 1e-5f * ext + 1e-4f;
 }
@@ -280,7 +283,7 @@ __global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__
 // ---------------------------------------------------------------------------------------------------------
 // Uniform grid, phase 1: cell id + arrival rank per agent; directional extremes for candidate pruning.
 __device__ __forceinline__ int cell_of(const Ctl* ctl, float x, float y) {
-    int ix = (int)floorf((x - ctl->x0) / ctl->h), iy = (int)floorf((y - ctl->y0) / ctl->h);
+    int ix = (int)floorf((x - ctl->x0) / ctl->hx), iy = (int)floorf((y - ctl->y0) / ctl->h);
     ix = min(max(ix, 0), ctl->nx - 1);
     iy = min(max(iy, 0), ctl->ny - 1);
     return iy * ctl->nx + ix;
@@ -347,7 +350,8 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
 }
 
 // Exclusive scan of the cell histogram: one 4096-cell tile per block, tile offsets by look-back over the aggregates the
-// earlier tiles publish (at most SCAN_TILES <= 64 blocks, all co-resident on 148 SMs, so the spin cannot deadlock).
+// earlier tiles publish (a tile only waits for lower-numbered tiles, and blocks are dispatched in index order, so the
+// spin cannot deadlock).
 // The extra last block folds k_bin's per-block directional extremes and builds the stage-1 pruning polygon.
 __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P, Buffers b) {
     Ctl* ctl = b.ctl;
@@ -628,15 +632,15 @@ __device__ __forceinline__ void pair_eval(const Buffers& b, int s, int j, float 
 template <bool HALF, bool FIRST, class N>
 __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
                                            float RR, float near_c, N&& note) {
-    const int st = ctl->stencil, nx = ctl->nx, ny = ctl->ny;
-    int ix = (int)floorf((px - ctl->x0) / ctl->h), iy = (int)floorf((py - ctl->y0) / ctl->h);
+    const int st = ctl->stencil, stx = ctl->stencil_x, nx = ctl->nx, ny = ctl->ny;
+    int ix = (int)floorf((px - ctl->x0) / ctl->hx), iy = (int)floorf((py - ctl->y0) / ctl->h);
     ix = min(max(ix, 0), nx - 1);
     iy = min(max(iy, 0), ny - 1);
     // Disc-shaped stencil: a row of cells whose nearest edge is gap_y away can only hold interaction partners within
     // sqrt(cutoff^2 - gap_y^2) in x.  Inflated by 1e-3 so that float rounding here can never exclude a cell that cell_of
     // (the same monotonic expression, applied to a position inside the disc) put an agent into.
     const float cut = ctl->cutoff * 1.001f + 1e-3f, cut2 = cut * cut;
-    const float inv_h = 1.f / ctl->h;
+    const float inv_h = 1.f / ctl->hx;
     const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
     const float2 RR2 = make_float2(RR, RR);
     const float4* __restrict__ pq = b.srt_pq;
@@ -653,6 +657,45 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
         const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
         if (!miss || (FIRST && c < near_c)) note(j);
     };
+    // The packed filter on one slot pair: cand = "may interact (ttc <= 5) or within reach of the collision pass".
+    // Straight-line on purpose: with 32 lanes x 2 candidates some lane always needs the whole filter, so "early outs" only
+    // added branches (the branchy version ran 77 instructions per iteration at 21 lanes); what survives is rare (~0.6
+    // interacting neighbours per agent in the plaza) and costs one predictable branch per iteration.
+    auto filter2 = [&](const float4 P4, const float4 V4, bool& cand0, bool& cand1) {
+        const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
+        const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
+        // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under -fmad=false, which would round once instead
+        // of twice: every sum that consumes a product is therefore a SCALAR __fadd_rn / __fsub_rn (never contracted);
+        // packed adds only ever consume loads or other sums.  tests/test_oracle_cpu.py checks the SASS for FFMA2.
+        const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
+        const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
+        const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
+        const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
+        const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
+        const float2 bb = mul2(bq, bq), ac = mul2(a, c);
+        const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
+        // Conservative "t > 5" filter, so that sqrt + division only run for near-certain neighbours.  With c >= 0 and
+        // b <= 0: t = (-b - sqrt(disc)) / a > 5  <=>  u = -b - 5a > sqrt(disc).  Requiring u > 0 and
+        // u^2 > disc + 1e-4 b^2 leaves u - sqrt(disc) > 5e-5 |b|, two orders of magnitude above the rounding error of
+        // the reference's float evaluation of t, so no pair with float ttc <= 5 is ever filtered.
+        const float2 a5 = mul2(a, make_float2(5.f, 5.f));
+        const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));  // scalar: keeps the SASS free of FFMA2
+        const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
+        if (FIRST) {
+            // near_c > 0 (the collision reach exceeds the contact distance), so beyond it c > 0 holds and the tests on the
+            // sign of c drop out: miss = b > 0 || disc < 0 || far.  Comparisons keep the polarity of the general form
+            // below, so a NaN anywhere still makes the pair a candidate.
+            const bool far0 = u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+            const bool far1 = u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+            cand0 = c.x < near_c || !(bq.x > 0.f || disc.x < 0.f || far0);
+            cand1 = c.y < near_c || !(bq.y > 0.f || disc.y < 0.f || far1);
+        } else {
+            const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+            const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+            cand0 = !((c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0);
+            cand1 = !((c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1);
+        }
+    };
     for (int yy = HALF ? iy : max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
         const float ylo = ctl->y0 + (float)yy * ctl->h;
         const float gap = yy == iy ? 0.f : (yy > iy ? ylo - py : py - (ylo + ctl->h));
@@ -662,49 +705,35 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
         // value, and the range only has to CONTAIN the cells cell_of() can have put a partner inside the disc into
         const float reach = rem * rsqrtf(rem) * 1.0002f + 1e-4f;
         const float xl = (px - reach - ctl->x0) * inv_h, xh = (px + reach - ctl->x0) * inv_h;
-        const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), max(ix - st, 0)), ix);
-        const int x_hi = max(min((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), min(ix + st, nx - 1)), ix);
+        const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), max(ix - stx, 0)), ix);
+        const int x_hi = max(min((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), min(ix + stx, nx - 1)), ix);
         // s lies in cell (ix, iy), x_lo <= ix <= x_hi: in its own row the partners after s start at slot s + 1
         int j0 = (HALF && yy == iy) ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
         if (j0 >= j1) continue;
         if (j0 & 1) single(j0++);
         if ((j1 & 1) && j1 > j0) single(--j1);
-        // two candidates per iteration: slots (j, j + 1), j even, are stored as (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
-        const float4* __restrict__ pp = pq + j0;
-        for (int j = j0; j < j1; j += 2, pp += 2) {
-            const float4 P4 = __ldg(pp), V4 = __ldg(pp + 1);  // (a software-prefetched variant measured 4% slower)
-            const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
-            const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
-            // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under -fmad=false, which would round once instead
-            // of twice: every sum that consumes a product is therefore a SCALAR __fadd_rn / __fsub_rn (never contracted);
-            // packed adds only ever consume loads or other sums.  tests/test_oracle_cpu.py checks the SASS for FFMA2.
-            const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
-            const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
-            const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
-            const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
-            const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
-            const float2 bb = mul2(bq, bq), ac = mul2(a, c);
-            const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
-            // Conservative "t > 5" filter, so that sqrt + division only run for near-certain neighbours.  With c >= 0 and
-            // b <= 0: t = (-b - sqrt(disc)) / a > 5  <=>  u = -b - 5a > sqrt(disc).  Requiring u > 0 and
-            // u^2 > disc + 1e-4 b^2 leaves u - sqrt(disc) > 5e-5 |b|, two orders of magnitude above the rounding error of
-            // the reference's float evaluation of t, so no pair with float ttc <= 5 is ever filtered.
-            const float2 a5 = mul2(a, make_float2(5.f, 5.f));
-            const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));  // scalar: keeps the SASS free of FFMA2
-            const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
-            const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
-            const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
-            // Straight-line up to here on purpose: with 32 lanes x 2 candidates some lane always needs the whole filter,
-            // so "early outs" only added branches (the branchy version ran 77 instructions per iteration at 21 lanes).
-            // What survives is rare (~0.6 interacting neighbours per agent in the plaza): one predictable branch.
-            const bool miss0 = (c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0;
-            const bool miss1 = (c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1;
-            const bool cand0 = !miss0 || (FIRST && c.x < near_c);
-            const bool cand1 = !miss1 || (FIRST && c.y < near_c);
-            if (cand0 | cand1) {
-                if (cand0) note(j);
-                if (cand1) note(j + 1);
+        // two candidates per packed operation: slots (j, j + 1), j even, are stored as (x0, x1, z0, z1), (vx0, vx1, vz0, vz1);
+        // two such slot pairs per iteration (loop overhead was a fifth of the instructions at one)
+        int p = j0 >> 1;
+        const int pe = j1 >> 1;
+        for (; p + 1 < pe; p += 2) {
+            const float4 A0 = __ldg(&pq[2 * p]), B0 = __ldg(&pq[2 * p + 1]), A1 = __ldg(&pq[2 * p + 2]), B1 = __ldg(&pq[2 * p + 3]);
+            bool c0, c1, c2, c3;
+            filter2(A0, B0, c0, c1);
+            filter2(A1, B1, c2, c3);
+            if (c0 | c1 | c2 | c3) {
+                if (c0) note(2 * p);
+                if (c1) note(2 * p + 1);
+                if (c2) note(2 * p + 2);
+                if (c3) note(2 * p + 3);
             }
+        }
+        if (p < pe) {
+            const float4 A0 = __ldg(&pq[2 * p]), B0 = __ldg(&pq[2 * p + 1]);
+            bool c0, c1;
+            filter2(A0, B0, c0, c1);
+            if (c0) note(2 * p);
+            if (c1) note(2 * p + 1);
         }
     }
 }
@@ -1068,16 +1097,16 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                 }
             } else {
                 // near-list overflow (more than MAX_NEAR agents within ~0.34 m): walk the cell block, one hit per pass
-                const int nx = ctl->nx, ny = ctl->ny, st = ctl->stencil;
+                const int nx = ctl->nx, ny = ctl->ny, st = ctl->stencil, stx = ctl->stencil_x;
                 const float4 old = b.srt.pv[s];  // frame-start position decides the cell block
-                int ix = min(max((int)floorf((old.x - ctl->x0) / ctl->h), 0), nx - 1);
+                int ix = min(max((int)floorf((old.x - ctl->x0) / ctl->hx), 0), nx - 1);
                 int iy = min(max((int)floorf((old.y - ctl->y0) / ctl->h), 0), ny - 1);
                 int last = -1;
                 for (;;) {
                     int bid = 0x7fffffff;
                     float bax = 0.f, bay = 0.f;
                     for (int yy = max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
-                        const int j0 = b.cell_start[yy * nx + max(ix - st, 0)], j1 = b.cell_start[yy * nx + min(ix + st, nx - 1) + 1];
+                        const int j0 = b.cell_start[yy * nx + max(ix - stx, 0)], j1 = b.cell_start[yy * nx + min(ix + stx, nx - 1) + 1];
                         for (int j = j0; j < j1; ++j) {
                             if (j == s) continue;
                             const float4 o = __ldg(&b.cur.pv[j]);
@@ -1310,7 +1339,8 @@ void upload_dirs() {
     cudaMemcpyToSymbol(c_dir2y, ey, sizeof ey);
 }
 
-void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev) {
+void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev,
+                  const SideStream* side) {
     // n = launch width (the capacity in domain mode; kernels read the live count from Params::n on the device)
     // ev (optional, FRAME_KERNELS + 1 events): per-kernel device timing for bench.py's roofline leg
     const bool dd = b.dd != nullptr;
@@ -1329,9 +1359,18 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     if (ev) cudaEventRecord(ev[3], st);
     k_reorder<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[4], st);
-    k_refine<<<1, 1024, 0, st>>>(dP, b);            // + candidate all-gather in domain mode
-    if (ev) cudaEventRecord(ev[5], st);
-    k_pairs<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    if (side && !ev) {  // (the profiled path stays serial so that the per-kernel times mean something)
+        cudaEventRecord(side->fork, st);
+        cudaStreamWaitEvent(side->st, side->fork, 0);
+        k_refine<<<1, 1024, 0, side->st>>>(dP, b);  // + candidate all-gather in domain mode
+        cudaEventRecord(side->join, side->st);
+        k_pairs<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+        cudaStreamWaitEvent(st, side->join, 0);
+    } else {
+        k_refine<<<1, 1024, 0, st>>>(dP, b);
+        if (ev) cudaEventRecord(ev[5], st);
+        k_pairs<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    }
     if (ev) cudaEventRecord(ev[6], st);
     k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[7], st);

@@ -12,7 +12,11 @@ constexpr int REFINE_MAX = 1 << 16; // stage 2 is skipped when stage 1 leaves mo
 constexpr int PAIR_CAP = 32;      // per-agent list of pair-filter survivors (k_pairs -> k_force); beyond it k_force scans the whole disc
 constexpr int MAX_HITS = 48;      // per-thread buffer of interacting neighbours (sorted by id before summation)
 constexpr int MAX_NEAR = 8;       // per-agent list of neighbours close enough to collide this frame
-constexpr int CELL_CAP = 1 << 18; // max grid cells (cell side grows beyond the cutoff if exceeded)
+constexpr int CELL_CAP = 1 << 20; // max grid cells (cell sides grow if exceeded)
+#ifndef LC_CELL_XSUB
+#define LC_CELL_XSUB 4
+#endif
+constexpr int CELL_XSUB = LC_CELL_XSUB;  // cells per cell height along x (grid_from_reductions)
 constexpr int SCAN_TILE = 4096;   // cells scanned per block of k_scan_hull
 constexpr int SCAN_TILES = CELL_CAP / SCAN_TILE + 1;  // tiles cover indices [0, ncells] inclusive
 constexpr int CELL_ALLOC = SCAN_TILES * SCAN_TILE;    // allocation of cell_count / cell_start
@@ -49,8 +53,8 @@ struct Ctl {
     int halt;       // frames after the all_done frame are no-ops
     int error;      // lc_status of the first device-side error
     // uniform grid of the current frame
-    float x0, y0, h, cutoff;
-    int nx, ny, ncells, stencil;
+    float x0, y0, h, hx, cutoff;   // cell height (y) and width (x)
+    int nx, ny, ncells, stencil, stencil_x;
     // comm-partner candidate pruning
     float cx, cy, delta;
     unsigned long long ext[HULL_K];
@@ -159,8 +163,11 @@ DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 void upload_dirs();
 constexpr int FRAME_KERNELS = 8;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, pairs, force, collide
 constexpr int DD_KERNELS = 1;     // domain mode: dd_pack + dd_sync_begin (replaces frame_begin); the candidate exchange rides in k_refine
+// Side stream of a frame: k_refine (one block: second pruning stage and, in domain mode, the candidate exchange with the
+// peers) does not feed k_pairs, so the two run side by side (fork after k_reorder, join before k_force).
+struct SideStream { cudaStream_t st; cudaEvent_t fork, join; };
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
-                  cudaEvent_t* ev = nullptr);
+                  cudaEvent_t* ev = nullptr, const SideStream* side = nullptr);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
