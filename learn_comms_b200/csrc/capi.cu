@@ -240,6 +240,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(cudaMemset(b.srt_pq, 0, sizeof(float4) * 2 * ((size_t)(n + 1) / 2)));
     CKC(dalloc(&b.cellrank, n)); s->allocs.push_back(b.cellrank);
     CKC(dalloc(&b.cell_count, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_count);
+    CKC(cudaMemset(b.cell_count, 0, sizeof(int) * lc::CELL_ALLOC));  // k_scan_hull leaves it cleared after every frame
     CKC(dalloc(&b.cell_start, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_start);
     CKC(dalloc(&b.tile_agg, lc::SCAN_TILES)); s->allocs.push_back(b.tile_agg);
     CKC(cudaMemset(b.tile_agg, 0, sizeof(unsigned long long) * lc::SCAN_TILES));

@@ -47,6 +47,16 @@ __constant__ float c_diry[HULL_K];
 __constant__ float c_dir2x[HULL_K2];
 __constant__ float c_dir2y[HULL_K2];
 
+// Programmatic dependent launch (opt-in, LC_PDL=1): every frame kernel is launched with
+// programmaticStreamSerializationAllowed, lets its successor's blocks take the slots its own blocks free up
+// (launch_dependents), and touches no memory before its predecessor is complete and flushed (wait).  Meant to hide the
+// launch gaps between the kernels of a frame; inside the 16-frame graph it measured SLOWER (plaza125k 75.0 vs 64.0 us
+// per frame, plaza1m 279 vs 278 us), so it is off by default.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // demo.cpp:655-663 update_runs (Welford, all float)
 __device__ __forceinline__ void update_runs(Ctl* ctl, float overhead) {
     float ftotal = (float)(++ctl->total_num_done);
@@ -278,7 +288,10 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
     if (tid < HULL_K) ctl->ext[tid] = 0ull;
 }
 
-__global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__ P, Buffers b) { frame_begin_body(P, b); }
+__global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
+    frame_begin_body(P, b);
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // Uniform grid, phase 1: cell id + arrival rank per agent; directional extremes for candidate pruning.
@@ -290,6 +303,7 @@ __device__ __forceinline__ int cell_of(const Ctl* ctl, float x, float y) {
 }
 
 __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     const Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int n = P->n;
@@ -354,6 +368,7 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
 // spin cannot deadlock).
 // The extra last block folds k_bin's per-block directional extremes and builds the stage-1 pruning polygon.
 __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -413,7 +428,10 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
     __shared__ int s_off;
     const unsigned long long epoch = (unsigned long long)ctl->frame << 32;
     const int base = t * SCAN_TILE + tid * 4;
-    const int4 v = *reinterpret_cast<const int4*>(b.cell_count + base);  // zero beyond ncells (whole array is cleared)
+    const int4 v = *reinterpret_cast<const int4*>(b.cell_count + base);  // zero beyond ncells
+    // the histogram is dead once read: leave it cleared for the next frame's k_bin (cells beyond this frame's grid were
+    // never touched and are still zero from lc_create) — saves a 4 MB memset node per frame
+    *reinterpret_cast<int4*>(b.cell_count + base) = make_int4(0, 0, 0, 0);
     const int sum = v.x + v.y + v.z + v.w;
     int incl = sum;
 #pragma unroll
@@ -452,6 +470,7 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
 // Uniform grid, phase 2: scatter the state into cell order (counting sort).  Also: the replan gate of
 // ai.cpp:151-168 (needs the two lowest ids that want a replan) and comm-partner candidate compaction.
 __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int n = P->n;
@@ -586,6 +605,7 @@ __device__ void dd_cand_body(const Params* __restrict__ P, const Buffers& b);
 
 // k_refine; in domain mode the same block then exchanges the survivors with the other ranks (domain.cuh)
 __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt || (P->flags & 1u)) return;
     refine_body(P, b);
@@ -754,6 +774,7 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
 #define LC_PAIR_BLOCKS 12
 #endif
 __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     const Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -773,6 +794,7 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
 #define LC_FORCE_BLOCKS 10
 #endif
 __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int n = P->n;
@@ -1058,6 +1080,7 @@ __device__ __forceinline__ void block_reduce_store(const Buffers& b, bool valid,
 // S3b: collision push-out (physics.cpp:58-69 + BVH.cpp:106-120), Jacobi: every agent tests the others at their
 // integrated, not yet pushed positions; hits are applied in table (id) order.  Then physics.cpp:72-76.
 __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     const int n = P->n;
@@ -1339,42 +1362,59 @@ void upload_dirs() {
     cudaMemcpyToSymbol(c_dir2y, ey, sizeof ey);
 }
 
+// Kernel launch, optionally with the programmatic-dependent-launch attribute (pdl_enter): LC_PDL=1 in the environment.
+static bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("LC_PDL"); return e && e[0] == '1'; }();
+    return on;
+}
+template <class... KArgs, class... Args>
+static void launch(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev,
                   const SideStream* side) {
     // n = launch width (the capacity in domain mode; kernels read the live count from Params::n on the device)
     // ev (optional, FRAME_KERNELS + 1 events): per-kernel device timing for bench.py's roofline leg
     const bool dd = b.dd != nullptr;
-    cudaMemsetAsync(b.cell_count, 0, sizeof(int) * CELL_ALLOC, st);
+    const Params* cP = dP;
     if (ev) cudaEventRecord(ev[0], st);
     if (dd) {  // boundary exchange over peer memory (domain.cuh); its time is attributed to k_frame_begin's slot in `ev`
-        k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
-        k_dd_sync_begin<<<1, 1024, 0, st>>>(dP, b);   // publish + wait + merge + k_frame_begin's work
+        launch(k_dd_pack, cdiv(n, 256), 256, st, cP, b);
+        launch(k_dd_sync_begin, 1, 1024, st, dP, b);   // publish + wait + merge + k_frame_begin's work
     } else {
-        k_frame_begin<<<1, 1024, 0, st>>>(dP, b);
+        launch(k_frame_begin, 1, 1024, st, cP, b);
     }
     if (ev) cudaEventRecord(ev[1], st);
-    k_bin<<<cdiv(n, 1024), 1024, 0, st>>>(dP, b);
+    launch(k_bin, cdiv(n, 1024), 1024, st, cP, b);
     if (ev) cudaEventRecord(ev[2], st);
-    k_scan_hull<<<SCAN_TILES + 1, 1024, 0, st>>>(dP, b);
+    launch(k_scan_hull, SCAN_TILES + 1, 1024, st, cP, b);
     if (ev) cudaEventRecord(ev[3], st);
-    k_reorder<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    launch(k_reorder, cdiv(n, 256), 256, st, cP, b);
     if (ev) cudaEventRecord(ev[4], st);
     if (side && !ev) {  // (the profiled path stays serial so that the per-kernel times mean something)
         cudaEventRecord(side->fork, st);
         cudaStreamWaitEvent(side->st, side->fork, 0);
         k_refine<<<1, 1024, 0, side->st>>>(dP, b);  // + candidate all-gather in domain mode
         cudaEventRecord(side->join, side->st);
-        k_pairs<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+        launch(k_pairs, cdiv(n, 128), 128, st, cP, b);
         cudaStreamWaitEvent(st, side->join, 0);
+        k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);  // two predecessors: a plain (full) dependency on both
     } else {
-        k_refine<<<1, 1024, 0, st>>>(dP, b);
+        launch(k_refine, 1, 1024, st, cP, b);
         if (ev) cudaEventRecord(ev[5], st);
-        k_pairs<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+        launch(k_pairs, cdiv(n, 128), 128, st, cP, b);
+        if (ev) cudaEventRecord(ev[6], st);
+        launch(k_force, cdiv(n, 128), 128, st, cP, b);
     }
-    if (ev) cudaEventRecord(ev[6], st);
-    k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (ev) cudaEventRecord(ev[7], st);
-    k_collide<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+    launch(k_collide, cdiv(n, 128), 128, st, cP, b);
     if (ev) cudaEventRecord(ev[8], st);
     if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
 }

@@ -72,6 +72,7 @@ __device__ __forceinline__ void dd_route(const Params* P, float x, int role[3]) 
 }
 
 __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     DomainDev* dd = b.dd;
     if (!dd_active(P, ctl)) return;
@@ -160,6 +161,7 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
 
 // publish + wait + merge + S0 (k_frame_begin's work) in ONE single-block kernel: three launch gaps less per frame
 __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
+    pdl_enter();
     Ctl* ctl = b.ctl;
     DomainDev* dd = b.dd;
     if (!dd_active(P, ctl)) { frame_begin_body(P, b); return; }  // latches halt, like every later frame of a finished run
