@@ -92,6 +92,16 @@ def test_stencil_variants_same_result(stencil):
     lockstep(pos, goal, md, rng, m_cv, m_f, frames=40, check_every=8, stencil=stencil)
 
 
+def test_pair_list_overflow_falls_back_to_full_scan():
+    """A dense patch inside a sparse crowd: some agents collect more filter survivors than PAIR_CAP, k_force then scans
+    the whole disc for them; everybody else takes the list path.  Same result either way."""
+    pos, goal, md, rng = wl.plaza(3000, 110.0, seed=21, goal_range=30.0)
+    rs = np.random.RandomState(3)
+    pos[:300] = rs.uniform(-2.5, 2.5, (300, 2)).astype(np.float32)
+    m_cv, m_f = wl.weights(4)
+    lockstep(pos, goal, md, rng, m_cv, m_f, frames=30, check_every=5)
+
+
 def test_dense_crowd_collisions():
     """Agents packed below contact distance: exercises the overlap predicate and push-out (physics.cpp:23-36,
     BVH.cpp:106-120) with many simultaneous hits, and t = 0 / mag = 20 TTC forces."""
