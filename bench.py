@@ -401,7 +401,7 @@ def main():
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(name, {}).get("k_force_dram_bytes_per_launch")
+        traffic = json.load(open(tp)).get(name, {}).get("k_pairs_k_force_dram_bytes_per_launch")
     frame_ms = sum(prof.values())
     roofline = {"bound": "hbm", "kernel": "k_pairs+k_force", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "kernel_ms": prof, "kernel_share": (prof["k_pairs"] + prof["k_force"]) / frame_ms,

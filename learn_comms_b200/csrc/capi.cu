@@ -79,6 +79,7 @@ struct lc_sim {
     lc::DomainDev* ddev = nullptr;
     int* owned_dev = nullptr;
     std::vector<void*> ipc_opened;
+    bool dd_packed = false;  // the records of the first frame are in the mailboxes (k_dd_pack ran); later frames: k_collide
     // staging (device) for state exchange, pinned host mirror of Ctl
     float* stage = nullptr;
     size_t stage_floats = 0;
@@ -406,9 +407,18 @@ int32_t lc_set_weights(lc_sim* s, const float* m_cv, const float* m_f) {
     return upload_weights(s);
 }
 
+// domain mode: the first frame's records are packed by a kernel of its own (every later frame's by the previous k_collide)
+static void ensure_packed(lc_sim* s) {
+    if (s->ddev && !s->dd_packed) {
+        lc::launch_dd_pack(s->dP, s->n, s->b, s->st, &s->launches);
+        s->dd_packed = true;
+    }
+}
+
 int32_t lc_step(lc_sim* s, int32_t nframes) {
     SIM_ENTER(s);
     if (nframes < 0) return fail(LC_ERR_ARG, "lc_step: nframes < 0");
+    if (nframes > 0) ensure_packed(s);
     int left = nframes;
     while (left >= GRAPH_BATCH) {
         CK(cudaGraphLaunch(s->gexec[1], s->st));
@@ -516,6 +526,7 @@ int32_t lc_get_rng(lc_sim* s, uint32_t* rng_state) {
 
 int32_t lc_set_rng(lc_sim* s, uint32_t rng_state) {
     SIM_ENTER(s);
+    if (s->ddev) return fail(LC_ERR_STATE, "lc_set_rng: not available on a domain-decomposed crowd (the next frame's records are already packed)");
     int rc = read_ctl(s);
     if (rc) return rc;
     // rng0 is defined relative to frame 0; rebase so that lc_get_rng stays consistent
@@ -596,6 +607,7 @@ int32_t lc_step_profiled(lc_sim* s, int32_t nframes, float* ms_per_kernel) {
     SIM_ENTER(s);
     if (nframes < 0 || !ms_per_kernel) return fail(LC_ERR_ARG, "lc_step_profiled: bad argument");
     constexpr int K = lc::FRAME_KERNELS;
+    if (nframes > 0) ensure_packed(s);
     cudaEvent_t ev[K + 1];
     for (auto& e : ev) CK(cudaEventCreate(&e));
     double acc[K] = {0};

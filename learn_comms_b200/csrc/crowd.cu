@@ -1,13 +1,15 @@
 // Single-crowd frame kernels for sm_100a.  One frame of the reference loop (enginee/src/main.cpp:98-150)
 //   S0 demo::run -> S1 comm::run -> S2 ai::update_agents (LMP::calc_sum_force) -> S3 physics::simulate -> S4 all_sync
-// is seven launches on one stream:
+// is eight launches (k_refine on a side stream, beside k_pairs):
 //   k_frame_begin  S0 scoring + latch; derives this frame's grid from last frame's reductions      (1 block)
 //   k_bin          cell id + rank per agent (counting sort, phase 1); directional extremes          (n threads)
-//   k_scan_hull    exclusive scan of the cell histogram; candidate-pruning polygon                  (1 block)
+//   k_scan_hull    exclusive scan of the cell histogram; candidate-pruning polygon                  (tiles + 1 block)
 //   k_reorder      scatter the whole SoA state into cell order; replan gate; candidate compaction   (n threads)
 //   k_refine       second pruning stage of the comm-partner candidates                              (1 block)
-//   k_force        S1 + S2 + S3a fused: partner arg-max, message update, goal + TTC forces over the
-//                  3x3 (stencil) cells, leap-frog integrate; emits near-lists for the collision pass (n threads)
+//   k_pairs        S2a: pair filter over the forward half of the disc-shaped cell stencil, every unordered pair
+//                  once; survivors go into both agents' pair lists                                  (n threads)
+//   k_force        S1 + S2b + S3a fused: partner arg-max, message update, goal + TTC forces from the pair list,
+//                  leap-frog integrate; emits near-lists for the collision pass                     (n threads)
 //   k_collide      S3b collision push-out (Jacobi) + avg_velocity + next frame's reductions         (n threads)
 // FP32 CUDA cores only: the path is a gather / pair-test loop, not a dense contraction.
 #include "crowd.cuh"
@@ -1077,8 +1079,12 @@ __device__ __forceinline__ void block_reduce_store(const Buffers& b, bool valid,
     }
 }
 
+template <int NT>
+__device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const Buffers& b);  // domain.cuh
+
 // S3b: collision push-out (physics.cpp:58-69 + BVH.cpp:106-120), Jacobi: every agent tests the others at their
 // integrated, not yet pushed positions; hits are applied in table (id) order.  Then physics.cpp:72-76.
+template <bool DD>
 __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
@@ -1161,6 +1167,9 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
         }
     }
     block_reduce_store(b, valid && px == px && py == py, px, py, speed, lv_id);
+    // domain mode: route every owned agent's record of the NEXT frame to its owner / ghost hosts (reads back what this
+    // thread just stored: posf, vfh)
+    if (DD) dd_pack_body<128>(P, b);
 }
 
 // reductions of an arbitrary state (after lc_create / lc_set_state)
@@ -1385,8 +1394,7 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     const bool dd = b.dd != nullptr;
     const Params* cP = dP;
     if (ev) cudaEventRecord(ev[0], st);
-    if (dd) {  // boundary exchange over peer memory (domain.cuh); its time is attributed to k_frame_begin's slot in `ev`
-        launch(k_dd_pack, cdiv(n, 256), 256, st, cP, b);
+    if (dd) {  // boundary exchange over peer memory (domain.cuh): the records were packed by the previous k_collide
         launch(k_dd_sync_begin, 1, 1024, st, dP, b);   // publish + wait + merge + k_frame_begin's work
     } else {
         launch(k_frame_begin, 1, 1024, st, cP, b);
@@ -1414,9 +1422,15 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
         launch(k_force, cdiv(n, 128), 128, st, cP, b);
     }
     if (ev) cudaEventRecord(ev[7], st);
-    launch(k_collide, cdiv(n, 128), 128, st, cP, b);
+    if (dd) launch(k_collide<true>, cdiv(n, 128), 128, st, cP, b);
+    else launch(k_collide<false>, cdiv(n, 128), 128, st, cP, b);
     if (ev) cudaEventRecord(ev[8], st);
     if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
+}
+
+void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
+    k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);  // before the first frame only; afterwards k_collide packs
+    if (launches) *launches += 1;
 }
 
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {

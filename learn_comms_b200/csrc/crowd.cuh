@@ -162,7 +162,8 @@ DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 
 void upload_dirs();
 constexpr int FRAME_KERNELS = 8;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, pairs, force, collide
-constexpr int DD_KERNELS = 1;     // domain mode: dd_pack + dd_sync_begin (replaces frame_begin); the candidate exchange rides in k_refine
+constexpr int DD_KERNELS = 0;     // domain mode: dd_sync_begin replaces frame_begin, the pack rides in k_collide, the candidate exchange in k_refine
+void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);  // once, before the first frame
 // Side stream of a frame: k_refine (one block: second pruning stage and, in domain mode, the candidate exchange with the
 // peers) does not feed k_pairs, so the two run side by side (fork after k_reorder, join before k_force).
 struct SideStream { cudaStream_t st; cudaEvent_t fork, join; };

@@ -4,9 +4,11 @@
 // Included at the end of crowd.cu (same translation unit: it reuses the block reductions).
 //
 // Frame f on every rank (all inside the CUDA graph):
-//   k_dd_pack     owned agents -> records in the mailbox of their new owner (stay / migrate to an adjacent strip) and,
+//   (pack)        owned agents -> records in the mailbox of their new owner (stay / migrate to an adjacent strip) and,
 //                 as ghosts, of every adjacent rank whose strip they are within `dd_halo` of; at the time-out frame
-//                 the finish times of demo.cpp:691-700 are scattered into the scoring rank's id-indexed table
+//                 the finish times of demo.cpp:691-700 are scattered into the scoring rank's id-indexed table.
+//                 Done by the tail of the PREVIOUS frame's k_collide (dd_pack_body; one pass over the state and one
+//                 launch less per frame); kernel k_dd_pack only runs once, before the first frame
 //   k_dd_publish  folds the per-block reductions of the previous frame, writes this rank's DomainBlob (record counts,
 //                 max speed, not-done count, avg_velocity inputs, replan gate, done-events) into every peer, then
 //                 releases flag[rank] = f with a system-scope fence
@@ -71,8 +73,10 @@ __device__ __forceinline__ void dd_route(const Params* P, float x, int role[3]) 
     }
 }
 
-__global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, Buffers b) {
-    pdl_enter();
+// Body of the pack step, for a block of NT threads.  Runs at the END of k_collide (the agent's final position of frame f
+// is what decides its owner and ghost roles in frame f + 1), and as a kernel of its own before the very first frame.
+template <int NT>
+__device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const Buffers& b) {
     Ctl* ctl = b.ctl;
     DomainDev* dd = b.dd;
     if (!dd_active(P, ctl)) return;
@@ -84,7 +88,7 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
     const int par = frame & 1u;
     // Slot allocation keeps the agents' order (ballot prefix inside the warp, warp totals, one global atomicAdd per block
     // and destination): the records stay in last frame's cell order, which k_bin's run-aggregated counting relies on.
-    __shared__ int s_wcnt[3][8], s_base[3];
+    __shared__ int s_wcnt[3][NT / 32], s_base[3];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int role[3] = {0, 0, 0}, rank_in_blk[3] = {0, 0, 0};
     int4 mt = make_int4(0, 0, 0, 0);
@@ -108,7 +112,7 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
     __syncthreads();
     if (threadIdx.x < 3) {
         int tot = 0;
-        for (int w = 0; w < 8; ++w) { const int c = s_wcnt[threadIdx.x][w]; s_wcnt[threadIdx.x][w] = tot; tot += c; }
+        for (int w = 0; w < NT / 32; ++w) { const int c = s_wcnt[threadIdx.x][w]; s_wcnt[threadIdx.x][w] = tot; tot += c; }
         s_base[threadIdx.x] = tot ? atomicAdd(&dd->count[threadIdx.x], tot) : 0;
     }
     __syncthreads();
@@ -157,6 +161,11 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
                 __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
         }
     }
+}
+
+__global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, Buffers b) {
+    pdl_enter();
+    dd_pack_body<256>(P, b);
 }
 
 // publish + wait + merge + S0 (k_frame_begin's work) in ONE single-block kernel: three launch gaps less per frame
