@@ -158,11 +158,20 @@ __device__ void grid_from_reductions(const Params* P, Ctl* ctl) {
 // ---------------------------------------------------------------------------------------------------------
 // S0: demo::run (demo.cpp:665-702)
 __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, const Buffers& b) {
-    Ctl* ctl = b.ctl;
+    // The control block is worked on in shared memory and written back at the end: thread 0's serial part (Welford
+    // updates, grid set-up, resets) is a chain of ~60 dependent accesses, each an L2 round trip on the global copy.
+    // Nothing else runs on the stream while this kernel does (k_refine's side stream joined before k_force).
+    Ctl* const gctl = b.ctl;
+    __shared__ Ctl s_ctl;
     __shared__ int2 s_ev[EV_SORT_CAP];
     __shared__ float s_ft[1024];
     __shared__ int s_flag[1024];
     const int tid = threadIdx.x;
+    static_assert(sizeof(Ctl) % 4 == 0, "Ctl is copied word-wise");
+    for (int i = tid; i < (int)(sizeof(Ctl) / 4); i += blockDim.x)
+        reinterpret_cast<uint32_t*>(&s_ctl)[i] = reinterpret_cast<const uint32_t*>(gctl)[i];
+    __syncthreads();
+    Ctl* ctl = &s_ctl;
     const int n = P->n_ids;  // everything below that walks "all agents" is indexed by global id
     const bool dd = P->dd_world > 1;
     consume_block_reductions(ctl, b);
@@ -174,7 +183,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
     const uint32_t frame = ctl->frame + 1;
     __syncthreads();
     if (was_finished && !(P->flags & 2u)) {
-        if (tid == 0) ctl->halt = 1;
+        if (tid == 0) gctl->halt = 1;  // nothing else of the shared copy is kept: the block partials stay queued for lc_get_scores
         return;
     }
     const float fake_time = __fmul_rn(LC_DT, (float)frame);
@@ -288,6 +297,9 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         ctl->coll_hits = 0ull;
     }
     if (tid < HULL_K) ctl->ext[tid] = 0ull;
+    __syncthreads();
+    for (int i = tid; i < (int)(sizeof(Ctl) / 4); i += blockDim.x)
+        reinterpret_cast<uint32_t*>(gctl)[i] = reinterpret_cast<const uint32_t*>(&s_ctl)[i];
 }
 
 __global__ void __launch_bounds__(1024) k_frame_begin(const Params* __restrict__ P, Buffers b) {
