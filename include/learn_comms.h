@@ -71,7 +71,7 @@ int32_t lc_get_state(lc_sim* sim, float* pos, float* vel, float* vel_forehalf, f
                      float* local_goal, float* goal_dist, int32_t* num_done);
 int32_t lc_set_state(lc_sim* sim, const float* pos, const float* vel, const float* vel_forehalf, const float* c,
                      const float* facing, const float* local_goal, const float* goal_dist, const int32_t* num_done);
-int32_t lc_set_rng(lc_sim* sim, uint32_t rng_state);
+int32_t lc_set_rng(lc_sim* sim, uint32_t rng_state); /* Seeder::seed (Seeder.cpp:5-20); like lc_set_state, LC_ERR_STATE on a lc_dd_* handle */
 int32_t lc_get_rng(lc_sim* sim, uint32_t* rng_state);
 
 /* comm::terminate's two numbers (comm.cpp:136-142) + demo's running statistics (demo.cpp:650-663) */

@@ -2,7 +2,8 @@
 //     <build>/bin/comm_norender <scene> --seed <u64> --data <dir>
 // Same argument grammar as enginee/src/main.cpp:53-69 + io.cpp:63-125 (options --help, --record u, --data dir,
 // --split n, --seed u; one positional `scene`; misuse -> message + usage on stderr, exit 1), same files:
-// reads <project>data/<dir>/comms.config (comm.cpp:74-131), writes <project>data/<dir>/comms.result (comm.cpp:136-142).
+// reads <project>data/<dir>/comms.config (comm.cpp:74-131), writes <project>data/<dir>/comms.result (comm.cpp:136-142)
+// and <project>data/<dir>/agent_paths.csv (demo.cpp:678-684; LEARN_COMMS_NO_PATHS=1 skips it and runs the rollout in one call).
 // The frame loop itself (main.cpp:98-150) runs on the GPU through the C ABI; there is no CPU fallback: without a CUDA
 // device the process exits 1 with the library's error text.  Build: tools/build_cli.sh (g++ + liblearncomms.so).
 // PROJECT_DIR: compile-time in the reference (CMake); here -DLC_PROJECT_DIR or the LEARN_COMMS_PROJECT_DIR variable.
@@ -10,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
 #include <string>
 #include <vector>
 
@@ -95,7 +97,30 @@ int main(int argc, char** argv) {
     lc_sim* sim = nullptr;
     if (lc_create(&d, &sim) != LC_OK) lib_error("lc_create");
     int32_t frames = 0;
-    if (lc_run_to_completion(sim, &frames) != LC_OK) lib_error("lc_run_to_completion");
+    if (getenv("LEARN_COMMS_NO_PATHS")) {
+        if (lc_run_to_completion(sim, &frames) != LC_OK) lib_error("lc_run_to_completion");
+    } else {
+        // demo.cpp:616,678-684: one row per agent and frame, written by demo::run BEFORE the frame is simulated:
+        //   id,groupID(0),pos.x,pos.z,vel.x,vel.z,radius,dt*(frame-1)     (default ostream float formatting)
+        // id: the reference prints its ECS entity id; here the agent's table index + 1 (fix_paths.py:15-25 only uses
+        // it as a key).  Rows of a frame come in ascending id instead of the reference's hash-map order.
+        std::ofstream paths(data_dir + "/agent_paths.csv", std::ios::binary);
+        if (!paths) { fprintf(stderr, "cannot write %s/agent_paths.csv\n", data_dir.c_str()); return EXIT_FAILURE; }
+        std::vector<float> p(2 * (size_t)n), v(2 * (size_t)n);
+        const float dt = static_cast<float>(1.0 / 60.0);
+        for (;;) {
+            if (lc_get_state(sim, p.data(), v.data(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr) != LC_OK) lib_error("lc_get_state");
+            const float t = dt * static_cast<float>(frames);
+            for (int i = 0; i < n; ++i)
+                paths << (i + 1) << ",0," << p[2 * i] << "," << p[2 * i + 1] << "," << v[2 * i] << "," << v[2 * i + 1] << ","
+                      << d.radius << "," << t << "\n";
+            if (lc_step(sim, 1) != LC_OK) lib_error("lc_step");
+            ++frames;
+            int32_t fin = 0;
+            if (lc_finished(sim, &fin, nullptr) != LC_OK) lib_error("lc_finished");
+            if (fin) break;
+        }
+    }
     float avg_velocity = 0.f, group_time = 0.f, run_avg = 0.f, run_std = 0.f;
     int32_t total = 0;
     int rc = lc_get_scores(sim, &avg_velocity, &group_time, &run_avg, &run_std, &total);

@@ -65,3 +65,22 @@ def test_cli_result_file_matches_oracle(tmp_path, exe, scene, seed):
     _oracle.lib().canon_write_result(os.fsencode(str(ref)), sc["avg_velocity"], sc["group_time"])
     assert (d / "comms.result").read_text() == ref.read_text()
     assert pso.read_result(str(d / "comms.result")) == pso.read_result(str(ref))
+    # agent_paths.csv (demo.cpp:678-684): n rows per executed frame — id, group, pos, vel, radius, time stamp — the way
+    # fix_paths.py:15-25 reads them; the first frame's rows are the initial state, the last frame's the oracle's state
+    # before its final frame
+    rows = np.loadtxt(d / "agent_paths.csv", delimiter=",", dtype=np.float64)
+    n = pos.shape[0]
+    assert rows.shape == (o.frame * n, 8)
+    assert np.array_equal(rows[:n, 0], np.arange(1, n + 1)) and not rows[:, 1].any()
+    assert np.allclose(rows[:n, 2:4], pos, rtol=1e-5, atol=1e-6) and not rows[:n, 4:6].any()
+    assert np.allclose(rows[:, 6], 0.15) and rows[0, 7] == 0.0
+    assert np.allclose(rows[-1, 7], (o.frame - 1) / 60.0, rtol=1e-5)
+    o2 = _oracle.CanonSim(pos, goal, rc_cv, rc_f, max_duration=md, rng_state=rng, comm=exe == "comm_norender")
+    o2.step(o.frame - 1)
+    st = o2.state()
+    assert np.allclose(rows[-n:, 2:4], st["pos"], rtol=1e-5, atol=1e-6) and np.allclose(rows[-n:, 4:6], st["vel"], rtol=1e-5, atol=1e-6)
+    # same scores when the CSV is switched off (one lc_run_to_completion call instead of frame-by-frame stepping)
+    env = dict(os.environ, LEARN_COMMS_PROJECT_DIR=str(tmp_path), LEARN_COMMS_NO_PATHS="1")
+    first = (d / "comms.result").read_text()
+    r2 = subprocess.run([os.path.join(BIN, exe), str(scene), "--seed", str(seed), "--data", "run/iters/"], capture_output=True, text=True, env=env, timeout=600)
+    assert r2.returncode == 0 and (d / "comms.result").read_text() == first
