@@ -247,16 +247,17 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
                     const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
                     const float2 bb = mul2(bq, bq), ac = mul2(a, c);
                     const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
-                    // conservative "t > 5" filter (same derivation as crowd.cu scan_neighbours / DESIGN.md)
+                    // conservative "t > 5" filter (same derivation as crowd.cu scan_cells / DESIGN.md)
                     const float2 a5 = mul2(a, make_float2(5.f, 5.f));
                     const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));
                     const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
-                    const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
-                    const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
-                    const bool miss0 = (c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0;
-                    const bool miss1 = (c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1;
-                    const bool cand0 = !miss0 || c.x < K.near_c;
-                    const bool cand1 = ok1 && (!miss1 || c.y < K.near_c);
+                    // near_c > 0 (the collision reach exceeds the contact distance), so beyond it c > 0 holds and the tests
+                    // on the sign of c drop out of the general form (crowd.cu filter2); comparison polarity kept, so a NaN
+                    // anywhere still makes the pair a candidate
+                    const bool far0 = u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+                    const bool far1 = u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+                    const bool cand0 = c.x < K.near_c || !(bq.x > 0.f || disc.x < 0.f || far0);
+                    const bool cand1 = ok1 && (c.y < K.near_c || !(bq.y > 0.f || disc.y < 0.f || far1));
                     m |= ((unsigned)cand0 | ((unsigned)cand1 << 1)) << jj;
                 }
                 if ((unsigned)(i - jb) < 32u) m &= ~(1u << (i - jb));  // the self pair (m = dv = 0) always survives

@@ -234,7 +234,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         CKC(cudaEventCreateWithFlags(&s->side.join, cudaEventDisableTiming));
     }
     CKB(alloc_arrays(s, s->b.cur, n));
-    CKB(alloc_arrays(s, s->b.srt, n + annex));  // annex: comm-partner payload of other ranks' candidates (k_dd_cand)
+    CKB(alloc_arrays(s, s->b.srt, n + annex));  // annex: comm-partner payload of other ranks' candidates (dd_cand_body)
     lc::Buffers& b = s->b;
     CKC(dalloc(&b.posf, n)); s->allocs.push_back(b.posf);
     CKC(dalloc(&b.srt_pq, (size_t)2 * ((n + 1) / 2))); s->allocs.push_back(b.srt_pq);

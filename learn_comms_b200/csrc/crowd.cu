@@ -289,7 +289,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
             rho -= 0.1f;
             ctl->gate_rho2 = rho > 0.f ? rho * rho : -1.f;
         }
-        if (!dd) ctl->replan1 = ctl->replan2 = 0x7fffffff;  // domain mode: k_dd_wait merged the global gate
+        if (!dd) ctl->replan1 = ctl->replan2 = 0x7fffffff;  // domain mode: k_dd_sync_begin merged the global gate
         if (dd) {  // the ghost band was sized for the speed bound (domain.cuh); a wider cutoff would miss neighbours
             if (!(P->R + 10.f * vm * 1.001f + 0.01f + P->near_reach <= P->dd_halo) && !ctl->error) ctl->error = -5;
         }
@@ -528,7 +528,7 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
             if (loser != 0x7fffffff) atomicMin(&ctl->replan2, loser);
         }
     }
-    if (!(P->flags & 1u) && !(mt.y & META_GHOST)) {  // ghosts are published as candidates by their owner (k_dd_cand)
+    if (!(P->flags & 1u) && !(mt.y & META_GHOST)) {  // ghosts are published as candidates by their owner (dd_cand_body)
         // keep every agent that is not inside (by delta) the polygon of extreme agents: only those can be
         // the arg-max of comm.cpp:201-220 for any query (proof in DESIGN.md)
         const int ne = ctl->n_edges;
@@ -1455,7 +1455,7 @@ __global__ void __launch_bounds__(1024) k_consume_only(Buffers b) { consume_bloc
 
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches) {
     // domain mode: avg_velocity of the last frame is a cross-rank quantity; only fold the block partials into Ctl
-    // (lc_dd_get_partials reads them, the host merges the ranks) and leave the rest to the next k_dd_publish
+    // (lc_dd_get_partials reads them, the host merges the ranks) and leave the rest to the next k_dd_sync_begin
     if (b.dd) k_consume_only<<<1, 1024, 0, st>>>(b);
     else k_finalize<<<1, 1024, 0, st>>>(dP, b);
     if (launches) *launches += 1;

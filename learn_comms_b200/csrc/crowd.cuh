@@ -153,7 +153,7 @@ struct DomainLayout {             // byte offsets inside one rank's mailbox allo
 struct DomainDev {
     char* mbox[DD_MAX_WORLD];     // mailbox base of every rank (own allocation + peer mappings)
     DomainLayout lay;
-    int count[3];                 // records packed this frame for (rank-1, self, rank+1); cleared by k_dd_wait
+    int count[3];                 // records packed this frame for (rank-1, self, rank+1); cleared by k_dd_sync_begin once published
     int recv[3];                  // records waiting in this rank's regions (from the right, self, from the left)
     int replan[2];
     unsigned long long spin_timeout_ns;

@@ -9,15 +9,15 @@
 //                 the finish times of demo.cpp:691-700 are scattered into the scoring rank's id-indexed table.
 //                 Done by the tail of the PREVIOUS frame's k_collide (dd_pack_body; one pass over the state and one
 //                 launch less per frame); kernel k_dd_pack only runs once, before the first frame
-//   k_dd_publish  folds the per-block reductions of the previous frame, writes this rank's DomainBlob (record counts,
+//   (publish)     folds the per-block reductions of the previous frame, writes this rank's DomainBlob (record counts,
 //                 max speed, not-done count, avg_velocity inputs, replan gate, done-events) into every peer, then
 //                 releases flag[rank] = f with a system-scope fence
-//   k_dd_wait     spins until every peer's flag reads f, merges the blobs into Ctl (GLOBAL max speed, not-done count,
+//   (wait)        spins until every peer's flag reads f, merges the blobs into Ctl (GLOBAL max speed, not-done count,
 //                 replan gate, events on rank 0) and sets Params::n to the number of local records
-//                 (k_dd_publish / k_dd_wait / k_frame_begin are ONE single-block kernel, k_dd_sync_begin)
+//                 (publish + wait + k_frame_begin's work are ONE single-block kernel, k_dd_sync_begin)
 //   k_bin, k_scan_hull, k_reorder read the records in place (owners and ghosts mixed; meta bit2 tells them apart) and sort
 //                 them into cell order like a single-GPU crowd; there is no unpack copy
-//   k_dd_cand     publishes this rank's surviving comm-partner candidates (with the partner payload x() needs:
+//   (candidates)  dd_cand_body, the tail of k_refine: publishes this rank's surviving comm-partner candidates (with the partner payload x() needs:
 //                 pos, vel.x, c) to every peer, waits for theirs and appends them (comm.cpp:201-220 is a GLOBAL arg-max)
 //   k_force, k_collide: ghosts are advanced too — the collision pass needs their integrated positions — but never
 //                 counted; their next state always comes from the owner.
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
             total = 0;
         }
         dd->recv[0] = n_r; dd->recv[1] = n_self; dd->recv[2] = n_l;
-        dd->count[0] = dd->count[1] = dd->count[2] = 0;  // k_dd_publish (earlier in the stream) has consumed them
+        dd->count[0] = dd->count[1] = dd->count[2] = 0;  // the publish step above has consumed them
         P->n = total;
         ctl->vmax = vmax;
         ctl->nnd_acc = nnd;
