@@ -102,6 +102,18 @@ def test_pair_list_overflow_falls_back_to_full_scan():
     lockstep(pos, goal, md, rng, m_cv, m_f, frames=30, check_every=5)
 
 
+def test_far_apart_clusters_grid_cap():
+    """Two clusters 8 km apart (in x and y): cutoff-sized cells would need ~1e7 grid cells, so the grid set-up has to
+    widen the cells (first back to square, then doubling) until they fit the 2^20-cell table; same result."""
+    pa, ga, _, _ = wl.plaza(120, 30.0, seed=12, goal_range=20.0)
+    pb, gb, _, _ = wl.plaza(120, 30.0, seed=13, goal_range=20.0)
+    off = np.float32(8000.0)
+    pos = np.concatenate([pa, pb + off]).astype(np.float32)
+    goal = np.concatenate([ga, gb + off]).astype(np.float32)
+    m_cv, m_f = wl.weights(6)
+    lockstep(pos, goal, 20.0, 3, m_cv, m_f, frames=40, check_every=8)
+
+
 def test_dense_crowd_collisions():
     """Agents packed below contact distance: exercises the overlap predicate and push-out (physics.cpp:23-36,
     BVH.cpp:106-120) with many simultaneous hits, and t = 0 / mag = 20 TTC forces."""
