@@ -45,12 +45,16 @@ __device__ __forceinline__ void dd_st_flag(unsigned long long* p, unsigned long 
 }
 // spin until *p == want; false on time-out (a peer died or the hosts enqueued different frame counts)
 __device__ __forceinline__ bool dd_wait_flag(const unsigned long long* p, unsigned long long want, unsigned long long timeout_ns) {
+    // Poll back to back; look at the clock (and yield for a moment) only every 32 polls.  A 200 ns sleep per poll added
+    // up to half a microsecond of wake-up delay to each of the two waits of a frame (8 GPUs: 9.81e9 -> 9.88e9 with 32 ns).
     const unsigned long long t0 = dd_now_ns();
-    while (dd_ld_flag(p) != want) {
-        __nanosleep(200);
-        if (dd_now_ns() - t0 > timeout_ns) return false;
+    for (unsigned it = 1;; ++it) {
+        if (dd_ld_flag(p) == want) return true;
+        if ((it & 31u) == 0u) {
+            if (dd_now_ns() - t0 > timeout_ns) return false;
+            __nanosleep(32);
+        }
     }
-    return true;
 }
 
 __device__ __forceinline__ bool dd_active(const Params* P, const Ctl* ctl) {

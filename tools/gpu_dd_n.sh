@@ -9,4 +9,4 @@ import json
 t=open('gpurun_out/dd_plaza_n$N.json').read(); d=json.loads(t[t.index('{'):])
 print(d['n_gpus'], '%.3e'%d['value'], '%.4f'%d['ms_per_step'], 'e2e', d.get('e2e'), {k:round(v*1e3,1) for k,v in d['roofline']['kernel_ms'].items()})
 PY
-tail -3 gpurun_out/dd_plaza_n$N.err | grep -v "^\*\|OMP\|^$" | tail -5
+tail -n 3 gpurun_out/dd_plaza_n$N.err | grep -v "^\*\|OMP\|^$" | tail -5

@@ -21,4 +21,4 @@ for f in sorted(glob.glob('gpurun_out/scale_*.json')):
         print(f, d['n_gpus'], '%.3e'%d['value'], '%.4f'%d['ms_per_step'], d.get('scenario_evals_per_sec'), d['roofline'].get('kernel_ms'))
     except Exception as e: print(f,'ERR',e)
 PY
-tail -3 gpurun_out/scale_plaza_n*.err | grep -v "^\*\|OMP\|^$" | tail -12
+tail -q -n 3 gpurun_out/scale_plaza_n*.err | grep -v "^\*\|OMP\|^$" | tail -12
