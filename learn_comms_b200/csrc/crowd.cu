@@ -817,9 +817,11 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
     int not_done_after = 0;
     // The agent's own state is only loaded after the candidate pruning and the pair list (register pressure); ask L2 for
     // it now so that those loads do not each pay a DRAM round trip on the block's critical path.
+    auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
+    int np_early = 0, j_first = 0;  // pair count and first list entry: loads issued now, consumed after the pruning
     if (s < n) {
-        auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
-        pf(&b.pair_cnt[s]); pf(&b.pair_list[s]);
+        np_early = b.pair_cnt[s];
+        j_first = b.pair_list[s];   // (stale or uninitialised when the count is 0: clamped before use)
         pf(&b.srt.meta[s]); pf(&b.srt.goal[s]); pf(&b.srt.lgoal[s]); pf(&b.srt.facing[s]); pf(&b.srt.c4[s]); pf(&b.srt.vfh[s]);
     }  // (k_force 81 -> 77 us at 1 M agents)
     // Third pruning stage of the comm-partner candidates, per block: the 128 agents of a block are neighbours in cell
@@ -846,6 +848,10 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             atomicMin(&s_bb[0], mnx); atomicMin(&s_bb[1], mny); atomicMax(&s_bb[2], mxx); atomicMax(&s_bb[3], mxy);
         }
         __syncthreads();
+        if (valid && np_early > 0) {  // the first list entry has arrived by now: get its partner on the way
+            const int jc = min(max(j_first, 0), n - 1);
+            pf(&b.srt.pv[jc]); pf(&b.srt.meta[jc]);
+        }
         const float bx0 = ord2f(s_bb[0]), by0 = ord2f(s_bb[1]), bx1 = ord2f(s_bb[2]), by1 = ord2f(s_bb[3]);
         float lmax = 0.f;
         for (int k = threadIdx.x; k < nc; k += blockDim.x) {
@@ -886,11 +892,12 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
             ++cnt;
         };
-        const int np = b.pair_cnt[s];
+        const int np = np_early;
         if (np <= PAIR_CAP) {  // survivors of k_pairs' filter (in no particular order: hits and near list are sorted by id)
             const size_t stride = (size_t)P->cap;
             for (int k = 0; k < np; ++k)
-                pair_eval<true>(b, s, b.pair_list[k * stride + s], px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, hit);
+                pair_eval<true>(b, s, k == 0 ? j_first : b.pair_list[k * stride + s], px, py, vx, vy, P->RR, P->near_c, n_near,
+                                n_overlap, hit);
         } else {
             scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, hit);
         }
