@@ -518,7 +518,10 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     }
     b.srt.goal[s] = g;
     b.srt.meta[s] = mt;
-    b.slot_of_id[mt.x] = s;
+    // The id -> slot table is a scattered 4-byte store per agent (a 32-byte sector each).  Its only reader inside the
+    // frame loop is the time-out walk of the NEXT k_frame_begin (demo.cpp:691-700, id order); lc_set_state rebuilds it
+    // in k_snapshot.  So it is written only by the frame before the time-out one (and every frame after it).
+    if (__fmul_rn(LC_DT, (float)(ctl->frame + 1u)) > P->max_duration) b.slot_of_id[mt.x] = s;
     // ai.cpp:154,161-163: need_replan = done && goal_dist > 1 (wall-free: the lost_frames clause cannot fire)
     if ((mt.y & 1) && P->dd_world <= 1) {
         float gd = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
@@ -1347,7 +1350,9 @@ __global__ void __launch_bounds__(256) k_snapshot(const Params* __restrict__ P, 
     b.srt.lgoal[i] = b.cur.lgoal[i];
     b.srt.facing[i] = b.cur.facing[i];
     b.srt.c4[i] = b.cur.c4[i];
-    b.srt.meta[i] = b.cur.meta[i];
+    const int4 mt = b.cur.meta[i];
+    b.srt.meta[i] = mt;
+    b.slot_of_id[mt.x] = i;  // k_reorder does not maintain the table (see there)
 }
 
 __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {

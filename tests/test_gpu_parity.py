@@ -71,6 +71,30 @@ def test_run_to_completion_matches_stepping():
     assert a.scores() == o.scores()
 
 
+def test_timeout_penalty_and_state_round_trip():
+    """A rollout that ends through the time-out penalty (demo.cpp:691-700: finish times of the not-done agents folded in
+    id order — the only in-loop reader of the id -> slot table, which k_reorder maintains only around that frame), with
+    a get_state / set_state round trip (rebuilds the table) in the middle: frames, scores and state equal the oracle's."""
+    pos, goal, _, rng = wl.plaza(1500, 90.0, seed=33, goal_range=60.0)
+    m_cv, m_f = wl.weights(13)
+    md = 2.5
+    g = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    g.step(70)
+    o.step(70)
+    st = g.state()
+    g.set_state(**st)
+    g.step(40)
+    o.step(40)
+    assert_state_equal(g.state(), o.state(), "after the round trip")
+    frames = g.run_to_completion()
+    o.step(10 ** 6)
+    assert frames == o.frame and 148 <= frames <= 152  # dt * frame first exceeds 2.5 s in float arithmetic
+    gs, os_ = g.scores(), o.scores()
+    assert gs == os_, (gs, os_)
+    assert_state_equal(g.state(), o.state(), "final")
+
+
 def test_nocomm_flavour():
     """nocomm_norender (main.cpp:130-132): comm::run compiled out."""
     pos, goal, md, rng = lcb.scene(4, 0)
