@@ -259,6 +259,10 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(dalloc(&b.ev_by_id, n_ids)); s->allocs.push_back(b.ev_by_id);
     CKC(dalloc(&b.partner_id, n_ids)); s->allocs.push_back(b.partner_id);
     CKC(dalloc(&b.nbr_cnt, n_ids)); s->allocs.push_back(b.nbr_cnt);
+    CKC(dalloc(&b.diag_partner, n)); s->allocs.push_back(b.diag_partner);
+    CKC(dalloc(&b.diag_cnt, n)); s->allocs.push_back(b.diag_cnt);
+    CKC(cudaMemset(b.diag_partner, 0xff, sizeof(int) * n));
+    CKC(cudaMemset(b.diag_cnt, 0, sizeof(int) * n));
     b.list_cap = 0;
     b.nbr_list = nullptr;
     if (d->flags & LC_FLAG_DEBUG_LISTS) {
@@ -556,6 +560,7 @@ int32_t lc_get_scores(lc_sim* s, float* avg_velocity, float* group_time, float* 
 
 int32_t lc_get_partners(lc_sim* s, int32_t* partner) {
     SIM_ENTER(s);
+    lc::launch_get_diag(s->dP, s->n, s->b, s->st, &s->launches);
     CK(cudaMemcpyAsync(partner, s->b.partner_id, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
@@ -563,6 +568,7 @@ int32_t lc_get_partners(lc_sim* s, int32_t* partner) {
 
 int32_t lc_get_neighbor_counts(lc_sim* s, int32_t* count) {
     SIM_ENTER(s);
+    lc::launch_get_diag(s->dP, s->n, s->b, s->st, &s->launches);
     CK(cudaMemcpyAsync(count, s->b.nbr_cnt, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;

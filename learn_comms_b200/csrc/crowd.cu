@@ -939,7 +939,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         int4 mt = b.srt.meta[s];
         const bool owned = !(mt.y & META_GHOST);  // ghosts are advanced too (the collision pass needs their integrated
                                                   // position) but never counted: their owner does that
-        if (owned) b.nbr_cnt[id] = cnt;
+        b.diag_cnt[s] = cnt;  // slot-indexed (coalesced); lc_get_neighbor_counts translates to ids (k_get_diag)
         if (n_near > MAX_NEAR) atomicAdd(&ctl->near_overflow, 1);
         b.near_cnt[s] = n_near;
         if (n_overlap && owned) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
@@ -979,7 +979,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             if (cand == s_cand) for (int k = 0; k < ncand; ++k) consider(s_cand[k]);
             else for (int k = 0; k < ncand; ++k) consider(__ldg(&cand[k]));
             if (best_id < 0) atomicCAS(&ctl->error, 0, -3);  // comm.cpp:273-285: null partner is UB in the reference
-            if (owned) b.partner_id[id] = best_id;
+            b.diag_partner[s] = best_id;  // slot-indexed; lc_get_partners translates to ids (k_get_diag)
             const float4 pj = __ldg(&b.srt.pv[best_slot]);
             const float4 cj = __ldg(&b.srt.c4[best_slot]);
             // comm.cpp:144-192 x(): COSINE_REL + PROX + SOFTSIGN_GOAL; partner (x, y) of a vec3 = (x, 0): quirk Q2
@@ -1261,6 +1261,18 @@ __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P,
     if (num_done) num_done[id] = mt.y & 1;
 }
 
+// Diagnostics of the last frame (comm partner, |{j : ttc_ij <= 5}|) are kept per slot by k_force — an id-indexed store
+// is a 32-byte sector per agent and frame — and brought into id order only when the host asks for them.  Ids this rank
+// does not own keep whatever the table held.
+__global__ void __launch_bounds__(256) k_get_diag(const Params* __restrict__ P, Buffers b) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P->n) return;
+    const int4 mt = b.cur.meta[s];
+    if (mt.y & META_GHOST) return;
+    b.partner_id[mt.x] = b.diag_partner[s];
+    b.nbr_cnt[mt.x] = b.diag_cnt[s];
+}
+
 // domain mode, host-facing shard: (id, pos, vel) of the agents this rank owns, compacted (order arbitrary)
 __global__ void __launch_bounds__(256) k_get_owned(const Params* __restrict__ P, Buffers b, int* ids, float2* pos, float2* vel,
                                                     int* count) {
@@ -1336,6 +1348,10 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
     b.cur.facing[i] = fc;
     b.cur.c4[i] = c4;
     b.cur.meta[i] = mt;
+    if (!init) {  // slot == id from here on: the per-slot diagnostics follow (launch_set_state ran k_get_diag first)
+        b.diag_partner[i] = b.partner_id[i];
+        b.diag_cnt[i] = b.nbr_cnt[i];
+    }
 }
 
 // snapshot cur -> srt (posf folded into pv) so k_set_state can permute in place
@@ -1469,6 +1485,11 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
 }
 
+void launch_get_diag(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
+    k_get_diag<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
+    if (launches) *launches += 1;
+}
+
 void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
     k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);  // before the first frame only; afterwards k_collide packs
     if (launches) *launches += 1;
@@ -1502,8 +1523,9 @@ void launch_set_state(const Params* dP, int n, const Buffers& b, const float2* p
                       const float* goal_dist, const int* num_done, const float2* goal, const float* min_time, int init,
                       cudaStream_t st, long long* launches, const int* ids) {
     if (!init) {
+        k_get_diag<<<cdiv(n, 256), 256, 0, st>>>(dP, b);  // per-slot diagnostics -> id order, before the slots change
         k_snapshot<<<cdiv(n, 256), 256, 0, st>>>(dP, b);
-        if (launches) *launches += 1;
+        if (launches) *launches += 2;
     }
     k_set_state<<<cdiv(n, 256), 256, 0, st>>>(dP, b, pos, vel, vfh, c3, facing, lgoal, goal_dist, num_done, goal,
                                               min_time, init, ids);

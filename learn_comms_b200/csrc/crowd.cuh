@@ -122,8 +122,10 @@ struct Buffers {
     int* pair_list;    // [PAIR_CAP][n] by slot: partner slots, entry k of all agents contiguous
     int2* events;      // (id, min_time bits) of agents that became done this frame
     float* ev_by_id;   // [n] per-id event path (NaN = none)
-    int* partner_id;   // [n] by id (diagnostic)
-    int* nbr_cnt;      // [n] by id (diagnostic)
+    int* partner_id;   // [n] by id (diagnostic; filled from diag_partner by k_get_diag when the host asks)
+    int* nbr_cnt;      // [n] by id (diagnostic; filled from diag_cnt by k_get_diag)
+    int* diag_partner; // [cap] by slot: comm partner id of the last frame (k_force)
+    int* diag_cnt;     // [cap] by slot: interacting neighbours of the last frame (k_force)
     int* nbr_list;     // [n][list_cap] by id (LC_FLAG_DEBUG_LISTS)
     int list_cap;
     Ctl* ctl;
@@ -163,6 +165,7 @@ DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);
 void upload_dirs();
 constexpr int FRAME_KERNELS = 8;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, pairs, force, collide
 constexpr int DD_KERNELS = 0;     // domain mode: dd_sync_begin replaces frame_begin, the pack rides in k_collide, the candidate exchange in k_refine
+void launch_get_diag(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);  // once, before the first frame
 // Side stream of a frame: k_refine (one block: second pruning stage and, in domain mode, the candidate exchange with the
 // peers) does not feed k_pairs, so the two run side by side (fork after k_reorder, join before k_force).
