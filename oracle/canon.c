@@ -91,6 +91,7 @@ struct canon_sim {
 static inline int is_done(const canon_sim* s, int i) { return s->num_done[i] == PLAN_SIZE; } /* Agent.h:22-24 */
 
 canon_sim* canon_create(const canon_desc* d) {
+    if (d->n_walls > 0) return NULL; /* walled rollouts need the planner (GMP.cpp), not restated yet */
     canon_sim* s = (canon_sim*)calloc(1, sizeof(*s));
     int n = d->n;
     s->n = n;
@@ -694,6 +695,188 @@ int32_t canon_set_order(canon_sim* s, const int32_t* order, int32_t gauss_seidel
     if (order) memcpy(s->order, order, sizeof(int32_t) * (size_t)s->n);
     s->gauss_seidel = gauss_seidel;
     return 0;
+}
+
+/* ---------- static walls: the geometry behind SURVEY §8 rows a10 / a14 / a16 (walled scenes, §8f-2) ----------
+ * Pinned bit for bit against the reference's own BoundVolume.cpp / LMP.cpp / PRM.cpp (oracle/ref/geom_main.cpp,
+ * tests/golden/wall_geometry.npz).  Not yet wired into the frame loop: canon_create refuses n_walls > 0 rollouts
+ * because the planner (PRM + A*, GMP.cpp) is not restated. */
+
+/* BoundVolume.cpp:160-188 Rect::intersect */
+float canon_rect_intersect(const canon_rect* r, const float* bo, const float* v) {
+    float tmin = 0.0f, tmax = FLT_MAX;
+    float rmin[2] = {r->ox - r->w / 2, r->oy - r->h / 2};
+    float rmax[2] = {r->ox + r->w / 2, r->oy + r->h / 2};
+    for (int i = 0; i < 2; ++i) {
+        if (fabs(v[i]) < 0.0000001f) {
+            if (bo[i] < rmin[i] || bo[i] > rmax[i]) return FLT_MAX;
+        } else {
+            float near = (rmin[i] - bo[i]) / v[i];
+            float far = (rmax[i] - bo[i]) / v[i];
+            if (near > far) { float t = near; near = far; far = t; }
+            tmin = (tmin < near) ? near : tmin; /* std::max(tmin, near) */
+            tmax = (far < tmax) ? far : tmax;   /* std::min(tmax, far) */
+            if (tmin > tmax) return FLT_MAX;
+        }
+    }
+    return tmin;
+}
+
+/* BoundVolume.cpp:131-155 Rect::line_of_sight (1 = segment a-b misses the rect) */
+int32_t canon_rect_line_of_sight(const canon_rect* r, const float* a, const float* b) {
+    v2 rmin = V2(r->ox - r->w / 2, r->oy - r->h / 2);
+    v2 rmax = V2(r->ox + r->w / 2, r->oy + r->h / 2);
+    v2 e = sub2(rmax, rmin);
+    v2 m = sub2(sub2(add2(V2(a[0], a[1]), V2(b[0], b[1])), rmin), rmax);
+    v2 d = sub2(V2(b[0], b[1]), V2(a[0], a[1]));
+    float adx = (float)fabs(d.x);
+    if ((float)fabs(m.x) > e.x + adx) return 1;
+    float ady = (float)fabs(d.y);
+    if ((float)fabs(m.y) > e.y + ady) return 1;
+    adx += 0.0000001f;
+    ady += 0.0000001f;
+    if ((float)fabs(m.x * d.y - m.y * d.x) > e.x * ady + e.y * adx) return 1;
+    return 0;
+}
+
+/* BoundVolume.cpp:76-98 Circ::line_of_sight */
+int32_t canon_circ_line_of_sight(const float* o, float r, const float* start, const float* end) {
+    v2 d = sub2(V2(end[0], end[1]), V2(start[0], start[1]));
+    v2 m = sub2(V2(start[0], start[1]), V2(o[0], o[1]));
+    float b = dot2(m, d);
+    float c = dot2(m, m) - r * r;
+    if (c > 0.f && b > 0.f) return 1;
+    float a = dot2(d, d);
+    float discrim = b * b - a * c;
+    if (discrim < 0.f) return 1;
+    float t = (-b - sqrtf(discrim)) / a;
+    if (t * t > a) return 1;
+    return 0;
+}
+
+/* BoundVolume.cpp:102-122 Circ::intersect on its own (ttc_circ_circ above folds the LMP::ttc wrapper in) */
+static inline float circ_intersect(v2 co, float r, v2 o, v2 d) {
+    v2 m = sub2(o, co);
+    float a = dot2(d, d);
+    float b = dot2(m, d);
+    float c = dot2(m, m) - r * r;
+    if (c > 0.f && b > 0.f) return FLT_MAX;
+    float discrim = b * b - a * c;
+    if (discrim < 0.f) return FLT_MAX;
+    float t = (-b - sqrtf(discrim)) / a;
+    if (t < 0.f) return 0.f;
+    return t;
+}
+
+/* LMP.cpp:13-34 ttc (Circ vs Rect branch) + :64-82 ttc_(Circ,Rect): min over the two extruded rects and four corner
+ * discs; jv = 0 for a wall (LMP.cpp:314-315) */
+float canon_ttc_circ_wall(const float* o, float r, const float* iv, const canon_rect* j) {
+    canon_rect h = {j->ox, j->oy, 2 * r + j->w, j->h};
+    canon_rect v = {j->ox, j->oy, j->w, 2 * r + j->h};
+    v2 corner[4] = {V2(j->ox + j->w / 2, j->oy + j->h / 2), V2(j->ox - j->w / 2, j->oy + j->h / 2),
+                    V2(j->ox + j->w / 2, j->oy - j->h / 2), V2(j->ox - j->w / 2, j->oy - j->h / 2)};
+    float dv[2] = {iv[0] - 0.f, iv[1] - 0.f};
+    float t_min = FLT_MAX, t;
+    t = canon_rect_intersect(&h, o, dv); if (t < t_min) t_min = t;
+    t = canon_rect_intersect(&v, o, dv); if (t < t_min) t_min = t;
+    for (int k = 0; k < 4; ++k) {
+        t = circ_intersect(corner[k], r, V2(o[0], o[1]), V2(dv[0], dv[1]));
+        if (t < t_min) t_min = t;
+    }
+    if (t_min < 0 || isnan(t_min)) return FLT_MAX;
+    return t_min;
+}
+
+/* LMP.cpp:307-319: one iteration of the statics loop of calc_sum_force (distance gate on length2 > 5 -- quirk Q10 --
+ * then ttc > 5, then ttc_forces(d, bv, bbv, ttc) :128-136).  Returns 1 and the force if the wall interacts. */
+int32_t canon_wall_force(const float* o, float r, const float* vel, const canon_rect* w, float* f) {
+    f[0] = f[1] = 0.f;
+    if (len2_2(sub2(V2(w->ox, w->oy), V2(o[0], o[1]))) > 5.0) return 0;
+    double ttc = canon_ttc_circ_wall(o, r, vel, w);
+    if (ttc > 5.0) return 0;
+    float tf = (float)ttc;
+    v2 dir = sub2(add2(V2(o[0], o[1]), V2(vel[0] * tf, vel[1] * tf)), V2(w->ox, w->oy));
+    v2 F = ttc_forces_(tf, dir);
+    f[0] = F.x; f[1] = F.y;
+    return 1;
+}
+
+/* BoundVolume.cpp:209-211 closest_circ_point */
+static inline v2 closest_circ_point(v2 o, v2 co, float r) { return add2(mul2s(normalize2(sub2(o, co)), r), co); }
+
+/* BoundVolume.cpp:213-230 closest_aabb_point: clamp into the rect; a point already inside goes to the nearer edge pair */
+static inline v2 closest_aabb_point(v2 o, const canon_rect* w) {
+    v2 closest = o;
+    closest.x = glm_clamp(closest.x, w->ox - w->w / 2, w->ox + w->w / 2);
+    closest.y = glm_clamp(closest.y, w->oy - w->h / 2, w->oy + w->h / 2);
+    if (closest.x == o.x && closest.y == o.y) {
+        v2 in = sub2(o, V2(w->ox, w->oy));
+        if (fabsf(in.x) > fabsf(in.y)) closest.x = w->ox + (in.x > 0 ? +w->w : -w->w) / 2;
+        else closest.y = w->oy + (in.y > 0 ? +w->h : -w->h) / 2;
+    }
+    return closest;
+}
+
+/* BVH.cpp:121-130 leaf normal for a Rect leaf: on_bv - on_q */
+static inline v2 circ_wall_normal(v2 qo, float r, const canon_rect* w) {
+    v2 on_q = closest_circ_point(V2(w->ox, w->oy), qo, r);
+    return sub2(closest_aabb_point(on_q, w), on_q);
+}
+
+/* BoundVolume.cpp:125-127 Rect::collides, :196-201 circ_rect_collider, BVH.cpp:121-130.  Returns 1 and the push
+ * vector on contact. */
+int32_t canon_circ_wall_hit(const float* o, float r, const canon_rect* w, float* away) {
+    v2 qo = V2(o[0], o[1]), ro = V2(w->ox, w->oy);
+    v2 on_q = closest_circ_point(ro, qo, r);
+    int q_has_ro = len2_2(sub2(ro, qo)) <= r * r;
+    int r_has_onq = fabs(on_q.x - w->ox) <= w->w / 2 && fabs(on_q.y - w->oy) <= w->h / 2;
+    away[0] = away[1] = 0.f;
+    if (!(q_has_ro || r_has_onq)) return 0;
+    v2 n = circ_wall_normal(qo, r, w);
+    away[0] = n.x;
+    away[1] = n.y;
+    return 1;
+}
+
+/* PRM.cpp:133-156,169-173 Cspace2d: the agent's bounding square (2r x 2r) summed into every wall
+ * (Rect::minkowski_sum_(Rect*), BoundVolume.cpp:55-58), line of sight = every inflated wall is missed */
+int32_t canon_cspace_line_of_sight(const canon_rect* walls, int32_t n_walls, float agent_r, const float* a,
+                                   const float* b) {
+    for (int32_t k = 0; k < n_walls; ++k) {
+        canon_rect infl = {walls[k].ox, walls[k].oy, 2 * agent_r + walls[k].w, 2 * agent_r + walls[k].h};
+        if (!canon_rect_line_of_sight(&infl, a, b)) return 0;
+    }
+    return 1;
+}
+
+/* the record layout of oracle/ref/geom_main.cpp (9 floats in, 12 words out), so one call checks a whole fixture */
+void canon_wall_geometry_batch(int32_t K, const float* in, void* out) {
+    for (int32_t k = 0; k < K; ++k) {
+        const float* p = in + (size_t)k * 9;
+        union { float f; int32_t i; } w[12];
+        canon_rect rect = {p[0], p[1], p[2], p[3]};
+        const float* a = p + 4;
+        const float* b = p + 6;
+        float r = p[8], away[2], F[2];
+        memset(w, 0, sizeof(w));
+        w[0].f = canon_rect_intersect(&rect, a, b);
+        w[1].i = canon_rect_line_of_sight(&rect, a, b);
+        w[2].i = canon_circ_line_of_sight(p, r, a, b);
+        w[3].f = canon_ttc_circ_wall(a, r, b, &rect);
+        w[4].i = canon_circ_wall_hit(a, r, &rect, away);
+        {   /* the harness evaluates the push vector whether or not the collider fires */
+            v2 nrm = circ_wall_normal(V2(a[0], a[1]), r, &rect);
+            away[0] = nrm.x;
+            away[1] = nrm.y;
+        }
+        w[5].f = away[0];
+        w[6].f = away[1];
+        w[7].i = canon_cspace_line_of_sight(&rect, 1, r, a, b);
+        w[8].i = canon_wall_force(a, r, b, &rect, F);
+        w[9].f = F[0];
+        w[10].f = F[1];
+        memcpy((char*)out + (size_t)k * 48, w, 48);
+    }
 }
 
 /* ---------- scene catalogue, wall-free scenes only (demo.cpp:48-104,141-206,356-373) ---------- */

@@ -82,6 +82,17 @@ uint32_t canon_lcg_next(uint32_t x);
 uint32_t canon_lcg_seed(uint64_t seed);
 float canon_uniform(uint32_t x_after_draw, float a, float b);
 
+/* static-wall geometry, pinned against the reference's BoundVolume.cpp / LMP.cpp /
+ * PRM.cpp through oracle/ref/geom_main.cpp.  2-vectors are float[2] = (x, z). */
+float canon_rect_intersect(const canon_rect* r, const float* bo, const float* v);              /* BoundVolume.cpp:160-188 */
+int32_t canon_rect_line_of_sight(const canon_rect* r, const float* a, const float* b);        /* BoundVolume.cpp:131-155 */
+int32_t canon_circ_line_of_sight(const float* o, float r, const float* start, const float* end); /* BoundVolume.cpp:76-98 */
+float canon_ttc_circ_wall(const float* o, float r, const float* iv, const canon_rect* j);     /* LMP.cpp:13-34,64-82 */
+int32_t canon_wall_force(const float* o, float r, const float* vel, const canon_rect* w, float* f); /* LMP.cpp:307-319,128-136 */
+int32_t canon_circ_wall_hit(const float* o, float r, const canon_rect* w, float* away);       /* BVH.cpp:121-130 */
+int32_t canon_cspace_line_of_sight(const canon_rect* walls, int32_t n_walls, float agent_r, const float* a,
+                                   const float* b);                                           /* PRM.cpp:133-156,169-173 */
+
 /* scene catalogue (demo.cpp:141-511): fills pos/goal for wall-free scenes; returns n (0 = unsupported).
  * rng_state is advanced by construction-time draws (scene 12). */
 int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration,

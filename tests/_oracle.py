@@ -63,12 +63,31 @@ def lib():
         L.canon_scene.restype = C.c_int32
         L.canon_read_config.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p]
         L.canon_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
+        L.canon_wall_geometry_batch.argtypes = [C.c_int32, C.c_void_p, C.c_void_p]
+        for fn in ("canon_rect_intersect", "canon_ttc_circ_wall"):
+            getattr(L, fn).restype = C.c_float
+        L.canon_rect_intersect.argtypes = [C.POINTER(Rect), C.c_void_p, C.c_void_p]
+        L.canon_rect_line_of_sight.argtypes = [C.POINTER(Rect), C.c_void_p, C.c_void_p]
+        L.canon_circ_line_of_sight.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
+        L.canon_ttc_circ_wall.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.POINTER(Rect)]
+        L.canon_wall_force.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.POINTER(Rect), C.c_void_p]
+        L.canon_circ_wall_hit.argtypes = [C.c_void_p, C.c_float, C.POINTER(Rect), C.c_void_p]
+        L.canon_cspace_line_of_sight.argtypes = [C.c_void_p, C.c_int32, C.c_float, C.c_void_p, C.c_void_p]
         _LIB = L
     return _LIB
 
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def wall_geometry(records):
+    """O-canon's static-wall functions on (K, 9) records {rect; a; b; r} -> (K, 12) uint32 words, in the layout of
+    oracle/ref/geom_main.cpp."""
+    rec = np.ascontiguousarray(records, np.float32)
+    out = np.zeros((len(rec), 12), np.uint32)
+    lib().canon_wall_geometry_batch(len(rec), _p(rec), _p(out))
+    return out
 
 
 def scene(scene_id, seed=0):

@@ -11,8 +11,23 @@ OREF = os.path.join(ROOT, "oracle", "_ref", "oref")
 OREF_NOCOMM = os.path.join(ROOT, "oracle", "_ref", "oref_nocomm")
 
 
+OREF_GEOM = os.path.join(ROOT, "oracle", "_ref", "oref_geom")
+
+
 def available():
     return os.path.exists(OREF)
+
+
+def geom_available():
+    return os.path.exists(OREF_GEOM)
+
+
+def run_geom(records):
+    """oracle/ref/geom_main.cpp: (K, 9) float32 records -> (K, 12) uint32 words of the reference's wall geometry."""
+    rec = np.ascontiguousarray(records, np.float32)
+    blob = np.int32(len(rec)).tobytes() + rec.tobytes()
+    out = subprocess.run([OREF_GEOM], input=blob, stdout=subprocess.PIPE, check=True).stdout
+    return np.frombuffer(out, np.uint32).reshape(len(rec), 12).copy()
 
 
 def write_config(path, m_cv, m_f):

@@ -11,7 +11,11 @@ import pytest
 import _oracle
 import _oref
 
-GOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scene*.npz")))
+WALLS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "wall_geometry.npz")
+WALL_WORDS = ("Rect::intersect", "Rect::line_of_sight", "Circ::line_of_sight", "LMP::ttc(Circ,Rect)",
+              "circ_rect_collider", "normal.x", "normal.y", "Cspace2d::line_of_sight", "wall interacts", "force.x",
+              "force.y", "pad")
 KEYS = ("pos", "vel", "vfh", "c", "facing", "local_goal", "goal_dist", "num_done")
 
 
@@ -26,7 +30,7 @@ def canon_from_golden(g):
 
 
 def test_fixtures_present():
-    assert len(GOLD) >= 7
+    assert len(GOLD) >= 7 and os.path.exists(WALLS)
 
 
 @pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p)[:-4] for p in GOLD])
@@ -109,3 +113,35 @@ def test_canonical_order_score_gap_is_small():
         o.step(10 ** 6)
         gaps.append(abs(o.scores()["group_time"] - r["scores"]["group_time"]) / r["scores"]["group_time"])
     assert max(gaps) < 0.25, gaps
+
+
+def _assert_wall_words_equal(mine, ref):
+    for col, name in enumerate(WALL_WORDS):
+        bad = np.nonzero(mine[:, col] != ref[:, col])[0]
+        assert bad.size == 0, "%s differs from the reference in %d records, first %d" % (name, bad.size, bad[0])
+
+
+def test_wall_geometry_matches_reference_golden():
+    """Static-wall geometry (BoundVolume.cpp:76-230, LMP.cpp:64-82,128-136,307-319,
+    BVH.cpp:121-130, PRM.cpp:133-173): O-canon equals the reference's own functions bit for bit, NaN patterns included,
+    on the 8 000 seeded records of tools/make_golden_walls.py."""
+    g = np.load(WALLS)
+    ref = g["words"]
+    f = ref.view(np.float32)
+    # the fixture exercises every branch: hits and misses, contacts, blocked and free sight lines, NaN normals
+    assert (f[:, 0] < 3e38).sum() > 1000 and (f[:, 0] > 3e38).sum() > 1000
+    assert ref[:, 4].sum() > 500 and ref[:, 8].sum() > 1000 and np.isnan(f[:, 5]).sum() == 50
+    assert 1000 < (ref[:, 1] == 0).sum() < 7000 and 1000 < (ref[:, 7] == 0).sum() < 7000
+    _assert_wall_words_equal(_oracle.wall_geometry(g["records"]), ref)
+
+
+@pytest.mark.skipif(not _oref.geom_available(), reason="oracle/_ref/oref_geom not built (needs /root/reference)")
+def test_live_reference_wall_geometry_matches_canon():
+    """Same pin against a live run of the reference functions on records the fixture does not hold."""
+    sys_path_tools = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_walls", os.path.join(sys_path_tools, "make_golden_walls.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    rec = mod.inputs(seed=2024, k=20000)
+    _assert_wall_words_equal(_oracle.wall_geometry(rec), _oref.run_geom(rec))

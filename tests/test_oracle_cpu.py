@@ -92,6 +92,67 @@ def test_overlapping_pair_t0_mag20():
     assert o.collision_hits == 2  # both agents query each other (physics.cpp:58-69)
 
 
+# ---------------------------------------------------------------- static walls
+def _wall_words(rect, a, b, r=0.15):
+    rec = np.array([list(rect) + list(a) + list(b) + [r]], np.float32)
+    w = _oracle.wall_geometry(rec)[0]
+    return w, w.view(np.float32)
+
+
+def test_wall_known_answers():
+    """Hand-derived cases for a 1 m square wall tile at the origin (BoundVolume.cpp:131-188, LMP.cpp:64-82,307-319)."""
+    tile = (0, 0, 1, 1)
+    fmax = np.finfo(np.float32).max
+    # agent 2 m to the left walking right at 1 m/s: the wall extruded by r starts at x = -0.65 -> t = 1.35 s
+    w, f = _wall_words(tile, (-2, 0), (1, 0))
+    assert abs(f[0] - 1.5) < 1e-6           # bare ray vs the tile face at x = -0.5
+    assert abs(f[3] - 1.35) < 1e-6
+    assert w[8] == 1 and f[9] < 0 and f[10] == 0  # pushes back along -x; mag = (5 - t)/(t + .001)
+    assert abs(f[9] + (5 - 1.35) / 1.351) < 1e-4
+    # walking away, or on a parallel track beside the tile: no time to collision, no force
+    w, f = _wall_words(tile, (-2, 0), (-1, 0))
+    assert f[3] == fmax and w[8] == 0
+    w, f = _wall_words(tile, (-2, 0.7), (1, 0))
+    assert f[0] == fmax and f[3] == fmax
+    # ... but a track 0.6 m off-centre clips the r-inflated tile (0.5 + 0.15)
+    w, f = _wall_words(tile, (-2, 0.6), (1, 0))
+    assert f[0] == fmax and f[3] < 5
+    # quirk Q10: the gate compares SQUARED distance with 5 (LMP.cpp:310), so a wall 2.3 m away is ignored
+    w, f = _wall_words(tile, (-2.3, 0), (1, 0))
+    assert f[3] < 5 and w[8] == 0
+    # sight lines: through the tile blocked, past it free; the planner's c-space inflates by the agent's square
+    w, _ = _wall_words(tile, (-2, 0), (2, 0))
+    assert w[1] == 0 and w[7] == 0
+    w, _ = _wall_words(tile, (-2, 0.6), (2, 0.6))
+    assert w[1] == 1 and w[7] == 0          # clear of the tile, inside the inflated one (0.5 + 0.15)
+    w, _ = _wall_words(tile, (-2, 0.7), (2, 0.7))
+    assert w[1] == 1 and w[7] == 1
+    # stationary agent: the slab test treats |v| < 1e-7 as parallel (BoundVolume.cpp:167-171)
+    w, f = _wall_words(tile, (-2, 0), (0, 0))
+    assert f[0] == fmax and f[3] == fmax
+
+
+def test_wall_contact_normal():
+    """BVH.cpp:121-130 + BoundVolume.cpp:196-230: an agent overlapping a face by 0.05 m is pushed out by exactly that."""
+    w, f = _wall_words((0, 0, 1, 1), (-0.6, 0), (0, 0))
+    assert w[4] == 1
+    assert abs(f[5] + 0.05) < 1e-6 and f[6] == 0
+    w, f = _wall_words((0, 0, 1, 1), (-0.66, 0), (0, 0))
+    assert w[4] == 0
+    # centre of the agent on the centre of the wall: normalize(0) -> NaN, as in the reference
+    w, f = _wall_words((0, 0, 1, 1), (0, 0), (0, 0))
+    assert np.isnan(f[5])
+
+
+def test_walled_rollouts_are_refused_by_the_oracle():
+    """Rollouts with walls need the PRM + A* planner (GMP.cpp), which is not restated: canon_create says no."""
+    L = _oracle.lib()
+    pos = np.zeros((1, 2), np.float32)
+    wall = _oracle.Rect(0, 0, 1, 1)
+    d = _oracle.Desc(1, pos.ctypes.data, pos.ctypes.data, 0.15, 45.0, 1, None, None, 1, 0, 1, C.addressof(wall))
+    assert L.canon_create(C.byref(d)) is None
+
+
 def test_zero_config_message_is_half_and_no_comm_force():
     """All-zero comms.config == pure-TTC baseline: c == 0.5 after frame 1 (CommComp.h:20-27), comm force == 0."""
     pos, goal, md, rng = _oracle.scene(0, 0)
