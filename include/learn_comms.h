@@ -170,6 +170,15 @@ int32_t lc_write_result(const char* path, float avg_velocity, float group_time);
 int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
                  uint32_t* rng_state_after);
 
+/* ---- static-wall geometry (walled scenes; not yet part of lc_step) ----
+ * Evaluates the device restatement of the reference's wall functions on n_records HOST records of 9 floats
+ * {wall ox, oy, w, h; a.x, a.y; b.x, b.y; r} and writes 12 words per record:
+ *   f32 Rect::intersect(a, b) (BoundVolume.cpp:160-188) | i32 Rect::line_of_sight(a, b) (:131-155) |
+ *   i32 Circ(wall origin, r)::line_of_sight(a, b) (:76-98) | f32 LMP::ttc(Circ(a, r), b, wall, 0) (LMP.cpp:13-34,64-82) |
+ *   i32 circ_rect_collider (BoundVolume.cpp:196-201) | f32 x2 push vector of BVH::query_ (BVH.cpp:121-130) |
+ *   i32 Cspace2d::line_of_sight(a, b) (PRM.cpp:133-173) | i32 wall interacts, f32 x2 its force (LMP.cpp:307-319,128-136) | 0 */
+int32_t lc_wall_geometry(int32_t n_records, const float* records, uint32_t* words, int32_t device);
+
 const char* lc_last_error(void);
 const char* lc_version(void);
 

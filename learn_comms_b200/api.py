@@ -41,7 +41,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_last_error", "lc_version",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_wall_geometry", "lc_last_error", "lc_version",
 ]
 
 
@@ -97,6 +97,7 @@ def lib():
         L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
+        L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
         L.lc_last_error.restype = C.c_char_p
         L.lc_version.restype = C.c_char_p
         _LIB = L
@@ -121,6 +122,17 @@ def scene(scene_id, seed=0):
     if n <= 0:
         raise LcError(n, f"scene {scene_id} is not in the wall-free catalogue")
     return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value)
+
+
+def wall_geometry(records, device=0):
+    """lc_wall_geometry: (K, 9) float32 records {wall ox, oy, w, h; a; b; r} -> (K, 12) uint32 words, computed on the
+    device (BoundVolume.cpp:76-230, LMP.cpp:64-82,307-319, BVH.cpp:121-130, PRM.cpp:133-173)."""
+    rec = np.ascontiguousarray(records, np.float32)
+    if rec.ndim != 2 or rec.shape[1] != 9:
+        raise LcError(-1, "wall_geometry: records must be (K, 9)")
+    out = np.zeros((len(rec), 12), np.uint32)
+    _ck(lib().lc_wall_geometry(len(rec), _p(rec), _p(out), device))
+    return out
 
 
 def read_config(path):

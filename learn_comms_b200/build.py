@@ -6,8 +6,8 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liblearncomms.so")
-SOURCES = ["crowd.cu", "batch.cu", "capi.cu", "host.cpp"]
-HEADERS = ["crowd.cuh", "domain.cuh", "lc_math.cuh", os.path.join("..", "..", "include", "learn_comms.h")]
+SOURCES = ["crowd.cu", "batch.cu", "capi.cu", "walls.cu", "host.cpp"]
+HEADERS = ["crowd.cuh", "domain.cuh", "lc_math.cuh", "walls.cuh", os.path.join("..", "..", "include", "learn_comms.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

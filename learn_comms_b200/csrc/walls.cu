@@ -1,0 +1,65 @@
+// Static-wall geometry on the device (walls.cuh) behind the C ABI.  lc_wall_geometry is the parity entry point for the
+// geometry of SURVEY §8 rows a10 / a14 / a16: it evaluates every wall function on caller-supplied records so the GPU
+// suite can hold the device code against the reference's own bit patterns (tests/golden/wall_geometry.npz) before the
+// functions are wired into k_force / k_collide for walled scenes.
+#include "../../include/learn_comms.h"
+#include "walls.cuh"
+#include <cuda_runtime.h>
+#include <cstdio>
+
+int lc_set_error(int code, const char* msg);  // capi.cu
+
+namespace {
+
+// one record per thread: 36 B in, 48 B out; the records are independent, so this is a plain grid-stride map
+__global__ void __launch_bounds__(256) k_wall_geometry(int32_t n, const float* __restrict__ rec, uint32_t* __restrict__ out) {
+    for (int32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        float p[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) p[i] = rec[(size_t)k * 9 + i];
+        uint32_t w[12];
+        lcw::geometry_record(p, w);
+        uint4* o = reinterpret_cast<uint4*>(out + (size_t)k * 12);  // 48 B per record: three 16 B stores
+        o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+        o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        o[2] = make_uint4(w[8], w[9], w[10], w[11]);
+    }
+}
+
+int cuda_fail(const char* what, cudaError_t e) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "lc_wall_geometry: %s failed: %s", what, cudaGetErrorString(e));
+    (void)cudaGetLastError();  // a refused call must not show up as the next launch's error
+    return lc_set_error(LC_ERR_CUDA, buf);
+}
+
+}  // namespace
+
+extern "C" int32_t lc_wall_geometry(int32_t n_records, const float* records, uint32_t* words, int32_t device) {
+    if (n_records < 0 || (n_records > 0 && (!records || !words)))
+        return lc_set_error(LC_ERR_ARG, "lc_wall_geometry: bad arguments");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail("cudaSetDevice", e);
+    if (n_records == 0) return LC_OK;
+    float* d_rec = nullptr;
+    uint32_t* d_out = nullptr;
+    size_t in_bytes = sizeof(float) * 9 * (size_t)n_records, out_bytes = sizeof(uint32_t) * 12 * (size_t)n_records;
+    if ((e = cudaMalloc((void**)&d_rec, in_bytes)) != cudaSuccess) return cuda_fail("cudaMalloc", e);
+    if ((e = cudaMalloc((void**)&d_out, out_bytes)) != cudaSuccess) {
+        cudaFree(d_rec);
+        return cuda_fail("cudaMalloc", e);
+    }
+    int rc = LC_OK;
+    if ((e = cudaMemcpy(d_rec, records, in_bytes, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail("cudaMemcpy", e);
+    if (rc == LC_OK) {
+        int blocks = (n_records + 255) / 256;
+        if (blocks > 148 * 8) blocks = 148 * 8;  // 148 SMs x 8 resident blocks of 256 threads
+        k_wall_geometry<<<blocks, 256>>>(n_records, d_rec, d_out);
+        if ((e = cudaGetLastError()) != cudaSuccess) rc = cuda_fail("k_wall_geometry launch", e);
+    }
+    if (rc == LC_OK && (e = cudaMemcpy(words, d_out, out_bytes, cudaMemcpyDeviceToHost)) != cudaSuccess)
+        rc = cuda_fail("cudaMemcpy", e);
+    cudaFree(d_rec);
+    cudaFree(d_out);
+    return rc;
+}

@@ -144,6 +144,21 @@ def test_wall_contact_normal():
     assert np.isnan(f[5])
 
 
+def test_device_wall_header_matches_reference_golden_when_compiled_for_the_host(tmp_path):
+    """learn_comms_b200/csrc/walls.cuh (what k_wall_geometry runs) compiled by g++ with contraction off: every word
+    equals the reference's, NaN patterns included.  The -m gpu suite repeats this on the device through the C ABI."""
+    so = tmp_path / "walls_host.so"
+    subprocess.check_call(["g++", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math", "-w", "-x", "c++",
+                           os.path.join(ROOT, "tests", "walls_host_shim.cpp"), "-o", str(so)])
+    L = C.CDLL(str(so))
+    g = np.load(os.path.join(ROOT, "tests", "golden", "wall_geometry.npz"))
+    rec = np.ascontiguousarray(g["records"], np.float32)
+    out = np.zeros((len(rec), 12), np.uint32)
+    L.walls_host_batch(C.c_int32(len(rec)), rec.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+    assert np.array_equal(out, g["words"])
+    assert np.array_equal(out, _oracle.wall_geometry(rec))
+
+
 def test_walled_rollouts_are_refused_by_the_oracle():
     """Rollouts with walls need the PRM + A* planner (GMP.cpp), which is not restated: canon_create says no."""
     L = _oracle.lib()
