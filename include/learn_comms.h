@@ -179,6 +179,19 @@ int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t
  *   i32 Cspace2d::line_of_sight(a, b) (PRM.cpp:133-173) | i32 wall interacts, f32 x2 its force (LMP.cpp:307-319,128-136) | 0 */
 int32_t lc_wall_geometry(int32_t n_records, const float* records, uint32_t* words, int32_t device);
 
+/* ---- host-side global planner for walled scenes: Cspace2d + PRM roadmap + A* as ai::init sets them up
+ * (ai.cpp:41-63: threshold 5*sqrt(2), no bin samples, eight points per inflated wall; PRM.cpp:8-105; GMP.cpp:7-110).
+ * The roadmap is stateful exactly as the reference's shared std_prm is: plan calls must come in the reference's order
+ * (ai::init's agent loop, then the replans of ai.cpp:161-166) for equal-cost ties to resolve identically. ---- */
+typedef struct lc_planner lc_planner;
+int32_t lc_planner_create(int32_t n_walls, const lc_rect* walls, float agent_radius, lc_planner** out);
+void lc_planner_destroy(lc_planner* p);
+int32_t lc_planner_roadmap_size(lc_planner* p, int32_t* vertices, int32_t* directed_edges);
+/* GMP::plan_one for one agent: waypoints [n][2] from the first after `start` to `goal` inclusive (n = 0: unreachable);
+ * min_time = path length - 1 (ai.cpp:118-126).  LC_ERR_CAPACITY (n still reported) when n > cap. */
+int32_t lc_planner_plan(lc_planner* p, const float* start, const float* goal, int32_t cap, float* waypoints,
+                        int32_t* n_waypoints, float* min_time);
+
 const char* lc_last_error(void);
 const char* lc_version(void);
 

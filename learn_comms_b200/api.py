@@ -41,7 +41,8 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_wall_geometry", "lc_last_error", "lc_version",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_wall_geometry", "lc_planner_create", "lc_planner_destroy",
+    "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
 
@@ -98,6 +99,11 @@ def lib():
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
+        L.lc_planner_create.argtypes = [i32, vp, C.c_float, C.POINTER(vp)]
+        L.lc_planner_destroy.argtypes = [vp]
+        L.lc_planner_destroy.restype = None
+        L.lc_planner_roadmap_size.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
+        L.lc_planner_plan.argtypes = [vp, vp, vp, i32, vp, C.POINTER(i32), f32p]
         L.lc_last_error.restype = C.c_char_p
         L.lc_version.restype = C.c_char_p
         _LIB = L
@@ -133,6 +139,37 @@ def wall_geometry(records, device=0):
     out = np.zeros((len(rec), 12), np.uint32)
     _ck(lib().lc_wall_geometry(len(rec), _p(rec), _p(out), device))
     return out
+
+
+class Planner:
+    """Host-side global planner for walled scenes (lc_planner_*): Cspace2d + PRM roadmap + A* as ai::init builds them
+    (ai.cpp:41-63, PRM.cpp:8-105, GMP.cpp:7-110).  Stateful like the reference's shared roadmap: call plan() in the
+    reference's order."""
+
+    def __init__(self, walls, agent_radius=0.15):
+        self._w = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+        self._h = C.c_void_p()
+        _ck(lib().lc_planner_create(len(self._w), _p(self._w), agent_radius, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().lc_planner_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def roadmap_size(self):
+        v, e = C.c_int32(0), C.c_int32(0)
+        _ck(lib().lc_planner_roadmap_size(self._h, C.byref(v), C.byref(e)))
+        return v.value, e.value
+
+    def plan(self, start, goal, cap=256):
+        """-> (waypoints [n][2], min_time); n = 0 when the goal is unreachable."""
+        s, g = np.asarray(start, np.float32).reshape(2).copy(), np.asarray(goal, np.float32).reshape(2).copy()
+        wp = np.zeros((cap, 2), np.float32)
+        n, mt = C.c_int32(0), C.c_float(0)
+        _ck(lib().lc_planner_plan(self._h, _p(s), _p(g), cap, _p(wp), C.byref(n), C.byref(mt)))
+        return wp[:n.value].copy(), float(mt.value)
 
 
 def read_config(path):

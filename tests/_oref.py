@@ -22,6 +22,32 @@ def geom_available():
     return os.path.exists(OREF_GEOM)
 
 
+OREF_PLAN = os.path.join(ROOT, "oracle", "_ref", "oref_plan")
+
+
+def plan_available():
+    return os.path.exists(OREF_PLAN)
+
+
+def run_plan(walls, radius, start, goal):
+    """oracle/ref/plan_main.cpp: the reference's c-space + roadmap + A* -> (vertices, directed edges, [(min_time, waypoints)])."""
+    import struct
+    walls = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    start = np.ascontiguousarray(np.asarray(start, np.float32).reshape(-1, 2))
+    goal = np.ascontiguousarray(np.asarray(goal, np.float32).reshape(-1, 2))
+    blob = (np.int32(len(walls)).tobytes() + walls.tobytes() + np.float32(radius).tobytes()
+            + np.int32(len(start)).tobytes() + start.tobytes() + goal.tobytes())
+    out = subprocess.run([OREF_PLAN], input=blob, stdout=subprocess.PIPE, check=True).stdout
+    nv, ne = struct.unpack_from("ii", out, 0)
+    off, plans = 8, []
+    for _ in range(len(start)):
+        n, mt = struct.unpack_from("if", out, off)
+        off += 8
+        plans.append((mt, np.frombuffer(out, np.float32, 2 * n, off).reshape(n, 2).copy()))
+        off += 8 * n
+    return nv, ne, plans
+
+
 def run_geom(records):
     """oracle/ref/geom_main.cpp: (K, 9) float32 records -> (K, 12) uint32 words of the reference's wall geometry."""
     rec = np.ascontiguousarray(records, np.float32)

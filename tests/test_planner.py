@@ -1,0 +1,76 @@
+"""Host-side global planner of the walled scenes (lc_planner_*, learn_comms_b200/csrc/planner.cpp) against
+the reference's own Cspace2d + PRM + GMP::plan_one (oracle/_ref/oref_plan; fixtures by tools/make_golden_planner.py).
+The planner runs on the host in the reference too (ai::init, ai.cpp:41-127), so these tests need no GPU.  Bar: roadmap
+size, every waypoint list (equal-cost ties included) and min_time identical, bit for bit."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+import _oref
+import learn_comms_b200 as lcb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden", "planner.npz")
+
+
+def _check(walls, start, goal, roadmap, plans):
+    p = lcb.Planner(walls, 0.15)
+    assert p.roadmap_size() == tuple(int(v) for v in roadmap)
+    for i in range(len(start)):  # same order as the reference: the roadmap is stateful (ids, hash-table history)
+        wp, mt = p.plan(start[i], goal[i])
+        ref_mt, ref_wp = plans[i]
+        assert wp.shape == ref_wp.shape and np.array_equal(wp, ref_wp), "agent %d: waypoints differ" % i
+        assert np.float32(mt) == np.float32(ref_mt), "agent %d: min_time differs" % i
+    p.close()
+
+
+def test_planner_matches_reference_golden():
+    g = np.load(GOLD)
+    multi = 0
+    for s in g["seeds"]:
+        cnt = g[f"cnt{s}"]
+        plans = [(g[f"min_time{s}"][i], g[f"wp{s}"][i, :cnt[i]]) for i in range(len(cnt))]
+        _check(g[f"walls{s}"], g[f"start{s}"], g[f"goal{s}"], g[f"roadmap{s}"], plans)
+        multi += int((cnt >= 3).sum())
+    assert multi >= 30  # the fixture holds real detours, not only straight lines
+
+
+@pytest.mark.skipif(not _oref.plan_available(), reason="oracle/_ref/oref_plan not built (needs /root/reference)")
+def test_live_reference_planner_matches():
+    spec = importlib.util.spec_from_file_location("mgp", os.path.join(ROOT, "tools", "make_golden_planner.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for seed in (100, 101, 102, 103, 104, 105):
+        walls, start, goal = mod.layout(seed, n_agents=60)
+        nv, ne, plans = _oref.run_plan(walls, 0.15, start, goal)
+        _check(walls, start, goal, (nv, ne), plans)
+
+
+def test_planner_known_answers():
+    """One 4 m block at the origin, agent radius 0.15: inflated half-side 2.15, roadmap points 0.3 m further out."""
+    p = lcb.Planner([[0, 0, 4, 4]], 0.15)
+    assert p.roadmap_size() == (8, 24)  # each point sees its two neighbours on the ring, plus the far corner of its face
+    wp, mt = p.plan((-8, 3), (8, 3))    # clear of the block: straight line
+    assert wp.tolist() == [[8.0, 3.0]] and abs(mt - 15.0) < 1e-6
+    wp, mt = p.plan((-8, 0), (8, 0))    # around a corner pair
+    assert len(wp) >= 3 and np.allclose(np.abs(wp[:-1, 1]), 2.45, atol=1e-6) and wp[-1].tolist() == [8.0, 0.0]
+    expected = 2 * np.hypot(8 - 2.45, 2.45) + 4.9 - 1
+    assert abs(mt - expected) < 1e-4
+    wp, mt = p.plan((0, 0), (8, 0))     # start inside the wall: unreachable, empty plan, min_time = -1 (ai.cpp:121)
+    assert len(wp) == 0 and mt == -1.0
+    wp, mt = p.plan((-8, 3), (8, 3))    # the temporary start / goal vertices left the roadmap again
+    assert p.roadmap_size() == (8, 24) and wp.tolist() == [[8.0, 3.0]]
+    # no walls: the plan is the goal (what the wall-free product path assumes)
+    q = lcb.Planner(np.zeros((0, 4), np.float32), 0.15)
+    wp, mt = q.plan((1, 1), (4, 5))
+    assert wp.tolist() == [[4.0, 5.0]] and abs(mt - 4.0) < 1e-6
+
+
+def test_planner_error_paths():
+    with pytest.raises(lcb.LcError):
+        lcb.Planner([[0, 0, 1, 1]], agent_radius=0.0)
+    p = lcb.Planner([[0, 0, 4, 4]], 0.15)
+    with pytest.raises(lcb.LcError):
+        p.plan((-8, 0), (8, 0), cap=1)  # LC_ERR_CAPACITY
