@@ -164,6 +164,36 @@ LCW_HD bool cspace_line_of_sight(Wall w, float agent_r, float ax, float ay, floa
     return rect_line_of_sight(infl, ax, ay, bx, by);
 }
 
+// LMP.cpp:84-113 lookahead: advance along the waypoint list.  The current target counts as reached within 1 m
+// (squared distance against ai::at_dist = 1); further waypoints are skipped while the one after the target is in line
+// of sight through the configuration space.  plan = [n_plan][2]; num_done and local_goal are updated in place
+// (local_goal keeps its old value when the reached target was the last waypoint, as in the reference).
+LCW_HD void lookahead(const Wall* walls, int n_walls, float agent_r, float px, float py, const float* plan, int n_plan,
+                      int& num_done, float& lgx, float& lgy) {
+    int target = num_done;
+    if (target < n_plan) {
+        float dx = px - plan[2 * target], dy = py - plan[2 * target + 1];
+        if (dot2(dx, dy, dx, dy) < 1.f) ++target;
+        if (target < n_plan) {
+            lgx = plan[2 * target];
+            lgy = plan[2 * target + 1];
+        }
+        for (int next = target + 1; next < n_plan; next = target + 1) {
+            bool visible = true;
+            for (int k = 0; k < n_walls && visible; ++k)
+                visible = cspace_line_of_sight(walls[k], agent_r, px, py, plan[2 * next], plan[2 * next + 1]);
+            if (!visible) break;
+            ++target;
+            lgx = plan[2 * target];
+            lgy = plan[2 * target + 1];
+        }
+        num_done = target;
+    } else {
+        lgx = plan[2 * (n_plan - 1)];
+        lgy = plan[2 * (n_plan - 1) + 1];
+    }
+}
+
 // One record of the parity fixture (oracle/ref/geom_main.cpp): 9 floats {wall; a; b; r} -> 12 words
 LCW_HD void geometry_record(const float* p, uint32_t* out) {
     union { float f; int32_t i; uint32_t u; } w[12];

@@ -849,6 +849,29 @@ int32_t canon_cspace_line_of_sight(const canon_rect* walls, int32_t n_walls, flo
     return 1;
 }
 
+/* LMP.cpp:84-113 lookahead with a multi-waypoint plan.  plan = [n_plan][2], n_plan >= 1; num_done / local_goal in, out */
+void canon_lookahead(const canon_rect* walls, int32_t n_walls, float agent_r, const float* pos, const float* plan,
+                     int32_t n_plan, int32_t* num_done, float* local_goal) {
+    size_t target = (size_t)*num_done;
+    if (target < (size_t)n_plan) {
+        v2 d = sub2(V2(pos[0], pos[1]), V2(plan[2 * target], plan[2 * target + 1]));
+        int at_target = len2_2(d) < 1.f; /* ai::at_dist, ai.cpp:14 */
+        if (at_target) ++target;
+        size_t next = target + 1;
+        if (target < (size_t)n_plan) { local_goal[0] = plan[2 * target]; local_goal[1] = plan[2 * target + 1]; }
+        while (1) {
+            if (!(next < (size_t)n_plan)) break;
+            if (!canon_cspace_line_of_sight(walls, n_walls, agent_r, pos, plan + 2 * next)) break;
+            ++target;
+            local_goal[0] = plan[2 * target]; local_goal[1] = plan[2 * target + 1];
+            next = target + 1;
+        }
+        *num_done = (int32_t)target;
+    } else {
+        local_goal[0] = plan[2 * (n_plan - 1)]; local_goal[1] = plan[2 * (n_plan - 1) + 1];
+    }
+}
+
 /* the record layout of oracle/ref/geom_main.cpp (9 floats in, 12 words out), so one call checks a whole fixture */
 void canon_wall_geometry_batch(int32_t K, const float* in, void* out) {
     for (int32_t k = 0; k < K; ++k) {

@@ -93,6 +93,9 @@ int32_t canon_circ_wall_hit(const float* o, float r, const canon_rect* w, float*
 int32_t canon_cspace_line_of_sight(const canon_rect* walls, int32_t n_walls, float agent_r, const float* a,
                                    const float* b);                                           /* PRM.cpp:133-156,169-173 */
 
+void canon_lookahead(const canon_rect* walls, int32_t n_walls, float agent_r, const float* pos, const float* plan,
+                     int32_t n_plan, int32_t* num_done, float* local_goal);                   /* LMP.cpp:84-113 */
+
 /* scene catalogue (demo.cpp:141-511): fills pos/goal for wall-free scenes; returns n (0 = unsupported).
  * rng_state is advanced by construction-time draws (scene 12). */
 int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration,

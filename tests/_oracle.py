@@ -81,6 +81,22 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def lookahead(walls, radius, recs):
+    """canon_lookahead on _oref.LOOK_REC records -> _oref.LOOK_OUT records."""
+    import _oref
+    L = lib()
+    L.canon_lookahead.argtypes = [C.c_void_p, C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_int32,
+                                  C.POINTER(C.c_int32), C.c_void_p]
+    walls = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    out = np.zeros(len(recs), _oref.LOOK_OUT)
+    for k, r in enumerate(recs):
+        pos, plan, lg = r["pos"].copy(), np.ascontiguousarray(r["plan"]), r["lg"].copy()
+        nd = C.c_int32(int(r["num_done"]))
+        L.canon_lookahead(_p(walls), len(walls), radius, _p(pos), _p(plan), int(r["n_plan"]), C.byref(nd), _p(lg))
+        out[k] = (nd.value, lg)
+    return out
+
+
 def wall_geometry(records):
     """O-canon's static-wall functions on (K, 9) records {rect; a; b; r} -> (K, 12) uint32 words, in the layout of
     oracle/ref/geom_main.cpp."""

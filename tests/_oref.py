@@ -48,6 +48,26 @@ def run_plan(walls, radius, start, goal):
     return nv, ne, plans
 
 
+OREF_LOOK = os.path.join(ROOT, "oracle", "_ref", "oref_look")
+LOOK_REC = np.dtype([("pos", np.float32, 2), ("lg", np.float32, 2), ("num_done", np.int32), ("n_plan", np.int32),
+                     ("plan", np.float32, (8, 2))])
+LOOK_OUT = np.dtype([("num_done", np.int32), ("lg", np.float32, 2)])
+
+
+def look_available():
+    return os.path.exists(OREF_LOOK)
+
+
+def run_look(walls, radius, recs):
+    """oracle/ref/look_main.cpp: the reference's LMP::lookahead on LOOK_REC records -> LOOK_OUT records."""
+    walls = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    recs = np.ascontiguousarray(recs, LOOK_REC)
+    blob = (np.int32(len(walls)).tobytes() + walls.tobytes() + np.float32(radius).tobytes()
+            + np.int32(len(recs)).tobytes() + recs.tobytes())
+    out = subprocess.run([OREF_LOOK], input=blob, stdout=subprocess.PIPE, check=True).stdout
+    return np.frombuffer(out, LOOK_OUT).copy()
+
+
 def run_geom(records):
     """oracle/ref/geom_main.cpp: (K, 9) float32 records -> (K, 12) uint32 words of the reference's wall geometry."""
     rec = np.ascontiguousarray(records, np.float32)

@@ -8,6 +8,10 @@ import os
 import numpy as np
 import pytest
 
+import ctypes as C
+import subprocess
+
+import _oracle
 import _oref
 import learn_comms_b200 as lcb
 
@@ -74,3 +78,51 @@ def test_planner_error_paths():
     p = lcb.Planner([[0, 0, 4, 4]], 0.15)
     with pytest.raises(lcb.LcError):
         p.plan((-8, 0), (8, 0), cap=1)  # LC_ERR_CAPACITY
+
+
+# ---------------------------------------------------------------- LMP::lookahead over the planned waypoint lists
+def _host_build_of_device_header(tmp_path):
+    so = tmp_path / "walls_host.so"
+    subprocess.check_call(["g++", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math", "-w", "-x", "c++",
+                           os.path.join(ROOT, "tests", "walls_host_shim.cpp"), "-o", str(so)])
+    return C.CDLL(str(so))
+
+
+def _device_header_lookahead(L, walls, recs):
+    walls = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    recs = np.ascontiguousarray(recs, _oref.LOOK_REC)
+    out = np.zeros(len(recs), _oref.LOOK_OUT)
+    L.walls_host_lookahead(C.c_int32(len(walls)), walls.ctypes.data_as(C.c_void_p), C.c_float(0.15), C.c_int32(len(recs)),
+                           recs.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+    return out
+
+
+def test_lookahead_matches_reference_golden(tmp_path):
+    """LMP::lookahead (LMP.cpp:84-113; SURVEY §8 row a10) with multi-waypoint plans and walls: O-canon's restatement and
+    the product's device header (walls.cuh lcw::lookahead, compiled for the host) both return the reference's num_done
+    and local_goal bit for bit on 2 454 records (positions scattered around the planned paths, every num_done)."""
+    L = _host_build_of_device_header(tmp_path)
+    g = np.load(GOLD)
+    total = advanced = 0
+    for s in g["seeds"]:
+        rin, rout = g[f"look_in{s}"], g[f"look_out{s}"]
+        assert _oracle.lookahead(g[f"walls{s}"], 0.15, rin).tobytes() == rout.tobytes()
+        assert _device_header_lookahead(L, g[f"walls{s}"], rin).tobytes() == rout.tobytes()
+        total += len(rin)
+        advanced += int((rout["num_done"] > rin["num_done"]).sum())
+    assert total > 2000 and advanced > 200
+
+
+@pytest.mark.skipif(not (_oref.look_available() and _oref.plan_available()), reason="oracle/_ref harnesses not built")
+def test_live_reference_lookahead_matches(tmp_path):
+    spec = importlib.util.spec_from_file_location("mgp", os.path.join(ROOT, "tools", "make_golden_planner.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    L = _host_build_of_device_header(tmp_path)
+    for seed in (200, 201, 202):
+        walls, start, goal = mod.layout(seed, n_agents=60)
+        _, _, plans = _oref.run_plan(walls, 0.15, start, goal)
+        recs = mod.look_records(seed, start, plans, per_plan=10)
+        ref = _oref.run_look(walls, 0.15, recs)
+        assert _oracle.lookahead(walls, 0.15, recs).tobytes() == ref.tobytes()
+        assert _device_header_lookahead(L, walls, recs).tobytes() == ref.tobytes()

@@ -34,6 +34,27 @@ def layout(seed, n_agents=40):
     return np.array(walls, np.float32).reshape(-1, 4), start, goal
 
 
+def look_records(seed, start, plans, per_plan=6):
+    """Agent positions scattered around their own path (so waypoints get reached, skipped or hidden behind walls), with
+    every admissible num_done, for LMP::lookahead.  Plans longer than 8 waypoints or empty are left out."""
+    g = np.random.default_rng(1000 + seed)
+    recs = []
+    for i, (_, wp) in enumerate(plans):
+        if not 1 <= len(wp) <= 8:
+            continue
+        line = np.vstack([start[i][None], wp])
+        for _ in range(per_plan):
+            k = g.integers(0, len(line) - 1)
+            t = g.random()
+            pos = line[k] * (1 - t) + line[k + 1] * t + g.normal(0, 0.4, 2)
+            r = np.zeros((), _oref.LOOK_REC)
+            r["pos"], r["lg"] = pos, g.uniform(-5, 5, 2)
+            r["num_done"], r["n_plan"] = g.integers(0, len(wp) + 1), len(wp)
+            r["plan"][:len(wp)] = wp
+            recs.append(r)
+    return np.array(recs, _oref.LOOK_REC)
+
+
 def main():
     d = {}
     seeds = list(range(12))
@@ -48,6 +69,8 @@ def main():
             cnt[i] = len(p)
         d.update({f"walls{s}": walls, f"start{s}": start, f"goal{s}": goal, f"wp{s}": wp, f"cnt{s}": cnt,
                   f"min_time{s}": np.array([p[0] for p in plans], np.float32), f"roadmap{s}": np.array([nv, ne], np.int32)})
+        recs = look_records(s, start, plans)
+        d[f"look_in{s}"], d[f"look_out{s}"] = recs, _oref.run_look(walls, 0.15, recs)
         print("layout", s, "walls", len(walls), "roadmap", nv, ne, "waypoints", np.bincount(cnt))
     d["seeds"] = np.array(seeds, np.int32)
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", "planner.npz"), **d)
