@@ -179,6 +179,21 @@ int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t
  *   i32 Cspace2d::line_of_sight(a, b) (PRM.cpp:133-173) | i32 wall interacts, f32 x2 its force (LMP.cpp:307-319,128-136) | 0 */
 int32_t lc_wall_geometry(int32_t n_records, const float* records, uint32_t* words, int32_t device);
 
+/* LMP::lookahead (LMP.cpp:84-113) on the device, one agent per record: advances num_done along the waypoint list (target
+ * reached within 1 m; later waypoints skipped while visible through the c-space of `walls`) and returns the new
+ * local_goal.  Parity entry point like lc_wall_geometry; plans here are capped at LC_LOOK_MAX_WAYPOINTS. */
+#define LC_LOOK_MAX_WAYPOINTS 8
+typedef struct lc_look_record {
+    float pos[2];        /* BoundVolume origin of the agent */
+    float local_goal[2]; /* Agent::local_goal before the call */
+    int32_t num_done;    /* Agent::num_done before the call, >= 0 */
+    int32_t n_plan;      /* 1..LC_LOOK_MAX_WAYPOINTS */
+    float plan[LC_LOOK_MAX_WAYPOINTS][2];
+} lc_look_record;
+typedef struct lc_look_result { int32_t num_done; float local_goal[2]; } lc_look_result;
+int32_t lc_lookahead(int32_t n_walls, const lc_rect* walls, float agent_radius, int32_t n_records,
+                     const lc_look_record* records, lc_look_result* results, int32_t device);
+
 /* ---- host-side global planner for walled scenes: Cspace2d + PRM roadmap + A* as ai::init sets them up
  * (ai.cpp:41-63: threshold 5*sqrt(2), no bin samples, eight points per inflated wall; PRM.cpp:8-105; GMP.cpp:7-110).
  * The roadmap is stateful exactly as the reference's shared std_prm is: plan calls must come in the reference's order

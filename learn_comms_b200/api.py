@@ -41,7 +41,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_wall_geometry", "lc_planner_create", "lc_planner_destroy",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -99,6 +99,7 @@ def lib():
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
+        L.lc_lookahead.argtypes = [i32, vp, C.c_float, i32, vp, vp, i32]
         L.lc_planner_create.argtypes = [i32, vp, C.c_float, C.POINTER(vp)]
         L.lc_planner_destroy.argtypes = [vp]
         L.lc_planner_destroy.restype = None
@@ -138,6 +139,22 @@ def wall_geometry(records, device=0):
         raise LcError(-1, "wall_geometry: records must be (K, 9)")
     out = np.zeros((len(rec), 12), np.uint32)
     _ck(lib().lc_wall_geometry(len(rec), _p(rec), _p(out), device))
+    return out
+
+
+LOOK_RECORD = np.dtype([("pos", np.float32, 2), ("local_goal", np.float32, 2), ("num_done", np.int32), ("n_plan", np.int32),
+                        ("plan", np.float32, (8, 2))])   # lc_look_record
+LOOK_RESULT = np.dtype([("num_done", np.int32), ("local_goal", np.float32, 2)])  # lc_look_result
+
+
+def lookahead(walls, records, agent_radius=0.15, device=0):
+    """lc_lookahead: LMP::lookahead (LMP.cpp:84-113) on the device for LOOK_RECORD records -> LOOK_RESULT records."""
+    w = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    rec = np.ascontiguousarray(records)
+    if rec.dtype.itemsize != LOOK_RECORD.itemsize:
+        raise LcError(-1, "lookahead: records must have the lc_look_record layout")
+    out = np.zeros(len(rec), LOOK_RESULT)
+    _ck(lib().lc_lookahead(len(w), _p(w), agent_radius, len(rec), _p(rec), _p(out), device))
     return out
 
 

@@ -26,9 +26,27 @@ __global__ void __launch_bounds__(256) k_wall_geometry(int32_t n, const float* _
     }
 }
 
+// LMP::lookahead for one agent per thread; the wall list is small (<= 60 tiles in the shipped scenes) and read by every
+// thread, so it is staged in shared memory once per block
+__global__ void __launch_bounds__(256) k_lookahead(int32_t n_walls, const lc_rect* __restrict__ walls, float agent_r, int32_t n,
+                                                   const lc_look_record* __restrict__ rec, lc_look_result* __restrict__ out) {
+    extern __shared__ lcw::Wall s_walls[];
+    for (int k = threadIdx.x; k < n_walls; k += blockDim.x) s_walls[k] = {walls[k].ox, walls[k].oy, walls[k].w, walls[k].h};
+    __syncthreads();
+    for (int32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        lc_look_record r = rec[k];
+        int nd = r.num_done;
+        float lgx = r.local_goal[0], lgy = r.local_goal[1];
+        lcw::lookahead(s_walls, n_walls, agent_r, r.pos[0], r.pos[1], &r.plan[0][0], r.n_plan, nd, lgx, lgy);
+        out[k].num_done = nd;
+        out[k].local_goal[0] = lgx;
+        out[k].local_goal[1] = lgy;
+    }
+}
+
 int cuda_fail(const char* what, cudaError_t e) {
     char buf[256];
-    snprintf(buf, sizeof buf, "lc_wall_geometry: %s failed: %s", what, cudaGetErrorString(e));
+    snprintf(buf, sizeof buf, "walls: %s failed: %s", what, cudaGetErrorString(e));
     (void)cudaGetLastError();  // a refused call must not show up as the next launch's error
     return lc_set_error(LC_ERR_CUDA, buf);
 }
@@ -59,6 +77,45 @@ extern "C" int32_t lc_wall_geometry(int32_t n_records, const float* records, uin
     }
     if (rc == LC_OK && (e = cudaMemcpy(words, d_out, out_bytes, cudaMemcpyDeviceToHost)) != cudaSuccess)
         rc = cuda_fail("cudaMemcpy", e);
+    cudaFree(d_rec);
+    cudaFree(d_out);
+    return rc;
+}
+
+extern "C" int32_t lc_lookahead(int32_t n_walls, const lc_rect* walls, float agent_radius, int32_t n_records,
+                                const lc_look_record* records, lc_look_result* results, int32_t device) {
+    if (n_walls < 0 || n_walls > 2048 || (n_walls > 0 && !walls) || n_records < 0 || (n_records > 0 && (!records || !results)))
+        return lc_set_error(LC_ERR_ARG, "lc_lookahead: bad arguments");
+    for (int32_t k = 0; k < n_records; ++k)
+        if (records[k].n_plan < 1 || records[k].n_plan > LC_LOOK_MAX_WAYPOINTS || records[k].num_done < 0)
+            return lc_set_error(LC_ERR_ARG, "lc_lookahead: n_plan must be 1..8 and num_done >= 0");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail("cudaSetDevice", e);
+    if (n_records == 0) return LC_OK;
+    lc_rect* d_walls = nullptr;
+    lc_look_record* d_rec = nullptr;
+    lc_look_result* d_out = nullptr;
+    int rc = LC_OK;
+    if ((e = cudaMalloc((void**)&d_walls, sizeof(lc_rect) * (size_t)(n_walls ? n_walls : 1))) != cudaSuccess ||
+        (e = cudaMalloc((void**)&d_rec, sizeof(lc_look_record) * (size_t)n_records)) != cudaSuccess ||
+        (e = cudaMalloc((void**)&d_out, sizeof(lc_look_result) * (size_t)n_records)) != cudaSuccess)
+        rc = cuda_fail("cudaMalloc", e);
+    if (rc == LC_OK && n_walls &&
+        (e = cudaMemcpy(d_walls, walls, sizeof(lc_rect) * (size_t)n_walls, cudaMemcpyHostToDevice)) != cudaSuccess)
+        rc = cuda_fail("cudaMemcpy", e);
+    if (rc == LC_OK &&
+        (e = cudaMemcpy(d_rec, records, sizeof(lc_look_record) * (size_t)n_records, cudaMemcpyHostToDevice)) != cudaSuccess)
+        rc = cuda_fail("cudaMemcpy", e);
+    if (rc == LC_OK) {
+        int blocks = (n_records + 255) / 256;
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        k_lookahead<<<blocks, 256, sizeof(lcw::Wall) * (size_t)n_walls>>>(n_walls, d_walls, agent_radius, n_records, d_rec, d_out);
+        if ((e = cudaGetLastError()) != cudaSuccess) rc = cuda_fail("k_lookahead launch", e);
+    }
+    if (rc == LC_OK &&
+        (e = cudaMemcpy(results, d_out, sizeof(lc_look_result) * (size_t)n_records, cudaMemcpyDeviceToHost)) != cudaSuccess)
+        rc = cuda_fail("cudaMemcpy", e);
+    cudaFree(d_walls);
     cudaFree(d_rec);
     cudaFree(d_out);
     return rc;

@@ -56,3 +56,29 @@ def test_wall_geometry_edges_and_errors():
         lcb.wall_geometry(np.zeros((4, 8), np.float32))
     with pytest.raises(lcb.LcError):
         lcb.wall_geometry(one, device=99)
+
+
+def test_lookahead_matches_reference_golden():
+    """lc_lookahead (k_lookahead, walls.cu) against the reference's LMP::lookahead on the committed records
+    (tests/golden/planner.npz, from oracle/_ref/oref_look): num_done and local_goal, every bit."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "planner.npz"))
+    total = 0
+    for s in g["seeds"]:
+        rin, rout = g[f"look_in{s}"], g[f"look_out{s}"]
+        got = lcb.lookahead(g[f"walls{s}"], rin)
+        assert got.tobytes() == rout.tobytes(), "layout %d" % s
+        total += len(rin)
+    assert total > 2000
+
+
+def test_lookahead_errors_and_no_walls():
+    rec = np.zeros(2, lcb.api.LOOK_RECORD)
+    rec["n_plan"] = [1, 2]
+    rec["plan"][:, 0] = [[5, 0], [0.5, 0]]
+    rec["plan"][1, 1] = [9, 9]
+    out = lcb.lookahead(np.zeros((0, 4), np.float32), rec)
+    assert out["num_done"].tolist() == [0, 1]           # far from its only waypoint; within 1 m of the first, second visible
+    assert out["local_goal"].tolist() == [[5, 0], [9, 9]]
+    rec["n_plan"][0] = 0
+    with pytest.raises(lcb.LcError):
+        lcb.lookahead(np.zeros((0, 4), np.float32), rec)
