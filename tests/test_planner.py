@@ -13,6 +13,7 @@ import subprocess
 
 import _oracle
 import _oref
+import _walled
 import learn_comms_b200 as lcb
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -126,3 +127,45 @@ def test_live_reference_lookahead_matches(tmp_path):
         ref = _oref.run_look(walls, 0.15, recs)
         assert _oracle.lookahead(walls, 0.15, recs).tobytes() == ref.tobytes()
         assert _device_header_lookahead(L, walls, recs).tobytes() == ref.tobytes()
+
+
+# ---------------------------------------------------------------- the reference's own walled rollout (scene 3)
+def _golden_rollout():
+    g = np.load(os.path.join(ROOT, "tests", "golden", "walled_scene3.npz"))
+    frames = [dict(frame=int(g["frame"][k]), pos=g["pos"][k], goal_dist=g["goal_dist"][k],
+                   num_done=g["num_done"][k].astype(np.int32), local_goal=g["local_goal"][k]) for k in range(len(g["frame"]))]
+    return dict(n=int(g["n"]), order=g["order"], pos0=g["pos0"], goal=g["goal"], min_time=g["min_time"], frames=frames)
+
+
+def test_walled_scene3_initial_plans_match_reference():
+    """ai::init on the reference's scene 3 (60 agents around one 4 m pillar): planning the agents in the reference's
+    table order gives every agent's min_time bit for bit (ai.cpp:107-127)."""
+    r = _golden_rollout()
+    p = lcb.Planner(_walled.SCENE3_WALLS, 0.15)
+    mt = np.zeros(r["n"], np.float32)
+    longest = 0
+    for i in r["order"]:
+        wp, mt[i] = p.plan(r["pos0"][i], r["goal"][i])
+        longest = max(longest, len(wp))
+    assert np.array_equal(mt, r["min_time"]) and longest == 3
+
+
+def test_walled_scene3_waypoint_bookkeeping_matches_reference_rollout():
+    """700 consecutive frames of the reference's own scene-3 rollout, teacher-forced on its positions: sight-line gate,
+    lost_frames replans (from frame 361), the two-per-frame replan limit in table order, an unreachable replan (agent
+    inside the inflated pillar: no plan, local_goal = own position) and LMP::lookahead give the reference's num_done
+    and local_goal for all 60 agents in every frame."""
+    first_bad, replans = _walled.follow(_golden_rollout(), _walled.SCENE3_WALLS)
+    assert first_bad is None, "differs from the reference at frame %s" % first_bad
+    assert replans >= 20
+
+
+@pytest.mark.skipif(not _oref.available(), reason="oracle/_ref/oref not built (needs /root/reference)")
+def test_live_walled_scene3_full_rollout_bookkeeping():
+    """The same replay over a complete live rollout (to all_done) with other weights."""
+    from learn_comms_b200 import workloads as wl
+    m_cv, m_f = wl.weights(9)
+    r = _oref.run(3, 0, m_cv, m_f, dump_every=1)
+    first_bad, replans = _walled.follow(r, _walled.SCENE3_WALLS)
+    assert first_bad is None, "differs from the reference at frame %s" % first_bad
+    assert r["n_walls"] == 1 and replans > 0
