@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <string>
 #include <vector>
 
@@ -382,11 +383,24 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
 #undef CKC
 }
 
+// no exception crosses the C ABI (learn_comms.h): allocation failures of the host containers become LC_ERR_CAPACITY
+static int create_guarded(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out) {
+    try {
+        return create_impl(d, dom, out);
+    } catch (const std::exception& e) {
+        if (out) *out = nullptr;
+        return fail(LC_ERR_CAPACITY, "lc_create: host allocation failed (%s)", e.what());
+    } catch (...) {
+        if (out) *out = nullptr;
+        return fail(LC_ERR_CAPACITY, "lc_create: host allocation failed");
+    }
+}
+
 extern "C" {
-int32_t lc_create(const lc_desc* d, lc_sim** out) { return create_impl(d, nullptr, out); }
+int32_t lc_create(const lc_desc* d, lc_sim** out) { return create_guarded(d, nullptr, out); }
 int32_t lc_dd_create(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out) {
     if (!dom) return fail(LC_ERR_ARG, "lc_dd_create: null domain description");
-    return create_impl(d, dom, out);
+    return create_guarded(d, dom, out);
 }
 }  // extern "C"
 
@@ -394,11 +408,19 @@ int32_t lc_dd_create(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out) 
     if (!(s)) return fail(LC_ERR_ARG, "%s: null handle", __func__);    \
     CK(cudaSetDevice((s)->device))
 
+// the status a device-side error maps to (Ctl::error holds the lc_status of the first one), from the host copy of Ctl
+static int device_error(lc_sim* s) {
+    const int e = s->hctl->error;
+    if (!e) return LC_OK;
+    const char* what = e == LC_ERR_STATE ? "non-finite state or an agent without comm partner, comm.cpp:273-285"
+                     : e == LC_ERR_CAPACITY ? "a fixed-capacity exchange / candidate / event buffer overflowed"
+                     : e == LC_ERR_CUDA ? "a peer rank did not arrive (spin time-out)" : "unexpected";
+    return fail(e, "device-side error %d at frame %u (%s)", e, s->hctl->frame, what);
+}
 static int check_device_error(lc_sim* s) {
     int rc = read_ctl(s);
     if (rc) return rc;
-    if (s->hctl->error) return fail(s->hctl->error, "device-side error %d at frame %u (non-finite state or an agent without comm partner)", s->hctl->error, s->hctl->frame);
-    return 0;
+    return device_error(s);
 }
 
 extern "C" {
@@ -450,7 +472,7 @@ int32_t lc_finished(lc_sim* s, int32_t* finished, uint32_t* frame) {
     if (rc) return rc;
     if (finished) *finished = s->hctl->finished;
     if (frame) *frame = s->hctl->frame;
-    return LC_OK;
+    return device_error(s);  // a host that only steps and polls still sees Ctl::error
 }
 
 int32_t lc_run_to_completion(lc_sim* s, int32_t* frames) {
@@ -473,8 +495,9 @@ int32_t lc_get_state(lc_sim* s, float* pos, float* vel, float* vfh, float* c, fl
     SIM_ENTER(s);
     const size_t n = (size_t)s->n_ids;
     float* st = s->stage;
+    // float2 tables first: every offset is a multiple of 2 n floats, i.e. 8-byte aligned for odd n too
     float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
-    float* dc = st + 6 * n; float2* dfac = (float2*)(st + 9 * n); float2* dlg = (float2*)(st + 11 * n);
+    float2* dfac = (float2*)(st + 6 * n); float2* dlg = (float2*)(st + 8 * n); float* dc = st + 10 * n;
     float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
     if (s->dd_world > 1) {  // domain mode: entries of agents owned by other ranks read as zero; lc_dd_get_owned tells which
         CK(cudaMemsetAsync(st, 0, sizeof(float) * s->stage_floats, s->st));
@@ -491,18 +514,18 @@ int32_t lc_get_state(lc_sim* s, float* pos, float* vel, float* vfh, float* c, fl
     if (lgoal) CK(cudaMemcpyAsync(lgoal, dlg, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
     if (goal_dist) CK(cudaMemcpyAsync(goal_dist, dgd, sizeof(float) * n, cudaMemcpyDeviceToHost, s->st));
     if (num_done) CK(cudaMemcpyAsync(num_done, dnd, sizeof(int) * n, cudaMemcpyDeviceToHost, s->st));
-    CK(cudaStreamSynchronize(s->st));
-    return LC_OK;
+    return check_device_error(s);  // synchronises; the tables are delivered either way
 }
 
 int32_t lc_set_state(lc_sim* s, const float* pos, const float* vel, const float* vfh, const float* c,
                      const float* facing, const float* lgoal, const float* goal_dist, const int32_t* num_done) {
     SIM_ENTER(s);
-    if (s->dd_world > 1) return fail(LC_ERR_ARG, "lc_set_state: not available for a domain-decomposed crowd (pass the initial tables to lc_dd_create)");
+    if (s->dd_world > 1) return fail(LC_ERR_STATE, "lc_set_state: not available for a domain-decomposed crowd (pass the initial tables to lc_dd_create)");
     const size_t n = (size_t)s->n;
     float* st = s->stage;
+    // float2 tables first: every offset is a multiple of 2 n floats, i.e. 8-byte aligned for odd n too
     float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
-    float* dc = st + 6 * n; float2* dfac = (float2*)(st + 9 * n); float2* dlg = (float2*)(st + 11 * n);
+    float2* dfac = (float2*)(st + 6 * n); float2* dlg = (float2*)(st + 8 * n); float* dc = st + 10 * n;
     float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
     if (pos) CK(cudaMemcpyAsync(dpos, pos, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
     if (vel) CK(cudaMemcpyAsync(dvel, vel, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st));
@@ -699,12 +722,12 @@ int32_t lc_dd_get_owned(lc_sim* s, int32_t* owned) {
 int32_t lc_dd_get_shard(lc_sim* s, int32_t* ids, float* pos, float* vel, int32_t cap, int32_t* count) {
     SIM_ENTER(s);
     if (s->dd_world <= 1 || !ids || !count) return fail(LC_ERR_ARG, "lc_dd_get_shard: bad argument");
-    // staging: [count | ids (cap) | pos (2 cap) | vel (2 cap)]; the rank never holds more than s->n agents
+    // staging: [count (16 B) | pos (2 cap) | vel (2 cap) | ids (cap)]; the rank never holds more than s->n agents
     const size_t m = (size_t)s->n;
     int* dcount = (int*)s->stage;
-    int* dids = dcount + 4;
-    float2* dpos = (float2*)(dids + m);
+    float2* dpos = (float2*)(dcount + 4);   // 16-byte header, then the float2 tables, ids last: aligned for odd m
     float2* dvel = dpos + m;
+    int* dids = (int*)(dvel + m);
     if ((4 + 5 * m) > s->stage_floats) return fail(LC_ERR_CAPACITY, "lc_dd_get_shard: staging too small");
     CK(cudaMemsetAsync(dcount, 0, sizeof(int), s->st));
     lc::launch_get_owned(s->dP, s->n, s->b, dids, dpos, dvel, dcount, s->st, &s->launches);
@@ -715,8 +738,7 @@ int32_t lc_dd_get_shard(lc_sim* s, int32_t* ids, float* pos, float* vel, int32_t
     CK(cudaMemcpyAsync(ids, dids, sizeof(int) * k, cudaMemcpyDeviceToHost, s->st));
     if (pos) CK(cudaMemcpyAsync(pos, dpos, sizeof(float2) * k, cudaMemcpyDeviceToHost, s->st));
     if (vel) CK(cudaMemcpyAsync(vel, dvel, sizeof(float2) * k, cudaMemcpyDeviceToHost, s->st));
-    CK(cudaStreamSynchronize(s->st));
-    return LC_OK;
+    return check_device_error(s);
 }
 
 int32_t lc_dd_get_partials(lc_sim* s, uint64_t* lastvel, int32_t* nonfinite, float* avg_velocity_before) {

@@ -136,11 +136,18 @@ extern "C" {
 int32_t lc_planner_create(int32_t n_walls, const lc_rect* walls, float agent_radius, lc_planner** out) {
     if (!out || n_walls < 0 || (n_walls > 0 && !walls) || !(agent_radius > 0.f))
         return lc_set_error(LC_ERR_ARG, "lc_planner_create: bad arguments");
-    lc_planner* p = new lc_planner();
-    p->agent_r = agent_radius;
-    for (int32_t k = 0; k < n_walls; ++k) p->walls.push_back({walls[k].ox, walls[k].oy, walls[k].w, walls[k].h});
-    p->sample();
-    p->connect();
+    lc_planner* p = nullptr;
+    try {  // no exception crosses the C ABI
+        p = new lc_planner();
+        p->agent_r = agent_radius;
+        for (int32_t k = 0; k < n_walls; ++k) p->walls.push_back({walls[k].ox, walls[k].oy, walls[k].w, walls[k].h});
+        p->sample();
+        p->connect();
+    } catch (...) {
+        delete p;
+        *out = nullptr;
+        return lc_set_error(LC_ERR_CAPACITY, "lc_planner_create: host allocation failed");
+    }
     *out = p;
     return LC_OK;
 }
@@ -161,13 +168,18 @@ int32_t lc_planner_plan(lc_planner* p, const float* start, const float* goal, in
     if (!p || !start || !goal || cap < 0 || (cap > 0 && !waypoints) || !n_waypoints)
         return lc_set_error(LC_ERR_ARG, "lc_planner_plan: bad arguments");
     // GMP.cpp:93-110 plan_one: start and goal join the roadmap for the duration of the search
-    uint32_t s = p->add_vertex({start[0], start[1]});
-    uint32_t g = p->add_vertex({goal[0], goal[1]});
-    p->connect_to_all(s);
-    p->connect_to_all(g);
-    std::vector<lc_planner::P> path = p->astar(s, g);
-    p->del_vertex(s);
-    p->del_vertex(g);
+    std::vector<lc_planner::P> path;
+    try {
+        uint32_t s = p->add_vertex({start[0], start[1]});
+        uint32_t g = p->add_vertex({goal[0], goal[1]});
+        p->connect_to_all(s);
+        p->connect_to_all(g);
+        path = p->astar(s, g);
+        p->del_vertex(s);
+        p->del_vertex(g);
+    } catch (...) {
+        return lc_set_error(LC_ERR_CAPACITY, "lc_planner_plan: host allocation failed");
+    }
     *n_waypoints = (int32_t)path.size();
     if (min_time) {  // ai.cpp:118-126: path length minus the untimed last metre (ai::at_dist)
         float t = -1.f;

@@ -121,6 +121,24 @@ def test_domain_nocomm_and_dense():
     assert hits > 0
 
 
+def test_domain_odd_capacity_shard_tables():
+    """Odd slot capacity (the default for 1M agents on 3 ranks is odd): the float2 tables of the lc_dd_get_shard staging
+    must stay 8-byte aligned."""
+    pos, goal = _crowd(1001, 80.0, 20.0, seed=5)
+    m_cv, m_f = wl.weights(2, 0.5)
+    sims = _make(pos, goal, 100.0, 9, m_cv, m_f, 2, capacity=1501, halo_capacity=333)
+    ref = lcb.Sim(pos, goal, m_cv, m_f, max_duration=100.0, rng_state=9)
+    lcb.DomainSim.step_all(sims, 12)
+    ref.step(12)
+    _assert_same(sims, ref, "odd capacity")
+    full = ref.state()
+    for s in sims:
+        assert s.counts()[1] == 1501
+        sh, k = s.shard()
+        ids = sh["ids"][:k]
+        assert np.array_equal(sh["pos"][:k], full["pos"][ids]) and np.array_equal(sh["vel"][:k], full["vel"][ids])
+
+
 def test_domain_error_paths():
     pos, goal = _crowd(500, 30.0, 30.0, seed=1)
     with pytest.raises(lcb.LcError):

@@ -202,6 +202,37 @@ def test_full_size_properties_plaza():
     assert (np.hypot(s["vfh"][:, 0], s["vfh"][:, 1]) <= 1.0 + 1e-3).all()
 
 
+@pytest.mark.parametrize("n", [33, 201])
+def test_odd_agent_count_state_tables(n):
+    """Odd agent counts: every sub-table of the lc_get_state / lc_set_state staging must stay aligned for its vector
+    type (float2 tables at offsets that are odd multiples of 4 bytes fault with cudaErrorMisalignedAddress)."""
+    pos, goal, md, rng = wl.plaza(n, 14.0, seed=n, goal_range=10.0)
+    m_cv, m_f = wl.weights(n)
+    g, o = lockstep(pos, goal, 30.0, rng, m_cv, m_f, frames=20, check_every=5)
+    st = g.state()
+    g.set_state(**st)
+    g.step(5)
+    o.step(5)
+    assert_state_equal(g.state(), o.state(), f"n = {n} after a set_state round trip")
+
+
+def test_device_error_surfaces_without_run_to_completion():
+    """A host that only steps and reads tables (the loop INTEGRATION.md recommends) must see Ctl::error: a non-finite
+    position poisons the grid set-up (LC_ERR_STATE) and lc_finished / lc_get_state report it."""
+    pos, goal, md, rng = lcb.scene(0, 0)
+    g = lcb.Sim(pos, goal, None, None, max_duration=md, rng_state=rng)
+    g.step(2)
+    st = g.state()
+    st["pos"][3] = np.nan
+    g.set_state(**st)
+    g.step(2)
+    with pytest.raises(lcb.LcError) as e:
+        _ = g.finished
+    assert e.value.code == -3
+    with pytest.raises(lcb.LcError):
+        g.state()
+
+
 def test_error_paths():
     pos, goal, md, rng = lcb.scene(0, 0)
     with pytest.raises(lcb.LcError):
