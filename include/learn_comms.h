@@ -48,6 +48,11 @@ typedef struct lc_desc {
     int32_t n_walls;        /* reserved for walled scenes; must be 0 */
     const lc_rect* walls;
     int32_t stencil;        /* grid cells per interaction cutoff (0 = default 2): cell side = cutoff / stencil */
+    const int32_t* table_order; /* [n] permutation: table_order[k] = index of the k-th agent the reference's component-table
+                                 * loops visit (quirk Q4: std::unordered_map order, Pool.h:24, Pool.cpp:156-160).  Decides
+                                 * which minstd_rand0 draw an agent gets, the order forces / hits / Welford updates are
+                                 * summed in, arg-max ties and the two replan slots.  NULL = ascending index.  lc_table_order
+                                 * returns the reference's own order; the comm_norender drop-in uses it. */
 } lc_desc;
 
 typedef struct lc_sim lc_sim;
@@ -140,6 +145,7 @@ typedef struct lc_batch_desc {
     float radius;
     uint32_t flags;
     int32_t device;
+    const int32_t* table_order; /* [n_agents] as in lc_desc, shared by all scenarios; NULL = ascending index */
 } lc_batch_desc;
 int32_t lc_batch_create(const lc_batch_desc* desc, lc_batch** out);
 void lc_batch_destroy(lc_batch* b);
@@ -165,6 +171,11 @@ int64_t lc_batch_kernel_launches(lc_batch* b);
 /* ---- files: comm::init / comm::terminate formats (comm.cpp:74-142, pso_opt.py:17-41) ---- */
 int32_t lc_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);
 int32_t lc_write_result(const char* path, float avg_velocity, float group_time);
+
+/* ---- iteration order of the reference's component tables (quirk Q4; Pool.h:24, Pool.cpp:7-16,156-160) for a scene
+ * with n_agents robots followed by n_walls walls (demo.cpp:628-635): agent_order[n_agents], wall_order[n_walls] (either may
+ * be NULL when its count is 0).  Ascending when the scene exceeds the reference's 65 535 entities (Entity.h:12). ---- */
+int32_t lc_table_order(int32_t n_agents, int32_t n_walls, int32_t* agent_order, int32_t* wall_order);
 
 /* ---- scene catalogue (demo.cpp:141-511), wall-free scenes; returns agent count or negative status ---- */
 int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,

@@ -20,7 +20,7 @@ class _Desc(C.Structure):
     _fields_ = [("n", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p), ("radius", C.c_float),
                 ("max_duration", C.c_float), ("rng_state", C.c_uint32), ("m_cv", C.c_void_p), ("m_f", C.c_void_p),
                 ("flags", C.c_uint32), ("device", C.c_int32), ("n_walls", C.c_int32), ("walls", C.c_void_p),
-                ("stencil", C.c_int32)]
+                ("stencil", C.c_int32), ("table_order", C.c_void_p)]
 
 
 class _DomainDesc(C.Structure):
@@ -31,7 +31,7 @@ class _DomainDesc(C.Structure):
 class _BatchDesc(C.Structure):
     _fields_ = [("n_scenarios", C.c_int32), ("n_agents", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p),
                 ("m_cv", C.c_void_p), ("m_f", C.c_void_p), ("max_duration", C.c_void_p), ("rng_state", C.c_void_p),
-                ("radius", C.c_float), ("flags", C.c_uint32), ("device", C.c_int32)]
+                ("radius", C.c_float), ("flags", C.c_uint32), ("device", C.c_int32), ("table_order", C.c_void_p)]
 
 
 EXPORTS = [
@@ -41,7 +41,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_table_order", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -98,6 +98,7 @@ def lib():
         L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
+        L.lc_table_order.argtypes = [i32, i32, vp, vp]
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
         L.lc_lookahead.argtypes = [i32, vp, C.c_float, i32, vp, vp, i32]
         L.lc_planner_create.argtypes = [i32, vp, C.c_float, C.POINTER(vp)]
@@ -129,6 +130,25 @@ def scene(scene_id, seed=0):
     if n <= 0:
         raise LcError(n, f"scene {scene_id} is not in the wall-free catalogue")
     return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value)
+
+
+def table_order(n_agents, n_walls=0):
+    """Iteration order of the reference's component tables (quirk Q4, lc_table_order): (agent_order, wall_order)."""
+    a = np.zeros(max(n_agents, 1), np.int32)
+    w = np.zeros(max(n_walls, 1), np.int32)
+    _ck(lib().lc_table_order(n_agents, n_walls, _p(a), _p(w)))
+    return a[:n_agents].copy(), w[:n_walls].copy()
+
+
+def _order(order, n):
+    if order is None:
+        return None
+    if isinstance(order, str):
+        assert order == "reference"
+        return table_order(n)[0]
+    o = np.ascontiguousarray(order, np.int32)
+    assert o.shape == (n,)
+    return o
 
 
 def wall_geometry(records, device=0):
@@ -210,15 +230,18 @@ class Sim:
     """One crowd resident on one GPU.  step(k) runs k frames of main.cpp:98-150."""
 
     def __init__(self, pos, goal, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15, comm=True,
-                 free_run=False, debug_lists=False, device=0, stencil=0):
+                 free_run=False, debug_lists=False, device=0, stencil=0, order=None):
+        """order: table iteration order (lc_desc::table_order) — None = ascending index, "reference" = the reference's
+        own (lc_table_order), or an explicit permutation."""
         self.n = int(pos.shape[0])
+        self._order = _order(order, self.n)
         pos = np.ascontiguousarray(pos, np.float32)
         goal = np.ascontiguousarray(goal, np.float32)
         m_cv = None if m_cv is None else np.ascontiguousarray(m_cv, np.float32)
         m_f = None if m_f is None else np.ascontiguousarray(m_f, np.float32)
         flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0) | (FLAG_DEBUG_LISTS if debug_lists else 0)
         d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0,
-                  None, stencil)
+                  None, stencil, _p(self._order))
         h = C.c_void_p()
         self.h = None
         _ck(lib().lc_create(C.byref(d), C.byref(h)))
@@ -318,7 +341,7 @@ class Sim:
         ptr = np.zeros(self.n + 1, np.int64)
         np.cumsum(cnt, out=ptr[1:])
         idx = np.concatenate([dense[i, :cnt[i]] for i in range(self.n)]) if self.n else np.zeros(0, np.int32)
-        return ptr, idx.astype(np.int32)
+        return ptr, idx.astype(np.int32)  # rows by agent index; entries in table order (ascending index by default)
 
     def counters(self):
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
@@ -352,8 +375,9 @@ class DomainSim(Sim):
     connect_dist().  state() returns global-size arrays that are zero outside the rank's own agents plus `owned`."""
 
     def __init__(self, pos, goal, rank, world, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15, comm=True,
-                 free_run=False, device=0, stencil=0, x_bounds=None, capacity=0, halo_capacity=0, vel=None, vfh=None):
+                 free_run=False, device=0, stencil=0, x_bounds=None, capacity=0, halo_capacity=0, vel=None, vfh=None, order=None):
         self.n = int(pos.shape[0])
+        self._order = _order(order, self.n)
         self.rank, self.world, self.device = int(rank), int(world), int(device)
         pos = np.ascontiguousarray(pos, np.float32)
         goal = np.ascontiguousarray(goal, np.float32)
@@ -363,7 +387,8 @@ class DomainSim(Sim):
         vel = None if vel is None else np.ascontiguousarray(vel, np.float32)
         vfh = None if vfh is None else np.ascontiguousarray(vfh, np.float32)
         flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0)
-        d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0, None, stencil)
+        d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0, None, stencil,
+                  _p(self._order))
         dom = _DomainDesc(rank, world, _p(xb), capacity, halo_capacity, _p(vel), _p(vfh))
         h = C.c_void_p()
         self.h = None
@@ -493,15 +518,16 @@ class DomainSim(Sim):
 class Batch:
     """Many independent small scenarios in one launch (pso_opt.py:236-267 simulate_set, in process)."""
 
-    def __init__(self, pos, goal, m_cv, m_f, max_duration, rng_state, radius=0.15, comm=True, device=0):
+    def __init__(self, pos, goal, m_cv, m_f, max_duration, rng_state, radius=0.15, comm=True, device=0, order=None):
         S, n = pos.shape[0], pos.shape[1]
         self.S, self.n = int(S), int(n)
+        self._order = _order(order, self.n)
         self._keep = [np.ascontiguousarray(pos, np.float32), np.ascontiguousarray(goal, np.float32),
                       np.ascontiguousarray(m_cv, np.float32), np.ascontiguousarray(m_f, np.float32),
                       np.ascontiguousarray(np.broadcast_to(np.asarray(max_duration, np.float32), (S,))),
                       np.ascontiguousarray(np.broadcast_to(np.asarray(rng_state, np.uint32), (S,)))]
         assert self._keep[2].shape == (S, 3, 8) and self._keep[3].shape == (S, 2, 3)
-        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, 0 if comm else FLAG_NO_COMM, device)
+        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, 0 if comm else FLAG_NO_COMM, device, _p(self._order))
         h = C.c_void_p()
         self.h = None
         _ck(lib().lc_batch_create(C.byref(d), C.byref(h)))

@@ -94,6 +94,10 @@ int main(int argc, char** argv) {
     memset(&d, 0, sizeof d);
     d.n = n; d.pos = pos.data(); d.goal = goal.data(); d.radius = 0.15f; d.max_duration = max_duration;
     d.rng_state = rng; d.m_cv = m_cv; d.m_f = m_f; d.flags = flags; d.device = 0;
+    // the reference's component-table iteration order (quirk Q4): which RNG draw an agent gets, summation and Welford order
+    std::vector<int32_t> order((size_t)n);
+    if (lc_table_order(n, 0, order.data(), nullptr) != LC_OK) lib_error("lc_table_order");
+    d.table_order = order.data();
     lc_sim* sim = nullptr;
     if (lc_create(&d, &sim) != LC_OK) lib_error("lc_create");
     int32_t frames = 0;
@@ -102,8 +106,8 @@ int main(int argc, char** argv) {
     } else {
         // demo.cpp:616,678-684: one row per agent and frame, written by demo::run BEFORE the frame is simulated:
         //   id,groupID(0),pos.x,pos.z,vel.x,vel.z,radius,dt*(frame-1)     (default ostream float formatting)
-        // id: the reference prints its ECS entity id; here the agent's table index + 1 (fix_paths.py:15-25 only uses
-        // it as a key).  Rows of a frame come in ascending id instead of the reference's hash-map order.
+        // id: the ECS entity id = creation index + 1 (demo.cpp:628-631); rows of a frame come in the reference's table
+        // iteration order (POOL.for_<Agent>, Pool.cpp:156-160).
         std::ofstream paths(data_dir + "/agent_paths.csv", std::ios::binary);
         if (!paths) { fprintf(stderr, "cannot write %s/agent_paths.csv\n", data_dir.c_str()); return EXIT_FAILURE; }
         std::vector<float> p(2 * (size_t)n), v(2 * (size_t)n);
@@ -111,9 +115,11 @@ int main(int argc, char** argv) {
         for (;;) {
             if (lc_get_state(sim, p.data(), v.data(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr) != LC_OK) lib_error("lc_get_state");
             const float t = dt * static_cast<float>(frames);
-            for (int i = 0; i < n; ++i)
+            for (int k = 0; k < n; ++k) {
+                const int i = order[k];
                 paths << (i + 1) << ",0," << p[2 * i] << "," << p[2 * i + 1] << "," << v[2 * i] << "," << v[2 * i + 1] << ","
                       << d.radius << "," << t << "\n";
+            }
             if (lc_step(sim, 1) != LC_OK) lib_error("lc_step");
             ++frames;
             int32_t fin = 0;

@@ -463,6 +463,13 @@ struct lc_batch {
     std::vector<float2> h_goal, h_facing;
     std::vector<int4> h_meta;
     lcbatch::ScenarioCtl* h_ctl = nullptr;
+    std::vector<int> order;  // lc_batch_desc::table_order: order[i] = caller's agent index of engine agent i (empty = identity)
+    // index of engine agent g (scenario-major) in the caller's tables
+    size_t ext(size_t g) const {
+        if (order.empty()) return g;
+        const size_t n = (size_t)a.n;
+        return (g / n) * n + (size_t)order[g % n];
+    }
 };
 
 static uint32_t b_lcg_pow(uint32_t a, uint64_t e) {
@@ -527,6 +534,15 @@ int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
     lc_batch* b = new lc_batch;
     b->device = d->device;
     const int S = b->a.S = d->n_scenarios, n = b->a.n = d->n_agents;
+    if (d->table_order) {
+        std::vector<char> seen((size_t)n, 0);
+        for (int i = 0; i < n; ++i) {
+            const int e = d->table_order[i];
+            if (e < 0 || e >= n || seen[e]) { delete b; return bfail(LC_ERR_ARG, "lc_batch_create: table_order is not a permutation of 0..n-1"); }
+            seen[e] = 1;
+        }
+        b->order.assign(d->table_order, d->table_order + n);
+    }
     const size_t N = (size_t)S * n;
 #define BCKB(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { bfail(LC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); lc_batch_destroy(b); return LC_ERR_CUDA; } } while (0)
     BCKB(cudaStreamCreateWithFlags(&b->st, cudaStreamNonBlocking));
@@ -558,8 +574,8 @@ int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
     for (int s = 0; s < S; ++s) {
         uint32_t x = d->rng_state[s];
         for (int i = 0; i < n; ++i) {
-            const size_t g = (size_t)s * n + i;
-            const float px = d->pos[2 * g], py = d->pos[2 * g + 1], gx = d->goal[2 * g], gy = d->goal[2 * g + 1];
+            const size_t g = (size_t)s * n + i, e = b->ext(g);  // engine agent i = table position; e = the caller's index
+            const float px = d->pos[2 * e], py = d->pos[2 * e + 1], gx = d->goal[2 * e], gy = d->goal[2 * e + 1];
             const float dx = gx - px, dy = gy - py;
             const float len = sqrtf(dx * dx + dy * dy);  // glm::length (ai.cpp:116)
             float mtime = -1.0f;                         // ai.cpp:121-126
@@ -646,23 +662,29 @@ int32_t lc_batch_get_state(lc_batch* b, float* pos, float* vel, float* vfh, floa
     if (pos || vel) {
         BCK(cudaMemcpy(pv.data(), b->a.pv, sizeof(float4) * N, cudaMemcpyDeviceToHost));
         for (size_t g = 0; g < N; ++g) {
-            if (pos) { pos[2 * g] = pv[g].x; pos[2 * g + 1] = pv[g].y; }
-            if (vel) { vel[2 * g] = pv[g].z; vel[2 * g + 1] = pv[g].w; }
+            const size_t e = b->ext(g);
+            if (pos) { pos[2 * e] = pv[g].x; pos[2 * e + 1] = pv[g].y; }
+            if (vel) { vel[2 * e] = pv[g].z; vel[2 * e + 1] = pv[g].w; }
         }
     }
-    if (vfh) BCK(cudaMemcpy(vfh, b->a.vfh, sizeof(float2) * N, cudaMemcpyDeviceToHost));
-    if (facing) BCK(cudaMemcpy(facing, b->a.facing, sizeof(float2) * N, cudaMemcpyDeviceToHost));
-    if (lgoal) BCK(cudaMemcpy(lgoal, b->a.lgoal, sizeof(float2) * N, cudaMemcpyDeviceToHost));
+    for (int t = 0; t < 3; ++t) {
+        float* dst = t == 0 ? vfh : t == 1 ? facing : lgoal;
+        const float2* src = t == 0 ? b->a.vfh : t == 1 ? b->a.facing : b->a.lgoal;
+        if (!dst) continue;
+        BCK(cudaMemcpy(f2.data(), src, sizeof(float2) * N, cudaMemcpyDeviceToHost));
+        for (size_t g = 0; g < N; ++g) { const size_t e = b->ext(g); dst[2 * e] = f2[g].x; dst[2 * e + 1] = f2[g].y; }
+    }
     if (c || goal_dist) {
         BCK(cudaMemcpy(c4.data(), b->a.c4, sizeof(float4) * N, cudaMemcpyDeviceToHost));
         for (size_t g = 0; g < N; ++g) {
-            if (c) { c[3 * g] = c4[g].x; c[3 * g + 1] = c4[g].y; c[3 * g + 2] = c4[g].z; }
-            if (goal_dist) goal_dist[g] = c4[g].w;
+            const size_t e = b->ext(g);
+            if (c) { c[3 * e] = c4[g].x; c[3 * e + 1] = c4[g].y; c[3 * e + 2] = c4[g].z; }
+            if (goal_dist) goal_dist[e] = c4[g].w;
         }
     }
     if (num_done) {
         BCK(cudaMemcpy(mt.data(), b->a.meta, sizeof(int4) * N, cudaMemcpyDeviceToHost));
-        for (size_t g = 0; g < N; ++g) num_done[g] = mt[g].x & 1;
+        for (size_t g = 0; g < N; ++g) num_done[b->ext(g)] = mt[g].x & 1;
     }
     return LC_OK;
 }
@@ -675,9 +697,16 @@ int32_t lc_batch_get_diag(lc_batch* b, int32_t* partner, int32_t* neighbor_count
     if (partner) {
         std::vector<int4> mt(N);
         BCK(cudaMemcpy(mt.data(), b->a.meta, sizeof(int4) * N, cudaMemcpyDeviceToHost));
-        for (size_t g = 0; g < N; ++g) partner[g] = mt[g].w;
+        for (size_t g = 0; g < N; ++g) {
+            const int pj = mt[g].w;  // engine index within the scenario
+            partner[b->ext(g)] = (pj >= 0 && !b->order.empty()) ? b->order[pj] : pj;
+        }
     }
-    if (neighbor_count) BCK(cudaMemcpy(neighbor_count, b->a.nbr_cnt, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    if (neighbor_count) {
+        std::vector<int> cnt(N);
+        BCK(cudaMemcpy(cnt.data(), b->a.nbr_cnt, sizeof(int) * N, cudaMemcpyDeviceToHost));
+        for (size_t g = 0; g < N; ++g) neighbor_count[b->ext(g)] = cnt[g];
+    }
     BCK(cudaMemcpy(b->h_ctl, b->a.ctl, sizeof(lcbatch::ScenarioCtl) * (size_t)b->a.S, cudaMemcpyDeviceToHost));
     for (int s = 0; s < b->a.S; ++s) {
         if (overlap_pairs) overlap_pairs[s] = (int64_t)(b->h_ctl[s].overlap2 / 2);

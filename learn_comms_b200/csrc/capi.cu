@@ -85,6 +85,8 @@ struct lc_sim {
     float* stage = nullptr;
     size_t stage_floats = 0;
     lc::Ctl* hctl = nullptr;
+    int* ext_of = nullptr;     // device copy of lc_desc::table_order (nullptr = ascending)
+    int* xlate = nullptr;      // staging for diagnostics translated to the caller's agent indices
     std::vector<void*> allocs;
 };
 
@@ -172,8 +174,18 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         return fail(LC_ERR_CUDA, "lc_create: no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
     if (d->device < 0 || d->device >= ndev) return fail(LC_ERR_ARG, "lc_create: device %d out of range", d->device);
     CK(cudaSetDevice(d->device));
-    // ---- domain decomposition: strip bounds, the initially owned subset, capacities ----
     const int n_ids = d->n;
+    // table order (quirk Q4): engine id = position in the reference's table iteration order
+    const int32_t* order = d->table_order;
+    if (order) {
+        std::vector<char> seen((size_t)n_ids, 0);
+        for (int i = 0; i < n_ids; ++i) {
+            if (order[i] < 0 || order[i] >= n_ids || seen[order[i]]) return fail(LC_ERR_ARG, "lc_create: table_order is not a permutation of 0..n-1");
+            seen[order[i]] = 1;
+        }
+    }
+    auto ext = [order](int i) { return order ? order[i] : i; };
+    // ---- domain decomposition: strip bounds, the initially owned subset, capacities ----
     const int world = dom ? dom->world : 1, rank = dom ? dom->rank : 0;
     std::vector<int> ids;
     std::vector<float> xb(lc::DD_MAX_WORLD + 1, 0.f);
@@ -206,7 +218,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         for (int r = 1; r < world; ++r)
             if (!(xb[r] > xb[r - 1])) return fail(LC_ERR_ARG, "lc_dd_create: x_bounds must increase");
         for (int i = 0; i < n_ids; ++i) {
-            const float x = d->pos[2 * i];
+            const float x = d->pos[2 * ext(i)];
             if (x >= xb[rank] && x < xb[rank + 1]) ids.push_back(i);
         }
         cap_halo = dom->halo_capacity > 0 ? dom->halo_capacity : std::max(65536, n_ids / world / 2);
@@ -280,6 +292,13 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(cudaMallocHost((void**)&s->hctl, sizeof(lc::Ctl)));
     s->stage_floats = std::max((size_t)n_ids * 16, (size_t)8 + 5 * (size_t)n);  // lc_get_state tables / lc_dd_get_shard
     CKC(cudaMalloc((void**)&s->stage, sizeof(float) * s->stage_floats));
+    b.ext_of = nullptr;
+    if (order) {
+        CKC(dalloc(&s->ext_of, n_ids)); s->allocs.push_back(s->ext_of);
+        CKC(cudaMemcpy(s->ext_of, order, sizeof(int) * (size_t)n_ids, cudaMemcpyHostToDevice));
+        CKC(dalloc(&s->xlate, (size_t)n_ids * std::max(1, b.list_cap))); s->allocs.push_back(s->xlate);
+        b.ext_of = s->ext_of;
+    }
     b.dd = nullptr;
     if (dom) {
         s->lay = lc::domain_layout(world, n, cap_halo, n_ids);
@@ -341,7 +360,8 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         int* hid = reinterpret_cast<int*>(h.data() + 12 * m);  // [m]
         const bool has_v = dom && dom->vel && dom->vel_forehalf;
         for (size_t k = 0; k < m; ++k) {
-            const int i = dom ? ids[k] : (int)k;
+            const int id = dom ? ids[k] : (int)k;   // engine id (table position)
+            const int i = ext(id);                   // the caller's agent index
             hpos[2 * k] = d->pos[2 * i]; hpos[2 * k + 1] = d->pos[2 * i + 1];
             hgoal[2 * k] = d->goal[2 * i]; hgoal[2 * k + 1] = d->goal[2 * i + 1];
             float dx = d->goal[2 * i] - d->pos[2 * i], dy = d->goal[2 * i + 1] - d->pos[2 * i + 1];
@@ -351,7 +371,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
             float mn = -1.0f;                                 // ai.cpp:121-126
             mn += len;
             mt[k] = mn;
-            hid[k] = i;
+            hid[k] = id;
             if (has_v) {
                 hvel[2 * k] = dom->vel[2 * i]; hvel[2 * k + 1] = dom->vel[2 * i + 1];
                 hvfh[2 * k] = dom->vel_forehalf[2 * i]; hvfh[2 * k + 1] = dom->vel_forehalf[2 * i + 1];
@@ -584,7 +604,9 @@ int32_t lc_get_scores(lc_sim* s, float* avg_velocity, float* group_time, float* 
 int32_t lc_get_partners(lc_sim* s, int32_t* partner) {
     SIM_ENTER(s);
     lc::launch_get_diag(s->dP, s->n, s->b, s->st, &s->launches);
-    CK(cudaMemcpyAsync(partner, s->b.partner_id, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
+    const int* src = s->b.partner_id;
+    if (s->ext_of) { lc::launch_to_external(s->b, src, s->xlate, s->n_ids, 1, 1, s->st, &s->launches); src = s->xlate; }
+    CK(cudaMemcpyAsync(partner, src, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }
@@ -592,7 +614,9 @@ int32_t lc_get_partners(lc_sim* s, int32_t* partner) {
 int32_t lc_get_neighbor_counts(lc_sim* s, int32_t* count) {
     SIM_ENTER(s);
     lc::launch_get_diag(s->dP, s->n, s->b, s->st, &s->launches);
-    CK(cudaMemcpyAsync(count, s->b.nbr_cnt, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
+    const int* src = s->b.nbr_cnt;
+    if (s->ext_of) { lc::launch_to_external(s->b, src, s->xlate, s->n_ids, 1, 0, s->st, &s->launches); src = s->xlate; }
+    CK(cudaMemcpyAsync(count, src, sizeof(int) * (size_t)s->n_ids, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }
@@ -601,7 +625,9 @@ int32_t lc_get_neighbor_lists(lc_sim* s, int32_t* idx, int32_t cap) {
     SIM_ENTER(s);
     if (!s->b.nbr_list) return fail(LC_ERR_ARG, "lc_get_neighbor_lists: create the simulation with LC_FLAG_DEBUG_LISTS");
     if (cap != s->b.list_cap) return fail(LC_ERR_ARG, "lc_get_neighbor_lists: cap_per_agent must be %d", s->b.list_cap);
-    CK(cudaMemcpyAsync(idx, s->b.nbr_list, sizeof(int) * (size_t)s->n_ids * cap, cudaMemcpyDeviceToHost, s->st));
+    const int* src = s->b.nbr_list;   // rows and entries in table order (the order LMP.cpp:288-304 accumulates in)
+    if (s->ext_of) { lc::launch_to_external(s->b, src, s->xlate, s->n_ids, cap, 1, s->st, &s->launches); src = s->xlate; }
+    CK(cudaMemcpyAsync(idx, src, sizeof(int) * (size_t)s->n_ids * cap, cudaMemcpyDeviceToHost, s->st));
     CK(cudaStreamSynchronize(s->st));
     return LC_OK;
 }

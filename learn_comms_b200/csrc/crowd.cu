@@ -1247,7 +1247,7 @@ __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P,
     if (s >= P->n) return;
     const int4 mt = b.cur.meta[s];
     if (mt.y & META_GHOST) return;  // the owner reports it
-    const int id = mt.x;
+    const int id = b.ext_of ? b.ext_of[mt.x] : mt.x;  // the caller's agent index
     if (owned) owned[id] = 1;
     const float4 pv = b.cur.pv[s];
     const float4 c4 = b.cur.c4[s];
@@ -1286,7 +1286,7 @@ __global__ void __launch_bounds__(256) k_get_owned(const Params* __restrict__ P,
     if (own) {
         const int k = base + __popc(m & ((1u << (threadIdx.x & 31)) - 1u));
         const float4 pv = b.cur.pv[s];
-        ids[k] = mt.x;
+        ids[k] = b.ext_of ? b.ext_of[mt.x] : mt.x;
         pos[k] = b.posf[s];
         vel[k] = make_float2(pv.z, pv.w);
     }
@@ -1330,16 +1330,19 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
     float2 fc = init ? make_float2(0, 0) : b.srt.facing[so];
     float4 c4 = init ? make_float4(0, 0, 0, 0) : b.srt.c4[so];
     int4 mt = init ? make_int4(ids ? ids[i] : i, 0, 0, 0) : b.srt.meta[so];
-    if (pos) p = pos[i];
-    if (vel) { pv.z = vel[i].x; pv.w = vel[i].y; }
-    if (vfh) h = vfh[i];
-    if (c3) { c4.x = c3[3 * i]; c4.y = c3[3 * i + 1]; c4.z = c3[3 * i + 2]; }
-    if (facing) fc = facing[i];
-    if (lgoal) lg = lgoal[i];
-    if (goal_dist) c4.w = goal_dist[i];
-    if (num_done) mt.y = (mt.y & ~1) | (num_done[i] & 1);
-    if (goal) g = goal[i];
-    if (min_time) mt.w = __float_as_int(min_time[i]);
+    // host tables: at creation (init) they were gathered by the host in local order; afterwards they are indexed by the
+    // caller's agent index
+    const int e = (init || !b.ext_of) ? i : b.ext_of[i];
+    if (pos) p = pos[e];
+    if (vel) { pv.z = vel[e].x; pv.w = vel[e].y; }
+    if (vfh) h = vfh[e];
+    if (c3) { c4.x = c3[3 * e]; c4.y = c3[3 * e + 1]; c4.z = c3[3 * e + 2]; }
+    if (facing) fc = facing[e];
+    if (lgoal) lg = lgoal[e];
+    if (goal_dist) c4.w = goal_dist[e];
+    if (num_done) mt.y = (mt.y & ~1) | (num_done[e] & 1);
+    if (goal) g = goal[e];
+    if (min_time) mt.w = __float_as_int(min_time[e]);
     b.cur.pv[i] = make_float4(p.x, p.y, pv.z, pv.w);
     b.posf[i] = p;
     b.cur.vfh[i] = h;
@@ -1483,6 +1486,21 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
     else launch(k_collide<false>, cdiv(n, 128), 128, st, cP, b);
     if (ev) cudaEventRecord(ev[8], st);
     if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
+}
+
+__global__ void __launch_bounds__(256) k_to_external(const int* __restrict__ ext_of, const int* __restrict__ src, int* __restrict__ dst,
+                                                     int rows, int width, int values) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (long long)rows * width) return;
+    const int i = (int)(t / width), k = (int)(t % width);
+    int v = src[t];
+    if (values && v >= 0) v = ext_of[v];
+    dst[(size_t)ext_of[i] * width + k] = v;
+}
+void launch_to_external(const Buffers& b, const int* src, int* dst, int rows, int width, int values, cudaStream_t st, long long* launches) {
+    const long long tot = (long long)rows * width;
+    k_to_external<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(b.ext_of, src, dst, rows, width, values);
+    if (launches) *launches += 1;
 }
 
 void launch_get_diag(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {

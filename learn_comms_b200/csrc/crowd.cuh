@@ -128,6 +128,10 @@ struct Buffers {
     int* diag_cnt;     // [cap] by slot: interacting neighbours of the last frame (k_force)
     int* nbr_list;     // [n][list_cap] by id (LC_FLAG_DEBUG_LISTS)
     int list_cap;
+    // Table order (quirk Q4): the engine's agent ids are POSITIONS in the reference's table iteration order, so that
+    // "ascending id" everywhere in the kernels is the reference's loop order.  ext_of[id] = the caller's agent index;
+    // nullptr = identity.  Only the host-facing kernels (get / set state, diagnostics, shards) translate.
+    const int* ext_of;
     Ctl* ctl;
     struct DomainDev* dd;  // device-side exchange state (domain.cuh); nullptr for a single-GPU crowd
 };
@@ -166,6 +170,8 @@ void upload_dirs();
 constexpr int FRAME_KERNELS = 8;  // kernels per frame, in launch order: frame_begin, bin, scan_hull, reorder, refine, pairs, force, collide
 constexpr int DD_KERNELS = 0;     // domain mode: dd_sync_begin replaces frame_begin, the pack rides in k_collide, the candidate exchange in k_refine
 void launch_get_diag(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
+// dst[ext_of[i] * width + k] = (values ? ext_of[src[i * width + k]] (negative entries kept) : src[...]) for i < rows
+void launch_to_external(const Buffers& b, const int* src, int* dst, int rows, int width, int values, cudaStream_t st, long long* launches);
 void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);  // once, before the first frame
 // Side stream of a frame: k_refine (one block: second pruning stage and, in domain mode, the candidate exchange with the
 // peers) does not feed k_pairs, so the two run side by side (fork after k_reorder, join before k_force).

@@ -9,6 +9,7 @@
 #include <functional>
 #include <sstream>
 #include <string>
+#include <unordered_map>
 
 namespace {
 
@@ -108,6 +109,38 @@ int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t
     if (max_duration) *max_duration = md;
     if (rng_state_after) *rng_state_after = rng.x;
     return n;
+}
+
+// Iteration order of the reference's component tables (quirk Q4).  Every DataTable is a
+// std::unordered_map<uint16_t, ...> whose keys 1, 2, 3, ... are emplaced in ascending order and never erased
+// (Pool.cpp:7-16), and every loop of the frame (comm.cpp:268,288; ai.cpp:153; LMP.cpp:288; physics.cpp:39; demo.cpp:669,692)
+// walks such a table from begin() to end().  Which order that is belongs to libstdc++ (bucket growth policy, insertion at
+// the head of the node list), so the same standard container is put through the same insertions here and read back;
+// nothing of its internals is restated.  agent_order[k] = 0-based index of the k-th agent visited; wall_order[k] =
+// 0-based index of the k-th wall visited by the statics loop (LMP.cpp:307: walls are keys n+1 .. n+W of the BoundVolume*
+// table, demo.cpp:628-635).  More than 65 535 entities do not fit the reference's uint16_t ids (Entity.h:12): ascending.
+int32_t lc_table_order(int32_t n_agents, int32_t n_walls, int32_t* agent_order, int32_t* wall_order) {
+    if (n_agents < 0 || n_walls < 0 || (n_agents > 0 && !agent_order) || (n_walls > 0 && !wall_order)) return LC_ERR_ARG;
+    if ((int64_t)n_agents + n_walls > 65535) {
+        for (int32_t i = 0; i < n_agents; ++i) agent_order[i] = i;
+        for (int32_t i = 0; i < n_walls; ++i) wall_order[i] = i;
+        return LC_OK;
+    }
+    try {
+        std::unordered_map<uint16_t, char> agents, volumes;
+        for (int32_t k = 1; k <= n_agents; ++k) agents.emplace(std::piecewise_construct, std::forward_as_tuple((uint16_t)k), std::forward_as_tuple(0));
+        int32_t m = 0;
+        for (const auto& kv : agents) agent_order[m++] = (int32_t)kv.first - 1;
+        if (n_walls > 0) {
+            for (int32_t k = 1; k <= n_agents + n_walls; ++k) volumes.emplace(std::piecewise_construct, std::forward_as_tuple((uint16_t)k), std::forward_as_tuple(0));
+            m = 0;
+            for (const auto& kv : volumes)
+                if ((int32_t)kv.first > n_agents) wall_order[m++] = (int32_t)kv.first - 1 - n_agents;
+        }
+    } catch (...) {
+        return LC_ERR_CAPACITY;
+    }
+    return LC_OK;
 }
 
 // comm.cpp:80-121: 3 rows of 8 tokens (M_c | M_vy M_s M_py M_d M_g), then 2 rows whose first 3 tokens are M_f.

@@ -79,7 +79,9 @@ class BatchEvaluator:
     """Fixed set of scenario layouts (pos, goal, max_duration, rng per scenario), re-evaluated with new per-scenario
     parameter matrices every PSO iteration.  evaluate() returns full-length host arrays on every rank."""
 
-    def __init__(self, pos, goal, max_duration, rng_state, device=0, rank=0, world=1, dist=None, comm=True):
+    def __init__(self, pos, goal, max_duration, rng_state, device=0, rank=0, world=1, dist=None, comm=True, order="reference"):
+        """order: table iteration order of every scenario (lc_batch_desc::table_order).  Default = the reference's own
+        (quirk Q4), which is what the comm_norender processes pso_opt.py spawns would use."""
         self.S, self.n = int(pos.shape[0]), int(pos.shape[1])
         self.rank, self.world, self.dist = rank, world, dist
         self.lo, self.hi = shard_range(self.S, rank, world)
@@ -89,7 +91,7 @@ class BatchEvaluator:
             S_loc = self.hi - self.lo
             self.batch = api.Batch(pos[sl], goal[sl], np.zeros((S_loc, 3, 8), np.float32), np.zeros((S_loc, 2, 3), np.float32),
                                    np.asarray(max_duration, np.float32)[sl], np.asarray(rng_state, np.uint32)[sl],
-                                   comm=comm, device=device)
+                                   comm=comm, device=device, order=order)
         S_loc = self.hi - self.lo
         self.h2d_bytes = S_loc * (30 * 4 + self.n * (16 + 8 + 8 + 16 + 16))  # weights + the initial tables reset re-uploads
         self.d2h_bytes = S_loc * 56                                          # one control block per scenario
@@ -108,7 +110,7 @@ class BatchEvaluator:
         return out
 
 
-def simulate_set(scene_layouts, configs, device=0, rank=0, world=1, dist=None, comm=True):
+def simulate_set(scene_layouts, configs, device=0, rank=0, world=1, dist=None, comm=True, order="reference"):
     """pso_opt.py:236-242 simulate_set for MANY particles at once: scene_layouts = list of (pos[n,2], goal[n,2],
     max_duration, rng_state) with a common n (lc_scene output for the reference's scenes), configs = [P] 5 x 8 matrices.
     Returns fitness [P][len(scene_layouts)] (read_result's aggregate of each comms.result)."""
@@ -122,6 +124,6 @@ def simulate_set(scene_layouts, configs, device=0, rank=0, world=1, dist=None, c
     split = [split_config(c) for c in configs]
     m_cv = np.stack([split[s // L][0] for s in range(P * L)])
     m_f = np.stack([split[s // L][1] for s in range(P * L)])
-    ev = BatchEvaluator(pos, goal, md, rng, device=device, rank=rank, world=world, dist=dist, comm=comm)
+    ev = BatchEvaluator(pos, goal, md, rng, device=device, rank=rank, world=world, dist=dist, comm=comm, order=order)
     out = ev.evaluate(m_cv, m_f)
     return out["fitness"].reshape(P, L), out

@@ -680,8 +680,15 @@ void canon_get_partners(const canon_sim* s, int32_t* partner) { memcpy(partner, 
 void canon_get_neighbor_counts(const canon_sim* s, int32_t* cnt) { memcpy(cnt, s->nbr_cnt, sizeof(int32_t) * (size_t)s->n); }
 int64_t canon_get_neighbor_lists(const canon_sim* s, int64_t* row_ptr, int32_t* idx) {
     if (!s->nbr_ptr) return -1;
-    if (row_ptr) memcpy(row_ptr, s->nbr_ptr, sizeof(int64_t) * ((size_t)s->n + 1));
-    if (idx) memcpy(idx, s->nbr_idx, sizeof(int32_t) * (size_t)s->nbr_total);
+    /* rows were recorded in table order (nbr_ptr[i] = where agent i's row starts); hand out a proper CSR by agent index,
+     * each row still in the order LMP.cpp:288-304 visited the neighbours */
+    int64_t at = 0;
+    for (int i = 0; i < s->n; ++i) {
+        if (row_ptr) row_ptr[i] = at;
+        if (idx) memcpy(idx + at, s->nbr_idx + s->nbr_ptr[i], sizeof(int32_t) * (size_t)s->nbr_cnt[i]);
+        at += s->nbr_cnt[i];
+    }
+    if (row_ptr) row_ptr[s->n] = at;
     return s->nbr_total;
 }
 int64_t canon_overlap_pairs(const canon_sim* s) { return s->overlap_pairs; }

@@ -80,6 +80,31 @@ int main(int argc, char** argv) {
     Seeder s;
     s.seed(seed);
     demo::init(scene, data_dir);
+    // Optional: start every robot from the positions in $OREF_POS_FILE (float32 [n][2], entity-id order) instead of the
+    // scene's own — the 1-ulp-perturbation ensembles that calibrate the rollout tolerance (tools/make_golden_ensemble.py).
+    // Goals keep the scene's values; every mirror of the position that demo::create_robo / POOL.all_sync maintain
+    // (Dynamics.pos, Agent.start, BoundVolume._o, Transform, CommComp.facing = goal - start, demo.cpp:563-581) follows.
+    if (const char* pf = getenv("OREF_POS_FILE")) {
+        FILE* f = fopen(pf, "rb");
+        if (!f) { fprintf(stderr, "oref: cannot open %s\n", pf); return 2; }
+        std::vector<float> xy;
+        float v[2];
+        while (fread(v, sizeof(float), 2, f) == 2) { xy.push_back(v[0]); xy.push_back(v[1]); }
+        fclose(f);
+        const size_t m = xy.size() / 2;
+        POOL.for_<Agent>([&](Agent& a, Entity& e) {
+            if (e.id < 1 || e.id > m) return;
+            const glm::vec2 p(xy[2 * (e.id - 1)], xy[2 * (e.id - 1) + 1]);
+            Dynamics& d = *POOL.get<Dynamics>(e);
+            d.pos = glm::vec3(p.x, 0, p.y);
+            a.start = p;
+            (*POOL.get<BoundVolume*>(e))->_o = p;
+            POOL.get<Transform>(e)->set_pos(d.pos);
+#ifndef NO_COMM
+            POOL.get<CommComp>(e)->facing = a.final_goal - a.start;
+#endif
+        });
+    }
     comm::init(data_dir);
     ai::init();
     physics::init();

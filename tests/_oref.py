@@ -88,16 +88,40 @@ def write_config(path, m_cv, m_f):
             f.write(" ".join(repr(float(np.float32(v))) for v in row) + "\n")
 
 
-def run(scene, seed=0, m_cv=None, m_f=None, max_frames=100000, dump_every=1, comm=True, keep_dir=None):
+def run(scene, seed=0, m_cv=None, m_f=None, max_frames=100000, dump_every=1, comm=True, keep_dir=None, pos_override=None):
+    """One run of the reference's own translation units.  pos_override: float32 [n][2] start positions that replace the
+    scene's own (goals keep the scene's values) — the 1-ulp-perturbation ensembles."""
+    import shutil
     d = keep_dir or tempfile.mkdtemp(prefix="oref_")
     write_config(os.path.join(d, "comms.config"), m_cv, m_f)
     dump = os.path.join(d, "dump.bin")
     exe = OREF if comm else OREF_NOCOMM
+    env = dict(os.environ)
+    if pos_override is not None:
+        pf = os.path.join(d, "pos_override.f32")
+        np.ascontiguousarray(pos_override, np.float32).tofile(pf)
+        env["OREF_POS_FILE"] = pf
     subprocess.run([exe, str(scene), str(seed), d, str(max_frames), str(dump_every), dump], check=True,
-                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d)
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d, env=env)
     out = read_dump(dump)
     res = open(os.path.join(d, "comms.result")).read().split()
     out["result_file"] = (res[0], res[1])
+    if keep_dir is None:
+        shutil.rmtree(d, ignore_errors=True)
+    return out
+
+
+def perturb_ulp(pos, k):
+    """Ensemble member k of the 1-ulp perturbation: every coordinate moves by -1, 0 or +1 ulp (member 0 = unperturbed)."""
+    pos = np.ascontiguousarray(pos, np.float32)
+    if k == 0:
+        return pos.copy()
+    step = np.random.RandomState(1000 + k).randint(-1, 2, pos.shape)
+    out = pos.copy()
+    up = np.nextafter(pos, np.float32(np.inf), dtype=np.float32)
+    dn = np.nextafter(pos, np.float32(-np.inf), dtype=np.float32)
+    out[step > 0] = up[step > 0]
+    out[step < 0] = dn[step < 0]
     return out
 
 

@@ -58,7 +58,10 @@ def test_cli_result_file_matches_oracle(tmp_path, exe, scene, seed):
     # str(float64) -> stof: what both parsers see
     rc_cv, rc_f = np.zeros((3, 8), np.float32), np.zeros((2, 3), np.float32)
     assert _oracle.lib().canon_read_config(os.fsencode(str(d / "comms.config")), _oracle._p(rc_cv), _oracle._p(rc_f)) == 0
+    import learn_comms_b200 as lcb
+    order = lcb.table_order(len(pos))[0]   # the drop-in runs in the reference's table iteration order (quirk Q4)
     o = _oracle.CanonSim(pos, goal, rc_cv, rc_f, max_duration=md, rng_state=rng, comm=exe == "comm_norender")
+    o.set_order(order, gauss_seidel=False)
     o.step(10 ** 6)
     sc = o.scores()
     ref = tmp_path / "oracle.result"
@@ -71,14 +74,15 @@ def test_cli_result_file_matches_oracle(tmp_path, exe, scene, seed):
     rows = np.loadtxt(d / "agent_paths.csv", delimiter=",", dtype=np.float64)
     n = pos.shape[0]
     assert rows.shape == (o.frame * n, 8)
-    assert np.array_equal(rows[:n, 0], np.arange(1, n + 1)) and not rows[:, 1].any()
-    assert np.allclose(rows[:n, 2:4], pos, rtol=1e-5, atol=1e-6) and not rows[:n, 4:6].any()
+    assert np.array_equal(rows[:n, 0], order + 1) and not rows[:, 1].any()   # entity ids in POOL.for_<Agent> order
+    assert np.allclose(rows[:n, 2:4], pos[order], rtol=1e-5, atol=1e-6) and not rows[:n, 4:6].any()
     assert np.allclose(rows[:, 6], 0.15) and rows[0, 7] == 0.0
     assert np.allclose(rows[-1, 7], (o.frame - 1) / 60.0, rtol=1e-5)
     o2 = _oracle.CanonSim(pos, goal, rc_cv, rc_f, max_duration=md, rng_state=rng, comm=exe == "comm_norender")
+    o2.set_order(order, gauss_seidel=False)
     o2.step(o.frame - 1)
     st = o2.state()
-    assert np.allclose(rows[-n:, 2:4], st["pos"], rtol=1e-5, atol=1e-6) and np.allclose(rows[-n:, 4:6], st["vel"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(rows[-n:, 2:4], st["pos"][order], rtol=1e-5, atol=1e-6) and np.allclose(rows[-n:, 4:6], st["vel"][order], rtol=1e-5, atol=1e-6)
     # same scores when the CSV is switched off (one lc_run_to_completion call instead of frame-by-frame stepping)
     env = dict(os.environ, LEARN_COMMS_PROJECT_DIR=str(tmp_path), LEARN_COMMS_NO_PATHS="1")
     first = (d / "comms.result").read_text()

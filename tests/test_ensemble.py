@@ -1,0 +1,215 @@
+"""Rollout-level parity (north_star: "aggregate scenario scores ... within a stated tolerance over full rollouts").
+
+Rollouts are chaotic: a 1-ulp change of one start coordinate changes comms.result by several percent, so a score is a
+SAMPLE and the tolerance has to be a statement about distributions.  Calibration:
+  * tests/golden/ensemble_oref.npz (tools/make_golden_ensemble.py): the REFERENCE'S OWN translation units (O-ref) on
+    scenes 0 / 1 / 4 / 5 / 12 with zero and learned weights, 24 members each, start positions perturbed by <= 1 ulp;
+  * tests/golden/pso64_oref.npz (tools/make_golden_pso64.py): O-ref's fitness of 64 random particles on scenes 0/4/5/12.
+What is held against them: the product's arithmetic in the reference's table iteration order (lc_table_order, quirk Q4)
+with the Jacobi collision pass — O-canon on the CPU, the CUDA batch kernel on the GPU, the two bit-identical.
+Stated tolerance: per case the ensemble mean of group_time differs from the reference's by < 3.5 standard errors
+(Welch) and the unperturbed score lies inside the reference's [min, max] widened by a quarter of its range; PSO loss
+(pso_opt.py:156-194): same argmin particle, Spearman rho >= 0.95.
+"""
+import os
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+import pytest
+
+import _oracle
+import _oref
+import learn_comms_b200 as lcb
+from learn_comms_b200 import workloads as wl
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+Z_MAX = 3.5
+THREADS = min(16, os.cpu_count() or 1)
+
+
+def _case_inputs(scene, wseed):
+    pos, goal, md, rng = _oracle.scene(int(scene), 0)
+    m_cv, m_f = (None, None) if wseed < 0 else wl.weights(int(wseed))
+    return pos, goal, md, rng, m_cv, m_f
+
+
+def _canon_score(pos, goal, md, rng, m_cv, m_f, order):
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    if order is not None:
+        o.set_order(order, gauss_seidel=False)
+    o.step(10 ** 6)
+    sc = o.scores()
+    return sc["avg_velocity"], sc["group_time"], o.frame, sc["n_done"]
+
+
+def _welch_z(a, b):
+    return (b.mean() - a.mean()) / np.sqrt(a.var(ddof=1) / len(a) + b.var(ddof=1) / len(b))
+
+
+def _spearman(a, b):
+    ra, rb = np.argsort(np.argsort(a)).astype(np.float64), np.argsort(np.argsort(b)).astype(np.float64)
+    return float(np.corrcoef(ra, rb)[0, 1])
+
+
+def _fitness(group_time):
+    """pso_opt.py:26-41 read_result of the comms.result text (6 significant digits, comm.cpp:136-142)."""
+    gt = float("%g" % np.float32(group_time))
+    return 1e99 if (np.isnan(gt) or gt > 1e99) else gt
+
+
+def test_table_order_is_the_reference_iteration_order():
+    """lc_table_order == the order O-ref dumped from POOL.for_<Agent> (Pool.cpp:156-160) for every fixture scene."""
+    import glob
+    seen = set()
+    for path in sorted(glob.glob(os.path.join(GOLD, "scene*.npz"))) + [os.path.join(GOLD, "walled_scene3.npz")]:
+        g = np.load(path)
+        order = g["order"]
+        n = len(order)
+        assert np.array_equal(lcb.table_order(n)[0], order), f"{os.path.basename(path)}: n = {n}"
+        seen.add(n)
+    assert seen >= {56, 60, 90, 200}
+    a, w = lcb.table_order(3, 2)
+    assert sorted(a) == [0, 1, 2] and sorted(w) == [0, 1]
+    big, _ = lcb.table_order(70000)  # beyond the reference's uint16_t ids (Entity.h:12): ascending
+    assert np.array_equal(big, np.arange(70000))
+
+
+@pytest.mark.skipif(not _oref.available(), reason="oracle/_ref/oref not built (needs /root/reference)")
+def test_table_order_matches_a_live_reference_run():
+    for scene in (0, 12):
+        r = _oref.run(scene, 0, None, None, max_frames=1, dump_every=0)
+        assert np.array_equal(lcb.table_order(r["n"])[0], r["order"])
+
+
+def test_canon_in_reference_order_has_the_reference_score_distribution():
+    g = np.load(os.path.join(GOLD, "ensemble_oref.npz"))
+    M = int(g["members"])
+    jobs = []
+    for s, w in g["cases"]:
+        pos, goal, md, rng, m_cv, m_f = _case_inputs(s, w)
+        order = lcb.table_order(len(pos))[0]
+        jobs += [(_oref.perturb_ulp(pos, k), goal, md, rng, m_cv, m_f, order) for k in range(M)]
+    with ThreadPoolExecutor(THREADS) as ex:
+        out = np.array(list(ex.map(lambda j: _canon_score(*j), jobs)), np.float64).reshape(len(g["cases"]), M, 4)
+    zs = []
+    for (s, w), ref, mine in zip(g["cases"], g["result"], out):
+        a, b = ref[:, 1], mine[:, 1]
+        z = _welch_z(a, b)
+        zs.append(z)
+        assert abs(z) < Z_MAX, f"scene {s} weights {w}: group_time {b.mean():.3f} vs reference {a.mean():.3f}, z = {z:.2f}"
+        slack = 0.25 * (a.max() - a.min())
+        assert a.min() - slack <= b[0] <= a.max() + slack, f"scene {s} weights {w}: unperturbed score {b[0]} outside the reference's spread"
+        # spread of the same size (the product is neither calmer nor wilder than the reference)
+        assert 0.4 < b.std(ddof=1) / a.std(ddof=1) < 2.5
+        # rollouts last as long
+        assert abs(mine[:, 2].mean() - ref[:, 2].mean()) < 0.05 * ref[:, 2].mean()
+    assert np.abs(zs).mean() < 1.5
+
+
+def test_pso_fitness_ranking_agrees_with_the_reference():
+    """64 particles x scenes 0/4/5/12, loss of pso_opt.py:156-194 (sum over scenes of score / baseline score):
+    O-canon in the reference's table order vs O-ref's fixture."""
+    g = np.load(os.path.join(GOLD, "pso64_oref.npz"))
+    cfg, scenes = g["configs"], g["scenes"]
+    P = len(cfg)
+    jobs = []
+    for k in list(range(P)) + [-1]:
+        c = (np.zeros((5, 8)) if k < 0 else cfg[k]).astype(np.float32)
+        for s in scenes:
+            pos, goal, md, rng = _oracle.scene(int(s), 0)
+            jobs.append((pos, goal, md, rng, c[:3], c[3:, :3], lcb.table_order(len(pos))[0]))
+    with ThreadPoolExecutor(THREADS) as ex:
+        out = np.array([_fitness(r[1]) for r in ex.map(lambda j: _canon_score(*j), jobs)]).reshape(P + 1, len(scenes))
+    _check_pso(out[:P], out[P], g)
+
+
+def _check_pso(fit, base, g):
+    loss = (fit / base[None]).sum(1)
+    ref_loss = (g["fitness"] / g["baseline"][None]).sum(1)
+    rho = _spearman(loss, ref_loss)
+    assert rho >= 0.95, rho
+    assert int(loss.argmin()) == int(ref_loss.argmin()), (int(loss.argmin()), int(ref_loss.argmin()))
+    for j, s in enumerate(g["scenes"]):
+        assert _spearman(fit[:, j], g["fitness"][:, j]) >= 0.9, f"scene {s}"
+    return rho
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_gpu_ensemble_equals_canon_and_the_reference_distribution():
+    """CUDA batch kernel in the reference's table order on every ensemble member: frames and scores bit-identical to
+    O-canon's, and the same statistical statement against the reference's frozen ensemble."""
+    g = np.load(os.path.join(GOLD, "ensemble_oref.npz"))
+    M = int(g["members"])
+    for (s, w), ref in zip(g["cases"], g["result"]):
+        pos, goal, md, rng, m_cv, m_f = _case_inputs(s, w)
+        n = len(pos)
+        order = lcb.table_order(n)[0]
+        P = np.stack([_oref.perturb_ulp(pos, k) for k in range(M)])
+        zc, zf = np.zeros((3, 8), np.float32), np.zeros((2, 3), np.float32)
+        b = lcb.Batch(P, np.broadcast_to(goal, P.shape).copy(), np.broadcast_to(zc if m_cv is None else m_cv, (M, 3, 8)).copy(),
+                      np.broadcast_to(zf if m_f is None else m_f, (M, 2, 3)).copy(), np.full(M, md, np.float32),
+                      np.full(M, rng, np.uint32), order=order)
+        out = b.run()
+        gt = out["group_time"].astype(np.float64)
+        z = _welch_z(ref[:, 1], gt)
+        assert abs(z) < Z_MAX, f"scene {s} weights {w}: z = {z:.2f}"
+        for k in (0, 1, M - 1):  # bit-identity with the CPU oracle, spot-checked (the CPU suite runs all members)
+            av, og, of, ond = _canon_score(P[k], goal, md, rng, m_cv, m_f, order)
+            assert (out["frames"][k], out["n_done"][k]) == (of, ond)
+            assert np.float32(og) == out["group_time"][k]
+            assert np.float32(av) == out["avg_velocity"][k] or (np.isnan(av) and np.isnan(out["avg_velocity"][k]))
+
+
+@pytest.mark.gpu
+def test_gpu_pso_fitness_ranking_agrees_with_the_reference():
+    """The in-process PSO evaluator (pso.simulate_set, default = the reference's table order) on the 64-particle
+    fixture: loss ranking and argmin against O-ref."""
+    from learn_comms_b200 import pso
+    g = np.load(os.path.join(GOLD, "pso64_oref.npz"))
+    cfg, scenes = g["configs"], g["scenes"]
+    P = len(cfg)
+    configs = [c for c in cfg] + [np.zeros((5, 8))]
+    fit = np.zeros((P + 1, len(scenes)))
+    for j, s in enumerate(scenes):  # one batch per scene: a batch holds scenarios of one agent count
+        f, _ = pso.simulate_set([lcb.scene(int(s), 0)], configs)
+        fit[:, j] = [_fitness(v) for v in f[:, 0]]
+    rho = _check_pso(fit[:P], fit[P], g)
+    # the exact comms.result text of the reference for the rollouts in which its BVH / Gauss-Seidel pass never differed
+    assert (fit[:P] == g["fitness"]).sum() >= 5, (fit[:P] == g["fitness"]).sum()
+    print(f"PSO fitness agreement: Spearman rho = {rho:.4f}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene_id,wseed,frames", [(0, 1, 400), (12, 3, 120)])
+def test_gpu_single_crowd_in_reference_order_bit_exact(scene_id, wseed, frames):
+    """lc_create with table_order = the reference's: state, partners, neighbour lists, RNG every few frames against
+    O-canon run in the same order."""
+    pos, goal, md, rng = lcb.scene(scene_id, 0)
+    m_cv, m_f = wl.weights(wseed)
+    order = lcb.table_order(len(pos))[0]
+    gsim = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, debug_lists=True, order=order)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    o.set_order(order, gauss_seidel=False)
+    o.record_neighbors(True)
+    for f in range(0, frames, 8):
+        gsim.step(8)
+        o.step(8)
+        a, b = gsim.state(), o.state()
+        for k in a:
+            assert np.array_equal(a[k], b[k], equal_nan=a[k].dtype.kind == "f"), f"frame {f + 8}: {k}"
+        assert np.array_equal(gsim.partners(), o.partners())
+        gp, gi = gsim.neighbor_lists()
+        op, oi = o.neighbor_lists()
+        assert np.array_equal(gp, op) and np.array_equal(gi, oi)
+        assert gsim.rng == o.rng
+    st = gsim.state()
+    gsim.set_state(**st)   # host tables are indexed by the caller's agent index whatever the table order
+    gsim.step(8)
+    o.step(8)
+    a, b = gsim.state(), o.state()
+    for k in a:
+        assert np.array_equal(a[k], b[k], equal_nan=a[k].dtype.kind == "f"), f"after set_state: {k}"
+    frames_g = gsim.run_to_completion()
+    o.step(10 ** 6)
+    assert frames_g == o.frame and gsim.scores() == o.scores()
