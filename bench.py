@@ -1,15 +1,20 @@
 #!/usr/bin/env python
 """bench.py — agent-steps/sec of the learn-comms per-frame loop on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload plaza1m|corridor100k|circle1k] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload plaza1m|corridor100k|circle1k|scene0|pso4096] [--impl reference]
 
 One "step" = one frame (main.cpp:98-150: demo::run, comm::run, ai::update_agents, physics::simulate, all_sync) of the
 whole crowd.  Default workload: BASELINE.json configs[4], the 1M-agent open plaza the north_star's target is quoted
 on (it fits one GPU).  `value` = agent-steps/s with the state resident in HBM; `e2e` = the same frame driven through
-the C ABI with HOST component tables (lc_set_state from pinned memory -> lc_step(1) -> lc_get_state) inside the
-timed region.  `roofline` is for the dominant pass (k_pairs + k_force: pair filter, forces, integration), timed live with CUDA events on the launch stream.
-`cpu_baseline` / `--impl reference` time the CPU restatement of the reference loop (oracle/, O-canon with the
-uniform grid; the reference's own store cannot hold more than 65 535 entities, Entity.h:12) on a bounded sample.
+the C ABI with HOST component tables inside the timed region; `e2e_read` = lc_step(1) + host read of (pos, vel), the
+one definition that exists at every N.  `roofline` is for the dominant pass (k_pairs + k_force), timed live with CUDA
+events on the launch stream, with an FP32 leg (counted pair tests x 22 flop against the measured CUDA-core peak).
+`state_hash` = order-independent 64-bit hash of (id, pos, vel) of every agent after exactly warmup + steps frames: the
+same value at every N is the bit-identity claim of the domain decomposition, shown on real peers.
+`secondary` carries the metric's second half (PSO scenario evals/s) from the pso4096 batch, sharded over the same N GPUs.
+`cpu_baseline` / `--impl reference` time the reference's CPU loop on ALL host cores: O-ref (the reference's own
+translation units) where it can hold the workload, else O-canon (its CPU restatement; the reference's entity store is
+limited to 65 535 entities, Entity.h:12, and its loop is O(N^2)).
 """
 import argparse
 import json
@@ -17,8 +22,8 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -31,6 +36,7 @@ RESULT_OUT = os.fdopen(os.dup(1), "w")
 os.dup2(2, 1)
 
 ALG_BYTES_PER_AGENT_STEP = 112  # 60 B compulsory read + 52 B compulsory write of live agent state
+FLOP_PER_PAIR_TEST = 22         # 2 vector subtractions, 3 dot products, b*b - a*c, compares
 WORKLOADS = {
     # name: (generator kwargs, description, cpu-sample kwargs)
     "plaza1m": dict(kind="plaza", n=1_000_000, side=2000.0, seed=5, wscale=0.1,
@@ -48,7 +54,17 @@ WORKLOADS = {
                     sample=dict(n_scenarios=8)),
     "circle1k": dict(kind="circle", n=1000, radius=80.0, seed=1, wscale=0.1,
                      desc="circle antipodal swap, 1,000 agents, r = 80 m, seed 1", sample=dict(n=1000, radius=80.0)),
+    "scene0": dict(kind="scene", scene=0, seed=0, wscale=1.0,
+                   desc="the reference's own scene 0 (demo.cpp:145-151: 60 agents on a 10 m circle, antipodal goals, <= 45 s), "
+                        "learned-weight rollouts to completion in the reference's table order", sample=dict()),
 }
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def make_workload(name, sample=False, seed_offset=0):
@@ -71,6 +87,19 @@ def walking_state(pos, goal):
     l = np.maximum(np.hypot(d[:, 0], d[:, 1]), np.float32(1e-6)).astype(np.float32)
     v = (d / l[:, None]).astype(np.float32)
     return dict(vel=v, vfh=v.copy())
+
+
+def state_hash_partial(ids, pos, vel):
+    """Sum over agents (mod 2^64) of a 64-bit mix of (id, pos bits, vel bits): independent of the order agents are
+    listed in and of how they are split over ranks."""
+    with np.errstate(over="ignore"):
+        h = (ids.astype(np.uint64) + np.uint64(1)) * np.uint64(0x9E3779B97F4A7C15)
+        for k, col in enumerate((pos[:, 0], pos[:, 1], vel[:, 0], vel[:, 1])):
+            b = np.ascontiguousarray(col, np.float32).view(np.uint32).astype(np.uint64)
+            h ^= (b + np.uint64(k + 1)) * np.uint64(0xBF58476D1CE4E5B9)
+            h = (h ^ (h >> np.uint64(29))) * np.uint64(0x94D049BB133111EB)
+        h ^= h >> np.uint64(32)
+        return int(h.sum(dtype=np.uint64))
 
 
 class ClockSampler:
@@ -133,106 +162,159 @@ def dist_setup(n_gpus):
     return rank, world, local, dist
 
 
-def cpu_sample_rate(name, frames, warm=1):
-    """Time O-canon (grid search, single thread) on the bounded sample of `name`; returns (agent-steps/s, n, frames)."""
+def hbm_peak():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        return float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_entry(name, key):
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        return json.load(open(tp)).get(name, {}).get(key)
+    return None
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU arms (test infrastructure executed ONLY here: the cpu_baseline leg and --impl reference)
+
+def _oracle_mod():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle
-    pos, goal, md, rng, m_cv, m_f = make_workload(name, sample=True)
-    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, grid=True)
-    o.set_state(**walking_state(pos, goal))
-    o.step(warm, fixed=True)
-    t0 = time.perf_counter()
-    o.step(frames, fixed=True)
-    dt = time.perf_counter() - t0
-    return pos.shape[0] * frames / dt, pos.shape[0], dt
+    return _oracle
 
 
-def sample_text(name):
+def crowd_cpu_rate(name, frames, warm, threads):
+    """O-canon (uniform-grid search) on the bounded sample of `name`, one independent sample crowd per host thread
+    (different seeds), all stepping `frames` frames at once: aggregate agent-steps/s of the box's host cores."""
+    _oracle = _oracle_mod()
+    brute = WORKLOADS[name]["kind"] == "circle"   # the reference's own all-pairs loop where it is affordable
+    sims, n = [], 0
+    for t in range(threads):
+        pos, goal, md, rng, m_cv, m_f = make_workload(name, sample=True, seed_offset=100 * t)
+        o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, grid=not brute)
+        o.set_state(**walking_state(pos, goal))
+        sims.append(o)
+        n = pos.shape[0]
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(lambda o: o.step(warm, fixed=True), sims))
+        t0 = time.perf_counter()
+        list(ex.map(lambda o: o.step(frames, fixed=True), sims))
+        dt = time.perf_counter() - t0
+    return threads * n * frames / dt, n, dt
+
+
+def sample_text(name, threads):
     w = WORKLOADS[name]
-    return f"{w['kind']} sample {w['sample']} of the workload at the same density, O-canon grid search, 1 thread"
+    how = "brute force (the reference's all-pairs loop)" if w["kind"] == "circle" else "uniform-grid search"
+    return (f"{w['kind']} sample {w['sample']} of the workload at the same density, O-canon {how}, one independent sample crowd "
+            f"per host thread x {threads} threads")
+
+
+def oref_rate(scene, threads, runs_per_thread=1):
+    """The reference's own translation units (oracle/_ref/oref) on a catalogue scene, rollouts to completion, one process
+    per host thread (pso_opt.py's own fan-out, pso_opt.py:236-242).  Returns (agent-steps/s, evals/s, frames, seconds) or None."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oref
+    if not _oref.available():
+        return None
+    from learn_comms_b200 import workloads as wl
+    m_cv, m_f = wl.weights(1)
+    jobs = list(range(threads * runs_per_thread))
+
+    def one(k):
+        r = _oref.run(scene, k, m_cv, m_f, dump_every=0)
+        return r["n"] * r["frames_executed"]
+
+    with ThreadPoolExecutor(threads) as ex:
+        t0 = time.perf_counter()
+        steps = sum(ex.map(one, jobs))
+        dt = time.perf_counter() - t0
+    return steps / dt, len(jobs) / dt, steps, dt
+
+
+def pso_cpu_rate(n_scenarios, n_agents, seed, count, threads):
+    """O-canon brute force (the reference's all-pairs loop) on `count` scenarios spread evenly over the batch, one
+    rollout per host thread at a time."""
+    _oracle = _oracle_mod()
+    from learn_comms_b200 import workloads as wl
+    pos, goal, m_cv, m_f, md, rng = wl.pso_batch(n_scenarios, n_agents, seed=seed)
+    pick = [int(k * n_scenarios / count) for k in range(count)]
+
+    def one(s):
+        o = _oracle.CanonSim(pos[s], goal[s], m_cv[s], m_f[s], max_duration=float(md[s]), rng_state=int(rng[s]))
+        o.step(10 ** 6)
+        return o.frame * n_agents
+
+    with ThreadPoolExecutor(threads) as ex:
+        t0 = time.perf_counter()
+        steps = sum(ex.map(one, pick))
+        dt = time.perf_counter() - t0
+    return steps / dt, count / dt, count, dt
+
+
+def reference_line(args, value, ms_per_step, config, cpu, extra=None):
+    line = {"impl": "reference", "metric": "agent_steps_per_sec", "value": value, "unit": "agent-steps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "cpu_baseline": cpu, "e2e": {"value": value, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if extra:
+        line.update(extra)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm (oracle port; the reference's own entity store is limited to
-    65 535 entities and its third-party headers are not vendored) on the host cores, one frame of the bounded sample per step."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    """--impl reference: the reference's CPU implementation of the path on the box's host cores, all of them."""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import _oracle
-    name = args.workload
-    pos, goal, md, rng, m_cv, m_f = make_workload(name, sample=True)
-    n = pos.shape[0]
-    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, grid=True)
-    o.set_state(**walking_state(pos, goal))
-    o.step(args.warmup, fixed=True)
-    t0 = time.perf_counter()
-    o.step(args.steps, fixed=True)
-    dt = time.perf_counter() - t0
-    v = n * args.steps / dt
-    line = {"impl": "reference", "metric": "agent_steps_per_sec", "value": v, "unit": "agent-steps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": name, "desc": WORKLOADS[name]["desc"], "agents": n, "frames_per_step": 1},
-            "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": "port", "sample": sample_text(name)},
-            "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), file=RESULT_OUT, flush=True)
+    name, T = args.workload, host_cores()
+    w = WORKLOADS[name]
+    if w["kind"] == "scene":
+        # the reference's own binary can hold this workload: O-ref, one process per core
+        tot_steps, tot_dt, tot_evals = 0.0, 0.0, 0
+        for k in range(args.warmup + args.steps):
+            r = oref_rate(w["scene"], T)
+            if r is None:
+                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/oref is not built (needs /root/reference at build time)"}),
+                      file=RESULT_OUT, flush=True)
+                return
+            if k >= args.warmup:
+                tot_steps += r[2]; tot_dt += r[3]; tot_evals += T
+        v = tot_steps / tot_dt
+        cpu = {"value": v, "unit": "agent-steps/s", "cores": T, "kind": "reference",
+               "sample": f"oracle/_ref/oref (the reference's unmodified translation units), scene {w['scene']}, seeds 0..{T - 1}, one process per core per step"}
+        return reference_line(args, v, 1e3 * tot_dt / args.steps, {"workload": name, "desc": w["desc"]}, cpu,
+                              {"scenario_evals_per_sec": tot_evals / tot_dt})
+    if w["kind"] == "pso":
+        S, n = w["n_scenarios"], w["n_agents"]
+        tot_steps, tot_evals, tot_dt = 0.0, 0, 0.0
+        for k in range(args.warmup + args.steps):
+            v, ev, evals, dt = pso_cpu_rate(S, n, w["seed"], T, T)
+            if k >= args.warmup:
+                tot_steps += v * dt; tot_evals += evals; tot_dt += dt
+        v = tot_steps / tot_dt
+        cpu = {"value": v, "unit": "agent-steps/s", "cores": T, "kind": "port",
+               "sample": f"{T} of the {S} scenarios per step (evenly spread), O-canon brute force, one rollout per host thread"}
+        return reference_line(args, v, 1e3 * tot_dt / args.steps,
+                              {"workload": name, "desc": w["desc"], "scenarios": S, "agents_per_scenario": n}, cpu,
+                              {"scenario_evals_per_sec": tot_evals / tot_dt})
+    v, n, dt = crowd_cpu_rate(name, args.steps, args.warmup, T)
+    cpu = {"value": v, "unit": "agent-steps/s", "cores": T, "kind": "port", "sample": sample_text(name, T),
+           "why_port": "the reference's entity store holds <= 65 535 entities (Entity.h:12) and its loops are O(N^2): it cannot run this workload"}
+    reference_line(args, v, 1e3 * dt / args.steps, {"workload": name, "desc": w["desc"], "agents": n * T, "frames_per_step": 1}, cpu)
 
 
-def pso_cpu_rate(n_scenarios, n_agents, seed, stride):
-    """O-canon brute force (the reference's all-pairs loop), one thread, on every `stride`-th scenario of the batch."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import _oracle
-    from learn_comms_b200 import workloads as wl
-    pos, goal, m_cv, m_f, md, rng = wl.pso_batch(n_scenarios, n_agents, seed=seed)
-    steps, evals = 0, 0
-    t0 = time.perf_counter()
-    for s in range(0, n_scenarios, stride):
-        o = _oracle.CanonSim(pos[s], goal[s], m_cv[s], m_f[s], max_duration=float(md[s]), rng_state=int(rng[s]))
-        o.step(10 ** 6)
-        steps += o.frame * n_agents
-        evals += 1
-    dt = time.perf_counter() - t0
-    return steps / dt, evals / dt, evals, dt
-
-
-def run_batch_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    w = WORKLOADS[args.workload]
-    S, n = w["n_scenarios"], w["n_agents"]
-    per_step = 4   # scenarios per step: a bounded sample of the batch (one of every S/per_step), ~1 s of CPU each
-    tot_steps, tot_evals, tot_dt = 0.0, 0, 0.0
-    for k in range(args.warmup + args.steps):
-        v, ev, evals, dt = pso_cpu_rate(S, n, w["seed"], S // per_step)
-        if k >= args.warmup:
-            tot_steps += v * dt; tot_evals += evals; tot_dt += dt
-    v = tot_steps / tot_dt
-    sample = f"{per_step} of the {S} scenarios per step (every {S // per_step}-th), O-canon brute force, 1 thread"
-    line = {"impl": "reference", "metric": "agent_steps_per_sec", "value": v, "unit": "agent-steps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_dt / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "desc": w["desc"], "scenarios": S, "agents_per_scenario": n},
-            "scenario_evals_per_sec": tot_evals / tot_dt,
-            "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": "port", "sample": sample},
-            "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), file=RESULT_OUT, flush=True)
-
-
-def run_batch(args):
+# ---------------------------------------------------------------------------------------------------------------------
+def batch_measure(name, K, W, rank, world, local, dist, with_e2e=True):
     """PSO fitness batch (BASELINE.json configs[2]): one step = every scenario of the batch rolled out to completion in
     ONE kernel launch per GPU.  N > 1: contiguous blocks of scenarios per rank, no data-path collective, scores gathered
-    (12 B per scenario); total work is fixed => strong scaling."""
+    (16 B per scenario); total work is fixed => strong scaling.  Returns the measurement dict (rank 0 prints it)."""
     import torch
     import learn_comms_b200 as lcb
     from learn_comms_b200 import workloads as wl
     from learn_comms_b200 import pso
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
-    rank, world, local, dist = dist_setup(args.gpus)
-    W, K = max(args.warmup, 3), args.steps
-    w = WORKLOADS[args.workload]
+    w = WORKLOADS[name]
     S, n = w["n_scenarios"], w["n_agents"]
     pos, goal, m_cv, m_f, md, rng = wl.pso_batch(S, n, seed=w["seed"], scale=w["wscale"])
     lo, hi = pso.shard_range(S, rank, world)
@@ -248,9 +330,6 @@ def run_batch(args):
         b.reset()
         out = b.run()
     barrier()
-    clocks = ClockSampler(local)
-    clocks.start()
-    barrier()
     dev_ms, frames_sum, l0 = 0.0, 0, b.launches
     for _ in range(K):
         b.reset()
@@ -259,7 +338,6 @@ def run_batch(args):
         frames_sum += int(out["frames"].sum())
     barrier()
     launches = b.launches - l0
-    clk = clocks.stop()
     pair_tests = int(b.diag()["pair_tests"].sum())
     steps_local = frames_sum * n
     if dist is not None:
@@ -270,54 +348,116 @@ def run_batch(args):
         steps_all = steps_local
     value = steps_all / (dev_ms * 1e-3)
     evals = S * K / (dev_ms * 1e-3)
-
-    # e2e: host parameter matrices in, host scores out, through the evaluator pso_opt.py would call (reset = H2D of the
-    # initial tables + weights, run = rollouts + D2H of the score block), wall clock, max over ranks
-    Ke = max(3, min(K, 10))
-    ev = pso.BatchEvaluator(pos, goal, md, rng, device=local, rank=rank, world=world, dist=dist)
-    ev.evaluate(m_cv, m_f)
-    barrier()
-    t0 = time.perf_counter()
-    fr = 0
-    for _ in range(Ke):
-        sc = ev.evaluate(m_cv, m_f)
-        fr += int(sc["frames"].sum())
-    barrier()
-    dt = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([dt], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t.item())
-    e2e = {"value": fr * n / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": ev.h2d_bytes * world, "d2h_bytes_per_step": ev.d2h_bytes * world,
-           "steps": Ke, "ms_per_step": 1e3 * dt / Ke, "scenario_evals_per_sec": S * Ke / dt,
-           "api": "pso.BatchEvaluator.evaluate(host M_cv[S], M_f[S]) -> host scores: lc_batch_reset + lc_batch_run"}
-
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    e2e = None
+    if with_e2e:
+        # host parameter matrices in, host scores out, through the evaluator pso_opt.py would call (reset = H2D of the
+        # initial tables + weights, run = rollouts + D2H of the score block), wall clock, max over ranks
+        Ke = max(3, min(K, 10))
+        ev = pso.BatchEvaluator(pos, goal, md, rng, device=local, rank=rank, world=world, dist=dist, order=None)
+        ev.evaluate(m_cv, m_f)
+        barrier()
+        t0 = time.perf_counter()
+        fr = 0
+        for _ in range(Ke):
+            sc = ev.evaluate(m_cv, m_f)
+            fr += int(sc["frames"].sum())
+        barrier()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t.item())
+        e2e = {"value": fr * n / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": ev.h2d_bytes * world, "d2h_bytes_per_step": ev.d2h_bytes * world,
+               "steps": Ke, "ms_per_step": 1e3 * dt / Ke, "scenario_evals_per_sec": S * Ke / dt,
+               "api": "pso.BatchEvaluator.evaluate(host M_cv[S], M_f[S]) -> host scores: lc_batch_reset + lc_batch_run"}
+    peak, peak_src = hbm_peak()
     achieved = ALG_BYTES_PER_AGENT_STEP * (steps_all / world) / (dev_ms * 1e-3) / 1e9
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(args.workload, {}).get("k_batch_rollout_dram_bytes_per_launch")
     roofline = {"bound": "hbm", "kernel": "k_batch_rollout", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel_share": 1.0,
+                "traffic": traffic_entry(name, "k_batch_rollout_dram_bytes_per_launch"), "peak_source": peak_src, "kernel_share": 1.0,
                 "pair_tests_per_sec": pair_tests * K / (dev_ms * 1e-3),
                 "note": "state lives in shared memory / registers for the whole rollout: HBM is touched once per scenario, the kernel "
                         "is FP32-issue bound on the all-pairs TTC loop (DESIGN.md); algorithmic bytes = 112 B x agent-steps"}
+    return {"agent_steps_per_sec": value, "scenario_evals_per_sec": evals, "ms_per_step": dev_ms / K, "steps": K, "warmup": W,
+            "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e, "scenarios": S, "agents_per_scenario": n, "desc": w["desc"]}
+
+
+def run_batch(args):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    rank, world, local, dist = dist_setup(args.gpus)
+    W, K = max(args.warmup, 3), args.steps
+    clocks = ClockSampler(local)
+    clocks.start()
+    m = batch_measure(args.workload, K, W, rank, world, local, dist)
+    clk = clocks.stop()
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, evs, k, dtc = pso_cpu_rate(S, n, w["seed"], S // 16)
-        cpu = {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": "port", "scenario_evals_per_sec": evs,
-               "sample": f"16 of the {S} scenarios (every {S // 16}-th), O-canon brute force, 1 thread, {dtc:.1f} s"}
+        T = host_cores()
+        w = WORKLOADS[args.workload]
+        v, evs, k, dtc = pso_cpu_rate(m["scenarios"], m["agents_per_scenario"], w["seed"], max(T, 16), T)
+        cpu = {"value": v, "unit": "agent-steps/s", "cores": T, "kind": "port", "scenario_evals_per_sec": evs,
+               "sample": f"{k} of the {m['scenarios']} scenarios (evenly spread), O-canon brute force, one rollout per host thread, {dtc:.1f} s"}
     if rank == 0:
-        line = {"metric": "agent_steps_per_sec", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "scenario_evals_per_sec": evals,
-                "config": {"workload": args.workload, "desc": w["desc"], "scenarios": S, "agents_per_scenario": n,
+        line = {"metric": "agent_steps_per_sec", "value": m["agent_steps_per_sec"], "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "scenario_evals_per_sec": m["scenario_evals_per_sec"],
+                "config": {"workload": args.workload, "desc": m["desc"], "scenarios": m["scenarios"], "agents_per_scenario": m["agents_per_scenario"],
                            "parallelism": f"{world} GPU(s), contiguous scenario blocks, score gather only",
                            "l2": "no HBM working set: state is staged once into shared memory; nothing to flush"},
-                "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+                "clocks": clk, "e2e": m["e2e"], "gpu_launches": m["gpu_launches"], "roofline": m["roofline"], "cpu_baseline": cpu}
+        print(json.dumps(line), file=RESULT_OUT, flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_scene(args):
+    """BASELINE.json configs[0]-style workload: the reference's own scene, rollouts to completion through lc_create /
+    lc_run_to_completion in the reference's table order; one step = one rollout."""
+    import torch
+    import learn_comms_b200 as lcb
+    from learn_comms_b200 import workloads as wl
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    rank, world, local, dist = dist_setup(args.gpus)
+    w = WORKLOADS[args.workload]
+    W, K = max(args.warmup, 3), args.steps
+    m_cv, m_f = wl.weights(1)
+    steps, ms, launches = 0, 0.0, 0
+    clocks = ClockSampler(local)
+    clocks.start()
+    for k in range(W + K):
+        pos, goal, md, rng = lcb.scene(w["scene"], k + 1000 * rank)
+        sim = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, device=local, order="reference")
+        sim.timer_start()
+        frames = sim.run_to_completion()
+        t = sim.timer_stop()
+        if k >= W:
+            steps += frames * pos.shape[0]; ms += t; launches += sim.launches
+        sim.close()
+    clk = clocks.stop()
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        t = torch.tensor([steps, launches], device="cuda", dtype=torch.int64); dist.all_reduce(t)
+        steps, launches = int(t[0].item()), int(t[1].item())
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        T = host_cores()
+        r = oref_rate(w["scene"], T)
+        if r is not None:
+            cpu = {"value": r[0], "unit": "agent-steps/s", "cores": T, "kind": "reference", "scenario_evals_per_sec": r[1],
+                   "sample": f"oracle/_ref/oref (the reference's unmodified translation units), scene {w['scene']}, seeds 0..{T - 1}, one process per core, {r[3]:.1f} s"}
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        achieved = ALG_BYTES_PER_AGENT_STEP * (steps / world) / (ms * 1e-3) / 1e9
+        line = {"metric": "agent_steps_per_sec", "value": steps / (ms * 1e-3), "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "scenario_evals_per_sec": K * world / (ms * 1e-3),
+                "config": {"workload": args.workload, "desc": w["desc"], "parallelism": f"{world} independent rollouts at a time, one per GPU",
+                           "l2": "60 agents: the whole state is cache resident; launch latency bound (the batched kernel is the tool for this size)"},
+                "clocks": clk, "e2e": None, "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                             "peak_source": peak_src, "note": "8 launches of latency per frame for 60 agents; nowhere near any roofline"},
+                "cpu_baseline": cpu}
         print(json.dumps(line), file=RESULT_OUT, flush=True)
     if dist is not None:
         dist.barrier()
@@ -334,12 +474,15 @@ def main():
     ap.add_argument("--stencil", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the PSO-batch leg of the default line")
     ap.add_argument("--replicas", action="store_true", help="N > 1: N independent crowds instead of one decomposed crowd")
     args = ap.parse_args()
-    if WORKLOADS[args.workload]["kind"] == "pso":
-        return run_batch_reference(args) if args.impl == "reference" else run_batch(args)
     if args.impl == "reference":
         return run_reference(args)
+    if WORKLOADS[args.workload]["kind"] == "pso":
+        return run_batch(args)
+    if WORKLOADS[args.workload]["kind"] == "scene":
+        return run_scene(args)
 
     import torch
     import learn_comms_b200 as lcb
@@ -389,86 +532,130 @@ def main():
     n_local = sim.counts()[0] if domain else n
     n_owned = int(sim.owned().sum()) if domain else n
 
+    # bit-identity across N: hash of (id, pos, vel) of every agent after exactly W + K frames (the same crowd at every N)
+    if domain:
+        sh, k_own = sim.shard()
+        part = state_hash_partial(sh["ids"][:k_own], sh["pos"][:k_own], sh["vel"][:k_own])
+        t = torch.tensor([part >> 32, part & 0xffffffff, k_own], device="cuda", dtype=torch.int64)
+        parts = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(parts, t)
+        total = sum((int(p[0].item()) << 32) | int(p[1].item()) for p in parts) & ((1 << 64) - 1)
+        hashed = sum(int(p[2].item()) for p in parts)
+    else:
+        st = sim.state(keys=("pos", "vel"))
+        total = state_hash_partial(np.arange(n, dtype=np.int64), st["pos"], st["vel"]) & ((1 << 64) - 1)
+        hashed = n
+    state_hash = {"hash": f"{total:016x}", "frames": W + K, "agents_hashed": hashed,
+                  "what": "sum mod 2^64 over all agents of mix64(id, pos bits, vel bits); equal at every N <=> the decomposed run is bit-identical"}
+
     # roofline leg: per-kernel device time, CUDA events between the launches on the simulation's stream
     prof = sim.step_profiled(20)
+    pair_tests = sim.pair_tests()
+    fp = lcb.fp32_peak(local)
     t_force = (prof["k_pairs"] + prof["k_force"]) * 1e-3  # S1-S3a: pair filter + force/integrate, one logical pass over the state
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    peak, peak_src = hbm_peak()
     achieved = ALG_BYTES_PER_AGENT_STEP * n_owned / t_force / 1e9  # this rank's own agents per k_pairs + k_force launch
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(name, {}).get("k_pairs_k_force_dram_bytes_per_launch")
     frame_ms = sum(prof.values())
+    fp_achieved = pair_tests * FLOP_PER_PAIR_TEST / (prof["k_pairs"] * 1e-3) / 1e12
     roofline = {"bound": "hbm", "kernel": "k_pairs+k_force", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel_ms": prof, "kernel_share": (prof["k_pairs"] + prof["k_force"]) / frame_ms,
+                "traffic": traffic_entry(name, "k_pairs_k_force_dram_bytes_per_launch"), "peak_source": peak_src, "kernel_ms": prof,
+                "kernel_share": (prof["k_pairs"] + prof["k_force"]) / frame_ms,
+                "frame": {"achieved": ALG_BYTES_PER_AGENT_STEP * n_owned / (ms / K * 1e-3) / 1e9,
+                          "frac": ALG_BYTES_PER_AGENT_STEP * n_owned / (ms / K * 1e-3) / 1e9 / peak,
+                          "traffic": traffic_entry(name, "frame_dram_bytes"), "algorithmic_bytes": ALG_BYTES_PER_AGENT_STEP * n_owned},
+                "fp32": {"kernel": "k_pairs", "pair_tests_per_launch": pair_tests, "flop_per_pair_test": FLOP_PER_PAIR_TEST,
+                         "achieved": fp_achieved, "unit": "TFLOP/s",
+                         "peak_fma": fp["fma"], "peak_mul_add_scalar": fp["mul_add"], "peak_mul_add_packed": fp["packed"],
+                         "frac_of_fma_peak": fp_achieved / fp["fma"] if fp["fma"] else None,
+                         "frac_of_packed_peak": fp_achieved / fp["packed"] if fp["packed"] else None,
+                         "pair_tests_per_agent": pair_tests / max(n_local, 1),
+                         "peak_source": "lc_fp32_peak, measured in this run: independent chains, no memory traffic; the library may not "
+                                        "contract mul+add (bit parity with the reference's SSE2 build), so the packed mul/add figure is its ceiling"},
                 "note": "pair loop is FP32/issue bound, not HBM bound (DESIGN.md); algorithmic bytes = 112 B x agents per launch"}
 
-    # e2e leg: host-resident component tables, pinned; set_state (H2D) -> one frame -> get_state (D2H) every step
-    e2e = None
-    if not args.no_e2e and domain:
-        # decomposed crowd: the state never leaves the GPUs between frames; the host-facing step is one frame plus the
-        # D2H read of the tables a host engine consumes every frame (pos, vel of the rank's own agents)
-        cap = sim.counts()[1]
-        pinned = dict(ids=torch.zeros(cap, dtype=torch.int32).pin_memory(), pos=torch.zeros((cap, 2)).pin_memory(),
-                      vel=torch.zeros((cap, 2)).pin_memory())
-        views = {k: v.numpy() for k, v in pinned.items()}
+    # e2e legs.  e2e_read (every N): lc_step(1) + host read of (pos, vel) [+ ids on a decomposed crowd], pinned host tables.
+    # e2e: the host engine owns the component tables — at N = 1 the full round trip lc_set_state -> lc_step(1) -> lc_get_state;
+    # teacher forcing is single-GPU only (learn_comms.h), so on a decomposed crowd e2e is e2e_read.
+    e2e, e2e_read = None, None
+    if not args.no_e2e:
         Ke = max(3, min(K, 50))
+        if domain:
+            cap = sim.counts()[1]
+            pinned = dict(ids=torch.zeros(cap, dtype=torch.int32).pin_memory(), pos=torch.zeros((cap, 2)).pin_memory(),
+                          vel=torch.zeros((cap, 2)).pin_memory())
+            views = {k: v.numpy() for k, v in pinned.items()}
+            read = lambda: sim.shard(out=views)[1] * 20 + 4  # noqa: E731
+            api = "lc_step(1) + lc_dd_get_shard (ids, pos, vel of the rank's own agents) per rank"
+        else:
+            pinned = dict(pos=torch.zeros((n, 2)).pin_memory(), vel=torch.zeros((n, 2)).pin_memory())
+            views = {k: v.numpy() for k, v in pinned.items()}
+            read = lambda: (sim.state(keys=("pos", "vel"), out=views), n * 16)[1]  # noqa: E731
+            api = "lc_step(1) + lc_get_state(pos, vel)"
         for _ in range(3):
             sim.step(1, sync=False)
-            _, k_own = sim.shard(out=views)
+            nb = read()
         barrier()
         t0 = time.perf_counter()
         for _ in range(Ke):
             sim.step(1, sync=False)
-            _, k_own = sim.shard(out=views)
+            nb = read()
         barrier()
         dt = time.perf_counter() - t0
-        d2h = torch.tensor([float(k_own * 20 + 4)], device="cuda")
-        dist.all_reduce(d2h)
-        t = torch.tensor([dt], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
-        d2h = int(d2h.item()) // world
-        e2e = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h * world,
-               "steps": Ke, "ms_per_step": 1e3 * dt / Ke,
-               "api": "lc_step(1) + lc_dd_get_shard (ids, pos, vel of the rank's own agents) per rank, pinned host tables; no per-frame H2D: the decomposed state is device-resident"}
-    elif not args.no_e2e:
-        st = sim.state()
-        pinned = {}
-        for k, a in st.items():
-            t = torch.from_numpy(a.copy()).pin_memory()
-            pinned[k] = t.numpy()
-        pinned_keep = pinned  # keep tensors alive through the views
-        h2d = sum(a.nbytes for a in pinned.values())
-        Ke = max(3, min(K, 50))
-        for _ in range(3):
-            sim.set_state(**pinned)
-            sim.step(1)
-            sim.state(out=pinned)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(Ke):
-            sim.set_state(**pinned)
-            sim.step(1, sync=False)
-            sim.state(out=pinned)
-        barrier()
-        dt = time.perf_counter() - t0
+        d2h = nb
         if dist is not None:
-            t = torch.tensor([dt], device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
-        e2e = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": h2d * world,
-               "steps": Ke, "ms_per_step": 1e3 * dt / Ke, "api": "lc_set_state + lc_step(1) + lc_get_state, pinned host tables"}
-        del pinned_keep
+            t = torch.tensor([dt], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t.item())
+            t = torch.tensor([float(nb)], device="cuda"); dist.all_reduce(t); d2h = int(t.item()) if domain else nb * world
+        e2e_read = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(d2h),
+                    "steps": Ke, "ms_per_step": 1e3 * dt / Ke, "api": api + ", pinned host tables; the state stays device-resident"}
+        if domain:
+            e2e = dict(e2e_read, note="decomposed crowd: lc_set_state (teacher forcing) is single-GPU only, so e2e = e2e_read here; "
+                                      "the like-for-like host round trip is the N = 1 line's e2e")
+        else:
+            st = sim.state()
+            pinned_t = {k: torch.from_numpy(a.copy()).pin_memory() for k, a in st.items()}
+            pinned = {k: t.numpy() for k, t in pinned_t.items()}
+            h2d = sum(a.nbytes for a in pinned.values())
+            for _ in range(3):
+                sim.set_state(**pinned)
+                sim.step(1)
+                sim.state(out=pinned)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(Ke):
+                sim.set_state(**pinned)
+                sim.step(1, sync=False)
+                sim.state(out=pinned)
+            barrier()
+            dt = time.perf_counter() - t0
+            if dist is not None:
+                t = torch.tensor([dt], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t.item())
+            e2e = {"value": n_total * Ke / dt, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": h2d * world,
+                   "steps": Ke, "ms_per_step": 1e3 * dt / Ke, "host_gb_per_s": 2 * h2d * world * Ke / dt / 1e9,
+                   "api": "lc_set_state + lc_step(1) + lc_get_state, all eight component tables, pinned host memory; the three calls "
+                          "are dependent (set -> step -> get), so the copies cannot overlap the frame"}
+            del pinned_t
+
+    counters = sim.counters()
+    barrier()   # a decomposed crowd's mailboxes are mapped into the peers: nobody frees before everybody is done
+    sim.close()
+
+    # the metric's second half: PSO scenario evals/s from the pso4096 batch, sharded over the same N GPUs
+    secondary = None
+    if not args.no_secondary:
+        m = batch_measure("pso4096", 3, 3, rank, world, local, dist, with_e2e=False)
+        secondary = {"workload": "pso4096", "scenario_evals_per_sec": m["scenario_evals_per_sec"], "agent_steps_per_sec": m["agent_steps_per_sec"],
+                     "ms_per_batch": m["ms_per_step"], "steps": m["steps"], "scaling": "strong", "roofline": m["roofline"],
+                     "gpu_launches": m["gpu_launches"], "desc": m["desc"]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, ns, dt = cpu_sample_rate(name, frames=30 if name != "circle1k" else 300)
-        cpu = {"value": v, "unit": "agent-steps/s", "cores": 1, "kind": "port", "sample": sample_text(name) + f", {dt:.1f} s"}
+        T = host_cores()
+        v, ns, dt = crowd_cpu_rate(name, frames=20 if name != "circle1k" else 200, warm=1, threads=T)
+        cpu = {"value": v, "unit": "agent-steps/s", "cores": T, "kind": "port", "per_core": v / T, "sample": sample_text(name, T) + f", {dt:.1f} s"}
+        r = oref_rate(0, T)
+        if r is not None:  # context: the reference's own binary on a workload it can hold
+            cpu["oref_scene0"] = {"value": r[0], "unit": "agent-steps/s", "cores": T, "kind": "reference", "scenario_evals_per_sec": r[1],
+                                  "sample": f"oracle/_ref/oref, scene 0 (60 agents) to completion, one process per core, {r[3]:.1f} s"}
 
     if rank == 0:
         line = {"metric": "agent_steps_per_sec", "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -480,7 +667,8 @@ def main():
                             f"inside the frame kernels (rank 0: {n_owned} own + {n_local - n_owned} ghost agents)" if domain
                             else f"{world} independent crowds, one per GPU, no exchange"),
                            "l2": "per-frame working set (2 x 88 B x agents + grid) exceeds the 126 MB L2 at 1M agents; no flush"},
-                "counters": sim.counters(), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+                "counters": counters, "clocks": clk, "e2e": e2e, "e2e_read": e2e_read, "gpu_launches": int(launches), "roofline": roofline,
+                "state_hash": state_hash, "secondary": secondary, "cpu_baseline": cpu}
         print(json.dumps(line), file=RESULT_OUT, flush=True)
     if dist is not None:
         dist.barrier()

@@ -89,6 +89,13 @@ int32_t lc_get_neighbor_counts(lc_sim* sim, int32_t* count);    /* [n] |{j : ttc
 int32_t lc_get_neighbor_lists(lc_sim* sim, int32_t* idx, int32_t cap_per_agent); /* [n][cap], ascending id; needs LC_FLAG_DEBUG_LISTS */
 int32_t lc_get_counters(lc_sim* sim, int64_t* overlap_pairs, int64_t* collision_hits, int64_t* candidates);
 
+/* pair-filter evaluations k_pairs performed in the last executed frame (recounted from that frame's grid; diagnostic for
+ * the FP32 leg of the roofline: the reference evaluates n (n - 1) pairs per frame, LMP.cpp:288-304) */
+int32_t lc_count_pair_tests(lc_sim* sim, int64_t* pair_tests);
+/* measured FP32 throughput of the device's CUDA cores, TFLOP/s, best of `repeats`: [0] independent scalar FMUL / FADD
+ * chains without contraction (the arithmetic this library is restricted to for bit parity), [1] the same as packed
+ * mul.rn.f32x2 / add.rn.f32x2 (what the pair filter issues), [2] FFMA chains (the hardware's nominal peak) */
+int32_t lc_fp32_peak(int32_t device, int32_t repeats, float* tflops /*[3]*/);
 /* timing on the simulation's own stream (CUDA events) */
 int32_t lc_timer_start(lc_sim* sim);
 int32_t lc_timer_stop(lc_sim* sim, float* milliseconds);

@@ -38,7 +38,7 @@ EXPORTS = [
     "lc_create", "lc_destroy", "lc_set_weights", "lc_step", "lc_run_to_completion", "lc_sync", "lc_finished",
     "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
-    "lc_kernel_launches", "lc_step_profiled", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
+    "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
     "lc_read_config", "lc_write_result", "lc_scene", "lc_table_order", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
@@ -75,6 +75,8 @@ def lib():
         L.lc_kernel_launches.argtypes = [vp]
         L.lc_kernel_launches.restype = C.c_int64
         L.lc_step_profiled.argtypes = [vp, i32, vp]
+        L.lc_count_pair_tests.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.lc_fp32_peak.argtypes = [i32, i32, vp]
         L.lc_dd_create.argtypes = [C.POINTER(_Desc), C.POINTER(_DomainDesc), C.POINTER(vp)]
         L.lc_dd_mailbox.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
         L.lc_dd_connect.argtypes = [vp, i32, vp, i32]
@@ -364,9 +366,23 @@ class Sim:
         _ck(lib().lc_step_profiled(self.h, n, _p(ms)))
         return dict(zip(self.KERNELS, ms.tolist()))
 
+    def pair_tests(self):
+        """pair-filter evaluations of the last executed frame (lc_count_pair_tests)."""
+        k = C.c_int64(0)
+        _ck(lib().lc_count_pair_tests(self.h, C.byref(k)))
+        return int(k.value)
+
     @property
     def launches(self):
         return int(lib().lc_kernel_launches(self.h))
+
+
+def fp32_peak(device=0, repeats=5):
+    """Measured FP32 TFLOP/s (lc_fp32_peak): dict(mul_add = scalar uncontracted FMUL + FADD chains, packed = the same as
+    f32x2 instructions, fma = FFMA chains)."""
+    t = np.zeros(3, np.float32)
+    _ck(lib().lc_fp32_peak(device, repeats, _p(t)))
+    return dict(mul_add=float(t[0]), packed=float(t[1]), fma=float(t[2]))
 
 
 class DomainSim(Sim):

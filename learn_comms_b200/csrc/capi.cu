@@ -67,7 +67,7 @@ struct lc_sim {
     cudaStream_t st = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     lc::SideStream side{nullptr, nullptr, nullptr};  // k_refine next to k_pairs (crowd.cuh)
-    cudaGraphExec_t gexec[2] = {nullptr, nullptr};  // 1 frame, GRAPH_BATCH frames
+    cudaGraphExec_t gexec[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // 1, 2, 4, 8, 16 frames
     long long launches = 0;
     int device = 0;
     int n = 0;           // launch width: slot capacity of the local arrays (== n_ids for a single-GPU crowd)
@@ -90,7 +90,11 @@ struct lc_sim {
     std::vector<void*> allocs;
 };
 
-static const int GRAPH_BATCH = 16;
+// lc_step(n) replays n frames as the binary decomposition of n over these graphs: 20 frames = 16 + 4, two launches
+// (with only 1- and 16-frame graphs it was 16 + 1 + 1 + 1 + 1: five, whose host-side skew between the ranks of a
+// decomposed crowd ended up in the peer-flag waits)
+static const int GRAPH_LEVELS = 5;
+static const int GRAPH_BATCH = 1 << (GRAPH_LEVELS - 1);
 
 static int alloc_arrays(lc_sim* s, lc::AgentArrays& a, int n) {
     CK(dalloc(&a.pv, n)); s->allocs.push_back(a.pv);
@@ -104,8 +108,8 @@ static int alloc_arrays(lc_sim* s, lc::AgentArrays& a, int n) {
 }
 
 static int build_graphs(lc_sim* s) {
-    for (int g = 0; g < 2; ++g) {
-        int frames = g == 0 ? 1 : GRAPH_BATCH;
+    for (int g = 0; g < GRAPH_LEVELS; ++g) {
+        int frames = 1 << g;
         cudaGraph_t graph;
         CK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
         for (int f = 0; f < frames; ++f) lc::launch_frame(s->dP, s->n, s->b, s->st, nullptr, nullptr, &s->side);
@@ -466,15 +470,13 @@ int32_t lc_step(lc_sim* s, int32_t nframes) {
     if (nframes < 0) return fail(LC_ERR_ARG, "lc_step: nframes < 0");
     if (nframes > 0) ensure_packed(s);
     int left = nframes;
-    while (left >= GRAPH_BATCH) {
-        CK(cudaGraphLaunch(s->gexec[1], s->st));
-        left -= GRAPH_BATCH;
-        s->launches += (lc::FRAME_KERNELS + (s->ddev ? lc::DD_KERNELS : 0)) * GRAPH_BATCH;
-    }
-    while (left > 0) {
-        CK(cudaGraphLaunch(s->gexec[0], s->st));
-        --left;
-        s->launches += lc::FRAME_KERNELS + (s->ddev ? lc::DD_KERNELS : 0);
+    for (int g = GRAPH_LEVELS - 1; g >= 0; --g) {
+        const int frames = 1 << g;
+        while (left >= frames) {
+            CK(cudaGraphLaunch(s->gexec[g], s->st));
+            left -= frames;
+            s->launches += (long long)(lc::FRAME_KERNELS + (s->ddev ? lc::DD_KERNELS : 0)) * frames;
+        }
     }
     return LC_OK;
 }
@@ -639,6 +641,19 @@ int32_t lc_get_counters(lc_sim* s, int64_t* overlap_pairs, int64_t* collision_hi
     if (overlap_pairs) *overlap_pairs = (int64_t)(s->hctl->overlap2 / 2);
     if (collision_hits) *collision_hits = (int64_t)s->hctl->coll_hits;
     if (candidates) *candidates = s->hctl->n_cand2;
+    return LC_OK;
+}
+
+int32_t lc_count_pair_tests(lc_sim* s, int64_t* pair_tests) {
+    SIM_ENTER(s);
+    if (!pair_tests) return fail(LC_ERR_ARG, "lc_count_pair_tests: null argument");
+    unsigned long long* d = (unsigned long long*)s->stage;
+    CK(cudaMemsetAsync(d, 0, sizeof(unsigned long long), s->st));
+    lc::launch_pair_count(s->dP, s->n, s->b, d, s->st, &s->launches);
+    unsigned long long h = 0;
+    CK(cudaMemcpyAsync(&h, d, sizeof h, cudaMemcpyDeviceToHost, s->st));
+    CK(cudaStreamSynchronize(s->st));
+    *pair_tests = (int64_t)h;
     return LC_OK;
 }
 

@@ -668,7 +668,7 @@ __device__ __forceinline__ void pair_eval(const Buffers& b, int s, int j, float 
 // product and sum is the same float, so one test serves both agents (k_pairs).
 template <bool HALF, bool FIRST, class N>
 __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
-                                           float RR, float near_c, N&& note) {
+                                           float RR, float near_c, N&& note, long long* tested = nullptr) {
     const int st = ctl->stencil, stx = ctl->stencil_x, nx = ctl->nx, ny = ctl->ny;
     int ix = (int)floorf((px - ctl->x0) / ctl->hx), iy = (int)floorf((py - ctl->y0) / ctl->h);
     ix = min(max(ix, 0), nx - 1);
@@ -747,6 +747,7 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
         // s lies in cell (ix, iy), x_lo <= ix <= x_hi: in its own row the partners after s start at slot s + 1
         int j0 = (HALF && yy == iy) ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
         if (j0 >= j1) continue;
+        if (tested) { *tested += j1 - j0; continue; }  // counting mode (lc_count_pair_tests): the ranges, not the filter
         if (j0 & 1) single(j0++);
         if ((j1 & 1) && j1 > j0) single(--j1);
         // two candidates per packed operation: slots (j, j + 1), j even, are stored as (x0, x1, z0, z1), (vx0, vx1, vz0, vz1);
@@ -805,6 +806,24 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
         k = atomicAdd(&b.pair_cnt[j], 1);
         if (k < PAIR_CAP) b.pair_list[k * stride + j] = s;
     });
+}
+
+// Diagnostic twin of k_pairs: how many pair-filter evaluations the last frame's k_pairs performed (the same row ranges,
+// nothing evaluated or written).  Feeds the FP32 leg of bench.py's roofline.
+__global__ void __launch_bounds__(128) k_pair_count(const Params* __restrict__ P, Buffers b, unsigned long long* out) {
+    const Ctl* ctl = b.ctl;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    long long tested = 0;
+    if (s < P->n) {
+        const float4 me = b.srt.pv[s];
+        scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [](int) {}, &tested);
+    }
+    for (int o = 16; o > 0; o >>= 1) tested += __shfl_xor_sync(0xffffffffu, tested, o);
+    if ((threadIdx.x & 31) == 0 && tested) atomicAdd(out, (unsigned long long)tested);
+}
+void launch_pair_count(const Params* dP, int n, const Buffers& b, unsigned long long* out, cudaStream_t st, long long* launches) {
+    k_pair_count<<<(n + 127) / 128, 128, 0, st>>>(dP, b, out);
+    if (launches) *launches += 1;
 }
 
 #ifndef LC_FORCE_BLOCKS

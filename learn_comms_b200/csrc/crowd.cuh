@@ -178,6 +178,7 @@ void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, 
 struct SideStream { cudaStream_t st; cudaEvent_t fork, join; };
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
                   cudaEvent_t* ev = nullptr, const SideStream* side = nullptr);
+void launch_pair_count(const Params* dP, int n, const Buffers& b, unsigned long long* out, cudaStream_t st, long long* launches);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
