@@ -184,6 +184,13 @@ int32_t lc_write_result(const char* path, float avg_velocity, float group_time);
  * be NULL when its count is 0).  Ascending when the scene exceeds the reference's 65 535 entities (Entity.h:12). ---- */
 int32_t lc_table_order(int32_t n_agents, int32_t n_walls, int32_t* agent_order, int32_t* wall_order);
 
+/* ---- static BVH over the walls as ai::init builds it (ai.cpp:16-18,36; BVH.cpp:9-49,144-251), flattened in pre-order.
+ * wall_order = the statics order (lc_table_order's wall_order; NULL = creation order).  Inner node: box + child indices;
+ * leaf: right = -1, left = creation index of the wall.  2 n_walls - 1 nodes.  lc_create builds it itself; exported for the
+ * parity tests (pinned node for node against the reference's own BVH) and for hosts that want to inspect it. ---- */
+typedef struct lc_bvh_node { float ox, oy, w, h; int32_t left, right; } lc_bvh_node;
+int32_t lc_static_bvh(int32_t n_walls, const lc_rect* walls, const int32_t* wall_order, lc_bvh_node* nodes, int32_t cap, int32_t* n_nodes);
+
 /* ---- scene catalogue (demo.cpp:141-511), wall-free scenes; returns agent count or negative status ---- */
 int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
                  uint32_t* rng_state_after);

@@ -41,7 +41,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_table_order", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_table_order", "lc_static_bvh", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -101,6 +101,7 @@ def lib():
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
         L.lc_table_order.argtypes = [i32, i32, vp, vp]
+        L.lc_static_bvh.argtypes = [i32, vp, vp, vp, i32, C.POINTER(i32)]
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
         L.lc_lookahead.argtypes = [i32, vp, C.c_float, i32, vp, vp, i32]
         L.lc_planner_create.argtypes = [i32, vp, C.c_float, C.POINTER(vp)]
@@ -140,6 +141,19 @@ def table_order(n_agents, n_walls=0):
     w = np.zeros(max(n_walls, 1), np.int32)
     _ck(lib().lc_table_order(n_agents, n_walls, _p(a), _p(w)))
     return a[:n_agents].copy(), w[:n_walls].copy()
+
+
+BVH_NODE = np.dtype([("ox", np.float32), ("oy", np.float32), ("w", np.float32), ("h", np.float32), ("left", np.int32), ("right", np.int32)])
+
+
+def static_bvh(walls, wall_order=None):
+    """lc_static_bvh: the static BVH of ai::init over the walls (statics in wall_order), pre-order BVH_NODE records."""
+    w = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    o = None if wall_order is None else np.ascontiguousarray(wall_order, np.int32)
+    out = np.zeros(2 * len(w), BVH_NODE)
+    m = C.c_int32(0)
+    _ck(lib().lc_static_bvh(len(w), _p(w), _p(o), _p(out), len(out), C.byref(m)))
+    return out[:m.value].copy()
 
 
 def _order(order, n):

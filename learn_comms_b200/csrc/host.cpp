@@ -8,8 +8,11 @@
 #include <fstream>
 #include <functional>
 #include <sstream>
+#include <algorithm>
+#include <limits>
 #include <string>
 #include <unordered_map>
+#include <vector>
 
 namespace {
 
@@ -137,6 +140,82 @@ int32_t lc_table_order(int32_t n_agents, int32_t n_walls, int32_t* agent_order, 
             for (const auto& kv : volumes)
                 if ((int32_t)kv.first > n_agents) wall_order[m++] = (int32_t)kv.first - 1 - n_agents;
         }
+    } catch (...) {
+        return LC_ERR_CAPACITY;
+    }
+    return LC_OK;
+}
+
+// ---- static BVH over the walls (ai.cpp:16-18,36: built once by ai::init from the statics in table order) ----
+// physics::simulate pushes an agent out of every wall static_bvh->query reports (physics.cpp:60,67-69).  That query is
+// NOT "every wall the disc touches": inner nodes are entered through circ_rect_collider on the node's box, which tests a
+// single point of the disc (BoundVolume.cpp:196-201, quirk Q8), so a wall near the END of a long row of tiles can be
+// missed, and the order of the reported hits (= order of the push-outs) is the tree's depth-first leaf order.  Both are a
+// function of the tree alone — walls never move — so the tree is rebuilt here exactly as BVH.cpp:9-49,144-251 does: two
+// index tables sorted by origin x / z with std::sort (ties between tiles of one row are decided by libstdc++'s
+// introsort on the same input sequence, hence the same container algorithm here), tight box per node, split of the
+// longer axis into floor(n/2) | rest while the other table is stably partitioned.  Nodes are emitted in pre-order.
+namespace {
+struct BvhIdx { unsigned obj, oth; };
+struct BvhBuild {
+    const lc_rect* walls;        // creation order
+    const int32_t* objs;         // statics order -> creation index
+    std::vector<lc_bvh_node>* out;
+    int32_t build(const std::vector<BvhIdx>& sx, const std::vector<BvhIdx>& sz) {
+        const int32_t me = (int32_t)out->size();
+        out->push_back(lc_bvh_node{0.f, 0.f, 0.f, 0.f, -1, -1});
+        if (sx.size() == 1) {  // leaf: the wall itself
+            (*out)[me].left = objs[sx[0].obj];
+            return me;
+        }
+        float min_x = std::numeric_limits<float>::max(), min_z = min_x, max_x = -min_x, max_z = -min_x;
+        for (const BvhIdx& k : sx) {
+            const lc_rect& r = walls[objs[k.obj]];
+            const float hx = r.w / 2, hz = r.h / 2;
+            min_x = std::min(min_x, r.ox - hx); max_x = std::max(max_x, r.ox + hx);
+            min_z = std::min(min_z, r.oy - hz); max_z = std::max(max_z, r.oy + hz);
+        }
+        const float dx = max_x - min_x, dz = max_z - min_z;
+        (*out)[me].ox = min_x + dx / 2; (*out)[me].oy = min_z + dz / 2; (*out)[me].w = dx; (*out)[me].h = dz;
+        std::vector<BvhIdx> xl, zl, xr, zr;
+        if (dx > dz) split(sx, sz, xl, zl, xr, zr); else split(sz, sx, zl, xl, zr, xr);
+        const int32_t l = build(xl, zl), r = build(xr, zr);
+        (*out)[me].left = l; (*out)[me].right = r;
+        return me;
+    }
+    // a = table of the split axis, b = the other one; each entry's .oth is its position in the other table
+    static void split(const std::vector<BvhIdx>& a, const std::vector<BvhIdx>& b, std::vector<BvhIdx>& al, std::vector<BvhIdx>& bl,
+                      std::vector<BvhIdx>& ar, std::vector<BvhIdx>& br) {
+        const unsigned half = static_cast<unsigned>(static_cast<float>(a.size()) / 2.f);
+        const unsigned rest = static_cast<unsigned>(static_cast<float>(a.size()) / 2.f + .5f);
+        al.assign(half, BvhIdx{0, 0}); bl.assign(half, BvhIdx{0, 0}); ar.assign(rest, BvhIdx{0, 0}); br.assign(rest, BvhIdx{0, 0});
+        for (size_t i = 0; i < a.size(); ++i) (i < half ? al[i] : ar[i - half]) = BvhIdx{a[i].obj, ~0u};
+        unsigned nl = 0, nr = 0;
+        for (const BvhIdx& e : b) {
+            if (e.oth < half) { bl[nl] = BvhIdx{e.obj, e.oth}; al[e.oth].oth = nl++; }
+            else { br[nr] = BvhIdx{e.obj, e.oth - half}; ar[e.oth - half].oth = nr++; }
+        }
+    }
+};
+}  // namespace
+
+int32_t lc_static_bvh(int32_t n_walls, const lc_rect* walls, const int32_t* wall_order, lc_bvh_node* nodes, int32_t cap, int32_t* n_nodes) {
+    if (n_walls < 1 || !walls || !nodes || !n_nodes) return LC_ERR_ARG;
+    try {
+        std::vector<int32_t> objs((size_t)n_walls);
+        for (int32_t k = 0; k < n_walls; ++k) objs[k] = wall_order ? wall_order[k] : k;
+        std::vector<BvhIdx> sx((size_t)n_walls), sz((size_t)n_walls);
+        for (unsigned i = 0; i < (unsigned)n_walls; ++i) sx[i] = sz[i] = BvhIdx{i, 0};
+        std::sort(sx.begin(), sx.end(), [&](BvhIdx a, BvhIdx b) { return walls[objs[a.obj]].ox < walls[objs[b.obj]].ox; });
+        for (size_t i = 0; i < sx.size(); ++i) sz[sx[i].obj].oth = (unsigned)i;
+        std::sort(sz.begin(), sz.end(), [&](BvhIdx a, BvhIdx b) { return walls[objs[a.obj]].oy < walls[objs[b.obj]].oy; });
+        for (size_t i = 0; i < sz.size(); ++i) sx[sz[i].oth].oth = (unsigned)i;
+        std::vector<lc_bvh_node> out;
+        BvhBuild bb{walls, objs.data(), &out};
+        bb.build(sx, sz);
+        *n_nodes = (int32_t)out.size();
+        if ((int32_t)out.size() > cap) return LC_ERR_CAPACITY;
+        std::copy(out.begin(), out.end(), nodes);
     } catch (...) {
         return LC_ERR_CAPACITY;
     }

@@ -80,6 +80,15 @@ struct canon_sim {
     /* table iteration order (default ascending index); reference = libstdc++ unordered_map order, quirk Q4 */
     int32_t* order;
     int gauss_seidel; /* physics pass sees already-processed agents at their integrated positions (reference, §3.4) */
+    /* walled scenes: per-agent waypoint lists (Agent::plan, Agent.h:14), planner callback, wall visiting order, static BVH */
+    float* plan;       /* [n][CANON_MAX_PLAN][2] */
+    int32_t* n_plan;   /* [n]; 0 = no plan (unreachable goal): has_plan() false, Agent.h:20-22 */
+    int32_t* wall_order;
+    int32_t (*plan_fn)(void*, int32_t, const float*, const float*, int32_t, float*);
+    void* plan_user;
+    int32_t n_bvh;
+    canon_bvh_node* bvh;
+    int64_t replans, wall_hits;
     /* scratch */
     v2* pos_new;
     /* grid scratch */
@@ -87,11 +96,30 @@ struct canon_sim {
     int32_t gcap;
 };
 
-#define PLAN_SIZE 1 /* wall-free scenes: GMP::plan_one yields plan = [final_goal] (GMP.cpp:91-110) */
-static inline int is_done(const canon_sim* s, int i) { return s->num_done[i] == PLAN_SIZE; } /* Agent.h:22-24 */
+/* Agent.h:20-26: has_plan() = plan non-empty; done() = has_plan() && num_done == plan->size().  Wall-free scenes:
+ * GMP::plan_one yields plan = [final_goal] (GMP.cpp:91-110). */
+static inline int has_plan(const canon_sim* s, int i) { return s->n_plan[i] > 0; }
+static inline int is_done(const canon_sim* s, int i) { return has_plan(s, i) && s->num_done[i] == s->n_plan[i]; }
+static inline float* plan_of(const canon_sim* s, int i) { return s->plan + (size_t)i * CANON_MAX_PLAN * 2; }
+
+/* GMP::plan_one (GMP.cpp:91-110): new waypoint list from the agent's current position, num_done = 0 */
+static int plan_one(canon_sim* s, int i) {
+    float* wp = plan_of(s, i);
+    if (s->n_walls > 0) {
+        float start[2] = {s->pos[i].x, s->pos[i].y}, goal[2] = {s->goal[i].x, s->goal[i].y};
+        int32_t k = s->plan_fn(s->plan_user, i, start, goal, CANON_MAX_PLAN, wp);
+        if (k < 0 || k > CANON_MAX_PLAN) { fprintf(stderr, "canon: planner failed for agent %d (%d)\n", i, k); abort(); }
+        s->n_plan[i] = k;
+    } else {
+        wp[0] = s->goal[i].x; wp[1] = s->goal[i].y;
+        s->n_plan[i] = 1;
+    }
+    s->num_done[i] = 0;
+    return s->n_plan[i];
+}
 
 canon_sim* canon_create(const canon_desc* d) {
-    if (d->n_walls > 0) return NULL; /* walled rollouts need the planner (GMP.cpp), not restated yet */
+    if (d->n_walls > 0 && !d->plan_fn) return NULL; /* walled rollouts need the global planner (canon.h) */
     canon_sim* s = (canon_sim*)calloc(1, sizeof(*s));
     int n = d->n;
     s->n = n;
@@ -114,18 +142,41 @@ canon_sim* canon_create(const canon_desc* d) {
 #undef AL
 #define AL2(p) s->p = (int32_t*)calloc((size_t)n + 1, sizeof(int32_t))
     AL2(order);
-    for (int i = 0; i < n; ++i) s->order[i] = i;
+    AL2(n_plan);
+    for (int i = 0; i < n; ++i) s->order[i] = d->table_order ? d->table_order[i] : i;
+    s->plan = (float*)calloc((size_t)(n + 1) * CANON_MAX_PLAN * 2, sizeof(float));
+    s->plan_fn = d->plan_fn;
+    s->plan_user = d->plan_user;
+    if (d->n_walls > 0) {
+        s->wall_order = (int32_t*)malloc(sizeof(int32_t) * (size_t)d->n_walls);
+        for (int k = 0; k < d->n_walls; ++k) s->wall_order[k] = d->wall_order ? d->wall_order[k] : k;
+        if (d->n_bvh > 0 && d->bvh) {
+            s->n_bvh = d->n_bvh;
+            s->bvh = (canon_bvh_node*)malloc(sizeof(canon_bvh_node) * (size_t)d->n_bvh);
+            memcpy(s->bvh, d->bvh, sizeof(canon_bvh_node) * (size_t)d->n_bvh);
+        }
+    }
     s->c = calloc((size_t)n + 1, sizeof(float[3]));
     s->c_buf = calloc((size_t)n + 1, sizeof(float[3]));
     for (int i = 0; i < n; ++i) {
-        /* demo.cpp:563-581 create_robo; ai.cpp:107-127 ai::init; physics.cpp:15-21 prewarm (all zero) */
+        /* demo.cpp:563-581 create_robo; physics.cpp:15-21 prewarm (all zero) */
         s->pos[i] = V2(d->pos[2 * i], d->pos[2 * i + 1]);
         s->goal[i] = V2(d->goal[2 * i], d->goal[2 * i + 1]);
         s->facing[i] = sub2(s->goal[i], s->pos[i]); /* un-normalised, demo.cpp:580 */
-        s->local_goal[i] = V2(0.f, 0.f);            /* ai.cpp:112 */
+    }
+    for (int oi = 0; oi < n; ++oi) { /* ai.cpp:107-127 ai::init, POOL.for_<Agent> = table order (the planner is stateful) */
+        int i = s->order[oi];
+        s->local_goal[i] = V2(0.f, 0.f); /* ai.cpp:112 */
+        plan_one(s, i);                  /* ai.cpp:115 */
         s->goal_dist[i] = len_2(sub2(s->goal[i], s->pos[i])); /* ai.cpp:116 */
-        float mt = -1.0f;                            /* ai.cpp:121-126 */
-        mt += len_2(sub2(s->goal[i], s->pos[i]));
+        float mt = -1.0f;                /* ai.cpp:121-126: path length minus the untimed last metre */
+        v2 last = s->pos[i];
+        const float* wp = plan_of(s, i);
+        for (int k = 0; k < s->n_plan[i]; ++k) {
+            v2 p = V2(wp[2 * k], wp[2 * k + 1]);
+            mt += len_2(sub2(p, last));
+            last = p;
+        }
         s->min_time[i] = mt;
     }
     return s;
@@ -137,7 +188,7 @@ void canon_destroy(canon_sim* s) {
     free(s->facing); free(s->c); free(s->c_buf); free(s->f_buf); free(s->goal_dist); free(s->min_time);
     free(s->num_done); free(s->counted); free(s->lost); free(s->partner); free(s->nbr_cnt);
     free(s->nbr_ptr); free(s->nbr_idx); free(s->pos_new); free(s->cell_start); free(s->cell_items);
-    free(s->walls); free(s->order);
+    free(s->walls); free(s->order); free(s->plan); free(s->n_plan); free(s->wall_order); free(s->bvh);
     free(s);
 }
 
@@ -437,33 +488,38 @@ static void update_agents(canon_sim* s) {
         int i = s->order[oi];
         /* ai.cpp:153-168 */
         s->goal_dist[i] = len_2(sub2(s->goal[i], s->pos[i]));
+        v2 o = s->pos[i];
+        const float opos[2] = {o.x, o.y};
         int next = s->num_done[i];
         int visible_next = 0;
-        if (next < PLAN_SIZE) visible_next = 1; /* Cspace2d::line_of_sight over zero obstacles (PRM.cpp:169-173) */
+        if (has_plan(s, i) && next < s->n_plan[i]) /* Cspace2d::line_of_sight (PRM.cpp:169-173): trivially true without walls */
+            visible_next = canon_cspace_line_of_sight(s->walls, s->n_walls, s->r, opos, plan_of(s, i) + 2 * next);
         s->lost[i] = visible_next ? 0 : s->lost[i] + 1;
-        int need_replan = (is_done(s, i) && s->goal_dist[i] > 1.f) ||
+        int need_replan = !has_plan(s, i) || (is_done(s, i) && s->goal_dist[i] > 1.f) ||
                           (!is_done(s, i) && !visible_next && s->lost[i] >= 360);
         if (replanned < limit && need_replan) {
-            s->num_done[i] = 0; /* GMP::plan_one: plan = [final_goal], num_done = 0 (GMP.cpp:91-110) */
+            plan_one(s, i); /* GMP::plan_one from the current (synced) position; num_done = 0 (GMP.cpp:91-110) */
             ++replanned;
+            ++s->replans;
             s->lost[i] = 0;
         }
-        /* LMP::calc_sum_force, LMP.cpp:244-273; lookahead LMP.cpp:84-113 */
-        v2 o = s->pos[i];
-        int target = s->num_done[i];
-        if (target < PLAN_SIZE) {
-            int at_target = len2_2(sub2(o, s->goal[i])) < 1.f; /* ai::at_dist */
-            if (at_target) ++target;
-            if (target < PLAN_SIZE) s->local_goal[i] = s->goal[i];
-            s->num_done[i] = target;
-        } else {
-            s->local_goal[i] = s->goal[i];
+        /* LMP::calc_sum_force, LMP.cpp:244-273 */
+        v2 goal_vel;
+        if (has_plan(s, i)) {
+            float lg[2] = {s->local_goal[i].x, s->local_goal[i].y};
+            int32_t nd = s->num_done[i];
+            canon_lookahead(s->walls, s->n_walls, s->r, opos, plan_of(s, i), s->n_plan[i], &nd, lg); /* LMP.cpp:84-113 */
+            s->num_done[i] = nd;
+            s->local_goal[i] = V2(lg[0], lg[1]);
+            s->rng = canon_lcg_next(s->rng); /* one draw, used for both components (LMP.cpp:261-263) */
+            float eps = canon_uniform(s->rng, -.01f, .01f);
+            v2 fuzzy = add2(s->local_goal[i], V2(eps, eps));
+            v2 diff = sub2(fuzzy, o);
+            goal_vel = mul2s(div2s(diff, glm_max(1.0f, len_2(diff))), 1.0f);
+        } else { /* LMP.cpp:267-270: no plan, no draw */
+            s->local_goal[i] = o;
+            goal_vel = V2(0.f, 0.f);
         }
-        s->rng = canon_lcg_next(s->rng); /* one draw, used for both components (LMP.cpp:261-263) */
-        float eps = canon_uniform(s->rng, -.01f, .01f);
-        v2 fuzzy = add2(s->local_goal[i], V2(eps, eps));
-        v2 diff = sub2(fuzzy, o);
-        v2 goal_vel = mul2s(div2s(diff, glm_max(1.0f, len_2(diff))), 1.0f);
         v2 vi = s->vel[i];
         v2 goal_F = mul2s(sub2(goal_vel, vi), 2.0f);
         v2 ttc_F = V2(0.f, 0.f);
@@ -515,6 +571,11 @@ static void update_agents(canon_sim* s) {
         }
 #undef PAIR
         s->nbr_cnt[i] = cnt;
+        for (int k = 0; k < s->n_walls; ++k) { /* LMP.cpp:307-319: the statics loop, in the BoundVolume* table's order */
+            float f[2];
+            const float vel2[2] = {vi.x, vi.y};
+            if (canon_wall_force(opos, s->r, vel2, &s->walls[s->wall_order[k]], f)) ttc_F = add2(ttc_F, V2(f[0], f[1]));
+        }
         v2 f2d = add2(goal_F, ttc_F);
         s->force[i] = add2(s->force[i], f2d); /* ai.cpp:172 */
     }
@@ -604,6 +665,27 @@ static void physics_simulate(canon_sim* s, float dt) {
             qsort(hits, (size_t)nh, sizeof(hit_t), hit_cmp);
             for (int q = 0; q < nh; ++q) { push_away(&p, &vfh, hits[q].f); s->coll_hits++; }
         }
+        if (s->n_walls > 0) { /* physics.cpp:60,67-69: static_bvh->query at the integrated position, after the agent hits */
+            const float q[2] = {pq.x, pq.y};
+            float away[2];
+            if (s->bvh) { /* BVH::query_(Circ*) (BVH.cpp:106-138): depth-first, left before right, approximate inner test */
+                int32_t stack[64], sp = 0;
+                stack[sp++] = 0;
+                while (sp > 0) {
+                    const canon_bvh_node* nd = &s->bvh[stack[--sp]];
+                    if (nd->right < 0) {
+                        if (canon_circ_wall_hit(q, r, &s->walls[nd->left], away)) { push_away(&p, &vfh, V2(away[0], away[1])); s->wall_hits++; }
+                    } else {
+                        canon_rect box = {nd->ox, nd->oy, nd->w, nd->h};
+                        float unused[2];
+                        if (canon_circ_wall_hit(q, r, &box, unused)) { stack[sp++] = nd->right; stack[sp++] = nd->left; }
+                    }
+                }
+            } else {
+                for (int k = 0; k < s->n_walls; ++k)
+                    if (canon_circ_wall_hit(q, r, &s->walls[s->wall_order[k]], away)) { push_away(&p, &vfh, V2(away[0], away[1])); s->wall_hits++; }
+            }
+        }
         s->pos[i] = p;
         s->vfh[i] = vfh;
         if (!is_done(s, i)) { /* physics.cpp:72-76; vel_count is never incremented (quirk Q6) */
@@ -690,6 +772,19 @@ int64_t canon_get_neighbor_lists(const canon_sim* s, int64_t* row_ptr, int32_t* 
     }
     if (row_ptr) row_ptr[s->n] = at;
     return s->nbr_total;
+}
+int32_t canon_get_plan(const canon_sim* s, int32_t agent, float* waypoints, int32_t cap) {
+    int32_t k = s->n_plan[agent];
+    if (waypoints) memcpy(waypoints, plan_of(s, agent), sizeof(float) * 2 * (size_t)(k < cap ? k : cap));
+    return k;
+}
+void canon_get_walled(const canon_sim* s, int32_t* n_plan, int32_t* lost_frames, int64_t* replans, int64_t* wall_hits) {
+    for (int i = 0; i < s->n; ++i) {
+        if (n_plan) n_plan[i] = s->n_plan[i];
+        if (lost_frames) lost_frames[i] = (int32_t)s->lost[i];
+    }
+    if (replans) *replans = s->replans;
+    if (wall_hits) *wall_hits = s->wall_hits;
 }
 int64_t canon_overlap_pairs(const canon_sim* s) { return s->overlap_pairs; }
 int64_t canon_collision_hits(const canon_sim* s) { return s->coll_hits; }
@@ -942,46 +1037,138 @@ static v2 axial_goal(v2 pos) { /* demo.cpp:36-41 */
     return V2(-faxis * pos.x, faxis * pos.y);
 }
 
-int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration, int32_t cap) {
-    int32_t n = 0;
-    float md = 0.f;
-    switch (scene) {
-    case 0: n = 60; md = 45.f; break;
-    case 1: n = 90; md = 70.f; break;
-    case 4: n = 56; md = 40.f; break;
-    case 5: n = 56; md = 70.f; break;
-    case 12: n = 200; md = 30.f; break;
-    default: return 0; /* walled scenes: not restated yet */
-    }
-    if (n > cap) return -n;
-    *max_duration = md;
+/* demo.cpp:106-124 wall layouts */
+static v2 hole_wall(unsigned i, float gap, float scale) { /* make_hole_wall */
+    float x = 0;
+    float side = ((i % 2) == 0 ? 1.f : -1.f);
+    float height = (float)(i / 2);
+    float y = side * (scale * (height + .5f) + gap / 2.f);
+    return V2(x, y);
+}
+static v2 hall_wall(unsigned i, float gap, float scale) { /* make_hall; (i + 2 % 4) / 4 == (i + 2) / 4 */
+    float side = ((i % 2) == 0 ? 1.f : -1.f);
+    float width = (float)((i + 2 % 4) / 4);
+    float xside = (i % 4 < 2 ? 1.f : -1.f);
+    float x = xside * scale * width;
+    float y = side * .5f * (gap + scale);
+    return V2(x, y);
+}
+static const float SCENE6_WALLS[12][2] = {{-3, -3}, {-3, 3}, {3, -3}, {3, 3}, {4, 4}, {4, -4}, {6, -5}, {6, 5}, {-4, 4}, {-6, 5}, {-4, -4}, {-6, -5}};
+static const float SCENE11_WALLS[32][2] = {
+    {0, 8}, {2, 8}, {4, 8}, {8, 8}, {-6, 8}, {-4, 8}, {-2, 8}, {-8, 0}, {-8, 2}, {-8, 4}, {-8, 6}, {-8, 8}, {-8, -6}, {-8, -4}, {-8, -2},
+    {-7.4f, -8}, {1.4f, -8}, {3.4f, -8}, {5.4f, -8}, {-5.4f, -8}, {-3.4f, -8}, {-1.4f, -8}, {8, 0}, {8, 2}, {8, 4}, {8, 6}, {7.4f, -8},
+    {8, -6}, {8, -4}, {8, -2}, {6, 3}, {4, 3}};
+static const float SCENE18_Y[20] = {1, -1, 3, -3, 6, -5, 8, -8, 10, -10, 12, -12, 14, -14, 16, -16, 18, -18, 20, -20};
+
+int32_t canon_scene_full(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration, int32_t cap,
+                         canon_rect* walls, int32_t* n_walls_out, int32_t wall_cap) {
+    int32_t n = 0, nw = 0;
+    float md = 0.f, ws = 0.f;
+    enum { G_OPPOSITE, G_AXIAL, G_MIRROR_X, G_TRANSLATE, G_RANDOM } gk = G_OPPOSITE;
+    enum { P_RADIAL, P_REGIMENT, P_LIST, P_RANDOM } pk = P_RADIAL;
+    float radius = 0.f;
+    v2 translate = V2(0.f, 0.f);
+    v2 list[4];
     regiment regs[4];
-    if (scene == 4 || scene == 5) { /* demo.cpp:96-104 make_intersecting_bots(14, 7, 6.f) */
+    memset(regs, 0, sizeof regs);
+#define REG2(a, b) do { regs[0] = center(a); regs[1] = center(b); pk = P_REGIMENT; } while (0)
+    switch (scene) { /* demo.cpp:141-511 make_scene */
+    case 0: n = 60; md = 45.f; radius = 10.f; break;
+    case 1: n = 90; md = 70.f; radius = 13.f; break;
+    case 2: n = 60; nw = 60; ws = 0.3f; md = 40.f; radius = 10.f; break;
+    case 3: n = 60; nw = 1; ws = 4.0f; md = 40.f; radius = 10.f; break;
+    case 4: case 5: case 6: { /* demo.cpp:96-104 make_intersecting_bots(14, 7, 6.f) */
+        n = 56; md = scene == 5 ? 70.f : 40.f; gk = scene == 5 ? G_OPPOSITE : G_AXIAL;
+        if (scene == 6) { nw = 12; ws = 2.0f; }
         float d = 6.f;
         regiment a = {{1, 0}, {-d, 0}, {1.f, 1.f}, 7, 14}, b = {{-1, 0}, {d, 0}, {1.f, 1.f}, 7, 14};
         regiment c = {{0, 1}, {0, -d}, {1.f, 1.f}, 7, 14}, e = {{0, -1}, {0, d}, {1.f, 1.f}, 7, 14};
         regs[0] = center(a); regs[1] = center(b); regs[2] = center(c); regs[3] = center(e);
+        pk = P_REGIMENT;
+        break;
     }
+    case 7: n = 2; nw = 30; ws = 2.0f; md = 70.f; gk = G_MIRROR_X; pk = P_LIST; list[0] = V2(-3.f, 0); list[1] = V2(3.f, 0); break;
+    case 8: { n = 4; nw = 30; ws = 2.0f; md = 30.f; gk = G_MIRROR_X;
+        regiment a = {{1, 0}, {-3, 0}, {1.f, 1.f}, 2, 2}, b = {{-1, 0}, {3, 0}, {1.f, 1.f}, 2, 2}; REG2(a, b); break; }
+    case 9: { n = 40; nw = 30; ws = 2.0f; md = 100.f; gk = G_MIRROR_X;
+        regiment a = {{1, 0}, {-3, 0}, {1.f, 1.f}, 5, 20}, b = {{-1, 0}, {3, 0}, {1.f, 1.f}, 5, 20}; REG2(a, b); break; }
+    case 10: { n = 40; nw = 30; ws = 2.0f; md = 100.f; gk = G_MIRROR_X;
+        regiment a = {{1, 0}, {-3, 0}, {1.f, 1.f}, 5, 5}, b = {{-1, 0}, {3, 0}, {1.f, 1.f}, 5, 35}; REG2(a, b); break; }
+    case 11: { n = 70; nw = 32; ws = 2.0f; md = 100.0f; gk = G_TRANSLATE; translate = V2(-20.f, 0.f);
+        regiment a = {{0, 1}, {1, 6}, {2.f, 1.5f}, 3, 6}, b = {{-1, 0}, {-4, -2}, {1.f, 1.f}, 8, 64}; REG2(a, b); break; }
+    case 12: n = 200; md = 30.f; pk = P_RANDOM; gk = G_RANDOM; break;
+    case 13: { n = 40; nw = 18; ws = 2.0f; md = 90.0f; gk = G_MIRROR_X;
+        regiment a = {{1, 0}, {-3, 0}, {.5f, .7f}, 5, 20}, b = {{-1, 0}, {3, 0}, {.5f, .7f}, 5, 20}; REG2(a, b); break; }
+    case 14: n = 2; md = 30.f; gk = G_MIRROR_X; pk = P_LIST; list[0] = V2(-5.f, .1f); list[1] = V2(3.f, 0); break;
+    case 15: n = 3; md = 40.f; gk = G_MIRROR_X; pk = P_LIST; list[0] = V2(-5.f, .1f); list[1] = V2(3.f, 0); list[2] = V2(7.f, 0); break;
+    case 16: n = 4; md = 40.f; gk = G_MIRROR_X; pk = P_LIST;
+        list[0] = V2(-5.f, .1f); list[1] = V2(3.f, 0); list[2] = V2(7.f, 0); list[3] = V2(-2.f, .1f); break;
+    case 17: { n = 4; md = 45.f; gk = G_MIRROR_X;
+        regiment a = {{1, 0}, {-5, .1f}, {1.f, 1.f}, 2, 2}, b = {{-1, 0}, {3, 0}, {1.f, 1.f}, 2, 2}; REG2(a, b); break; }
+    case 18: { n = 65; nw = 20; ws = 2.0f; md = 60.f; gk = G_TRANSLATE; translate = V2(-15.f, 0.f);
+        regiment a = {{-1, 0}, {3, 3}, {1.f, 1.f}, 5, 5}, b = {{-1, 0}, {3, -6}, {1.f, 1.f}, 10, 60}; REG2(a, b); break; }
+    default:
+        if (scene > 100 && scene >= 900) { /* demo.cpp:490-508: variable-size doorway, num_robos = 40 + (scn - 900) */
+            n = 40 + (int32_t)(scene - 900); nw = 30; ws = 2.0f; md = 100.f; gk = G_MIRROR_X;
+            unsigned even_size = (unsigned)n / 2, odd_size = even_size + (unsigned)n % 2;
+            regiment a = {{1, 0}, {-3, 0}, {1.f, 1.f}, 5, odd_size}, b = {{-1, 0}, {3, 0}, {1.f, 1.f}, 5, even_size};
+            REG2(a, b);
+        } else return 0; /* 19..100: the reference leaves num_robos uninitialised */
+    }
+#undef REG2
+    if (n > cap) return -n;
+    if (nw > 0 && (!walls || nw > wall_cap)) return 0;
+    *max_duration = md;
+    uint32_t x = *rng_state;
     for (int32_t i = 0; i < n; ++i) {
         v2 p, g;
-        switch (scene) {
-        case 0: p = radial((unsigned)i, 60, 10.f); g = V2(-p.x, -p.y); break;
-        case 1: p = radial((unsigned)i, 90, 13.f); g = V2(-p.x, -p.y); break;
-        case 4: p = regimented(regs, (unsigned)i); g = axial_goal(p); break;
-        case 5: p = regimented(regs, (unsigned)i); g = V2(-p.x, -p.y); break;
-        default: { /* scene 12, demo.cpp:358-371: glm::vec2(inside(gen), inside(gen)); g++ evaluates the
-                      constructor arguments right to left, so the first draw lands in .y (checked against O-ref) */
-            uint32_t x = *rng_state;
+        if (pk == P_RADIAL) p = radial((unsigned)i, (unsigned)n, radius);
+        else if (pk == P_REGIMENT) p = regimented(regs, (unsigned)i);
+        else if (pk == P_LIST) p = list[i];
+        else { /* scene 12, demo.cpp:358-371: glm::vec2(inside(gen), inside(gen)); g++ evaluates the constructor
+                  arguments right to left, so the first draw lands in .y (checked against O-ref) */
             x = canon_lcg_next(x); p.y = canon_uniform(x, -10.f, 10.f);
             x = canon_lcg_next(x); p.x = canon_uniform(x, -10.f, 10.f);
+        }
+        switch (gk) {
+        case G_OPPOSITE: g = V2(-p.x, -p.y); break;
+        case G_AXIAL: g = axial_goal(p); break;
+        case G_MIRROR_X: g = V2(-p.x, p.y); break;
+        case G_TRANSLATE: g = add2(p, translate); break;
+        default:
             x = canon_lcg_next(x); g.y = canon_uniform(x, -10.f, 10.f);
             x = canon_lcg_next(x); g.x = canon_uniform(x, -10.f, 10.f);
-            *rng_state = x;
-        }
         }
         pos[2 * i] = p.x; pos[2 * i + 1] = p.y;
         goal[2 * i] = g.x; goal[2 * i + 1] = g.y;
     }
+    for (int32_t i = 0; i < nw; ++i) { /* demo.cpp:633-635 create_wall(wall_pos_of(i)): square Rect of side wall_scale */
+        v2 p;
+        if (scene == 2) { /* demo.cpp:170-174: two draws per wall, right-to-left argument evaluation as above */
+            x = canon_lcg_next(x); p.y = canon_uniform(x, -7.f, 7.f);
+            x = canon_lcg_next(x); p.x = canon_uniform(x, -7.f, 7.f);
+        } else if (scene == 3) p = V2(0.f, 0.f);
+        else if (scene == 6) p = V2(SCENE6_WALLS[i][0], SCENE6_WALLS[i][1]);
+        else if (scene == 11) p = V2(SCENE11_WALLS[i][0], SCENE11_WALLS[i][1]);
+        else if (scene == 13) p = hall_wall((unsigned)i, 3.f, ws);
+        else if (scene == 18) p = V2(0.f, SCENE18_Y[i]);
+        else p = hole_wall((unsigned)i, 1.f, ws);
+        walls[i].ox = p.x; walls[i].oy = p.y; walls[i].w = ws; walls[i].h = ws;
+    }
+    *rng_state = x;
+    if (n_walls_out) *n_walls_out = nw;
+    return n;
+}
+
+int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration, int32_t cap) {
+    canon_rect walls[64];
+    int32_t nw = 0;
+    uint32_t x = *rng_state;
+    float md = 0.f;
+    int32_t n = canon_scene_full(scene, &x, pos, goal, &md, cap, walls, &nw, 64);
+    if (n <= 0 || nw > 0) return n < 0 ? n : 0; /* walled scenes: canon_scene_full */
+    *rng_state = x;
+    *max_duration = md;
     return n;
 }
 

@@ -37,7 +37,26 @@ typedef struct {
     int32_t use_grid;        /* 0 = brute-force all pairs (reference), 1 = uniform-grid search (same result) */
     int32_t n_walls;         /* static Rect obstacles (0 in wall-free scenes) */
     const canon_rect* walls;
+    /* table iteration orders (quirk Q4): table_order[k] = index of the k-th agent every component-table loop visits,
+     * wall_order[k] = index of the k-th wall the statics loop (LMP.cpp:307) and the static push-out visit; NULL = ascending */
+    const int32_t* table_order;
+    const int32_t* wall_order;
+    /* global planner (GMP::plan_one, GMP.cpp:91-110), required when n_walls > 0: fills waypoints[cap][2] with the path from
+     * the first waypoint after `start` to `goal` inclusive and returns their number (0 = unreachable, < 0 = error).  Called
+     * once per agent in table order at creation (ai::init, ai.cpp:107-127) and for every replan (ai.cpp:161-166).  The
+     * roadmap behind it is stateful in the reference (shared std_prm), so it is NOT restated here: tests bind the host
+     * planner that tests/test_planner.py pins bit for bit against the reference's own Cspace2d / PRM / GMP. */
+    int32_t (*plan_fn)(void* user, int32_t agent, const float* start, const float* goal, int32_t cap, float* waypoints);
+    void* plan_user;
+    /* optional flattened static BVH (BVH.cpp:9-49,144-251 over the walls): n_bvh nodes of 6 floats + 2 ints laid out as
+     * canon_bvh_node; NULL = every wall is tested with the exact leaf predicate in wall_order */
+    int32_t n_bvh;
+    const void* bvh;
 } canon_desc;
+
+/* one node of the static BVH: aabb (Rect), children (left, right >= 0) or leaf (right < 0, left = wall index) */
+typedef struct { float ox, oy, w, h; int32_t left, right; } canon_bvh_node;
+#define CANON_MAX_PLAN 64
 
 canon_sim* canon_create(const canon_desc* d);
 void canon_destroy(canon_sim* s);
@@ -96,10 +115,16 @@ int32_t canon_cspace_line_of_sight(const canon_rect* walls, int32_t n_walls, flo
 void canon_lookahead(const canon_rect* walls, int32_t n_walls, float agent_r, const float* pos, const float* plan,
                      int32_t n_plan, int32_t* num_done, float* local_goal);                   /* LMP.cpp:84-113 */
 
-/* scene catalogue (demo.cpp:141-511): fills pos/goal for wall-free scenes; returns n (0 = unsupported).
- * rng_state is advanced by construction-time draws (scene 12). */
+/* scene catalogue (demo.cpp:141-511): fills pos/goal; returns n (0 = unsupported or walled: use canon_scene_full).
+ * rng_state is advanced by construction-time draws (scenes 2 and 12). */
 int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration,
                     int32_t cap);
+/* the whole catalogue incl. walls (demo.cpp:161-511, create_wall :515-537: square Rects of side wall_scale) */
+int32_t canon_scene_full(uint32_t scene, uint32_t* rng_state, float* pos, float* goal, float* max_duration, int32_t cap,
+                         canon_rect* walls, int32_t* n_walls, int32_t wall_cap);
+/* walled-scene diagnostics of the last frame: plan of an agent, lost_frames, replans / wall hits so far */
+int32_t canon_get_plan(const canon_sim* s, int32_t agent, float* waypoints, int32_t cap);
+void canon_get_walled(const canon_sim* s, int32_t* n_plan, int32_t* lost_frames, int64_t* replans, int64_t* wall_hits);
 
 /* config / result files (comm.cpp:74-142, pso_opt.py:17-41) */
 int32_t canon_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);

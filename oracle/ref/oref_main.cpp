@@ -9,6 +9,8 @@
 //   int32 magic 0x4f524546, n, n_walls, frames_dumped_capacity
 //   int32 order[n]            iteration order of POOL.for_<Agent> as entity ids (the unordered_map order, quirk Q4)
 //   float pos0[n][2], goal[n][2], min_time[n]          state after ai::init + prewarm + all_sync, entity-id order
+//   int32 wall_order[n_walls]  iteration order of the walls in POOL.for_<BoundVolume*> (0-based wall index);
+//   float walls[n_walls][4]    Rect origin x, z, width, height in creation order (demo.cpp:633-635)
 //   per dumped frame: int32 frame; float pos[n][2], vel[n][2], vfh[n][2], c[n][3], facing[n][2], local_goal[n][2],
 //                     goal_dist[n]; int32 num_done[n]; float run_avg, run_std, avg_velocity; int32 total_num_done, all_done
 //   trailer: int32 -1, frames_executed; float avg_velocity, group_time, run_avg, run_std; int32 total_num_done
@@ -124,6 +126,17 @@ int main(int argc, char** argv) {
         for (auto& r : rows) put(r.pos, 2);
         for (auto& r : rows) put(r.goal, 2);
         for (auto& r : rows) put_f(r.min_time);
+        std::vector<int32_t> worder;
+        std::vector<float> wrect(4 * (size_t)(n_other - n), 0.f);
+        POOL.for_<BoundVolume*>([&](BoundVolume*& bv, Entity& e) {
+            if (e.id <= n) return;
+            worder.push_back((int32_t)(e.id - n - 1));
+            Rect* r = static_cast<Rect*>(bv);
+            float* w = &wrect[4 * (size_t)(e.id - n - 1)];
+            w[0] = r->_o.x; w[1] = r->_o.y; w[2] = r->_w; w[3] = r->_h;
+        });
+        put(worder.data(), worder.size());
+        put(wrect.data(), wrect.size());
     }
 
     auto t0 = std::chrono::steady_clock::now();

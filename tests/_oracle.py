@@ -13,11 +13,17 @@ class Rect(C.Structure):
     _fields_ = [("ox", C.c_float), ("oy", C.c_float), ("w", C.c_float), ("h", C.c_float)]
 
 
+PLAN_FN = C.CFUNCTYPE(C.c_int32, C.c_void_p, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int32, C.POINTER(C.c_float))
+MAX_PLAN = 64  # CANON_MAX_PLAN
+BVH_NODE = np.dtype([("ox", np.float32), ("oy", np.float32), ("w", np.float32), ("h", np.float32), ("left", np.int32), ("right", np.int32)])
+
+
 class Desc(C.Structure):
     _fields_ = [("n", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p), ("radius", C.c_float),
                 ("max_duration", C.c_float), ("rng_state", C.c_uint32), ("m_cv", C.c_void_p),
                 ("m_f", C.c_void_p), ("comm_enabled", C.c_int32), ("use_grid", C.c_int32),
-                ("n_walls", C.c_int32), ("walls", C.c_void_p)]
+                ("n_walls", C.c_int32), ("walls", C.c_void_p), ("table_order", C.c_void_p), ("wall_order", C.c_void_p),
+                ("plan_fn", PLAN_FN), ("plan_user", C.c_void_p), ("n_bvh", C.c_int32), ("bvh", C.c_void_p)]
 
 
 def lib():
@@ -61,6 +67,12 @@ def lib():
         L.canon_scene.argtypes = [C.c_uint32, C.POINTER(C.c_uint32), C.c_void_p, C.c_void_p,
                                   C.POINTER(C.c_float), C.c_int32]
         L.canon_scene.restype = C.c_int32
+        L.canon_scene_full.argtypes = [C.c_uint32, C.POINTER(C.c_uint32), C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.c_int32,
+                                       C.c_void_p, C.POINTER(C.c_int32), C.c_int32]
+        L.canon_scene_full.restype = C.c_int32
+        L.canon_get_plan.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+        L.canon_get_plan.restype = C.c_int32
+        L.canon_get_walled.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.canon_read_config.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p]
         L.canon_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.canon_wall_geometry_batch.argtypes = [C.c_int32, C.c_void_p, C.c_void_p]
@@ -117,18 +129,63 @@ def scene(scene_id, seed=0):
     return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value)
 
 
+def scene_full(scene_id, seed=0):
+    """The whole catalogue incl. walls -> pos, goal, max_duration, rng_state, walls [W][4]."""
+    L = lib()
+    rng = C.c_uint32(L.canon_lcg_seed(seed))
+    pos = np.zeros((4096, 2), np.float32)
+    goal = np.zeros((4096, 2), np.float32)
+    walls = np.zeros((64, 4), np.float32)
+    md, nw = C.c_float(0), C.c_int32(0)
+    n = L.canon_scene_full(scene_id, C.byref(rng), _p(pos), _p(goal), C.byref(md), 4096, _p(walls), C.byref(nw), 64)
+    assert n > 0, f"scene {scene_id} unsupported by the oracle"
+    return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value), walls[:nw.value].copy()
+
+
 class CanonSim:
     def __init__(self, pos, goal, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15,
-                 comm=True, grid=False):
+                 comm=True, grid=False, walls=None, order=None, wall_order=None, planner=None, bvh=None):
+        """walls [W][4] + planner (an object with plan(start, goal) -> (waypoints [k][2], min_time), e.g. the host planner
+        learn_comms_b200.Planner that tests/test_planner.py pins against the reference's own): walled rollouts.
+        order / wall_order: table iteration orders (quirk Q4); bvh: flattened static BVH (BVH_NODE records)."""
         L = lib()
         self.n = int(pos.shape[0])
         pos = np.ascontiguousarray(pos, np.float32)
         goal = np.ascontiguousarray(goal, np.float32)
         m_cv = np.zeros((3, 8), np.float32) if m_cv is None else np.ascontiguousarray(m_cv, np.float32)
         m_f = np.zeros((2, 3), np.float32) if m_f is None else np.ascontiguousarray(m_f, np.float32)
+        walls = np.zeros((0, 4), np.float32) if walls is None else np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+        order = None if order is None else np.ascontiguousarray(order, np.int32)
+        wall_order = None if wall_order is None else np.ascontiguousarray(wall_order, np.int32)
+        bvh = None if bvh is None else np.ascontiguousarray(bvh, BVH_NODE)
+        self.planner, self.plan_calls = planner, 0
+
+        def _plan(user, agent, start, goal_, cap, out):
+            wp, _ = self.planner.plan([start[0], start[1]], [goal_[0], goal_[1]])
+            self.plan_calls += 1
+            if len(wp) > cap:
+                return -1
+            for k in range(len(wp)):
+                out[2 * k], out[2 * k + 1] = wp[k][0], wp[k][1]
+            return len(wp)
+
+        self._cb = PLAN_FN(_plan) if planner is not None else PLAN_FN()
         d = Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f),
-                 1 if comm else 0, 1 if grid else 0, 0, None)
+                 1 if comm else 0, 1 if grid else 0, len(walls), _p(walls) if len(walls) else None, _p(order), _p(wall_order),
+                 self._cb, None, 0 if bvh is None else len(bvh), _p(bvh))
         self.h = L.canon_create(C.byref(d))
+        assert self.h, "canon_create refused the description (walled scene without a planner?)"
+
+    def plan(self, agent):
+        wp = np.zeros((MAX_PLAN, 2), np.float32)
+        k = lib().canon_get_plan(self.h, agent, _p(wp), MAX_PLAN)
+        return wp[:k].copy()
+
+    def walled(self):
+        n_plan, lost = np.zeros(self.n, np.int32), np.zeros(self.n, np.int32)
+        rp, wh = C.c_int64(0), C.c_int64(0)
+        lib().canon_get_walled(self.h, _p(n_plan), _p(lost), C.byref(rp), C.byref(wh))
+        return dict(n_plan=n_plan, lost_frames=lost, replans=int(rp.value), wall_hits=int(wh.value))
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -68,6 +68,23 @@ def run_look(walls, radius, recs):
     return np.frombuffer(out, LOOK_OUT).copy()
 
 
+OREF_BVH = os.path.join(ROOT, "oracle", "_ref", "oref_bvh")
+BVH_NODE = np.dtype([("ox", np.float32), ("oy", np.float32), ("w", np.float32), ("h", np.float32), ("left", np.int32), ("right", np.int32)])
+
+
+def bvh_available():
+    return os.path.exists(OREF_BVH)
+
+
+def run_bvh(walls_in_statics_order):
+    """oracle/ref/bvh_main.cpp: the reference's BVH over the walls (given in statics order) -> pre-order BVH_NODE records;
+    leaf.left = position of the wall in the input list."""
+    w = np.ascontiguousarray(np.asarray(walls_in_statics_order, np.float32).reshape(-1, 4))
+    out = subprocess.run([OREF_BVH], input=np.int32(len(w)).tobytes() + w.tobytes(), stdout=subprocess.PIPE, check=True).stdout
+    m = int(np.frombuffer(out, np.int32, 1)[0])
+    return np.frombuffer(out, BVH_NODE, m, 4).copy()
+
+
 def run_geom(records):
     """oracle/ref/geom_main.cpp: (K, 9) float32 records -> (K, 12) uint32 words of the reference's wall geometry."""
     rec = np.ascontiguousarray(records, np.float32)
@@ -143,6 +160,8 @@ def read_dump(path):
     out["pos0"] = take(np.float32, 2 * n).reshape(n, 2)
     out["goal"] = take(np.float32, 2 * n).reshape(n, 2)
     out["min_time"] = take(np.float32, n)
+    out["wall_order"] = take(np.int32, n_walls)
+    out["walls"] = take(np.float32, 4 * n_walls).reshape(n_walls, 4)
     frames = []
     while True:
         f = int(take(np.int32, 1)[0])

@@ -70,6 +70,87 @@ def test_canon_matches_reference_golden(path):
         assert ("%g" % got[0], "%g" % got[1]) == tuple(str(x) for x in g["result_file"])
 
 
+WALLED = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "walled_rollout_*.npz")))
+
+
+def test_walled_fixtures_present():
+    assert len(WALLED) >= 9
+
+
+@pytest.mark.parametrize("path", WALLED, ids=[os.path.basename(p)[15:-4] for p in WALLED])
+def test_canon_walled_rollout_matches_reference_golden(path):
+    """Walled scenes: O-canon's frame loop with per-agent waypoint lists, the
+    sight-line / lost_frames replan gate (ai.cpp:152-168), multi-waypoint lookahead (LMP.cpp:84-113), wall TTC forces in
+    statics order (LMP.cpp:306-319) and the static-BVH push-out (physics.cpp:60-69, BVH.cpp:106-138) — in the
+    reference's table order with its Gauss-Seidel collision pass — equals the reference's own rollout bit for bit:
+    every kept frame, the Welford statistics, frame count and comms.result.  Replans go through the host planner
+    (learn_comms_b200.Planner, pinned in test_planner.py), the static BVH through lc_static_bvh (pinned below)."""
+    import learn_comms_b200 as lcb
+    g = np.load(path)
+    m_cv = g["m_cv"] if "m_cv" in g else None
+    m_f = g["m_f"] if "m_f" in g else None
+    pos, goal, md, rng, walls = _oracle.scene_full(int(g["scene"]), int(g["seed"]))
+    assert np.array_equal(pos, g["pos0"]) and np.array_equal(goal, g["goal"]) and np.array_equal(walls, g["walls"]), "scene catalogue differs from demo.cpp"
+    order, wall_order = lcb.table_order(len(pos), len(walls))
+    assert np.array_equal(order, g["order"]) and np.array_equal(wall_order, g["wall_order"])
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, walls=walls, order=order, wall_order=wall_order,
+                         planner=lcb.Planner(walls, 0.15), bvh=lcb.static_bvh(walls, wall_order))
+    o.set_order(None, gauss_seidel=True)
+    assert np.array_equal(np.array([s for s in o.state()["pos"]]), pos)
+    at = 0
+    for k, f in enumerate(g["frames"]):
+        o.step(int(f) - at)
+        at = int(f)
+        st = o.state()
+        for key in KEYS:
+            assert np.array_equal(st[key], g[key][k], equal_nan=True), f"{os.path.basename(path)} frame {f}: {key}"
+        sc = o.scores()
+        ra, rs, av, nd = g["progress"][k]
+        assert (np.float32(sc["run_avg"]), np.float32(sc["run_std"]), sc["n_done"]) == (np.float32(ra), np.float32(rs), int(nd))
+    if int(g["complete"]):
+        assert o.finished and o.frame == int(g["frames_executed"])
+        sc = o.scores()
+        got = np.array([sc[k] for k in ("avg_velocity", "group_time", "run_avg", "run_std")], np.float32)
+        assert np.array_equal(got, g["scores"], equal_nan=True) and sc["n_done"] == int(g["n_done"])
+        assert ("%g" % got[0], "%g" % got[1]) == tuple(str(x) for x in g["result_file"])
+
+
+def test_walled_min_time_matches_reference():
+    """ai.cpp:118-126: min_time = length of the initial plan minus the untimed last metre, planned in table order."""
+    import learn_comms_b200 as lcb
+    for path in WALLED:
+        g = np.load(path)
+        walls = g["walls"]
+        P = lcb.Planner(walls, 0.15)
+        mt = np.zeros(len(g["pos0"]), np.float32)
+        for i in g["order"]:
+            _, mt[i] = P.plan(g["pos0"][i], g["goal"][i])
+        assert np.array_equal(mt, g["min_time"]), os.path.basename(path)
+
+
+@pytest.mark.skipif(not _oref.bvh_available(), reason="oracle/_ref/oref_bvh not built (needs /root/reference)")
+def test_static_bvh_matches_reference_bvh():
+    """lc_static_bvh (host.cpp) against the reference's own BVH class (oracle/ref/bvh_main.cpp) node for node: catalogue
+    scenes and random layouts whose rounded coordinates produce the sort ties rows of tiles have."""
+    import learn_comms_b200 as lcb
+    rs = np.random.RandomState(0)
+    cases = []
+    for sc in (2, 3, 6, 7, 9, 11, 13, 18):
+        pos, goal, md, rng, walls = _oracle.scene_full(sc, 0)
+        cases.append((walls, lcb.table_order(len(pos), len(walls))[1]))
+    for t in range(60):
+        k = rs.randint(1, 60)
+        q = 2.0 if t % 2 else 1.0
+        walls = np.concatenate([np.round(rs.uniform(-10, 10, (k, 2)) * q) / q, rs.choice([0.3, 2.0, 4.0], (k, 1)).repeat(2, 1)], 1).astype(np.float32)
+        cases.append((walls, rs.permutation(k).astype(np.int32)))
+    for walls, wo in cases:
+        mine = lcb.static_bvh(walls, wo)
+        ref = _oref.run_bvh(walls[wo])
+        leaf = ref["right"] < 0
+        ref["left"][leaf] = wo[ref["left"][leaf]]   # the harness numbers leaves by position in the statics list
+        assert len(mine) == 2 * len(walls) - 1 and mine.tobytes() == ref.tobytes()
+
+
 def test_mintime_matches_reference():
     g = np.load([p for p in GOLD if p.endswith("scene4_w2.npz")][0])
     d = g["goal"] - g["pos0"]

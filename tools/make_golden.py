@@ -23,13 +23,27 @@ CASES = [
     ("scene0_w1", 0, 0, 1, True, 1100, 50),
     ("scene1_w5", 1, 0, 5, True, 575, 50),
     ("scene12_w3", 12, 0, 3, True, 1, 1),          # random layout: frame 1 only (initial overlaps hit the BVH path)
+    # walled scenes (fixtures also hold the wall rectangles and the statics order); "to the end" where the reference's
+    # dynamic BVH never resolves a contact differently from the exact leaf predicate (quirk Q8), else up to that frame
+    ("walled_rollout_6_zero", 6, 0, None, True, None, 97),    # curbed intersection, 11 replans
+    ("walled_rollout_18_zero", 18, 0, None, True, None, 97),  # two-door, 27 replans
+    ("walled_rollout_10_w30", 10, 0, 30, True, None, 97),     # clogged doorway 5 vs 35, 40 replans
+    ("walled_rollout_13_w33", 13, 0, 33, True, None, 97),     # hall
+    ("walled_rollout_8_w28", 8, 0, 28, True, None, 50),       # doorway 2 vs 2
+    ("walled_rollout_3_w23", 3, 0, 23, True, 600, 50),        # pillar: 283 wall contacts before the first Q8 event
+    ("walled_rollout_9_w29", 9, 0, 29, True, 1000, 50),       # clogged doorway 20 vs 20
+    ("walled_rollout_2_zero", 2, 0, None, True, 2000, 100),   # 60 random posts (walls drawn from the seeded stream)
+    ("walled_rollout_11_w31", 11, 0, 31, True, 1600, 100),    # escaping room
 ]
 
 
 def main():
     out_dir = os.path.join(ROOT, "tests", "golden")
     os.makedirs(out_dir, exist_ok=True)
+    only = sys.argv[1:]
     for name, scene, seed, wseed, comm, upto, stride in CASES:
+        if only and not any(name.startswith(o) for o in only):
+            continue
         m_cv, m_f = (None, None) if wseed is None else wl.weights(wseed)
         r = _oref.run(scene, seed, m_cv, m_f, comm=comm)
         frames = [fr for fr in r["frames"] if (upto is None or fr["frame"] <= upto)]
@@ -40,6 +54,8 @@ def main():
                  scores=np.array([r["scores"][k] for k in ("avg_velocity", "group_time", "run_avg", "run_std")], np.float32),
                  n_done=r["scores"]["n_done"], result_file=np.array(r["result_file"]),
                  progress=np.array([[fr["run_avg"], fr["run_std"], fr["avg_velocity"], fr["total_num_done"]] for fr in keep]))
+        if r["n_walls"]:
+            d["walls"], d["wall_order"] = r["walls"], r["wall_order"]
         if m_cv is not None:
             d["m_cv"], d["m_f"] = m_cv, m_f
         for k in KEYS:
