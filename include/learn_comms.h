@@ -45,14 +45,18 @@ typedef struct lc_desc {
     const float* m_f;       /* [2][3] row-major force matrix M_f (comm.cpp:112-121); NULL = zeros */
     uint32_t flags;
     int32_t device;         /* CUDA device ordinal */
-    int32_t n_walls;        /* reserved for walled scenes; must be 0 */
-    const lc_rect* walls;
+    int32_t n_walls;        /* static walls (demo.cpp:515-537 create_wall); 0 = wall-free scene.  Walled scenes: the global
+                             * planner (Cspace2d + PRM + A*, ai.cpp:41-127) runs on the host at creation and for every
+                             * replan (ai.cpp:162-168), so lc_step is synchronous for them; single GPU only */
+    const lc_rect* walls;   /* [n_walls] in creation order */
     int32_t stencil;        /* grid cells per interaction cutoff (0 = default 2): cell side = cutoff / stencil */
     const int32_t* table_order; /* [n] permutation: table_order[k] = index of the k-th agent the reference's component-table
                                  * loops visit (quirk Q4: std::unordered_map order, Pool.h:24, Pool.cpp:156-160).  Decides
                                  * which minstd_rand0 draw an agent gets, the order forces / hits / Welford updates are
                                  * summed in, arg-max ties and the two replan slots.  NULL = ascending index.  lc_table_order
                                  * returns the reference's own order; the comm_norender drop-in uses it. */
+    const int32_t* wall_order;  /* [n_walls] order in which the statics loop (LMP.cpp:307-319) visits the walls and in which
+                                 * ai::init hands them to the static BVH (ai.cpp:28-36); NULL = creation order */
 } lc_desc;
 
 typedef struct lc_sim lc_sim;
@@ -82,6 +86,14 @@ int32_t lc_get_rng(lc_sim* sim, uint32_t* rng_state);
 /* comm::terminate's two numbers (comm.cpp:136-142) + demo's running statistics (demo.cpp:650-663) */
 int32_t lc_get_scores(lc_sim* sim, float* avg_velocity, float* group_time, float* run_avg, float* run_std,
                       int32_t* total_num_done);
+
+/* demo::update_runs' per-finisher log (demo.cpp:662 prints "t:%f u:%f s:%f" for each): [count][3] = overhead, running mean,
+ * running sigma, in the order the reference's Welford update saw the finishers */
+int32_t lc_get_finish_log(lc_sim* sim, float* log /*[cap][3]*/, int32_t cap, int32_t* count);
+/* walled scenes: Agent::plan->size() and Agent::lost_frames per agent (Agent.h:14,28), replans served so far (ai.cpp:164-168),
+ * wall push-outs so far (physics.cpp:67-69); any pointer may be NULL */
+int32_t lc_get_walled(lc_sim* sim, int32_t* n_plan, int32_t* lost_frames, int64_t* replans, int64_t* wall_hits);
+int32_t lc_get_plan(lc_sim* sim, int32_t agent, float* waypoints /*[cap][2]*/, int32_t cap, int32_t* n_waypoints);
 
 /* diagnostics of the last executed frame (parity tests) */
 int32_t lc_get_partners(lc_sim* sim, int32_t* partner);         /* [n] select_nearest result, comm.cpp:201-220 */
@@ -191,9 +203,13 @@ int32_t lc_table_order(int32_t n_agents, int32_t n_walls, int32_t* agent_order, 
 typedef struct lc_bvh_node { float ox, oy, w, h; int32_t left, right; } lc_bvh_node;
 int32_t lc_static_bvh(int32_t n_walls, const lc_rect* walls, const int32_t* wall_order, lc_bvh_node* nodes, int32_t cap, int32_t* n_nodes);
 
-/* ---- scene catalogue (demo.cpp:141-511), wall-free scenes; returns agent count or negative status ---- */
+/* ---- scene catalogue (demo.cpp:141-511 make_scene + :611-635 the create_robo / create_wall loops): scenes 0-18 and the
+ * variable-size doorway 900 + k; returns the agent count or a negative status.  lc_scene serves the wall-free scenes (and
+ * refuses the others: the walls are part of the scene), lc_scene_full all of them. ---- */
 int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
                  uint32_t* rng_state_after);
+int32_t lc_scene_full(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
+                      uint32_t* rng_state_after, lc_rect* walls, int32_t wall_cap, int32_t* n_walls);
 
 /* ---- static-wall geometry (walled scenes; not yet part of lc_step) ----
  * Evaluates the device restatement of the reference's wall functions on n_records HOST records of 9 floats

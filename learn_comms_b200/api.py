@@ -20,7 +20,7 @@ class _Desc(C.Structure):
     _fields_ = [("n", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p), ("radius", C.c_float),
                 ("max_duration", C.c_float), ("rng_state", C.c_uint32), ("m_cv", C.c_void_p), ("m_f", C.c_void_p),
                 ("flags", C.c_uint32), ("device", C.c_int32), ("n_walls", C.c_int32), ("walls", C.c_void_p),
-                ("stencil", C.c_int32), ("table_order", C.c_void_p)]
+                ("stencil", C.c_int32), ("table_order", C.c_void_p), ("wall_order", C.c_void_p)]
 
 
 class _DomainDesc(C.Structure):
@@ -41,7 +41,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_table_order", "lc_static_bvh", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -100,6 +100,10 @@ def lib():
         L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
+        L.lc_scene_full.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32), vp, i32, C.POINTER(i32)]
+        L.lc_get_finish_log.argtypes = [vp, vp, i32, C.POINTER(i32)]
+        L.lc_get_walled.argtypes = [vp, vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.lc_get_plan.argtypes = [vp, i32, vp, i32, C.POINTER(i32)]
         L.lc_table_order.argtypes = [i32, i32, vp, vp]
         L.lc_static_bvh.argtypes = [i32, vp, vp, vp, i32, C.POINTER(i32)]
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
@@ -133,6 +137,18 @@ def scene(scene_id, seed=0):
     if n <= 0:
         raise LcError(n, f"scene {scene_id} is not in the wall-free catalogue")
     return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value)
+
+
+def scene_full(scene_id, seed=0):
+    """The whole catalogue incl. walled scenes (lc_scene_full) -> pos, goal, max_duration, rng_state, walls [W][4]."""
+    pos = np.zeros((4096, 2), np.float32)
+    goal = np.zeros((4096, 2), np.float32)
+    walls = np.zeros((64, 4), np.float32)
+    md, rng, nw = C.c_float(0), C.c_uint32(0), C.c_int32(0)
+    n = lib().lc_scene_full(scene_id, seed, _p(pos), _p(goal), 4096, C.byref(md), C.byref(rng), _p(walls), 64, C.byref(nw))
+    if n <= 0:
+        raise LcError(n, f"scene {scene_id} is not in the catalogue")
+    return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value), walls[:nw.value].copy()
 
 
 def table_order(n_agents, n_walls=0):
@@ -246,18 +262,24 @@ class Sim:
     """One crowd resident on one GPU.  step(k) runs k frames of main.cpp:98-150."""
 
     def __init__(self, pos, goal, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15, comm=True,
-                 free_run=False, debug_lists=False, device=0, stencil=0, order=None):
+                 free_run=False, debug_lists=False, device=0, stencil=0, order=None, walls=None, wall_order=None):
         """order: table iteration order (lc_desc::table_order) — None = ascending index, "reference" = the reference's
-        own (lc_table_order), or an explicit permutation."""
+        own (lc_table_order), or an explicit permutation.  walls [W][4] (origin x, z, width, height): a walled scene;
+        wall_order = statics order (None = creation order; with order="reference" the reference's own)."""
         self.n = int(pos.shape[0])
+        self._walls = None if walls is None or len(walls) == 0 else np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+        nw = 0 if self._walls is None else len(self._walls)
+        if isinstance(order, str) and nw and wall_order is None:
+            wall_order = table_order(self.n, nw)[1]
+        self._wall_order = None if (wall_order is None or nw == 0) else np.ascontiguousarray(wall_order, np.int32)
         self._order = _order(order, self.n)
         pos = np.ascontiguousarray(pos, np.float32)
         goal = np.ascontiguousarray(goal, np.float32)
         m_cv = None if m_cv is None else np.ascontiguousarray(m_cv, np.float32)
         m_f = None if m_f is None else np.ascontiguousarray(m_f, np.float32)
         flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0) | (FLAG_DEBUG_LISTS if debug_lists else 0)
-        d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0,
-                  None, stencil, _p(self._order))
+        d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, nw,
+                  _p(self._walls), stencil, _p(self._order), _p(self._wall_order))
         h = C.c_void_p()
         self.h = None
         _ck(lib().lc_create(C.byref(d), C.byref(h)))
@@ -380,6 +402,25 @@ class Sim:
         _ck(lib().lc_step_profiled(self.h, n, _p(ms)))
         return dict(zip(self.KERNELS, ms.tolist()))
 
+    def finish_log(self):
+        """[k][3] (overhead, running mean, running sigma) of every counted finisher, in Welford order (demo.cpp:655-663)."""
+        log = np.zeros((self.n, 3), np.float32)
+        k = C.c_int32(0)
+        _ck(lib().lc_get_finish_log(self.h, _p(log), self.n, C.byref(k)))
+        return log[:k.value].copy()
+
+    def walled(self):
+        n_plan, lost = np.zeros(self.n, np.int32), np.zeros(self.n, np.int32)
+        rp, wh = C.c_int64(0), C.c_int64(0)
+        _ck(lib().lc_get_walled(self.h, _p(n_plan), _p(lost), C.byref(rp), C.byref(wh)))
+        return dict(n_plan=n_plan, lost_frames=lost, replans=int(rp.value), wall_hits=int(wh.value))
+
+    def plan(self, agent):
+        wp = np.zeros((64, 2), np.float32)
+        k = C.c_int32(0)
+        _ck(lib().lc_get_plan(self.h, agent, _p(wp), 64, C.byref(k)))
+        return wp[:k.value].copy()
+
     def pair_tests(self):
         """pair-filter evaluations of the last executed frame (lc_count_pair_tests)."""
         k = C.c_int64(0)
@@ -418,7 +459,7 @@ class DomainSim(Sim):
         vfh = None if vfh is None else np.ascontiguousarray(vfh, np.float32)
         flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0)
         d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, 0, None, stencil,
-                  _p(self._order))
+                  _p(self._order), None)
         dom = _DomainDesc(rank, world, _p(xb), capacity, halo_capacity, _p(vel), _p(vfh))
         h = C.c_void_p()
         self.h = None

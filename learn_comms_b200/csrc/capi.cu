@@ -85,6 +85,13 @@ struct lc_sim {
     float* stage = nullptr;
     size_t stage_floats = 0;
     lc::Ctl* hctl = nullptr;
+    // walled scenes: host planner (stateful roadmap, planner.cpp), host mirrors indexed by engine id
+    lc_planner* planner = nullptr;
+    std::vector<float> h_goal;   // [n_ids][2]
+    std::vector<int> h_nplan;    // [n_ids]
+    long long replans = 0;
+    std::vector<int> h_order;    // lc_desc::table_order (empty = ascending)
+    int hp_ext(size_t id) const { return h_order.empty() ? (int)id : h_order[id]; }
     int* ext_of = nullptr;     // device copy of lc_desc::table_order (nullptr = ascending)
     int* xlate = nullptr;      // staging for diagnostics translated to the caller's agent indices
     std::vector<void*> allocs;
@@ -112,7 +119,7 @@ static int build_graphs(lc_sim* s) {
         int frames = 1 << g;
         cudaGraph_t graph;
         CK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
-        for (int f = 0; f < frames; ++f) lc::launch_frame(s->dP, s->n, s->b, s->st, nullptr, nullptr, &s->side);
+        for (int f = 0; f < frames; ++f) lc::launch_frame(s->dP, s->n, s->b, s->st, nullptr, nullptr, &s->side, s->hp.n_walls > 0);
         CK(cudaStreamEndCapture(s->st, &graph));
         CK(cudaGraphInstantiate(&s->gexec[g], graph, 0));
         CK(cudaGraphDestroy(graph));
@@ -150,6 +157,7 @@ void lc_destroy(lc_sim* s) {
     if (s->side.st) cudaStreamDestroy(s->side.st);
     if (s->side.fork) cudaEventDestroy(s->side.fork);
     if (s->side.join) cudaEventDestroy(s->side.join);
+    if (s->planner) lc_planner_destroy(s->planner);
     for (void* p : s->ipc_opened) cudaIpcCloseMemHandle(p);
     for (void* p : s->allocs) cudaFree(p);
     if (s->mailbox) cudaFree(s->mailbox);
@@ -164,13 +172,80 @@ void lc_destroy(lc_sim* s) {
 
 }  // extern "C"
 
+// Walled scene set-up (ai::init, ai.cpp:24-129): static BVH, configuration space + roadmap (host planner), one plan per
+// agent in table order — engine ids ARE table positions — and min_time = plan length minus the untimed last metre.
+template <class Ext>
+static int setup_walls(lc_sim* s, const lc_desc* d, Ext ext, std::vector<float>& min_time) {
+    const int n = d->n, nw = d->n_walls;
+    std::vector<int32_t> worder((size_t)nw);
+    std::vector<char> seen((size_t)nw, 0);
+    for (int k = 0; k < nw; ++k) {
+        worder[k] = d->wall_order ? d->wall_order[k] : k;
+        if (worder[k] < 0 || worder[k] >= nw || seen[worder[k]]) return fail(LC_ERR_ARG, "lc_create: wall_order is not a permutation of 0..n_walls-1");
+        seen[worder[k]] = 1;
+    }
+    std::vector<lc_bvh_node> bvh((size_t)2 * nw);
+    int32_t n_bvh = 0;
+    int rc = lc_static_bvh(nw, d->walls, worder.data(), bvh.data(), (int32_t)bvh.size(), &n_bvh);
+    if (rc) return fail(rc, "lc_create: static BVH construction failed");
+    rc = lc_planner_create(nw, d->walls, d->radius, &s->planner);
+    if (rc) return rc;
+    std::vector<float> plan((size_t)n * lc::WP_CAP * 2, 0.f);
+    std::vector<int> noplan((size_t)n, 0);
+    s->h_nplan.assign((size_t)n, 0);
+    s->h_goal.resize((size_t)2 * n);
+    min_time.assign((size_t)n, 0.f);
+    int missing = 0;
+    for (int id = 0; id < n; ++id) {
+        const int e = ext(id);
+        const float start[2] = {d->pos[2 * e], d->pos[2 * e + 1]}, goal[2] = {d->goal[2 * e], d->goal[2 * e + 1]};
+        s->h_goal[2 * id] = goal[0]; s->h_goal[2 * id + 1] = goal[1];
+        int32_t k = 0;
+        rc = lc_planner_plan(s->planner, start, goal, lc::WP_CAP, &plan[(size_t)id * lc::WP_CAP * 2], &k, &min_time[id]);
+        if (rc) return fail(rc, "lc_create: the plan of agent %d has %d waypoints (capacity %d)", e, k, lc::WP_CAP);
+        s->h_nplan[id] = k;
+        noplan[id] = missing;
+        if (k == 0) ++missing;
+    }
+    lc::WalledArrays& W = s->b.w;
+    lc::WallRect* dw = nullptr; int* dwo = nullptr; lc::BvhNode* dbvh = nullptr;
+    static_assert(sizeof(lc::WallRect) == sizeof(lc_rect) && sizeof(lc::BvhNode) == sizeof(lc_bvh_node), "layouts shared with the C ABI");
+#define WCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(LC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); } while (0)
+#define WAL(ptr, count) do { WCK(dalloc(&ptr, count)); s->allocs.push_back(ptr); } while (0)
+    WAL(dw, nw); WAL(dwo, nw); WAL(dbvh, n_bvh);
+    WAL(W.plan, (size_t)n * lc::WP_CAP); WAL(W.n_plan, n); WAL(W.num_done, n); WAL(W.lost, n); WAL(W.lost_next, n);
+    WAL(W.noplan_before, n); WAL(W.req_pos, n);
+    WCK(cudaMemcpy(dw, d->walls, sizeof(lc_rect) * (size_t)nw, cudaMemcpyHostToDevice));
+    WCK(cudaMemcpy(dwo, worder.data(), sizeof(int) * (size_t)nw, cudaMemcpyHostToDevice));
+    WCK(cudaMemcpy(dbvh, bvh.data(), sizeof(lc_bvh_node) * (size_t)n_bvh, cudaMemcpyHostToDevice));
+    WCK(cudaMemcpy(W.plan, plan.data(), sizeof(float) * plan.size(), cudaMemcpyHostToDevice));
+    WCK(cudaMemcpy(W.n_plan, s->h_nplan.data(), sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
+    WCK(cudaMemcpy(W.noplan_before, noplan.data(), sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
+    WCK(cudaMemset(W.num_done, 0, sizeof(int) * (size_t)n));
+    WCK(cudaMemset(W.lost, 0, sizeof(int) * (size_t)n));
+    WCK(cudaMemset(W.lost_next, 0, sizeof(int) * (size_t)n));
+    WCK(cudaMemset(W.req_pos, 0, sizeof(float2) * (size_t)n));
+    W.walls = dw; W.wall_order = dwo; W.bvh = dbvh;
+    s->hp.n_bvh = n_bvh;
+    // control block: draws per frame, no request pending
+    lc::Ctl c0;
+    memset(&c0, 0, sizeof c0);
+    c0.wr1 = c0.wr2 = 0x7fffffff;
+    c0.n_planned = n - missing;
+    WCK(cudaMemcpy(s->b.ctl, &c0, sizeof c0, cudaMemcpyHostToDevice));
+#undef WAL
+#undef WCK
+    return 0;
+}
+
 // lc_create (dom == nullptr) and lc_dd_create share everything but the choice of the initially local agents
 static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out) {
     if (!d || !out) return fail(LC_ERR_ARG, "lc_create: null argument");
     *out = nullptr;
     if (d->n < 2) return fail(LC_ERR_ARG, "lc_create: n must be >= 2 (the reference dereferences a null comm partner for n == 1, comm.cpp:273-285)");
     if (!d->pos || !d->goal) return fail(LC_ERR_ARG, "lc_create: pos/goal are required");
-    if (d->n_walls != 0) return fail(LC_ERR_ARG, "lc_create: walled scenes are not supported yet");
+    if (d->n_walls < 0 || (d->n_walls > 0 && !d->walls)) return fail(LC_ERR_ARG, "lc_create: n_walls > 0 needs the wall rectangles");
+    if (d->n_walls > 0 && dom) return fail(LC_ERR_ARG, "lc_dd_create: walled scenes run on one GPU (replans go through the host planner between frames)");
     if (!(d->radius > 0.f)) return fail(LC_ERR_ARG, "lc_create: radius must be positive");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -287,6 +362,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         CKC(dalloc(&b.nbr_list, (size_t)n_ids * b.list_cap)); s->allocs.push_back(b.nbr_list);
         CKC(cudaMemset(b.nbr_list, 0xff, sizeof(int) * (size_t)n_ids * b.list_cap));
     }
+    CKC(dalloc(&b.fin_log, (size_t)3 * n_ids)); s->allocs.push_back(b.fin_log);
     CKC(dalloc(&b.ctl, 1)); s->allocs.push_back(b.ctl);
     CKC(cudaMemset(b.ctl, 0, sizeof(lc::Ctl)));
     CKC(cudaMemset(b.partner_id, 0xff, sizeof(int) * n_ids));
@@ -297,6 +373,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     s->stage_floats = std::max((size_t)n_ids * 16, (size_t)8 + 5 * (size_t)n);  // lc_get_state tables / lc_dd_get_shard
     CKC(cudaMalloc((void**)&s->stage, sizeof(float) * s->stage_floats));
     b.ext_of = nullptr;
+    if (order) s->h_order.assign(order, order + n_ids);
     if (order) {
         CKC(dalloc(&s->ext_of, n_ids)); s->allocs.push_back(s->ext_of);
         CKC(cudaMemcpy(s->ext_of, order, sizeof(int) * (size_t)n_ids, cudaMemcpyHostToDevice));
@@ -343,10 +420,16 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     P.lcg_stride = lcg_pow(16807u, (uint64_t)n_ids);
     P.flags = d->flags;
     P.stencil_req = d->stencil > 0 ? d->stencil : 2;
+    P.n_walls = d->n_walls;
+    P.n_bvh = 0;
+    P.rng0 = d->rng_state;
     memset(P.m_cv, 0, sizeof P.m_cv);
     memset(P.m_f, 0, sizeof P.m_f);
     if (d->m_cv) memcpy(P.m_cv, d->m_cv, sizeof P.m_cv);
     if (d->m_f) memcpy(P.m_f, d->m_f, sizeof P.m_f);
+    std::vector<float> w_min_time;  // walled scenes: min_time by engine id (ai.cpp:118-126)
+    memset(&b.w, 0, sizeof b.w);
+    if (d->n_walls > 0) CKB(setup_walls(s, d, ext, w_min_time));
     CKB(upload_params(s));
     lc::upload_dirs();
 
@@ -374,7 +457,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
             gd[k] = len;
             float mn = -1.0f;                                 // ai.cpp:121-126
             mn += len;
-            mt[k] = mn;
+            mt[k] = w_min_time.empty() ? mn : w_min_time[id];  // walled: length of the planned path instead of the bee line
             hid[k] = id;
             if (has_v) {
                 hvel[2 * k] = dom->vel[2 * i]; hvel[2 * k + 1] = dom->vel[2 * i + 1];
@@ -398,6 +481,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     s->rng0 = d->rng_state;
     lc::launch_set_rng(s->dP, n, b, s->rng0, s->st, &s->launches);
     lc::launch_init_reduce(s->dP, n, b, s->st, &s->launches);
+    if (d->n_walls > 0) lc::launch_walled_gate(s->dP, n, b, s->st, &s->launches);  // replan requests of frame 1
     CKC(cudaStreamSynchronize(s->st));
     CKC(cudaGetLastError());
     CKB(build_graphs(s));
@@ -465,10 +549,7 @@ static void ensure_packed(lc_sim* s) {
     }
 }
 
-int32_t lc_step(lc_sim* s, int32_t nframes) {
-    SIM_ENTER(s);
-    if (nframes < 0) return fail(LC_ERR_ARG, "lc_step: nframes < 0");
-    if (nframes > 0) ensure_packed(s);
+static int enqueue_frames(lc_sim* s, int nframes) {
     int left = nframes;
     for (int g = GRAPH_LEVELS - 1; g >= 0; --g) {
         const int frames = 1 << g;
@@ -477,6 +558,75 @@ int32_t lc_step(lc_sim* s, int32_t nframes) {
             left -= frames;
             s->launches += (long long)(lc::FRAME_KERNELS + (s->ddev ? lc::DD_KERNELS : 0)) * frames;
         }
+    }
+    return LC_OK;
+}
+
+// Walled scenes: GMP::plan_one for the (at most two) agents the paused frame's gate selected (ai.cpp:151-168), in table
+// order, from the position the agent asked from; new waypoint list, num_done = 0, lost_frames = 0 (GMP.cpp:109, ai.cpp:167).
+static int serve_replans(lc_sim* s) {
+    const lc::WalledArrays& W = s->b.w;
+    const int ids[2] = {s->hctl->wr1, s->hctl->wr2};
+    bool plan_set_changed = false;
+    int served = 0;
+    for (int q = 0; q < 2; ++q) {
+        const int id = ids[q];
+        if (id == 0x7fffffff) continue;
+        if (id < 0 || id >= s->n_ids) return fail(LC_ERR_STATE, "lc_step: replan request for agent %d out of range", id);
+        float start[2];
+        CK(cudaMemcpy(start, W.req_pos + id, sizeof start, cudaMemcpyDeviceToHost));
+        float wp[2 * lc::WP_CAP];
+        int32_t k = 0;
+        int rc = lc_planner_plan(s->planner, start, &s->h_goal[2 * (size_t)id], lc::WP_CAP, wp, &k, nullptr);
+        if (rc) return fail(rc, "lc_step: a replan produced %d waypoints (capacity %d)", k, lc::WP_CAP);
+        const int zero = 0;
+        if (k > 0) CK(cudaMemcpy(W.plan + (size_t)id * lc::WP_CAP, wp, sizeof(float) * 2 * (size_t)k, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(W.n_plan + id, &k, sizeof(int), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(W.num_done + id, &zero, sizeof(int), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(W.lost_next + id, &zero, sizeof(int), cudaMemcpyHostToDevice));
+        if ((s->h_nplan[id] == 0) != (k == 0)) plan_set_changed = true;
+        s->h_nplan[id] = k;
+        ++served;
+    }
+    int n_planned = s->hctl->n_planned;
+    if (plan_set_changed) {  // who draws from the global stream changed (LMP.cpp:259-270)
+        std::vector<int> noplan((size_t)s->n_ids);
+        int missing = 0;
+        for (int i = 0; i < s->n_ids; ++i) { noplan[i] = missing; missing += s->h_nplan[i] == 0; }
+        CK(cudaMemcpy(W.noplan_before, noplan.data(), sizeof(int) * noplan.size(), cudaMemcpyHostToDevice));
+        n_planned = s->n_ids - missing;
+    }
+    s->replans += served;
+    const int one = 1, zero = 0;
+    char* c = (char*)s->b.ctl;
+    CK(cudaMemcpy(c + offsetof(lc::Ctl, n_planned), &n_planned, sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c + offsetof(lc::Ctl, w_served), &one, sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c + offsetof(lc::Ctl, halt), &zero, sizeof(int), cudaMemcpyHostToDevice));
+    return LC_OK;
+}
+
+int32_t lc_step(lc_sim* s, int32_t nframes) {
+    SIM_ENTER(s);
+    if (nframes < 0) return fail(LC_ERR_ARG, "lc_step: nframes < 0");
+    if (nframes > 0) ensure_packed(s);
+    if (s->hp.n_walls == 0) return enqueue_frames(s, nframes);
+    // Walled scene: frames pause on the device whenever the replan gate fires; serve and resume until the requested
+    // number of frames has executed (or demo::run reported all_done: later frames are no-ops, as without walls).
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    const uint32_t target = s->hctl->frame + (uint32_t)nframes;
+    for (int guard = 0; s->hctl->frame < target; ++guard) {
+        if (s->hctl->halt == 2) {
+            rc = serve_replans(s);
+            if (rc) return rc;
+        } else if (s->hctl->halt == 1 || guard > 4 * nframes + 8) {
+            break;  // finished (frames after all_done do not execute), or no progress: never spin
+        }
+        rc = enqueue_frames(s, (int)(target - s->hctl->frame));
+        if (rc) return rc;
+        rc = read_ctl(s);
+        if (rc) return rc;
+        if (s->hctl->error) return device_error(s);
     }
     return LC_OK;
 }
@@ -561,6 +711,7 @@ int32_t lc_set_state(lc_sim* s, const float* pos, const float* vel, const float*
                          c ? dc : nullptr, facing ? dfac : nullptr, lgoal ? dlg : nullptr, goal_dist ? dgd : nullptr,
                          num_done ? dnd : nullptr, nullptr, nullptr, 0, s->st, &s->launches);
     lc::launch_init_reduce(s->dP, s->n, s->b, s->st, &s->launches);
+    if (s->hp.n_walls > 0) lc::launch_walled_gate(s->dP, s->n, s->b, s->st, &s->launches);  // requests of the coming frame
     return LC_OK;
 }
 
@@ -569,7 +720,10 @@ int32_t lc_get_rng(lc_sim* s, uint32_t* rng_state) {
     SIM_ENTER(s);
     int rc = read_ctl(s);
     if (rc) return rc;
-    *rng_state = lcm::lcg_mul(s->rng0, lcg_pow(16807u, (uint64_t)s->hctl->frame * (uint64_t)s->n_ids));
+    if (s->hp.n_walls > 0)  // plan-less agents do not draw (LMP.cpp:267-270): the device counts the draws
+        *rng_state = lcm::lcg_mul(s->hp.rng0, lcg_pow(16807u, (uint64_t)s->hctl->draws + (uint64_t)s->hctl->drawn_last));
+    else
+        *rng_state = lcm::lcg_mul(s->rng0, lcg_pow(16807u, (uint64_t)s->hctl->frame * (uint64_t)s->n_ids));
     return LC_OK;
 }
 
@@ -578,6 +732,13 @@ int32_t lc_set_rng(lc_sim* s, uint32_t rng_state) {
     if (s->ddev) return fail(LC_ERR_STATE, "lc_set_rng: not available on a domain-decomposed crowd (the next frame's records are already packed)");
     int rc = read_ctl(s);
     if (rc) return rc;
+    if (s->hp.n_walls > 0) {  // rebase the stream so that the next draw is the first after rng_state
+        const uint64_t used = (uint64_t)s->hctl->draws + (uint64_t)s->hctl->drawn_last;
+        s->hp.rng0 = lcm::lcg_mul(rng_state, lcg_pow(lcg_pow(16807u, used), 2147483647ull - 2ull));
+        CK(cudaStreamSynchronize(s->st));
+        CK(cudaMemcpy((char*)s->dP + offsetof(lc::Params, rng0), &s->hp.rng0, sizeof(uint32_t), cudaMemcpyHostToDevice));
+        return LC_OK;
+    }
     // rng0 is defined relative to frame 0; rebase so that lc_get_rng stays consistent
     uint64_t consumed = (uint64_t)s->hctl->frame * (uint64_t)s->n_ids;
     // inverse of 16807^consumed mod (2^31-1): a^(m-2) is the modular inverse (m prime)
@@ -657,6 +818,50 @@ int32_t lc_count_pair_tests(lc_sim* s, int64_t* pair_tests) {
     return LC_OK;
 }
 
+int32_t lc_get_finish_log(lc_sim* s, float* log, int32_t cap, int32_t* count) {
+    SIM_ENTER(s);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    const int k = s->hctl->total_num_done;
+    if (count) *count = k;
+    if (log && k > 0) {
+        if (k > cap) return fail(LC_ERR_CAPACITY, "lc_get_finish_log: %d finishers, the buffer holds %d", k, cap);
+        CK(cudaMemcpy(log, s->b.fin_log, sizeof(float) * 3 * (size_t)k, cudaMemcpyDeviceToHost));
+    }
+    return LC_OK;
+}
+
+int32_t lc_get_walled(lc_sim* s, int32_t* n_plan, int32_t* lost_frames, int64_t* replans, int64_t* wall_hits) {
+    SIM_ENTER(s);
+    if (s->hp.n_walls == 0) return fail(LC_ERR_ARG, "lc_get_walled: not a walled scene");
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    const size_t n = (size_t)s->n_ids;
+    std::vector<int> tmp(n);
+    for (int t = 0; t < 2; ++t) {
+        int32_t* dst = t == 0 ? n_plan : lost_frames;
+        if (!dst) continue;
+        CK(cudaMemcpy(tmp.data(), t == 0 ? s->b.w.n_plan : s->b.w.lost, sizeof(int) * n, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) dst[s->hp_ext(i)] = tmp[i];
+    }
+    if (replans) *replans = s->replans;
+    if (wall_hits) *wall_hits = (int64_t)s->hctl->wall_hits;
+    return LC_OK;
+}
+
+int32_t lc_get_plan(lc_sim* s, int32_t agent, float* waypoints, int32_t cap, int32_t* n_waypoints) {
+    SIM_ENTER(s);
+    if (s->hp.n_walls == 0 || agent < 0 || agent >= s->n_ids || !n_waypoints) return fail(LC_ERR_ARG, "lc_get_plan: bad argument");
+    int id = agent;
+    if (!s->h_order.empty()) { id = -1; for (int i = 0; i < s->n_ids; ++i) if (s->h_order[i] == agent) { id = i; break; } }
+    CK(cudaStreamSynchronize(s->st));
+    const int k = s->h_nplan[id];
+    *n_waypoints = k;
+    if (k > cap) return fail(LC_ERR_CAPACITY, "lc_get_plan: %d waypoints, the buffer holds %d", k, cap);
+    if (waypoints && k > 0) CK(cudaMemcpy(waypoints, s->b.w.plan + (size_t)id * lc::WP_CAP, sizeof(float) * 2 * (size_t)k, cudaMemcpyDeviceToHost));
+    return LC_OK;
+}
+
 int32_t lc_timer_start(lc_sim* s) {
     SIM_ENTER(s);
     CK(cudaEventRecord(s->ev0, s->st));
@@ -676,6 +881,7 @@ int64_t lc_kernel_launches(lc_sim* s) { return s ? s->launches : 0; }
 int32_t lc_step_profiled(lc_sim* s, int32_t nframes, float* ms_per_kernel) {
     SIM_ENTER(s);
     if (nframes < 0 || !ms_per_kernel) return fail(LC_ERR_ARG, "lc_step_profiled: bad argument");
+    if (s->hp.n_walls > 0) return fail(LC_ERR_ARG, "lc_step_profiled: wall-free crowds only (walled frames pause for host replans)");
     constexpr int K = lc::FRAME_KERNELS;
     if (nframes > 0) ensure_packed(s);
     cudaEvent_t ev[K + 1];

@@ -14,6 +14,7 @@
 // FP32 CUDA cores only: the path is a gather / pair-test loop, not a dense contraction.
 #include "crowd.cuh"
 #include "lc_math.cuh"
+#include "walls.cuh"
 #include <math_constants.h>
 
 namespace lc {
@@ -60,13 +61,17 @@ __device__ __forceinline__ void pdl_enter() {
 }
 
 // demo.cpp:655-663 update_runs (Welford, all float)
-__device__ __forceinline__ void update_runs(Ctl* ctl, float overhead) {
+__device__ __forceinline__ void update_runs(Ctl* ctl, float overhead, float* fin_log) {
     float ftotal = (float)(++ctl->total_num_done);
     float delta = __fsub_rn(overhead, ctl->run_avg);
     ctl->run_avg = __fadd_rn(ctl->run_avg, __fdiv_rn(delta, ftotal));
     float delta2 = __fsub_rn(overhead, ctl->run_avg);
     ctl->M2 = __fadd_rn(ctl->M2, __fmul_rn(delta, delta2));
     ctl->run_std = __fsqrt_rn(__fdiv_rn(ctl->M2, ftotal));
+    if (fin_log) {  // demo.cpp:662: the reference prints "t:%f u:%f s:%f" per finisher; kept for the drop-in's stdout
+        float* l = fin_log + 3 * (size_t)(ctl->total_num_done - 1);
+        l[0] = overhead; l[1] = ctl->run_avg; l[2] = ctl->run_std;
+    }
 }
 
 // physics.cpp:72-76 with vel_count == 0 forever (quirk Q6): avg = (avg*0 + |vel|) / (0 + 1) per not-done agent in
@@ -186,6 +191,13 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         if (tid == 0) gctl->halt = 1;  // nothing else of the shared copy is kept: the block partials stay queued for lc_get_scores
         return;
     }
+    if (P->n_walls > 0 && ctl->wr1 != 0x7fffffff && !ctl->w_served) {
+        // walled scene: some agent needs GMP::plan_one before this frame's update_agents (ai.cpp:162-168).  The planner
+        // lives on the host (planner.cpp): stop here — this and every later frame of the graph replay is a no-op and the
+        // frame counter does not advance — until lc_step has uploaded the new waypoint lists.
+        if (tid == 0) gctl->halt = 2;
+        return;
+    }
     const float fake_time = __fmul_rn(LC_DT, (float)frame);
     if (!was_finished) {
         // newly done agents, table order (demo.cpp:669-676)
@@ -207,7 +219,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
                     __syncthreads();
                 }
             if (tid == 0)
-                for (int i = 0; i < cnt; ++i) update_runs(ctl, __fsub_rn(fake_time, __int_as_float(s_ev[i].y)));
+                for (int i = 0; i < cnt; ++i) update_runs(ctl, __fsub_rn(fake_time, __int_as_float(s_ev[i].y)), b.fin_log);
         } else if (cnt > EV_SORT_CAP) {
             for (int i = tid; i < n; i += blockDim.x) b.ev_by_id[i] = CUDART_NAN_F;
             __syncthreads();
@@ -221,7 +233,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
                 __syncthreads();
                 if (tid == 0)
                     for (int k = 0; k < blockDim.x; ++k)
-                        if (s_flag[k]) update_runs(ctl, __fsub_rn(fake_time, s_ft[k]));
+                        if (s_flag[k]) update_runs(ctl, __fsub_rn(fake_time, s_ft[k]), b.fin_log);
                 __syncthreads();
             }
         }
@@ -240,7 +252,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
                     __syncthreads();
                     if (tid == 0)
                         for (int k = 0; k < blockDim.x; ++k)
-                            if (s_flag[k]) update_runs(ctl, s_ft[k]);
+                            if (s_flag[k]) update_runs(ctl, s_ft[k], b.fin_log);
                     __syncthreads();
                 }
             }
@@ -265,7 +277,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
                 __syncthreads();
                 if (tid == 0)
                     for (int k = 0; k < blockDim.x; ++k)
-                        if (s_flag[k]) update_runs(ctl, s_ft[k]);
+                        if (s_flag[k]) update_runs(ctl, s_ft[k], b.fin_log);
                 __syncthreads();
             }
             all_done = true;
@@ -295,6 +307,12 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         }
         ctl->overlap2 = 0ull;
         ctl->coll_hits = 0ull;
+        if (P->n_walls > 0) {  // this frame's k_collide collects the next frame's replan requests
+            ctl->wr1 = ctl->wr2 = 0x7fffffff;
+            ctl->w_served = 0;
+            ctl->draws += (unsigned long long)ctl->drawn_last;  // plan-less agents do not draw (LMP.cpp:267-270)
+            ctl->drawn_last = ctl->n_planned;
+        }
     }
     if (tid < HULL_K) ctl->ext[tid] = 0ull;
     __syncthreads();
@@ -829,10 +847,64 @@ void launch_pair_count(const Params* dP, int n, const Buffers& b, unsigned long 
 #ifndef LC_FORCE_BLOCKS
 #define LC_FORCE_BLOCKS 10
 #endif
+// minstd_rand0 skip-ahead: 16807^e mod (2^31 - 1)
+__device__ __forceinline__ uint32_t lcg_pow_dev(unsigned long long e) {
+    uint32_t r = 1u, a = 16807u;
+    while (e) {
+        if (e & 1ull) r = lcg_mul(r, a);
+        a = lcg_mul(a, a);
+        e >>= 1;
+    }
+    return r;
+}
+
+// walls of the scene for one block: shared memory when they fit, else straight from global (L1-resident: every thread
+// walks the same list)
+__device__ __forceinline__ const lcw::Wall* stage_walls(const Params* P, const Buffers& b, lcw::Wall* s_walls) {
+    const int nw = P->n_walls;
+    if (nw > WALL_SMEM) return reinterpret_cast<const lcw::Wall*>(b.w.walls);
+    for (int k = threadIdx.x; k < nw; k += blockDim.x) {
+        const WallRect w = b.w.walls[k];
+        s_walls[k] = lcw::Wall{w.ox, w.oy, w.w, w.h};
+    }
+    __syncthreads();
+    return s_walls;
+}
+
+// ai.cpp:152-163 for the COMING frame, evaluated on the final (synced) position of this one: sight line to the next
+// waypoint, lost_frames, need_replan; requests are reduced to the two lowest ids (= the first two in table order, the
+// only ones the reference serves per frame, ai.cpp:151-152,164).
+__device__ __forceinline__ void walled_gate(const Params* P, const Buffers& b, const lcw::Wall* walls, int id, float px, float py,
+                                            float gx, float gy) {
+    const WalledArrays& W = b.w;
+    const int np = W.n_plan[id], nd = W.num_done[id];
+    const bool has = np > 0, done = has && nd == np;
+    const float gd = len2(__fsub_rn(gx, px), __fsub_rn(gy, py));
+    bool visible = false;
+    if (has && nd < np) {
+        const float2 t = W.plan[(size_t)id * WP_CAP + nd];
+        visible = true;
+        for (int k = 0; k < P->n_walls && visible; ++k) visible = lcw::cspace_line_of_sight(walls[k], P->r, px, py, t.x, t.y);
+    }
+    const int lost = visible ? 0 : W.lost[id] + 1;
+    W.lost_next[id] = lost;
+    const bool need = !has || (done && gd > 1.f) || (!done && !visible && lost >= 360);
+    if (need) {
+        W.req_pos[id] = make_float2(px, py);
+        const int old = atomicMin(&b.ctl->wr1, id);
+        const int loser = old < id ? id : old;
+        if (loser != 0x7fffffff) atomicMin(&b.ctl->wr2, loser);
+    }
+}
+
+template <bool WALLS>
 __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    __shared__ lcw::Wall s_walls[WALLS ? WALL_SMEM : 1];
+    const lcw::Wall* walls = nullptr;
+    if constexpr (WALLS) walls = stage_walls(P, b, s_walls);
     const int n = P->n;
     if ((int)(blockIdx.x * blockDim.x) >= n) return;  // domain mode launches for the capacity, not the count
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -955,6 +1027,15 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
                 if (lst && k < b.list_cap) lst[k] = bid;
             }
         }
+        if constexpr (WALLS) {  // LMP.cpp:306-319: the statics loop, after the agents, in the BoundVolume* table's order
+            for (int k = 0; k < P->n_walls; ++k) {
+                float fx, fy;
+                if (lcw::wall_force(px, py, P->r, vx, vy, walls[b.w.wall_order[k]], fx, fy)) {
+                    ttcFx = __fadd_rn(ttcFx, fx);
+                    ttcFy = __fadd_rn(ttcFy, fy);
+                }
+            }
+        }
         int4 mt = b.srt.meta[s];
         const bool owned = !(mt.y & META_GHOST);  // ghosts are advanced too (the collision pass needs their integrated
                                                   // position) but never counted: their owner does that
@@ -1052,14 +1133,42 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         // ---- S2: ai::update_agents (ai.cpp:153-172) ----
         const float gd = len2(__fsub_rn(goal.x, px), __fsub_rn(goal.y, py));
         c4.w = gd;
-        int num_done = mt.y & 1;
-        if (num_done && gd > 1.f && (id == ctl->replan1 || id == ctl->replan2)) num_done = 0;  // GMP::plan_one
-        // LMP::lookahead (LMP.cpp:84-113) with plan = [final_goal]
-        if (num_done < 1) {
-            const float ox = __fsub_rn(px, goal.x), oy = __fsub_rn(py, goal.y);
-            if (dot2(ox, oy, ox, oy) < 1.f) num_done = 1; else lgoal = goal;
+        int num_done;       // 1 = Agent::done() after this frame's lookahead (Agent.h:24-26)
+        bool planned = true;  // Agent::has_plan()
+        float eps = 0.f;
+        if constexpr (!WALLS) {
+            num_done = mt.y & 1;
+            if (num_done && gd > 1.f && (id == ctl->replan1 || id == ctl->replan2)) num_done = 0;  // GMP::plan_one
+            // LMP::lookahead (LMP.cpp:84-113) with plan = [final_goal]
+            if (num_done < 1) {
+                const float ox = __fsub_rn(px, goal.x), oy = __fsub_rn(py, goal.y);
+                if (dot2(ox, oy, ox, oy) < 1.f) num_done = 1; else lgoal = goal;
+            } else {
+                lgoal = goal;
+            }
+            // LMP.cpp:261-273: one draw for both components
+            eps = lcg_uniform((uint32_t)mt.z, -.01f, .01f);
+            mt.z = (int)lcg_mul((uint32_t)mt.z, P->lcg_stride);
         } else {
-            lgoal = goal;
+            // Walled scene: the waypoint list lives by engine id; replans of this frame (ai.cpp:164-168) were served by the
+            // host before the frame started (new list, num_done = 0, lost_frames = 0), S0 / S1 above still saw the old
+            // done() through the flag bit, as demo::run and comm::run do in the reference.
+            const WalledArrays& W = b.w;
+            const int np = W.n_plan[id];
+            int nd = W.num_done[id];
+            W.lost[id] = W.lost_next[id];  // ai.cpp:161 (the gate evaluated it on this frame's start position)
+            planned = np > 0;
+            if (planned) {
+                lcw::lookahead(walls, P->n_walls, P->r, px, py, reinterpret_cast<const float*>(W.plan + (size_t)id * WP_CAP), np, nd,
+                               lgoal.x, lgoal.y);  // LMP.cpp:84-113
+                // agent k of the table draws element draws + (planned agents before it) + 1 of the global stream
+                const unsigned long long e = ctl->draws + (unsigned long long)(id - W.noplan_before[id]) + 1ull;
+                eps = lcg_uniform(lcg_mul(P->rng0, lcg_pow_dev(e)), -.01f, .01f);
+            } else {
+                lgoal = make_float2(px, py);  // LMP.cpp:267-270: no plan, no draw, goal_vel = 0
+            }
+            W.num_done[id] = nd;
+            num_done = planned && nd == np;
         }
         if (num_done == 1 && !(mt.y & 2)) {  // will be counted by demo::run at the start of the next frame
             mt.y |= 2;
@@ -1070,12 +1179,10 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         }
         mt.y = (mt.y & ~1) | num_done;
         not_done_after = num_done == 0 && owned;
-        // LMP.cpp:261-273: one draw for both components
-        const float eps = lcg_uniform((uint32_t)mt.z, -.01f, .01f);
-        mt.z = (int)lcg_mul((uint32_t)mt.z, P->lcg_stride);
         const float dgx = __fsub_rn(__fadd_rn(lgoal.x, eps), px), dgy = __fsub_rn(__fadd_rn(lgoal.y, eps), py);
         const float dl = glm_max(1.0f, len2(dgx, dgy));
-        const float gvx = __fmul_rn(1.0f, __fdiv_rn(dgx, dl)), gvy = __fmul_rn(1.0f, __fdiv_rn(dgy, dl));
+        float gvx = __fmul_rn(1.0f, __fdiv_rn(dgx, dl)), gvy = __fmul_rn(1.0f, __fdiv_rn(dgy, dl));
+        if (WALLS && !planned) gvx = gvy = 0.f;
         const float goalFx = __fmul_rn(2.0f, __fsub_rn(gvx, vx)), goalFy = __fmul_rn(2.0f, __fsub_rn(gvy, vy));
 
         forcex = __fadd_rn(forcex, __fadd_rn(goalFx, ttcFx));  // ai.cpp:172
@@ -1142,11 +1249,14 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
 
 // S3b: collision push-out (physics.cpp:58-69 + BVH.cpp:106-120), Jacobi: every agent tests the others at their
 // integrated, not yet pushed positions; hits are applied in table (id) order.  Then physics.cpp:72-76.
-template <bool DD>
+template <bool DD, bool WALLS>
 __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    __shared__ lcw::Wall s_walls[WALLS ? WALL_SMEM : 1];
+    const lcw::Wall* walls = nullptr;
+    if constexpr (WALLS) walls = stage_walls(P, b, s_walls);
     const int n = P->n;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     bool valid = s < n;
@@ -1215,7 +1325,34 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                 if (!(mt.y & META_GHOST)) atomicAdd(&ctl->coll_hits, (unsigned long long)cnt);
             }
         }
+        if constexpr (WALLS) {
+            // physics.cpp:60,67-69: static_bvh->query at the integrated position, pushed out after the agent hits.
+            // BVH::query_(Circ*) (BVH.cpp:106-138): depth first, left before right; inner nodes are entered through the
+            // same single-point test as the leaves (quirk Q8), so hits can be missed exactly as the reference misses them.
+            float2 h = b.cur.vfh[s];
+            int wcnt = 0, sp = 0;
+            int stack[48];
+            stack[sp++] = 0;
+            while (sp > 0) {
+                const BvhNode nd = b.w.bvh[stack[--sp]];
+                float nx, ny;
+                if (nd.right < 0) {
+                    if (lcw::circ_wall_hit(qx, qy, P->r, walls[nd.left], nx, ny)) { push_away(px, py, h.x, h.y, nx, ny); ++wcnt; }
+                } else if (lcw::circ_wall_hit(qx, qy, P->r, lcw::Wall{nd.ox, nd.oy, nd.w, nd.h}, nx, ny) && sp + 2 <= 48) {
+                    stack[sp++] = nd.right;
+                    stack[sp++] = nd.left;
+                }
+            }
+            if (wcnt) {
+                b.cur.vfh[s] = h;
+                atomicAdd(&ctl->wall_hits, (unsigned long long)wcnt);
+            }
+        }
         b.posf[s] = make_float2(px, py);
+        if constexpr (WALLS) {  // replan gate of the coming frame (ai.cpp:152-163) on the position all_sync publishes
+            const float2 g = b.cur.goal[s];
+            walled_gate(P, b, walls, mt.x, px, py, g.x, g.y);
+        }
         speed = __fsqrt_rn(dot3_xz(me.z, me.w, me.z, me.w));
         if (!(mt.y & 1) && !(mt.y & META_GHOST)) {  // physics.cpp:72-76
             lv_id = (uint32_t)(mt.x + 1);
@@ -1251,6 +1388,16 @@ __global__ void __launch_bounds__(128) k_init_reduce(const Params* __restrict__ 
     block_reduce_store(b, valid && x == x && y == y, x, y, speed, 0u);
 }
 
+// replan gate of the coming frame from an arbitrary state (after lc_create / lc_set_state); later frames: k_collide's tail
+__global__ void __launch_bounds__(128) k_walled_gate(const Params* __restrict__ P, Buffers b) {
+    __shared__ lcw::Wall s_walls[WALL_SMEM];
+    const lcw::Wall* walls = stage_walls(P, b, s_walls);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P->n) return;
+    const float2 p = b.posf[i], g = b.cur.goal[i];
+    walled_gate(P, b, walls, b.cur.meta[i].x, p.x, p.y, g.x, g.y);
+}
+
 __global__ void __launch_bounds__(1024) k_finalize(const Params* __restrict__ P, Buffers b) {
     // lc_get_scores between frames: fold the last frame's lastvel partial, but leave the bbox/vmax partials for the
     // next k_frame_begin (consume is idempotent on those: min/max into Ctl, which frame_begin resets after use)
@@ -1277,7 +1424,7 @@ __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P,
     if (facing) facing[id] = b.cur.facing[s];
     if (lgoal) lgoal[id] = b.cur.lgoal[s];
     if (goal_dist) goal_dist[id] = c4.w;
-    if (num_done) num_done[id] = mt.y & 1;
+    if (num_done) num_done[id] = P->n_walls > 0 ? b.w.num_done[mt.x] : (mt.y & 1);  // Agent::num_done (waypoints passed)
 }
 
 // Diagnostics of the last frame (comm partner, |{j : ttc_ij <= 5}|) are kept per slot by k_force — an id-indexed store
@@ -1359,7 +1506,15 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
     if (facing) fc = facing[e];
     if (lgoal) lg = lgoal[e];
     if (goal_dist) c4.w = goal_dist[e];
-    if (num_done) mt.y = (mt.y & ~1) | (num_done[e] & 1);
+    if (num_done) {
+        if (P->n_walls > 0 && !init) {  // walled: the waypoint counter itself; the flag bit is Agent::done()
+            const int np = b.w.n_plan[mt.x];
+            b.w.num_done[mt.x] = num_done[e];
+            mt.y = (mt.y & ~1) | ((np > 0 && num_done[e] == np) ? 1 : 0);
+        } else {
+            mt.y = (mt.y & ~1) | (num_done[e] & 1);
+        }
+    }
     if (goal) g = goal[e];
     if (min_time) mt.w = __float_as_int(min_time[e]);
     b.cur.pv[i] = make_float4(p.x, p.y, pv.z, pv.w);
@@ -1402,6 +1557,8 @@ __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
         ctl->nnd_acc = 0;
+        ctl->wr1 = ctl->wr2 = 0x7fffffff;  // walled scenes: k_walled_gate re-evaluates the requests on the new state
+        ctl->w_served = 0;
         for (int k = 0; k < HULL_K; ++k) ctl->ext_val[k] = -CUDART_INF_F;  // arbitrary new state: no gate next frame
     }
 }
@@ -1467,7 +1624,7 @@ static void launch(void (*kernel)(KArgs...), unsigned grid, unsigned block, cuda
 }
 
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches, cudaEvent_t* ev,
-                  const SideStream* side) {
+                  const SideStream* side, bool walled) {
     // n = launch width (the capacity in domain mode; kernels read the live count from Params::n on the device)
     // ev (optional, FRAME_KERNELS + 1 events): per-kernel device timing for bench.py's roofline leg
     const bool dd = b.dd != nullptr;
@@ -1492,17 +1649,21 @@ void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long lon
         cudaEventRecord(side->join, side->st);
         launch(k_pairs, cdiv(n, 128), 128, st, cP, b);
         cudaStreamWaitEvent(st, side->join, 0);
-        k_force<<<cdiv(n, 128), 128, 0, st>>>(dP, b);  // two predecessors: a plain (full) dependency on both
+        // two predecessors: a plain (full) dependency on both
+        if (walled) k_force<true><<<cdiv(n, 128), 128, 0, st>>>(dP, b);
+        else k_force<false><<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     } else {
         launch(k_refine, 1, 1024, st, cP, b);
         if (ev) cudaEventRecord(ev[5], st);
         launch(k_pairs, cdiv(n, 128), 128, st, cP, b);
         if (ev) cudaEventRecord(ev[6], st);
-        launch(k_force, cdiv(n, 128), 128, st, cP, b);
+        if (walled) launch(k_force<true>, cdiv(n, 128), 128, st, cP, b);
+        else launch(k_force<false>, cdiv(n, 128), 128, st, cP, b);
     }
     if (ev) cudaEventRecord(ev[7], st);
-    if (dd) launch(k_collide<true>, cdiv(n, 128), 128, st, cP, b);
-    else launch(k_collide<false>, cdiv(n, 128), 128, st, cP, b);
+    if (dd) launch(k_collide<true, false>, cdiv(n, 128), 128, st, cP, b);
+    else if (walled) launch(k_collide<false, true>, cdiv(n, 128), 128, st, cP, b);
+    else launch(k_collide<false, false>, cdiv(n, 128), 128, st, cP, b);
     if (ev) cudaEventRecord(ev[8], st);
     if (launches) *launches += dd ? FRAME_KERNELS + DD_KERNELS : FRAME_KERNELS;
 }
@@ -1529,6 +1690,11 @@ void launch_get_diag(const Params* dP, int n, const Buffers& b, cudaStream_t st,
 
 void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
     k_dd_pack<<<cdiv(n, 256), 256, 0, st>>>(dP, b);  // before the first frame only; afterwards k_collide packs
+    if (launches) *launches += 1;
+}
+
+void launch_walled_gate(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches) {
+    k_walled_gate<<<cdiv(n, 128), 128, 0, st>>>(dP, b);
     if (launches) *launches += 1;
 }
 

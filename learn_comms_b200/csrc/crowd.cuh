@@ -78,6 +78,15 @@ struct Ctl {
     // counters (diagnostics)
     unsigned long long overlap2, coll_hits;
     int near_overflow, hit_overflow;
+    // walled scenes (walls.cuh): replans are served by the host planner between frames.  The tail of k_collide evaluates
+    // the gate of ai.cpp:152-168 for the NEXT frame and leaves the two lowest requesting ids here; k_frame_begin then
+    // pauses the graph replay (halt = 2, frame not advanced) until the host has uploaded the new waypoint lists.
+    int wr1, wr2;                // requesting ids (0x7fffffff = none)
+    int w_served;                // the host has served wr1 / wr2 for the coming frame
+    int n_planned;               // agents with a non-empty plan = minstd_rand0 draws per frame (LMP.cpp:259-263)
+    int drawn_last;              // draws the last executed frame consumed
+    unsigned long long draws;    // draws consumed BEFORE the last executed frame (its agent k draws element draws + k + 1)
+    unsigned long long wall_hits, replans;
 };
 
 constexpr int DD_MAX_WORLD = 8;     // ranks of one spatially decomposed crowd (one B200 box)
@@ -98,8 +107,28 @@ struct Params {
     uint32_t lcg_stride;  // 16807^n mod (2^31-1): advances an agent's private stream by one frame
     uint32_t flags;
     int stencil_req;
+    int n_walls, n_bvh;   // static walls (0 = wall-free: the kernels' WALLS = false instantiations)
+    uint32_t rng0;        // walled: stream state before frame 1's first draw (draw k of the run = rng0 * 16807^k)
     float m_cv[24];
     float m_f[6];
+};
+
+constexpr int WP_CAP = 32;        // waypoints per agent in walled scenes (the catalogue's plans have <= ~10)
+constexpr int WALL_SMEM = 128;    // walls staged in shared memory per block; beyond that they are read from global
+struct WallRect { float ox, oy, w, h; };                      // == lcw::Wall
+struct BvhNode { float ox, oy, w, h; int left, right; };     // == lc_bvh_node
+// Walled-scene state, indexed by ENGINE ID (not slot: nothing here is reordered with the grid)
+struct WalledArrays {
+    const WallRect* walls;   // [n_walls] creation order
+    const int* wall_order;   // [n_walls] statics order (LMP.cpp:307 loop)
+    const BvhNode* bvh;      // [n_bvh] static BVH, pre-order (lc_static_bvh)
+    float2* plan;            // [n_ids][WP_CAP]  Agent::plan (Agent.h:14)
+    int* n_plan;             // [n_ids]  0 = no plan (unreachable goal)
+    int* num_done;           // [n_ids]  Agent::num_done (Agent.h:13)
+    int* lost;               // [n_ids]  Agent::lost_frames after the last executed update_agents (Agent.h:28)
+    int* lost_next;          // [n_ids]  ... as the coming frame's gate will leave it (0 for an agent the host replanned)
+    int* noplan_before;      // [n_ids]  plan-less agents with a smaller id (they do not draw, LMP.cpp:267-270)
+    float2* req_pos;         // [n_ids]  position a requesting agent replans from (GMP.cpp:96: a.start)
 };
 
 struct Buffers {
@@ -132,6 +161,8 @@ struct Buffers {
     // "ascending id" everywhere in the kernels is the reference's loop order.  ext_of[id] = the caller's agent index;
     // nullptr = identity.  Only the host-facing kernels (get / set state, diagnostics, shards) translate.
     const int* ext_of;
+    WalledArrays w;    // valid when Params::n_walls > 0
+    float* fin_log;    // [n_ids][3] (overhead, run_avg, run_std) per counted finisher, in Welford order (demo.cpp:655-663)
     Ctl* ctl;
     struct DomainDev* dd;  // device-side exchange state (domain.cuh); nullptr for a single-GPU crowd
 };
@@ -177,9 +208,10 @@ void launch_dd_pack(const Params* dP, int n, const Buffers& b, cudaStream_t st, 
 // peers) does not feed k_pairs, so the two run side by side (fork after k_reorder, join before k_force).
 struct SideStream { cudaStream_t st; cudaEvent_t fork, join; };
 void launch_frame(Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches,
-                  cudaEvent_t* ev = nullptr, const SideStream* side = nullptr);
+                  cudaEvent_t* ev = nullptr, const SideStream* side = nullptr, bool walled = false);
 void launch_pair_count(const Params* dP, int n, const Buffers& b, unsigned long long* out, cudaStream_t st, long long* launches);
 void launch_init_reduce(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);
+void launch_walled_gate(const Params* dP, int n, const Buffers& b, cudaStream_t st, long long* launches);  // gate of the coming frame
 void launch_finalize(const Params* dP, const Buffers& b, cudaStream_t st, long long* launches);
 void launch_get_state(const Params* dP, int n, const Buffers& b, float2* pos, float2* vel, float2* vfh, float* c3,
                       float2* facing, float2* lgoal, float* goal_dist, int* num_done, cudaStream_t st,

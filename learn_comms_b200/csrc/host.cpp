@@ -77,41 +77,152 @@ Vec2 axial_goal(Vec2 p) {  // demo.cpp:36-41
 
 }  // namespace
 
+// ---- scene catalogue, demo.cpp:141-511 make_scene ----
+namespace {
+
+enum class Goal { opposite, axial, mirror_x, translate, random };
+enum class Place { radial, regiments, list, random };
+enum class Walls { none, random_posts, centre, table, hole, hall, column };
+
+struct SceneSpec {
+    int n = 0, n_walls = 0;
+    float wall_scale = 0.f, max_duration = 0.f, radius = 0.f;
+    Goal goal = Goal::opposite;
+    Place place = Place::radial;
+    Walls walls = Walls::none;
+    Vec2 shift{0.f, 0.f};
+    Regiment regs[4];
+    Vec2 list[4];
+    const float (*wall_table)[2] = nullptr;
+};
+
+// demo.cpp:214-231 (scene 6), :312-353 (scene 11), :461-486 (scene 18)
+const float kCurbs[12][2] = {{-3, -3}, {-3, 3}, {3, -3}, {3, 3}, {4, 4}, {4, -4}, {6, -5}, {6, 5}, {-4, 4}, {-6, 5}, {-4, -4}, {-6, -5}};
+const float kRoom[32][2] = {{0, 8},     {2, 8},     {4, 8},     {8, 8},      {-6, 8},     {-4, 8},     {-2, 8},  {-8, 0},
+                            {-8, 2},    {-8, 4},    {-8, 6},    {-8, 8},     {-8, -6},    {-8, -4},    {-8, -2}, {-7.4f, -8},
+                            {1.4f, -8}, {3.4f, -8}, {5.4f, -8}, {-5.4f, -8}, {-3.4f, -8}, {-1.4f, -8}, {8, 0},   {8, 2},
+                            {8, 4},     {8, 6},     {7.4f, -8}, {8, -6},     {8, -4},     {8, -2},     {6, 3},   {4, 3}};
+const float kTwoDoorY[20] = {1, -1, 3, -3, 6, -5, 8, -8, 10, -10, 12, -12, 14, -14, 16, -16, 18, -18, 20, -20};
+
+void two_regiments(SceneSpec& s, Regiment a, Regiment b) {
+    s.place = Place::regiments;
+    s.regs[0] = centered(a);
+    s.regs[1] = centered(b);
+}
+void doorway(SceneSpec& s) {  // demo.cpp:106-114 make_hole_wall(1.f, 2.f): two columns of 2 m tiles with a 1 m gap at the origin
+    s.n_walls = 30; s.wall_scale = 2.0f; s.walls = Walls::hole; s.goal = Goal::mirror_x;
+}
+
+bool scene_spec(uint32_t scene, SceneSpec& s) {
+    switch (scene) {
+    case 0: s.n = 60; s.max_duration = 45.f; s.radius = 10.f; return true;   // demo.cpp:145-151
+    case 1: s.n = 90; s.max_duration = 70.f; s.radius = 13.f; return true;   // :153-159
+    case 2: s.n = 60; s.max_duration = 40.f; s.radius = 10.f; s.n_walls = 60; s.wall_scale = 0.3f; s.walls = Walls::random_posts; return true;  // :161-175
+    case 3: s.n = 60; s.max_duration = 40.f; s.radius = 10.f; s.n_walls = 1; s.wall_scale = 4.0f; s.walls = Walls::centre; return true;        // :177-187
+    case 4: case 5: case 6:  // :189-232, make_intersecting_bots(14, 7, 6.f) :96-104
+        s.n = 56; s.max_duration = scene == 5 ? 70.f : 40.f; s.goal = scene == 5 ? Goal::opposite : Goal::axial;
+        s.place = Place::regiments;
+        s.regs[0] = centered({{1, 0}, {-6.f, 0}, {1.f, 1.f}, 7, 14}); s.regs[1] = centered({{-1, 0}, {6.f, 0}, {1.f, 1.f}, 7, 14});
+        s.regs[2] = centered({{0, 1}, {0, -6.f}, {1.f, 1.f}, 7, 14}); s.regs[3] = centered({{0, -1}, {0, 6.f}, {1.f, 1.f}, 7, 14});
+        if (scene == 6) { s.n_walls = 12; s.wall_scale = 2.0f; s.walls = Walls::table; s.wall_table = kCurbs; }
+        return true;
+    case 7: s.n = 2; s.max_duration = 70.f; doorway(s); s.place = Place::list; s.list[0] = {-3.f, 0}; s.list[1] = {3.f, 0}; return true;  // :234-246
+    case 8: s.n = 4; s.max_duration = 30.f; doorway(s); two_regiments(s, {{1, 0}, {-3, 0}, {1.f, 1.f}, 2, 2}, {{-1, 0}, {3, 0}, {1.f, 1.f}, 2, 2}); return true;
+    case 9: s.n = 40; s.max_duration = 100.f; doorway(s); two_regiments(s, {{1, 0}, {-3, 0}, {1.f, 1.f}, 5, 20}, {{-1, 0}, {3, 0}, {1.f, 1.f}, 5, 20}); return true;
+    case 10: s.n = 40; s.max_duration = 100.f; doorway(s); two_regiments(s, {{1, 0}, {-3, 0}, {1.f, 1.f}, 5, 5}, {{-1, 0}, {3, 0}, {1.f, 1.f}, 5, 35}); return true;
+    case 11:  // escaping room, :300-355
+        s.n = 70; s.max_duration = 100.0f; s.n_walls = 32; s.wall_scale = 2.0f; s.walls = Walls::table; s.wall_table = kRoom;
+        s.goal = Goal::translate; s.shift = {-20.f, 0.f};
+        two_regiments(s, {{0, 1}, {1, 6}, {2.f, 1.5f}, 3, 6}, {{-1, 0}, {-4, -2}, {1.f, 1.f}, 8, 64});
+        return true;
+    case 12: s.n = 200; s.max_duration = 30.f; s.place = Place::random; s.goal = Goal::random; return true;  // :358-373
+    case 13:  // two formations in a hall, :375-390
+        s.n = 40; s.max_duration = 90.0f; s.n_walls = 18; s.wall_scale = 2.0f; s.walls = Walls::hall; s.goal = Goal::mirror_x;
+        two_regiments(s, {{1, 0}, {-3, 0}, {.5f, .7f}, 5, 20}, {{-1, 0}, {3, 0}, {.5f, .7f}, 5, 20});
+        return true;
+    case 14: s.n = 2; s.max_duration = 30.f; s.goal = Goal::mirror_x; s.place = Place::list; s.list[0] = {-5.f, .1f}; s.list[1] = {3.f, 0}; return true;
+    case 15: s.n = 3; s.max_duration = 40.f; s.goal = Goal::mirror_x; s.place = Place::list;
+        s.list[0] = {-5.f, .1f}; s.list[1] = {3.f, 0}; s.list[2] = {7.f, 0}; return true;
+    case 16: s.n = 4; s.max_duration = 40.f; s.goal = Goal::mirror_x; s.place = Place::list;
+        s.list[0] = {-5.f, .1f}; s.list[1] = {3.f, 0}; s.list[2] = {7.f, 0}; s.list[3] = {-2.f, .1f}; return true;
+    case 17: s.n = 4; s.max_duration = 45.f; s.goal = Goal::mirror_x;
+        two_regiments(s, {{1, 0}, {-5, .1f}, {1.f, 1.f}, 2, 2}, {{-1, 0}, {3, 0}, {1.f, 1.f}, 2, 2}); return true;
+    case 18:  // two-door, :448-488
+        s.n = 65; s.max_duration = 60.f; s.n_walls = 20; s.wall_scale = 2.0f; s.walls = Walls::column;
+        s.goal = Goal::translate; s.shift = {-15.f, 0.f};
+        two_regiments(s, {{-1, 0}, {3, 3}, {1.f, 1.f}, 5, 5}, {{-1, 0}, {3, -6}, {1.f, 1.f}, 10, 60});
+        return true;
+    default:
+        if (scene >= 900 && scene < 900 + 3000) {  // :490-508: scene 9 with 40 + (scn - 900) robots (the reference needs scn > 100)
+            s.n = 40 + (int)(scene - 900); s.max_duration = 100.f; doorway(s);
+            const unsigned even = (unsigned)s.n / 2, odd = even + (unsigned)s.n % 2;
+            two_regiments(s, {{1, 0}, {-3, 0}, {1.f, 1.f}, 5, odd}, {{-1, 0}, {3, 0}, {1.f, 1.f}, 5, even});
+            return true;
+        }
+        return false;  // 19 .. 899: the reference leaves Scene::num_robos uninitialised
+    }
+}
+
+}  // namespace
+
 extern "C" {
 
-int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
-                 uint32_t* rng_state_after) {
-    int32_t n;
-    float md;
-    switch (scene) {
-    case 0: n = 60; md = 45.f; break;   // demo.cpp:145-151
-    case 1: n = 90; md = 70.f; break;   // demo.cpp:153-159
-    case 4: n = 56; md = 40.f; break;   // demo.cpp:189-195
-    case 5: n = 56; md = 70.f; break;   // demo.cpp:197-203
-    case 12: n = 200; md = 30.f; break; // demo.cpp:356-373
-    default: return LC_ERR_ARG;         // walled scenes: SURVEY §8f-2, not built yet
-    }
-    if (cap < n || !pos || !goal) return LC_ERR_ARG;
+// demo::init's make_scene + the create_robo / create_wall loops (demo.cpp:611-635): robots first, then walls; scenes 2
+// and 12 draw from the seeded global stream while they are built.
+int32_t lc_scene_full(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
+                      uint32_t* rng_state_after, lc_rect* walls, int32_t wall_cap, int32_t* n_walls) {
+    SceneSpec sp;
+    if (!scene_spec(scene, sp)) return LC_ERR_ARG;
+    if (cap < sp.n || !pos || !goal) return LC_ERR_ARG;
+    if (sp.n_walls > 0 && (!walls || wall_cap < sp.n_walls)) return LC_ERR_ARG;
     Lcg rng(seed);
-    Regiment regs[4] = {centered({{1, 0}, {-6.f, 0}, {1.f, 1.f}, 7, 14}), centered({{-1, 0}, {6.f, 0}, {1.f, 1.f}, 7, 14}),
-                        centered({{0, 1}, {0, -6.f}, {1.f, 1.f}, 7, 14}), centered({{0, -1}, {0, 6.f}, {1.f, 1.f}, 7, 14})};
-    for (int32_t i = 0; i < n; ++i) {
+    for (int32_t i = 0; i < sp.n; ++i) {
         Vec2 p{}, g{};
-        if (scene == 0) { p = radial_pos((unsigned)i, 60, 10.f); g = -p; }
-        else if (scene == 1) { p = radial_pos((unsigned)i, 90, 13.f); g = -p; }
-        else if (scene == 4) { p = regiment_pos(regs, (unsigned)i); g = axial_goal(p); }
-        else if (scene == 5) { p = regiment_pos(regs, (unsigned)i); g = -p; }
-        else {
-            // glm::vec2(inside(gen), inside(gen)): g++ evaluates the arguments right to left (verified with O-ref)
-            p.y = rng.uniform(-10.f, 10.f); p.x = rng.uniform(-10.f, 10.f);
-            g.y = rng.uniform(-10.f, 10.f); g.x = rng.uniform(-10.f, 10.f);
+        switch (sp.place) {
+        case Place::radial: p = radial_pos((unsigned)i, (unsigned)sp.n, sp.radius); break;
+        case Place::regiments: p = regiment_pos(sp.regs, (unsigned)i); break;
+        case Place::list: p = sp.list[i]; break;
+        case Place::random:  // glm::vec2(inside(gen), inside(gen)): g++ evaluates the arguments right to left (verified with O-ref)
+            p.y = rng.uniform(-10.f, 10.f); p.x = rng.uniform(-10.f, 10.f); break;
+        }
+        switch (sp.goal) {
+        case Goal::opposite: g = -p; break;                       // demo.cpp:29
+        case Goal::axial: g = axial_goal(p); break;               // :36-41
+        case Goal::mirror_x: g = {-p.x, p.y}; break;              // :33-35
+        case Goal::translate: g = p + sp.shift; break;            // :30-32
+        case Goal::random: g.y = rng.uniform(-10.f, 10.f); g.x = rng.uniform(-10.f, 10.f); break;
         }
         pos[2 * i] = p.x; pos[2 * i + 1] = p.y;
         goal[2 * i] = g.x; goal[2 * i + 1] = g.y;
     }
-    if (max_duration) *max_duration = md;
+    for (int32_t i = 0; i < sp.n_walls; ++i) {  // create_wall: square Rect of side wall_scale (demo.cpp:44-46,523)
+        Vec2 p{};
+        const float side = (i % 2) == 0 ? 1.f : -1.f;
+        switch (sp.walls) {
+        case Walls::random_posts: p.y = rng.uniform(-7.f, 7.f); p.x = rng.uniform(-7.f, 7.f); break;  // demo.cpp:170-174
+        case Walls::centre: break;
+        case Walls::table: p = {sp.wall_table[i][0], sp.wall_table[i][1]}; break;
+        case Walls::hole: p = {0.f, side * (sp.wall_scale * (static_cast<float>(i / 2) + .5f) + 1.f / 2.f)}; break;  // :106-114
+        case Walls::hall:  // make_hall(3.f, scale), :115-124; (i + 2 % 4) / 4 parses as (i + 2) / 4
+            p = {(i % 4 < 2 ? 1.f : -1.f) * sp.wall_scale * static_cast<float>((i + 2 % 4) / 4), side * .5f * (3.f + sp.wall_scale)};
+            break;
+        case Walls::column: p = {0.f, kTwoDoorY[i]}; break;
+        case Walls::none: break;
+        }
+        walls[i] = lc_rect{p.x, p.y, sp.wall_scale, sp.wall_scale};
+    }
+    if (max_duration) *max_duration = sp.max_duration;
     if (rng_state_after) *rng_state_after = rng.x;
-    return n;
+    if (n_walls) *n_walls = sp.n_walls;
+    return sp.n;
+}
+
+// the wall-free scenes through the original entry point; walled ones need lc_scene_full (the walls are part of the scene)
+int32_t lc_scene(uint32_t scene, uint64_t seed, float* pos, float* goal, int32_t cap, float* max_duration,
+                 uint32_t* rng_state_after) {
+    SceneSpec sp;
+    if (!scene_spec(scene, sp) || sp.n_walls > 0) return LC_ERR_ARG;
+    return lc_scene_full(scene, seed, pos, goal, cap, max_duration, rng_state_after, nullptr, 0, nullptr);
 }
 
 // Iteration order of the reference's component tables (quirk Q4).  Every DataTable is a
