@@ -165,6 +165,9 @@ typedef struct lc_batch_desc {
     uint32_t flags;
     int32_t device;
     const int32_t* table_order; /* [n_agents] as in lc_desc, shared by all scenarios; NULL = ascending index */
+    int32_t n_walls;            /* one wall layout shared by all scenarios of the batch (<= 64 walls); 0 = wall-free.  Replans */
+    const lc_rect* walls;       /* (ai.cpp:162-168) are served by the host planner: lc_batch_run relaunches the rollout kernel */
+    const int32_t* wall_order;  /* until no scenario waits for one.  wall_order as in lc_desc */
 } lc_batch_desc;
 int32_t lc_batch_create(const lc_batch_desc* desc, lc_batch** out);
 void lc_batch_destroy(lc_batch* b);
@@ -184,6 +187,8 @@ int32_t lc_batch_get_state(lc_batch* b, float* pos, float* vel, float* vel_foreh
  * executed frames of overlapping pairs at frame start, collision-pass hits and TTC pair evaluations */
 int32_t lc_batch_get_diag(lc_batch* b, int32_t* partner, int32_t* neighbor_count, int64_t* overlap_pairs,
                           int64_t* collision_hits, int64_t* pair_tests);
+/* walled batches: Agent::plan->size() and lost_frames [S][n], wall push-outs per scenario [S], replans served (total) */
+int32_t lc_batch_get_walled(lc_batch* b, int32_t* n_plan, int32_t* lost_frames, int64_t* wall_hits, int64_t* replans);
 int32_t lc_batch_timer(lc_batch* b, float* milliseconds); /* device time of the last lc_batch_run (CUDA events) */
 int64_t lc_batch_kernel_launches(lc_batch* b);
 
@@ -242,6 +247,7 @@ int32_t lc_lookahead(int32_t n_walls, const lc_rect* walls, float agent_radius, 
 typedef struct lc_planner lc_planner;
 int32_t lc_planner_create(int32_t n_walls, const lc_rect* walls, float agent_radius, lc_planner** out);
 void lc_planner_destroy(lc_planner* p);
+int32_t lc_planner_clone(const lc_planner* p, lc_planner** out);  /* same roadmap state (ids handed out, tie order), independent from then on */
 int32_t lc_planner_roadmap_size(lc_planner* p, int32_t* vertices, int32_t* directed_edges);
 /* GMP::plan_one for one agent: waypoints [n][2] from the first after `start` to `goal` inclusive (n = 0: unreachable);
  * min_time = path length - 1 (ai.cpp:118-126).  LC_ERR_CAPACITY (n still reported) when n > cap. */

@@ -31,7 +31,8 @@ class _DomainDesc(C.Structure):
 class _BatchDesc(C.Structure):
     _fields_ = [("n_scenarios", C.c_int32), ("n_agents", C.c_int32), ("pos", C.c_void_p), ("goal", C.c_void_p),
                 ("m_cv", C.c_void_p), ("m_f", C.c_void_p), ("max_duration", C.c_void_p), ("rng_state", C.c_void_p),
-                ("radius", C.c_float), ("flags", C.c_uint32), ("device", C.c_int32), ("table_order", C.c_void_p)]
+                ("radius", C.c_float), ("flags", C.c_uint32), ("device", C.c_int32), ("table_order", C.c_void_p),
+                ("n_walls", C.c_int32), ("walls", C.c_void_p), ("wall_order", C.c_void_p)]
 
 
 EXPORTS = [
@@ -39,9 +40,9 @@ EXPORTS = [
     "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
-    "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_kernel_launches",
+    "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy",
+    "lc_read_config", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -95,6 +96,7 @@ def lib():
         L.lc_batch_reset.argtypes = [vp, vp, vp]
         L.lc_batch_finished.argtypes = [vp, C.POINTER(i32)]
         L.lc_batch_get_diag.argtypes = [vp] + [vp] * 5
+        L.lc_batch_get_walled.argtypes = [vp, vp, vp, vp, C.POINTER(C.c_int64)]
         L.lc_batch_kernel_launches.argtypes = [vp]
         L.lc_batch_kernel_launches.restype = C.c_int64
         L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
@@ -109,6 +111,7 @@ def lib():
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
         L.lc_lookahead.argtypes = [i32, vp, C.c_float, i32, vp, vp, i32]
         L.lc_planner_create.argtypes = [i32, vp, C.c_float, C.POINTER(vp)]
+        L.lc_planner_clone.argtypes = [vp, C.POINTER(vp)]
         L.lc_planner_destroy.argtypes = [vp]
         L.lc_planner_destroy.restype = None
         L.lc_planner_roadmap_size.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
@@ -226,6 +229,14 @@ class Planner:
             self._h = C.c_void_p()
 
     __del__ = close
+
+    def clone(self):
+        """Independent planner with the same roadmap state (lc_planner_clone)."""
+        c = Planner.__new__(Planner)
+        c._w = self._w
+        c._h = C.c_void_p()
+        _ck(lib().lc_planner_clone(self._h, C.byref(c._h)))
+        return c
 
     def roadmap_size(self):
         v, e = C.c_int32(0), C.c_int32(0)
@@ -589,16 +600,25 @@ class DomainSim(Sim):
 class Batch:
     """Many independent small scenarios in one launch (pso_opt.py:236-267 simulate_set, in process)."""
 
-    def __init__(self, pos, goal, m_cv, m_f, max_duration, rng_state, radius=0.15, comm=True, device=0, order=None):
+    def __init__(self, pos, goal, m_cv, m_f, max_duration, rng_state, radius=0.15, comm=True, device=0, order=None, walls=None,
+                 wall_order=None):
+        """walls [W][4]: one wall layout shared by every scenario of the batch (replans are served by the host planner
+        between relaunches of the rollout kernel); order / wall_order as for Sim."""
         S, n = pos.shape[0], pos.shape[1]
         self.S, self.n = int(S), int(n)
+        self._walls = None if walls is None or len(walls) == 0 else np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+        nw = 0 if self._walls is None else len(self._walls)
+        if isinstance(order, str) and nw and wall_order is None:
+            wall_order = table_order(self.n, nw)[1]
+        self._wall_order = None if (wall_order is None or nw == 0) else np.ascontiguousarray(wall_order, np.int32)
         self._order = _order(order, self.n)
         self._keep = [np.ascontiguousarray(pos, np.float32), np.ascontiguousarray(goal, np.float32),
                       np.ascontiguousarray(m_cv, np.float32), np.ascontiguousarray(m_f, np.float32),
                       np.ascontiguousarray(np.broadcast_to(np.asarray(max_duration, np.float32), (S,))),
                       np.ascontiguousarray(np.broadcast_to(np.asarray(rng_state, np.uint32), (S,)))]
         assert self._keep[2].shape == (S, 3, 8) and self._keep[3].shape == (S, 2, 3)
-        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, 0 if comm else FLAG_NO_COMM, device, _p(self._order))
+        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, 0 if comm else FLAG_NO_COMM, device, _p(self._order),
+                       nw, _p(self._walls), _p(self._wall_order))
         h = C.c_void_p()
         self.h = None
         _ck(lib().lc_batch_create(C.byref(d), C.byref(h)))
@@ -652,6 +672,14 @@ class Batch:
                    pair_tests=np.zeros(S, np.int64))
         _ck(lib().lc_batch_get_diag(self.h, *[_p(out[k]) for k in ("partner", "neighbor_count", "overlap_pairs",
                                                                      "collision_hits", "pair_tests")]))
+        return out
+
+    def walled(self):
+        S, n = self.S, self.n
+        out = dict(n_plan=np.zeros((S, n), np.int32), lost_frames=np.zeros((S, n), np.int32), wall_hits=np.zeros(S, np.int64))
+        rp = C.c_int64(0)
+        _ck(lib().lc_batch_get_walled(self.h, _p(out["n_plan"]), _p(out["lost_frames"]), _p(out["wall_hits"]), C.byref(rp)))
+        out["replans"] = int(rp.value)
         return out
 
     def device_ms(self):

@@ -2,7 +2,7 @@
 //     <build>/bin/comm_norender <scene> --seed <u64> --data <dir>
 // Same argument grammar as enginee/src/main.cpp:53-69 + io.cpp:63-125 (options --help, --record u, --data dir,
 // --split n, --seed u; one positional `scene`; misuse -> message + usage on stderr, exit 1), same files:
-// reads <project>data/<dir>/comms.config (comm.cpp:74-131), writes <project>data/<dir>/comms.result (comm.cpp:136-142)
+// every catalogue scene, walled ones included; reads <project>data/<dir>/comms.config (comm.cpp:74-131), writes <project>data/<dir>/comms.result (comm.cpp:136-142)
 // and <project>data/<dir>/agent_paths.csv (demo.cpp:678-684; LEARN_COMMS_NO_PATHS=1 skips it and runs the rollout in one call).
 // The frame loop itself (main.cpp:98-150) runs on the GPU through the C ABI; there is no CPU fallback: without a CUDA
 // device the process exits 1 with the library's error text.  Build: tools/build_cli.sh (g++ + liblearncomms.so).
@@ -73,11 +73,13 @@ int main(int argc, char** argv) {
 
     // demo::init (scene catalogue) + Seeder::seed (main.cpp:69-70)
     std::vector<float> pos(2 * 4096), goal(2 * 4096);
+    std::vector<lc_rect> walls(64);
     float max_duration = 0.f;
     uint32_t rng = 0;
-    int n = lc_scene((uint32_t)scene, seed, pos.data(), goal.data(), 4096, &max_duration, &rng);
+    int32_t n_walls = 0;
+    int n = lc_scene_full((uint32_t)scene, seed, pos.data(), goal.data(), 4096, &max_duration, &rng, walls.data(), 64, &n_walls);
     if (n <= 0) {
-        fprintf(stderr, "scene %ld is not available on the GPU path (wall-free scenes 0, 1, 4, 5, 12 only)\n", scene);
+        fprintf(stderr, "scene %ld is not in the catalogue (0-18 and 900+k, demo.cpp:141-511)\n", scene);
         return EXIT_FAILURE;
     }
     float m_cv[24] = {0}, m_f[6] = {0};
@@ -95,9 +97,10 @@ int main(int argc, char** argv) {
     d.n = n; d.pos = pos.data(); d.goal = goal.data(); d.radius = 0.15f; d.max_duration = max_duration;
     d.rng_state = rng; d.m_cv = m_cv; d.m_f = m_f; d.flags = flags; d.device = 0;
     // the reference's component-table iteration order (quirk Q4): which RNG draw an agent gets, summation and Welford order
-    std::vector<int32_t> order((size_t)n);
-    if (lc_table_order(n, 0, order.data(), nullptr) != LC_OK) lib_error("lc_table_order");
+    std::vector<int32_t> order((size_t)n), wall_order((size_t)(n_walls > 0 ? n_walls : 1));
+    if (lc_table_order(n, n_walls, order.data(), wall_order.data()) != LC_OK) lib_error("lc_table_order");
     d.table_order = order.data();
+    d.n_walls = n_walls; d.walls = walls.data(); d.wall_order = wall_order.data();
     lc_sim* sim = nullptr;
     if (lc_create(&d, &sim) != LC_OK) lib_error("lc_create");
     int32_t frames = 0;
@@ -132,7 +135,12 @@ int main(int argc, char** argv) {
     int rc = lc_get_scores(sim, &avg_velocity, &group_time, &run_avg, &run_std, &total);
     if (rc != LC_OK && rc != LC_ERR_STATE) lib_error("lc_get_scores");
     fprintf(stderr, "\nFRAMES: %d\nNUM DONE: %d\n", frames, total);  // main.cpp:118-119, demo.cpp:686
-    printf("u:%f s:%f\n", run_avg, run_std);                           // last line of demo.cpp:662's log
+    {   // demo.cpp:662: one "t:%f u:%f s:%f" line per finisher, in the order the Welford update saw them
+        std::vector<float> log(3 * (size_t)(total > 0 ? total : 1));
+        int32_t k = 0;
+        if (lc_get_finish_log(sim, log.data(), total, &k) != LC_OK) lib_error("lc_get_finish_log");
+        for (int i = 0; i < k; ++i) printf("t:%f u:%f s:%f\n", log[3 * i], log[3 * i + 1], log[3 * i + 2]);
+    }
     if (lc_write_result((data_dir + "/comms.result").c_str(), avg_velocity, group_time) != LC_OK) {
         fprintf(stderr, "cannot write %s/comms.result\n", data_dir.c_str());
         return EXIT_FAILURE;

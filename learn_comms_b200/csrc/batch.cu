@@ -12,10 +12,13 @@
 // sum, the comm-partner arg-max (comm.cpp:201-220) and the push-out order need no sorting.
 #include "../../include/learn_comms.h"
 #include "lc_math.cuh"
+#include "walls.cuh"
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
 #include <math_constants.h>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -26,6 +29,9 @@ constexpr int MAX_N = 256;
 constexpr int MAX_WARPS = MAX_N / 32;
 constexpr int MAX_NEAR = 8;
 
+constexpr int WP_CAP = 32;      // waypoints per agent (walled scenarios)
+constexpr int MAX_WALLS = 64;   // walls of the layout a batch shares (the catalogue's largest scene has 60)
+
 struct ScenarioCtl {
     uint32_t frame;
     int finished;
@@ -35,6 +41,12 @@ struct ScenarioCtl {
     unsigned long long overlap2;   // ordered overlapping pairs at frame start, summed over all frames
     unsigned long long coll_hits;  // ordered (q, bv) hits of the collision pass, summed over all frames
     unsigned long long pair_tests; // TTC pair evaluations (throughput accounting)
+    // walled scenarios: the block stops in front of a frame whose replan gate fired (ai.cpp:152-168) and waits for the
+    // host planner; wr1 / wr2 = the two lowest requesting agents, req = where they replan from
+    int pause, served, wr1, wr2;
+    float req[4];
+    unsigned long long draws;      // minstd_rand0 draws consumed so far (plan-less agents do not draw, LMP.cpp:267-270)
+    unsigned long long wall_hits;
 };
 
 struct Arrays {
@@ -51,6 +63,17 @@ struct Arrays {
     float* m_f;      // [S][6]
     float* max_duration;  // [S]
     ScenarioCtl* ctl;     // [S]
+    // walled scenarios (one wall layout per batch); per-agent arrays [S][n]
+    int n_walls, n_bvh;
+    const lcw::Wall* walls;      // [n_walls] creation order
+    const int* wall_order;       // [n_walls] statics order (LMP.cpp:307)
+    const lc_bvh_node* bvh;      // [n_bvh] static BVH, pre-order (lc_static_bvh)
+    float2* plan;                // [S][n][WP_CAP]  Agent::plan
+    int* n_plan;                 // Agent::plan->size(); 0 = no plan
+    int* wnd;                    // Agent::num_done (waypoints passed)
+    int* lost;                   // Agent::lost_frames; -1 = "replanned by the host for the coming frame"
+    uint32_t* rng0;              // [S] stream state before the scenario's first draw
+    uint32_t* frame_target;      // [S] lc_batch_run stops a scenario in front of this frame
 };
 
 struct Consts {
@@ -85,6 +108,17 @@ __device__ __forceinline__ void fold_avg_velocity(ScenarioCtl& c, const unsigned
     c.avg_velocity = poisoned ? CUDART_NAN_F : sp;
 }
 
+__device__ __forceinline__ uint32_t lcg_pow_dev(unsigned long long e) {  // 16807^e mod (2^31 - 1)
+    uint32_t r = 1u, a = 16807u;
+    while (e) {
+        if (e & 1ull) r = lcg_mul(r, a);
+        a = lcg_mul(a, a);
+        e >>= 1;
+    }
+    return r;
+}
+
+template <bool WALLS>
 __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int max_frames) {
     extern __shared__ float4 s_dyn[];
     const int n = A.n;
@@ -102,6 +136,10 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
     __shared__ unsigned s_ndm[MAX_WARPS], s_nfm[MAX_WARPS];
     __shared__ float s_spd[MAX_WARPS];
     __shared__ ScenarioCtl s_ctl;
+    __shared__ lcw::Wall s_walls[WALLS ? MAX_WALLS : 1];
+    __shared__ int s_worder[WALLS ? MAX_WALLS : 1];
+    __shared__ lc_bvh_node s_bvh[WALLS ? 2 * MAX_WALLS : 1];
+    __shared__ unsigned s_req[MAX_WARPS], s_plm[MAX_WARPS];  // per-warp ballots: needs a replan / has a plan
 
     const int sc = blockIdx.x;
     const int i = threadIdx.x, lane = i & 31, wid = i >> 5, nwarps = nt >> 5;
@@ -130,17 +168,32 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
     if (i >= 24 && i < 30) s_w[i] = A.m_f[(size_t)sc * 6 + (i - 24)];
     if (i == 0) s_ctl = A.ctl[sc];
     if (i < MAX_WARPS) { s_ndm[i] = 0u; s_nfm[i] = 0u; s_spd[i] = 0.f; }
+    // walled scenario: waypoint list (global, by agent), counters in registers, the shared wall layout in shared memory
+    int np_ = 0, nd = 0, lost = 0;
+    const float2* myplan = nullptr;
+    if constexpr (WALLS) {
+        if (valid) { np_ = A.n_plan[g]; nd = A.wnd[g]; lost = A.lost[g]; }
+        myplan = A.plan + g * WP_CAP;
+        for (int k = i; k < A.n_walls; k += nt) { s_walls[k] = A.walls[k]; s_worder[k] = A.wall_order[k]; }
+        for (int k = i; k < A.n_bvh; k += nt) s_bvh[k] = A.bvh[k];
+    }
     __syncthreads();
     const float max_duration = A.max_duration[sc];
     const uint32_t frame0 = s_ctl.frame;
     bool finished = s_ctl.finished != 0;
+    bool served = WALLS && s_ctl.served != 0;
+    int paused = 0, wr1 = -1, wr2 = -1;
+    unsigned long long draws = s_ctl.draws, wall_hits = 0ull;
+    const uint32_t rng0 = WALLS ? A.rng0[sc] : 0u;
+    const uint32_t target = WALLS ? A.frame_target[sc] : 0u;
     const bool comm = !(K.flags & LC_FLAG_NO_COMM);
     unsigned long long overlap2 = 0ull, coll_hits = 0ull, pair_tests = 0ull;
     int err = 0;
     int executed = 0;
 
-    for (int it = 0; it < max_frames && !finished; ++it) {
+    for (int it = 0; (WALLS || it < max_frames) && !finished; ++it) {
         const uint32_t frame = frame0 + (uint32_t)it + 1u;
+        if (WALLS && frame0 + (uint32_t)it >= target) break;
         const int par = it & 1;
         const float4* __restrict__ pvA = s_pv0;
         const float4* cA = par ? s_c1 : s_c0;
@@ -149,12 +202,55 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
         const float fake_time = __fmul_rn(LC_DT, (float)frame);
         const bool timeout = fake_time > max_duration;
 
+        // ---- walled: the replan gate of this frame (ai.cpp:152-163), BEFORE anything of the frame has side effects.
+        // The two lowest requesting agents (= the first two in table order, ai.cpp:151-152,164) are planned by the host
+        // (GMP::plan_one needs the roadmap); the block stops here and is resumed by the next launch. ----
+        int lost_next = 0;
+        if constexpr (WALLS) {
+            bool need = false;
+            if (valid) {
+                if (lost < 0) {
+                    lost_next = 0;  // replanned for this frame: lost_frames = 0 (ai.cpp:167), no second request
+                } else {
+                    const bool has = np_ > 0, done = has && nd == np_;
+                    const float gd0 = len2(__fsub_rn(goal.x, px), __fsub_rn(goal.y, py));
+                    bool visible = false;
+                    if (has && nd < np_) {
+                        const float2 t = myplan[nd];
+                        visible = true;
+                        for (int k = 0; k < A.n_walls && visible; ++k) visible = lcw::cspace_line_of_sight(s_walls[k], K.r, px, py, t.x, t.y);
+                    }
+                    lost_next = visible ? 0 : lost + 1;
+                    need = !has || (done && gd0 > 1.f) || (!done && !visible && lost_next >= 360);
+                }
+            }
+            const unsigned m_req = __ballot_sync(0xffffffffu, need);
+            const unsigned m_pl = __ballot_sync(0xffffffffu, valid && np_ > 0);
+            if (lane == 0) { s_req[wid] = m_req; s_plm[wid] = m_pl; }
+            __syncthreads();  // B0
+            if (!served) {
+                wr1 = wr2 = -1;
+                for (int w = 0; w < nwarps && wr2 < 0; ++w)
+                    for (unsigned m = s_req[w]; m && wr2 < 0; m &= m - 1u) {
+                        const int id = 32 * w + __ffs(m) - 1;
+                        if (wr1 < 0) wr1 = id; else wr2 = id;
+                    }
+                if (wr1 >= 0) {
+                    if (i == wr1) { s_ctl.req[0] = px; s_ctl.req[1] = py; }
+                    if (i == wr2) { s_ctl.req[2] = px; s_ctl.req[3] = py; }
+                    paused = 1;
+                    break;
+                }
+            }
+            served = false;
+        }
+
         // ---- S0: demo::run (demo.cpp:665-702), block-wide facts through per-warp ballots ----
         const bool done_before = mt.x & 1;
         const float gd = len2(__fsub_rn(goal.x, px), __fsub_rn(goal.y, py));  // ai.cpp:154
         const bool f_new = valid && done_before && !(mt.x & 2);
         const bool f_nd = valid && !done_before;
-        const bool f_rp = valid && done_before && gd > 1.f;                   // ai.cpp:161-163 (wall-free)
+        const bool f_rp = !WALLS && valid && done_before && gd > 1.f;         // ai.cpp:161-163 (wall-free; walled: the gate above)
         const unsigned m_new = __ballot_sync(0xffffffffu, f_new);
         const unsigned m_nd = __ballot_sync(0xffffffffu, f_nd);
         const unsigned m_rp = __ballot_sync(0xffffffffu, f_rp);
@@ -267,6 +363,15 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
                     slow(j);
                 }
             }
+            if constexpr (WALLS) {  // LMP.cpp:306-319: the statics loop, after the agents, in the BoundVolume* table's order
+                for (int k = 0; k < A.n_walls; ++k) {
+                    float fx, fy;
+                    if (lcw::wall_force(px, py, K.r, vx, vy, s_walls[s_worder[k]], fx, fy)) {
+                        ttcFx = __fadd_rn(ttcFx, fx);
+                        ttcFy = __fadd_rn(ttcFy, fy);
+                    }
+                }
+            }
             last_cnt = cnt;
             overlap2 += (unsigned long long)n_overlap;
             pair_tests += (unsigned long long)(n - 1);
@@ -327,23 +432,42 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
 
             // ---- S2: ai::update_agents (ai.cpp:153-172) ----
             c4.w = gd;
-            int num_done = mt.x & 1;
-            if (f_rp && rp_below < 2) num_done = 0;  // replan gate: the first two in table order (ai.cpp:151-168) -> GMP::plan_one
-            // LMP::lookahead (LMP.cpp:84-113) with plan = [final_goal]
-            if (num_done < 1) {
-                const float ox = __fsub_rn(px, goal.x), oy = __fsub_rn(py, goal.y);
-                if (dot2(ox, oy, ox, oy) < 1.f) num_done = 1; else lgoal = goal;
+            int num_done;         // 1 = Agent::done() after this frame's lookahead
+            bool planned = true;  // Agent::has_plan()
+            float eps = 0.f;
+            if constexpr (!WALLS) {
+                num_done = mt.x & 1;
+                if (f_rp && rp_below < 2) num_done = 0;  // replan gate: the first two in table order (ai.cpp:151-168) -> GMP::plan_one
+                // LMP::lookahead (LMP.cpp:84-113) with plan = [final_goal]
+                if (num_done < 1) {
+                    const float ox = __fsub_rn(px, goal.x), oy = __fsub_rn(py, goal.y);
+                    if (dot2(ox, oy, ox, oy) < 1.f) num_done = 1; else lgoal = goal;
+                } else {
+                    lgoal = goal;
+                }
+                // LMP.cpp:261-273: one draw for both components
+                eps = lcg_uniform((uint32_t)mt.y, -.01f, .01f);
+                mt.y = (int)lcg_mul((uint32_t)mt.y, K.lcg_stride);
             } else {
-                lgoal = goal;
+                lost = lost_next;  // ai.cpp:161
+                planned = np_ > 0;
+                if (planned) {
+                    lcw::lookahead(s_walls, A.n_walls, K.r, px, py, reinterpret_cast<const float*>(myplan), np_, nd, lgoal.x, lgoal.y);
+                    // this agent draws element draws + (planned agents before it in the table) + 1 of the scenario's stream
+                    int rank = __popc(s_plm[wid] & ((1u << lane) - 1u));
+                    for (int w = 0; w < wid; ++w) rank += __popc(s_plm[w]);
+                    eps = lcg_uniform(lcg_mul(rng0, lcg_pow_dev(draws + (unsigned long long)rank + 1ull)), -.01f, .01f);
+                } else {
+                    lgoal = make_float2(px, py);  // LMP.cpp:267-270: no plan, no draw, goal_vel = 0
+                }
+                num_done = planned && nd == np_;
             }
             mt.x = (mt.x & ~1) | num_done;
             not_done_after = num_done == 0;
-            // LMP.cpp:261-273: one draw for both components
-            const float eps = lcg_uniform((uint32_t)mt.y, -.01f, .01f);
-            mt.y = (int)lcg_mul((uint32_t)mt.y, K.lcg_stride);
             const float dgx = __fsub_rn(__fadd_rn(lgoal.x, eps), px), dgy = __fsub_rn(__fadd_rn(lgoal.y, eps), py);
             const float dl = glm_max(1.0f, len2(dgx, dgy));
-            const float gvx = __fmul_rn(1.0f, __fdiv_rn(dgx, dl)), gvy = __fmul_rn(1.0f, __fdiv_rn(dgy, dl));
+            float gvx = __fmul_rn(1.0f, __fdiv_rn(dgx, dl)), gvy = __fmul_rn(1.0f, __fdiv_rn(dgy, dl));
+            if (WALLS && !planned) gvx = gvy = 0.f;
             const float goalFx = __fmul_rn(2.0f, __fsub_rn(gvx, vx)), goalFy = __fmul_rn(2.0f, __fsub_rn(gvy, vy));
             forcex = __fadd_rn(forcex, __fadd_rn(goalFx, ttcFx));  // ai.cpp:172
             forcey = __fadd_rn(forcey, __fadd_rn(goalFy, ttcFy));
@@ -385,6 +509,27 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
             }
             coll_hits += (unsigned long long)cnt;
         }
+        if constexpr (WALLS) {
+            // physics.cpp:60,67-69: static_bvh->query at the integrated position, pushed out after the agent hits;
+            // BVH::query_(Circ*) (BVH.cpp:106-138): depth first, left before right, single-point inner test (quirk Q8)
+            if (valid && A.n_bvh > 0) {
+                int stack[32], sp = 0;
+                stack[sp++] = 0;
+                while (sp > 0) {
+                    const lc_bvh_node nd_ = s_bvh[stack[--sp]];
+                    float nx, ny;
+                    if (nd_.right < 0) {
+                        if (lcw::circ_wall_hit(npx, npy, K.r, s_walls[nd_.left], nx, ny)) { push_away(fx_, fy_, vfh.x, vfh.y, nx, ny); ++wall_hits; }
+                    } else if (lcw::circ_wall_hit(npx, npy, K.r, lcw::Wall{nd_.ox, nd_.oy, nd_.w, nd_.h}, nx, ny) && sp + 2 <= 32) {
+                        stack[sp++] = nd_.right;
+                        stack[sp++] = nd_.left;
+                    }
+                }
+            }
+            int npl = 0;  // draws this frame consumed = agents with a plan (block-uniform)
+            for (int w = 0; w < nwarps; ++w) npl += __popc(s_plm[w]);
+            draws += (unsigned long long)npl;
+        }
         me = make_float4(fx_, fy_, nvx, nvy);
         if (valid) {  // read again only after the next B1 (or the final barrier)
             s_pv0[i] = me;
@@ -401,6 +546,20 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
         ++executed;
     }
     __syncthreads();
+    if constexpr (WALLS) {
+        if (valid) {
+            A.wnd[g] = nd;
+            A.lost[g] = lost;
+            if (wall_hits) atomicAdd(&A.ctl[sc].wall_hits, wall_hits);
+        }
+        if (i == 0) {
+            A.ctl[sc].pause = paused;
+            A.ctl[sc].served = 0;
+            A.ctl[sc].wr1 = wr1; A.ctl[sc].wr2 = wr2;
+            A.ctl[sc].req[0] = s_ctl.req[0]; A.ctl[sc].req[1] = s_ctl.req[1]; A.ctl[sc].req[2] = s_ctl.req[2]; A.ctl[sc].req[3] = s_ctl.req[3];
+            A.ctl[sc].draws = draws;
+        }
+    }
     if (i == 0) {
         if (executed) fold_avg_velocity(s_ctl, s_ndm, s_spd, s_nfm, nwarps);
         A.ctl[sc].frame = s_ctl.frame;
@@ -425,6 +584,22 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
         atomicAdd(&A.ctl[sc].pair_tests, pair_tests);
         if (err) atomicCAS(&A.ctl[sc].error, 0, err);
     }
+}
+
+// Replans served by the host (GMP::plan_one, GMP.cpp:91-110): new waypoint list, num_done = 0, "replanned" marker for
+// lost_frames; the scenario may run again.
+struct ReplanUpdate { int scenario, agent, n_waypoints, pad; float wp[2 * WP_CAP]; };
+__global__ void k_batch_apply_replans(Arrays A, const ReplanUpdate* up, int count) {
+    const int u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= count) return;
+    const ReplanUpdate& r = up[u];
+    const size_t g = (size_t)r.scenario * A.n + r.agent;
+    for (int k = 0; k < r.n_waypoints; ++k) A.plan[g * WP_CAP + k] = make_float2(r.wp[2 * k], r.wp[2 * k + 1]);
+    A.n_plan[g] = r.n_waypoints;
+    A.wnd[g] = 0;
+    A.lost[g] = -1;
+    A.ctl[r.scenario].served = 1;
+    A.ctl[r.scenario].pause = 0;
 }
 
 }  // namespace lcbatch
@@ -460,9 +635,24 @@ struct lc_batch {
     std::vector<void*> allocs;
     // host copies of the initial state (lc_batch_reset) and a pinned mirror of the per-scenario control blocks
     std::vector<float4> h_pv, h_c4;
-    std::vector<float2> h_goal, h_facing;
+    std::vector<float2> h_goal2, h_facing;
     std::vector<int4> h_meta;
     lcbatch::ScenarioCtl* h_ctl = nullptr;
+    // walled batches: one wall layout; scenarios with identical start / goal tables form a group that shares its initial
+    // plans and a template planner (state after ai::init's planning loop); a scenario gets its own copy of the roadmap at
+    // its first replan (the reference's roadmap is per process and stateful)
+    int n_walls = 0;
+    std::vector<lc_rect> walls;
+    std::vector<int> group_of;            // [S]
+    std::vector<lc_planner*> tmpl;        // [G]
+    std::vector<lc_planner*> planner;     // [S] lazily cloned
+    std::vector<float> plan0;             // [G][n][WP_CAP][2]
+    std::vector<int> nplan0;              // [G][n]
+    std::vector<float> h_goal;            // [S][n][2] by engine index
+    std::vector<uint32_t> h_rng0;         // [S]
+    lcbatch::ReplanUpdate* d_updates = nullptr;
+    size_t updates_cap = 0;
+    long long replans = 0;
     std::vector<int> order;  // lc_batch_desc::table_order: order[i] = caller's agent index of engine agent i (empty = identity)
     // index of engine agent g (scenario-major) in the caller's tables
     size_t ext(size_t g) const {
@@ -492,13 +682,31 @@ static int batch_upload_initial(lc_batch* b) {
     const size_t N = (size_t)b->a.S * b->a.n;
     BCK(cudaMemcpyAsync(b->a.pv, b->h_pv.data(), sizeof(float4) * N, cudaMemcpyHostToDevice, b->st));
     BCK(cudaMemsetAsync(b->a.vfh, 0, sizeof(float2) * N, b->st));
-    BCK(cudaMemcpyAsync(b->a.goal, b->h_goal.data(), sizeof(float2) * N, cudaMemcpyHostToDevice, b->st));
+    BCK(cudaMemcpyAsync(b->a.goal, b->h_goal2.data(), sizeof(float2) * N, cudaMemcpyHostToDevice, b->st));
     BCK(cudaMemsetAsync(b->a.lgoal, 0, sizeof(float2) * N, b->st));
     BCK(cudaMemcpyAsync(b->a.facing, b->h_facing.data(), sizeof(float2) * N, cudaMemcpyHostToDevice, b->st));
     BCK(cudaMemcpyAsync(b->a.c4, b->h_c4.data(), sizeof(float4) * N, cudaMemcpyHostToDevice, b->st));
     BCK(cudaMemcpyAsync(b->a.meta, b->h_meta.data(), sizeof(int4) * N, cudaMemcpyHostToDevice, b->st));
     BCK(cudaMemsetAsync(b->a.nbr_cnt, 0, sizeof(int) * N, b->st));
     BCK(cudaMemsetAsync(b->a.ctl, 0, sizeof(lcbatch::ScenarioCtl) * (size_t)b->a.S, b->st));
+    if (b->n_walls > 0) {  // initial plans of every scenario = its group's; counters at zero; roadmaps back to the templates
+        const size_t n = (size_t)b->a.n;
+        std::vector<float> plan((size_t)b->a.S * n * lcbatch::WP_CAP * 2);
+        std::vector<int> nplan((size_t)b->a.S * n);
+        for (int s = 0; s < b->a.S; ++s) {
+            const size_t gi = (size_t)b->group_of[s];
+            std::copy(b->plan0.begin() + gi * n * lcbatch::WP_CAP * 2, b->plan0.begin() + (gi + 1) * n * lcbatch::WP_CAP * 2,
+                      plan.begin() + (size_t)s * n * lcbatch::WP_CAP * 2);
+            std::copy(b->nplan0.begin() + gi * n, b->nplan0.begin() + (gi + 1) * n, nplan.begin() + (size_t)s * n);
+        }
+        BCK(cudaMemcpyAsync(b->a.plan, plan.data(), sizeof(float) * plan.size(), cudaMemcpyHostToDevice, b->st));
+        BCK(cudaMemcpyAsync(b->a.n_plan, nplan.data(), sizeof(int) * nplan.size(), cudaMemcpyHostToDevice, b->st));
+        BCK(cudaMemsetAsync(b->a.wnd, 0, sizeof(int) * N, b->st));
+        BCK(cudaMemsetAsync(b->a.lost, 0, sizeof(int) * N, b->st));
+        BCK(cudaStreamSynchronize(b->st));
+        for (lc_planner*& p : b->planner) { if (p) lc_planner_destroy(p); p = nullptr; }
+        b->replans = 0;
+    }
     BCK(cudaStreamSynchronize(b->st));
     return LC_OK;
 }
@@ -510,6 +718,9 @@ void lc_batch_destroy(lc_batch* b) {
     cudaSetDevice(b->device);
     if (b->st) cudaStreamSynchronize(b->st);
     for (void* p : b->allocs) cudaFree(p);
+    for (lc_planner* p : b->planner) if (p) lc_planner_destroy(p);
+    for (lc_planner* p : b->tmpl) if (p) lc_planner_destroy(p);
+    if (b->d_updates) cudaFree(b->d_updates);
     if (b->h_ctl) cudaFreeHost(b->h_ctl);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
@@ -525,6 +736,8 @@ int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
         return bfail(LC_ERR_ARG, "lc_batch_create: n_agents must be in [2, %d] (use lc_create for larger crowds)", lcbatch::MAX_N);
     if (!d->pos || !d->goal || !d->max_duration || !d->rng_state) return bfail(LC_ERR_ARG, "lc_batch_create: pos, goal, max_duration and rng_state are required");
     if (!(d->radius > 0.f)) return bfail(LC_ERR_ARG, "lc_batch_create: radius must be positive");
+    if (d->n_walls < 0 || d->n_walls > lcbatch::MAX_WALLS || (d->n_walls > 0 && !d->walls))
+        return bfail(LC_ERR_ARG, "lc_batch_create: n_walls must be in [0, %d] with the rectangles given", lcbatch::MAX_WALLS);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
@@ -569,8 +782,63 @@ int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
     b->k.near_c = reach * reach - b->k.RR;
     b->k.lcg_stride = b_lcg_pow(16807u, (uint64_t)n);
     b->k.flags = d->flags;
+    // walled batch (ai::init, ai.cpp:24-129): static BVH, one planner per group of identical scenarios, initial plans in
+    // table order (engine index = table position), min_time = plan length minus the untimed last metre
+    std::vector<float> g_min_time;  // [G][n]
+    if (d->n_walls > 0) {
+        const int nw = b->n_walls = d->n_walls;
+        b->walls.assign(d->walls, d->walls + nw);
+        std::vector<int32_t> worder((size_t)nw);
+        std::vector<char> seen((size_t)nw, 0);
+        for (int k = 0; k < nw; ++k) {
+            worder[k] = d->wall_order ? d->wall_order[k] : k;
+            if (worder[k] < 0 || worder[k] >= nw || seen[worder[k]]) { lc_batch_destroy(b); return bfail(LC_ERR_ARG, "lc_batch_create: wall_order is not a permutation"); }
+            seen[worder[k]] = 1;
+        }
+        std::vector<lc_bvh_node> bvh((size_t)2 * nw);
+        int32_t n_bvh = 0;
+        if (lc_static_bvh(nw, d->walls, worder.data(), bvh.data(), (int32_t)bvh.size(), &n_bvh) != LC_OK) { lc_batch_destroy(b); return bfail(LC_ERR_ARG, "lc_batch_create: static BVH construction failed"); }
+        b->group_of.assign((size_t)S, 0);
+        b->planner.assign((size_t)S, nullptr);
+        std::map<std::string, int> groups;
+        for (int s = 0; s < S; ++s) {
+            std::string key((const char*)(d->pos + (size_t)2 * s * n), sizeof(float) * 2 * (size_t)n);
+            key.append((const char*)(d->goal + (size_t)2 * s * n), sizeof(float) * 2 * (size_t)n);
+            auto it = groups.find(key);
+            if (it != groups.end()) { b->group_of[s] = it->second; continue; }
+            const int gi = (int)b->tmpl.size();
+            groups.emplace(std::move(key), gi);
+            b->group_of[s] = gi;
+            lc_planner* pl = nullptr;
+            if (lc_planner_create(nw, d->walls, d->radius, &pl) != LC_OK) { lc_batch_destroy(b); return LC_ERR_CAPACITY; }
+            b->tmpl.push_back(pl);
+            b->plan0.resize((size_t)(gi + 1) * n * lcbatch::WP_CAP * 2, 0.f);
+            b->nplan0.resize((size_t)(gi + 1) * n, 0);
+            g_min_time.resize((size_t)(gi + 1) * n, 0.f);
+            for (int i = 0; i < n; ++i) {
+                const size_t e = b->ext((size_t)s * n + i);
+                int32_t k = 0;
+                const int rc = lc_planner_plan(pl, d->pos + 2 * e, d->goal + 2 * e, lcbatch::WP_CAP,
+                                               &b->plan0[((size_t)gi * n + i) * lcbatch::WP_CAP * 2], &k, &g_min_time[(size_t)gi * n + i]);
+                if (rc) { lc_batch_destroy(b); return bfail(rc, "lc_batch_create: the plan of agent %d of scenario %d has %d waypoints (capacity %d)", i, s, k, lcbatch::WP_CAP); }
+                b->nplan0[(size_t)gi * n + i] = k;
+            }
+        }
+        lcw::Wall* dw = nullptr; int* dwo = nullptr; lc_bvh_node* dbvh = nullptr;
+        BCKB(balloc(b, &dw, (size_t)nw)); BCKB(balloc(b, &dwo, (size_t)nw)); BCKB(balloc(b, &dbvh, (size_t)n_bvh));
+        static_assert(sizeof(lcw::Wall) == sizeof(lc_rect), "wall layout shared with the C ABI");
+        BCKB(cudaMemcpy(dw, d->walls, sizeof(lc_rect) * (size_t)nw, cudaMemcpyHostToDevice));
+        BCKB(cudaMemcpy(dwo, worder.data(), sizeof(int) * (size_t)nw, cudaMemcpyHostToDevice));
+        BCKB(cudaMemcpy(dbvh, bvh.data(), sizeof(lc_bvh_node) * (size_t)n_bvh, cudaMemcpyHostToDevice));
+        b->a.n_walls = nw; b->a.n_bvh = n_bvh; b->a.walls = dw; b->a.wall_order = dwo; b->a.bvh = dbvh;
+        BCKB(balloc(b, &b->a.plan, N * lcbatch::WP_CAP)); BCKB(balloc(b, &b->a.n_plan, N)); BCKB(balloc(b, &b->a.wnd, N));
+        BCKB(balloc(b, &b->a.lost, N)); BCKB(balloc(b, &b->a.rng0, (size_t)S)); BCKB(balloc(b, &b->a.frame_target, (size_t)S));
+        b->h_rng0.assign(d->rng_state, d->rng_state + S);
+        BCKB(cudaMemcpy(b->a.rng0, d->rng_state, sizeof(uint32_t) * (size_t)S, cudaMemcpyHostToDevice));
+        b->h_goal.resize((size_t)2 * N);
+    }
     // initial component values: demo.cpp:563-581 create_robo, ai.cpp:107-127 ai::init, physics.cpp:15-21 prewarm
-    b->h_pv.resize(N); b->h_c4.resize(N); b->h_goal.resize(N); b->h_facing.resize(N); b->h_meta.resize(N);
+    b->h_pv.resize(N); b->h_c4.resize(N); b->h_goal2.resize(N); b->h_facing.resize(N); b->h_meta.resize(N);
     for (int s = 0; s < S; ++s) {
         uint32_t x = d->rng_state[s];
         for (int i = 0; i < n; ++i) {
@@ -582,7 +850,11 @@ int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
             mtime += len;
             x = lcm::lcg_mul(x, 16807u);                 // agent i draws element (frame-1)*n + i + 1 of the scenario's stream
             b->h_pv[g] = make_float4(px, py, 0.f, 0.f);
-            b->h_goal[g] = make_float2(gx, gy);
+            b->h_goal2[g] = make_float2(gx, gy);
+            if (b->n_walls > 0) {
+                b->h_goal[2 * g] = gx; b->h_goal[2 * g + 1] = gy;
+                mtime = g_min_time[(size_t)b->group_of[s] * n + i];  // length of the planned path instead of the bee line
+            }
             b->h_facing[g] = make_float2(dx, dy);        // un-normalised (demo.cpp:580)
             b->h_c4[g] = make_float4(0.f, 0.f, 0.f, len);
             int mbits;
@@ -620,14 +892,71 @@ int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float
     if (max_frames < 0) return bfail(LC_ERR_ARG, "lc_batch_run: max_frames < 0");
     const int nt = (b->a.n + 31) & ~31;
     const size_t smem = sizeof(float4) * 5 * nt + sizeof(int) * lcbatch::MAX_NEAR * nt;
-    BCK(cudaEventRecord(b->ev0, b->st));
-    lcbatch::k_batch_rollout<<<b->a.S, nt, smem, b->st>>>(b->a, b->k, max_frames);
-    BCK(cudaEventRecord(b->ev1, b->st));
-    b->launches += 1;
-    BCK(cudaMemcpyAsync(b->h_ctl, b->a.ctl, sizeof(lcbatch::ScenarioCtl) * (size_t)b->a.S, cudaMemcpyDeviceToHost, b->st));
-    BCK(cudaStreamSynchronize(b->st));
-    BCK(cudaGetLastError());
-    BCK(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
+    const int S = b->a.S, n = b->a.n;
+    if (b->n_walls == 0) {
+        BCK(cudaEventRecord(b->ev0, b->st));
+        lcbatch::k_batch_rollout<false><<<S, nt, smem, b->st>>>(b->a, b->k, max_frames);
+        BCK(cudaEventRecord(b->ev1, b->st));
+        b->launches += 1;
+        BCK(cudaMemcpyAsync(b->h_ctl, b->a.ctl, sizeof(lcbatch::ScenarioCtl) * (size_t)S, cudaMemcpyDeviceToHost, b->st));
+        BCK(cudaStreamSynchronize(b->st));
+        BCK(cudaGetLastError());
+        BCK(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
+    } else {
+        // Walled batch: every block runs until its scenario is done, reaches its frame budget, or stops in front of a frame
+        // whose replan gate fired; the host plans for the waiting scenarios (each on its own copy of the roadmap, created at
+        // its first replan) and launches again.  Device time = sum over the launches.
+        BCK(cudaMemcpyAsync(b->h_ctl, b->a.ctl, sizeof(lcbatch::ScenarioCtl) * (size_t)S, cudaMemcpyDeviceToHost, b->st));
+        BCK(cudaStreamSynchronize(b->st));
+        std::vector<uint32_t> target((size_t)S);
+        for (int s = 0; s < S; ++s) {
+            const uint64_t t = (uint64_t)b->h_ctl[s].frame + (uint64_t)max_frames;
+            target[s] = t > 0xffffffffull ? 0xffffffffu : (uint32_t)t;
+        }
+        BCK(cudaMemcpyAsync(b->a.frame_target, target.data(), sizeof(uint32_t) * (size_t)S, cudaMemcpyHostToDevice, b->st));
+        b->last_ms = 0.f;
+        std::vector<lcbatch::ReplanUpdate> ups;
+        for (int round = 0;; ++round) {
+            BCK(cudaEventRecord(b->ev0, b->st));
+            lcbatch::k_batch_rollout<true><<<S, nt, smem, b->st>>>(b->a, b->k, max_frames);
+            BCK(cudaEventRecord(b->ev1, b->st));
+            b->launches += 1;
+            BCK(cudaMemcpyAsync(b->h_ctl, b->a.ctl, sizeof(lcbatch::ScenarioCtl) * (size_t)S, cudaMemcpyDeviceToHost, b->st));
+            BCK(cudaStreamSynchronize(b->st));
+            BCK(cudaGetLastError());
+            float ms = 0.f;
+            BCK(cudaEventElapsedTime(&ms, b->ev0, b->ev1));
+            b->last_ms += ms;
+            ups.clear();
+            for (int s = 0; s < S; ++s) {
+                const lcbatch::ScenarioCtl& c = b->h_ctl[s];
+                if (!c.pause || c.finished || c.frame >= target[s]) continue;
+                if (!b->planner[s] && lc_planner_clone(b->tmpl[(size_t)b->group_of[s]], &b->planner[s]) != LC_OK) return LC_ERR_CAPACITY;
+                const int ids[2] = {c.wr1, c.wr2};
+                for (int q = 0; q < 2; ++q) {
+                    if (ids[q] < 0 || ids[q] >= n) continue;
+                    lcbatch::ReplanUpdate u;
+                    u.scenario = s; u.agent = ids[q]; u.pad = 0;
+                    int32_t k = 0;
+                    const int rc = lc_planner_plan(b->planner[s], &c.req[2 * q], &b->h_goal[2 * ((size_t)s * n + ids[q])], lcbatch::WP_CAP, u.wp, &k, nullptr);
+                    if (rc) return bfail(rc, "lc_batch_run: a replan of scenario %d produced %d waypoints (capacity %d)", s, k, lcbatch::WP_CAP);
+                    u.n_waypoints = k;
+                    ups.push_back(u);
+                }
+            }
+            if (ups.empty()) break;
+            b->replans += (long long)ups.size();
+            if (ups.size() > b->updates_cap) {
+                if (b->d_updates) cudaFree(b->d_updates);
+                b->updates_cap = ups.size() * 2;
+                BCK(cudaMalloc((void**)&b->d_updates, sizeof(lcbatch::ReplanUpdate) * b->updates_cap));
+            }
+            BCK(cudaMemcpyAsync(b->d_updates, ups.data(), sizeof(lcbatch::ReplanUpdate) * ups.size(), cudaMemcpyHostToDevice, b->st));
+            lcbatch::k_batch_apply_replans<<<(unsigned)((ups.size() + 127) / 128), 128, 0, b->st>>>(b->a, b->d_updates, (int)ups.size());
+            b->launches += 1;
+            BCK(cudaStreamSynchronize(b->st));  // `ups` is the copy source
+        }
+    }
     int first_err = 0, first_err_s = -1;
     for (int s = 0; s < b->a.S; ++s) {
         const lcbatch::ScenarioCtl& c = b->h_ctl[s];
@@ -685,6 +1014,11 @@ int32_t lc_batch_get_state(lc_batch* b, float* pos, float* vel, float* vfh, floa
     if (num_done) {
         BCK(cudaMemcpy(mt.data(), b->a.meta, sizeof(int4) * N, cudaMemcpyDeviceToHost));
         for (size_t g = 0; g < N; ++g) num_done[b->ext(g)] = mt[g].x & 1;
+        if (b->n_walls > 0) {  // walled: Agent::num_done counts the waypoints passed
+            std::vector<int> wnd(N);
+            BCK(cudaMemcpy(wnd.data(), b->a.wnd, sizeof(int) * N, cudaMemcpyDeviceToHost));
+            for (size_t g = 0; g < N; ++g) num_done[b->ext(g)] = wnd[g];
+        }
     }
     return LC_OK;
 }
@@ -713,6 +1047,26 @@ int32_t lc_batch_get_diag(lc_batch* b, int32_t* partner, int32_t* neighbor_count
         if (collision_hits) collision_hits[s] = (int64_t)b->h_ctl[s].coll_hits;
         if (pair_tests) pair_tests[s] = (int64_t)b->h_ctl[s].pair_tests;
     }
+    return LC_OK;
+}
+
+int32_t lc_batch_get_walled(lc_batch* b, int32_t* n_plan, int32_t* lost_frames, int64_t* wall_hits, int64_t* replans) {
+    BATCH_ENTER(b);
+    if (b->n_walls == 0) return bfail(LC_ERR_ARG, "lc_batch_get_walled: not a walled batch");
+    const size_t N = (size_t)b->a.S * b->a.n;
+    BCK(cudaStreamSynchronize(b->st));
+    std::vector<int> tmp(N);
+    for (int t = 0; t < 2; ++t) {
+        int32_t* dst = t == 0 ? n_plan : lost_frames;
+        if (!dst) continue;
+        BCK(cudaMemcpy(tmp.data(), t == 0 ? b->a.n_plan : b->a.lost, sizeof(int) * N, cudaMemcpyDeviceToHost));
+        for (size_t g = 0; g < N; ++g) dst[b->ext(g)] = tmp[g];
+    }
+    if (wall_hits) {
+        BCK(cudaMemcpy(b->h_ctl, b->a.ctl, sizeof(lcbatch::ScenarioCtl) * (size_t)b->a.S, cudaMemcpyDeviceToHost));
+        for (int s = 0; s < b->a.S; ++s) wall_hits[s] = (int64_t)b->h_ctl[s].wall_hits;
+    }
+    if (replans) *replans = b->replans;
     return LC_OK;
 }
 

@@ -154,6 +154,21 @@ int32_t lc_planner_create(int32_t n_walls, const lc_rect* walls, float agent_rad
 
 void lc_planner_destroy(lc_planner* p) { delete p; }
 
+// Independent copy with the same roadmap STATE (vertex ids handed out so far, container layouts): many scenarios that share
+// a wall layout and an initial planning history (a PSO batch) need one roadmap each only from their first replan on.
+// libstdc++ copies an unordered container node by node in iteration order into the same number of buckets, so the copy
+// iterates — and breaks A* ties — exactly like the original (tests/test_planner.py holds a clone against a fresh planner).
+int32_t lc_planner_clone(const lc_planner* p, lc_planner** out) {
+    if (!p || !out) return lc_set_error(LC_ERR_ARG, "lc_planner_clone: null argument");
+    try {
+        *out = new lc_planner(*p);
+    } catch (...) {
+        *out = nullptr;
+        return lc_set_error(LC_ERR_CAPACITY, "lc_planner_clone: host allocation failed");
+    }
+    return LC_OK;
+}
+
 int32_t lc_planner_roadmap_size(lc_planner* p, int32_t* vertices, int32_t* directed_edges) {
     if (!p) return lc_set_error(LC_ERR_ARG, "lc_planner_roadmap_size: null planner");
     size_t e = 0;

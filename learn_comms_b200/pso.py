@@ -24,7 +24,7 @@ def write_config(file, config):
 
 def aggregate(avg_vel, confident_time):
     """pso_opt.py:30-35: the fitness is the mean + 3 sigma overhead time; NaN or absurd values become 1e99."""
-    if np.isnan(confident_time) or confident_time > 1e99:
+    if np.isnan(confident_time) or float(confident_time) > 1e99:
         return 1e99
     return confident_time
 
@@ -79,9 +79,11 @@ class BatchEvaluator:
     """Fixed set of scenario layouts (pos, goal, max_duration, rng per scenario), re-evaluated with new per-scenario
     parameter matrices every PSO iteration.  evaluate() returns full-length host arrays on every rank."""
 
-    def __init__(self, pos, goal, max_duration, rng_state, device=0, rank=0, world=1, dist=None, comm=True, order="reference"):
+    def __init__(self, pos, goal, max_duration, rng_state, device=0, rank=0, world=1, dist=None, comm=True, order="reference",
+                 walls=None):
         """order: table iteration order of every scenario (lc_batch_desc::table_order).  Default = the reference's own
-        (quirk Q4), which is what the comm_norender processes pso_opt.py spawns would use."""
+        (quirk Q4), which is what the comm_norender processes pso_opt.py spawns would use.  walls [W][4]: the wall layout
+        all scenarios share (a walled catalogue scene evaluated for many particles)."""
         self.S, self.n = int(pos.shape[0]), int(pos.shape[1])
         self.rank, self.world, self.dist = rank, world, dist
         self.lo, self.hi = shard_range(self.S, rank, world)
@@ -91,7 +93,7 @@ class BatchEvaluator:
             S_loc = self.hi - self.lo
             self.batch = api.Batch(pos[sl], goal[sl], np.zeros((S_loc, 3, 8), np.float32), np.zeros((S_loc, 2, 3), np.float32),
                                    np.asarray(max_duration, np.float32)[sl], np.asarray(rng_state, np.uint32)[sl],
-                                   comm=comm, device=device, order=order)
+                                   comm=comm, device=device, order=order, walls=walls)
         S_loc = self.hi - self.lo
         self.h2d_bytes = S_loc * (30 * 4 + self.n * (16 + 8 + 8 + 16 + 16))  # weights + the initial tables reset re-uploads
         self.d2h_bytes = S_loc * 56                                          # one control block per scenario
@@ -112,18 +114,24 @@ class BatchEvaluator:
 
 def simulate_set(scene_layouts, configs, device=0, rank=0, world=1, dist=None, comm=True, order="reference"):
     """pso_opt.py:236-242 simulate_set for MANY particles at once: scene_layouts = list of (pos[n,2], goal[n,2],
-    max_duration, rng_state) with a common n (lc_scene output for the reference's scenes), configs = [P] 5 x 8 matrices.
-    Returns fitness [P][len(scene_layouts)] (read_result's aggregate of each comms.result)."""
+    max_duration, rng_state[, walls[W,4]]) — lc_scene_full output for the reference's scenes, walled ones included —
+    configs = [P] 5 x 8 matrices.  One batch per scene (a batch holds scenarios of one agent count and one wall layout),
+    every particle a scenario of it.  Returns fitness [P][len(scene_layouts)] (read_result's aggregate of each
+    comms.result) and the raw per-scene score arrays."""
     L, P = len(scene_layouts), len(configs)
-    n = scene_layouts[0][0].shape[0]
-    assert all(l[0].shape[0] == n for l in scene_layouts), "one batch holds scenarios of one agent count"
-    pos = np.stack([scene_layouts[s % L][0] for s in range(P * L)]).astype(np.float32)
-    goal = np.stack([scene_layouts[s % L][1] for s in range(P * L)]).astype(np.float32)
-    md = np.array([scene_layouts[s % L][2] for s in range(P * L)], np.float32)
-    rng = np.array([scene_layouts[s % L][3] for s in range(P * L)], np.uint32)
     split = [split_config(c) for c in configs]
-    m_cv = np.stack([split[s // L][0] for s in range(P * L)])
-    m_f = np.stack([split[s // L][1] for s in range(P * L)])
-    ev = BatchEvaluator(pos, goal, md, rng, device=device, rank=rank, world=world, dist=dist, comm=comm, order=order)
-    out = ev.evaluate(m_cv, m_f)
-    return out["fitness"].reshape(P, L), out
+    m_cv = np.stack([sp[0] for sp in split])
+    m_f = np.stack([sp[1] for sp in split])
+    fitness = np.zeros((P, L), np.float64)
+    raw = []
+    for l, lay in enumerate(scene_layouts):
+        pos0, goal0, md0, rng0 = lay[:4]
+        walls = lay[4] if len(lay) > 4 else None
+        pos = np.broadcast_to(np.asarray(pos0, np.float32), (P,) + pos0.shape).copy()
+        goal = np.broadcast_to(np.asarray(goal0, np.float32), (P,) + goal0.shape).copy()
+        ev = BatchEvaluator(pos, goal, np.full(P, md0, np.float32), np.full(P, rng0, np.uint32), device=device, rank=rank, world=world,
+                            dist=dist, comm=comm, order=order, walls=walls)
+        out = ev.evaluate(m_cv, m_f)
+        fitness[:, l] = out["fitness"]
+        raw.append(out)
+    return fitness, raw

@@ -38,7 +38,8 @@ def test_cli_argument_grammar(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("exe,scene,seed", [("comm_norender", 4, 0), ("nocomm_norender", 0, 2), ("comm_norender", 12, 7)])
+@pytest.mark.parametrize("exe,scene,seed", [("comm_norender", 4, 0), ("nocomm_norender", 0, 2), ("comm_norender", 12, 7),
+                                            ("comm_norender", 18, 0), ("comm_norender", 8, 3), ("nocomm_norender", 13, 1)])
 def test_cli_result_file_matches_oracle(tmp_path, exe, scene, seed):
     """Whole-process drop-in: config file in, comms.result out, byte-identical to what the oracle's writer produces."""
     import _oracle
@@ -54,14 +55,18 @@ def test_cli_result_file_matches_oracle(tmp_path, exe, scene, seed):
         pso.write_config(f, cfg)
     r = _run(exe, [scene, "--seed", seed, "--data", "run/iters/"], tmp_path)
     assert r.returncode == 0, r.stderr
-    pos, goal, md, rng = _oracle.scene(scene, seed)
+    pos, goal, md, rng, walls = _oracle.scene_full(scene, seed)
     # str(float64) -> stof: what both parsers see
     rc_cv, rc_f = np.zeros((3, 8), np.float32), np.zeros((2, 3), np.float32)
     assert _oracle.lib().canon_read_config(os.fsencode(str(d / "comms.config")), _oracle._p(rc_cv), _oracle._p(rc_f)) == 0
     import learn_comms_b200 as lcb
-    order = lcb.table_order(len(pos))[0]   # the drop-in runs in the reference's table iteration order (quirk Q4)
-    o = _oracle.CanonSim(pos, goal, rc_cv, rc_f, max_duration=md, rng_state=rng, comm=exe == "comm_norender")
-    o.set_order(order, gauss_seidel=False)
+    order, wall_order = lcb.table_order(len(pos), len(walls))   # the drop-in runs in the reference's table iteration order (quirk Q4)
+
+    def oracle():
+        kw = dict(walls=walls, wall_order=wall_order, planner=lcb.Planner(walls, 0.15), bvh=lcb.static_bvh(walls, wall_order)) if len(walls) else {}
+        return _oracle.CanonSim(pos, goal, rc_cv, rc_f, max_duration=md, rng_state=rng, comm=exe == "comm_norender", order=order, **kw)
+
+    o = oracle()
     o.step(10 ** 6)
     sc = o.scores()
     ref = tmp_path / "oracle.result"
@@ -78,8 +83,10 @@ def test_cli_result_file_matches_oracle(tmp_path, exe, scene, seed):
     assert np.allclose(rows[:n, 2:4], pos[order], rtol=1e-5, atol=1e-6) and not rows[:n, 4:6].any()
     assert np.allclose(rows[:, 6], 0.15) and rows[0, 7] == 0.0
     assert np.allclose(rows[-1, 7], (o.frame - 1) / 60.0, rtol=1e-5)
-    o2 = _oracle.CanonSim(pos, goal, rc_cv, rc_f, max_duration=md, rng_state=rng, comm=exe == "comm_norender")
-    o2.set_order(order, gauss_seidel=False)
+    # demo.cpp:662: one "t:%f u:%f s:%f" line per counted finisher on stdout, the last one carrying the final statistics
+    lines = [l for l in r.stdout.splitlines() if l.startswith("t:")]
+    assert len(lines) == sc["n_done"] and lines[-1].endswith("u:%f s:%f" % (sc["run_avg"], sc["run_std"]))
+    o2 = oracle()
     o2.step(o.frame - 1)
     st = o2.state()
     assert np.allclose(rows[-n:, 2:4], st["pos"][order], rtol=1e-5, atol=1e-6) and np.allclose(rows[-n:, 4:6], st["vel"][order], rtol=1e-5, atol=1e-6)

@@ -142,6 +142,37 @@ def test_gpu_equals_the_reference_rollout_directly(name, upto):
         assert ("%g" % got[0], "%g" % got[1]) == tuple(str(x) for x in gd["result_file"])
 
 
+@pytest.mark.parametrize("scene,seed", [(9, 0), (18, 2), (13, 1), (3, 0)])
+def test_walled_batch_equals_single_crowd(scene, seed):
+    """k_batch_rollout with walls (one layout per batch, per-scenario roadmaps cloned at the first replan): 6 particles of a
+    walled catalogue scene, rolled out to completion by relaunching while scenarios wait for the host planner, against the
+    single-crowd path (itself held against O-canon above): frames, scores, final state, plans, wall hits, replans."""
+    pos, goal, md, rng, walls = lcb.scene_full(scene, seed)
+    P = 6
+    m_cv, m_f = wl.weights(100 + scene, batch=P)
+    m_cv[0] = 0
+    m_f[0] = 0
+    b = lcb.Batch(np.broadcast_to(pos, (P,) + pos.shape).copy(), np.broadcast_to(goal, (P,) + goal.shape).copy(), m_cv, m_f,
+                  np.full(P, md, np.float32), np.full(P, rng, np.uint32), walls=walls, order="reference")
+    part = b.run(max_frames=150)     # resumable: a bounded first leg
+    assert (part["frames"] == 150).all()
+    out = b.run()
+    bs, bw = b.state(), b.walled()
+    replans = 0
+    for k in range(P):
+        g = lcb.Sim(pos, goal, m_cv[k], m_f[k], max_duration=md, rng_state=rng, walls=walls, order="reference")
+        frames = g.run_to_completion()
+        sc = g.scores()
+        assert out["frames"][k] == frames and out["n_done"][k] == sc["n_done"], (k, out["frames"][k], frames)
+        assert out["group_time"][k] == np.float32(sc["group_time"])
+        assert out["avg_velocity"][k] == np.float32(sc["avg_velocity"]) or (np.isnan(out["avg_velocity"][k]) and np.isnan(sc["avg_velocity"]))
+        _same({key: bs[key][k] for key in KEYS}, g.state(), f"scenario {k}")
+        gw = g.walled()
+        assert np.array_equal(bw["n_plan"][k], gw["n_plan"]) and bw["wall_hits"][k] == gw["wall_hits"]
+        replans += gw["replans"]
+    assert bw["replans"] == replans
+
+
 def test_walled_error_paths():
     pos, goal, md, rng, walls = lcb.scene_full(3, 0)
     with pytest.raises(lcb.LcError):  # a decomposed crowd cannot have walls (replans pause the frame for the host planner)

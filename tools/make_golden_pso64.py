@@ -37,12 +37,16 @@ def one(job):
 
 
 def main():
-    cfg = particles()
+    global SCENES, P
+    name = "pso64_oref.npz"
+    if len(sys.argv) > 1 and sys.argv[1] == "walled":  # the walled half of pso_opt.py's default scene universe (pso_opt.py:514)
+        SCENES, P, name = (8, 9, 13, 18), 32, "pso32_walled_oref.npz"
+    cfg = particles(P, 64 if name.startswith("pso64") else 32)
     jobs = [(k, s, cfg[k]) for k in range(P) for s in SCENES] + [(-1, s, np.zeros((5, 8))) for s in SCENES]
     with ThreadPoolExecutor(max_workers=os.cpu_count()) as ex:
         out = np.array(list(ex.map(one, jobs)), np.float64)
     res, base = out[:P * len(SCENES)].reshape(P, len(SCENES), 3), out[P * len(SCENES):]
-    path = os.path.join(ROOT, "tests", "golden", "pso64_oref.npz")
+    path = os.path.join(ROOT, "tests", "golden", name)
     np.savez_compressed(path, scenes=np.array(SCENES, np.int32), configs=cfg, fitness=res[:, :, 0], frames=res[:, :, 1].astype(np.int32),
                         avg_velocity=res[:, :, 2], baseline=base[:, 0], baseline_frames=base[:, 1].astype(np.int32))
     loss = (res[:, :, 0] / base[None, :, 0]).sum(1)
