@@ -548,6 +548,24 @@ def main():
     state_hash = {"hash": f"{total:016x}", "frames": W + K, "agents_hashed": hashed,
                   "what": "sum mod 2^64 over all agents of mix64(id, pos bits, vel bits); equal at every N <=> the decomposed run is bit-identical"}
 
+    # timeline of one frame INSIDE the graph replay (device clock stamps at kernel entries; the two peer waits of a decomposed
+    # crowd): what the frame's critical path really is — per-kernel CUDA events need a serial, host-paced launch sequence
+    sim.step(16)
+    tr = sim.trace()
+    order = ["begin", "bin", "scan_hull", "reorder", "pairs", "force", "collide"]
+    seg = {f"{a}->{b_}": (tr[b_] - tr[a]) / 1e3 for a, b_ in zip(order[:-1], order[1:]) if tr[a] is not None and tr[b_] is not None}
+    timeline = {"unit": "us", "entry_to_entry": seg, "refine_entry": None if tr["refine"] is None else tr["refine"] / 1e3,
+                "refine_end": None if tr["refine_end"] is None else tr["refine_end"] / 1e3}
+    if domain:
+        mine = {"rank": rank, "nbr_wait": (tr["nbr_wait_end"] - tr["nbr_wait_begin"]) / 1e3, "all_wait": (tr["all_wait_end"] - tr["all_wait_begin"]) / 1e3,
+                "begin_kernel": (tr["begin_end"] - tr["begin"]) / 1e3 if tr["begin_end"] else None, "entry_to_entry": seg,
+                "refine_end": timeline["refine_end"], "force_entry": tr["force"] / 1e3}
+        allr = [None] * world
+        dist.all_gather_object(allr, mine)
+        timeline["ranks"] = allr
+        timeline["nbr_wait_max"] = max(r["nbr_wait"] for r in allr)
+        timeline["all_wait_max"] = max(r["all_wait"] for r in allr)
+
     # roofline leg: per-kernel device time, CUDA events between the launches on the simulation's stream
     prof = sim.step_profiled(20)
     pair_tests = sim.pair_tests()
@@ -668,7 +686,7 @@ def main():
                             else f"{world} independent crowds, one per GPU, no exchange"),
                            "l2": "per-frame working set (2 x 88 B x agents + grid) exceeds the 126 MB L2 at 1M agents; no flush"},
                 "counters": counters, "clocks": clk, "e2e": e2e, "e2e_read": e2e_read, "gpu_launches": int(launches), "roofline": roofline,
-                "state_hash": state_hash, "secondary": secondary, "cpu_baseline": cpu}
+                "state_hash": state_hash, "timeline": timeline, "secondary": secondary, "cpu_baseline": cpu}
         print(json.dumps(line), file=RESULT_OUT, flush=True)
     if dist is not None:
         dist.barrier()

@@ -108,6 +108,11 @@ int32_t lc_count_pair_tests(lc_sim* sim, int64_t* pair_tests);
  * chains without contraction (the arithmetic this library is restricted to for bit parity), [1] the same as packed
  * mul.rn.f32x2 / add.rn.f32x2 (what the pair filter issues), [2] FFMA chains (the hardware's nominal peak) */
 int32_t lc_fp32_peak(int32_t device, int32_t repeats, float* tflops /*[3]*/);
+/* device-clock timeline of the last executed frame (ns, %globaltimer): entry of k_frame_begin, k_bin, k_scan_hull, k_reorder,
+ * k_refine, k_pairs, k_force, k_collide [0..7]; a decomposed crowd also stamps its two peer waits: neighbour handshake begin /
+ * end [8, 9], all-rank exchange begin / end [10, 11], end of k_refine [12], end of the frame-start kernel [13] */
+#define LC_TRACE_STAMPS 16
+int32_t lc_get_trace(lc_sim* sim, uint64_t* ts /*[LC_TRACE_STAMPS]*/);
 /* timing on the simulation's own stream (CUDA events) */
 int32_t lc_timer_start(lc_sim* sim);
 int32_t lc_timer_stop(lc_sim* sim, float* milliseconds);

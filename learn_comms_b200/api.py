@@ -39,7 +39,7 @@ EXPORTS = [
     "lc_create", "lc_destroy", "lc_set_weights", "lc_step", "lc_run_to_completion", "lc_sync", "lc_finished",
     "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
-    "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
+    "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_get_trace", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
     "lc_read_config", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
@@ -77,6 +77,7 @@ def lib():
         L.lc_kernel_launches.restype = C.c_int64
         L.lc_step_profiled.argtypes = [vp, i32, vp]
         L.lc_count_pair_tests.argtypes = [vp, C.POINTER(C.c_int64)]
+        L.lc_get_trace.argtypes = [vp, vp]
         L.lc_fp32_peak.argtypes = [i32, i32, vp]
         L.lc_dd_create.argtypes = [C.POINTER(_Desc), C.POINTER(_DomainDesc), C.POINTER(vp)]
         L.lc_dd_mailbox.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
@@ -431,6 +432,15 @@ class Sim:
         k = C.c_int32(0)
         _ck(lib().lc_get_plan(self.h, agent, _p(wp), 64, C.byref(k)))
         return wp[:k.value].copy()
+
+    def trace(self):
+        """Device-clock stamps (ns) of the last executed frame (lc_get_trace): dict name -> ns relative to the frame's start."""
+        ts = np.zeros(16, np.uint64)
+        _ck(lib().lc_get_trace(self.h, _p(ts)))
+        names = ("begin", "bin", "scan_hull", "reorder", "refine", "pairs", "force", "collide", "nbr_wait_begin", "nbr_wait_end",
+                 "all_wait_begin", "all_wait_end", "refine_end", "begin_end")
+        t0 = int(ts[0])
+        return {k: (int(ts[i]) - t0 if ts[i] else None) for i, k in enumerate(names)}
 
     def pair_tests(self):
         """pair-filter evaluations of the last executed frame (lc_count_pair_tests)."""

@@ -100,6 +100,7 @@ struct lc_sim {
 // lc_step(n) replays n frames as the binary decomposition of n over these graphs: 20 frames = 16 + 4, two launches
 // (with only 1- and 16-frame graphs it was 16 + 1 + 1 + 1 + 1: five, whose host-side skew between the ranks of a
 // decomposed crowd ended up in the peer-flag waits)
+static_assert(LC_TRACE_STAMPS == lc::TS_COUNT, "trace layout shared with the C ABI");
 static const int GRAPH_LEVELS = 5;
 static const int GRAPH_BATCH = 1 << (GRAPH_LEVELS - 1);
 
@@ -332,6 +333,8 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     CKC(dalloc(&b.srt_pq, (size_t)2 * ((n + 1) / 2))); s->allocs.push_back(b.srt_pq);
     CKC(cudaMemset(b.srt_pq, 0, sizeof(float4) * 2 * ((size_t)(n + 1) / 2)));
     CKC(dalloc(&b.cellrank, n)); s->allocs.push_back(b.cellrank);
+    CKC(dalloc(&b.slot_cell, n)); s->allocs.push_back(b.slot_cell);
+    CKC(cudaMemset(b.slot_cell, 0, sizeof(int) * (size_t)n));
     CKC(dalloc(&b.cell_count, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_count);
     CKC(cudaMemset(b.cell_count, 0, sizeof(int) * lc::CELL_ALLOC));  // k_scan_hull leaves it cleared after every frame
     CKC(dalloc(&b.cell_start, lc::CELL_ALLOC)); s->allocs.push_back(b.cell_start);
@@ -392,6 +395,12 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         hd.lay = s->lay;
         hd.mbox[rank] = s->mailbox;
         hd.replan[0] = hd.replan[1] = 0x7fffffff;
+        {   // per-slot "stays on this rank" marks written by the pack, read by the next frame's sort
+            unsigned char* keep = nullptr;
+            CKC(cudaMalloc((void**)&keep, (size_t)n)); s->allocs.push_back(keep);
+            CKC(cudaMemset(keep, 0, (size_t)n));
+            hd.keep = keep;
+        }
         {   // how long a rank waits for a peer's flag before it reports LC_ERR_CUDA instead of hanging the GPU
             const char* e = getenv("LC_DD_TIMEOUT_MS");
             const unsigned long long ms = e ? strtoull(e, nullptr, 10) : 10000ull;
@@ -403,6 +412,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
 
     lc::Params& P = s->hp;
     P.n = n_loc;
+    P.n_in = n_loc;
     P.n_ids = n_ids;
     P.cap = n;
     P.dd_rank = rank; P.dd_world = world;
@@ -420,6 +430,11 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     P.lcg_stride = lcg_pow(16807u, (uint64_t)n_ids);
     P.flags = d->flags;
     P.stencil_req = d->stencil > 0 ? d->stencil : 2;
+    {   // grid re-sort period (crowd.cuh: skin).  A decomposed crowd re-sorts every frame: its local set changes every frame.
+        const char* e = getenv("LC_REBIN_EVERY");
+        const int k = e ? atoi(e) : 8;
+        P.rebin_every = dom ? 1 : (k < 1 ? 1 : k);
+    }
     P.n_walls = d->n_walls;
     P.n_bvh = 0;
     P.rng0 = d->rng_state;
@@ -859,6 +874,15 @@ int32_t lc_get_plan(lc_sim* s, int32_t agent, float* waypoints, int32_t cap, int
     *n_waypoints = k;
     if (k > cap) return fail(LC_ERR_CAPACITY, "lc_get_plan: %d waypoints, the buffer holds %d", k, cap);
     if (waypoints && k > 0) CK(cudaMemcpy(waypoints, s->b.w.plan + (size_t)id * lc::WP_CAP, sizeof(float) * 2 * (size_t)k, cudaMemcpyDeviceToHost));
+    return LC_OK;
+}
+
+int32_t lc_get_trace(lc_sim* s, uint64_t* ts) {
+    SIM_ENTER(s);
+    if (!ts) return fail(LC_ERR_ARG, "lc_get_trace: null argument");
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    for (int k = 0; k < LC_TRACE_STAMPS; ++k) ts[k] = (uint64_t)s->hctl->ts[k];
     return LC_OK;
 }
 

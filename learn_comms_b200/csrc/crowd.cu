@@ -20,29 +20,36 @@
 namespace lc {
 using namespace lcm;
 
-// Domain mode: the input of a frame is the set of records the ranks' k_dd_pack stored in this rank's mailbox (own
-// stayers, then what the left / right neighbour sent).  k_bin / k_scan_hull / k_reorder read them in place — no unpack copy.
+// Domain mode: the input of a frame's counting sort is (a) last frame's local slots, read in place from `cur` — an
+// owned agent that stays on this rank is kept, one that left or was a ghost is skipped — followed by (b) the records the
+// left and (c) the right neighbour's k_collide stored into this rank's mailbox (migrants and ghosts).  No unpack copy and
+// no self copy: only boundary agents ever travel.
 struct DDRec {
     const float4* base;  // plane 0 of the region; plane p is at base + p * cap
     int cap, idx;
     __device__ __forceinline__ float4 plane(int p) const { return base[(size_t)p * cap + idx]; }
 };
+// i >= recv[1]: which neighbour record input index i is
 __device__ __forceinline__ DDRec dd_locate(const Params* P, const Buffers& b, int i) {
     const DomainDev* dd = b.dd;
     const int par = b.ctl->frame & 1u;  // k_dd_sync_begin already advanced the frame counter
-    const int n_self = dd->recv[1], n_l = dd->recv[2];
+    const int n_prev = dd->recv[1], n_l = dd->recv[2];
     int reg;
     DDRec r;
-    if (i < n_self) { reg = 1; r.idx = i; }
-    else if (i < n_self + n_l) { reg = 2; r.idx = i - n_self; }   // from the left neighbour
-    else { reg = 0; r.idx = i - n_self - n_l; }                    // from the right neighbour
-    r.cap = reg == 1 ? dd->lay.cap_self : dd->lay.cap_halo;
+    if (i < n_prev + n_l) { reg = 2; r.idx = i - n_prev; }   // from the left neighbour
+    else { reg = 0; r.idx = i - n_prev - n_l; }              // from the right neighbour
+    r.cap = dd->lay.cap_halo;
     r.base = reinterpret_cast<const float4*>(dd->mbox[P->dd_rank] + dd->lay.region[par][reg]);
     return r;
 }
-__device__ __forceinline__ float2 input_pos(const Params* P, const Buffers& b, int i) {
-    if (b.dd) { const float4 r0 = dd_locate(P, b, i).plane(0); return make_float2(r0.x, r0.y); }
-    return b.posf[i];
+// position of input record i; false = the slot is not part of this frame's local set
+__device__ __forceinline__ bool input_pos(const Params* P, const Buffers& b, int i, float2& p) {
+    if (b.dd) {
+        if (i >= b.dd->recv[1]) { const float4 r0 = dd_locate(P, b, i).plane(0); p = make_float2(r0.x, r0.y); return true; }
+        if (!b.dd->keep[i]) return false;
+    }
+    p = b.posf[i];
+    return true;
 }
 
 __constant__ float c_dirx[HULL_K];
@@ -55,6 +62,15 @@ __constant__ float c_dir2y[HULL_K2];
 // (launch_dependents), and touches no memory before its predecessor is complete and flushed (wait).  Meant to hide the
 // launch gaps between the kernels of a frame; inside the 16-frame graph it measured SLOWER (plaza125k 75.0 vs 64.0 us
 // per frame, plaza1m 279 vs 278 us), so it is off by default.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void stamp(Ctl* ctl, int which) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    ctl->ts[which] = t;
+}
+// entry stamp of a frame kernel (thread 0 of block 0)
+__device__ __forceinline__ void stamp_entry(Ctl* ctl, int which) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) stamp(ctl, which);
+}
 __device__ __forceinline__ void pdl_enter() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -90,20 +106,23 @@ __device__ __forceinline__ void fold_avg_velocity(Ctl* ctl) {
 
 // Fold the per-block partials written by k_collide / k_init_reduce into Ctl.  Called by every thread of ONE block.
 __device__ void consume_block_reductions(Ctl* ctl, const Buffers& b) {
-    __shared__ uint32_t s_r[5];
+    __shared__ uint32_t s_r[5], s_dm;
     __shared__ unsigned long long s_lv;
     const int nb = ctl->n_blkred;
-    if (threadIdx.x == 0) { s_r[0] = s_r[1] = 0xffffffffu; s_r[2] = s_r[3] = s_r[4] = 0u; s_lv = 0ull; }
+    if (threadIdx.x == 0) { s_r[0] = s_r[1] = 0xffffffffu; s_r[2] = s_r[3] = s_r[4] = 0u; s_lv = 0ull; s_dm = 0u; }
     __syncthreads();
     if (nb > 0) {
-        uint32_t mnx = 0xffffffffu, mny = 0xffffffffu, mxx = 0u, mxy = 0u, sp = 0u;
+        uint32_t mnx = 0xffffffffu, mny = 0xffffffffu, mxx = 0u, mxy = 0u, sp = 0u, dm = 0u;
         unsigned long long lv = 0ull;
         for (int i = threadIdx.x; i < nb; i += blockDim.x) {
             const BlockRed r = b.blkred[i];
             mnx = min(mnx, r.minx); mny = min(mny, r.miny); mxx = max(mxx, r.maxx); mxy = max(mxy, r.maxy);
             sp = max(sp, r.vmax);
+            dm = max(dm, r.dmax);
             lv = r.lastvel > lv ? r.lastvel : lv;
         }
+        dm = __reduce_max_sync(0xffffffffu, dm);
+        if ((threadIdx.x & 31) == 0 && dm) atomicMax(&s_dm, dm);
         // warp first: 1024 same-address shared atomics per value serialise (they were most of this kernel's time)
         mnx = __reduce_min_sync(0xffffffffu, mnx); mny = __reduce_min_sync(0xffffffffu, mny);
         mxx = __reduce_max_sync(0xffffffffu, mxx); mxy = __reduce_max_sync(0xffffffffu, mxy);
@@ -120,6 +139,7 @@ __device__ void consume_block_reductions(Ctl* ctl, const Buffers& b) {
         ctl->minx = min(ctl->minx, s_r[0]); ctl->miny = min(ctl->miny, s_r[1]);
         ctl->maxx = max(ctl->maxx, s_r[2]); ctl->maxy = max(ctl->maxy, s_r[3]);
         ctl->vmax = max(ctl->vmax, s_r[4]);
+        ctl->dmax = max(ctl->dmax, s_dm);
         ctl->lastvel = s_lv > ctl->lastvel ? s_lv : ctl->lastvel;
         ctl->n_blkred = 0;
     }
@@ -160,6 +180,100 @@ __device__ void grid_from_reductions(const Params* P, Ctl* ctl) {
     ctl->delta = 1e-5f * ext + 1e-4f;
 }
 
+// S0 proper: demo::run (demo.cpp:665-702) for frame `frame` on a (shared-memory) copy of the control block — the agents
+// that became done in the last frame are counted in table order (Welford), the time-out penalty folds every agent that
+// is still walking, the all_done latch is set.  cnt = done-events waiting in b.events, nnd = agents not done.  Called by
+// every thread of ONE block of 1024 threads.
+__device__ void demo_run_score(const Params* __restrict__ P, const Buffers& b, Ctl* ctl, uint32_t frame, int cnt, int nnd, bool dd,
+                               int2* s_ev, float* s_ft, int* s_flag) {
+    const int tid = threadIdx.x;
+    const int n = P->n_ids;
+    const float fake_time = __fmul_rn(LC_DT, (float)frame);
+    // newly done agents, table order (demo.cpp:669-676)
+    if (cnt > 0 && cnt <= EV_SORT_CAP) {
+        int m = 1;
+        while (m < cnt) m <<= 1;
+        for (int i = tid; i < m; i += blockDim.x) s_ev[i] = i < cnt ? b.events[i] : make_int2(0x7fffffff, 0);
+        __syncthreads();
+        for (int k = 2; k <= m; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = tid; i < m; i += blockDim.x) {
+                    int ixj = i ^ j;
+                    if (ixj > i) {
+                        int2 a = s_ev[i], c = s_ev[ixj];
+                        bool up = (i & k) == 0;
+                        if ((a.x > c.x) == up) { s_ev[i] = c; s_ev[ixj] = a; }
+                    }
+                }
+                __syncthreads();
+            }
+        if (tid == 0)
+            for (int i = 0; i < cnt; ++i) update_runs(ctl, __fsub_rn(fake_time, __int_as_float(s_ev[i].y)), b.fin_log);
+    } else if (cnt > EV_SORT_CAP) {
+        for (int i = tid; i < n; i += blockDim.x) b.ev_by_id[i] = CUDART_NAN_F;
+        __syncthreads();
+        for (int i = tid; i < cnt; i += blockDim.x) b.ev_by_id[b.events[i].x] = __int_as_float(b.events[i].y);
+        __syncthreads();
+        for (int base = 0; base < n; base += blockDim.x) {
+            int i = base + tid;
+            float v = i < n ? b.ev_by_id[i] : CUDART_NAN_F;
+            s_ft[tid] = v;
+            s_flag[tid] = (v == v);
+            __syncthreads();
+            if (tid == 0)
+                for (int k = 0; k < blockDim.x; ++k)
+                    if (s_flag[k]) update_runs(ctl, __fsub_rn(fake_time, s_ft[k]), b.fin_log);
+            __syncthreads();
+        }
+    }
+    __syncthreads();
+    bool all_done = nnd == 0;
+    if (fake_time > P->max_duration && dd) {
+        // domain mode: k_dd_pack of every rank scattered the finish times of its owned, not-done agents into the
+        // scoring rank's id-indexed table (NaN = none); fold them in id order there.  Other ranks only latch.
+        if (P->dd_rank == 0) {
+            float* tab = reinterpret_cast<float*>(b.dd->mbox[0] + b.dd->lay.ev_by_id);
+            for (int base = 0; base < n; base += blockDim.x) {
+                const int id = base + tid;
+                const float v = id < n ? tab[id] : CUDART_NAN_F;
+                s_ft[tid] = v;
+                s_flag[tid] = (v == v);
+                __syncthreads();
+                if (tid == 0)
+                    for (int k = 0; k < blockDim.x; ++k)
+                        if (s_flag[k]) update_runs(ctl, s_ft[k], b.fin_log);
+                __syncthreads();
+            }
+        }
+        all_done = true;
+    } else if (fake_time > P->max_duration) {  // demo.cpp:691-700
+        for (int base = 0; base < n; base += blockDim.x) {
+            int id = base + tid;
+            int flag = 0;
+            float ft = 0.f;
+            if (id < n) {
+                int s = b.slot_of_id[id];
+                int4 mt = b.cur.meta[s];
+                if (!(mt.y & 1)) {
+                    float2 g = b.cur.goal[s], p = b.posf[s];
+                    float l = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
+                    ft = __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
+                    flag = 1;
+                }
+            }
+            s_ft[tid] = ft;
+            s_flag[tid] = flag;
+            __syncthreads();
+            if (tid == 0)
+                for (int k = 0; k < blockDim.x; ++k)
+                    if (s_flag[k]) update_runs(ctl, s_ft[k], b.fin_log);
+            __syncthreads();
+        }
+        all_done = true;
+    }
+    if (tid == 0 && all_done) ctl->finished = 1;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // S0: demo::run (demo.cpp:665-702)
 __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, const Buffers& b) {
@@ -177,6 +291,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         reinterpret_cast<uint32_t*>(&s_ctl)[i] = reinterpret_cast<const uint32_t*>(gctl)[i];
     __syncthreads();
     Ctl* ctl = &s_ctl;
+    if (tid == 0) stamp(ctl, TS_BEGIN);
     const int n = P->n_ids;  // everything below that walks "all agents" is indexed by global id
     const bool dd = P->dd_world > 1;
     consume_block_reductions(ctl, b);
@@ -198,99 +313,34 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         if (tid == 0) gctl->halt = 2;
         return;
     }
-    const float fake_time = __fmul_rn(LC_DT, (float)frame);
-    if (!was_finished) {
-        // newly done agents, table order (demo.cpp:669-676)
-        if (cnt > 0 && cnt <= EV_SORT_CAP) {
-            int m = 1;
-            while (m < cnt) m <<= 1;
-            for (int i = tid; i < m; i += blockDim.x) s_ev[i] = i < cnt ? b.events[i] : make_int2(0x7fffffff, 0);
-            __syncthreads();
-            for (int k = 2; k <= m; k <<= 1)
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    for (int i = tid; i < m; i += blockDim.x) {
-                        int ixj = i ^ j;
-                        if (ixj > i) {
-                            int2 a = s_ev[i], c = s_ev[ixj];
-                            bool up = (i & k) == 0;
-                            if ((a.x > c.x) == up) { s_ev[i] = c; s_ev[ixj] = a; }
-                        }
-                    }
-                    __syncthreads();
-                }
-            if (tid == 0)
-                for (int i = 0; i < cnt; ++i) update_runs(ctl, __fsub_rn(fake_time, __int_as_float(s_ev[i].y)), b.fin_log);
-        } else if (cnt > EV_SORT_CAP) {
-            for (int i = tid; i < n; i += blockDim.x) b.ev_by_id[i] = CUDART_NAN_F;
-            __syncthreads();
-            for (int i = tid; i < cnt; i += blockDim.x) b.ev_by_id[b.events[i].x] = __int_as_float(b.events[i].y);
-            __syncthreads();
-            for (int base = 0; base < n; base += blockDim.x) {
-                int i = base + tid;
-                float v = i < n ? b.ev_by_id[i] : CUDART_NAN_F;
-                s_ft[tid] = v;
-                s_flag[tid] = (v == v);
-                __syncthreads();
-                if (tid == 0)
-                    for (int k = 0; k < blockDim.x; ++k)
-                        if (s_flag[k]) update_runs(ctl, __fsub_rn(fake_time, s_ft[k]), b.fin_log);
-                __syncthreads();
-            }
-        }
-        __syncthreads();
-        bool all_done = nnd == 0;
-        if (fake_time > P->max_duration && dd) {
-            // domain mode: k_dd_pack of every rank scattered the finish times of its owned, not-done agents into the
-            // scoring rank's id-indexed table (NaN = none); fold them in id order there.  Other ranks only latch.
-            if (P->dd_rank == 0) {
-                float* tab = reinterpret_cast<float*>(b.dd->mbox[0] + b.dd->lay.ev_by_id);
-                for (int base = 0; base < n; base += blockDim.x) {
-                    const int id = base + tid;
-                    const float v = id < n ? tab[id] : CUDART_NAN_F;
-                    s_ft[tid] = v;
-                    s_flag[tid] = (v == v);
-                    __syncthreads();
-                    if (tid == 0)
-                        for (int k = 0; k < blockDim.x; ++k)
-                            if (s_flag[k]) update_runs(ctl, s_ft[k], b.fin_log);
-                    __syncthreads();
-                }
-            }
-            all_done = true;
-        } else if (fake_time > P->max_duration) {  // demo.cpp:691-700
-            for (int base = 0; base < n; base += blockDim.x) {
-                int id = base + tid;
-                int flag = 0;
-                float ft = 0.f;
-                if (id < n) {
-                    int s = b.slot_of_id[id];
-                    int4 mt = b.cur.meta[s];
-                    if (!(mt.y & 1)) {
-                        float2 g = b.cur.goal[s], p = b.posf[s];
-                        float l = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
-                        ft = __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
-                        flag = 1;
-                    }
-                }
-                s_ft[tid] = ft;
-                s_flag[tid] = flag;
-                __syncthreads();
-                if (tid == 0)
-                    for (int k = 0; k < blockDim.x; ++k)
-                        if (s_flag[k]) update_runs(ctl, s_ft[k], b.fin_log);
-                __syncthreads();
-            }
-            all_done = true;
-        }
-        if (tid == 0 && all_done) ctl->finished = 1;
-    }
+    if (!was_finished) demo_run_score(P, b, ctl, frame, cnt, nnd, dd, s_ev, s_ft, s_flag);
     if (tid == 0) {
         ctl->frame = frame;
         ctl->ev_count = 0;
         ctl->n_not_done = nnd;
         ctl->nnd_acc = 0;
         const float vm = __uint_as_float(ctl->vmax);
-        grid_from_reductions(P, ctl);
+        {   // re-sort this frame, or keep last re-sort's slot order and search a skin wider (crowd.cuh)
+            const float moved = ctl->skin + __uint_as_float(ctl->dmax);   // NaN / inf (a non-finite state) forces the re-sort
+            const bool rebin = P->rebin_every <= 1 || ctl->force_rebin || ctl->since + 1 >= P->rebin_every || !(moved <= 0.25f * ctl->h);
+            if (rebin) {
+                grid_from_reductions(P, ctl);
+                ctl->skin = 0.f;
+                ctl->since = 0;
+            } else {
+                // same cells, same slots; the cutoff follows this frame's speeds as it does on a re-sort frame
+                float vmax = vm;
+                if (!(vmax <= 1.0e3f)) { vmax = 1.0e3f; if (!ctl->error) ctl->error = -3; }
+                ctl->cutoff = fmaxf(P->R + 10.f * vmax * 1.001f + 0.01f, P->near_reach);
+                ctl->skin = moved;
+                ctl->since += 1;
+                ctl->stencil = (int)ceilf((ctl->cutoff + 2.f * moved) / ctl->h);     // clamps of the rare full-block walks
+                ctl->stencil_x = (int)ceilf((ctl->cutoff + 2.f * moved) / ctl->hx);
+            }
+            ctl->rebin = rebin;
+            ctl->force_rebin = 0;
+            ctl->dmax = 0u;
+        }
         ctl->minx = ctl->miny = 0xffffffffu;
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
@@ -338,15 +388,18 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
     pdl_enter();
     const Ctl* ctl = b.ctl;
     if (ctl->halt) return;
-    const int n = P->n;
+    stamp_entry(b.ctl, TS_BIN);
+    if (!ctl->rebin) return;  // slot order and cell_start of the last re-sort stay in force
+    const int n = P->n_in;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
     float2 p = make_float2(0.f, 0.f);
     int cell = -1;
+    bool present = false;
     if (i < n) {
-        p = input_pos(P, b, i);
-        cell = cell_of(ctl, p.x, p.y);
-        b.pair_cnt[i] = 0;  // k_pairs' lists, indexed by this frame's slots
+        present = input_pos(P, b, i, p);
+        if (present) cell = cell_of(ctl, p.x, p.y);
+        b.pair_cnt[i] = 0;  // k_pairs' lists, indexed by this frame's slots (never more than input records)
     }
     {   // Counting sort, phase 1.  The agents arrive in last frame's cell order, so equal cells form runs of
         // consecutive lanes: one atomicAdd per run instead of one per agent (same-address atomics serialise in L2).
@@ -370,7 +423,7 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
     // at least min_k ext_val[k] - margin away from the centre can be this frame's extremes.  Warps whose agents are all
     // inside that circle (3/4 of a square crowd) skip the 16 warp reductions.  If the guess is ever wrong the polygon just
     // gets a vertex that is not extreme, or an edge less — any polygon through agents keeps the pruning exact.
-    const bool ok = i < n && rx == rx && ry == ry && (rx * rx + ry * ry >= ctl->gate_rho2);
+    const bool ok = present && rx == rx && ry == ry && (rx * rx + ry * ry >= ctl->gate_rho2);
     if (__any_sync(0xffffffffu, ok)) {
 #pragma unroll
         for (int k = 0; k < HULL_K; ++k) {
@@ -403,13 +456,15 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    stamp_entry(ctl, TS_SCAN);
+    if (!ctl->rebin) return;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (blockIdx.x == gridDim.x - 1) {
         if (P->flags & 1u) return;
         __shared__ unsigned long long s_ext[HULL_K];
         if (tid < HULL_K) s_ext[tid] = 0ull;
         __syncthreads();
-        const int nblk = (P->n + 1023) / 1024;
+        const int nblk = (P->n_in + 1023) / 1024;
         unsigned long long m = 0ull;
         for (int q = tid / HULL_K; q < nblk; q += 1024 / HULL_K) {
             const unsigned long long v = b.blkext[(size_t)q * HULL_K + (tid % HULL_K)];
@@ -429,7 +484,9 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
             if (ka != 0ull && kb != 0ull) {
                 const int a = (int)(ka & 0xffffffffull), c = (int)(kb & 0xffffffffull);
                 if (a != c) {
-                    const float2 pa = input_pos(P, b, a), pc = input_pos(P, b, c);
+                    float2 pa, pc;
+                    input_pos(P, b, a, pa);  // extremes are present records by construction
+                    input_pos(P, b, c, pc);
                     const double ux = (double)pc.x - pa.x, uy = (double)pc.y - pa.y, l = sqrt(ux * ux + uy * uy);
                     if (l > 0.0) {
                         s_e[k][0] = pa.x; s_e[k][1] = pa.y;
@@ -505,15 +562,24 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
-    const int n = P->n;
+    stamp_entry(ctl, TS_REORDER);
+    const int n = P->n_in;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int2 cr = b.cellrank[i];
-    const int s = b.cell_start[cr.x] + cr.y;
+    const bool rebin = ctl->rebin;
+    int s = i;   // between re-sorts the agents keep their slots: a straight copy of last frame's output
+    if (rebin) {
+        const int2 cr = b.cellrank[i];
+        if (cr.x < 0) return;  // domain mode: a slot that is not part of this frame's local set (left, or was a ghost)
+        s = b.cell_start[cr.x] + cr.y;
+        b.slot_cell[s] = cr.x;
+    } else {
+        b.pair_cnt[i] = 0;  // (k_bin does it on re-sort frames)
+    }
     float2 p, g;
     float4 pv;
     int4 mt;
-    if (b.dd) {  // records of k_dd_pack: (posf.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
+    if (b.dd && i >= b.dd->recv[1]) {  // records of the neighbours' pack: (posf.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
         const DDRec r = dd_locate(P, b, i);
         const float4 r0 = r.plane(0), r1 = r.plane(1), r2 = r.plane(2), r4 = r.plane(4);
         p = make_float2(r0.x, r0.y); pv = r0; g = make_float2(r1.z, r1.w);
@@ -524,6 +590,7 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
         b.srt.c4[s] = r.plane(3);
     } else {
         p = b.posf[i]; pv = b.cur.pv[i]; mt = b.cur.meta[i]; g = b.cur.goal[i];
+        if (b.dd && b.dd->keep[i] == 2) mt.y |= META_GHOST;  // crossed into the adjacent strip last frame: its ghost from now on
         b.srt.vfh[s] = b.cur.vfh[i];
         b.srt.lgoal[s] = b.cur.lgoal[i];
         b.srt.facing[s] = b.cur.facing[i];
@@ -554,7 +621,9 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
         // the arg-max of comm.cpp:201-220 for any query (proof in DESIGN.md)
         const int ne = ctl->n_edges;
         bool inside = ne >= 3;
-        const float delta = ctl->delta;
+        // the polygon's vertices are where the extreme agents stood at the last re-sort; eroded by what anybody can have
+        // moved since, it still lies inside the hull of the current positions
+        const float delta = ctl->delta + ctl->skin;
         for (int e = 0; e < ne && inside; ++e) {
             float d = (p.x - ctl->ex[e]) * ctl->enx[e] + (p.y - ctl->ey[e]) * ctl->eny[e];
             if (!(d >= delta)) inside = false;
@@ -636,18 +705,22 @@ __device__ __forceinline__ void refine_body(const Params* __restrict__ P, const 
     if (tid == 0) { ctl->cand_sel = 1; ctl->n_cand2 = s_out; }
 }
 
-__device__ void dd_cand_body(const Params* __restrict__ P, const Buffers& b);
+__device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b);
 
-// k_refine; in domain mode the same block then exchanges the survivors with the other ranks (domain.cuh)
+// k_refine; in domain mode the same block then does the frame's all-rank exchange (comm-partner candidates, scoring
+// inputs, replan gate, latch) and S0 (domain.cuh) — beside k_pairs, off the frame's critical path
 __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
-    if (ctl->halt || (P->flags & 1u)) return;
-    refine_body(P, b);
+    if (ctl->halt) return;
+    stamp_entry(ctl, TS_REFINE);
+    if (!(P->flags & 1u)) refine_body(P, b);
     if (b.dd) {
         __syncthreads();
-        dd_cand_body(P, b);
+        dd_global_body(P, b);
     }
+    __syncthreads();
+    stamp_entry(ctl, TS_REFINE_END);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -687,15 +760,20 @@ __device__ __forceinline__ void pair_eval(const Buffers& b, int s, int j, float 
 template <bool HALF, bool FIRST, class N>
 __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
                                            float RR, float near_c, N&& note, long long* tested = nullptr) {
-    const int st = ctl->stencil, stx = ctl->stencil_x, nx = ctl->nx, ny = ctl->ny;
-    int ix = (int)floorf((px - ctl->x0) / ctl->hx), iy = (int)floorf((py - ctl->y0) / ctl->h);
-    ix = min(max(ix, 0), nx - 1);
-    iy = min(max(iy, 0), ny - 1);
-    // Disc-shaped stencil: a row of cells whose nearest edge is gap_y away can only hold interaction partners within
-    // sqrt(cutoff^2 - gap_y^2) in x.  Inflated by 1e-3 so that float rounding here can never exclude a cell that cell_of
-    // (the same monotonic expression, applied to a position inside the disc) put an agent into.
-    const float cut = ctl->cutoff * 1.001f + 1e-3f, cut2 = cut * cut;
-    const float inv_h = 1.f / ctl->hx;
+    const int nx = ctl->nx, ny = ctl->ny;
+    // Disc-shaped stencil around the agent's CURRENT position: a row of cells whose nearest edge is gap_y away can only hold
+    // partners within sqrt(reach^2 - gap_y^2) in x, reach = cutoff + skin (the cells hold the agents where they stood at
+    // the last re-sort; skin bounds how far anybody has moved since).  Inflated by 1e-3 so that float rounding here can
+    // never exclude a cell that cell_of (the same monotonic expression, applied to a position inside the disc) put an
+    // agent into.
+    const float cut = ctl->cutoff * 1.001f + 1e-3f + ctl->skin, cut2 = cut * cut;
+    const float inv_h = 1.f / ctl->hx, inv_hy = 1.f / ctl->h;
+    // HALF: every unordered pair is tested by the agent that comes first in SLOT order, i.e. in the order of the cells of
+    // the last re-sort: rows from the agent's sorted-into row upwards, in that row the slots after its own
+    const int row_b = HALF ? b.slot_cell[s] / nx : 0;
+    const float yl = (py - cut - ctl->y0) * inv_hy, yh = (py + cut - ctl->y0) * inv_hy;
+    const int row_lo = HALF ? row_b : min(max((int)floorf(yl - (1e-3f + 1e-6f * fabsf(yl))), 0), ny - 1);
+    const int row_hi = min(max((int)floorf(yh + (1e-3f + 1e-6f * fabsf(yh))), HALF ? row_b : 0), ny - 1);
     const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
     const float2 RR2 = make_float2(RR, RR);
     const float4* __restrict__ pq = b.srt_pq;
@@ -751,19 +829,22 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
             cand1 = !((c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1);
         }
     };
-    for (int yy = HALF ? iy : max(iy - st, 0); yy <= min(iy + st, ny - 1); ++yy) {
+    for (int yy = row_lo; yy <= row_hi; ++yy) {
+        // distance from the agent to the row; the outermost rows also hold whatever was clamped into them, so they reach to
+        // infinity on their outer side
         const float ylo = ctl->y0 + (float)yy * ctl->h;
-        const float gap = yy == iy ? 0.f : (yy > iy ? ylo - py : py - (ylo + ctl->h));
-        const float rem = cut2 - (gap > 0.f ? gap * gap : 0.f);
+        const float below = yy == 0 ? 0.f : ylo - py, above = yy == ny - 1 ? 0.f : py - (ylo + ctl->h);
+        const float gap = fmaxf(fmaxf(below, above), 0.f);
+        const float rem = cut2 - gap * gap;
         if (!(rem > 0.f)) continue;
         // approximate, but widened beyond every rounding: rsqrt is good to 2 ulp, the product with 1/h to < 1e-6 of its
         // value, and the range only has to CONTAIN the cells cell_of() can have put a partner inside the disc into
         const float reach = rem * rsqrtf(rem) * 1.0002f + 1e-4f;
         const float xl = (px - reach - ctl->x0) * inv_h, xh = (px + reach - ctl->x0) * inv_h;
-        const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), max(ix - stx, 0)), ix);
-        const int x_hi = max(min((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), min(ix + stx, nx - 1)), ix);
-        // s lies in cell (ix, iy), x_lo <= ix <= x_hi: in its own row the partners after s start at slot s + 1
-        int j0 = (HALF && yy == iy) ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
+        const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), 0), nx - 1);
+        const int x_hi = min(max((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), 0), nx - 1);
+        // in its own row the partners after s start at slot s + 1
+        int j0 = (HALF && yy == row_b) ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
         if (j0 >= j1) continue;
         if (tested) { *tested += j1 - j0; continue; }  // counting mode (lc_count_pair_tests): the ranges, not the filter
         if (j0 & 1) single(j0++);
@@ -813,6 +894,7 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
     pdl_enter();
     const Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    stamp_entry(b.ctl, TS_PAIRS);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
     const float4 me = b.srt.pv[s];
@@ -902,6 +984,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    stamp_entry(ctl, TS_FORCE);
     __shared__ lcw::Wall s_walls[WALLS ? WALL_SMEM : 1];
     const lcw::Wall* walls = nullptr;
     if constexpr (WALLS) walls = stage_walls(P, b, s_walls);
@@ -1217,10 +1300,10 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
 // Per-block partials instead of global atomics: one hot cache line shared by ~10^4 warps serialises in a single
 // L2 slice.  Every block stores one BlockRed; the next k_frame_begin (one block) folds them.
 __device__ __forceinline__ void block_reduce_store(const Buffers& b, bool valid, float x, float y, float speed,
-                                                   uint32_t lv_id) {
-    __shared__ uint32_t s_r[5];
+                                                   uint32_t lv_id, float disp = 0.f) {
+    __shared__ uint32_t s_r[5], s_dmax;
     __shared__ unsigned long long s_lv;
-    if (threadIdx.x == 0) { s_r[0] = s_r[1] = 0xffffffffu; s_r[2] = s_r[3] = s_r[4] = 0u; s_lv = 0ull; }
+    if (threadIdx.x == 0) { s_r[0] = s_r[1] = 0xffffffffu; s_r[2] = s_r[3] = s_r[4] = 0u; s_lv = 0ull; s_dmax = 0u; }
     __syncthreads();
     const uint32_t mnx = __reduce_min_sync(0xffffffffu, valid ? f2ord(x) : 0xffffffffu);
     const uint32_t mxx = __reduce_max_sync(0xffffffffu, valid ? f2ord(x) : 0u);
@@ -1230,15 +1313,18 @@ __device__ __forceinline__ void block_reduce_store(const Buffers& b, bool valid,
     const uint32_t sp = __reduce_max_sync(0xffffffffu, valid ? __float_as_uint(speed) : 0u);
     // highest-id not-done agent (physics.cpp:72-76 with vel_count == 0: the last one processed wins)
     const uint32_t top = __reduce_max_sync(0xffffffffu, lv_id);
+    // displacement >= 0 (or NaN, which sorts above everything and forces a re-sort)
+    const uint32_t dm = __reduce_max_sync(0xffffffffu, __float_as_uint(disp));
     if ((threadIdx.x & 31) == 0) {
         atomicMin(&s_r[0], mnx); atomicMin(&s_r[1], mny);
         atomicMax(&s_r[2], mxx); atomicMax(&s_r[3], mxy); atomicMax(&s_r[4], sp);
+        atomicMax(&s_dmax, dm);
     }
     if (top != 0u && lv_id == top) atomicMax(&s_lv, ((unsigned long long)top << 32) | __float_as_uint(speed));
     __syncthreads();
     if (threadIdx.x == 0) {
         BlockRed r;
-        r.minx = s_r[0]; r.miny = s_r[1]; r.maxx = s_r[2]; r.maxy = s_r[3]; r.vmax = s_r[4]; r.pad = 0u; r.lastvel = s_lv;
+        r.minx = s_r[0]; r.miny = s_r[1]; r.maxx = s_r[2]; r.maxy = s_r[3]; r.vmax = s_r[4]; r.dmax = s_dmax; r.lastvel = s_lv;
         b.blkred[blockIdx.x] = r;
         if (blockIdx.x == 0) b.ctl->n_blkred = (int)gridDim.x;
     }
@@ -1254,13 +1340,14 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    stamp_entry(ctl, TS_COLLIDE);
     __shared__ lcw::Wall s_walls[WALLS ? WALL_SMEM : 1];
     const lcw::Wall* walls = nullptr;
     if constexpr (WALLS) walls = stage_walls(P, b, s_walls);
     const int n = P->n;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     bool valid = s < n;
-    float px = 0.f, py = 0.f, speed = 0.f;
+    float px = 0.f, py = 0.f, speed = 0.f, disp = 0.f;
     uint32_t lv_id = 0u;
     if (valid) {
         const float4 me = b.cur.pv[s];
@@ -1349,6 +1436,10 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
             }
         }
         b.posf[s] = make_float2(px, py);
+        {
+            const float ex = px - qx, ey = py - qy;
+            disp = LC_DT * 1.0001f + sqrtf(ex * ex + ey * ey);
+        }
         if constexpr (WALLS) {  // replan gate of the coming frame (ai.cpp:152-163) on the position all_sync publishes
             const float2 g = b.cur.goal[s];
             walled_gate(P, b, walls, mt.x, px, py, g.x, g.y);
@@ -1361,7 +1452,8 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
             if (!(speed <= LC_FLT_MAX)) atomicAdd(&ctl->nonfinite, 1);
         }
     }
-    block_reduce_store(b, valid && px == px && py == py, px, py, speed, lv_id);
+    // how far the agent got this frame at most: the integration step (|vel_forehalf| <= 1 after the clamp) plus the push-out
+    block_reduce_store(b, valid && px == px && py == py, px, py, speed, lv_id, valid ? disp : 0.f);
     // domain mode: route every owned agent's record of the NEXT frame to its owner / ghost hosts (reads back what this
     // thread just stored: posf, vfh)
     if (DD) dd_pack_body<128>(P, b);
@@ -1557,6 +1649,8 @@ __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
         ctl->nnd_acc = 0;
+        ctl->force_rebin = 1;              // arbitrary new state: the next frame re-sorts the grid
+        ctl->dmax = 0u;
         ctl->wr1 = ctl->wr2 = 0x7fffffff;  // walled scenes: k_walled_gate re-evaluates the requests on the new state
         ctl->w_served = 0;
         for (int k = 0; k < HULL_K; ++k) ctl->ext_val[k] = -CUDART_INF_F;  // arbitrary new state: no gate next frame
@@ -1574,11 +1668,11 @@ DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids) {
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     L.cap_self = cap_self; L.cap_halo = cap_halo;
     for (int p = 0; p < 2; ++p) {
+        L.nblob[p] = take(sizeof(NeighbourBlob) * 3);
+        L.nflag[p] = take(sizeof(unsigned long long) * 3);
         L.blob[p] = take(sizeof(DomainBlob) * DD_MAX_WORLD);
-        L.flag[p] = take(sizeof(unsigned long long) * DD_MAX_WORLD);
         L.cflag[p] = take(sizeof(unsigned long long) * DD_MAX_WORLD);
-        L.ncand[p] = take(sizeof(int) * DD_MAX_WORLD);
-        for (int r = 0; r < 3; ++r) L.region[p][r] = take(sizeof(float4) * DD_PLANES * (size_t)(r == 1 ? cap_self : cap_halo));
+        for (int r = 0; r < 3; ++r) L.region[p][r] = r == 1 ? 0 : take(sizeof(float4) * DD_PLANES * (size_t)cap_halo);  // stayers do not travel
         L.events[p] = take(sizeof(int2) * (size_t)DD_MAX_WORLD * DD_EV_CAP);
         L.cand[p] = take(sizeof(float4) * 2 * (size_t)DD_MAX_WORLD * DD_CAND_CAP);
     }

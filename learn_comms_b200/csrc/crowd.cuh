@@ -42,19 +42,29 @@ struct AgentArrays {
 
 // per-block partial reductions of k_collide / k_init_reduce (128-thread blocks), folded by the next k_frame_begin
 struct BlockRed {
-    uint32_t minx, miny, maxx, maxy, vmax, pad;
+    uint32_t minx, miny, maxx, maxy, vmax, dmax;   // dmax: float bits of the largest displacement of the frame (>= 0)
     unsigned long long lastvel;
 };
 
+enum { TS_BEGIN = 0, TS_BIN, TS_SCAN, TS_REORDER, TS_REFINE, TS_PAIRS, TS_FORCE, TS_COLLIDE, TS_NBR_WAIT0, TS_NBR_WAIT1,
+       TS_ALL_WAIT0, TS_ALL_WAIT1, TS_REFINE_END, TS_BEGIN_END, TS_COUNT = 16 };
 struct Ctl {
     // frame / latch (main.cpp:98-150)
     uint32_t frame;
     int finished;   // demo::run returned all_done in some frame <= frame
     int halt;       // frames after the all_done frame are no-ops
     int error;      // lc_status of the first device-side error
-    // uniform grid of the current frame
+    // uniform grid: geometry of the last re-sort, cutoff of the current frame
     float x0, y0, h, hx, cutoff;   // cell height (y) and width (x)
     int nx, ny, ncells, stencil, stencil_x;
+    // Skin: the agents are re-sorted into cells only every Params::rebin_every frames.  In between, slot order and
+    // cell_start stay as they are; a search from an agent's CURRENT position reaches cutoff + skin, where skin bounds how
+    // far anybody has moved since the re-sort, so the candidate set is still a superset and the exact predicate decides.
+    int rebin;         // this frame re-sorts (k_bin / k_scan_hull / scatter in k_reorder); else k_reorder copies slot to slot
+    int since;         // frames since the last re-sort
+    int force_rebin;   // the state was replaced (lc_create / lc_set_state)
+    float skin;        // sum of the per-frame maximum displacements since the last re-sort, at this frame's start
+    uint32_t dmax;     // largest displacement of the frame in flight (float bits; consumed by the next frame_begin)
     // comm-partner candidate pruning
     float cx, cy, delta;
     unsigned long long ext[HULL_K];
@@ -87,6 +97,9 @@ struct Ctl {
     int drawn_last;              // draws the last executed frame consumed
     unsigned long long draws;    // draws consumed BEFORE the last executed frame (its agent k draws element draws + k + 1)
     unsigned long long wall_hits, replans;
+    // device-clock timeline of the last executed frame (globaltimer, ns): thread 0 of block 0 of every frame kernel stamps its
+    // entry; the two peer waits of a decomposed crowd stamp begin and end.  lc_get_trace reads it (bench.py's timeline).
+    unsigned long long ts[TS_COUNT];
 };
 
 constexpr int DD_MAX_WORLD = 8;     // ranks of one spatially decomposed crowd (one B200 box)
@@ -95,7 +108,10 @@ constexpr int DD_CAND_CAP = 4096;    // comm-partner candidates one rank can pub
 constexpr int META_GHOST = 4;        // meta.y bit2: halo copy of an agent owned by a neighbouring rank
 
 struct Params {
-    int n;          // agents in the local arrays this frame; in domain mode (dd_world > 1) rewritten on the device every frame
+    int n;          // agents in the local (cell-sorted) arrays this frame; in domain mode (dd_world > 1) rewritten on the device every frame
+    int n_in;       // input records of this frame's counting sort (k_bin / k_reorder): == n for a single-GPU crowd; domain mode:
+                    // last frame's local slots (stayers are read in place, leavers and old ghosts are skipped) + the records the
+                    // neighbours sent
     int n_ids;      // size of the global id space (id-indexed tables, LCG stride); == n for a single-GPU crowd
     int cap;        // capacity of the slot-indexed arrays (launch width); == n for a single-GPU crowd
     // spatial domain decomposition in x strips: rank r owns xb[r] <= pos.x < xb[r+1]
@@ -107,6 +123,7 @@ struct Params {
     uint32_t lcg_stride;  // 16807^n mod (2^31-1): advances an agent's private stream by one frame
     uint32_t flags;
     int stencil_req;
+    int rebin_every;      // re-sort the grid every this many frames (1 = every frame: decomposed crowds, whose local set changes every frame)
     int n_walls, n_bvh;   // static walls (0 = wall-free: the kernels' WALLS = false instantiations)
     uint32_t rng0;        // walled: stream state before frame 1's first draw (draw k of the run = rng0 * 16807^k)
     float m_cv[24];
@@ -137,6 +154,7 @@ struct Buffers {
     float4* srt_pq;    // [2 * ceil(n/2)] pair-interleaved copy of srt.pv: (x0,x1,z0,z1), (vx0,vx1,vz0,vz1) per slot pair
     float2* posf;      // final (post-push) positions, same order as cur
     int2* cellrank;    // (cell, rank within cell) per agent, cur order
+    int* slot_cell;    // [n] by slot: the cell the agent was sorted into at the last re-sort
     int* cell_count;   // [CELL_ALLOC]
     int* cell_start;   // [CELL_ALLOC]
     unsigned long long* tile_agg; // [SCAN_TILES] (frame << 32) | tile total, published by k_scan_hull
@@ -170,29 +188,40 @@ struct Buffers {
 // ---- spatial domain decomposition over NVLink peer memory (domain.cuh) ----
 // Agent record on the wire: 5 x 16 B planes (posf.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
 constexpr int DD_PLANES = 5;
-struct DomainBlob {               // one per (sender, parity), written into EVERY peer's mailbox
-    int n_sent[3];                // records the sender put into the regions of rank-1, itself, rank+1
-    uint32_t vmax;                // max speed bits over the sender's agents (interaction cutoff must be global)
-    uint32_t bbox[4];             // order-encoded min x, min y, max x, max y of the sender's agents
+// Frame start needs the two ADJACENT ranks only: how many records they sent, and bounds (max speed, y extent) of the
+// agents those records can be — the grid of a rank is a matter of the records it holds.  One per (neighbour, parity).
+struct NeighbourBlob {
+    int n_sent;                   // records the sender put into this rank's region
+    uint32_t vmax;                // max speed bits over the sender's local agents
+    uint32_t miny, maxy;          // order-encoded y extent of the sender's local agents
+    int error;
+    int pad[3];
+};
+// Everything that is global (scoring, latch, replan gate, comm-partner candidates) travels later in the frame, in the
+// side-stream kernel beside k_pairs.  One per (sender, parity), written into EVERY peer's mailbox.
+struct DomainBlob {
     int nnd;                      // owned agents that are not done (demo.cpp:667-669)
     int nonfinite;
     unsigned long long lastvel;   // physics.cpp:72-76: ((id + 1) << 32) | speed bits of the highest-id owned not-done agent
     int replan[2];                // two lowest owned ids that need a replan (ai.cpp:151-168)
     int n_events;                 // done-events forwarded to the scoring rank (rank 0)
+    int n_cand;                   // comm-partner candidates published this frame
     int error;
-    int pad[2];
+    int pad;
 };
-static_assert(sizeof(DomainBlob) % 8 == 0, "DomainBlob is copied word-wise");
+static_assert(sizeof(DomainBlob) % 8 == 0 && sizeof(NeighbourBlob) % 8 == 0, "blobs are copied word-wise");
 struct DomainLayout {             // byte offsets inside one rank's mailbox allocation; identical on every rank
-    size_t blob[2], flag[2], cflag[2], ncand[2], region[2][3], events[2], cand[2], ev_by_id, total;
+    size_t nblob[2], nflag[2], blob[2], cflag[2], region[2][3], events[2], cand[2], ev_by_id, total;   // region[.][1] is unused
     int cap_self, cap_halo;
 };
 struct DomainDev {
     char* mbox[DD_MAX_WORLD];     // mailbox base of every rank (own allocation + peer mappings)
     DomainLayout lay;
-    int count[3];                 // records packed this frame for (rank-1, self, rank+1); cleared by k_dd_sync_begin once published
-    int recv[3];                  // records waiting in this rank's regions (from the right, self, from the left)
+    int count[3];                 // this frame's pack: records sent to rank-1, agents that stay, records sent to rank+1
+    int recv[3];                  // this frame's input: records from the right, last frame's local slots, records from the left
     int replan[2];
+    unsigned char* keep;          // [cap] by last frame's slot: 0 = not part of the next frame's local set, 1 = stays as owned agent,
+                                  // 2 = stays as ghost of its new owner; 1 / 2 are read in place from `cur` by the next frame's sort
     unsigned long long spin_timeout_ns;
 };
 DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);

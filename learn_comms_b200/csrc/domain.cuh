@@ -4,30 +4,33 @@
 // Included at the end of crowd.cu (same translation unit: it reuses the block reductions).
 //
 // Frame f on every rank (all inside the CUDA graph):
-//   (pack)        owned agents -> records in the mailbox of their new owner (stay / migrate to an adjacent strip) and,
-//                 as ghosts, of every adjacent rank whose strip they are within `dd_halo` of; at the time-out frame
-//                 the finish times of demo.cpp:691-700 are scattered into the scoring rank's id-indexed table.
-//                 Done by the tail of the PREVIOUS frame's k_collide (dd_pack_body; one pass over the state and one
-//                 launch less per frame); kernel k_dd_pack only runs once, before the first frame
-//   (publish)     folds the per-block reductions of the previous frame, writes this rank's DomainBlob (record counts,
-//                 max speed, not-done count, avg_velocity inputs, replan gate, done-events) into every peer, then
-//                 releases flag[rank] = f with a system-scope fence
-//   (wait)        spins until every peer's flag reads f, merges the blobs into Ctl (GLOBAL max speed, not-done count,
-//                 replan gate, events on rank 0) and sets Params::n to the number of local records
-//                 (publish + wait + k_frame_begin's work are ONE single-block kernel, k_dd_sync_begin)
-//   k_bin, k_scan_hull, k_reorder read the records in place (owners and ghosts mixed; meta bit2 tells them apart) and sort
-//                 them into cell order like a single-GPU crowd; there is no unpack copy
-//   (candidates)  dd_cand_body, the tail of k_refine: publishes this rank's surviving comm-partner candidates (with the partner payload x() needs:
-//                 pos, vel.x, c) to every peer, waits for theirs and appends them (comm.cpp:201-220 is a GLOBAL arg-max)
+//   (pack)        tail of the PREVIOUS frame's k_collide (dd_pack_body; k_dd_pack only before the very first frame): an
+//                 owned agent that stays on this rank is merely marked (keep[slot] = 1: next frame's sort reads it in
+//                 place); one that migrates to an adjacent strip, or lies within `dd_halo` of one, is stored as an
+//                 80-byte record into that neighbour's mailbox.  Only boundary agents ever travel.  At the time-out
+//                 frame the finish times of demo.cpp:691-700 go into the scoring rank's id-indexed table.
+//   (frame start) k_dd_sync_begin, one block: tells the two ADJACENT ranks how many records they got and bounds of what
+//                 those can be (max speed, y extent), waits for THEIR two flags only, sets this frame's record counts and
+//                 grid.  Nothing global is needed to start a frame: the grid of a rank is a matter of the records it
+//                 holds, and any cutoff that covers them yields a candidate superset, i.e. the same result.
+//   k_bin, k_scan_hull, k_reorder sort stayers (from `cur`) and received records (from the mailbox, in place) into cell order.
+//   (global)      dd_global_body, the tail of k_refine on the side stream BESIDE k_pairs: every rank publishes its
+//                 comm-partner candidates (comm.cpp:201-220 is a GLOBAL arg-max) and its scoring inputs (not-done count,
+//                 avg_velocity inputs, replan requests, done-events) to all ranks, waits for all of theirs — the only
+//                 all-rank wait of the frame, off the critical path — merges, and runs S0 (demo::run: Welford on rank 0,
+//                 all_done latch, replan gate).  Its consumers are k_force (partner, replan gate) and the next frame
+//                 (latch), both after the join.
 //   k_force, k_collide: ghosts are advanced too — the collision pass needs their integrated positions — but never
 //                 counted; their next state always comes from the owner.
 // Why the result is bit-identical to the single-GPU run: an owned agent sees every neighbour within the interaction
 // cutoff (ghost band = cutoff at the speed bound + collision reach), forces and hits are summed in id order, the
-// comm partner is the global arg-max over the union of the per-rank hull survivors, and the replan gate, max speed,
-// done count and scoring inputs are merged across ranks before they are used.  tests/test_gpu_domain.py checks it.
+// comm partner is the global arg-max over the union of the per-rank hull survivors, and the replan gate, done count
+// and scoring inputs are merged across ranks before they are used.  tests/test_gpu_domain.py checks it, bench.py's
+// state_hash shows it at every N.
 //
-// Mailboxes are double-buffered by frame parity: a peer can be at most one exchange ahead (it needs our flag of
-// frame f before it can start frame f + 1's pack), so parity f + 2 is only written after we consumed parity f.
+// Mailboxes are double-buffered by frame parity: no rank can pass k_force of frame f before every rank has reached the
+// global exchange of frame f, so the ranks are never more than a frame apart and parity f + 2 is only written after
+// parity f has been consumed.
 #pragma once
 
 __device__ __forceinline__ unsigned long long dd_now_ns() {
@@ -45,8 +48,7 @@ __device__ __forceinline__ void dd_st_flag(unsigned long long* p, unsigned long 
 }
 // spin until *p == want; false on time-out (a peer died or the hosts enqueued different frame counts)
 __device__ __forceinline__ bool dd_wait_flag(const unsigned long long* p, unsigned long long want, unsigned long long timeout_ns) {
-    // Poll back to back; look at the clock (and yield for a moment) only every 32 polls.  A 200 ns sleep per poll added
-    // up to half a microsecond of wake-up delay to each of the two waits of a frame (8 GPUs: 9.81e9 -> 9.88e9 with 32 ns).
+    // Poll back to back; look at the clock (and yield for a moment) only every 32 polls.
     const unsigned long long t0 = dd_now_ns();
     for (unsigned it = 1;; ++it) {
         if (dd_ld_flag(p) == want) return true;
@@ -61,7 +63,7 @@ __device__ __forceinline__ bool dd_active(const Params* P, const Ctl* ctl) {
     return !(ctl->finished && !(P->flags & 2u));  // frames after the all_done frame are no-ops on every rank alike
 }
 
-// which of (rank-1, self, rank+1) gets a record of an owned agent at x, and in which role (1 = owner, 2 = ghost)
+// which of (rank-1, self, rank+1) gets an owned agent at x, and in which role (1 = owner, 2 = ghost)
 __device__ __forceinline__ void dd_route(const Params* P, float x, int role[3]) {
     const int me = P->dd_rank, w = P->dd_world;
     int own = me;
@@ -90,8 +92,8 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
     const int me = P->dd_rank;
     const uint32_t frame = ctl->frame + 1u;
     const int par = frame & 1u;
-    // Slot allocation keeps the agents' order (ballot prefix inside the warp, warp totals, one global atomicAdd per block
-    // and destination): the records stay in last frame's cell order, which k_bin's run-aggregated counting relies on.
+    // Slot allocation in the neighbours' regions keeps the agents' order (ballot prefix inside the warp, warp totals, one
+    // global atomicAdd per block and destination); stayers are only counted.
     __shared__ int s_wcnt[3][NT / 32], s_base[3];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int role[3] = {0, 0, 0}, rank_in_blk[3] = {0, 0, 0};
@@ -106,6 +108,10 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
             g = b.cur.goal[i];
             dd_route(P, p.x, role);
         }
+        // stays in the local set: as owner, or — having just crossed into the adjacent strip while still inside our ghost
+        // band — as a ghost of its new owner (who only learns of it next frame).  Next frame's sort reads it from `cur`.
+        // (`cur` itself is left alone: until the next frame runs, this rank is still the one that reports the agent)
+        dd->keep[i] = (unsigned char)role[1];
     }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -123,29 +129,30 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
 #pragma unroll
     for (int k = 0; k < 3; ++k) rank_in_blk[k] += s_wcnt[k][wid];
     if (!owned) return;
-    const float4 pv = b.cur.pv[i];
-    const float2 vfh = b.cur.vfh[i], lg = b.cur.lgoal[i], fc = b.cur.facing[i];
-    const float4 c4 = b.cur.c4[i];
-    const float4 r0 = make_float4(p.x, p.y, pv.z, pv.w), r1 = make_float4(vfh.x, vfh.y, g.x, g.y),
-                 r2 = make_float4(lg.x, lg.y, fc.x, fc.y);
+    if (role[0] | role[2]) {  // a boundary agent: its record goes to the adjacent rank(s), as owner (migration) or as ghost
+        const float4 pv = b.cur.pv[i];
+        const float2 vfh = b.cur.vfh[i], lg = b.cur.lgoal[i], fc = b.cur.facing[i];
+        const float4 c4 = b.cur.c4[i];
+        const float4 r0 = make_float4(p.x, p.y, pv.z, pv.w), r1 = make_float4(vfh.x, vfh.y, g.x, g.y),
+                     r2 = make_float4(lg.x, lg.y, fc.x, fc.y);
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        if (!role[k]) continue;
-        const int q = me - 1 + k;
-        // region of the receiver: 0 = from ITS right neighbour (we are that when we send left, k == 0), 1 = itself,
-        // 2 = from its left neighbour (we send right, k == 2)
-        const int reg = k;
-        const int cap = reg == 1 ? dd->lay.cap_self : dd->lay.cap_halo;
-        const int slot = s_base[k] + rank_in_blk[k];
-        if (slot >= cap) { atomicCAS(&ctl->error, 0, -5); continue; }
-        float4* dst = reinterpret_cast<float4*>(dd->mbox[q] + dd->lay.region[par][reg]);
-        int4 m = mt;
-        m.y = role[k] == 2 ? (mt.y | META_GHOST) : (mt.y & ~META_GHOST);
-        dst[slot] = r0;
-        dst[(size_t)cap + slot] = r1;
-        dst[(size_t)2 * cap + slot] = r2;
-        dst[(size_t)3 * cap + slot] = c4;
-        dst[(size_t)4 * cap + slot] = make_float4(__int_as_float(m.x), __int_as_float(m.y), __int_as_float(m.z), __int_as_float(m.w));
+        for (int k = 0; k < 3; k += 2) {
+            if (!role[k]) continue;
+            const int q = me - 1 + k;
+            // region of the receiver: 0 = from ITS right neighbour (we are that when we send left, k == 0),
+            // 2 = from its left neighbour (we send right, k == 2)
+            const int cap = dd->lay.cap_halo;
+            const int slot = s_base[k] + rank_in_blk[k];
+            if (slot >= cap) { atomicCAS(&ctl->error, 0, -5); continue; }
+            float4* dst = reinterpret_cast<float4*>(dd->mbox[q] + dd->lay.region[par][k]);
+            int4 m = mt;
+            m.y = role[k] == 2 ? (mt.y | META_GHOST) : (mt.y & ~META_GHOST);
+            dst[slot] = r0;
+            dst[(size_t)cap + slot] = r1;
+            dst[(size_t)2 * cap + slot] = r2;
+            dst[(size_t)3 * cap + slot] = c4;
+            dst[(size_t)4 * cap + slot] = make_float4(__int_as_float(m.x), __int_as_float(m.y), __int_as_float(m.z), __int_as_float(m.w));
+        }
     }
     // replan gate (ai.cpp:151-168): done && goal_dist > 1, the two lowest ids over ALL ranks; this rank's two lowest here
     if (mt.y & 1) {
@@ -172,137 +179,137 @@ __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, B
     dd_pack_body<256>(P, b);
 }
 
-// publish + wait + merge + S0 (k_frame_begin's work) in ONE single-block kernel: three launch gaps less per frame
+// Frame start: neighbour handshake + this frame's record counts and grid, ONE single-block kernel.
 __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
     pdl_enter();
-    Ctl* ctl = b.ctl;
+    Ctl* const gctl = b.ctl;
     DomainDev* dd = b.dd;
-    if (!dd_active(P, ctl)) { frame_begin_body(P, b); return; }  // latches halt, like every later frame of a finished run
     const int me = P->dd_rank, w = P->dd_world, tid = threadIdx.x;
+    __shared__ Ctl s_ctl;
+    for (int i = tid; i < (int)(sizeof(Ctl) / 4); i += blockDim.x)
+        reinterpret_cast<uint32_t*>(&s_ctl)[i] = reinterpret_cast<const uint32_t*>(gctl)[i];
+    __syncthreads();
+    Ctl* ctl = &s_ctl;
+    if (tid == 0) stamp(ctl, TS_BEGIN);
+    if (!dd_active(P, ctl)) {  // latched: this and every later frame is a no-op on every rank alike
+        if (tid == 0) gctl->halt = 1;
+        return;
+    }
     const uint32_t frame = ctl->frame + 1u;
     const int par = frame & 1u;
-    consume_block_reductions(ctl, b);  // max speed / lastvel of the frame that just ended (owned agents)
-    __shared__ DomainBlob s_blob;
-    const int nev = min(ctl->ev_count, DD_EV_CAP);
-    if (tid == 0) {
-        if (ctl->ev_count > DD_EV_CAP && !ctl->error) ctl->error = -5;
-        s_blob.n_sent[0] = dd->count[0]; s_blob.n_sent[1] = dd->count[1]; s_blob.n_sent[2] = dd->count[2];
-        s_blob.vmax = ctl->vmax;
-        s_blob.bbox[0] = ctl->minx; s_blob.bbox[1] = ctl->miny; s_blob.bbox[2] = ctl->maxx; s_blob.bbox[3] = ctl->maxy;
-        s_blob.nnd = ctl->nnd_acc;
-        s_blob.nonfinite = ctl->nonfinite;
-        s_blob.lastvel = ctl->lastvel;
-        s_blob.replan[0] = dd->replan[0]; s_blob.replan[1] = dd->replan[1];
-        s_blob.n_events = nev;
-        s_blob.error = ctl->error;
-        s_blob.pad[0] = s_blob.pad[1] = 0;
+    consume_block_reductions(ctl, b);  // bounds of last frame's local agents (owned and ghosts): max speed, box, lastvel
+    // ---- tell the adjacent ranks what they got from us ----
+    if (tid < 3 && tid != 1) {
+        const int q = me - 1 + tid;
+        if (q >= 0 && q < w) {
+            NeighbourBlob nb;
+            nb.n_sent = dd->count[tid];
+            nb.vmax = ctl->vmax; nb.miny = ctl->miny; nb.maxy = ctl->maxy;
+            nb.error = ctl->error;
+            nb.pad[0] = nb.pad[1] = nb.pad[2] = 0;
+            // slot in the receiver: 0 = from its right neighbour (we send left), 2 = from its left neighbour (we send right)
+            *(reinterpret_cast<NeighbourBlob*>(dd->mbox[q] + dd->lay.nblob[par]) + tid) = nb;
+            __threadfence_system();
+            dd_st_flag(reinterpret_cast<unsigned long long*>(dd->mbox[q] + dd->lay.nflag[par]) + tid, (unsigned long long)frame);
+        }
     }
-    // done-events of the frame that just ended go to the scoring rank (rank 0), which folds them in id order
-    int2* evdst = reinterpret_cast<int2*>(dd->mbox[0] + dd->lay.events[par]) + (size_t)me * DD_EV_CAP;
-    for (int k = tid; k < nev; k += blockDim.x) evdst[k] = b.events[k];
-    __syncthreads();
-    constexpr int WORDS = sizeof(DomainBlob) / 4;
-    for (int k = tid; k < w * WORDS; k += blockDim.x) {
-        const int q = k / WORDS, o = k % WORDS;
-        reinterpret_cast<int*>(reinterpret_cast<DomainBlob*>(dd->mbox[q] + dd->lay.blob[par]) + me)[o] = reinterpret_cast<const int*>(&s_blob)[o];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (tid < w) dd_st_flag(reinterpret_cast<unsigned long long*>(dd->mbox[tid] + dd->lay.flag[par]) + me, (unsigned long long)frame);
-
-    // ---- wait for every peer's blob of this frame and merge ----
+    // ---- wait for the adjacent ranks' word on what we got ----
     __shared__ int s_ok;
-    __shared__ int s_evoff[DD_MAX_WORLD + 1];
-    if (tid == 0) s_ok = 1;
+    if (tid == 0) { s_ok = 1; stamp(ctl, TS_NBR_WAIT0); }
     __syncthreads();
-    if (tid < w) {
-        const unsigned long long* fl = reinterpret_cast<const unsigned long long*>(dd->mbox[me] + dd->lay.flag[par]) + tid;
-        // after a time-out every later wait gives up at once: a broken run ends in milliseconds, not minutes
-        if (!dd_wait_flag(fl, (unsigned long long)frame, ctl->error == -2 ? 0ull : dd->spin_timeout_ns)) s_ok = 0;
+    if (tid < 3 && tid != 1) {
+        const int q = me - 1 + tid;   // the rank whose records sit in region (2 - tid): left neighbour -> slot 2, right -> slot 0
+        if (q >= 0 && q < w) {
+            const unsigned long long* fl = reinterpret_cast<const unsigned long long*>(dd->mbox[me] + dd->lay.nflag[par]) + (2 - tid);
+            // after a time-out every later wait gives up at once: a broken run ends in milliseconds, not minutes
+            if (!dd_wait_flag(fl, (unsigned long long)frame, ctl->error == -2 ? 0ull : dd->spin_timeout_ns)) s_ok = 0;
+        }
     }
     __syncthreads();
     __threadfence_system();
-    const DomainBlob* blobs = reinterpret_cast<const DomainBlob*>(dd->mbox[me] + dd->lay.blob[par]);
     if (tid == 0) {
-        if (!s_ok && !ctl->error) ctl->error = -2;
-        uint32_t vmax = 0u, bb0 = 0xffffffffu, bb1 = 0xffffffffu, bb2 = 0u, bb3 = 0u;
-        int nnd = 0, nonfinite = 0, err = ctl->error;
-        unsigned long long lastvel = 0ull;
-        int r1 = 0x7fffffff, r2 = 0x7fffffff;
-        int evoff = 0;
-        for (int q = 0; q < w; ++q) {
-            const DomainBlob bl = blobs[q];
-            vmax = max(vmax, bl.vmax);
-            bb0 = min(bb0, bl.bbox[0]); bb1 = min(bb1, bl.bbox[1]); bb2 = max(bb2, bl.bbox[2]); bb3 = max(bb3, bl.bbox[3]);
-            nnd += bl.nnd;
-            nonfinite += bl.nonfinite;
-            lastvel = bl.lastvel > lastvel ? bl.lastvel : lastvel;
-            for (int k = 0; k < 2; ++k) {  // two smallest distinct ids of the union
-                const int v = bl.replan[k];
-                if (v < r1) { r2 = r1; r1 = v; } else if (v > r1 && v < r2) r2 = v;
-            }
-            if (bl.error && !err) err = bl.error;
-            s_evoff[q] = evoff;
-            evoff += (me == 0) ? bl.n_events : 0;
+        stamp(ctl, TS_NBR_WAIT1);
+        const NeighbourBlob* nbs = reinterpret_cast<const NeighbourBlob*>(dd->mbox[me] + dd->lay.nblob[par]);
+        int err = ctl->error;
+        if (!s_ok && !err) err = -2;
+        int n_l = 0, n_r = 0;
+        uint32_t vmax = ctl->vmax, miny = ctl->miny, maxy = ctl->maxy;
+        if (s_ok) {
+            if (me > 0) { const NeighbourBlob nb = nbs[2]; n_l = nb.n_sent; vmax = max(vmax, nb.vmax); miny = min(miny, nb.miny); maxy = max(maxy, nb.maxy); if (nb.error && !err) err = nb.error; }
+            if (me < w - 1) { const NeighbourBlob nb = nbs[0]; n_r = nb.n_sent; vmax = max(vmax, nb.vmax); miny = min(miny, nb.miny); maxy = max(maxy, nb.maxy); if (nb.error && !err) err = nb.error; }
         }
-        s_evoff[w] = evoff;
-        // records addressed to this rank: own stayers, then what the left / right neighbour sent (owners and ghosts mixed)
-        const int n_self = blobs[me].n_sent[1];
-        const int n_l = me > 0 ? blobs[me - 1].n_sent[2] : 0;
-        const int n_r = me < w - 1 ? blobs[me + 1].n_sent[0] : 0;
-        int total = n_self + n_l + n_r;
-        if (total > P->cap || n_self > dd->lay.cap_self || n_l > dd->lay.cap_halo || n_r > dd->lay.cap_halo) {
+        const int n_prev = P->n, n_stay = dd->count[1];
+        int n_in = n_prev + n_l + n_r, n_new = n_stay + n_l + n_r;
+        if (n_in > P->cap || n_l > dd->lay.cap_halo || n_r > dd->lay.cap_halo || n_l < 0 || n_r < 0) {
             if (!err) err = -5;
-            total = 0;
+            n_in = n_new = 0;
         }
-        dd->recv[0] = n_r; dd->recv[1] = n_self; dd->recv[2] = n_l;
-        dd->count[0] = dd->count[1] = dd->count[2] = 0;  // the publish step above has consumed them
-        P->n = total;
-        ctl->vmax = vmax;
-        ctl->nnd_acc = nnd;
-        ctl->nonfinite = nonfinite;
-        ctl->lastvel = lastvel;
-        ctl->replan1 = r1; ctl->replan2 = r2;
-        ctl->ev_count = evoff;
+        dd->recv[0] = n_r; dd->recv[1] = n_prev; dd->recv[2] = n_l;
+        dd->count[0] = dd->count[1] = dd->count[2] = 0;  // consumed
+        P->n = n_new;
+        P->n_in = n_in;
         ctl->error = err;
-        // Grid extent of the new local set: every record routed here lies in the ghost-extended strip, and inside the
-        // crowd's global box in y.  (A box that is too small would still be correct — cell_of clamps, and clamping never
-        // increases a cell distance — a box that is too large only wastes cells.)
+        // Grid of the new local set: every record here lies in the ghost-extended strip; its y extent and speed are bounded
+        // by the senders' local bounds.  (A box that is too small would still be correct — cell_of clamps, and clamping
+        // never increases a cell distance — a box that is too large only wastes cells.)
+        ctl->vmax = vmax; ctl->miny = miny; ctl->maxy = maxy;
         {
-            float gx0 = ord2f(bb0), gx1 = ord2f(bb2);
-            const float sx0 = P->dd_xb[me] - P->dd_halo - 0.25f, sx1 = P->dd_xb[me + 1] + P->dd_halo + 0.25f;
-            if (bb0 <= bb2) { gx0 = fmaxf(gx0, sx0); gx1 = fminf(gx1, sx1); if (!(gx1 >= gx0)) gx1 = gx0; }
-            ctl->minx = bb0 <= bb2 ? f2ord(gx0) : bb0; ctl->maxx = bb0 <= bb2 ? f2ord(gx1) : bb2;
-            ctl->miny = bb1; ctl->maxy = bb3;
+            const bool any = ctl->minx <= ctl->maxx;
+            float lo = any ? ord2f(ctl->minx) : 3.0e38f, hi = any ? ord2f(ctl->maxx) : -3.0e38f;
+            // what the neighbours sent lies in the ghost band on their side of the cut (ghosts) or just inside ours (migrants)
+            if (me > 0 && n_l > 0) lo = fminf(lo, P->dd_xb[me] - P->dd_halo - 0.25f);
+            if (me < w - 1 && n_r > 0) hi = fmaxf(hi, P->dd_xb[me + 1] + P->dd_halo + 0.25f);
+            // ... and nothing local lies beyond the ghost-extended strip
+            if (me > 0) lo = fmaxf(lo, P->dd_xb[me] - P->dd_halo - 0.25f);
+            if (me < w - 1) hi = fminf(hi, P->dd_xb[me + 1] + P->dd_halo + 0.25f);
+            if (!(hi >= lo)) lo = hi = (me > 0 ? P->dd_xb[me] : (me < w - 1 ? P->dd_xb[me + 1] : 0.f));
+            ctl->minx = f2ord(lo); ctl->maxx = f2ord(hi);
         }
-        dd->replan[0] = dd->replan[1] = 0x7fffffff;
-    }
-    __syncthreads();
-    if (me == 0) {  // gather every rank's done-events; k_frame_begin sorts them by id before the Welford update
-        const int2* evsrc = reinterpret_cast<const int2*>(dd->mbox[0] + dd->lay.events[par]);
-        for (int q = 0; q < w; ++q) {
-            const int cnt = s_evoff[q + 1] - s_evoff[q];
-            for (int k = tid; k < cnt; k += blockDim.x) b.events[s_evoff[q] + k] = evsrc[(size_t)q * DD_EV_CAP + k];
+        const float vm = __uint_as_float(ctl->vmax);
+        ctl->frame = frame;
+        grid_from_reductions(P, ctl);
+        ctl->rebin = 1;   // the local set changes every frame (migrants, ghosts): every frame re-sorts
+        ctl->skin = 0.f; ctl->since = 0; ctl->force_rebin = 0; ctl->dmax = 0u;
+        ctl->minx = ctl->miny = 0xffffffffu;
+        ctl->maxx = ctl->maxy = 0u;
+        ctl->vmax = 0u;
+        ctl->n_cand = 0;
+        {   // k_bin's gate radius from last frame's directional extremes
+            float rho = CUDART_INF_F;
+            for (int k = 0; k < HULL_K; ++k) rho = fminf(rho, ctl->ext_val[k]);
+            rho -= 0.1f;
+            ctl->gate_rho2 = rho > 0.f ? rho * rho : -1.f;
         }
+        // the ghost band was sized for the speed bound (capi.cu); a wider cutoff would miss neighbours
+        if (!(P->R + 10.f * vm * 1.001f + 0.01f + P->near_reach <= P->dd_halo) && !ctl->error) ctl->error = -5;
+        ctl->overlap2 = 0ull;
+        ctl->coll_hits = 0ull;
     }
-    __threadfence();
+    if (tid < HULL_K) ctl->ext[tid] = 0ull;
+    if (tid == 0) stamp(ctl, TS_BEGIN_END);
     __syncthreads();
-    frame_begin_body(P, b);  // S0: scoring + latch + this frame's grid (demo.cpp:665-702), as on a single GPU
+    // everything S0 works on (ev_count, nnd_acc, lastvel, nonfinite, the Welford state) is handed on untouched to
+    // dd_global_body, the only other writer of the control block, which runs strictly later in this frame
+    for (int i = tid; i < (int)(sizeof(Ctl) / 4); i += blockDim.x)
+        reinterpret_cast<uint32_t*>(gctl)[i] = reinterpret_cast<const uint32_t*>(&s_ctl)[i];
 }
 
-// Comm-partner candidates are a global matter (comm.cpp:201-220 scans ALL agents).  Each rank's list after k_refine
-// holds the hull survivors of its own agents; publish them with the payload comm::x reads from the partner and
-// append everybody else's behind the local arrays ("annex" slots >= cap of srt.pv / srt.c4).
-__device__ void dd_cand_body(const Params* __restrict__ P, const Buffers& b) {
-    Ctl* ctl = b.ctl;
+// The frame's one all-rank exchange, in the tail of k_refine on the side stream.  Publishes this rank's comm-partner
+// candidates (with the payload comm::x reads from the partner) and scoring inputs, waits for everybody's, appends their
+// candidates behind the local arrays ("annex" slots >= cap of srt.pv / srt.c4), merges the scoring inputs and runs S0.
+__device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
+    Ctl* const gctl = b.ctl;
     DomainDev* dd = b.dd;
     const int me = P->dd_rank, w = P->dd_world, tid = threadIdx.x;
-    const uint32_t frame = ctl->frame;  // k_frame_begin already advanced it
+    const uint32_t frame = gctl->frame;  // k_dd_sync_begin already advanced it
     const int par = frame & 1u;
-    float4* list = ctl->cand_sel ? b.cand2 : b.cand;
-    const int nloc = ctl->n_cand2;
+    const bool comm = !(P->flags & 1u);
+    float4* list = gctl->cand_sel ? b.cand2 : b.cand;
+    const int nloc = comm ? gctl->n_cand2 : 0;
     const int nsend = min(nloc, DD_CAND_CAP);
-    if (tid == 0 && nloc > DD_CAND_CAP) atomicCAS(&ctl->error, 0, -5);
+    const int nev = min(gctl->ev_count, DD_EV_CAP);
+    if (tid == 0 && (nloc > DD_CAND_CAP || gctl->ev_count > DD_EV_CAP)) atomicCAS(&gctl->error, 0, -5);
+    // ---- publish ----
     for (int k = tid; k < nsend; k += blockDim.x) {
         const float4 cd = list[k];
         const int slot = __float_as_int(cd.w);
@@ -315,46 +322,130 @@ __device__ void dd_cand_body(const Params* __restrict__ P, const Buffers& b) {
             dst[2 * k + 1] = B;
         }
     }
-    __threadfence_system();
-    __syncthreads();
-    if (tid < w && tid != me) {
-        reinterpret_cast<int*>(dd->mbox[tid] + dd->lay.ncand[par])[me] = nsend;
-        __threadfence_system();
-        dd_st_flag(reinterpret_cast<unsigned long long*>(dd->mbox[tid] + dd->lay.cflag[par]) + me, (unsigned long long)frame);
+    {   // done-events of the frame that just ended go to the scoring rank (rank 0), which folds them in id order
+        int2* evdst = reinterpret_cast<int2*>(dd->mbox[0] + dd->lay.events[par]) + (size_t)me * DD_EV_CAP;
+        if (me != 0) for (int k = tid; k < nev; k += blockDim.x) evdst[k] = b.events[k];
     }
-    __shared__ int s_off[DD_MAX_WORLD + 1];
-    __shared__ int s_ok;
-    if (tid == 0) s_ok = 1;
-    __syncthreads();
-    if (tid < w && tid != me) {
-        const unsigned long long* fl = reinterpret_cast<const unsigned long long*>(dd->mbox[me] + dd->lay.cflag[par]) + tid;
-        if (!dd_wait_flag(fl, (unsigned long long)frame, ctl->error == -2 ? 0ull : dd->spin_timeout_ns)) s_ok = 0;
-    }
-    __syncthreads();
-    __threadfence_system();
+    __shared__ DomainBlob s_blob;
     if (tid == 0) {
-        if (!s_ok) atomicCAS(&ctl->error, 0, -2);
-        const int* nc = reinterpret_cast<const int*>(dd->mbox[me] + dd->lay.ncand[par]);
-        int off = 0;
+        s_blob.nnd = gctl->nnd_acc;
+        s_blob.nonfinite = gctl->nonfinite;
+        s_blob.lastvel = gctl->lastvel;
+        s_blob.replan[0] = dd->replan[0]; s_blob.replan[1] = dd->replan[1];
+        s_blob.n_events = nev;
+        s_blob.n_cand = nsend;
+        s_blob.error = gctl->error;
+        s_blob.pad = 0;
+    }
+    __syncthreads();
+    constexpr int WORDS = sizeof(DomainBlob) / 4;
+    for (int k = tid; k < w * WORDS; k += blockDim.x) {
+        const int q = k / WORDS, o = k % WORDS;
+        reinterpret_cast<int*>(reinterpret_cast<DomainBlob*>(dd->mbox[q] + dd->lay.blob[par]) + me)[o] = reinterpret_cast<const int*>(&s_blob)[o];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < w) dd_st_flag(reinterpret_cast<unsigned long long*>(dd->mbox[tid] + dd->lay.cflag[par]) + me, (unsigned long long)frame);
+    // ---- wait for every rank ----
+    __shared__ int s_off[DD_MAX_WORLD + 1], s_evoff[DD_MAX_WORLD + 1];
+    __shared__ int s_ok;
+    if (tid == 0) { s_ok = 1; stamp(gctl, TS_ALL_WAIT0); }
+    __syncthreads();
+    if (tid < w) {
+        const unsigned long long* fl = reinterpret_cast<const unsigned long long*>(dd->mbox[me] + dd->lay.cflag[par]) + tid;
+        if (!dd_wait_flag(fl, (unsigned long long)frame, gctl->error == -2 ? 0ull : dd->spin_timeout_ns)) s_ok = 0;
+    }
+    __syncthreads();
+    __threadfence_system();
+    if (tid == 0) stamp(gctl, TS_ALL_WAIT1);
+    // ---- merge ----
+    __shared__ Ctl s_ctl;   // S0 works on a copy; only the scoring fields go back (k_pairs is reading the grid fields meanwhile)
+    for (int i = tid; i < (int)(sizeof(Ctl) / 4); i += blockDim.x)
+        reinterpret_cast<uint32_t*>(&s_ctl)[i] = reinterpret_cast<const uint32_t*>(gctl)[i];
+    __syncthreads();
+    Ctl* ctl = &s_ctl;
+    const DomainBlob* blobs = reinterpret_cast<const DomainBlob*>(dd->mbox[me] + dd->lay.blob[par]);
+    if (tid == 0) {
+        int nnd = 0, nonfinite = 0, err = ctl->error;
+        if (!s_ok && !err) err = -2;
+        unsigned long long lastvel = 0ull;
+        int r1 = 0x7fffffff, r2 = 0x7fffffff;
+        int off = 0, evoff = 0;
         for (int q = 0; q < w; ++q) {
+            const DomainBlob bl = s_ok ? blobs[q] : s_blob;
+            nnd += bl.nnd;
+            nonfinite += bl.nonfinite;
+            lastvel = bl.lastvel > lastvel ? bl.lastvel : lastvel;
+            for (int k = 0; k < 2; ++k) {  // two smallest distinct ids of the union
+                const int v = bl.replan[k];
+                if (v < r1) { r2 = r1; r1 = v; } else if (v > r1 && v < r2) r2 = v;
+            }
+            if (bl.error && !err) err = bl.error;
             s_off[q] = off;
-            off += (q == me || !s_ok) ? 0 : min(nc[q], DD_CAND_CAP);
+            off += (q == me || !s_ok) ? 0 : min(bl.n_cand, DD_CAND_CAP);
+            s_evoff[q] = evoff;
+            evoff += (me == 0 && s_ok) ? min(bl.n_events, DD_EV_CAP) : 0;
         }
         s_off[w] = off;
-        ctl->n_cand2 = nloc + off;
+        s_evoff[w] = evoff;
+        ctl->nnd_acc = nnd;
+        ctl->nonfinite = nonfinite;
+        ctl->lastvel = lastvel;
+        ctl->replan1 = r1; ctl->replan2 = r2;
+        ctl->ev_count = evoff;
+        ctl->error = err;
+        dd->replan[0] = dd->replan[1] = 0x7fffffff;
+        if (comm) gctl->n_cand2 = nloc + off;   // k_force's candidate list: local survivors + everybody else's
     }
     __syncthreads();
-    const int cap = P->cap;
-    for (int q = 0; q < w; ++q) {
-        const int cnt = s_off[q + 1] - s_off[q];
-        const float4* src = reinterpret_cast<const float4*>(dd->mbox[me] + dd->lay.cand[par]) + (size_t)q * 2 * DD_CAND_CAP;
-        for (int k = tid; k < cnt; k += blockDim.x) {
-            const float4 A = src[2 * k], B = src[2 * k + 1];
-            const int annex = cap + s_off[q] + k;
-            b.srt.pv[annex] = make_float4(A.x, A.y, A.w, 0.f);  // comm::x reads pos.x and vel.x of the partner only (quirk Q2)
-            b.srt.c4[annex] = B;
-            list[nloc + s_off[q] + k] = make_float4(A.x, A.y, A.z, __int_as_float(annex));
+    if (comm) {
+        const int cap = P->cap;
+        for (int q = 0; q < w; ++q) {
+            const int cnt = s_off[q + 1] - s_off[q];
+            const float4* src = reinterpret_cast<const float4*>(dd->mbox[me] + dd->lay.cand[par]) + (size_t)q * 2 * DD_CAND_CAP;
+            for (int k = tid; k < cnt; k += blockDim.x) {
+                const float4 A = src[2 * k], B = src[2 * k + 1];
+                const int annex = cap + s_off[q] + k;
+                b.srt.pv[annex] = make_float4(A.x, A.y, A.w, 0.f);  // comm::x reads pos.x and vel.x of the partner only (quirk Q2)
+                b.srt.c4[annex] = B;
+                list[nloc + s_off[q] + k] = make_float4(A.x, A.y, A.z, __int_as_float(annex));
+            }
         }
+    }
+    if (me == 0) {  // gather every rank's done-events (own ones are already in b.events[0 .. own count)); S0 sorts them by id
+        const int2* evsrc = reinterpret_cast<const int2*>(dd->mbox[0] + dd->lay.events[par]);
+        // other ranks' events go behind our own: shift by our own count
+        const int own = s_evoff[1] - s_evoff[0];
+        for (int q = 1; q < w; ++q) {
+            const int cnt = s_evoff[q + 1] - s_evoff[q];
+            for (int k = tid; k < cnt; k += blockDim.x) b.events[s_evoff[q] + k] = evsrc[(size_t)q * DD_EV_CAP + k];
+        }
+        (void)own;
+    }
+    __threadfence();
+    __syncthreads();
+    // ---- S0: demo::run (demo.cpp:665-702) with the merged inputs, exactly as k_frame_begin does it on one GPU ----
+    __shared__ int2 s_ev[EV_SORT_CAP];
+    __shared__ float s_ft[1024];
+    __shared__ int s_flag[1024];
+    if (tid == 0) fold_avg_velocity(ctl);
+    __syncthreads();
+    const int was_finished = ctl->finished;
+    const int cnt = ctl->ev_count, nnd = ctl->nnd_acc;
+    __syncthreads();
+    if (!was_finished) demo_run_score(P, b, ctl, frame, cnt, nnd, true, s_ev, s_ft, s_flag);
+    __syncthreads();
+    if (tid == 0) {  // only the scoring fields go back
+        gctl->total_num_done = ctl->total_num_done;
+        gctl->run_avg = ctl->run_avg; gctl->M2 = ctl->M2; gctl->run_std = ctl->run_std;
+        gctl->avg_velocity = ctl->avg_velocity;
+        gctl->lastvel = ctl->lastvel; gctl->nonfinite = ctl->nonfinite;
+        gctl->finished = ctl->finished;
+        gctl->n_not_done = nnd;
+        gctl->replan1 = ctl->replan1; gctl->replan2 = ctl->replan2;
+        gctl->ev_count = 0;   // k_force of this frame collects the next frame's events and not-done count
+        gctl->nnd_acc = 0;
+        gctl->error = ctl->error;
     }
 }
 
