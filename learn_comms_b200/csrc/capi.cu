@@ -105,6 +105,9 @@ static const int GRAPH_LEVELS = 5;
 static const int GRAPH_BATCH = 1 << (GRAPH_LEVELS - 1);
 
 static int alloc_arrays(lc_sim* s, lc::AgentArrays& a, int n) {
+    CK(dalloc(&a.pvf, n)); s->allocs.push_back(a.pvf);
+    CK(dalloc(&a.pq, (size_t)n + 2)); s->allocs.push_back(a.pq);  // 2 float4 per slot PAIR, padded to a whole pair
+    CK(cudaMemset(a.pq, 0, sizeof(float4) * ((size_t)n + 2)));
     CK(dalloc(&a.pv, n)); s->allocs.push_back(a.pv);
     CK(dalloc(&a.vfh, n)); s->allocs.push_back(a.vfh);
     CK(dalloc(&a.goal, n)); s->allocs.push_back(a.goal);
@@ -124,6 +127,9 @@ static int build_graphs(lc_sim* s) {
         CK(cudaStreamEndCapture(s->st, &graph));
         CK(cudaGraphInstantiate(&s->gexec[g], graph, 0));
         CK(cudaGraphDestroy(graph));
+        // have the executable graph resident before its first launch: without this the first cudaGraphLaunch of each size
+        // pays the upload inside the caller's timed region (≈0.3 ms for the 16-frame graph)
+        CK(cudaGraphUpload(s->gexec[g], s->st));
     }
     return 0;
 }
@@ -326,12 +332,9 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         CKC(cudaEventCreateWithFlags(&s->side.fork, cudaEventDisableTiming));
         CKC(cudaEventCreateWithFlags(&s->side.join, cudaEventDisableTiming));
     }
-    CKB(alloc_arrays(s, s->b.cur, n));
-    CKB(alloc_arrays(s, s->b.srt, n + annex));  // annex: comm-partner payload of other ranks' candidates (dd_cand_body)
+    CKB(alloc_arrays(s, s->b.set[0], n + annex));  // annex: comm-partner payload of other ranks' candidates (dd_global_body)
+    CKB(alloc_arrays(s, s->b.set[1], n + annex));
     lc::Buffers& b = s->b;
-    CKC(dalloc(&b.posf, n)); s->allocs.push_back(b.posf);
-    CKC(dalloc(&b.srt_pq, (size_t)2 * ((n + 1) / 2))); s->allocs.push_back(b.srt_pq);
-    CKC(cudaMemset(b.srt_pq, 0, sizeof(float4) * 2 * ((size_t)(n + 1) / 2)));
     CKC(dalloc(&b.cellrank, n)); s->allocs.push_back(b.cellrank);
     CKC(dalloc(&b.slot_cell, n)); s->allocs.push_back(b.slot_cell);
     CKC(cudaMemset(b.slot_cell, 0, sizeof(int) * (size_t)n));

@@ -20,6 +20,12 @@
 namespace lc {
 using namespace lcm;
 
+// roles of the two state copies in the frame in flight (crowd.cuh Buffers)
+__device__ __forceinline__ const AgentArrays& set_in(const Buffers& b) { return b.set[b.ctl->in_set]; }       // frame-start state, read
+__device__ __forceinline__ const AgentArrays& set_out(const Buffers& b) { return b.set[b.ctl->in_set ^ 1]; }  // this frame's result, written
+__device__ __forceinline__ const AgentArrays& set_src(const Buffers& b) { return b.set[b.ctl->src_set]; }     // last frame's result (input of a re-sort)
+__device__ __forceinline__ const AgentArrays& set_live(const Buffers& b) { return b.set[b.ctl->live]; }       // state after the last executed frame
+
 // Domain mode: the input of a frame's counting sort is (a) last frame's local slots, read in place from `cur` — an
 // owned agent that stays on this rank is kept, one that left or was a ghost is skipped — followed by (b) the records the
 // left and (c) the right neighbour's k_collide stored into this rank's mailbox (migrants and ghosts).  No unpack copy and
@@ -48,7 +54,8 @@ __device__ __forceinline__ bool input_pos(const Params* P, const Buffers& b, int
         if (i >= b.dd->recv[1]) { const float4 r0 = dd_locate(P, b, i).plane(0); p = make_float2(r0.x, r0.y); return true; }
         if (!b.dd->keep[i]) return false;
     }
-    p = b.posf[i];
+    const float4 q = set_src(b).pvf[i];
+    p = make_float2(q.x, q.y);
     return true;
 }
 
@@ -253,9 +260,10 @@ __device__ void demo_run_score(const Params* __restrict__ P, const Buffers& b, C
             float ft = 0.f;
             if (id < n) {
                 int s = b.slot_of_id[id];
-                int4 mt = b.cur.meta[s];
+                const AgentArrays& last = b.set[ctl->live];
+                    int4 mt = last.meta[s];
                 if (!(mt.y & 1)) {
-                    float2 g = b.cur.goal[s], p = b.posf[s];
+                    float2 g = last.goal[s]; const float4 pf = last.pvf[s]; const float2 p = make_float2(pf.x, pf.y);
                     float l = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
                     ft = __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
                     flag = 1;
@@ -340,6 +348,12 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
             ctl->rebin = rebin;
             ctl->force_rebin = 0;
             ctl->dmax = 0u;
+            // roles of the two state copies (crowd.cuh Buffers): a re-sort scatters last frame's result into the other copy
+            // and the frame reads that; otherwise last frame's result is read in place
+            const int last = ctl->live;
+            ctl->src_set = last;
+            ctl->in_set = rebin ? last ^ 1 : last;
+            ctl->live = ctl->in_set ^ 1;
         }
         ctl->minx = ctl->miny = 0xffffffffu;
         ctl->maxx = ctl->maxy = 0u;
@@ -567,7 +581,9 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const bool rebin = ctl->rebin;
-    int s = i;   // between re-sorts the agents keep their slots: a straight copy of last frame's output
+    const AgentArrays& src = set_src(b);
+    const AgentArrays& dst = set_in(b);   // re-sort frames: this frame reads what is scattered here
+    int s = i;   // between re-sorts the agents keep their slots and last frame's output IS this frame's input (src == dst)
     if (rebin) {
         const int2 cr = b.cellrank[i];
         if (cr.x < 0) return;  // domain mode: a slot that is not part of this frame's local set (left, or was a ghost)
@@ -576,33 +592,46 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
     } else {
         b.pair_cnt[i] = 0;  // (k_bin does it on re-sort frames)
     }
-    float2 p, g;
-    float4 pv;
+    float2 p, g = make_float2(0.f, 0.f);
     int4 mt;
-    if (b.dd && i >= b.dd->recv[1]) {  // records of the neighbours' pack: (posf.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
+    if (b.dd && i >= b.dd->recv[1]) {  // records of the neighbours' pack: (pos.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
         const DDRec r = dd_locate(P, b, i);
         const float4 r0 = r.plane(0), r1 = r.plane(1), r2 = r.plane(2), r4 = r.plane(4);
-        p = make_float2(r0.x, r0.y); pv = r0; g = make_float2(r1.z, r1.w);
+        p = make_float2(r0.x, r0.y); g = make_float2(r1.z, r1.w);
         mt = make_int4(__float_as_int(r4.x), __float_as_int(r4.y), __float_as_int(r4.z), __float_as_int(r4.w));
-        b.srt.vfh[s] = make_float2(r1.x, r1.y);
-        b.srt.lgoal[s] = make_float2(r2.x, r2.y);
-        b.srt.facing[s] = make_float2(r2.z, r2.w);
-        b.srt.c4[s] = r.plane(3);
+        dst.pvf[s] = r0;
+        {
+            float* q = reinterpret_cast<float*>(dst.pq + 2 * (s >> 1)) + (s & 1);
+            q[0] = r0.x; q[2] = r0.y; q[4] = r0.z; q[6] = r0.w;
+        }
+        dst.vfh[s] = make_float2(r1.x, r1.y);
+        dst.goal[s] = g;
+        dst.lgoal[s] = make_float2(r2.x, r2.y);
+        dst.facing[s] = make_float2(r2.z, r2.w);
+        dst.c4[s] = r.plane(3);
+        dst.meta[s] = mt;
     } else {
-        p = b.posf[i]; pv = b.cur.pv[i]; mt = b.cur.meta[i]; g = b.cur.goal[i];
+        const float4 pf = src.pvf[i];
+        p = make_float2(pf.x, pf.y);
+        mt = src.meta[i];
         if (b.dd && b.dd->keep[i] == 2) mt.y |= META_GHOST;  // crossed into the adjacent strip last frame: its ghost from now on
-        b.srt.vfh[s] = b.cur.vfh[i];
-        b.srt.lgoal[s] = b.cur.lgoal[i];
-        b.srt.facing[s] = b.cur.facing[i];
-        b.srt.c4[s] = b.cur.c4[i];
+        if (rebin) {
+            g = src.goal[i];
+            dst.pvf[s] = pf;
+            {   // pair-interleaved copy for the packed pair loop: slots (2k, 2k+1) -> (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
+                float* q = reinterpret_cast<float*>(dst.pq + 2 * (s >> 1)) + (s & 1);
+                q[0] = pf.x; q[2] = pf.y; q[4] = pf.z; q[6] = pf.w;
+            }
+            dst.vfh[s] = src.vfh[i];
+            dst.goal[s] = g;
+            dst.lgoal[s] = src.lgoal[i];
+            dst.facing[s] = src.facing[i];
+            dst.c4[s] = src.c4[i];
+            dst.meta[s] = mt;
+        } else if (mt.y & 1) {
+            g = src.goal[i];  // only the replan gate below needs it
+        }
     }
-    b.srt.pv[s] = make_float4(p.x, p.y, pv.z, pv.w);
-    {   // pair-interleaved copy for the packed pair loop: slots (2k, 2k+1) -> (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
-        float* q = reinterpret_cast<float*>(b.srt_pq + 2 * (s >> 1)) + (s & 1);
-        q[0] = p.x; q[2] = p.y; q[4] = pv.z; q[6] = pv.w;
-    }
-    b.srt.goal[s] = g;
-    b.srt.meta[s] = mt;
     // The id -> slot table is a scattered 4-byte store per agent (a 32-byte sector each).  Its only reader inside the
     // frame loop is the time-out walk of the NEXT k_frame_begin (demo.cpp:691-700, id order); lc_set_state rebuilds it
     // in k_snapshot.  So it is written only by the frame before the time-out one (and every frame after it).
@@ -732,7 +761,7 @@ __global__ void __launch_bounds__(1024) k_refine(const Params* __restrict__ P, B
 template <bool FIRST, class F>
 __device__ __forceinline__ void pair_eval(const Buffers& b, int s, int j, float px, float py, float vx, float vy, float RR,
                                           float near_c, int& n_near, int& n_overlap, F&& f) {
-    const float4 q = __ldg(&b.srt.pv[j]);
+    const float4 q = __ldg(&set_in(b).pvf[j]);
     const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
     const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
     const float a = dot2(dvx, dvy, dvx, dvy);
@@ -776,10 +805,11 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
     const int row_hi = min(max((int)floorf(yh + (1e-3f + 1e-6f * fabsf(yh))), HALF ? row_b : 0), ny - 1);
     const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
     const float2 RR2 = make_float2(RR, RR);
-    const float4* __restrict__ pq = b.srt_pq;
+    const float4* __restrict__ pq = set_in(b).pq;
+    const float4* __restrict__ pvf = set_in(b).pvf;
     // scalar version of the filter for the odd slot at either end of a row range
     auto single = [&](int j) {
-        const float4 q = __ldg(&b.srt.pv[j]);
+        const float4 q = __ldg(&pvf[j]);
         const float mx = __fsub_rn(q.x, px), my = __fsub_rn(q.y, py), dvx = __fsub_rn(q.z, vx), dvy = __fsub_rn(q.w, vy);
         const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
         if (bq > 0.f && c >= near_c) return;
@@ -897,7 +927,7 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
     stamp_entry(b.ctl, TS_PAIRS);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
-    const float4 me = b.srt.pv[s];
+    const float4 me = set_in(b).pvf[s];
     const size_t stride = (size_t)P->cap;
     scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [&](int j) {
         // entries past PAIR_CAP are only counted: k_force then scans the whole disc for that agent
@@ -915,7 +945,7 @@ __global__ void __launch_bounds__(128) k_pair_count(const Params* __restrict__ P
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     long long tested = 0;
     if (s < P->n) {
-        const float4 me = b.srt.pv[s];
+        const float4 me = set_in(b).pvf[s];
         scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [](int) {}, &tested);
     }
     for (int o = 16; o > 0; o >>= 1) tested += __shfl_xor_sync(0xffffffffu, tested, o);
@@ -984,6 +1014,8 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    const AgentArrays& in = set_in(b);
+    const AgentArrays& out = set_out(b);
     stamp_entry(ctl, TS_FORCE);
     __shared__ lcw::Wall s_walls[WALLS ? WALL_SMEM : 1];
     const lcw::Wall* walls = nullptr;
@@ -999,7 +1031,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
     if (s < n) {
         np_early = b.pair_cnt[s];
         j_first = b.pair_list[s];   // (stale or uninitialised when the count is 0: clamped before use)
-        pf(&b.srt.meta[s]); pf(&b.srt.goal[s]); pf(&b.srt.lgoal[s]); pf(&b.srt.facing[s]); pf(&b.srt.c4[s]); pf(&b.srt.vfh[s]);
+        pf(&in.meta[s]); pf(&in.goal[s]); pf(&in.lgoal[s]); pf(&in.facing[s]); pf(&in.c4[s]); pf(&in.vfh[s]);
     }  // (k_force 81 -> 77 us at 1 M agents)
     // Third pruning stage of the comm-partner candidates, per block: the 128 agents of a block are neighbours in cell
     // order, so they share a small bounding box B.  Candidate k can be the arg-max of comm.cpp:201-220 for some query
@@ -1016,7 +1048,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         if (threadIdx.x == 0) { s_bb[0] = s_bb[1] = 0xffffffffu; s_bb[2] = s_bb[3] = 0u; s_bb[4] = 0u; s_nc = 0; }
         __syncthreads();
         const bool valid = s < n;
-        const float4 me0 = valid ? b.srt.pv[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 me0 = valid ? in.pvf[s] : make_float4(0.f, 0.f, 0.f, 0.f);
         const uint32_t mnx = __reduce_min_sync(0xffffffffu, valid ? f2ord(me0.x) : 0xffffffffu);
         const uint32_t mxx = __reduce_max_sync(0xffffffffu, valid ? f2ord(me0.x) : 0u);
         const uint32_t mny = __reduce_min_sync(0xffffffffu, valid ? f2ord(me0.y) : 0xffffffffu);
@@ -1027,7 +1059,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         __syncthreads();
         if (valid && np_early > 0) {  // the first list entry has arrived by now: get its partner on the way
             const int jc = min(max(j_first, 0), n - 1);
-            pf(&b.srt.pv[jc]); pf(&b.srt.meta[jc]);
+            pf(&in.pvf[jc]); pf(&in.meta[jc]);
         }
         const float bx0 = ord2f(s_bb[0]), by0 = ord2f(s_bb[1]), bx1 = ord2f(s_bb[2]), by1 = ord2f(s_bb[3]);
         float lmax = 0.f;
@@ -1055,9 +1087,9 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         if (s_nc <= CAND_SMEM) { cand = s_cand; ncand = s_nc; } else { cand = gc; ncand = nc; }
     }
     if (s < n) {
-        const float4 me = b.srt.pv[s];
+        const float4 me = in.pvf[s];
         const float px = me.x, py = me.y, vx = me.z, vy = me.w;
-        const int id = b.srt.meta[s].x;
+        const int id = in.meta[s].x;
 
         // The pair loop runs first, while only (pos, vel, id) are live, so that it gets by with few registers; the
         // rest of the agent's state is loaded after it.  Order of the float operations is unaffected.
@@ -1066,7 +1098,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         float hfx[MAX_HITS], hfy[MAX_HITS];
         int cnt = 0, n_near = 0, n_overlap = 0;
         auto hit = [&](int j, float fx, float fy) {
-            if (cnt < MAX_HITS) { hid[cnt] = __ldg(&b.srt.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
+            if (cnt < MAX_HITS) { hid[cnt] = __ldg(&in.meta[j].x); hfx[cnt] = fx; hfy[cnt] = fy; }
             ++cnt;
         };
         const int np = np_early;
@@ -1079,7 +1111,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             scan_neighbours<true>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, n_near, n_overlap, hit);
         }
         float ttcFx = 0.f, ttcFy = 0.f;
-        int* lst = ((P->flags & 4u) && !(b.srt.meta[s].y & META_GHOST)) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
+        int* lst = ((P->flags & 4u) && !(in.meta[s].y & META_GHOST)) ? b.nbr_list + (size_t)id * b.list_cap : nullptr;
         if (cnt <= MAX_HITS) {
             int last = -1;
             for (int k = 0; k < cnt; ++k) {
@@ -1101,7 +1133,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
                 float bfx = 0.f, bfy = 0.f;
                 scan_neighbours<false>(b, ctl, s, px, py, vx, vy, P->RR, P->near_c, dummy0, dummy1,
                                        [&](int j, float fx, float fy) {
-                                           int v = __ldg(&b.srt.meta[j].x);
+                                           int v = __ldg(&in.meta[j].x);
                                            if (v > last && v < bid) { bid = v; bfx = fx; bfy = fy; }
                                        });
                 ttcFx = __fadd_rn(ttcFx, bfx);
@@ -1119,7 +1151,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
                 }
             }
         }
-        int4 mt = b.srt.meta[s];
+        int4 mt = in.meta[s];
         const bool owned = !(mt.y & META_GHOST);  // ghosts are advanced too (the collision pass needs their integrated
                                                   // position) but never counted: their owner does that
         b.diag_cnt[s] = cnt;  // slot-indexed (coalesced); lc_get_neighbor_counts translates to ids (k_get_diag)
@@ -1127,10 +1159,10 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         b.near_cnt[s] = n_near;
         if (n_overlap && owned) atomicAdd(&ctl->overlap2, (unsigned long long)n_overlap);
 
-        const float2 goal = b.srt.goal[s];
-        float2 lgoal = b.srt.lgoal[s];
-        float2 facing = b.srt.facing[s];
-        float4 c4 = b.srt.c4[s];
+        const float2 goal = in.goal[s];
+        float2 lgoal = in.lgoal[s];
+        float2 facing = in.facing[s];
+        float4 c4 = in.c4[s];
         const bool done_before = mt.y & 1;
         float forcex = 0.f, forcey = 0.f;
 
@@ -1163,8 +1195,8 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             else for (int k = 0; k < ncand; ++k) consider(__ldg(&cand[k]));
             if (best_id < 0) atomicCAS(&ctl->error, 0, -3);  // comm.cpp:273-285: null partner is UB in the reference
             b.diag_partner[s] = best_id;  // slot-indexed; lc_get_partners translates to ids (k_get_diag)
-            const float4 pj = __ldg(&b.srt.pv[best_slot]);
-            const float4 cj = __ldg(&b.srt.c4[best_slot]);
+            const float4 pj = __ldg(&in.pvf[best_slot]);
+            const float4 cj = __ldg(&in.c4[best_slot]);
             // comm.cpp:144-192 x(): COSINE_REL + PROX + SOFTSIGN_GOAL; partner (x, y) of a vec3 = (x, 0): quirk Q2
             const float rightx = facing.y, righty = -facing.x;
             const float dvx = __fsub_rn(pj.z, vx), dvy = __fsub_rn(0.f, vy);
@@ -1272,7 +1304,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         forcey = __fadd_rn(forcey, __fadd_rn(goalFy, ttcFy));
 
         // ---- S3a: physics::simulate leap-frog (physics.cpp:41-51), mass == 1 ----
-        const float2 vbh = b.srt.vfh[s];
+        const float2 vbh = in.vfh[s];
         float hx = __fadd_rn(vbh.x, __fmul_rn(LC_DT, forcex)), hy = __fadd_rn(vbh.y, __fmul_rn(LC_DT, forcey));
         const float h2 = dot3_xz(hx, hy, hx, hy);
         if (h2 > 1.f) {
@@ -1282,13 +1314,13 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
         const float nvx = __fadd_rn(__fdiv_rn(hx, 2.f), __fdiv_rn(vbh.x, 2.f));
         const float nvy = __fadd_rn(__fdiv_rn(hy, 2.f), __fdiv_rn(vbh.y, 2.f));
         const float npx = __fadd_rn(px, __fmul_rn(hx, LC_DT)), npy = __fadd_rn(py, __fmul_rn(hy, LC_DT));
-        b.cur.pv[s] = make_float4(npx, npy, nvx, nvy);
-        b.cur.vfh[s] = make_float2(hx, hy);
-        b.cur.goal[s] = goal;
-        b.cur.lgoal[s] = lgoal;
-        b.cur.facing[s] = facing;
-        b.cur.c4[s] = c4;
-        b.cur.meta[s] = mt;
+        out.pv[s] = make_float4(npx, npy, nvx, nvy);
+        out.vfh[s] = make_float2(hx, hy);
+        out.goal[s] = goal;
+        out.lgoal[s] = lgoal;
+        out.facing[s] = facing;
+        out.c4[s] = c4;
+        out.meta[s] = mt;
     }
     // demo.cpp:667-669: all_done of the next frame needs the number of agents that are not done after lookahead
     const int nnd = __syncthreads_count(not_done_after);
@@ -1340,6 +1372,8 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
+    const AgentArrays& in = set_in(b);
+    const AgentArrays& out = set_out(b);
     stamp_entry(ctl, TS_COLLIDE);
     __shared__ lcw::Wall s_walls[WALLS ? WALL_SMEM : 1];
     const lcw::Wall* walls = nullptr;
@@ -1350,23 +1384,23 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
     float px = 0.f, py = 0.f, speed = 0.f, disp = 0.f;
     uint32_t lv_id = 0u;
     if (valid) {
-        const float4 me = b.cur.pv[s];
+        const float4 me = out.pv[s];
         px = me.x; py = me.y;
         const float qx = me.x, qy = me.y;
-        const int4 mt = b.cur.meta[s];
+        const int4 mt = out.meta[s];
         int nn = b.near_cnt[s];
         if (nn > 0) {
-            float2 h = b.cur.vfh[s];
+            float2 h = out.vfh[s];
             int hid[MAX_NEAR];
             float hax[MAX_NEAR], hay[MAX_NEAR];
             int cnt = 0;
             if (nn <= MAX_NEAR) {
                 for (int k = 0; k < nn; ++k) {
                     const int j = b.near_idx[(size_t)s * MAX_NEAR + k];
-                    const float4 o = __ldg(&b.cur.pv[j]);
+                    const float4 o = __ldg(&out.pv[j]);
                     float ax, ay;
                     if (circ_circ_hit(qx, qy, o.x, o.y, P->r, P->RR, ax, ay)) {
-                        hid[cnt] = __ldg(&b.cur.meta[j].x); hax[cnt] = ax; hay[cnt] = ay; ++cnt;
+                        hid[cnt] = __ldg(&out.meta[j].x); hax[cnt] = ax; hay[cnt] = ay; ++cnt;
                     }
                 }
                 int last = -1;
@@ -1382,7 +1416,7 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
             } else {
                 // near-list overflow (more than MAX_NEAR agents within ~0.34 m): walk the cell block, one hit per pass
                 const int nx = ctl->nx, ny = ctl->ny, st = ctl->stencil, stx = ctl->stencil_x;
-                const float4 old = b.srt.pv[s];  // frame-start position decides the cell block
+                const float4 old = in.pvf[s];  // frame-start position decides the cell block
                 int ix = min(max((int)floorf((old.x - ctl->x0) / ctl->hx), 0), nx - 1);
                 int iy = min(max((int)floorf((old.y - ctl->y0) / ctl->h), 0), ny - 1);
                 int last = -1;
@@ -1393,10 +1427,10 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                         const int j0 = b.cell_start[yy * nx + max(ix - stx, 0)], j1 = b.cell_start[yy * nx + min(ix + stx, nx - 1) + 1];
                         for (int j = j0; j < j1; ++j) {
                             if (j == s) continue;
-                            const float4 o = __ldg(&b.cur.pv[j]);
+                            const float4 o = __ldg(&out.pv[j]);
                             float ax, ay;
                             if (circ_circ_hit(qx, qy, o.x, o.y, P->r, P->RR, ax, ay)) {
-                                int v = __ldg(&b.cur.meta[j].x);
+                                int v = __ldg(&out.meta[j].x);
                                 if (v > last && v < bid) { bid = v; bax = ax; bay = ay; }
                             }
                         }
@@ -1408,7 +1442,7 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                 }
             }
             if (cnt) {
-                b.cur.vfh[s] = h;
+                out.vfh[s] = h;
                 if (!(mt.y & META_GHOST)) atomicAdd(&ctl->coll_hits, (unsigned long long)cnt);
             }
         }
@@ -1416,7 +1450,7 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
             // physics.cpp:60,67-69: static_bvh->query at the integrated position, pushed out after the agent hits.
             // BVH::query_(Circ*) (BVH.cpp:106-138): depth first, left before right; inner nodes are entered through the
             // same single-point test as the leaves (quirk Q8), so hits can be missed exactly as the reference misses them.
-            float2 h = b.cur.vfh[s];
+            float2 h = out.vfh[s];
             int wcnt = 0, sp = 0;
             int stack[48];
             stack[sp++] = 0;
@@ -1431,17 +1465,21 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                 }
             }
             if (wcnt) {
-                b.cur.vfh[s] = h;
+                out.vfh[s] = h;
                 atomicAdd(&ctl->wall_hits, (unsigned long long)wcnt);
             }
         }
-        b.posf[s] = make_float2(px, py);
+        out.pvf[s] = make_float4(px, py, me.z, me.w);  // the state all_sync publishes = the next frame's frame-start state
+        {   // ... and its pair-interleaved copy for the next frame's pair loop
+            float* q = reinterpret_cast<float*>(out.pq + 2 * (s >> 1)) + (s & 1);
+            q[0] = px; q[2] = py; q[4] = me.z; q[6] = me.w;
+        }
         {
             const float ex = px - qx, ey = py - qy;
             disp = LC_DT * 1.0001f + sqrtf(ex * ex + ey * ey);
         }
         if constexpr (WALLS) {  // replan gate of the coming frame (ai.cpp:152-163) on the position all_sync publishes
-            const float2 g = b.cur.goal[s];
+            const float2 g = out.goal[s];
             walled_gate(P, b, walls, mt.x, px, py, g.x, g.y);
         }
         speed = __fsqrt_rn(dot3_xz(me.z, me.w, me.z, me.w));
@@ -1461,6 +1499,7 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
 
 // reductions of an arbitrary state (after lc_create / lc_set_state)
 __global__ void __launch_bounds__(128) k_init_reduce(const Params* __restrict__ P, Buffers b) {
+    const AgentArrays& live = set_live(b);
     Ctl* ctl = b.ctl;
     const int n = P->n;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1468,12 +1507,11 @@ __global__ void __launch_bounds__(128) k_init_reduce(const Params* __restrict__ 
     float x = 0.f, y = 0.f, speed = 0.f;
     int nd = 0;
     if (valid) {
-        float2 p = b.posf[i];
-        float4 pv = b.cur.pv[i];
-        x = p.x; y = p.y;
+        const float4 pv = live.pvf[i];
+        x = pv.x; y = pv.y;
         speed = __fsqrt_rn(dot3_xz(pv.z, pv.w, pv.z, pv.w));
-        nd = !(b.cur.meta[i].y & 1);
-        b.slot_of_id[b.cur.meta[i].x] = i;
+        nd = !(live.meta[i].y & 1);
+        b.slot_of_id[live.meta[i].x] = i;
     }
     const int cnt = __syncthreads_count(nd);
     if (threadIdx.x == 0 && cnt) atomicAdd(&ctl->nnd_acc, cnt);
@@ -1482,12 +1520,14 @@ __global__ void __launch_bounds__(128) k_init_reduce(const Params* __restrict__ 
 
 // replan gate of the coming frame from an arbitrary state (after lc_create / lc_set_state); later frames: k_collide's tail
 __global__ void __launch_bounds__(128) k_walled_gate(const Params* __restrict__ P, Buffers b) {
+    const AgentArrays& live = set_live(b);
     __shared__ lcw::Wall s_walls[WALL_SMEM];
     const lcw::Wall* walls = stage_walls(P, b, s_walls);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P->n) return;
-    const float2 p = b.posf[i], g = b.cur.goal[i];
-    walled_gate(P, b, walls, b.cur.meta[i].x, p.x, p.y, g.x, g.y);
+    const float4 p = live.pvf[i];
+    const float2 g = live.goal[i];
+    walled_gate(P, b, walls, live.meta[i].x, p.x, p.y, g.x, g.y);
 }
 
 __global__ void __launch_bounds__(1024) k_finalize(const Params* __restrict__ P, Buffers b) {
@@ -1501,20 +1541,21 @@ __global__ void __launch_bounds__(1024) k_finalize(const Params* __restrict__ P,
 __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P, Buffers b, float2* pos, float2* vel,
                                                     float2* vfh, float* c3, float2* facing, float2* lgoal,
                                                     float* goal_dist, int* num_done, int* owned) {
+    const AgentArrays& live = set_live(b);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
-    const int4 mt = b.cur.meta[s];
+    const int4 mt = live.meta[s];
     if (mt.y & META_GHOST) return;  // the owner reports it
     const int id = b.ext_of ? b.ext_of[mt.x] : mt.x;  // the caller's agent index
     if (owned) owned[id] = 1;
-    const float4 pv = b.cur.pv[s];
-    const float4 c4 = b.cur.c4[s];
-    if (pos) pos[id] = b.posf[s];
+    const float4 pv = live.pvf[s];
+    const float4 c4 = live.c4[s];
+    if (pos) pos[id] = make_float2(pv.x, pv.y);
     if (vel) vel[id] = make_float2(pv.z, pv.w);
-    if (vfh) vfh[id] = b.cur.vfh[s];
+    if (vfh) vfh[id] = live.vfh[s];
     if (c3) { c3[3 * id] = c4.x; c3[3 * id + 1] = c4.y; c3[3 * id + 2] = c4.z; }
-    if (facing) facing[id] = b.cur.facing[s];
-    if (lgoal) lgoal[id] = b.cur.lgoal[s];
+    if (facing) facing[id] = live.facing[s];
+    if (lgoal) lgoal[id] = live.lgoal[s];
     if (goal_dist) goal_dist[id] = c4.w;
     if (num_done) num_done[id] = P->n_walls > 0 ? b.w.num_done[mt.x] : (mt.y & 1);  // Agent::num_done (waypoints passed)
 }
@@ -1523,9 +1564,10 @@ __global__ void __launch_bounds__(256) k_get_state(const Params* __restrict__ P,
 // is a 32-byte sector per agent and frame — and brought into id order only when the host asks for them.  Ids this rank
 // does not own keep whatever the table held.
 __global__ void __launch_bounds__(256) k_get_diag(const Params* __restrict__ P, Buffers b) {
+    const AgentArrays& live = set_live(b);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
-    const int4 mt = b.cur.meta[s];
+    const int4 mt = live.meta[s];
     if (mt.y & META_GHOST) return;
     b.partner_id[mt.x] = b.diag_partner[s];
     b.nbr_cnt[mt.x] = b.diag_cnt[s];
@@ -1534,8 +1576,9 @@ __global__ void __launch_bounds__(256) k_get_diag(const Params* __restrict__ P, 
 // domain mode, host-facing shard: (id, pos, vel) of the agents this rank owns, compacted (order arbitrary)
 __global__ void __launch_bounds__(256) k_get_owned(const Params* __restrict__ P, Buffers b, int* ids, float2* pos, float2* vel,
                                                     int* count) {
+    const AgentArrays& live = set_live(b);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    const int4 mt = s < P->n ? b.cur.meta[s] : make_int4(0, META_GHOST, 0, 0);
+    const int4 mt = s < P->n ? live.meta[s] : make_int4(0, META_GHOST, 0, 0);
     const bool own = !(mt.y & META_GHOST);
     const unsigned m = __ballot_sync(0xffffffffu, own);
     int base = 0;
@@ -1543,9 +1586,9 @@ __global__ void __launch_bounds__(256) k_get_owned(const Params* __restrict__ P,
     base = __shfl_sync(0xffffffffu, base, 0);
     if (own) {
         const int k = base + __popc(m & ((1u << (threadIdx.x & 31)) - 1u));
-        const float4 pv = b.cur.pv[s];
+        const float4 pv = live.pvf[s];
         ids[k] = b.ext_of ? b.ext_of[mt.x] : mt.x;
-        pos[k] = b.posf[s];
+        pos[k] = make_float2(pv.x, pv.y);
         vel[k] = make_float2(pv.z, pv.w);
     }
 }
@@ -1557,9 +1600,10 @@ void launch_get_owned(const Params* dP, int n, const Buffers& b, int* ids, float
 
 // per-agent private LCG streams: agent id draws x0 * 16807^((frame-1)*n + id + 1) in frame `frame` (Seeder.cpp, LMP.cpp:261-263)
 __global__ void __launch_bounds__(256) k_set_rng(const Params* __restrict__ P, Buffers b, uint32_t base) {
+    const AgentArrays& live = set_live(b);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
-    int4 mt = b.cur.meta[s];
+    int4 mt = live.meta[s];
     uint32_t e = (uint32_t)mt.x + 1u, a = 16807u, x = base;
     while (e) {
         if (e & 1u) x = lcg_mul(x, a);
@@ -1567,7 +1611,7 @@ __global__ void __launch_bounds__(256) k_set_rng(const Params* __restrict__ P, B
         e >>= 1;
     }
     mt.z = (int)x;
-    b.cur.meta[s] = mt;
+    live.meta[s] = mt;
 }
 
 // state upload in id order (slot == id): demo.cpp:563-581 create_robo / teacher forcing
@@ -1579,15 +1623,17 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P->n) return;
     // bring the agent with id i to slot i
+    const AgentArrays& live = set_live(b);
+    const AgentArrays& snap = b.set[b.ctl->live ^ 1];  // k_snapshot's copy of the state before the call
     const int so = init ? i : b.slot_of_id[i];
-    float4 pv = init ? make_float4(0, 0, 0, 0) : b.srt.pv[so];      // srt holds a snapshot made by the caller
+    float4 pv = init ? make_float4(0, 0, 0, 0) : snap.pvf[so];
     float2 p = init ? make_float2(0, 0) : make_float2(pv.x, pv.y);
-    float2 h = init ? make_float2(0, 0) : b.srt.vfh[so];
-    float2 g = init ? make_float2(0, 0) : b.srt.goal[so];
-    float2 lg = init ? make_float2(0, 0) : b.srt.lgoal[so];
-    float2 fc = init ? make_float2(0, 0) : b.srt.facing[so];
-    float4 c4 = init ? make_float4(0, 0, 0, 0) : b.srt.c4[so];
-    int4 mt = init ? make_int4(ids ? ids[i] : i, 0, 0, 0) : b.srt.meta[so];
+    float2 h = init ? make_float2(0, 0) : snap.vfh[so];
+    float2 g = init ? make_float2(0, 0) : snap.goal[so];
+    float2 lg = init ? make_float2(0, 0) : snap.lgoal[so];
+    float2 fc = init ? make_float2(0, 0) : snap.facing[so];
+    float4 c4 = init ? make_float4(0, 0, 0, 0) : snap.c4[so];
+    int4 mt = init ? make_int4(ids ? ids[i] : i, 0, 0, 0) : snap.meta[so];
     // host tables: at creation (init) they were gathered by the host in local order; afterwards they are indexed by the
     // caller's agent index
     const int e = (init || !b.ext_of) ? i : b.ext_of[i];
@@ -1609,14 +1655,13 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
     }
     if (goal) g = goal[e];
     if (min_time) mt.w = __float_as_int(min_time[e]);
-    b.cur.pv[i] = make_float4(p.x, p.y, pv.z, pv.w);
-    b.posf[i] = p;
-    b.cur.vfh[i] = h;
-    b.cur.goal[i] = g;
-    b.cur.lgoal[i] = lg;
-    b.cur.facing[i] = fc;
-    b.cur.c4[i] = c4;
-    b.cur.meta[i] = mt;
+    live.pvf[i] = make_float4(p.x, p.y, pv.z, pv.w);
+    live.vfh[i] = h;
+    live.goal[i] = g;
+    live.lgoal[i] = lg;
+    live.facing[i] = fc;
+    live.c4[i] = c4;
+    live.meta[i] = mt;
     if (!init) {  // slot == id from here on: the per-slot diagnostics follow (launch_set_state ran k_get_diag first)
         b.diag_partner[i] = b.partner_id[i];
         b.diag_cnt[i] = b.nbr_cnt[i];
@@ -1627,16 +1672,16 @@ __global__ void __launch_bounds__(256) k_set_state(const Params* __restrict__ P,
 __global__ void __launch_bounds__(256) k_snapshot(const Params* __restrict__ P, Buffers b) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P->n) return;
-    float4 pv = b.cur.pv[i];
-    float2 p = b.posf[i];
-    b.srt.pv[i] = make_float4(p.x, p.y, pv.z, pv.w);
-    b.srt.vfh[i] = b.cur.vfh[i];
-    b.srt.goal[i] = b.cur.goal[i];
-    b.srt.lgoal[i] = b.cur.lgoal[i];
-    b.srt.facing[i] = b.cur.facing[i];
-    b.srt.c4[i] = b.cur.c4[i];
-    const int4 mt = b.cur.meta[i];
-    b.srt.meta[i] = mt;
+    const AgentArrays& live = set_live(b);
+    const AgentArrays& snap = b.set[b.ctl->live ^ 1];
+    snap.pvf[i] = live.pvf[i];
+    snap.vfh[i] = live.vfh[i];
+    snap.goal[i] = live.goal[i];
+    snap.lgoal[i] = live.lgoal[i];
+    snap.facing[i] = live.facing[i];
+    snap.c4[i] = live.c4[i];
+    const int4 mt = live.meta[i];
+    snap.meta[i] = mt;
     b.slot_of_id[mt.x] = i;  // k_reorder does not maintain the table (see there)
 }
 

@@ -23,7 +23,7 @@ constexpr int CELL_ALLOC = SCAN_TILES * SCAN_TILE;    // allocation of cell_coun
 constexpr int EV_SORT_CAP = 2048; // events sorted in shared memory; above this the per-id path is used
 
 // One copy of the per-agent state, structure of arrays.  All arrays have n elements.
-//   pv     (pos.x, pos.z, vel.x, vel.z)          Dynamics.h:4,6   — one 16-byte load per neighbour in the pair loop
+//   pv     (pos.x, pos.z, vel.x, vel.z)          Dynamics.h:4,6   — integrated, not yet pushed out (k_force -> k_collide)
 //   vfh    vel_forehalf.xz                       Dynamics.h:7
 //   goal   final_goal                            Agent.h:11
 //   lgoal  local_goal                            Agent.h:12
@@ -31,6 +31,9 @@ constexpr int EV_SORT_CAP = 2048; // events sorted in shared memory; above this 
 //   c4     (c[0], c[1], c[2], goal_dist)         CommComp.h:14, Agent.h:19
 //   meta   (id, flags, rng, min_time bits)       Agent.h:14,17-18; flags bit0 = num_done, bit1 = overhead_counted
 struct AgentArrays {
+    float4* pvf;    // (pos.x, pos.z, vel.x, vel.z) at the END of the frame that wrote the set (after the push-out) = the
+                    // frame-start state of the next frame: what all_sync publishes (Pool.cpp:69-91)
+    float4* pq;     // [2 * ceil(n/2)] pair-interleaved copy of pvf: (x0,x1,z0,z1), (vx0,vx1,vz0,vz1) per slot pair
     float4* pv;
     float2* vfh;
     float2* goal;
@@ -60,7 +63,8 @@ struct Ctl {
     // Skin: the agents are re-sorted into cells only every Params::rebin_every frames.  In between, slot order and
     // cell_start stay as they are; a search from an agent's CURRENT position reaches cutoff + skin, where skin bounds how
     // far anybody has moved since the re-sort, so the candidate set is still a superset and the exact predicate decides.
-    int rebin;         // this frame re-sorts (k_bin / k_scan_hull / scatter in k_reorder); else k_reorder copies slot to slot
+    int in_set, src_set, live;   // Buffers::set roles of the frame in flight (crowd.cuh Buffers)
+    int rebin;         // this frame re-sorts (k_bin / k_scan_hull / scatter in k_reorder); else the slots stay and the copies swap roles
     int since;         // frames since the last re-sort
     int force_rebin;   // the state was replaced (lc_create / lc_set_state)
     float skin;        // sum of the per-frame maximum displacements since the last re-sort, at this frame's start
@@ -149,10 +153,11 @@ struct WalledArrays {
 };
 
 struct Buffers {
-    AgentArrays cur;   // state at frame start (arbitrary slot order) / K4 output (pre-push), new slot order
-    AgentArrays srt;   // frame-start state reordered by grid cell
-    float4* srt_pq;    // [2 * ceil(n/2)] pair-interleaved copy of srt.pv: (x0,x1,z0,z1), (vx0,vx1,vz0,vz1) per slot pair
-    float2* posf;      // final (post-push) positions, same order as cur
+    // Two copies of the per-agent state.  A frame reads one (frame-start state: Ctl::in_set) and writes the other, slot for
+    // slot, so between grid re-sorts the roles simply alternate and nothing is copied; a re-sort frame first scatters the
+    // last frame's output (Ctl::src_set) into the other copy and reads that.  Ctl::live = the copy holding the state after
+    // the last executed frame (what lc_get_state reads).
+    AgentArrays set[2];
     int2* cellrank;    // (cell, rank within cell) per agent, cur order
     int* slot_cell;    // [n] by slot: the cell the agent was sorted into at the last re-sort
     int* cell_count;   // [CELL_ALLOC]

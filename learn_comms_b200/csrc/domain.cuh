@@ -90,6 +90,7 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
     if ((int)(blockIdx.x * blockDim.x) >= n) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int me = P->dd_rank;
+    const AgentArrays& cur = set_live(b);   // the frame that just ended wrote it (before the first frame: the initial state)
     const uint32_t frame = ctl->frame + 1u;
     const int par = frame & 1u;
     // Slot allocation in the neighbours' regions keeps the agents' order (ballot prefix inside the warp, warp totals, one
@@ -101,11 +102,12 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
     float2 p = make_float2(0.f, 0.f), g = make_float2(0.f, 0.f);
     bool owned = false;
     if (i < n) {
-        mt = b.cur.meta[i];
+        mt = cur.meta[i];
         owned = !(mt.y & META_GHOST);
         if (owned) {
-            p = b.posf[i];
-            g = b.cur.goal[i];
+            const float4 pf = cur.pvf[i];
+            p = make_float2(pf.x, pf.y);
+            g = cur.goal[i];
             dd_route(P, p.x, role);
         }
         // stays in the local set: as owner, or — having just crossed into the adjacent strip while still inside our ghost
@@ -130,9 +132,9 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
     for (int k = 0; k < 3; ++k) rank_in_blk[k] += s_wcnt[k][wid];
     if (!owned) return;
     if (role[0] | role[2]) {  // a boundary agent: its record goes to the adjacent rank(s), as owner (migration) or as ghost
-        const float4 pv = b.cur.pv[i];
-        const float2 vfh = b.cur.vfh[i], lg = b.cur.lgoal[i], fc = b.cur.facing[i];
-        const float4 c4 = b.cur.c4[i];
+        const float4 pv = cur.pvf[i];
+        const float2 vfh = cur.vfh[i], lg = cur.lgoal[i], fc = cur.facing[i];
+        const float4 c4 = cur.c4[i];
         const float4 r0 = make_float4(p.x, p.y, pv.z, pv.w), r1 = make_float4(vfh.x, vfh.y, g.x, g.y),
                      r2 = make_float4(lg.x, lg.y, fc.x, fc.y);
 #pragma unroll
@@ -270,6 +272,9 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
         grid_from_reductions(P, ctl);
         ctl->rebin = 1;   // the local set changes every frame (migrants, ghosts): every frame re-sorts
         ctl->skin = 0.f; ctl->since = 0; ctl->force_rebin = 0; ctl->dmax = 0u;
+        ctl->src_set = ctl->live;          // roles of the two state copies (crowd.cuh Buffers)
+        ctl->in_set = ctl->live ^ 1;
+        ctl->live = ctl->in_set ^ 1;       // (unchanged: a re-sort frame writes its result back into the copy it scattered from)
         ctl->minx = ctl->miny = 0xffffffffu;
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
@@ -313,7 +318,7 @@ __device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
     for (int k = tid; k < nsend; k += blockDim.x) {
         const float4 cd = list[k];
         const int slot = __float_as_int(cd.w);
-        const float4 pj = b.srt.pv[slot], cj = b.srt.c4[slot];
+        const float4 pj = set_in(b).pvf[slot], cj = set_in(b).c4[slot];
         const float4 A = make_float4(cd.x, cd.y, cd.z, pj.z), B = make_float4(cj.x, cj.y, cj.z, 0.f);
         for (int q = 0; q < w; ++q) {
             if (q == me) continue;
@@ -406,8 +411,8 @@ __device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
             for (int k = tid; k < cnt; k += blockDim.x) {
                 const float4 A = src[2 * k], B = src[2 * k + 1];
                 const int annex = cap + s_off[q] + k;
-                b.srt.pv[annex] = make_float4(A.x, A.y, A.w, 0.f);  // comm::x reads pos.x and vel.x of the partner only (quirk Q2)
-                b.srt.c4[annex] = B;
+                set_in(b).pvf[annex] = make_float4(A.x, A.y, A.w, 0.f);  // comm::x reads pos.x and vel.x of the partner only (quirk Q2)
+                set_in(b).c4[annex] = B;
                 list[nloc + s_off[q] + k] = make_float4(A.x, A.y, A.z, __int_as_float(annex));
             }
         }
