@@ -107,8 +107,10 @@ struct Ctl {
 };
 
 constexpr int DD_MAX_WORLD = 8;     // ranks of one spatially decomposed crowd (one B200 box)
-constexpr int DD_EV_CAP = 4096;      // done-events one rank can forward to the scoring rank per frame
-constexpr int DD_CAND_CAP = 4096;    // comm-partner candidates one rank can publish per frame
+// Per-rank, per-frame capacities of the all-rank exchange; beyond them the frame raises LC_ERR_CAPACITY (-5) on every rank
+// (tests/test_gpu_domain.py drives both).  4x the round-1 values: 8 ranks x 16384 x 32 B = 4 MB of mailbox per parity.
+constexpr int DD_EV_CAP = 16384;     // done-events one rank can forward to the scoring rank per frame
+constexpr int DD_CAND_CAP = 16384;   // comm-partner candidates one rank can publish per frame
 constexpr int META_GHOST = 4;        // meta.y bit2: halo copy of an agent owned by a neighbouring rank
 
 struct Params {

@@ -139,6 +139,61 @@ def test_domain_odd_capacity_shard_tables():
         assert np.array_equal(sh["pos"][:k], full["pos"][ids]) and np.array_equal(sh["vel"][:k], full["vel"][ids])
 
 
+def test_domain_exchange_capacities_fail_cleanly():
+    """The two fixed capacities of the all-rank exchange (crowd.cuh DD_EV_CAP / DD_CAND_CAP = 16 384 per rank and frame):
+    (a) a mass arrival — 40 000 agents that are within a metre of their goals from the start, so each rank has 20 000
+    done-events to forward in one frame; (b) a crowd that is nothing but outline — 36 000 agents on a circle, every one a
+    hull vertex and therefore a comm-partner candidate.  Both must surface LC_ERR_CAPACITY (-5) on the ranks through the
+    calls a stepping host makes (lc_finished / lc_get_state), not hang and not go unnoticed.  Below the capacities the same
+    shapes run bit-identically to one GPU."""
+    rs = np.random.RandomState(8)
+    # (a) mass arrival
+    n = 40000
+    side = 200.0
+    m = int(np.ceil(np.sqrt(n)))
+    gx, gy = np.meshgrid(np.arange(m), np.arange(m))
+    pos = (np.stack([gx.ravel(), gy.ravel()], 1)[:n] * (side / m) - side / 2).astype(np.float32)
+    goal = (pos + rs.uniform(-0.3, 0.3, (n, 2))).astype(np.float32)
+    sims = _make(pos, goal, 50.0, 3, None, None, 2)
+    lcb.DomainSim.step_all(sims, 3)
+    codes = []
+    for s in sims:
+        with pytest.raises(lcb.LcError) as e:
+            _ = s.finished
+        codes.append(e.value.code)
+    assert codes == [-5, -5], codes
+    # the same shape below the capacity: 12 000 agents, 6 000 events per rank in one frame
+    k = 12000
+    sims = _make(pos[:k], goal[:k], 50.0, 3, None, None, 2)
+    ref = lcb.Sim(pos[:k], goal[:k], None, None, max_duration=50.0, rng_state=3)
+    lcb.DomainSim.step_all(sims, 4)
+    ref.step(4)
+    _assert_same(sims, ref, "mass arrival below the capacity")
+    a, b = lcb.DomainSim.merged_scores(sims), ref.scores()
+    assert a["n_done"] == b["n_done"] == k and a["run_avg"] == b["run_avg"] and a["run_std"] == b["run_std"]
+    # (b) all outline
+    n = 36000
+    th = np.arange(n) * (2 * np.pi / n)
+    pos = np.stack([2000.0 * np.cos(th), 2000.0 * np.sin(th)], 1).astype(np.float32)
+    sims = _make(pos, (-pos).astype(np.float32), 50.0, 3, *wl.weights(4, 0.5), 2)
+    lcb.DomainSim.step_all(sims, 2)
+    codes = []
+    for s in sims:
+        with pytest.raises(lcb.LcError) as e:
+            s.state()
+        codes.append(e.value.code)
+    assert codes == [-5, -5], codes
+    k = 9000
+    th = np.arange(k) * (2 * np.pi / k)
+    pos = np.stack([600.0 * np.cos(th), 600.0 * np.sin(th)], 1).astype(np.float32)
+    m_cv, m_f = wl.weights(4, 0.5)
+    sims = _make(pos, (-pos).astype(np.float32), 50.0, 3, m_cv, m_f, 2)
+    ref = lcb.Sim(pos, (-pos).astype(np.float32), m_cv, m_f, max_duration=50.0, rng_state=3)
+    lcb.DomainSim.step_all(sims, 6)
+    ref.step(6)
+    _assert_same(sims, ref, "all-outline crowd below the capacity")
+
+
 def test_domain_error_paths():
     pos, goal = _crowd(500, 30.0, 30.0, seed=1)
     with pytest.raises(lcb.LcError):
