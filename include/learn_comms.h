@@ -30,6 +30,13 @@ typedef enum {
 #define LC_FLAG_FREE_RUN 2u       /* keep stepping the dynamics after demo::run reported all_done (fixed-step benchmarks) */
 #define LC_FLAG_DEBUG_LISTS 4u    /* record per-agent neighbour lists {j : ttc_ij <= 5} each frame (parity tests) */
 
+/* feature-set variants of comm::x (the #defines at comm.cpp:22-28; HEAD builds with COSINE_REL + PROX + SOFTSIGN_GOAL = no bit set) */
+#define LC_FLAG_FEAT_PLAIN 32u        /* neither COSINE_REL nor NORM_REL: x = [c_j, rel_v.x, rel_v.y, rel_p.x, rel_p.y, g] (comm.cpp:130,189).
+                                       * M_cv columns in that order.  HEAD cannot be built this way (its parser does not compile without
+                                       * COSINE_REL): this is the feature set of the legacy "3 5" config files, see lc_read_config_legacy */
+#define LC_FLAG_FEAT_NO_PROX 64u      /* PROX undefined (comm.cpp:172-174) */
+#define LC_FLAG_FEAT_NO_SOFTSIGN 128u /* SOFTSIGN_GOAL undefined (comm.cpp:178-180) */
+
 typedef struct lc_rect { float ox, oy, w, h; } lc_rect; /* BoundVolume.h Rect: origin (centre), width, height */
 
 /* Scene description: replaces demo::init + ai::init + physics::init/prewarm (demo.cpp:611-648, ai.cpp:24-129,
@@ -200,6 +207,13 @@ int64_t lc_batch_kernel_launches(lc_batch* b);
 /* ---- files: comm::init / comm::terminate formats (comm.cpp:74-142, pso_opt.py:17-41) ---- */
 int32_t lc_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);
 int32_t lc_write_result(const char* path, float avg_velocity, float group_time);
+/* The legacy parameter files at the reference's root (comms_good.config, comms_82.config, comms_g.config, comms_hand.config;
+ * written by optimizer.py:20-27): a "3 5" header, then a 3 x 5 matrix of an older one-channel model — row 0 =
+ * [M_c | M_vx M_vy M_px M_py] (plain relative velocity / position components, no goal input), rows 1-2 column 0 = M_f
+ * (2 x 1); optimizer.py:66-73 only ever varies those seven entries.  HEAD's parser aborts on them (comm.cpp:80-121).
+ * Embedded into HEAD's three-channel layout with the plain feature set: m_cv[3][8] / m_f[2][3] for LC_FLAG_FEAT_PLAIN
+ * (channel 0 carries the model, channels 1-2 and the goal input have zero weights).  *flags receives LC_FLAG_FEAT_PLAIN. */
+int32_t lc_read_config_legacy(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/, uint32_t* flags);
 
 /* ---- iteration order of the reference's component tables (quirk Q4; Pool.h:24, Pool.cpp:7-16,156-160) for a scene
  * with n_agents robots followed by n_walls walls (demo.cpp:628-635): agent_order[n_agents], wall_order[n_walls] (either may

@@ -7,6 +7,7 @@ import numpy as np
 from . import build as _build
 
 FLAG_NO_COMM, FLAG_FREE_RUN, FLAG_DEBUG_LISTS = 1, 2, 4
+FEAT_PLAIN, FEAT_NO_PROX, FEAT_NO_SOFTSIGN = 32, 64, 128  # comm::x feature-set variants (LC_FLAG_FEAT_*)
 _LIB = None
 
 
@@ -42,7 +43,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_get_trace", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
+    "lc_read_config", "lc_read_config_legacy", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -101,6 +102,7 @@ def lib():
         L.lc_batch_kernel_launches.argtypes = [vp]
         L.lc_batch_kernel_launches.restype = C.c_int64
         L.lc_read_config.argtypes = [C.c_char_p, vp, vp]
+        L.lc_read_config_legacy.argtypes = [C.c_char_p, vp, vp, C.POINTER(u32)]
         L.lc_write_result.argtypes = [C.c_char_p, C.c_float, C.c_float]
         L.lc_scene.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32)]
         L.lc_scene_full.argtypes = [u32, C.c_uint64, vp, vp, i32, f32p, C.POINTER(u32), vp, i32, C.POINTER(i32)]
@@ -261,6 +263,16 @@ def read_config(path):
     return m_cv, m_f
 
 
+def read_config_legacy(path):
+    """lc_read_config_legacy: a "3 5"-headed legacy file -> (m_cv [3][8], m_f [2][3], feature flags)."""
+    m_cv, m_f = np.zeros((3, 8), np.float32), np.zeros((2, 3), np.float32)
+    fl = C.c_uint32(0)
+    rc = lib().lc_read_config_legacy(os.fsencode(path), _p(m_cv), _p(m_f), C.byref(fl))
+    if rc:
+        raise LcError(rc, f"cannot parse {path} as a legacy 3 x 5 config (optimizer.py:20-27)")
+    return m_cv, m_f, int(fl.value)
+
+
 def write_result(path, avg_velocity, group_time):
     rc = lib().lc_write_result(os.fsencode(path), avg_velocity, group_time)
     if rc:
@@ -274,7 +286,7 @@ class Sim:
     """One crowd resident on one GPU.  step(k) runs k frames of main.cpp:98-150."""
 
     def __init__(self, pos, goal, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15, comm=True,
-                 free_run=False, debug_lists=False, device=0, stencil=0, order=None, walls=None, wall_order=None):
+                 free_run=False, debug_lists=False, device=0, stencil=0, order=None, walls=None, wall_order=None, features=0):
         """order: table iteration order (lc_desc::table_order) — None = ascending index, "reference" = the reference's
         own (lc_table_order), or an explicit permutation.  walls [W][4] (origin x, z, width, height): a walled scene;
         wall_order = statics order (None = creation order; with order="reference" the reference's own)."""
@@ -289,7 +301,7 @@ class Sim:
         goal = np.ascontiguousarray(goal, np.float32)
         m_cv = None if m_cv is None else np.ascontiguousarray(m_cv, np.float32)
         m_f = None if m_f is None else np.ascontiguousarray(m_f, np.float32)
-        flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0) | (FLAG_DEBUG_LISTS if debug_lists else 0)
+        flags = (0 if comm else FLAG_NO_COMM) | (FLAG_FREE_RUN if free_run else 0) | (FLAG_DEBUG_LISTS if debug_lists else 0) | features
         d = _Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f), flags, device, nw,
                   _p(self._walls), stencil, _p(self._order), _p(self._wall_order))
         h = C.c_void_p()
@@ -611,7 +623,7 @@ class Batch:
     """Many independent small scenarios in one launch (pso_opt.py:236-267 simulate_set, in process)."""
 
     def __init__(self, pos, goal, m_cv, m_f, max_duration, rng_state, radius=0.15, comm=True, device=0, order=None, walls=None,
-                 wall_order=None):
+                 wall_order=None, features=0):
         """walls [W][4]: one wall layout shared by every scenario of the batch (replans are served by the host planner
         between relaunches of the rollout kernel); order / wall_order as for Sim."""
         S, n = pos.shape[0], pos.shape[1]
@@ -627,7 +639,7 @@ class Batch:
                       np.ascontiguousarray(np.broadcast_to(np.asarray(max_duration, np.float32), (S,))),
                       np.ascontiguousarray(np.broadcast_to(np.asarray(rng_state, np.uint32), (S,)))]
         assert self._keep[2].shape == (S, 3, 8) and self._keep[3].shape == (S, 2, 3)
-        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, 0 if comm else FLAG_NO_COMM, device, _p(self._order),
+        d = _BatchDesc(S, n, *[_p(a) for a in self._keep], radius, (0 if comm else FLAG_NO_COMM) | features, device, _p(self._order),
                        nw, _p(self._walls), _p(self._wall_order))
         h = C.c_void_p()
         self.h = None

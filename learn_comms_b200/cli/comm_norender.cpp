@@ -88,8 +88,15 @@ int main(int argc, char** argv) {
     flags |= LC_FLAG_NO_COMM;  // main.cpp:130-132: comm::run compiled out; comm::init still runs but reads nothing
 #else
     if (lc_read_config((data_dir + "/comms.config").c_str(), m_cv, m_f) != LC_OK) {
-        fprintf(stderr, "gg! Failed to open file %s/comms.config\n", data_dir.c_str());  // io.cpp:130
-        return EXIT_FAILURE;  // the reference dereferences an empty optional / throws from stof here
+        // not HEAD's 5 x 8 format: one of the legacy "3 5" files (optimizer.py:20-27; comms_good.config ...)?  HEAD's own
+        // parser aborts on those; the drop-in runs them with the plain feature set they were written for
+        uint32_t feat = 0;
+        if (lc_read_config_legacy((data_dir + "/comms.config").c_str(), m_cv, m_f, &feat) == LC_OK) {
+            flags |= feat;
+        } else {
+            fprintf(stderr, "gg! Failed to open file %s/comms.config\n", data_dir.c_str());  // io.cpp:130
+            return EXIT_FAILURE;  // the reference dereferences an empty optional / throws from stof here
+        }
     }
 #endif
     lc_desc d;

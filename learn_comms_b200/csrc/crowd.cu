@@ -1200,19 +1200,9 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             // comm.cpp:144-192 x(): COSINE_REL + PROX + SOFTSIGN_GOAL; partner (x, y) of a vec3 = (x, 0): quirk Q2
             const float rightx = facing.y, righty = -facing.x;
             const float dvx = __fsub_rn(pj.z, vx), dvy = __fsub_rn(0.f, vy);
-            float rvx = dot2(rightx, righty, dvx, dvy), rvy = dot2(facing.x, facing.y, dvx, dvy);
-            const float mag_rv = len2(rvx, rvy);
-            if (mag_rv > 0.f) { rvx = __fdiv_rn(rvx, mag_rv); rvy = __fdiv_rn(rvy, mag_rv); }
             const float dpx = __fsub_rn(pj.x, px), dpy = __fsub_rn(0.f, py);
-            float rpx = dot2(rightx, righty, dpx, dpy), rpy = dot2(facing.x, facing.y, dpx, dpy);
-            float mag_rp = len2(rpx, rpy);
-            if (mag_rp > 0.f) {
-                rpx = __fdiv_rn(rpx, mag_rp); rpy = __fdiv_rn(rpy, mag_rp);
-                mag_rp = __fdiv_rn(1.f, mag_rp);
-            }
-            float g = c4.w;
-            g = __fdiv_rn(g, __fadd_rn(1.f, g));
-            const float x[8] = {cj.x, cj.y, cj.z, rvy, mag_rv, rpy, mag_rp, g};
+            float x[8];  // goal_dist is last frame's (ai.cpp:154 runs after comm::run)
+            comm_features(P->flags, rightx, righty, facing.x, facing.y, dvx, dvy, dpx, dpy, c4.w, cj.x, cj.y, cj.z, x);
             float cn[3];
 #pragma unroll
             for (int r = 0; r < 3; ++r) {  // comm.cpp:285 M_cv * x (Eigen 3.3 unrolled redux order, see oracle/canon.c)

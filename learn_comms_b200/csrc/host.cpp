@@ -359,6 +359,26 @@ int32_t lc_read_config(const char* path, float* m_cv, float* m_f) {
     return LC_OK;
 }
 
+// optimizer.py:20-27's format (the four comms_*.config files at the reference's root): "3 5", then 3 rows of 5
+int32_t lc_read_config_legacy(const char* path, float* m_cv, float* m_f, uint32_t* flags) {
+    if (!path || !m_cv || !m_f) return LC_ERR_ARG;
+    std::ifstream in(path);
+    if (!in) return LC_ERR_IO;
+    int rows = 0, cols = 0;
+    if (!(in >> rows >> cols) || rows != 3 || cols != 5) return LC_ERR_IO;
+    float m[15];
+    for (float& v : m)
+        if (!(in >> v)) return LC_ERR_IO;
+    for (int k = 0; k < 24; ++k) m_cv[k] = 0.f;
+    for (int k = 0; k < 6; ++k) m_f[k] = 0.f;
+    m_cv[0] = m[0];                              // M_c (1 x 1) -> channel 0's self weight
+    m_cv[3] = m[1]; m_cv[4] = m[2];              // M_vx, M_vy
+    m_cv[5] = m[3]; m_cv[6] = m[4];              // M_px, M_py
+    m_f[0] = m[5]; m_f[3] = m[10];               // M_f (2 x 1) -> column 0
+    if (flags) *flags = LC_FLAG_FEAT_PLAIN;
+    return LC_OK;
+}
+
 // comm.cpp:136-142: default ostream formatting (6 significant digits), avg_velocity then mean + 3 sigma
 int32_t lc_write_result(const char* path, float avg_velocity, float group_time) {
     if (!path) return LC_ERR_ARG;

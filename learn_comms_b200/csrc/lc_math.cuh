@@ -63,6 +63,35 @@ __device__ __forceinline__ float2 mul2(float2 a, float2 b) {
     return r;
 }
 
+// Feature-set variants of comm::x (comm.cpp:22-28: the #defines COSINE_REL, PROX, SOFTSIGN_GOAL; HEAD builds with all
+// three).  Bits of lc_desc::flags / lc_batch_desc::flags (learn_comms.h LC_FLAG_FEAT_*).
+#define LCM_FEAT_PLAIN 32u        /* neither COSINE_REL nor NORM_REL: x = [c_j, rel_v.x, rel_v.y, rel_p.x, rel_p.y, g] (comm.cpp:189) */
+#define LCM_FEAT_NO_PROX 64u      /* PROX undefined: mag_rp stays |rel_p| (comm.cpp:172-174) */
+#define LCM_FEAT_NO_SOFTSIGN 128u /* SOFTSIGN_GOAL undefined: g = goal_dist (comm.cpp:178-180) */
+
+// comm.cpp:144-192 x(): the 8 inputs of M_cv from the partner's message c_j, the relative velocity dv = v_j - v_i and
+// position dp = p_j - p_i expressed in the agent's (right, facing) frame, and its goal distance.
+__device__ __forceinline__ void comm_features(uint32_t flags, float rightx, float righty, float fx, float fy, float dvx, float dvy,
+                                              float dpx, float dpy, float goal_dist, float cjx, float cjy, float cjz, float x[8]) {
+    float rvx = dot2(rightx, righty, dvx, dvy), rvy = dot2(fx, fy, dvx, dvy);
+    float rpx = dot2(rightx, righty, dpx, dpy), rpy = dot2(fx, fy, dpx, dpy);
+    float g = goal_dist;
+    if (!(flags & LCM_FEAT_NO_SOFTSIGN)) g = __fdiv_rn(g, __fadd_rn(1.f, g));
+    x[0] = cjx; x[1] = cjy; x[2] = cjz;
+    if (flags & LCM_FEAT_PLAIN) {
+        x[3] = rvx; x[4] = rvy; x[5] = rpx; x[6] = rpy; x[7] = g;
+        return;
+    }
+    const float mag_rv = len2(rvx, rvy);
+    if (mag_rv > 0.f) { rvx = __fdiv_rn(rvx, mag_rv); rvy = __fdiv_rn(rvy, mag_rv); }
+    float mag_rp = len2(rpx, rpy);
+    if (mag_rp > 0.f) {
+        rpx = __fdiv_rn(rpx, mag_rp); rpy = __fdiv_rn(rpy, mag_rp);
+        if (!(flags & LCM_FEAT_NO_PROX)) mag_rp = __fdiv_rn(1.f, mag_rp);
+    }
+    x[3] = rvy; x[4] = mag_rv; x[5] = rpy; x[6] = mag_rp; x[7] = g;
+}
+
 // order-preserving float <-> uint encoding for atomicMin/atomicMax reductions
 __device__ __forceinline__ uint32_t f2ord(float f) {
     uint32_t u = __float_as_uint(f);

@@ -53,6 +53,7 @@ struct canon_sim {
     uint32_t rng;
     float m_cv[24], m_f[6];
     int comm_enabled, use_grid;
+    uint32_t features;
     int32_t n_walls;
     canon_rect* walls;
     /* Dynamics.h:2-11 (live subset), Agent.h:6-33, CommComp.h:13-17 */
@@ -128,6 +129,7 @@ canon_sim* canon_create(const canon_desc* d) {
     s->rng = d->rng_state;
     s->comm_enabled = d->comm_enabled;
     s->use_grid = d->use_grid;
+    s->features = d->features;
     if (d->m_cv) memcpy(s->m_cv, d->m_cv, sizeof(s->m_cv));
     if (d->m_f) memcpy(s->m_f, d->m_f, sizeof(s->m_f));
     s->n_walls = d->n_walls;
@@ -328,18 +330,26 @@ static void comm_run(canon_sim* s) { /* comm.cpp:267-305 */
         v2 right = V2(facing.y, -facing.x); /* CommComp.h:38 */
         v2 diff_v = sub2(v_j, s->vel[i]);
         v2 rel_v = V2(right.x * diff_v.x + right.y * diff_v.y, facing.x * diff_v.x + facing.y * diff_v.y);
-        float mag_rv = len_2(rel_v);
-        if (mag_rv > 0) rel_v = div2s(rel_v, mag_rv);
+        const int plain = (s->features & 32u) != 0; /* neither COSINE_REL nor NORM_REL (comm.cpp:158-163,167-176) */
+        float mag_rv = 0.f;
+        if (!plain) {
+            mag_rv = len_2(rel_v);
+            if (mag_rv > 0) rel_v = div2s(rel_v, mag_rv);
+        }
         v2 diff_p = sub2(p_j, s->pos[i]);
         v2 rel_p = V2(right.x * diff_p.x + right.y * diff_p.y, facing.x * diff_p.x + facing.y * diff_p.y);
-        float mag_rp = len_2(rel_p);
-        if (mag_rp > 0) {
-            rel_p = div2s(rel_p, mag_rp);
-            mag_rp = 1 / mag_rp;
+        float mag_rp = 0.f;
+        if (!plain) {
+            mag_rp = len_2(rel_p);
+            if (mag_rp > 0) {
+                rel_p = div2s(rel_p, mag_rp);
+                if (!(s->features & 64u)) mag_rp = 1 / mag_rp; /* PROX */
+            }
         }
         float g = s->goal_dist[i];
-        g /= 1 + g;
+        if (!(s->features & 128u)) g /= 1 + g; /* SOFTSIGN_GOAL */
         float x[8] = {s->c[j][0], s->c[j][1], s->c[j][2], rel_v.y, mag_rv, rel_p.y, mag_rp, g};
+        if (plain) { x[3] = rel_v.x; x[4] = rel_v.y; x[5] = rel_p.x; x[6] = rel_p.y; } /* comm.cpp:189 */
         /* comm.cpp:285 M_cv * x_i, M_f * c_j.  Eigen 3.3 coeff-based lazy product, non-vectorised redux:
          * pairwise tree ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)); depth 3: p0+(p1+p2).  Eigen is not vendored
          * (lib/init.sh:58-59) so this order is restated from the 3.3 sources' redux_novec_unroller —

@@ -52,6 +52,9 @@ typedef struct {
      * canon_bvh_node; NULL = every wall is tested with the exact leaf predicate in wall_order */
     int32_t n_bvh;
     const void* bvh;
+    /* feature-set variant of comm::x (comm.cpp:22-28): 0 = HEAD (COSINE_REL + PROX + SOFTSIGN_GOAL); bit 32 = plain
+     * (x = [c_j, rel_v, rel_p, g], comm.cpp:189), 64 = PROX undefined, 128 = SOFTSIGN_GOAL undefined */
+    uint32_t features;
 } canon_desc;
 
 /* one node of the static BVH: aabb (Rect), children (left, right >= 0) or leaf (right < 0, left = wall index) */

@@ -23,7 +23,7 @@ class Desc(C.Structure):
                 ("max_duration", C.c_float), ("rng_state", C.c_uint32), ("m_cv", C.c_void_p),
                 ("m_f", C.c_void_p), ("comm_enabled", C.c_int32), ("use_grid", C.c_int32),
                 ("n_walls", C.c_int32), ("walls", C.c_void_p), ("table_order", C.c_void_p), ("wall_order", C.c_void_p),
-                ("plan_fn", PLAN_FN), ("plan_user", C.c_void_p), ("n_bvh", C.c_int32), ("bvh", C.c_void_p)]
+                ("plan_fn", PLAN_FN), ("plan_user", C.c_void_p), ("n_bvh", C.c_int32), ("bvh", C.c_void_p), ("features", C.c_uint32)]
 
 
 def lib():
@@ -144,7 +144,7 @@ def scene_full(scene_id, seed=0):
 
 class CanonSim:
     def __init__(self, pos, goal, m_cv=None, m_f=None, max_duration=45.0, rng_state=1, radius=0.15,
-                 comm=True, grid=False, walls=None, order=None, wall_order=None, planner=None, bvh=None):
+                 comm=True, grid=False, walls=None, order=None, wall_order=None, planner=None, bvh=None, features=0):
         """walls [W][4] + planner (an object with plan(start, goal) -> (waypoints [k][2], min_time), e.g. the host planner
         learn_comms_b200.Planner that tests/test_planner.py pins against the reference's own): walled rollouts.
         order / wall_order: table iteration orders (quirk Q4); bvh: flattened static BVH (BVH_NODE records)."""
@@ -172,7 +172,7 @@ class CanonSim:
         self._cb = PLAN_FN(_plan) if planner is not None else PLAN_FN()
         d = Desc(self.n, _p(pos), _p(goal), radius, max_duration, rng_state, _p(m_cv), _p(m_f),
                  1 if comm else 0, 1 if grid else 0, len(walls), _p(walls) if len(walls) else None, _p(order), _p(wall_order),
-                 self._cb, None, 0 if bvh is None else len(bvh), _p(bvh))
+                 self._cb, None, 0 if bvh is None else len(bvh), _p(bvh), features)
         self.h = L.canon_create(C.byref(d))
         assert self.h, "canon_create refused the description (walled scene without a planner?)"
 

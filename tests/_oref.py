@@ -105,14 +105,17 @@ def write_config(path, m_cv, m_f):
             f.write(" ".join(repr(float(np.float32(v))) for v in row) + "\n")
 
 
-def run(scene, seed=0, m_cv=None, m_f=None, max_frames=100000, dump_every=1, comm=True, keep_dir=None, pos_override=None):
+OREF_NOPROX_NOSOFTSIGN = os.path.join(ROOT, "oracle", "_ref", "oref_noprox_nosoftsign")
+
+
+def run(scene, seed=0, m_cv=None, m_f=None, max_frames=100000, dump_every=1, comm=True, keep_dir=None, pos_override=None, exe=None):
     """One run of the reference's own translation units.  pos_override: float32 [n][2] start positions that replace the
     scene's own (goals keep the scene's values) — the 1-ulp-perturbation ensembles."""
     import shutil
     d = keep_dir or tempfile.mkdtemp(prefix="oref_")
     write_config(os.path.join(d, "comms.config"), m_cv, m_f)
     dump = os.path.join(d, "dump.bin")
-    exe = OREF if comm else OREF_NOCOMM
+    exe = exe or (OREF if comm else OREF_NOCOMM)
     env = dict(os.environ)
     if pos_override is not None:
         pf = os.path.join(d, "pos_override.f32")

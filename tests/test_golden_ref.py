@@ -22,10 +22,18 @@ KEYS = ("pos", "vel", "vfh", "c", "facing", "local_goal", "goal_dist", "num_done
 def canon_from_golden(g):
     m_cv = g["m_cv"] if "m_cv" in g else None
     m_f = g["m_f"] if "m_f" in g else None
-    pos, goal, md, rng = _oracle.scene(int(g["scene"]), int(g["seed"]))
+    pos, goal, md, rng = _oracle.scene_full(int(g["scene"]), int(g["seed"]))[:4]
     assert np.array_equal(pos, g["pos0"]) and np.array_equal(goal, g["goal"]), "scene catalogue differs from demo.cpp"
-    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=bool(g["comm"]))
-    o.set_order(g["order"], gauss_seidel=True)
+    if "walls" in g:
+        import learn_comms_b200 as lcb
+        walls = _oracle.scene_full(int(g["scene"]), int(g["seed"]))[4]
+        wo = g["wall_order"]
+        kw = dict(walls=walls, wall_order=wo, planner=lcb.Planner(walls, 0.15), bvh=lcb.static_bvh(walls, wo))
+    else:
+        kw = {}
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=bool(g["comm"]), order=g["order"],
+                         features=int(g["features"]) if "features" in g else 0, **kw)
+    o.set_order(None, gauss_seidel=True)
     return o
 
 

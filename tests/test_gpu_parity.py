@@ -23,9 +23,9 @@ def assert_state_equal(g, o, tag):
             raise AssertionError(f"{tag}: {k} differs, max abs {np.nanmax(d):.3e}, {(d > 0).sum()} elements")
 
 
-def lockstep(pos, goal, md, rng, m_cv, m_f, frames, comm=True, grid=False, lists=True, check_every=1, stencil=0):
-    g = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=comm, debug_lists=lists, stencil=stencil)
-    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=comm, grid=grid)
+def lockstep(pos, goal, md, rng, m_cv, m_f, frames, comm=True, grid=False, lists=True, check_every=1, stencil=0, features=0):
+    g = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=comm, debug_lists=lists, stencil=stencil, features=features)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, comm=comm, grid=grid, features=features)
     o.record_neighbors(lists)
     f = 0
     while f < frames and not o.finished:
@@ -58,6 +58,54 @@ def test_scene_rollout_bit_exact(scene_id, wseed):
     gs, os_ = g.scores(), o.scores()
     for k in gs:
         assert gs[k] == os_[k] or (np.isnan(gs[k]) and np.isnan(os_[k])), (k, gs, os_)
+
+
+@pytest.mark.parametrize("features", [lcb.FEAT_NO_PROX | lcb.FEAT_NO_SOFTSIGN, lcb.FEAT_NO_PROX, lcb.FEAT_PLAIN, lcb.FEAT_PLAIN | lcb.FEAT_NO_SOFTSIGN])
+def test_feature_set_variants(features):
+    """comm::x's #define variants (comm.cpp:22-28): O-canon's flags are pinned against the reference built with PROX and
+    SOFTSIGN_GOAL off (tests/golden/scene4_w2_noprox_nosoftsign.npz); the CUDA path follows O-canon bit for bit in each."""
+    pos, goal, md, rng = lcb.scene(4, 0)
+    m_cv, m_f = wl.weights(2)
+    g, o = lockstep(pos, goal, md, rng, m_cv, m_f, frames=10 ** 6, check_every=11, features=features)
+    assert g.finished and g.frame == o.frame and g.scores() == o.scores()
+    # and the batched kernel
+    b = lcb.Batch(pos[None], goal[None], m_cv[None], m_f[None], [md], [rng], features=features)
+    out = b.run()
+    assert out["frames"][0] == o.frame and out["group_time"][0] == np.float32(o.scores()["group_time"])
+
+
+def test_gpu_equals_reference_variant_golden_directly():
+    """... and against the reference variant's own rollout, no oracle in between (reference table order; scene 8 has no
+    agent contacts, so the Jacobi pass equals the reference's)."""
+    import os
+    gd = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scene8_w28_noprox_nosoftsign.npz"))
+    pos, goal, md, rng, walls = lcb.scene_full(8, 0)
+    g = lcb.Sim(pos, goal, gd["m_cv"], gd["m_f"], max_duration=md, rng_state=rng, walls=walls, order="reference", features=int(gd["features"]))
+    at = 0
+    for k, f in enumerate(gd["frames"]):
+        g.step(int(f) - at)
+        at = int(f)
+        st = g.state()
+        for key in KEYS:
+            assert np.array_equal(st[key], gd[key][k], equal_nan=True), f"frame {f}: {key}"
+    sc = g.scores()
+    assert ("%g" % np.float32(sc["avg_velocity"]), "%g" % np.float32(sc["group_time"])) == tuple(str(x) for x in gd["result_file"])
+
+
+@pytest.mark.parametrize("name", ["comms_good", "comms_82", "comms_g", "comms_hand"])
+def test_legacy_config_files_run(name):
+    """BASELINE.json configs[0]: the reference's legacy "3 5" parameter files (HEAD's own parser aborts on them) through
+    lc_read_config_legacy -> plain feature set, scene 0 to completion, CUDA path == O-canon."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "legacy_configs", name + ".config")
+    m_cv, m_f, feat = lcb.read_config_legacy(path)
+    assert feat == lcb.FEAT_PLAIN and m_cv[0, 3] != 0 and not m_cv[1:].any() and not m_f[:, 1:].any()
+    with pytest.raises(lcb.LcError):
+        lcb.read_config(path)   # HEAD's format: the file is rejected, as the reference's parser rejects it
+    pos, goal, md, rng = lcb.scene(0, 0)
+    g, o = lockstep(pos, goal, md, rng, m_cv, m_f, frames=10 ** 6, check_every=50, features=feat, lists=False)
+    assert g.finished and g.frame == o.frame and g.scores() == o.scores()
+    assert np.isfinite(g.scores()["group_time"])
 
 
 def test_run_to_completion_matches_stepping():

@@ -37,15 +37,21 @@ CASES = [
 ]
 
 
+# comm::x feature-set variants (the #defines inside comm.cpp:22-28): (name, scene, weight seed, O-ref build, LC_FLAG_FEAT_* bits)
+VARIANTS = [("scene4_w2_noprox_nosoftsign", 4, 2, "OREF_NOPROX_NOSOFTSIGN", 64 | 128),
+            ("scene8_w28_noprox_nosoftsign", 8, 28, "OREF_NOPROX_NOSOFTSIGN", 64 | 128)]
+
+
 def main():
     out_dir = os.path.join(ROOT, "tests", "golden")
     os.makedirs(out_dir, exist_ok=True)
     only = sys.argv[1:]
-    for name, scene, seed, wseed, comm, upto, stride in CASES:
+    cases = [c + (None, 0) for c in CASES] + [(n, sc, 0, ws, True, None, 97, getattr(_oref, exe), feat) for n, sc, ws, exe, feat in VARIANTS]
+    for name, scene, seed, wseed, comm, upto, stride, exe, feat in cases:
         if only and not any(name.startswith(o) for o in only):
             continue
         m_cv, m_f = (None, None) if wseed is None else wl.weights(wseed)
-        r = _oref.run(scene, seed, m_cv, m_f, comm=comm)
+        r = _oref.run(scene, seed, m_cv, m_f, comm=comm, exe=exe)
         frames = [fr for fr in r["frames"] if (upto is None or fr["frame"] <= upto)]
         keep = [fr for fr in frames if fr["frame"] % stride == 0 or fr["frame"] == 1 or fr is frames[-1]]
         d = dict(scene=scene, seed=seed, wseed=-1 if wseed is None else wseed, comm=int(comm), order=r["order"],
@@ -56,6 +62,8 @@ def main():
                  progress=np.array([[fr["run_avg"], fr["run_std"], fr["avg_velocity"], fr["total_num_done"]] for fr in keep]))
         if r["n_walls"]:
             d["walls"], d["wall_order"] = r["walls"], r["wall_order"]
+        if feat:
+            d["features"] = feat
         if m_cv is not None:
             d["m_cv"], d["m_f"] = m_cv, m_f
         for k in KEYS:
