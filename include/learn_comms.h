@@ -94,6 +94,12 @@ int32_t lc_get_rng(lc_sim* sim, uint32_t* rng_state);
 int32_t lc_get_scores(lc_sim* sim, float* avg_velocity, float* group_time, float* run_avg, float* run_std,
                       int32_t* total_num_done);
 
+/* Headless picture of the crowd as render::draw shows it (render.cpp:364-415; no graphics API: CUDA kernels into a buffer):
+ * top-down orthographic window of 25 cam_dist metres (Camera.cpp:86-90, render.cpp:354), robots as discs coloured by
+ * comm_vis(c) (render.cpp:87-172; vis_f = render::VisF: 0 XYZ2LAB, 1 X2RG, 2 Y2RG, 3 Z2RG, 4 XYZ2LUV) with their black outline,
+ * walls as grey squares, background of render.cpp:365.  rgba: HOST buffer [height][width][4], row 0 = far side (-z). */
+int32_t lc_render(lc_sim* sim, int32_t vis_f, float cam_dist, int32_t width, int32_t height, uint8_t* rgba);
+
 /* demo::update_runs' per-finisher log (demo.cpp:662 prints "t:%f u:%f s:%f" for each): [count][3] = overhead, running mean,
  * running sigma, in the order the reference's Welford update saw the finishers */
 int32_t lc_get_finish_log(lc_sim* sim, float* log /*[cap][3]*/, int32_t cap, int32_t* count);

@@ -6,7 +6,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liblearncomms.so")
-SOURCES = ["crowd.cu", "batch.cu", "capi.cu", "walls.cu", "peak.cu", "host.cpp", "planner.cpp"]
+SOURCES = ["crowd.cu", "batch.cu", "capi.cu", "walls.cu", "peak.cu", "splat.cu", "host.cpp", "planner.cpp"]
 HEADERS = ["crowd.cuh", "domain.cuh", "lc_math.cuh", "walls.cuh", os.path.join("..", "..", "include", "learn_comms.h")]
 
 NVCC_FLAGS = [

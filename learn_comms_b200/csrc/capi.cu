@@ -889,6 +889,25 @@ int32_t lc_get_trace(lc_sim* s, uint64_t* ts) {
     return LC_OK;
 }
 
+}  // extern "C"
+
+// splat.cu: the tables lc_render draws from, in engine-id order on the simulation's stream (staging buffer)
+int lc_render_state(lc_sim* s, float2** pos, float** c3, int* n, const lc::WallRect** walls, int* n_walls, cudaStream_t* st) {
+    SIM_ENTER(s);
+    if (s->dd_world > 1) return fail(LC_ERR_ARG, "lc_render: single-GPU crowds only");
+    const size_t m = (size_t)s->n_ids;
+    float2* dpos = (float2*)s->stage;
+    float* dc = s->stage + 10 * m;
+    // k_get_state writes by the caller's agent index; the picture only needs SOME fixed order, and "later in the table wins"
+    // is defined on that index
+    lc::launch_get_state(s->dP, s->n, s->b, dpos, nullptr, nullptr, dc, nullptr, nullptr, nullptr, nullptr, s->st, &s->launches, s->owned_dev);
+    *pos = dpos; *c3 = dc; *n = s->n_ids; *walls = s->b.w.walls; *n_walls = s->hp.n_walls; *st = s->st;
+    s->launches += 3;
+    return LC_OK;
+}
+
+extern "C" {
+
 int32_t lc_timer_start(lc_sim* s) {
     SIM_ENTER(s);
     CK(cudaEventRecord(s->ev0, s->st));

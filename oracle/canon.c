@@ -1182,6 +1182,72 @@ int32_t canon_scene(uint32_t scene, uint32_t* rng_state, float* pos, float* goal
     return n;
 }
 
+/* ---------- render.cpp:87-172 comm_vis colour maps + the picture of render::draw (unpinned: needs OpenGL to build) ---------- */
+static void vis_xyz2(const float* c, float* lab) { /* render.cpp:87-96; vec3::b is .z */
+    float pi = GLM_PI_F;
+    float rx = cosf(2 * pi / 3), ry = sinf(2 * pi / 3), gx = cosf(4 * pi / 3), gy = sinf(4 * pi / 3), bx = cosf(2 * pi), by = sinf(pi);
+    lab[1] = rx * c[0] + gx * c[1] + bx * c[2];
+    lab[2] = ry * c[0] + gy * c[1] + by * c[2];
+    lab[0] = sqrtf(sqrtf(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]) / sqrtf(3.f));
+}
+static double vis_maybe_cube(double a) { double cube = a * a * a; return cube > 0.008856 ? cube : (a - 16. / 116.) / 7.787; }
+static double vis_finish(double a) {
+    if (a > 0.0031308) a = 1.055 * pow(a, 1. / 2.4) - 0.055; else a *= 12.92;
+    return pow(fmax(0., fmin(1., a)), 2.2);
+}
+void canon_comm_vis(int32_t vis_f, const float* c, float* rgb) {
+    if (vis_f >= 1 && vis_f <= 3) { /* render.cpp:157-170 */
+        float v = c[vis_f - 1];
+        rgb[0] = v < 0 ? -v : 0.f; rgb[1] = v < 0 ? 0.f : v; rgb[2] = 0.f;
+        return;
+    }
+    float lab[3];
+    vis_xyz2(c, lab);
+    if (vis_f == 4) { /* render.cpp:98-112 Luv2rgb */
+        float r[3] = {0.000f * lab[1] + 1.140f * lab[2], -0.395f * lab[1] - 0.581f * lab[2], 2.032f * lab[1] + 0.000f * lab[2]};
+        for (int k = 0; k < 3; ++k) rgb[k] = fmaxf(0.f, fminf(1.f, r[k] + lab[0]));
+        return;
+    }
+    /* render.cpp:114-155 Lab2rgb */
+    float L = lab[0] * 100.f, A = lab[1] * 128.f, B = lab[2] * 128.f, X[3];
+    X[0] = (float)((L + 16.) / 116.);
+    X[1] = (float)(A / 500. + X[0]);
+    X[2] = (float)(X[0] - B / 200.);
+    X[0] = (float)(0.95047 * vis_maybe_cube(X[0]));
+    X[1] = (float)(1.00000 * vis_maybe_cube(X[1]));
+    X[2] = (float)(1.08883 * vis_maybe_cube(X[2]));
+    static const float m[3][3] = {{3.2406f, -1.5372f, -0.4986f}, {-0.9689f, 1.8758f, 0.0415f}, {0.0557f, -0.2040f, 1.0570f}};
+    for (int k = 0; k < 3; ++k) rgb[k] = (float)vis_finish((double)(X[0] * m[k][0] + X[1] * m[k][1] + X[2] * m[k][2]));
+}
+static uint32_t vis_pack(const float* rgb) {
+    uint32_t out = 0xff000000u;
+    for (int k = 0; k < 3; ++k) {
+        float v = fmaxf(0.f, fminf(1.f, rgb[k]));
+        out |= (uint32_t)(v * 255.f + 0.5f) << (8 * k);
+    }
+    return out;
+}
+void canon_render(int32_t n, const float* pos, const float* c, int32_t n_walls, const canon_rect* walls, int32_t vis_f,
+                  float cam_dist, int32_t width, int32_t height, uint8_t* rgba) {
+    const float size = 25.f * cam_dist / 2.f; /* Camera.cpp:86-90 */
+    const float body_r = 0.5f * 0.75f * 0.3f, ring_r = 0.5f * 0.3f;
+    uint32_t* img = (uint32_t*)rgba;
+    for (int r = 0; r < height; ++r)
+        for (int u = 0; u < width; ++u) {
+            float x = -size + ((float)u + 0.5f) * (2.f * size / (float)width), z = -size + ((float)r + 0.5f) * (2.f * size / (float)height);
+            uint32_t px = 0xff000000u | (227u << 16) | (246u << 8) | 253u; /* render.cpp:365 */
+            for (int q = 0; q < n_walls; ++q)
+                if (fabsf(x - walls[q].ox) <= walls[q].w / 2 && fabsf(z - walls[q].oy) <= walls[q].h / 2) px = 0xff808080u;
+            for (int i = 0; i < n; ++i) { /* later in the table wins */
+                float dx = x - pos[2 * i], dz = z - pos[2 * i + 1], d2 = dx * dx + dz * dz;
+                if (d2 > ring_r * ring_r) continue;
+                if (d2 <= body_r * body_r) { float rgb[3]; canon_comm_vis(vis_f, c + 3 * i, rgb); px = vis_pack(rgb); }
+                else px = 0xff000000u;
+            }
+            img[(size_t)r * width + u] = px;
+        }
+}
+
 /* ---------- comms.config / comms.result (comm.cpp:74-142; pso_opt.py:17-41) ---------- */
 int32_t canon_read_config(const char* path, float* m_cv, float* m_f) {
     FILE* f = fopen(path, "r");

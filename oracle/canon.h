@@ -129,6 +129,14 @@ int32_t canon_scene_full(uint32_t scene, uint32_t* rng_state, float* pos, float*
 int32_t canon_get_plan(const canon_sim* s, int32_t agent, float* waypoints, int32_t cap);
 void canon_get_walled(const canon_sim* s, int32_t* n_plan, int32_t* lost_frames, int64_t* replans, int64_t* wall_hits);
 
+/* the renderer's message -> colour maps (render.cpp:87-172; vis_f = render::VisF: 0 XYZ2LAB, 1 X2RG, 2 Y2RG, 3 Z2RG,
+ * 4 XYZ2LUV) and a CPU restatement of the top-down picture render::draw produces (render.cpp:352-355,364-415;
+ * Camera.cpp:83-93; demo.cpp:540-541,559,598): checker of lc_render.  render.cpp itself needs an OpenGL context and cannot
+ * be built here, so this half of the oracle is unpinned.  rgba = [height][width][4] bytes. */
+void canon_comm_vis(int32_t vis_f, const float* c, float* rgb);
+void canon_render(int32_t n, const float* pos, const float* c, int32_t n_walls, const canon_rect* walls, int32_t vis_f,
+                  float cam_dist, int32_t width, int32_t height, uint8_t* rgba);
+
 /* config / result files (comm.cpp:74-142, pso_opt.py:17-41) */
 int32_t canon_read_config(const char* path, float* m_cv /*[24]*/, float* m_f /*[6]*/);
 int32_t canon_write_result(const char* path, float avg_velocity, float group_time);

@@ -109,6 +109,27 @@ def lookahead(walls, radius, recs):
     return out
 
 
+def comm_vis(vis_f, c):
+    L = lib()
+    L.canon_comm_vis.argtypes = [C.c_int32, C.c_void_p, C.c_void_p]
+    cc = np.ascontiguousarray(c, np.float32)
+    out = np.zeros(3, np.float32)
+    L.canon_comm_vis(vis_f, _p(cc), _p(out))
+    return out
+
+
+def render(pos, c, walls, vis_f=0, cam_dist=1.0, width=500, height=500):
+    """canon_render: CPU restatement of render::draw's picture -> uint8 [height][width][4]."""
+    L = lib()
+    L.canon_render.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_float, C.c_int32, C.c_int32, C.c_void_p]
+    pos = np.ascontiguousarray(pos, np.float32)
+    c = np.ascontiguousarray(c, np.float32)
+    walls = np.ascontiguousarray(np.asarray(walls, np.float32).reshape(-1, 4))
+    img = np.zeros((height, width, 4), np.uint8)
+    L.canon_render(len(pos), _p(pos), _p(c), len(walls), _p(walls) if len(walls) else None, vis_f, cam_dist, width, height, _p(img))
+    return img
+
+
 def wall_geometry(records):
     """O-canon's static-wall functions on (K, 9) records {rect; a; b; r} -> (K, 12) uint32 words, in the layout of
     oracle/ref/geom_main.cpp."""
