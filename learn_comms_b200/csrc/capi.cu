@@ -106,8 +106,8 @@ static const int GRAPH_BATCH = 1 << (GRAPH_LEVELS - 1);
 
 static int alloc_arrays(lc_sim* s, lc::AgentArrays& a, int n) {
     CK(dalloc(&a.pvf, n)); s->allocs.push_back(a.pvf);
-    CK(dalloc(&a.pq, (size_t)n + 2)); s->allocs.push_back(a.pq);  // 2 float4 per slot PAIR, padded to a whole pair
-    CK(cudaMemset(a.pq, 0, sizeof(float4) * ((size_t)n + 2)));
+    CK(dalloc(&a.pq, (size_t)n + 4)); s->allocs.push_back(a.pq);  // 2 float4 per slot PAIR, padded to a whole pair + one pair of over-read (scan_pairs_flat)
+    CK(cudaMemset(a.pq, 0, sizeof(float4) * ((size_t)n + 4)));
     CK(dalloc(&a.pv, n)); s->allocs.push_back(a.pv);
     CK(dalloc(&a.vfh, n)); s->allocs.push_back(a.vfh);
     CK(dalloc(&a.goal, n)); s->allocs.push_back(a.goal);

@@ -330,7 +330,9 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         const float vm = __uint_as_float(ctl->vmax);
         {   // re-sort this frame, or keep last re-sort's slot order and search a skin wider (crowd.cuh)
             const float moved = ctl->skin + __uint_as_float(ctl->dmax);   // NaN / inf (a non-finite state) forces the re-sort
-            const bool rebin = P->rebin_every <= 1 || ctl->force_rebin || ctl->since + 1 >= P->rebin_every || !(moved <= 0.25f * ctl->h);
+            // (the candidate list k_collide compiled for this frame allowed for CAND_MARGIN of movement in its frame)
+            const bool rebin = P->rebin_every <= 1 || ctl->force_rebin || ctl->since + 1 >= P->rebin_every || !(moved <= 0.25f * ctl->h) ||
+                               !(__uint_as_float(ctl->dmax) <= CAND_MARGIN);
             if (rebin) {
                 grid_from_reductions(P, ctl);
                 ctl->skin = 0.f;
@@ -358,14 +360,18 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
         ctl->minx = ctl->miny = 0xffffffffu;
         ctl->maxx = ctl->maxy = 0u;
         ctl->vmax = 0u;
-        ctl->n_cand = 0;
+        ctl->n_cand = ctl->rebin ? 0 : ctl->n_cand_next;   // re-sort frames: k_reorder compiles the list
+        ctl->n_cand_next = 0;
         {   // k_bin's gate radius from last frame's directional extremes (0.1 m covers the agents' and the centre's motion)
             float rho = CUDART_INF_F;
             for (int k = 0; k < HULL_K; ++k) rho = fminf(rho, ctl->ext_val[k]);
             rho -= 0.1f;
             ctl->gate_rho2 = rho > 0.f ? rho * rho : -1.f;
         }
-        if (!dd) ctl->replan1 = ctl->replan2 = 0x7fffffff;  // domain mode: k_dd_sync_begin merged the global gate
+        if (!dd) {  // the gate k_collide evaluated on the positions this frame starts from (domain mode: dd_global_body merges it)
+            ctl->replan1 = ctl->replan1n; ctl->replan2 = ctl->replan2n;
+            ctl->replan1n = ctl->replan2n = 0x7fffffff;
+        }
         if (dd) {  // the ghost band was sized for the speed bound (domain.cuh); a wider cutoff would miss neighbours
             if (!(P->R + 10.f * vm * 1.001f + 0.01f + P->near_reach <= P->dd_halo) && !ctl->error) ctl->error = -5;
         }
@@ -413,7 +419,6 @@ __global__ void __launch_bounds__(1024) k_bin(const Params* __restrict__ P, Buff
     if (i < n) {
         present = input_pos(P, b, i, p);
         if (present) cell = cell_of(ctl, p.x, p.y);
-        b.pair_cnt[i] = 0;  // k_pairs' lists, indexed by this frame's slots (never more than input records)
     }
     {   // Counting sort, phase 1.  The agents arrive in last frame's cell order, so equal cells form runs of
         // consecutive lanes: one atomicAdd per run instead of one per agent (same-address atomics serialise in L2).
@@ -521,6 +526,21 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
                 ++ne;
             }
             ctl->n_edges = ne;
+            // Inner box: centre +- t (half extents of the bounding box), t the largest factor that keeps all four corners
+            // inside every edge by D = delta + the most anybody can move before the next re-sort is forced (0.25 h) + the
+            // margin of the early list (k_collide).  Empty when the polygon is degenerate.
+            const float hxw = ctl->cx - ctl->x0, hyw = ctl->cy - ctl->y0;
+            const float D = ctl->delta + 0.25f * ctl->h + 2.f * CAND_MARGIN;
+            float t = ne >= 3 ? 1.f : 0.f;
+            for (int e = 0; e < ne; ++e) {
+                const float clear = (ctl->cx - ctl->ex[e]) * ctl->enx[e] + (ctl->cy - ctl->ey[e]) * ctl->eny[e] - D;
+                const float span = hxw * fabsf(ctl->enx[e]) + hyw * fabsf(ctl->eny[e]);
+                t = fminf(t, span > 0.f ? clear / span : 0.f);
+            }
+            t = t * 0.999f - 1e-3f;
+            const bool ok = t > 0.f && hxw > 0.f && hyw > 0.f;   // (NaN anywhere: no box)
+            ctl->ibx0 = ok ? ctl->cx - t * hxw : 1.f; ctl->ibx1 = ok ? ctl->cx + t * hxw : 0.f;
+            ctl->iby0 = ok ? ctl->cy - t * hyw : 1.f; ctl->iby1 = ok ? ctl->cy + t * hyw : 0.f;
         }
         return;
     }
@@ -570,34 +590,45 @@ __global__ void __launch_bounds__(1024) k_scan_hull(const Params* __restrict__ P
     *reinterpret_cast<int4*>(b.cell_start + base) = o4;
 }
 
-// Uniform grid, phase 2: scatter the state into cell order (counting sort).  Also: the replan gate of
-// ai.cpp:151-168 (needs the two lowest ids that want a replan) and comm-partner candidate compaction.
+// Stage 1 of the comm-partner pruning: is (x, z) inside the polygon of extreme agents, by more than `delta`?  The polygon's
+// vertices are where the extreme agents stood at the last re-sort; eroded by what anybody can have moved since, it still
+// lies inside the hull of the current positions.  The box test first: the box lies inside the polygon eroded by
+// more than any delta in use, and holds all but a few per cent of a compact crowd.  NaN-safe: a non-finite position is
+// never "inside".
+__device__ __forceinline__ bool candidate_inside(const Ctl* ctl, float x, float y, float delta) {
+    if (x > ctl->ibx0 && x < ctl->ibx1 && y > ctl->iby0 && y < ctl->iby1) return true;
+    const int ne = ctl->n_edges;
+    bool inside = ne >= 3;
+    for (int e = 0; e < ne && inside; ++e) {
+        const float d = (x - ctl->ex[e]) * ctl->enx[e] + (y - ctl->ey[e]) * ctl->eny[e];
+        if (!(d >= delta)) inside = false;
+    }
+    return inside;
+}
+
+// Uniform grid, phase 2 (re-sort frames only): scatter the state into cell order (counting sort) and compile the stage-1
+// list of comm-partner candidates.
 __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     stamp_entry(ctl, TS_REORDER);
+    if (!ctl->rebin) return;  // the agents keep their slots, last frame's output IS this frame's input, and k_collide compiled the candidates
     const int n = P->n_in;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const bool rebin = ctl->rebin;
     const AgentArrays& src = set_src(b);
-    const AgentArrays& dst = set_in(b);   // re-sort frames: this frame reads what is scattered here
-    int s = i;   // between re-sorts the agents keep their slots and last frame's output IS this frame's input (src == dst)
-    if (rebin) {
-        const int2 cr = b.cellrank[i];
-        if (cr.x < 0) return;  // domain mode: a slot that is not part of this frame's local set (left, or was a ghost)
-        s = b.cell_start[cr.x] + cr.y;
-        b.slot_cell[s] = cr.x;
-    } else {
-        b.pair_cnt[i] = 0;  // (k_bin does it on re-sort frames)
-    }
-    float2 p, g = make_float2(0.f, 0.f);
+    const AgentArrays& dst = set_in(b);   // this frame reads what is scattered here
+    const int2 cr = b.cellrank[i];
+    if (cr.x < 0) return;  // domain mode: a slot that is not part of this frame's local set (left, or was a ghost)
+    const int s = b.cell_start[cr.x] + cr.y;
+    b.slot_cell[s] = cr.x;
+    float2 p;
     int4 mt;
     if (b.dd && i >= b.dd->recv[1]) {  // records of the neighbours' pack: (pos.xy vel.xy | vfh goal | lgoal facing | c4 | meta)
         const DDRec r = dd_locate(P, b, i);
         const float4 r0 = r.plane(0), r1 = r.plane(1), r2 = r.plane(2), r4 = r.plane(4);
-        p = make_float2(r0.x, r0.y); g = make_float2(r1.z, r1.w);
+        p = make_float2(r0.x, r0.y);
         mt = make_int4(__float_as_int(r4.x), __float_as_int(r4.y), __float_as_int(r4.z), __float_as_int(r4.w));
         dst.pvf[s] = r0;
         {
@@ -605,7 +636,7 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
             q[0] = r0.x; q[2] = r0.y; q[4] = r0.z; q[6] = r0.w;
         }
         dst.vfh[s] = make_float2(r1.x, r1.y);
-        dst.goal[s] = g;
+        dst.goal[s] = make_float2(r1.z, r1.w);
         dst.lgoal[s] = make_float2(r2.x, r2.y);
         dst.facing[s] = make_float2(r2.z, r2.w);
         dst.c4[s] = r.plane(3);
@@ -615,49 +646,24 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
         p = make_float2(pf.x, pf.y);
         mt = src.meta[i];
         if (b.dd && b.dd->keep[i] == 2) mt.y |= META_GHOST;  // crossed into the adjacent strip last frame: its ghost from now on
-        if (rebin) {
-            g = src.goal[i];
-            dst.pvf[s] = pf;
-            {   // pair-interleaved copy for the packed pair loop: slots (2k, 2k+1) -> (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
-                float* q = reinterpret_cast<float*>(dst.pq + 2 * (s >> 1)) + (s & 1);
-                q[0] = pf.x; q[2] = pf.y; q[4] = pf.z; q[6] = pf.w;
-            }
-            dst.vfh[s] = src.vfh[i];
-            dst.goal[s] = g;
-            dst.lgoal[s] = src.lgoal[i];
-            dst.facing[s] = src.facing[i];
-            dst.c4[s] = src.c4[i];
-            dst.meta[s] = mt;
-        } else if (mt.y & 1) {
-            g = src.goal[i];  // only the replan gate below needs it
+        dst.pvf[s] = pf;
+        {   // pair-interleaved copy for the packed pair loop: slots (2k, 2k+1) -> (x0, x1, z0, z1), (vx0, vx1, vz0, vz1)
+            float* q = reinterpret_cast<float*>(dst.pq + 2 * (s >> 1)) + (s & 1);
+            q[0] = pf.x; q[2] = pf.y; q[4] = pf.z; q[6] = pf.w;
         }
+        dst.vfh[s] = src.vfh[i];
+        dst.goal[s] = src.goal[i];
+        dst.lgoal[s] = src.lgoal[i];
+        dst.facing[s] = src.facing[i];
+        dst.c4[s] = src.c4[i];
+        dst.meta[s] = mt;
     }
-    // The id -> slot table is a scattered 4-byte store per agent (a 32-byte sector each).  Its only reader inside the
-    // frame loop is the time-out walk of the NEXT k_frame_begin (demo.cpp:691-700, id order); lc_set_state rebuilds it
-    // in k_snapshot.  So it is written only by the frame before the time-out one (and every frame after it).
-    if (__fmul_rn(LC_DT, (float)(ctl->frame + 1u)) > P->max_duration) b.slot_of_id[mt.x] = s;
-    // ai.cpp:154,161-163: need_replan = done && goal_dist > 1 (wall-free: the lost_frames clause cannot fire)
-    if ((mt.y & 1) && P->dd_world <= 1) {
-        float gd = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
-        if (gd > 1.f) {
-            int old = atomicMin(&ctl->replan1, mt.x);
-            int loser = old < mt.x ? mt.x : old;
-            if (loser != 0x7fffffff) atomicMin(&ctl->replan2, loser);
-        }
-    }
-    if (!(P->flags & 1u) && !(mt.y & META_GHOST)) {  // ghosts are published as candidates by their owner (dd_cand_body)
+    // (the id -> slot table and the wall-free replan gate of ai.cpp:151-168 are k_collide's business: both are a matter of
+    // the final state of the previous frame)
+    if (!(P->flags & 1u) && !(mt.y & META_GHOST)) {  // ghosts are published as candidates by their owner (dd_global_body)
         // keep every agent that is not inside (by delta) the polygon of extreme agents: only those can be
         // the arg-max of comm.cpp:201-220 for any query (proof in DESIGN.md)
-        const int ne = ctl->n_edges;
-        bool inside = ne >= 3;
-        // the polygon's vertices are where the extreme agents stood at the last re-sort; eroded by what anybody can have
-        // moved since, it still lies inside the hull of the current positions
-        const float delta = ctl->delta + ctl->skin;
-        for (int e = 0; e < ne && inside; ++e) {
-            float d = (p.x - ctl->ex[e]) * ctl->enx[e] + (p.y - ctl->ey[e]) * ctl->eny[e];
-            if (!(d >= delta)) inside = false;
-        }
-        if (!inside) {
+        if (!candidate_inside(ctl, p.x, p.y, ctl->delta)) {
             int k = atomicAdd(&ctl->n_cand, 1);
             b.cand[k] = make_float4(p.x, p.y, __int_as_float(mt.x), __int_as_float(s));
         }
@@ -781,6 +787,48 @@ __device__ __forceinline__ void pair_eval(const Buffers& b, int s, int j, float 
     f(j, fx, fy);
 }
 
+// The packed filter on one slot pair: cand = "may interact (ttc <= 5) or within reach of the collision pass".
+// Straight-line on purpose: with 32 lanes x 2 candidates some lane always needs the whole filter, so "early outs" only
+// added branches (the branchy version ran 77 instructions per iteration at 21 lanes); what survives is rare (~0.6
+// interacting neighbours per agent in the plaza) and costs one predictable branch per iteration.
+template <bool FIRST>
+__device__ __forceinline__ void pair_filter2(const float4 P4, const float4 V4, const float2 px2, const float2 py2, const float2 vx2,
+                                             const float2 vy2, const float2 RR2, const float near_c, bool& cand0, bool& cand1) {
+    const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
+    const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
+    // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under -fmad=false, which would round once instead
+    // of twice: every sum that consumes a product is therefore a SCALAR __fadd_rn / __fsub_rn (never contracted);
+    // packed adds only ever consume loads or other sums.  tests/test_oracle_cpu.py checks the SASS for FFMA2.
+    const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
+    const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
+    const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
+    const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
+    const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
+    const float2 bb = mul2(bq, bq), ac = mul2(a, c);
+    const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
+    // Conservative "t > 5" filter, so that sqrt + division only run for near-certain neighbours.  With c >= 0 and
+    // b <= 0: t = (-b - sqrt(disc)) / a > 5  <=>  u = -b - 5a > sqrt(disc).  Requiring u > 0 and
+    // u^2 > disc + 1e-4 b^2 leaves u - sqrt(disc) > 5e-5 |b|, two orders of magnitude above the rounding error of
+    // the reference's float evaluation of t, so no pair with float ttc <= 5 is ever filtered.
+    const float2 a5 = mul2(a, make_float2(5.f, 5.f));
+    const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));  // scalar: keeps the SASS free of FFMA2
+    const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
+    if (FIRST) {
+        // near_c > 0 (the collision reach exceeds the contact distance), so beyond it c > 0 holds and the tests on the
+        // sign of c drop out: miss = b > 0 || disc < 0 || far.  Comparisons keep the polarity of the general form
+        // below, so a NaN anywhere still makes the pair a candidate.
+        const bool far0 = u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+        const bool far1 = u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+        cand0 = c.x < near_c || !(bq.x > 0.f || disc.x < 0.f || far0);
+        cand1 = c.y < near_c || !(bq.y > 0.f || disc.y < 0.f || far1);
+    } else {
+        const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
+        const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
+        cand0 = !((c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0);
+        cand1 = !((c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1);
+    }
+}
+
 // Pair filter over the cell block of agent s: note(j) for every j in the block that MAY interact with s (ttc <= 5) or
 // is within reach of the collision pass (FIRST).  Cells of one grid row are contiguous in the sorted arrays, so each
 // row of the block is ONE contiguous slot range.  HALF: only partners that come after s in slot order (the rest of
@@ -820,44 +868,8 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
         const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
         if (!miss || (FIRST && c < near_c)) note(j);
     };
-    // The packed filter on one slot pair: cand = "may interact (ttc <= 5) or within reach of the collision pass".
-    // Straight-line on purpose: with 32 lanes x 2 candidates some lane always needs the whole filter, so "early outs" only
-    // added branches (the branchy version ran 77 instructions per iteration at 21 lanes); what survives is rare (~0.6
-    // interacting neighbours per agent in the plaza) and costs one predictable branch per iteration.
     auto filter2 = [&](const float4 P4, const float4 V4, bool& cand0, bool& cand1) {
-        const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
-        const float2 dvx = sub2(make_float2(V4.x, V4.y), vx2), dvy = sub2(make_float2(V4.z, V4.w), vy2);
-        // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under -fmad=false, which would round once instead
-        // of twice: every sum that consumes a product is therefore a SCALAR __fadd_rn / __fsub_rn (never contracted);
-        // packed adds only ever consume loads or other sums.  tests/test_oracle_cpu.py checks the SASS for FFMA2.
-        const float2 xx = mul2(mx, mx), yy2 = mul2(my, my), xd = mul2(mx, dvx), yd = mul2(my, dvy);
-        const float2 bq = make_float2(__fadd_rn(xd.x, yd.x), __fadd_rn(xd.y, yd.y));
-        const float2 c = sub2(make_float2(__fadd_rn(xx.x, yy2.x), __fadd_rn(xx.y, yy2.y)), RR2);
-        const float2 dxx = mul2(dvx, dvx), dyy = mul2(dvy, dvy);
-        const float2 a = make_float2(__fadd_rn(dxx.x, dyy.x), __fadd_rn(dxx.y, dyy.y));
-        const float2 bb = mul2(bq, bq), ac = mul2(a, c);
-        const float2 disc = make_float2(__fsub_rn(bb.x, ac.x), __fsub_rn(bb.y, ac.y));
-        // Conservative "t > 5" filter, so that sqrt + division only run for near-certain neighbours.  With c >= 0 and
-        // b <= 0: t = (-b - sqrt(disc)) / a > 5  <=>  u = -b - 5a > sqrt(disc).  Requiring u > 0 and
-        // u^2 > disc + 1e-4 b^2 leaves u - sqrt(disc) > 5e-5 |b|, two orders of magnitude above the rounding error of
-        // the reference's float evaluation of t, so no pair with float ttc <= 5 is ever filtered.
-        const float2 a5 = mul2(a, make_float2(5.f, 5.f));
-        const float2 u = make_float2(__fsub_rn(-bq.x, a5.x), __fsub_rn(-bq.y, a5.y));  // scalar: keeps the SASS free of FFMA2
-        const float2 uu = mul2(u, u), mb = mul2(bb, make_float2(1e-4f, 1e-4f));
-        if (FIRST) {
-            // near_c > 0 (the collision reach exceeds the contact distance), so beyond it c > 0 holds and the tests on the
-            // sign of c drop out: miss = b > 0 || disc < 0 || far.  Comparisons keep the polarity of the general form
-            // below, so a NaN anywhere still makes the pair a candidate.
-            const bool far0 = u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
-            const bool far1 = u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
-            cand0 = c.x < near_c || !(bq.x > 0.f || disc.x < 0.f || far0);
-            cand1 = c.y < near_c || !(bq.y > 0.f || disc.y < 0.f || far1);
-        } else {
-            const bool far0 = c.x >= 0.f && u.x > 0.f && uu.x > __fadd_rn(disc.x, mb.x);
-            const bool far1 = c.y >= 0.f && u.y > 0.f && uu.y > __fadd_rn(disc.y, mb.y);
-            cand0 = !((c.x > 0.f && bq.x > 0.f) || disc.x < 0.f || far0);
-            cand1 = !((c.y > 0.f && bq.y > 0.f) || disc.y < 0.f || far1);
-        }
+        pair_filter2<FIRST>(P4, V4, px2, py2, vx2, vy2, RR2, near_c, cand0, cand1);
     };
     for (int yy = row_lo; yy <= row_hi; ++yy) {
         // distance from the agent to the row; the outermost rows also hold whatever was clamped into them, so they reach to
@@ -905,6 +917,76 @@ __device__ __forceinline__ void scan_cells(const Buffers& b, const Ctl* ctl, int
     }
 }
 
+// EXPERIMENT (LC_PAIRS_FLAT=1, off by default): k_pairs' walk over the HALF block of agent s as ONE loop over all its rows.
+// Idea: in scan_cells every row is a loop of its own and the lanes of a warp have different trip counts per row (22 of 32
+// lanes active, profiles/prof_k_pairs_r2j_raw.csv); with the row ranges set up first, in lock step, one loop could run
+// through them back to back.  Measured on a B200 (profiles/ab_r2k_*): SLOWER, 130 vs 105 us at 1 M agents, 19 lanes
+// active.  The imbalance is not between rows but between agents: the half block of an agent at the bottom of its row is
+// up to twice that of one at the top, so the totals differ as much as the per-row counts do (a model of both loops over
+// the plaza gives 0.82 vs 0.84 lane efficiency), and widening the ranges to whole groups of four costs 10 % more tests.
+// Kept for the record and for finer stencils, where the rows are shorter.
+constexpr int FLAT_ROWS = 3;
+template <class N>
+__device__ __forceinline__ bool scan_pairs_flat(const Buffers& b, const Ctl* ctl, int s, float px, float py, float vx, float vy,
+                                                float RR, float near_c, N&& note, long long* tested = nullptr) {
+    const int nx = ctl->nx, ny = ctl->ny;
+    const float cut = ctl->cutoff * 1.001f + 1e-3f + ctl->skin, cut2 = cut * cut;   // as in scan_cells
+    const float inv_h = 1.f / ctl->hx, inv_hy = 1.f / ctl->h;
+    const int row_b = b.slot_cell[s] / nx;
+    const float yh = (py + cut - ctl->y0) * inv_hy;
+    const int row_hi = min(max((int)floorf(yh + (1e-3f + 1e-6f * fabsf(yh))), row_b), ny - 1);
+    if (row_hi - row_b >= FLAT_ROWS) return false;
+    int lo[FLAT_ROWS], hi[FLAT_ROWS];
+#pragma unroll
+    for (int r = 0; r < FLAT_ROWS; ++r) {
+        const int yy = min(row_b + r, ny - 1);
+        const float ylo = ctl->y0 + (float)yy * ctl->h;
+        const float below = yy == 0 ? 0.f : ylo - py, above = yy == ny - 1 ? 0.f : py - (ylo + ctl->h);
+        const float gap = fmaxf(fmaxf(below, above), 0.f);
+        const float rem = cut2 - gap * gap;
+        const bool live = row_b + r <= row_hi && rem > 0.f;
+        const float remc = live ? rem : 1.f;
+        const float reach = remc * rsqrtf(remc) * 1.0002f + 1e-4f;
+        const float xl = (px - reach - ctl->x0) * inv_h, xh = (px + reach - ctl->x0) * inv_h;
+        const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), 0), nx - 1);
+        const int x_hi = min(max((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), 0), nx - 1);
+        const int j0 = r == 0 ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
+        lo[r] = live && j0 < j1 ? j0 : 0;
+        hi[r] = live && j0 < j1 ? j1 : 0;
+    }
+    if (tested) {  // counting mode: the filter evaluations the loop below performs
+#pragma unroll
+        for (int r = 0; r < FLAT_ROWS; ++r) *tested += 4 * ((((hi[r] + 1) >> 1) - (lo[r] >> 1) + 1) >> 1);
+        return true;
+    }
+    const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
+    const float2 RR2 = make_float2(RR, RR);
+    const float4* __restrict__ pq = set_in(b).pq;
+    int r = 0, jl = lo[0], jh = hi[0], p = jl >> 1, pe = (jh + 1) >> 1;
+    for (;;) {
+        while (p >= pe) {  // next row (register selects: the arrays are never indexed dynamically)
+            if (++r >= FLAT_ROWS) return true;
+            jl = r == 1 ? lo[1] : lo[2];
+            jh = r == 1 ? hi[1] : hi[2];
+            p = jl >> 1; pe = (jh + 1) >> 1;
+        }
+        // slot pairs p and p + 1 (the second may lie past the range, even past the last agent: the arrays are padded and
+        // the range check below drops whatever it yields)
+        const float4 A0 = __ldg(&pq[2 * p]), B0 = __ldg(&pq[2 * p + 1]), A1 = __ldg(&pq[2 * p + 2]), B1 = __ldg(&pq[2 * p + 3]);
+        bool c0, c1, c2, c3;
+        pair_filter2<true>(A0, B0, px2, py2, vx2, vy2, RR2, near_c, c0, c1);
+        pair_filter2<true>(A1, B1, px2, py2, vx2, vy2, RR2, near_c, c2, c3);
+        if (c0 | c1 | c2 | c3) {
+            const int j = 2 * p;
+            if (c0 && j >= jl && j < jh) note(j);
+            if (c1 && j + 1 >= jl && j + 1 < jh) note(j + 1);
+            if (c2 && j + 2 >= jl && j + 2 < jh) note(j + 2);
+            if (c3 && j + 3 >= jl && j + 3 < jh) note(j + 3);
+        }
+        p += 2;
+    }
+}
+
 // Every interacting neighbour of agent s, evaluated on the spot over its whole cell block.  The rare paths only: an
 // agent whose pair list overflowed, and the per-neighbour re-scan when the hit buffer overflowed.
 template <bool FIRST, class F>
@@ -920,6 +1002,18 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
 #ifndef LC_PAIR_BLOCKS
 #define LC_PAIR_BLOCKS 12
 #endif
+#ifndef LC_PAIRS_FLAT
+#define LC_PAIRS_FLAT 0   // 1: scan_pairs_flat — measured and lost (130 vs 105 us at 1 M agents: profiles/ab_r2k_*.json, prof_k_pairs_r2k_flat_raw.csv)
+#endif
+struct PairNote {   // record the pair in the lists of both agents; entries past PAIR_CAP are only counted: k_force then scans the whole disc
+    const Buffers& b; int s; size_t stride;
+    __device__ __forceinline__ void operator()(int j) const {
+        int k = atomicAdd(&b.pair_cnt[s], 1);
+        if (k < PAIR_CAP) b.pair_list[k * stride + s] = j;
+        k = atomicAdd(&b.pair_cnt[j], 1);
+        if (k < PAIR_CAP) b.pair_list[k * stride + j] = s;
+    }
+};
 __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     const Ctl* ctl = b.ctl;
@@ -928,14 +1022,12 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P->n) return;
     const float4 me = set_in(b).pvf[s];
-    const size_t stride = (size_t)P->cap;
-    scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [&](int j) {
-        // entries past PAIR_CAP are only counted: k_force then scans the whole disc for that agent
-        int k = atomicAdd(&b.pair_cnt[s], 1);
-        if (k < PAIR_CAP) b.pair_list[k * stride + s] = j;
-        k = atomicAdd(&b.pair_cnt[j], 1);
-        if (k < PAIR_CAP) b.pair_list[k * stride + j] = s;
-    });
+    const PairNote note{b, s, (size_t)P->cap};
+#if LC_PAIRS_FLAT
+    if (scan_pairs_flat(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, note)) return;
+#endif
+    // more rows than scan_pairs_flat handles (a finer stencil was requested): the per-row walk
+    scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, note);
 }
 
 // Diagnostic twin of k_pairs: how many pair-filter evaluations the last frame's k_pairs performed (the same row ranges,
@@ -946,6 +1038,9 @@ __global__ void __launch_bounds__(128) k_pair_count(const Params* __restrict__ P
     long long tested = 0;
     if (s < P->n) {
         const float4 me = set_in(b).pvf[s];
+#if LC_PAIRS_FLAT
+        if (!scan_pairs_flat(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [](int) {}, &tested))
+#endif
         scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, [](int) {}, &tested);
     }
     for (int o = 16; o > 0; o >>= 1) tested += __shfl_xor_sync(0xffffffffu, tested, o);
@@ -959,6 +1054,7 @@ void launch_pair_count(const Params* dP, int n, const Buffers& b, unsigned long 
 #ifndef LC_FORCE_BLOCKS
 #define LC_FORCE_BLOCKS 10
 #endif
+
 // minstd_rand0 skip-ahead: 16807^e mod (2^31 - 1)
 __device__ __forceinline__ uint32_t lcg_pow_dev(unsigned long long e) {
     uint32_t r = 1u, a = 16807u;
@@ -1040,7 +1136,8 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
     __shared__ float4 s_cand[CAND_SMEM];
     __shared__ uint32_t s_bb[5];
     __shared__ int s_nc;
-    const float4* __restrict__ cand = nullptr;
+    const float4* __restrict__ cand = nullptr;   // the global list, when the block's survivors do not fit into shared memory
+    bool staged = false;
     int ncand = 0;
     if (!(P->flags & 1u)) {
         const int nc = ctl->n_cand2;
@@ -1084,7 +1181,7 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             }
         }
         __syncthreads();
-        if (s_nc <= CAND_SMEM) { cand = s_cand; ncand = s_nc; } else { cand = gc; ncand = nc; }
+        if (s_nc <= CAND_SMEM) { staged = true; ncand = s_nc; } else { cand = gc; ncand = nc; }
     }
     if (s < n) {
         const float4 me = in.pvf[s];
@@ -1177,22 +1274,31 @@ __global__ void __launch_bounds__(128, LC_FORCE_BLOCKS) k_force(const Params* __
             // within that margin go through the reference's own arithmetic, predicate and tie rule.  NaN-safe polarity:
             // a non-finite estimate is never rejected here.
             float thr = 0.f;
-            auto consider = [&](const float4 cd) {
-                const float dx = __fsub_rn(cd.x, px), dy = __fsub_rn(cd.y, py);
+            auto consider = [&](float cx, float cy, int cid, int cslot) {
+                const float dx = __fsub_rn(cx, px), dy = __fsub_rn(cy, py);
                 const float est = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
                 if (est < thr) return;
-                const int cid = __float_as_int(cd.z);
                 if (cid == id) return;
                 const float d2 = dot2(dx, dy, dx, dy);
                 if (d2 > best || (d2 == best && best_id >= 0 && cid < best_id)) {
-                    best = d2; best_id = cid; best_slot = __float_as_int(cd.w);
+                    best = d2; best_id = cid; best_slot = cslot;
                 }
                 const float t = __fmul_rn(est, 0.99999f);
                 if (t > thr) thr = t;
             };
-            // two loops so that the common case compiles to shared-memory loads instead of generic ones
-            if (cand == s_cand) for (int k = 0; k < ncand; ++k) consider(s_cand[k]);
-            else for (int k = 0; k < ncand; ++k) consider(__ldg(&cand[k]));
+            // (A packed version of this loop — two candidates per FADD2 / FMUL2 — made no difference on a B200,
+            // profiles/ab_r2n_*.json: the kernel waits on memory and barriers here, not on issue slots.)
+            if (staged) {
+                for (int k = 0; k < ncand; ++k) {
+                    const float4 cd = s_cand[k];
+                    consider(cd.x, cd.y, __float_as_int(cd.z), __float_as_int(cd.w));
+                }
+            } else {
+                for (int k = 0; k < ncand; ++k) {
+                    const float4 cd = __ldg(&cand[k]);
+                    consider(cd.x, cd.y, __float_as_int(cd.z), __float_as_int(cd.w));
+                }
+            }
             if (best_id < 0) atomicCAS(&ctl->error, 0, -3);  // comm.cpp:273-285: null partner is UB in the reference
             b.diag_partner[s] = best_id;  // slot-indexed; lc_get_partners translates to ids (k_get_diag)
             const float4 pj = __ldg(&in.pvf[best_slot]);
@@ -1459,6 +1565,9 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                 atomicAdd(&ctl->wall_hits, (unsigned long long)wcnt);
             }
         }
+        // k_force consumed the pair list: next frame's k_pairs counts from zero again.  (Here, not in k_force right after its
+        // load: there the store cost 30 us at 1 M agents, profiles/ab_r2n_*.json.)
+        b.pair_cnt[s] = 0;
         out.pvf[s] = make_float4(px, py, me.z, me.w);  // the state all_sync publishes = the next frame's frame-start state
         {   // ... and its pair-interleaved copy for the next frame's pair loop
             float* q = reinterpret_cast<float*>(out.pq + 2 * (s >> 1)) + (s & 1);
@@ -1471,6 +1580,29 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
         if constexpr (WALLS) {  // replan gate of the coming frame (ai.cpp:152-163) on the position all_sync publishes
             const float2 g = out.goal[s];
             walled_gate(P, b, walls, mt.x, px, py, g.x, g.y);
+        }
+        // The id -> slot table is a scattered 4-byte store per agent (a 32-byte sector each).  Its only reader inside the
+        // frame loop is the time-out walk of k_frame_begin (demo.cpp:691-700, id order); lc_set_state rebuilds it in
+        // k_snapshot.  So it is written only by the frame before the time-out one (and every frame after it).
+        if (__fmul_rn(LC_DT, (float)(ctl->frame + 1u)) > P->max_duration) b.slot_of_id[mt.x] = s;
+        if (!DD) {
+            // ai.cpp:154,161-163 for the coming frame: need_replan = done && goal_dist > 1 on the position it starts from
+            // (wall-free: the lost_frames clause cannot fire); the two lowest ids are served (ai.cpp:151-152,164)
+            if (mt.y & 1) {
+                const float2 g = out.goal[s];
+                if (len2(__fsub_rn(g.x, px), __fsub_rn(g.y, py)) > 1.f) {
+                    const int old = atomicMin(&ctl->replan1n, mt.x);
+                    const int loser = old < mt.x ? mt.x : old;
+                    if (loser != 0x7fffffff) atomicMin(&ctl->replan2n, loser);
+                }
+            }
+            // stage-1 comm-partner candidates of the coming frame, if it keeps the slots (k_frame_begin re-sorts after all
+            // when this frame turns out to have moved somebody by more than CAND_MARGIN)
+            if (!(P->flags & 1u) && ctl->since + 1 < P->rebin_every &&
+                !candidate_inside(ctl, px, py, ctl->delta + ctl->skin + CAND_MARGIN)) {
+                const int k = atomicAdd(&ctl->n_cand_next, 1);
+                b.cand[k] = make_float4(px, py, __int_as_float(mt.x), __int_as_float(s));
+            }
         }
         speed = __fsqrt_rn(dot3_xz(me.z, me.w, me.z, me.w));
         if (!(mt.y & 1) && !(mt.y & META_GHOST)) {  // physics.cpp:72-76
@@ -1500,8 +1632,17 @@ __global__ void __launch_bounds__(128) k_init_reduce(const Params* __restrict__ 
         const float4 pv = live.pvf[i];
         x = pv.x; y = pv.y;
         speed = __fsqrt_rn(dot3_xz(pv.z, pv.w, pv.z, pv.w));
-        nd = !(live.meta[i].y & 1);
-        b.slot_of_id[live.meta[i].x] = i;
+        const int4 mt = live.meta[i];
+        nd = !(mt.y & 1);
+        b.slot_of_id[mt.x] = i;
+        if (!nd && P->dd_world <= 1) {  // replan gate of the coming frame (later frames: k_collide)
+            const float2 g = live.goal[i];
+            if (len2(__fsub_rn(g.x, x), __fsub_rn(g.y, y)) > 1.f) {
+                const int old = atomicMin(&ctl->replan1n, mt.x);
+                const int loser = old < mt.x ? mt.x : old;
+                if (loser != 0x7fffffff) atomicMin(&ctl->replan2n, loser);
+            }
+        }
     }
     const int cnt = __syncthreads_count(nd);
     if (threadIdx.x == 0 && cnt) atomicAdd(&ctl->nnd_acc, cnt);
@@ -1686,6 +1827,8 @@ __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {
         ctl->nnd_acc = 0;
         ctl->force_rebin = 1;              // arbitrary new state: the next frame re-sorts the grid
         ctl->dmax = 0u;
+        ctl->n_cand_next = 0;
+        ctl->replan1n = ctl->replan2n = 0x7fffffff;  // k_init_reduce re-evaluates the gate on the new state
         ctl->wr1 = ctl->wr2 = 0x7fffffff;  // walled scenes: k_walled_gate re-evaluates the requests on the new state
         ctl->w_served = 0;
         for (int k = 0; k < HULL_K; ++k) ctl->ext_val[k] = -CUDART_INF_F;  // arbitrary new state: no gate next frame

@@ -21,6 +21,7 @@ constexpr int SCAN_TILE = 4096;   // cells scanned per block of k_scan_hull
 constexpr int SCAN_TILES = CELL_CAP / SCAN_TILE + 1;  // tiles cover indices [0, ncells] inclusive
 constexpr int CELL_ALLOC = SCAN_TILES * SCAN_TILE;    // allocation of cell_count / cell_start
 constexpr int EV_SORT_CAP = 2048; // events sorted in shared memory; above this the per-id path is used
+constexpr float CAND_MARGIN = 0.1f; // displacement per frame the early candidate list allows for; a frame that moved somebody further re-sorts
 
 // One copy of the per-agent state, structure of arrays.  All arrays have n elements.
 //   pv     (pos.x, pos.z, vel.x, vel.z)          Dynamics.h:4,6   — integrated, not yet pushed out (k_force -> k_collide)
@@ -78,6 +79,11 @@ struct Ctl {
     float ex[HULL_K], ey[HULL_K], enx[HULL_K], eny[HULL_K];
     int n_cand;
     int n_cand2, cand_sel;   // list k_force scans: cand_sel ? cand2 : cand, n_cand2 entries
+    // Between re-sorts the stage-1 list of a frame is compiled by the tail of the PREVIOUS frame's k_collide (it holds the
+    // final positions in registers; a pass of its own over all agents cost 11 us at 1 M): entries wait here until the next
+    // k_frame_begin, which adopts them unless it decides to re-sort after all (then k_reorder compiles the list).
+    int n_cand_next;
+    float ibx0, iby0, ibx1, iby1;   // axis-aligned box well inside the stage-1 polygon (k_scan_hull): agents in it skip the edge tests
     // reductions over the final positions / velocities of the frame (consumed by the next frame_begin)
     uint32_t minx, miny, maxx, maxy, vmax;
     // scoring: demo.cpp:650-702, physics.cpp:72-76
@@ -89,6 +95,7 @@ struct Ctl {
     int n_blkred;                // BlockRed entries waiting to be folded
     int ev_count;
     int replan1, replan2;        // ai.cpp:151-168: first two agents (table order) that need a replan
+    int replan1n, replan2n;      // ... of the coming frame, collected by k_collide (k_init_reduce after lc_create / lc_set_state)
     // counters (diagnostics)
     unsigned long long overlap2, coll_hits;
     int near_overflow, hit_overflow;

@@ -99,7 +99,7 @@ def test_legacy_config_files_run(name):
     import os
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "legacy_configs", name + ".config")
     m_cv, m_f, feat = lcb.read_config_legacy(path)
-    assert feat == lcb.FEAT_PLAIN and m_cv[0, 3] != 0 and not m_cv[1:].any() and not m_f[:, 1:].any()
+    assert feat == lcb.FEAT_PLAIN and m_cv[0].any() and not m_cv[1:].any() and not m_f[:, 1:].any()
     with pytest.raises(lcb.LcError):
         lcb.read_config(path)   # HEAD's format: the file is rejected, as the reference's parser rejects it
     pos, goal, md, rng = lcb.scene(0, 0)
