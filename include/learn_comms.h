@@ -113,6 +113,9 @@ int32_t lc_get_partners(lc_sim* sim, int32_t* partner);         /* [n] select_ne
 int32_t lc_get_neighbor_counts(lc_sim* sim, int32_t* count);    /* [n] |{j : ttc_ij <= 5}|, LMP.cpp:297-300 */
 int32_t lc_get_neighbor_lists(lc_sim* sim, int32_t* idx, int32_t cap_per_agent); /* [n][cap], ascending id; needs LC_FLAG_DEBUG_LISTS */
 int32_t lc_get_counters(lc_sim* sim, int64_t* overlap_pairs, int64_t* collision_hits, int64_t* candidates);
+/* how many of the frames executed so far re-sorted the uniform grid (the others kept slots, owners and ghosts: env
+ * LC_REBIN_EVERY, default 8; a frame that moved somebody too far re-sorts early) */
+int32_t lc_get_resorts(lc_sim* sim, int64_t* resorts);
 
 /* pair-filter evaluations k_pairs performed in the last executed frame (recounted from that frame's grid; diagnostic for
  * the FP32 leg of the roofline: the reference evaluates n (n - 1) pairs per frame, LMP.cpp:288-304) */

@@ -39,7 +39,7 @@ class _BatchDesc(C.Structure):
 EXPORTS = [
     "lc_create", "lc_destroy", "lc_set_weights", "lc_step", "lc_run_to_completion", "lc_sync", "lc_finished",
     "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
-    "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_timer_start", "lc_timer_stop",
+    "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_get_resorts", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_get_trace", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
@@ -72,6 +72,7 @@ def lib():
         L.lc_get_neighbor_counts.argtypes = [vp, vp]
         L.lc_get_neighbor_lists.argtypes = [vp, vp, i32]
         L.lc_get_counters.argtypes = [vp] + [C.POINTER(C.c_int64)] * 3
+        L.lc_get_resorts.argtypes = [vp, C.POINTER(C.c_int64)]
         L.lc_timer_start.argtypes = [vp]
         L.lc_timer_stop.argtypes = [vp, f32p]
         L.lc_kernel_launches.argtypes = [vp]
@@ -410,6 +411,12 @@ class Sim:
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         _ck(lib().lc_get_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return dict(overlap_pairs=a.value, collision_hits=b.value, candidates=c.value)
+
+    def resorts(self):
+        """Frames so far that re-sorted the grid (the others kept slots — and, decomposed, owners and ghosts)."""
+        a = C.c_int64()
+        _ck(lib().lc_get_resorts(self.h, C.byref(a)))
+        return a.value
 
     def timer_start(self):
         _ck(lib().lc_timer_start(self.h))

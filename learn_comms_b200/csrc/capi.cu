@@ -276,7 +276,8 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     std::vector<int> ids;
     std::vector<float> xb(lc::DD_MAX_WORLD + 1, 0.f);
     float halo = 0.f;
-    int cap = n_ids, annex = 0, cap_halo = 0;
+    int cap = n_ids, annex = 0, cap_halo = 0, dd_every = 1;
+    float dd_skin_allow = 0.f;
     if (dom) {
         if (world < 2 || world > lc::DD_MAX_WORLD || rank < 0 || rank >= world)
             return fail(LC_ERR_ARG, "lc_dd_create: need 2 <= world <= %d and 0 <= rank < world", lc::DD_MAX_WORLD);
@@ -285,7 +286,16 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         const float reach = R + 2.f * (1.f / 60.f) * 1.01f + 0.002f + 0.002f;
         // |vel| <= 1.045 always (unit clamp, physics.cpp:45-48, then at most 9 % from push_away, physics.cpp:32-34);
         // the band covers the TTC cutoff at 1.05 plus the collision reach.  k_frame_begin checks the live cutoff against it.
-        halo = R + 10.f * 1.05f * 1.001f + 0.01f + reach + 0.05f;
+        // Between grid re-sorts (every dd_every frames) owners, ghosts and slots are frozen and only the ghosts' records are
+        // refreshed (domain.cuh): the band is widened by twice the movement allowed for in that time.
+        {
+            const char* e = getenv("LC_REBIN_EVERY");
+            dd_every = e ? atoi(e) : 8;
+            if (dd_every < 1) dd_every = 1;
+            if (dd_every > 64) dd_every = 64;
+        }
+        dd_skin_allow = dd_every > 1 ? 0.05f * (float)dd_every + 0.1f : 0.f;
+        halo = R + 10.f * 1.05f * 1.001f + 0.01f + reach + 0.05f + 2.f * dd_skin_allow;
         xb[0] = -3.0e38f; xb[world] = 3.0e38f;
         if (dom->x_bounds) {
             for (int r = 1; r < world; ++r) xb[r] = dom->x_bounds[r];
@@ -403,6 +413,11 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
             CKC(cudaMalloc((void**)&keep, (size_t)n)); s->allocs.push_back(keep);
             CKC(cudaMemset(keep, 0, (size_t)n));
             hd.keep = keep;
+            int2* si = nullptr;
+            CKC(cudaMalloc((void**)&si, sizeof(int2) * (size_t)n)); s->allocs.push_back(si);
+            CKC(cudaMemset(si, 0xff, sizeof(int2) * (size_t)n));
+            hd.send_idx = si;
+            hd.skin_allow = dd_skin_allow;
         }
         {   // how long a rank waits for a peer's flag before it reports LC_ERR_CUDA instead of hanging the GPU
             const char* e = getenv("LC_DD_TIMEOUT_MS");
@@ -433,10 +448,10 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
     P.lcg_stride = lcg_pow(16807u, (uint64_t)n_ids);
     P.flags = d->flags;
     P.stencil_req = d->stencil > 0 ? d->stencil : 2;
-    {   // grid re-sort period (crowd.cuh: skin).  A decomposed crowd re-sorts every frame: its local set changes every frame.
+    {   // grid re-sort period (crowd.cuh: skin); a decomposed crowd also freezes owners and ghosts in between (domain.cuh)
         const char* e = getenv("LC_REBIN_EVERY");
         const int k = e ? atoi(e) : 8;
-        P.rebin_every = dom ? 1 : (k < 1 ? 1 : k);
+        P.rebin_every = dom ? dd_every : (k < 1 ? 1 : k);
     }
     P.n_walls = d->n_walls;
     P.n_bvh = 0;
@@ -820,6 +835,14 @@ int32_t lc_get_counters(lc_sim* s, int64_t* overlap_pairs, int64_t* collision_hi
     if (overlap_pairs) *overlap_pairs = (int64_t)(s->hctl->overlap2 / 2);
     if (collision_hits) *collision_hits = (int64_t)s->hctl->coll_hits;
     if (candidates) *candidates = s->hctl->n_cand2;
+    return LC_OK;
+}
+
+int32_t lc_get_resorts(lc_sim* s, int64_t* resorts) {
+    SIM_ENTER(s);
+    int rc = read_ctl(s);
+    if (rc) return rc;
+    if (resorts) *resorts = (int64_t)s->hctl->n_resorts;
     return LC_OK;
 }
 

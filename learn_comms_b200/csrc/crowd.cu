@@ -348,6 +348,7 @@ __device__ __forceinline__ void frame_begin_body(const Params* __restrict__ P, c
                 ctl->stencil_x = (int)ceilf((ctl->cutoff + 2.f * moved) / ctl->hx);
             }
             ctl->rebin = rebin;
+            ctl->n_resorts += rebin ? 1ull : 0ull;
             ctl->force_rebin = 0;
             ctl->dmax = 0u;
             // roles of the two state copies (crowd.cuh Buffers): a re-sort scatters last frame's result into the other copy
@@ -608,14 +609,47 @@ __device__ __forceinline__ bool candidate_inside(const Ctl* ctl, float x, float 
 
 // Uniform grid, phase 2 (re-sort frames only): scatter the state into cell order (counting sort) and compile the stage-1
 // list of comm-partner candidates.
+__device__ __forceinline__ void dd_route(const Params* P, float x, int role[3]);  // domain.cuh
 __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
     stamp_entry(ctl, TS_REORDER);
-    if (!ctl->rebin) return;  // the agents keep their slots, last frame's output IS this frame's input, and k_collide compiled the candidates
-    const int n = P->n_in;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (!ctl->rebin) {
+        // the agents keep their slots, last frame's output IS this frame's input, and k_collide compiled the candidates.
+        // Decomposed crowd: the neighbours' k_collide refreshed the records of our ghosts (dd_push_body); copy each over its
+        // ghost's slot.  The id -> slot table holds the ghosts' slots since the re-sort.
+        if (!b.dd) return;
+        const DomainDev* dd = b.dd;
+        const int n_l = dd->recv[2], n_r = dd->recv[0];
+        if (i >= n_l + n_r) return;
+        DDRec r;
+        r.cap = dd->lay.cap_halo;
+        r.idx = i < n_l ? i : i - n_l;
+        r.base = reinterpret_cast<const float4*>(dd->mbox[P->dd_rank] + dd->lay.region[ctl->frame & 1u][i < n_l ? 2 : 0]);
+        const float4 r0 = r.plane(0), r1 = r.plane(1), r2 = r.plane(2), r4 = r.plane(4);
+        const int id = __float_as_int(r4.x);
+        const AgentArrays& dst = set_in(b);
+        const int s = (id >= 0 && id < P->n_ids) ? b.slot_of_id[id] : -1;
+        if (s < 0 || s >= P->n || dst.meta[s].x != id || !(dst.meta[s].y & META_GHOST)) {  // the two ranks disagree on the frozen set
+            atomicCAS(&ctl->error, 0, -5);
+            return;
+        }
+        dst.pvf[s] = r0;
+        {
+            float* q = reinterpret_cast<float*>(dst.pq + 2 * (s >> 1)) + (s & 1);
+            q[0] = r0.x; q[2] = r0.y; q[4] = r0.z; q[6] = r0.w;
+        }
+        dst.vfh[s] = make_float2(r1.x, r1.y);
+        dst.goal[s] = make_float2(r1.z, r1.w);
+        dst.lgoal[s] = make_float2(r2.x, r2.y);
+        dst.facing[s] = make_float2(r2.z, r2.w);
+        dst.c4[s] = r.plane(3);
+        dst.meta[s] = make_int4(id, __float_as_int(r4.y), __float_as_int(r4.z), __float_as_int(r4.w));
+        return;
+    }
+    const int n = P->n_in;
     if (i >= n) return;
     const AgentArrays& src = set_src(b);
     const AgentArrays& dst = set_in(b);   // this frame reads what is scattered here
@@ -658,8 +692,23 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
         dst.c4[s] = src.c4[i];
         dst.meta[s] = mt;
     }
-    // (the id -> slot table and the wall-free replan gate of ai.cpp:151-168 are k_collide's business: both are a matter of
-    // the final state of the previous frame)
+    if (b.dd) {
+        // The local set is now frozen until the next re-sort.  An owned agent inside a neighbour's ghost band is that
+        // neighbour's ghost for the whole period (the neighbour reached the same verdict on the same position, either when it
+        // routed the record to us or when it kept the agent as a ghost): give it a fixed index in the neighbour's region.
+        int2 si = make_int2(-1, -1);
+        if (!(mt.y & META_GHOST)) {
+            int role[3];
+            dd_route(P, p.x, role);
+            if (role[0]) si.x = atomicAdd(&b.dd->rcount[0], 1);
+            if (role[2]) si.y = atomicAdd(&b.dd->rcount[2], 1);
+        } else {
+            b.slot_of_id[mt.x] = s;   // where the owner's refreshes of this ghost go
+        }
+        b.dd->send_idx[s] = si;
+    }
+    // (the id -> slot table of the owned agents and the wall-free replan gate of ai.cpp:151-168 are k_collide's business:
+    // both are a matter of the final state of the previous frame)
     if (!(P->flags & 1u) && !(mt.y & META_GHOST)) {  // ghosts are published as candidates by their owner (dd_global_body)
         // keep every agent that is not inside (by delta) the polygon of extreme agents: only those can be
         // the arg-max of comm.cpp:201-220 for any query (proof in DESIGN.md)
@@ -1460,6 +1509,7 @@ __device__ __forceinline__ void block_reduce_store(const Buffers& b, bool valid,
 
 template <int NT>
 __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const Buffers& b);  // domain.cuh
+__device__ __forceinline__ void dd_push_body(const Params* __restrict__ P, const Buffers& b);
 
 // S3b: collision push-out (physics.cpp:58-69 + BVH.cpp:106-120), Jacobi: every agent tests the others at their
 // integrated, not yet pushed positions; hits are applied in table (id) order.  Then physics.cpp:72-76.
@@ -1584,7 +1634,7 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
         // The id -> slot table is a scattered 4-byte store per agent (a 32-byte sector each).  Its only reader inside the
         // frame loop is the time-out walk of k_frame_begin (demo.cpp:691-700, id order); lc_set_state rebuilds it in
         // k_snapshot.  So it is written only by the frame before the time-out one (and every frame after it).
-        if (__fmul_rn(LC_DT, (float)(ctl->frame + 1u)) > P->max_duration) b.slot_of_id[mt.x] = s;
+        if (!DD && __fmul_rn(LC_DT, (float)(ctl->frame + 1u)) > P->max_duration) b.slot_of_id[mt.x] = s;
         if (!DD) {
             // ai.cpp:154,161-163 for the coming frame: need_replan = done && goal_dist > 1 on the position it starts from
             // (wall-free: the lost_frames clause cannot fire); the two lowest ids are served (ai.cpp:151-152,164)
@@ -1603,6 +1653,11 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
                 const int k = atomicAdd(&ctl->n_cand_next, 1);
                 b.cand[k] = make_float4(px, py, __int_as_float(mt.x), __int_as_float(s));
             }
+        } else if (!(P->flags & 1u) && !ctl->rebin_next && !(mt.y & META_GHOST) &&
+                   !candidate_inside(ctl, px, py, ctl->delta + ctl->skin + CAND_MARGIN)) {
+            // decomposed crowd: the same early list, over the owned agents (ghosts are published by their owner)
+            const int k = atomicAdd(&ctl->n_cand_next, 1);
+            b.cand[k] = make_float4(px, py, __int_as_float(mt.x), __int_as_float(s));
         }
         speed = __fsqrt_rn(dot3_xz(me.z, me.w, me.z, me.w));
         if (!(mt.y & 1) && !(mt.y & META_GHOST)) {  // physics.cpp:72-76
@@ -1616,7 +1671,10 @@ __global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, B
     block_reduce_store(b, valid && px == px && py == py, px, py, speed, lv_id, valid ? disp : 0.f);
     // domain mode: route every owned agent's record of the NEXT frame to its owner / ghost hosts (reads back what this
     // thread just stored: posf, vfh)
-    if (DD) dd_pack_body<128>(P, b);
+    if (DD) {
+        if (ctl->rebin_next) dd_pack_body<128>(P, b);
+        else dd_push_body(P, b);
+    }
 }
 
 // reductions of an arbitrary state (after lc_create / lc_set_state)
@@ -1828,6 +1886,7 @@ __global__ void __launch_bounds__(1024) k_reset_reductions(Buffers b) {
         ctl->force_rebin = 1;              // arbitrary new state: the next frame re-sorts the grid
         ctl->dmax = 0u;
         ctl->n_cand_next = 0;
+        ctl->rebin_next = 1;               // decomposed crowds: the first frame routes and sorts
         ctl->replan1n = ctl->replan2n = 0x7fffffff;  // k_init_reduce re-evaluates the gate on the new state
         ctl->wr1 = ctl->wr2 = 0x7fffffff;  // walled scenes: k_walled_gate re-evaluates the requests on the new state
         ctl->w_served = 0;

@@ -66,10 +66,13 @@ struct Ctl {
     // far anybody has moved since the re-sort, so the candidate set is still a superset and the exact predicate decides.
     int in_set, src_set, live;   // Buffers::set roles of the frame in flight (crowd.cuh Buffers)
     int rebin;         // this frame re-sorts (k_bin / k_scan_hull / scatter in k_reorder); else the slots stay and the copies swap roles
+    int rebin_next;    // decomposed crowds: the NEXT frame re-sorts — the same decision on every rank (dd_global_body), known before
+                       // this frame's k_collide chooses between routing records (dd_pack_body) and refreshing ghosts (dd_push_body)
     int since;         // frames since the last re-sort
     int force_rebin;   // the state was replaced (lc_create / lc_set_state)
     float skin;        // sum of the per-frame maximum displacements since the last re-sort, at this frame's start
     uint32_t dmax;     // largest displacement of the frame in flight (float bits; consumed by the next frame_begin)
+    float dmax_last;   // decomposed crowds: largest displacement of the last executed frame, over this rank and its neighbours
     // comm-partner candidate pruning
     float cx, cy, delta;
     unsigned long long ext[HULL_K];
@@ -98,6 +101,7 @@ struct Ctl {
     int replan1n, replan2n;      // ... of the coming frame, collected by k_collide (k_init_reduce after lc_create / lc_set_state)
     // counters (diagnostics)
     unsigned long long overlap2, coll_hits;
+    unsigned long long n_resorts;   // frames that re-sorted the grid (lc_get_resorts)
     int near_overflow, hit_overflow;
     // walled scenes (walls.cuh): replans are served by the host planner between frames.  The tail of k_collide evaluates
     // the gate of ai.cpp:152-168 for the NEXT frame and leaves the two lowest requesting ids here; k_frame_begin then
@@ -209,7 +213,8 @@ struct NeighbourBlob {
     uint32_t vmax;                // max speed bits over the sender's local agents
     uint32_t miny, maxy;          // order-encoded y extent of the sender's local agents
     int error;
-    int pad[3];
+    uint32_t dmax;                // largest displacement bits of the sender's last frame (the skin covers the ghosts' true movement)
+    int pad[2];
 };
 // Everything that is global (scoring, latch, replan gate, comm-partner candidates) travels later in the frame, in the
 // side-stream kernel beside k_pairs.  One per (sender, parity), written into EVERY peer's mailbox.
@@ -221,7 +226,7 @@ struct DomainBlob {
     int n_events;                 // done-events forwarded to the scoring rank (rank 0)
     int n_cand;                   // comm-partner candidates published this frame
     int error;
-    int pad;
+    int want_rebin;               // this rank's skin has used up half of what the ghost band allows for: re-sort next frame
 };
 static_assert(sizeof(DomainBlob) % 8 == 0 && sizeof(NeighbourBlob) % 8 == 0, "blobs are copied word-wise");
 struct DomainLayout {             // byte offsets inside one rank's mailbox allocation; identical on every rank
@@ -236,6 +241,12 @@ struct DomainDev {
     int replan[2];
     unsigned char* keep;          // [cap] by last frame's slot: 0 = not part of the next frame's local set, 1 = stays as owned agent,
                                   // 2 = stays as ghost of its new owner; 1 / 2 are read in place from `cur` by the next frame's sort
+    // Between re-sorts the local set is frozen: every rank keeps its owned agents and its ghosts in their slots, and the tail
+    // of k_collide only REFRESHES the ghosts (dd_push_body): the record of an owned boundary agent goes to the same index of
+    // the neighbour's region every frame, and the neighbour copies it over its ghost's slot (k_reorder, looked up by id).
+    int2* send_idx;               // [cap] by slot: record index in the left (x) / right (y) neighbour's region, -1 = not its ghost
+    int rcount[3];                // records of this rank's refresh lists (left, -, right), built by the re-sort frame's k_reorder
+    float skin_allow;             // movement since the last re-sort the ghost band was widened for (lc_dd_create)
     unsigned long long spin_timeout_ns;
 };
 DomainLayout domain_layout(int world, int cap_self, int cap_halo, int n_ids);

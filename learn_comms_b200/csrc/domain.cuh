@@ -79,6 +79,31 @@ __device__ __forceinline__ void dd_route(const Params* P, float x, int role[3]) 
     }
 }
 
+// What every owned agent contributes to the coming frame's global exchange, whichever way its record travels
+__device__ __forceinline__ void dd_owned_tail(const Params* __restrict__ P, const Buffers& b, const int4 mt, const float2 p, const float2 g,
+                                              const uint32_t frame) {
+    Ctl* ctl = b.ctl;
+    DomainDev* dd = b.dd;
+    // replan gate (ai.cpp:151-168): done && goal_dist > 1, the two lowest ids over ALL ranks; this rank's two lowest here
+    if (mt.y & 1) {
+        const float gd = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
+        if (gd > 1.f) {
+            const int old = atomicMin(&dd->replan[0], mt.x);
+            const int loser = old < mt.x ? mt.x : old;
+            if (loser != 0x7fffffff) atomicMin(&dd->replan[1], loser);
+        }
+    }
+    // demo.cpp:691-700 at the time-out frame: finish time of every not-done agent, folded in id order by the scoring rank
+    if (!ctl->finished && !(mt.y & 1)) {
+        const float fake_time = __fmul_rn(LC_DT, (float)frame);
+        if (fake_time > P->max_duration) {
+            const float l = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
+            reinterpret_cast<float*>(dd->mbox[0] + dd->lay.ev_by_id)[mt.x] =
+                __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
+        }
+    }
+}
+
 // Body of the pack step, for a block of NT threads.  Runs at the END of k_collide (the agent's final position of frame f
 // is what decides its owner and ghost roles in frame f + 1), and as a kernel of its own before the very first frame.
 template <int NT>
@@ -156,24 +181,44 @@ __device__ __forceinline__ void dd_pack_body(const Params* __restrict__ P, const
             dst[(size_t)4 * cap + slot] = make_float4(__int_as_float(m.x), __int_as_float(m.y), __int_as_float(m.z), __int_as_float(m.w));
         }
     }
-    // replan gate (ai.cpp:151-168): done && goal_dist > 1, the two lowest ids over ALL ranks; this rank's two lowest here
-    if (mt.y & 1) {
-        const float gd = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
-        if (gd > 1.f) {
-            const int old = atomicMin(&dd->replan[0], mt.x);
-            const int loser = old < mt.x ? mt.x : old;
-            if (loser != 0x7fffffff) atomicMin(&dd->replan[1], loser);
+    dd_owned_tail(P, b, mt, p, g, frame);
+}
+
+// Between re-sorts (k_collide's tail when the next frame keeps the slots): nothing is routed — owners, ghosts and slots are
+// frozen — the record of every owned agent that is a neighbour's ghost is stored at ITS index of that neighbour's region,
+// from where the neighbour copies it over the ghost's slot (k_reorder).  Same wire format as the pack, no counting.
+__device__ __forceinline__ void dd_push_body(const Params* __restrict__ P, const Buffers& b) {
+    Ctl* ctl = b.ctl;
+    DomainDev* dd = b.dd;
+    if (!dd_active(P, ctl)) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P->n) return;
+    const AgentArrays& cur = set_live(b);
+    const int4 mt = cur.meta[i];
+    if (mt.y & META_GHOST) return;
+    const uint32_t frame = ctl->frame + 1u;
+    const int par = frame & 1u, me = P->dd_rank;
+    const float4 pv = cur.pvf[i];
+    const float2 g = cur.goal[i];
+    const int2 si = dd->send_idx[i];
+    if ((si.x & si.y) != -1) {
+        const float2 vfh = cur.vfh[i], lg = cur.lgoal[i], fc = cur.facing[i];
+        const float4 c4 = cur.c4[i];
+        const int cap = dd->lay.cap_halo;
+#pragma unroll
+        for (int k = 0; k < 3; k += 2) {
+            const int slot = k == 0 ? si.x : si.y;
+            if (slot < 0) continue;
+            if (slot >= cap) { atomicCAS(&ctl->error, 0, -5); continue; }
+            float4* dst = reinterpret_cast<float4*>(dd->mbox[me - 1 + k] + dd->lay.region[par][k]);
+            dst[slot] = pv;
+            dst[(size_t)cap + slot] = make_float4(vfh.x, vfh.y, g.x, g.y);
+            dst[(size_t)2 * cap + slot] = make_float4(lg.x, lg.y, fc.x, fc.y);
+            dst[(size_t)3 * cap + slot] = c4;
+            dst[(size_t)4 * cap + slot] = make_float4(__int_as_float(mt.x), __int_as_float(mt.y | META_GHOST), __int_as_float(mt.z), __int_as_float(mt.w));
         }
     }
-    // demo.cpp:691-700 at the time-out frame: finish time of every not-done agent, folded in id order by the scoring rank
-    if (!ctl->finished && !(mt.y & 1)) {
-        const float fake_time = __fmul_rn(LC_DT, (float)frame);
-        if (fake_time > P->max_duration) {
-            const float l = len2(__fsub_rn(g.x, p.x), __fsub_rn(g.y, p.y));
-            reinterpret_cast<float*>(dd->mbox[0] + dd->lay.ev_by_id)[mt.x] =
-                __fsub_rn(__fadd_rn(__fmul_rn(2.f, l), fake_time), __int_as_float(mt.w));
-        }
-    }
+    dd_owned_tail(P, b, mt, make_float2(pv.x, pv.y), g, frame);
 }
 
 __global__ void __launch_bounds__(256) k_dd_pack(const Params* __restrict__ P, Buffers b) {
@@ -205,10 +250,11 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
         const int q = me - 1 + tid;
         if (q >= 0 && q < w) {
             NeighbourBlob nb;
-            nb.n_sent = dd->count[tid];
+            nb.n_sent = ctl->rebin_next ? dd->count[tid] : dd->rcount[tid];   // routed records / refreshed ghosts
             nb.vmax = ctl->vmax; nb.miny = ctl->miny; nb.maxy = ctl->maxy;
             nb.error = ctl->error;
-            nb.pad[0] = nb.pad[1] = nb.pad[2] = 0;
+            nb.dmax = ctl->dmax;
+            nb.pad[0] = nb.pad[1] = 0;
             // slot in the receiver: 0 = from its right neighbour (we send left), 2 = from its left neighbour (we send right)
             *(reinterpret_cast<NeighbourBlob*>(dd->mbox[q] + dd->lay.nblob[par]) + tid) = nb;
             __threadfence_system();
@@ -235,11 +281,44 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
         int err = ctl->error;
         if (!s_ok && !err) err = -2;
         int n_l = 0, n_r = 0;
-        uint32_t vmax = ctl->vmax, miny = ctl->miny, maxy = ctl->maxy;
+        uint32_t vmax = ctl->vmax, miny = ctl->miny, maxy = ctl->maxy, dmax = ctl->dmax;
         if (s_ok) {
-            if (me > 0) { const NeighbourBlob nb = nbs[2]; n_l = nb.n_sent; vmax = max(vmax, nb.vmax); miny = min(miny, nb.miny); maxy = max(maxy, nb.maxy); if (nb.error && !err) err = nb.error; }
-            if (me < w - 1) { const NeighbourBlob nb = nbs[0]; n_r = nb.n_sent; vmax = max(vmax, nb.vmax); miny = min(miny, nb.miny); maxy = max(maxy, nb.maxy); if (nb.error && !err) err = nb.error; }
+            if (me > 0) { const NeighbourBlob nb = nbs[2]; n_l = nb.n_sent; vmax = max(vmax, nb.vmax); miny = min(miny, nb.miny); maxy = max(maxy, nb.maxy); dmax = max(dmax, nb.dmax); if (nb.error && !err) err = nb.error; }
+            if (me < w - 1) { const NeighbourBlob nb = nbs[0]; n_r = nb.n_sent; vmax = max(vmax, nb.vmax); miny = min(miny, nb.miny); maxy = max(maxy, nb.maxy); dmax = max(dmax, nb.dmax); if (nb.error && !err) err = nb.error; }
         }
+        const float vm_now = __uint_as_float(vmax);
+        ctl->dmax_last = __uint_as_float(dmax);
+        if (!ctl->rebin_next) {
+            // ---- the slots stay: the neighbours refreshed our ghosts in place (k_reorder copies the records over them) ----
+            if (n_l > dd->lay.cap_halo || n_r > dd->lay.cap_halo || n_l < 0 || n_r < 0) { if (!err) err = -5; n_l = n_r = 0; }
+            dd->recv[0] = n_r; dd->recv[2] = n_l;
+            ctl->error = err;
+            float vmaxf = vm_now;
+            if (!(vmaxf <= 1.0e3f)) { vmaxf = 1.0e3f; if (!ctl->error) ctl->error = -3; }
+            // the ghosts' true movement is their owner's to report: the skin grows by the largest displacement either side saw
+            const float moved = ctl->skin + __uint_as_float(dmax);
+            ctl->cutoff = fmaxf(P->R + 10.f * vmaxf * 1.001f + 0.01f, P->near_reach);
+            ctl->skin = moved;
+            ctl->since += 1;
+            ctl->stencil = (int)ceilf((ctl->cutoff + 2.f * moved) / ctl->h);
+            ctl->stencil_x = (int)ceilf((ctl->cutoff + 2.f * moved) / ctl->hx);
+            // the band was widened by 2 * skin_allow for exactly this (lc_dd_create); dd_global_body asks for a re-sort at
+            // half of it, so only a single frame that moves somebody by metres ends up here
+            if (!(moved <= dd->skin_allow) && !ctl->error) ctl->error = -5;
+            ctl->frame = frame;
+            ctl->rebin = 0;
+            ctl->dmax = 0u;
+            const int last = ctl->live;
+            ctl->src_set = last; ctl->in_set = last; ctl->live = last ^ 1;
+            ctl->n_cand = ctl->n_cand_next;   // compiled by k_collide
+            ctl->n_cand_next = 0;
+            ctl->minx = ctl->miny = 0xffffffffu;
+            ctl->maxx = ctl->maxy = 0u;
+            ctl->vmax = 0u;
+            if (!(P->R + 10.f * vm_now * 1.001f + 0.01f + P->near_reach + 2.f * dd->skin_allow <= P->dd_halo) && !ctl->error) ctl->error = -5;
+            ctl->overlap2 = 0ull;
+            ctl->coll_hits = 0ull;
+        } else {
         const int n_prev = P->n, n_stay = dd->count[1];
         int n_in = n_prev + n_l + n_r, n_new = n_stay + n_l + n_r;
         if (n_in > P->cap || n_l > dd->lay.cap_halo || n_r > dd->lay.cap_halo || n_l < 0 || n_r < 0) {
@@ -270,8 +349,11 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
         const float vm = __uint_as_float(ctl->vmax);
         ctl->frame = frame;
         grid_from_reductions(P, ctl);
-        ctl->rebin = 1;   // the local set changes every frame (migrants, ghosts): every frame re-sorts
+        ctl->rebin = 1;   // ownership and ghost roles are re-decided: a full re-sort of stayers and received records
+        ctl->n_resorts += 1ull;
         ctl->skin = 0.f; ctl->since = 0; ctl->force_rebin = 0; ctl->dmax = 0u;
+        dd->rcount[0] = dd->rcount[1] = dd->rcount[2] = 0;   // k_reorder rebuilds the refresh lists
+        ctl->n_cand_next = 0;
         ctl->src_set = ctl->live;          // roles of the two state copies (crowd.cuh Buffers)
         ctl->in_set = ctl->live ^ 1;
         ctl->live = ctl->in_set ^ 1;       // (unchanged: a re-sort frame writes its result back into the copy it scattered from)
@@ -286,9 +368,10 @@ __global__ void __launch_bounds__(1024) k_dd_sync_begin(Params* P, Buffers b) {
             ctl->gate_rho2 = rho > 0.f ? rho * rho : -1.f;
         }
         // the ghost band was sized for the speed bound (capi.cu); a wider cutoff would miss neighbours
-        if (!(P->R + 10.f * vm * 1.001f + 0.01f + P->near_reach <= P->dd_halo) && !ctl->error) ctl->error = -5;
+        if (!(P->R + 10.f * vm * 1.001f + 0.01f + P->near_reach + 2.f * dd->skin_allow <= P->dd_halo) && !ctl->error) ctl->error = -5;
         ctl->overlap2 = 0ull;
         ctl->coll_hits = 0ull;
+        }
     }
     if (tid < HULL_K) ctl->ext[tid] = 0ull;
     if (tid == 0) stamp(ctl, TS_BEGIN_END);
@@ -340,7 +423,9 @@ __device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
         s_blob.n_events = nev;
         s_blob.n_cand = nsend;
         s_blob.error = gctl->error;
-        s_blob.pad = 0;
+        // (the frame in flight will add its own displacement, unknown yet: allow for four times the last one)
+        // and nothing is known about it in the very first frame
+        s_blob.want_rebin = frame < 2u || !(gctl->skin + 4.f * gctl->dmax_last <= 0.5f * dd->skin_allow);
     }
     __syncthreads();
     constexpr int WORDS = sizeof(DomainBlob) / 4;
@@ -371,7 +456,7 @@ __device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
     Ctl* ctl = &s_ctl;
     const DomainBlob* blobs = reinterpret_cast<const DomainBlob*>(dd->mbox[me] + dd->lay.blob[par]);
     if (tid == 0) {
-        int nnd = 0, nonfinite = 0, err = ctl->error;
+        int nnd = 0, nonfinite = 0, err = ctl->error, want = 0;
         if (!s_ok && !err) err = -2;
         unsigned long long lastvel = 0ull;
         int r1 = 0x7fffffff, r2 = 0x7fffffff;
@@ -386,6 +471,7 @@ __device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
                 if (v < r1) { r2 = r1; r1 = v; } else if (v > r1 && v < r2) r2 = v;
             }
             if (bl.error && !err) err = bl.error;
+            want |= bl.want_rebin;
             s_off[q] = off;
             off += (q == me || !s_ok) ? 0 : min(bl.n_cand, DD_CAND_CAP);
             s_evoff[q] = evoff;
@@ -401,6 +487,10 @@ __device__ void dd_global_body(const Params* __restrict__ P, const Buffers& b) {
         ctl->error = err;
         dd->replan[0] = dd->replan[1] = 0x7fffffff;
         if (comm) gctl->n_cand2 = nloc + off;   // k_force's candidate list: local survivors + everybody else's
+        // Does the NEXT frame re-sort?  By the frame count, or because somebody's skin is half used up: every rank sees the
+        // same blobs and the same counter, so every rank decides the same — this frame's k_collide routes records if so and
+        // only refreshes the ghosts if not.
+        gctl->rebin_next = (P->rebin_every <= 1 || ctl->since + 1 >= P->rebin_every || want || !s_ok) ? 1 : 0;
     }
     __syncthreads();
     if (comm) {

@@ -47,12 +47,16 @@ def _crowd(n, w, h, seed, goal_range=None):
     return pos, goal
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_domain_lockstep_bit_exact(world):
-    """4 000 agents in a 120 x 40 m field, goals all over it (agents cross strip boundaries all the time)."""
+@pytest.mark.parametrize("world,every", [(2, 8), (3, 8), (2, 1), (3, 3), (2, 16)])
+def test_domain_lockstep_bit_exact(world, every, monkeypatch):
+    """4 000 agents in a 120 x 40 m field, goals all over it (agents cross strip boundaries all the time).  `every` = the
+    re-sort period (env LC_REBIN_EVERY): in between, owners, ghosts and slots are frozen and the neighbours only refresh each
+    other's ghost records (domain.cuh dd_push_body); 1 = the frame-by-frame routing of every boundary agent."""
+    monkeypatch.setenv("LC_REBIN_EVERY", str(every))
     pos, goal = _crowd(4000, 120.0, 40.0, seed=world)
     m_cv, m_f = wl.weights(7, 0.5)
     sims = _make(pos, goal, 200.0, 12345, m_cv, m_f, world)
+    monkeypatch.delenv("LC_REBIN_EVERY")   # the single-GPU reference keeps its own default
     ref = lcb.Sim(pos, goal, m_cv, m_f, max_duration=200.0, rng_state=12345)
     migrated = 0
     own0 = np.stack([s.owned() for s in sims])
@@ -63,6 +67,8 @@ def test_domain_lockstep_bit_exact(world):
     own1 = np.stack([s.owned() for s in sims])
     migrated = int((own0 != own1).any(0).sum())
     assert migrated > 0, "no agent changed owner: the test does not exercise migration"
+    for s in sims:   # 300 frames: the first one always sorts, then one in `every` (more only if somebody moved too far)
+        assert s.resorts() == (300 if every == 1 else 2 + 298 // every), (every, s.resorts())   # (frames 1 and 2 always sort)
     full = ref.state()
     seen = np.zeros(pos.shape[0], np.int32)
     for s in sims:
@@ -108,7 +114,7 @@ def test_domain_nocomm_and_dense():
     rs = np.random.RandomState(4)   # 0.25 m mean spacing < 2 r: hundreds of initial overlaps on both sides of the cut
     pos = rs.uniform([-12, -4], [12, 4], (3000, 2)).astype(np.float32)
     goal = (pos + rs.uniform(-30, 30, (3000, 2))).astype(np.float32)
-    sims = _make(pos, goal, 100.0, 5, None, None, 2, comm=False)
+    sims = _make(pos, goal, 100.0, 5, None, None, 2, comm=False)   # (push-outs of decimetres: re-sorts every frame at first)
     ref = lcb.Sim(pos, goal, None, None, max_duration=100.0, rng_state=5, comm=False)
     hits = 0
     for chunk in range(12):
