@@ -87,6 +87,14 @@ int32_t lc_get_state(lc_sim* sim, float* pos, float* vel, float* vel_forehalf, f
                      float* local_goal, float* goal_dist, int32_t* num_done);
 int32_t lc_set_state(lc_sim* sim, const float* pos, const float* vel, const float* vel_forehalf, const float* c,
                      const float* facing, const float* local_goal, const float* goal_dist, const int32_t* num_done);
+/* lc_get_state(out...) followed by lc_set_state(in...) in one call, for teacher forcing from a recorded trajectory: the `in`
+ * tables are uploaded on a copy stream of their own while the frame still executing finishes and while the `out` tables
+ * travel the other way, and applied once the current state has been read out.  Null tables as in the two calls.
+ * Single-GPU crowds only. */
+int32_t lc_exchange_state(lc_sim* sim, float* out_pos, float* out_vel, float* out_vel_forehalf, float* out_c, float* out_facing,
+                          float* out_local_goal, float* out_goal_dist, int32_t* out_num_done, const float* pos, const float* vel,
+                          const float* vel_forehalf, const float* c, const float* facing, const float* local_goal,
+                          const float* goal_dist, const int32_t* num_done);
 int32_t lc_set_rng(lc_sim* sim, uint32_t rng_state); /* Seeder::seed (Seeder.cpp:5-20); like lc_set_state, LC_ERR_STATE on a lc_dd_* handle */
 int32_t lc_get_rng(lc_sim* sim, uint32_t* rng_state);
 

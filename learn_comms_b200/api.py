@@ -38,7 +38,7 @@ class _BatchDesc(C.Structure):
 
 EXPORTS = [
     "lc_create", "lc_destroy", "lc_set_weights", "lc_step", "lc_run_to_completion", "lc_sync", "lc_finished",
-    "lc_get_state", "lc_set_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
+    "lc_get_state", "lc_set_state", "lc_exchange_state", "lc_set_rng", "lc_get_rng", "lc_get_scores", "lc_get_partners",
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_get_resorts", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_get_trace", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
@@ -65,6 +65,7 @@ def lib():
         L.lc_finished.argtypes = [vp, C.POINTER(i32), C.POINTER(u32)]
         L.lc_get_state.argtypes = [vp] + [vp] * 8
         L.lc_set_state.argtypes = [vp] + [vp] * 8
+        L.lc_exchange_state.argtypes = [vp] + [vp] * 16
         L.lc_set_rng.argtypes = [vp, u32]
         L.lc_get_rng.argtypes = [vp, C.POINTER(u32)]
         L.lc_get_scores.argtypes = [vp, f32p, f32p, f32p, f32p, C.POINTER(i32)]
@@ -369,6 +370,18 @@ class Sim:
             arrs.append(a)
         _ck(lib().lc_set_state(self.h, *[_p(a) for a in arrs]))
         _ck(lib().lc_sync(self.h))
+
+    def exchange_state(self, out, **kw):
+        """state() into the preallocated arrays of `out` and set_state(**kw), as one call whose two copies overlap
+        (lc_exchange_state).  Keys missing from `out` / kw are skipped."""
+        ins = []
+        for k in _STATE_KEYS:
+            a = kw.get(k)
+            if a is not None:
+                a = np.ascontiguousarray(a, np.int32 if k == "num_done" else np.float32)
+            ins.append(a)
+        _ck(lib().lc_exchange_state(self.h, *[_p(out[k]) if k in out else None for k in _STATE_KEYS], *[_p(a) for a in ins]))
+        return out
 
     @property
     def rng(self):

@@ -84,6 +84,11 @@ struct lc_sim {
     // staging (device) for state exchange, pinned host mirror of Ctl
     float* stage = nullptr;
     size_t stage_floats = 0;
+    // lc_exchange_state: second staging area and copy stream, so that the upload of the next forced state runs beside the
+    // download of the current one (and beside whatever frame is still executing)
+    float* stage_in = nullptr;
+    cudaStream_t st_in = nullptr;
+    cudaEvent_t ev_in = nullptr;
     lc::Ctl* hctl = nullptr;
     // walled scenes: host planner (stateful roadmap, planner.cpp), host mirrors indexed by engine id
     lc_planner* planner = nullptr;
@@ -170,6 +175,9 @@ void lc_destroy(lc_sim* s) {
     if (s->mailbox) cudaFree(s->mailbox);
     if (s->dP) cudaFree(s->dP);
     if (s->stage) cudaFree(s->stage);
+    if (s->stage_in) cudaFree(s->stage_in);
+    if (s->st_in) cudaStreamDestroy(s->st_in);
+    if (s->ev_in) cudaEventDestroy(s->ev_in);
     if (s->hctl) cudaFreeHost(s->hctl);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -746,6 +754,68 @@ int32_t lc_set_state(lc_sim* s, const float* pos, const float* vel, const float*
     lc::launch_init_reduce(s->dP, s->n, s->b, s->st, &s->launches);
     if (s->hp.n_walls > 0) lc::launch_walled_gate(s->dP, s->n, s->b, s->st, &s->launches);  // requests of the coming frame
     return LC_OK;
+}
+
+// lc_get_state(out...) followed by lc_set_state(in...), as one call: the upload of the `in` tables starts at once on a copy
+// stream of its own — beside the frame that may still be executing and beside the download of the `out` tables (the two
+// directions of the link are independent) — and is applied once the current state has been read out.
+int32_t lc_exchange_state(lc_sim* s, float* o_pos, float* o_vel, float* o_vfh, float* o_c, float* o_facing, float* o_lgoal,
+                          float* o_goal_dist, int32_t* o_num_done, const float* pos, const float* vel, const float* vfh,
+                          const float* c, const float* facing, const float* lgoal, const float* goal_dist,
+                          const int32_t* num_done) {
+    SIM_ENTER(s);
+    if (s->dd_world > 1) return fail(LC_ERR_STATE, "lc_exchange_state: not available for a domain-decomposed crowd");
+    const size_t n = (size_t)s->n;
+    if (!s->stage_in) {
+        CK(cudaMalloc((void**)&s->stage_in, sizeof(float) * 16 * n));
+        CK(cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&s->ev_in, cudaEventDisableTiming));
+    }
+    // ---- upload (copy stream): nothing on the compute stream reads stage_in until the event below ----
+    {
+        float* st = s->stage_in;
+        float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
+        float2* dfac = (float2*)(st + 6 * n); float2* dlg = (float2*)(st + 8 * n); float* dc = st + 10 * n;
+        float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
+        if (pos) CK(cudaMemcpyAsync(dpos, pos, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st_in));
+        if (vel) CK(cudaMemcpyAsync(dvel, vel, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st_in));
+        if (vfh) CK(cudaMemcpyAsync(dvfh, vfh, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st_in));
+        if (c) CK(cudaMemcpyAsync(dc, c, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, s->st_in));
+        if (facing) CK(cudaMemcpyAsync(dfac, facing, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st_in));
+        if (lgoal) CK(cudaMemcpyAsync(dlg, lgoal, sizeof(float) * 2 * n, cudaMemcpyHostToDevice, s->st_in));
+        if (goal_dist) CK(cudaMemcpyAsync(dgd, goal_dist, sizeof(float) * n, cudaMemcpyHostToDevice, s->st_in));
+        if (num_done) CK(cudaMemcpyAsync(dnd, num_done, sizeof(int) * n, cudaMemcpyHostToDevice, s->st_in));
+        CK(cudaEventRecord(s->ev_in, s->st_in));
+    }
+    // ---- download (compute stream): gather into id order, then the copies ----
+    {
+        float* st = s->stage;
+        float2* dpos = (float2*)st; float2* dvel = (float2*)(st + 2 * n); float2* dvfh = (float2*)(st + 4 * n);
+        float2* dfac = (float2*)(st + 6 * n); float2* dlg = (float2*)(st + 8 * n); float* dc = st + 10 * n;
+        float* dgd = st + 13 * n; int* dnd = (int*)(st + 14 * n);
+        lc::launch_get_state(s->dP, s->n, s->b, o_pos ? dpos : nullptr, o_vel ? dvel : nullptr, o_vfh ? dvfh : nullptr,
+                             o_c ? dc : nullptr, o_facing ? dfac : nullptr, o_lgoal ? dlg : nullptr, o_goal_dist ? dgd : nullptr,
+                             o_num_done ? dnd : nullptr, s->st, &s->launches, s->owned_dev);
+        if (o_pos) CK(cudaMemcpyAsync(o_pos, dpos, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_vel) CK(cudaMemcpyAsync(o_vel, dvel, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_vfh) CK(cudaMemcpyAsync(o_vfh, dvfh, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_c) CK(cudaMemcpyAsync(o_c, dc, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_facing) CK(cudaMemcpyAsync(o_facing, dfac, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_lgoal) CK(cudaMemcpyAsync(o_lgoal, dlg, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_goal_dist) CK(cudaMemcpyAsync(o_goal_dist, dgd, sizeof(float) * n, cudaMemcpyDeviceToHost, s->st));
+        if (o_num_done) CK(cudaMemcpyAsync(o_num_done, dnd, sizeof(int) * n, cudaMemcpyDeviceToHost, s->st));
+        // ---- apply the new state (it has been arriving on the copy stream all the while) ----
+        CK(cudaStreamWaitEvent(s->st, s->ev_in, 0));
+        float* si = s->stage_in;
+        lc::launch_set_state(s->dP, s->n, s->b, pos ? (const float2*)si : nullptr, vel ? (const float2*)(si + 2 * n) : nullptr,
+                             vfh ? (const float2*)(si + 4 * n) : nullptr, c ? si + 10 * n : nullptr,
+                             facing ? (const float2*)(si + 6 * n) : nullptr, lgoal ? (const float2*)(si + 8 * n) : nullptr,
+                             goal_dist ? si + 13 * n : nullptr, num_done ? (const int*)(si + 14 * n) : nullptr, nullptr, nullptr, 0,
+                             s->st, &s->launches);
+        lc::launch_init_reduce(s->dP, s->n, s->b, s->st, &s->launches);
+        if (s->hp.n_walls > 0) lc::launch_walled_gate(s->dP, s->n, s->b, s->st, &s->launches);
+    }
+    return check_device_error(s);  // synchronises: the out tables are complete, the new state is in place
 }
 
 // stream state before the first draw of the NEXT frame; every frame consumes n draws (LMP.cpp:261-263)

@@ -219,6 +219,37 @@ def test_teacher_forced_single_step():
         assert np.array_equal(g.neighbor_counts(), o2.neighbor_counts())
 
 
+def test_exchange_state_equals_get_then_set():
+    """lc_exchange_state == lc_get_state followed by lc_set_state (the two copies overlap; the result may not differ):
+    teacher forcing along an oracle trajectory, reference table order, reading every frame's result back."""
+    pos, goal, md, rng = lcb.scene(5, 0)
+    m_cv, m_f = wl.weights(23)
+    o = _oracle.CanonSim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng)
+    a = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, order="reference")
+    b = lcb.Sim(pos, goal, m_cv, m_f, max_duration=md, rng_state=rng, order="reference")
+    out = {k: np.zeros_like(v) for k, v in a.state().items()}
+    for hop in (3, 40, 41, 90):
+        o.step(hop)
+        forced = o.state()
+        a.step(1)
+        b.step(1)
+        want = b.state()
+        b.set_state(**forced)
+        got = a.exchange_state(out, **forced)
+        assert_state_equal(got, want, f"exchange_state out tables at hop {hop}")
+        assert_state_equal(a.state(), b.state(), f"state after exchange_state at hop {hop}")
+        a.rng = b.rng = o.rng
+    a.step(5)
+    b.step(5)
+    assert_state_equal(a.state(), b.state(), "five frames on")
+    part = {"pos": out["pos"], "vel": out["vel"]}   # partial tables: the others keep what they were
+    a.exchange_state(part, pos=forced["pos"])
+    b_st = b.state()
+    assert np.array_equal(part["pos"], b_st["pos"]) and np.array_equal(part["vel"], b_st["vel"])
+    b.set_state(pos=forced["pos"])
+    assert_state_equal(a.state(), b.state(), "partial exchange")
+
+
 def test_corridor_grid_oracle_medium():
     """C4 shape at 1/10 scale (10 000 agents) against the grid-accelerated oracle (itself checked against brute
     force in the CPU suite)."""
