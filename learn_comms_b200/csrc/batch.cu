@@ -718,7 +718,7 @@ void lc_batch_destroy(lc_batch* b) {
     delete b;
 }
 
-int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
+static int32_t batch_create_impl(const lc_batch_desc* d, lc_batch** out) {
     if (!d || !out) return bfail(LC_ERR_ARG, "lc_batch_create: null argument");
     *out = nullptr;
     if (d->n_scenarios < 1) return bfail(LC_ERR_ARG, "lc_batch_create: n_scenarios must be >= 1");
@@ -876,8 +876,8 @@ int32_t lc_batch_reset(lc_batch* b, const float* m_cv, const float* m_f) {
     return LC_OK;
 }
 
-int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float* group_time, int32_t* n_done,
-                     int32_t* frames) {
+static int32_t batch_run_impl(lc_batch* b, int32_t max_frames, float* avg_velocity, float* group_time, int32_t* n_done,
+                              int32_t* frames) {
     BATCH_ENTER(b);
     if (max_frames < 0) return bfail(LC_ERR_ARG, "lc_batch_run: max_frames < 0");
     const int nt = (b->a.n + 31) & ~31;
@@ -958,6 +958,23 @@ int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float
     }
     if (first_err) return bfail(first_err, "scenario %d: device-side error %d (an agent without comm partner, comm.cpp:273-285)", first_err_s, first_err);
     return LC_OK;
+}
+
+// no exception crosses the C ABI (learn_comms.h): allocation failures of the host containers become LC_ERR_CAPACITY
+int32_t lc_batch_create(const lc_batch_desc* d, lc_batch** out) {
+    try {
+        return batch_create_impl(d, out);
+    } catch (...) {
+        if (out) *out = nullptr;
+        return bfail(LC_ERR_CAPACITY, "lc_batch_create: host allocation failed");
+    }
+}
+int32_t lc_batch_run(lc_batch* b, int32_t max_frames, float* avg_velocity, float* group_time, int32_t* n_done, int32_t* frames) {
+    try {
+        return batch_run_impl(b, max_frames, avg_velocity, group_time, n_done, frames);
+    } catch (...) {
+        return bfail(LC_ERR_CAPACITY, "lc_batch_run: host allocation failed while serving replans");
+    }
 }
 
 int32_t lc_batch_finished(lc_batch* b, int32_t* n_finished) {

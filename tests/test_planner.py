@@ -73,6 +73,35 @@ def test_planner_known_answers():
     assert wp.tolist() == [[4.0, 5.0]] and abs(mt - 4.0) < 1e-6
 
 
+def test_planner_clone_is_independent_and_resolves_ties_identically():
+    """lc_planner_clone: the walled batch gives every scenario its own copy of the layout's roadmap (the roadmap is
+    stateful: temporary vertices come and go, hash containers remember their history).  A clone must answer a sequence of
+    queries exactly like the original would have, and must not see what happens to the original afterwards."""
+    rs = np.random.RandomState(3)
+    walls = [[x, y, 2.0, 2.0] for x in (-6, -2, 2, 6) for y in (-4, 0, 4)]
+    a = lcb.Planner(walls, 0.15)
+    warm = [(rs.uniform(-9, 9, 2), rs.uniform(-9, 9, 2)) for _ in range(25)]
+    for s_, g_ in warm:
+        a.plan(tuple(s_), tuple(g_))
+    b = a.clone()
+    assert b.roadmap_size() == a.roadmap_size()
+    queries = [(rs.uniform(-9, 9, 2), rs.uniform(-9, 9, 2)) for _ in range(40)]
+    ra = [a.plan(tuple(s_), tuple(g_)) for s_, g_ in queries]
+    for _ in range(10):   # the original moves on; the clone is asked the same 40 questions afterwards
+        a.plan((-9.0, -9.0), (9.0, 9.0))
+    rb = [b.plan(tuple(s_), tuple(g_)) for s_, g_ in queries]
+    for (wa, ta), (wb, tb) in zip(ra, rb):
+        assert np.array_equal(wa, wb) and np.float32(ta) == np.float32(tb)
+    fresh = lcb.Planner(walls, 0.15)   # ... and like a planner that replays the whole history
+    for s_, g_ in warm:
+        fresh.plan(tuple(s_), tuple(g_))
+    for (s_, g_), (wa, ta) in zip(queries, ra):
+        wf, tf = fresh.plan(tuple(s_), tuple(g_))
+        assert np.array_equal(wa, wf) and np.float32(ta) == np.float32(tf)
+    b.close()
+    assert a.roadmap_size()[0] > 0   # closing a clone leaves the original intact
+
+
 def test_planner_error_paths():
     with pytest.raises(lcb.LcError):
         lcb.Planner([[0, 0, 1, 1]], agent_radius=0.0)
