@@ -107,6 +107,16 @@ int32_t lc_get_scores(lc_sim* sim, float* avg_velocity, float* group_time, float
  * comm_vis(c) (render.cpp:87-172; vis_f = render::VisF: 0 XYZ2LAB, 1 X2RG, 2 Y2RG, 3 Z2RG, 4 XYZ2LUV) with their black outline,
  * walls as grey squares, background of render.cpp:365.  rgba: HOST buffer [height][width][4], row 0 = far side (-z). */
 int32_t lc_render(lc_sim* sim, int32_t vis_f, float cam_dist, int32_t width, int32_t height, uint8_t* rgba);
+/* lc_render without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments and same picture as lc_render; the per-pixel scratch lc_render allocates per call lives in static device
+ * arrays of LC_RENDER_STATIC_MAX_PIXELS entries (12 MiB on every GPU that loads the library, held until exit), so
+ * width * height above that limit is refused with LC_ERR_CAPACITY.  rgba may be host or device memory.  The call performs
+ * no cudaMalloc / cudaFree and calls no allocating library routine.  All calls (of all handles on one GPU) share the
+ * scratch: every call rewrites the part it uses before reading it, but calls that overlap on the GPU race — serialise
+ * them.  The call returns after the picture has arrived in rgba. */
+#define LC_RENDER_STATIC_MAX_PIXELS (1 << 20)
+int32_t lc_render_static(lc_sim* sim, int32_t vis_f, float cam_dist, int32_t width, int32_t height, uint8_t* rgba);
 
 /* demo::update_runs' per-finisher log (demo.cpp:662 prints "t:%f u:%f s:%f" for each): [count][3] = overhead, running mean,
  * running sigma, in the order the reference's Welford update saw the finishers */

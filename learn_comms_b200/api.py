@@ -43,7 +43,7 @@ EXPORTS = [
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_get_trace", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
     "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
-    "lc_read_config", "lc_read_config_legacy", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_render", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
+    "lc_read_config", "lc_read_config_legacy", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_render", "lc_render_static", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
 
@@ -112,6 +112,7 @@ def lib():
         L.lc_get_walled.argtypes = [vp, vp, vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.lc_get_plan.argtypes = [vp, i32, vp, i32, C.POINTER(i32)]
         L.lc_render.argtypes = [vp, i32, C.c_float, i32, i32, vp]
+        L.lc_render_static.argtypes = [vp, i32, C.c_float, i32, i32, vp]
         L.lc_table_order.argtypes = [i32, i32, vp, vp]
         L.lc_static_bvh.argtypes = [i32, vp, vp, vp, i32, C.POINTER(i32)]
         L.lc_wall_geometry.argtypes = [i32, vp, vp, i32]
@@ -451,6 +452,13 @@ class Sim:
         """lc_render: RGBA8 picture [height][width][4] of the crowd coloured by comm_vis(c) (render.cpp:87-172,364-415)."""
         img = np.zeros((height, width, 4), np.uint8)
         _ck(lib().lc_render(self.h, vis_f, cam_dist, width, height, _p(img)))
+        return img
+
+    def render_static(self, vis_f=0, cam_dist=1.0, width=500, height=500, out=None):
+        """lc_render_static: the picture of render() through the entry point that allocates nothing on the device (static
+        scratch, at most 2^20 pixels).  `out` = optional preallocated uint8 array [height][width][4]."""
+        img = np.zeros((height, width, 4), np.uint8) if out is None else out
+        _ck(lib().lc_render_static(self.h, vis_f, cam_dist, width, height, _p(img)))
         return img
 
     def finish_log(self):

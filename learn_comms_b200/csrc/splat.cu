@@ -147,3 +147,57 @@ extern "C" int32_t lc_render(lc_sim* sim, int32_t vis_f, float cam_dist, int32_t
     if (e != cudaSuccess) return lc_set_error(LC_ERR_CUDA, cudaGetErrorString(e));
     return LC_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// lc_render_static: the same picture without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The per-pixel winner keys lc_render keeps in a cudaMalloc'ed buffer, and its device-side RGBA staging, live
+// in file-scope __device__ arrays of LC_RENDER_STATIC_MAX_PIXELS entries (12 MiB on every GPU that loads the library, held
+// until exit).  Host code may not hand the arrays' NAMES to a kernel — on the host they are stand-ins, not device
+// addresses — so their device addresses are looked up once per device with cudaGetSymbolAddress, with that device current.
+// Every call shares the arrays: k_splat_walls rewrites all width x height keys of the call before the agents are splatted
+// (nothing of the previous call survives in the part that is used), and calls that overlap on the GPU race.
+namespace lcv {
+static __device__ __align__(256) unsigned long long g_static_key[LC_RENDER_STATIC_MAX_PIXELS];
+static __device__ __align__(256) unsigned g_static_rgba[LC_RENDER_STATIC_MAX_PIXELS];
+constexpr int STATIC_MAX_DEVICES = 64;
+struct StaticScratch { unsigned long long* key; unsigned* rgba; };
+static StaticScratch g_static_ptr[STATIC_MAX_DEVICES];   // zero-initialised: not looked up yet
+}  // namespace lcv
+
+extern "C" int32_t lc_render_static(lc_sim* sim, int32_t vis_f, float cam_dist, int32_t width, int32_t height, uint8_t* rgba) {
+    if (!sim || !rgba || width < 1 || height < 1 || !(cam_dist > 0.f) || vis_f < 0 || vis_f > 4)
+        return lc_set_error(LC_ERR_ARG, "lc_render_static: bad argument");
+    if ((long long)width * (long long)height > (long long)LC_RENDER_STATIC_MAX_PIXELS)
+        return lc_set_error(LC_ERR_CAPACITY, "lc_render_static: width x height exceeds LC_RENDER_STATIC_MAX_PIXELS (1048576 pixels: the "
+                                             "static scratch of this entry point); use lc_render for larger pictures");
+    float2* pos = nullptr; float* c3 = nullptr; const lc::WallRect* walls = nullptr;
+    int n = 0, n_walls = 0;
+    cudaStream_t st = nullptr;
+    int rc = lc_render_state(sim, &pos, &c3, &n, &walls, &n_walls, &st);   // makes the handle's device current; allocates nothing
+    if (rc) return rc;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= lcv::STATIC_MAX_DEVICES)
+        return lc_set_error(LC_ERR_CUDA, "lc_render_static: cannot identify the current device");
+    lcv::StaticScratch& sc = lcv::g_static_ptr[dev];
+    if (!sc.key) {   // once per device, with that device current (a handle is confined to one host thread at a time;
+                     // two threads racing here on one device would both store the same two addresses)
+        unsigned long long* k = nullptr;
+        unsigned* o = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&k, lcv::g_static_key);
+        if (e == cudaSuccess) e = cudaGetSymbolAddress((void**)&o, lcv::g_static_rgba);
+        if (e != cudaSuccess || !k || !o) return lc_set_error(LC_ERR_CUDA, e != cudaSuccess ? cudaGetErrorString(e) : "lc_render_static: null symbol address");
+        sc.rgba = o;
+        sc.key = k;
+    }
+    const lcv::View v{width, height, 25.f * cam_dist / 2.f};
+    const size_t px = (size_t)width * height;
+    lcv::k_splat_walls<<<dim3((width + 15) / 16, (height + 15) / 16), dim3(16, 16), 0, st>>>(v, walls, n_walls, sc.key);   // rewrites every key in use
+    lcv::k_splat_agents<<<(n + 127) / 128, 128, 0, st>>>(v, pos, c3, n, vis_f, sc.key);
+    lcv::k_splat_resolve<<<(unsigned)((px + 255) / 256), 256, 0, st>>>(v, sc.key, sc.rgba);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgba, sc.rgba, px * 4, cudaMemcpyDefault, st);   // rgba: host or device memory
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return lc_set_error(LC_ERR_CUDA, cudaGetErrorString(e));
+    return LC_OK;
+}
