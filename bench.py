@@ -52,6 +52,8 @@ WORKLOADS = {
                     desc="PSO fitness batch: 4096 independent scenarios (512 particles x 8 wall-free layouts) x 64 agents, "
                          "per-particle comm parameters, each rolled out to its own all_done (<= 45 s = 2701 frames)",
                     sample=dict(n_scenarios=8)),
+    "pso512": dict(kind="pso", n_scenarios=512, n_agents=64, seed=3, wscale=1.0,
+                   desc="development: the first 512 scenarios of pso4096 = one rank's share of it at 8 GPUs", sample=dict(n_scenarios=8)),
     "circle1k": dict(kind="circle", n=1000, radius=80.0, seed=1, wscale=0.1,
                      desc="circle antipodal swap, 1,000 agents, r = 80 m, seed 1", sample=dict(n=1000, radius=80.0)),
     "scene0": dict(kind="scene", scene=0, seed=0, wscale=1.0,

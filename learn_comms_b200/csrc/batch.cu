@@ -118,6 +118,10 @@ __device__ __forceinline__ uint32_t lcg_pow_dev(unsigned long long e) {  // 1680
     return r;
 }
 
+#ifndef LC_BATCH_UNROLL
+#define LC_BATCH_UNROLL 2
+#endif
+constexpr int PAIR_UNROLL = LC_BATCH_UNROLL;  // slot pairs per iteration of the pair loop (#pragma unroll does not expand macros)
 template <bool WALLS>
 __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int max_frames) {
     extern __shared__ float4 s_dyn[];
@@ -326,7 +330,7 @@ __global__ void __launch_bounds__(MAX_N) k_batch_rollout(Arrays A, Consts K, int
                 unsigned m = 0u;
                 const int je = min(32, n - jb);
                 const float4* __restrict__ pp = s_pq + jb;
-#pragma unroll 2
+#pragma unroll PAIR_UNROLL
                 for (int jj = 0; jj < je; jj += 2, pp += 2) {
                     const float4 P4 = pp[0], V4 = pp[1];
                     const float2 mx = sub2(make_float2(P4.x, P4.y), px2), my = sub2(make_float2(P4.z, P4.w), py2);
