@@ -1048,6 +1048,132 @@ __device__ __forceinline__ void scan_neighbours(const Buffers& b, const Ctl* ctl
 
 // S2a: pair filter, each unordered pair tested ONCE (by the agent that comes first in cell order) and recorded in the
 // pair lists of both; k_force evaluates the lists.  Halves the pair tests of a per-agent scan of the whole disc.
+// EXPERIMENT (LC_PAIRS_STAGED=1, off by default): north_star's "stage each grid cell's agents in shared memory".  The 128
+// agents of a block are neighbours in slot order, so the slot ranges their half blocks cover overlap almost entirely: per
+// row offset (own row, the two rows above) the block stages the UNION of its threads' ranges — pair-interleaved (pos, vel)
+// records, ~450 slots = 7 KB — with coalesced loads, and every thread then runs the per-row walk of scan_cells over shared
+// memory instead of through L1.  Blocks that straddle two grid rows, see more than three rows or would need more than
+// STAGE_PAIRS slot pairs take the ordinary path (block-uniform decision).  Same tests, same order, same notes.
+// Measured on a B200: see DESIGN.md section 5 (profiles/ab_r2v_*, prof_k_pairs_r2v_staged_raw.csv).
+#ifndef LC_PAIRS_STAGED
+#define LC_PAIRS_STAGED 0
+#endif
+constexpr int STAGE_PAIRS = 352;   // slot pairs a block stages (704 agents, 11 KB)
+template <class N>
+__device__ __forceinline__ bool pairs_staged(const Buffers& b, const Ctl* ctl, int s, bool valid, float4 me, float RR, float near_c, N&& note) {
+    __shared__ float4 s_pq[2 * STAGE_PAIRS];
+    __shared__ int s_lo[3], s_hi[3], s_rowmin, s_rowmax, s_bad;
+    const float px = me.x, py = me.y, vx = me.z, vy = me.w;
+    const int nx = ctl->nx, ny = ctl->ny;
+    if (threadIdx.x < 3) { s_lo[threadIdx.x] = 0x7fffffff; s_hi[threadIdx.x] = 0; }
+    if (threadIdx.x == 0) { s_rowmin = 0x7fffffff; s_rowmax = -1; s_bad = 0; }
+    __syncthreads();
+    int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    int row_b = 0x7fffffff;
+    bool bad = false;
+    if (valid) {
+        const float cut = ctl->cutoff * 1.001f + 1e-3f + ctl->skin, cut2 = cut * cut;   // as in scan_cells
+        const float inv_h = 1.f / ctl->hx, inv_hy = 1.f / ctl->h;
+        row_b = b.slot_cell[s] / nx;
+        const float yh = (py + cut - ctl->y0) * inv_hy;
+        const int row_hi = min(max((int)floorf(yh + (1e-3f + 1e-6f * fabsf(yh))), row_b), ny - 1);
+        bad = row_hi - row_b >= 3;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const int yy = min(row_b + r, ny - 1);
+            const float ylo = ctl->y0 + (float)yy * ctl->h;
+            const float below = yy == 0 ? 0.f : ylo - py, above = yy == ny - 1 ? 0.f : py - (ylo + ctl->h);
+            const float gap = fmaxf(fmaxf(below, above), 0.f);
+            const float rem = cut2 - gap * gap;
+            const bool live = row_b + r <= row_hi && rem > 0.f;
+            const float remc = live ? rem : 1.f;
+            const float reach = remc * rsqrtf(remc) * 1.0002f + 1e-4f;
+            const float xl = (px - reach - ctl->x0) * inv_h, xh = (px + reach - ctl->x0) * inv_h;
+            const int x_lo = min(max((int)floorf(xl - (1e-3f + 1e-6f * fabsf(xl))), 0), nx - 1);
+            const int x_hi = min(max((int)floorf(xh + (1e-3f + 1e-6f * fabsf(xh))), 0), nx - 1);
+            const int j0 = r == 0 ? s + 1 : b.cell_start[yy * nx + x_lo], j1 = b.cell_start[yy * nx + x_hi + 1];
+            if (live && j0 < j1) { lo[r] = j0; hi[r] = j1; }
+        }
+    }
+    {   // union of the block's ranges per row offset; do all its agents sit in one grid row?
+        const unsigned full = 0xffffffffu;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const int l = __reduce_min_sync(full, hi[r] > lo[r] ? lo[r] : 0x7fffffff), h = __reduce_max_sync(full, hi[r]);
+            if ((threadIdx.x & 31) == 0) { if (l != 0x7fffffff) atomicMin(&s_lo[r], l); if (h) atomicMax(&s_hi[r], h); }
+        }
+        const int rmin = __reduce_min_sync(full, row_b), rmax = __reduce_max_sync(full, valid ? row_b : -1);
+        const int anybad = __any_sync(full, bad);
+        if ((threadIdx.x & 31) == 0) { atomicMin(&s_rowmin, rmin); atomicMax(&s_rowmax, rmax); if (anybad) s_bad = 1; }
+    }
+    __syncthreads();
+    int base[3], plo[3];
+    int total = 0;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const int L = s_lo[r], H = s_hi[r];
+        plo[r] = L == 0x7fffffff ? 0 : L >> 1;
+        const int cnt = L == 0x7fffffff ? 0 : ((H + 1) >> 1) - plo[r];
+        base[r] = total;
+        total += cnt;
+    }
+    if (s_bad || s_rowmin != s_rowmax || total > STAGE_PAIRS) return false;   // block-uniform
+    const float4* __restrict__ pq = set_in(b).pq;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const int cnt = (r < 2 ? base[r + 1] : total) - base[r];
+        for (int k = threadIdx.x; k < 2 * cnt; k += blockDim.x) s_pq[2 * base[r] + k] = __ldg(&pq[2 * plo[r] + k]);
+    }
+    __syncthreads();
+    if (!valid) return true;
+    const float2 px2 = make_float2(px, px), py2 = make_float2(py, py), vx2 = make_float2(vx, vx), vy2 = make_float2(vy, vy);
+    const float2 RR2 = make_float2(RR, RR);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        int j0 = lo[r], j1 = hi[r];
+        if (j0 >= j1) continue;
+        const float4* sp = s_pq + 2 * (base[r] - plo[r]);   // sp[2 p], sp[2 p + 1] = slot pair p
+        auto single = [&](int j) {   // the scalar filter of scan_cells on one half of a slot pair
+            const float4 P4 = sp[2 * (j >> 1)], V4 = sp[2 * (j >> 1) + 1];
+            const bool odd = j & 1;
+            const float qx = odd ? P4.y : P4.x, qy = odd ? P4.w : P4.z, qvx = odd ? V4.y : V4.x, qvy = odd ? V4.w : V4.z;
+            const float mx = __fsub_rn(qx, px), my = __fsub_rn(qy, py), dvx = __fsub_rn(qvx, vx), dvy = __fsub_rn(qvy, vy);
+            const float bq = dot2(mx, my, dvx, dvy), c = __fsub_rn(dot2(mx, my, mx, my), RR);
+            if (bq > 0.f && c >= near_c) return;
+            const float a = dot2(dvx, dvy, dvx, dvy);
+            const float bb = __fmul_rn(bq, bq), disc = __fsub_rn(bb, __fmul_rn(a, c));
+            const float u = __fsub_rn(-bq, __fmul_rn(a, 5.f));
+            const bool far = c >= 0.f && u > 0.f && __fmul_rn(u, u) > __fadd_rn(disc, __fmul_rn(bb, 1e-4f));
+            const bool miss = (c > 0.f && bq > 0.f) || disc < 0.f || far;
+            if (!miss || c < near_c) note(j);
+        };
+        if (j0 & 1) single(j0++);
+        if ((j1 & 1) && j1 > j0) single(--j1);
+        int p = j0 >> 1;
+        const int pe = j1 >> 1;
+        for (; p + 1 < pe; p += 2) {
+            const float4 A0 = sp[2 * p], B0 = sp[2 * p + 1], A1 = sp[2 * p + 2], B1 = sp[2 * p + 3];
+            bool c0, c1, c2, c3;
+            pair_filter2<true>(A0, B0, px2, py2, vx2, vy2, RR2, near_c, c0, c1);
+            pair_filter2<true>(A1, B1, px2, py2, vx2, vy2, RR2, near_c, c2, c3);
+            if (c0 | c1 | c2 | c3) {
+                if (c0) note(2 * p);
+                if (c1) note(2 * p + 1);
+                if (c2) note(2 * p + 2);
+                if (c3) note(2 * p + 3);
+            }
+        }
+        if (p < pe) {
+            const float4 A0 = sp[2 * p], B0 = sp[2 * p + 1];
+            bool c0, c1;
+            pair_filter2<true>(A0, B0, px2, py2, vx2, vy2, RR2, near_c, c0, c1);
+            if (c0) note(2 * p);
+            if (c1) note(2 * p + 1);
+        }
+    }
+    return true;
+}
+
 #ifndef LC_PAIR_BLOCKS
 #define LC_PAIR_BLOCKS 12
 #endif
@@ -1069,6 +1195,14 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
     if (ctl->halt) return;
     stamp_entry(b.ctl, TS_PAIRS);
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
+#if LC_PAIRS_STAGED
+    {
+        if ((int)(blockIdx.x * blockDim.x) >= P->n) return;
+        const bool valid = s < P->n;
+        const float4 me0 = valid ? set_in(b).pvf[s] : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pairs_staged(b, ctl, s, valid, me0, P->RR, P->near_c, PairNote{b, s, (size_t)P->cap})) return;
+    }
+#endif
     if (s >= P->n) return;
     const float4 me = set_in(b).pvf[s];
     const PairNote note{b, s, (size_t)P->cap};
