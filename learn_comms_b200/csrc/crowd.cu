@@ -1189,6 +1189,42 @@ struct PairNote {   // record the pair in the lists of both agents; entries past
         if (k < PAIR_CAP) b.pair_list[k * stride + j] = s;
     }
 };
+// The same, deferred: survivors are parked in a small per-thread queue in shared memory and recorded when the queue is
+// full and at the end of the walk.  A survivor costs two atomics whose results are needed for the list stores — an L2
+// round trip in the middle of the pair loop — and although only ~1 % of the tests survive, with 32 lanes x 4 candidates
+// per iteration SOME lane has one in most iterations, so the whole warp sat through that round trip again and again
+// (long-scoreboard was the kernel's top stall, and staging the candidates in shared memory did not move it).  Flushing
+// puts a thread's atomics in flight together, one count for its own list, and the warp waits once.
+#ifndef LC_NOTE_QUEUE
+#define LC_NOTE_QUEUE 4   // 0: record every survivor on the spot (PairNote)
+#endif
+struct QueuedNote {
+    const Buffers& b; int s; size_t stride;
+    int* q;    // this thread's queue: entry k at q[k * 128]
+    int nq;
+    __device__ __forceinline__ void flush() {
+        constexpr int Q = LC_NOTE_QUEUE > 0 ? LC_NOTE_QUEUE : 1;
+        if (nq == 0) return;
+        const int base = atomicAdd(&b.pair_cnt[s], nq);
+        int js[Q], kj[Q];
+#pragma unroll
+        for (int k = 0; k < Q; ++k)
+            if (k < nq) { js[k] = q[k * 128]; kj[k] = atomicAdd(&b.pair_cnt[js[k]], 1); }
+#pragma unroll
+        for (int k = 0; k < Q; ++k)
+            if (k < nq) {
+                if (base + k < PAIR_CAP) b.pair_list[(size_t)(base + k) * stride + s] = js[k];
+                if (kj[k] < PAIR_CAP) b.pair_list[(size_t)kj[k] * stride + js[k]] = s;
+            }
+        nq = 0;
+    }
+    __device__ __forceinline__ void operator()(int j) {
+        constexpr int Q = LC_NOTE_QUEUE > 0 ? LC_NOTE_QUEUE : 1;
+        if (nq == Q) flush();
+        q[nq * 128] = j;
+        ++nq;
+    }
+};
 __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     const Ctl* ctl = b.ctl;
@@ -1205,12 +1241,19 @@ __global__ void __launch_bounds__(128, LC_PAIR_BLOCKS) k_pairs(const Params* __r
 #endif
     if (s >= P->n) return;
     const float4 me = set_in(b).pvf[s];
+#if LC_NOTE_QUEUE > 0
+    __shared__ int s_queue[LC_NOTE_QUEUE][128];
+    QueuedNote note{b, s, (size_t)P->cap, &s_queue[0][threadIdx.x], 0};
+    scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, note);
+    note.flush();
+#else
     const PairNote note{b, s, (size_t)P->cap};
 #if LC_PAIRS_FLAT
     if (scan_pairs_flat(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, note)) return;
 #endif
     // more rows than scan_pairs_flat handles (a finer stencil was requested): the per-row walk
     scan_cells<true, true>(b, ctl, s, me.x, me.y, me.z, me.w, P->RR, P->near_c, note);
+#endif
 }
 
 // Diagnostic twin of k_pairs: how many pair-filter evaluations the last frame's k_pairs performed (the same row ranges,
