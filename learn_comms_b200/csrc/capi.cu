@@ -290,6 +290,7 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         if (world < 2 || world > lc::DD_MAX_WORLD || rank < 0 || rank >= world)
             return fail(LC_ERR_ARG, "lc_dd_create: need 2 <= world <= %d and 0 <= rank < world", lc::DD_MAX_WORLD);
         if (d->flags & LC_FLAG_DEBUG_LISTS) return fail(LC_ERR_ARG, "lc_dd_create: LC_FLAG_DEBUG_LISTS is single-GPU only");
+        if (n_ids < 2 * world) return fail(LC_ERR_ARG, "lc_dd_create: %d agents cannot be cut into %d strips", n_ids, world);
         const float R = d->radius + d->radius;
         const float reach = R + 2.f * (1.f / 60.f) * 1.01f + 0.002f + 0.002f;
         // |vel| <= 1.045 always (unit clamp, physics.cpp:45-48, then at most 9 % from push_away, physics.cpp:32-34);
@@ -307,14 +308,29 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         xb[0] = -3.0e38f; xb[world] = 3.0e38f;
         if (dom->x_bounds) {
             for (int r = 1; r < world; ++r) xb[r] = dom->x_bounds[r];
-        } else {  // balanced strips: cut at the n/world quantiles of the initial x coordinates (same on every rank)
+        } else {
+            // Balanced strips (same on every rank: a function of the global table only).  What a rank's kernels work on is its
+            // LOCAL set — the agents it owns plus the ghosts of its one (edge strips) or two (interior strips) bands — and the
+            // ranks run in lock step through the neighbour waits, so it is the local counts that are equalised: start from the
+            // n/world quantiles of the initial x coordinates, then shift every cut by half the difference of the loads either
+            // side of it, a few sweeps.
             std::vector<float> xs(n_ids);
             for (int i = 0; i < n_ids; ++i) xs[i] = d->pos[2 * i];
             std::sort(xs.begin(), xs.end());
-            for (int r = 1; r < world; ++r) {
-                const size_t k = (size_t)r * n_ids / world;
-                xb[r] = 0.5f * (xs[k - 1] + xs[k]);
-            }
+            std::vector<long long> cut(world + 1);   // cut[r] = agents left of strip r
+            for (int r = 0; r <= world; ++r) cut[r] = (long long)r * n_ids / world;
+            auto cut_x = [&](long long k) { return 0.5f * (xs[k - 1] + xs[k]); };
+            auto load = [&](int r) {   // agents in the ghost-extended strip r
+                const float lo = r == 0 ? -3.0e38f : cut_x(cut[r]) - halo, hi = r == world - 1 ? 3.0e38f : cut_x(cut[r + 1]) + halo;
+                return (long long)(std::lower_bound(xs.begin(), xs.end(), hi) - std::lower_bound(xs.begin(), xs.end(), lo));
+            };
+            for (int sweep = 0; sweep < 12; ++sweep)
+                for (int r = 1; r < world; ++r) {
+                    const long long shift = (load(r - 1) - load(r)) / 2;   // > 0: the left strip is heavier, the cut moves left
+                    const long long k = cut[r] - shift;
+                    cut[r] = std::min(std::max(k, cut[r - 1] + 1), cut[r + 1] - 1);
+                }
+            for (int r = 1; r < world; ++r) xb[r] = cut_x(std::min<long long>(std::max<long long>(cut[r], 1), n_ids - 1));
         }
         for (int r = 1; r + 1 < world; ++r)
             if (!(xb[r + 1] - xb[r] >= 1.05f * halo))
