@@ -477,6 +477,11 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         const int k = e ? atoi(e) : 8;
         P.rebin_every = dom ? dd_every : (k < 1 ? 1 : k);
     }
+    {   // directions of the second comm-partner pruning stage: 0 = chosen per frame by the length of the stage-1 list
+        const char* e = getenv("LC_HULL_K2");
+        const int k = e ? atoi(e) : 0;
+        P.hull_k2 = (k == 64 || k == 128 || k == 256) ? k : 0;
+    }
     P.n_walls = d->n_walls;
     P.n_bvh = 0;
     P.rng0 = d->rng_state;

@@ -742,8 +742,19 @@ __device__ __forceinline__ void refine_body(const Params* __restrict__ P, const 
     if (staged)
         for (int c = tid; c < nc; c += blockDim.x) { const float4 cd = b.cand[c]; s_cd[c] = make_float2(cd.x, cd.y); }
     __syncthreads();
-    for (int k = wid; k < HULL_K2; k += 32) {
-        const float dx = c_dir2x[k], dy = c_dir2y[k];
+    // How many directions?  The search costs K2 x nc / 1024 steps of this one block; every survivor it removes saves work in
+    // the third stage of ALL blocks of k_force.  On one GPU the kernel runs beside k_pairs and is never the longer of the
+    // two (plaza, 1 M agents: 64 / 128 / 256 directions leave 195 / 90 / 90 candidates, k_force 87 / 77 / 74 us, k_refine
+    // 15 / 19 / 28 us beside 101 us of k_pairs; corridor with its 1 400 collinear outline agents and the 1 000-agent circle,
+    // all of them hull vertices: nothing to gain, and more directions make k_refine the longer one — profiles/ab_r2y_*,
+    // bench_r2z_*).
+    // Both kernels take about 1e-4 us per unit — direction x candidate here, agent there — so the search stays the
+    // shorter one while K2 x nc is well below the agent count.
+    const long long budget = (long long)P->n / 2;
+    const int K2 = P->hull_k2 > 0 ? P->hull_k2 : (256ll * nc <= budget ? 256 : 128ll * nc <= budget ? 128 : 64);
+    const int kstep = HULL_K2 / K2;   // the K2 directions are every kstep-th of the table's
+    for (int k = wid; k < K2; k += 32) {
+        const float dx = c_dir2x[k * kstep], dy = c_dir2y[k * kstep];
         unsigned long long key = 0ull;
         for (int c = lane; c < nc; c += 32) {
             float2 q;
@@ -760,8 +771,8 @@ __device__ __forceinline__ void refine_body(const Params* __restrict__ P, const 
         if (lane == 0) s_ext[k] = key;
     }
     __syncthreads();
-    if (tid < HULL_K2) {  // edge from extreme k to extreme k+1 (CCW), inward unit normal
-        const int a = (int)(s_ext[tid] & 0xffffffffull), c = (int)(s_ext[(tid + 1) % HULL_K2] & 0xffffffffull);
+    if (tid < K2) {  // edge from extreme k to extreme k+1 (CCW), inward unit normal
+        const int a = (int)(s_ext[tid] & 0xffffffffull), c = (int)(s_ext[(tid + 1) % K2] & 0xffffffffull);
         if (a != c) {
             const float4 pa = b.cand[a], pc = b.cand[c];
             const double ux = (double)pc.x - pa.x, uy = (double)pc.y - pa.y, l = sqrt(ux * ux + uy * uy);

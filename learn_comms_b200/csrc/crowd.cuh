@@ -6,7 +6,8 @@
 namespace lc {
 
 constexpr int HULL_K = 16;        // directional extremes used to prune comm-partner candidates (stage 1, all agents)
-constexpr int HULL_K2 = 64;       // stage 2, over the stage-1 survivors only (one block does it: 256 directions cost 20 us)
+constexpr int HULL_K2 = 256;      // stage 2, over the stage-1 survivors only: UP TO this many directions (refine_body picks 64 / 128 / 256
+                                  // by the length of the stage-1 list; Params::hull_k2 / env LC_HULL_K2 force a value)
 constexpr int CAND_SMEM = 128;     // per-block candidate list of k_force (stage 3); falls back to the global list beyond
 constexpr int REFINE_MAX = 1 << 16; // stage 2 is skipped when stage 1 leaves more than this many candidates
 constexpr int PAIR_CAP = 32;      // per-agent list of pair-filter survivors (k_pairs -> k_force); beyond it k_force scans the whole disc
@@ -140,6 +141,7 @@ struct Params {
     uint32_t lcg_stride;  // 16807^n mod (2^31-1): advances an agent's private stream by one frame
     uint32_t flags;
     int stencil_req;
+    int hull_k2;          // directions of the second pruning stage (0 = by the length of the stage-1 list)
     int rebin_every;      // re-sort the grid every this many frames (1 = every frame: decomposed crowds, whose local set changes every frame)
     int n_walls, n_bvh;   // static walls (0 = wall-free: the kernels' WALLS = false instantiations)
     uint32_t rng0;        // walled: stream state before frame 1's first draw (draw k of the run = rng0 * 16807^k)
