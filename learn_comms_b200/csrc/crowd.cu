@@ -723,6 +723,40 @@ __global__ void __launch_bounds__(256) k_reorder(const Params* __restrict__ P, B
 // tested against the polygon through THEIR HULL_K2 directional extremes.  Any convex polygon whose vertices are
 // agents lies inside the true hull, so the margin argument of stage 1 applies unchanged; only the
 // number of survivors depends on the polygon.  Typically leaves the hull vertices plus a few near-hull agents.
+// Directional extremes of the stage-1 candidates, D directions per warp in one pass: the running maxima are D independent
+// chains (one direction per pass left every warp waiting on a single dependent chain: 256 directions cost 14 us more
+// than 64 that way, 6.6 us this way).  Any maximiser is a valid polygon vertex: the first lane that holds the maximum.
+template <int D>
+__device__ __forceinline__ void refine_search(const Buffers& b, int nc, bool staged, const float2* s_cd, float cx, float cy, int kstep,
+                                              unsigned long long* s_ext) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t bv[D];
+    int bc[D];
+    float ddx[D], ddy[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        bv[d] = 0u; bc[d] = 0;
+        ddx[d] = c_dir2x[(wid + 32 * d) * kstep]; ddy[d] = c_dir2y[(wid + 32 * d) * kstep];
+    }
+    for (int c = lane; c < nc; c += 32) {
+        float2 q;
+        if (staged) q = s_cd[c]; else { const float4 cd = b.cand[c]; q = make_float2(cd.x, cd.y); }
+        const float rx = q.x - cx, ry = q.y - cy;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const uint32_t ov = f2ord(rx * ddx[d] + ry * ddy[d]);
+            if (ov > bv[d]) { bv[d] = ov; bc[d] = c; }
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const uint32_t best = __reduce_max_sync(0xffffffffu, bv[d]);
+        const unsigned who = __ballot_sync(0xffffffffu, bv[d] == best);
+        const int cc = __shfl_sync(0xffffffffu, bc[d], __ffs(who) - 1);
+        if (lane == 0) s_ext[wid + 32 * d] = ((unsigned long long)best << 32) | (uint32_t)cc;
+    }
+}
+
 constexpr int REFINE_SMEM = 2048;  // candidates staged in shared memory (typical: a few hundred); beyond that they are read from global
 __device__ __forceinline__ void refine_body(const Params* __restrict__ P, const Buffers& b) {
     Ctl* ctl = b.ctl;
@@ -753,23 +787,10 @@ __device__ __forceinline__ void refine_body(const Params* __restrict__ P, const 
     const long long budget = (long long)P->n / 2;
     const int K2 = P->hull_k2 > 0 ? P->hull_k2 : (256ll * nc <= budget ? 256 : 128ll * nc <= budget ? 128 : 64);
     const int kstep = HULL_K2 / K2;   // the K2 directions are every kstep-th of the table's
-    for (int k = wid; k < K2; k += 32) {
-        const float dx = c_dir2x[k * kstep], dy = c_dir2y[k * kstep];
-        unsigned long long key = 0ull;
-        for (int c = lane; c < nc; c += 32) {
-            float2 q;
-            if (staged) q = s_cd[c]; else { const float4 cd = b.cand[c]; q = make_float2(cd.x, cd.y); }
-            const float v = (q.x - cx) * dx + (q.y - cy) * dy;
-            const unsigned long long kk = ((unsigned long long)f2ord(v) << 32) | (uint32_t)c;
-            key = kk > key ? kk : key;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
-            key = other > key ? other : key;
-        }
-        if (lane == 0) s_ext[k] = key;
-    }
+    // warp `wid` finds the extremes of directions wid, wid + 32, ... in ONE pass over the candidates (refine_search)
+    if (K2 == 256) refine_search<8>(b, nc, staged, s_cd, cx, cy, kstep, s_ext);
+    else if (K2 == 128) refine_search<4>(b, nc, staged, s_cd, cx, cy, kstep, s_ext);
+    else refine_search<2>(b, nc, staged, s_cd, cx, cy, kstep, s_ext);
     __syncthreads();
     if (tid < K2) {  // edge from extreme k to extreme k+1 (CCW), inward unit normal
         const int a = (int)(s_ext[tid] & 0xffffffffull), c = (int)(s_ext[(tid + 1) % K2] & 0xffffffffull);
