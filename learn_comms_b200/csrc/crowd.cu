@@ -1,16 +1,18 @@
 // Single-crowd frame kernels for sm_100a.  One frame of the reference loop (enginee/src/main.cpp:98-150)
 //   S0 demo::run -> S1 comm::run -> S2 ai::update_agents (LMP::calc_sum_force) -> S3 physics::simulate -> S4 all_sync
 // is eight launches (k_refine on a side stream, beside k_pairs):
-//   k_frame_begin  S0 scoring + latch; derives this frame's grid from last frame's reductions      (1 block)
-//   k_bin          cell id + rank per agent (counting sort, phase 1); directional extremes          (n threads)
-//   k_scan_hull    exclusive scan of the cell histogram; candidate-pruning polygon                  (tiles + 1 block)
-//   k_reorder      scatter the whole SoA state into cell order; replan gate; candidate compaction   (n threads)
-//   k_refine       second pruning stage of the comm-partner candidates                              (1 block)
+//   k_frame_begin  S0 scoring + latch; re-sort this frame or keep the slots (skin)? grid / roles of the two state copies (1 block)
+//   k_bin          re-sort frames: cell id + rank per agent (counting sort, phase 1); directional extremes  (n threads)
+//   k_scan_hull    re-sort frames: exclusive scan of the cell histogram; candidate-pruning polygon          (tiles + 1 block)
+//   k_reorder      re-sort frames: scatter the whole SoA state into cell order, stage-1 candidates          (n threads)
+//   k_refine       second pruning stage of the comm-partner candidates (64 - 256 directions)                (1 block)
 //   k_pairs        S2a: pair filter over the forward half of the disc-shaped cell stencil, every unordered pair
 //                  once; survivors go into both agents' pair lists                                  (n threads)
-//   k_force        S1 + S2b + S3a fused: partner arg-max, message update, goal + TTC forces from the pair list,
-//                  leap-frog integrate; emits near-lists for the collision pass                     (n threads)
-//   k_collide      S3b collision push-out (Jacobi) + avg_velocity + next frame's reductions         (n threads)
+//   k_force        S1 + S2b + S3a fused: partner arg-max, message update, goal + TTC (+ wall) forces from the pair list,
+//                  lookahead, leap-frog integrate; emits near-lists for the collision pass          (n threads)
+//   k_collide      S3b collision push-out (Jacobi; walls through the static BVH) + avg_velocity + next frame's
+//                  reductions, stage-1 candidates, replan gate                                      (n threads)
+// Seven frames in eight keep the slot order of the last re-sort (k_bin / k_scan_hull / k_reorder return at once).
 // FP32 CUDA cores only: the path is a gather / pair-test loop, not a dense contraction.
 #include "crowd.cuh"
 #include "lc_math.cuh"
