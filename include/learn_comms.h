@@ -82,7 +82,9 @@ int32_t lc_sync(lc_sim* sim);
 int32_t lc_finished(lc_sim* sim, int32_t* finished, uint32_t* frame);
 
 /* state exchange with the host engine's component tables (Dynamics.h, Agent.h, CommComp.h); HOST pointers, any may be NULL.
- * get = what POOL.all_sync publishes (Pool.cpp:69-91); set = teacher forcing / a host engine that owns the state. */
+ * get = what POOL.all_sync publishes (Pool.cpp:69-91); set = teacher forcing / a host engine that owns the state.
+ * Teacher forcing (lc_set_state, lc_exchange_state, lc_set_rng) is for single-GPU crowds only: on a lc_dd_* handle these
+ * return LC_ERR_STATE (the initial tables go to lc_dd_create; the host reads a decomposed crowd through lc_dd_get_shard). */
 int32_t lc_get_state(lc_sim* sim, float* pos, float* vel, float* vel_forehalf, float* c, float* facing,
                      float* local_goal, float* goal_dist, int32_t* num_done);
 int32_t lc_set_state(lc_sim* sim, const float* pos, const float* vel, const float* vel_forehalf, const float* c,
