@@ -107,10 +107,14 @@ def state_hash_partial(ids, pos, vel):
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,timestamp")
 
     def __init__(self, index):
-        self.index, self.proc, self.path = index, None, None
+        self.index, self.proc, self.path, self.t_mark = index, None, None, None
+
+    def mark(self):
+        """Samples taken before this moment are dropped (the sampler may be started early: nvidia-smi is slow to come up)."""
+        self.t_mark = time.time()
 
     def start(self):
         try:
@@ -126,6 +130,13 @@ class ClockSampler:
         if not self.proc:
             return out
         time.sleep(0.15)
+        t_end = time.time() + 3.0
+        late = False
+        while time.time() < t_end and os.path.getsize(self.path) == 0:   # no line yet (slow start with 8 samplers at once): wait for one
+            late = True
+            time.sleep(0.05)
+        if late:
+            out["note"] = "first sample arrived after the sampled window ended"
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -133,10 +144,27 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
         for line in open(self.path):
             f = [x.strip() for x in line.split(",")]
             if len(f) < 9:
                 continue
+            ts = None
+            if len(f) >= 10:
+                try:
+                    import datetime
+                    ts = datetime.datetime.strptime(f[9], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                except ValueError:
+                    ts = None
+            rows.append((ts, f))
+        if self.t_mark is not None:
+            inside = [r for r in rows if r[0] is not None and r[0] >= self.t_mark - 0.02]
+            if inside:
+                rows = inside
+            elif rows:
+                rows = rows[-1:]
+                out["note"] = "no sample inside the window; the last one before it"
+        for ts, f in rows:
             try:
                 sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
             except ValueError:
@@ -496,6 +524,8 @@ def main():
     # N > 1: ONE crowd of the named shape, decomposed into N x strips (one per GPU); boundary agents, comm-partner
     # candidates and the global reductions travel through peer memory over NVLink inside the frame kernels (domain.cuh)
     domain = world > 1 and not args.replicas
+    clocks = ClockSampler(local)   # started now, counted from clocks.mark() on: with 8 samplers at once nvidia-smi takes > 1 s to come up
+    clocks.start()
     pos, goal, md, rng, m_cv, m_f = make_workload(name, seed_offset=0 if domain else rank)
     n = pos.shape[0]
     if domain:
@@ -513,10 +543,12 @@ def main():
         torch.cuda.synchronize()
         sim.sync()
 
+    # nvidia-smi needs a few hundred ms for its first line and the timed region can be as short as 2 ms (20 frames on 8 GPUs):
+    # the sampler starts before the warm-up steps and runs through the timed region and the frames that follow it (timeline,
+    # per-kernel profiling: the same frames of the same crowd), so its samples are taken under this very load
+    clocks.mark()
     sim.step(W)
     barrier()
-    clocks = ClockSampler(local)
-    clocks.start()
     l0 = sim.launches
     barrier()
     sim.timer_start()
@@ -524,7 +556,6 @@ def main():
     ms = sim.timer_stop()
     barrier()
     launches = sim.launches - l0
-    clk = clocks.stop()
     if dist is not None:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -570,6 +601,8 @@ def main():
 
     # roofline leg: per-kernel device time, CUDA events between the launches on the simulation's stream
     prof = sim.step_profiled(20)
+    clk = clocks.stop()
+    clk["window"] = "warm-up + timed region + the timeline / per-kernel profiling frames right after it (same crowd, same kernels)"
     pair_tests = sim.pair_tests()
     fp = lcb.fp32_peak(local)
     t_force = (prof["k_pairs"] + prof["k_force"]) * 1e-3  # S1-S3a: pair filter + force/integrate, one logical pass over the state
