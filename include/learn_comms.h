@@ -172,6 +172,10 @@ typedef struct lc_domain_desc {
     const float* vel_forehalf;
 } lc_domain_desc;
 int32_t lc_dd_create(const lc_desc* global_desc, const lc_domain_desc* dom, lc_sim** out);
+/* the strips lc_dd_create picks when x_bounds is NULL (host code, no GPU needed): cuts x_bounds[1 .. world-1] such that the
+ * LOCAL agent counts — own strip plus the ghost bands of width ghost_band on its inner sides — are equal; x[i * stride] = pos.x
+ * of agent i; x_bounds[0] / [world] = -/+ 3e38.  No counterpart in the reference (single-threaded). */
+int32_t lc_dd_strips(int32_t n, const float* x, int32_t stride, int32_t world, float ghost_band, float* x_bounds /*[world + 1]*/);
 /* wiring: every rank needs a device pointer to every other rank's mailbox.  Same process: lc_dd_mailbox + lc_dd_connect
  * (enables peer access).  One process per GPU: lc_dd_ipc_handle (64-byte cudaIpcMemHandle_t, exchanged by the host's
  * own means, e.g. torch.distributed.all_gather) + lc_dd_connect_ipc. */

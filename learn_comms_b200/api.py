@@ -42,7 +42,7 @@ EXPORTS = [
     "lc_get_neighbor_counts", "lc_get_neighbor_lists", "lc_get_counters", "lc_get_resorts", "lc_timer_start", "lc_timer_stop",
     "lc_kernel_launches", "lc_step_profiled", "lc_count_pair_tests", "lc_fp32_peak", "lc_get_trace", "lc_batch_create", "lc_batch_destroy", "lc_batch_run", "lc_batch_get_state",
     "lc_batch_timer", "lc_batch_reset", "lc_batch_finished", "lc_batch_get_diag", "lc_batch_get_walled", "lc_batch_kernel_launches",
-    "lc_dd_create", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
+    "lc_dd_create", "lc_dd_strips", "lc_dd_mailbox", "lc_dd_connect", "lc_dd_ipc_handle", "lc_dd_connect_ipc", "lc_dd_get_owned", "lc_dd_counts", "lc_dd_get_partials", "lc_dd_get_shard",
     "lc_read_config", "lc_read_config_legacy", "lc_write_result", "lc_scene", "lc_scene_full", "lc_table_order", "lc_static_bvh", "lc_get_finish_log", "lc_get_walled", "lc_get_plan", "lc_render", "lc_render_static", "lc_wall_geometry", "lc_lookahead", "lc_planner_create", "lc_planner_destroy", "lc_planner_clone",
     "lc_planner_roadmap_size", "lc_planner_plan", "lc_last_error", "lc_version",
 ]
@@ -72,6 +72,7 @@ def lib():
         L.lc_get_partners.argtypes = [vp, vp]
         L.lc_get_neighbor_counts.argtypes = [vp, vp]
         L.lc_get_neighbor_lists.argtypes = [vp, vp, i32]
+        L.lc_dd_strips.argtypes = [i32, vp, i32, i32, C.c_float, vp]
         L.lc_get_counters.argtypes = [vp] + [C.POINTER(C.c_int64)] * 3
         L.lc_get_resorts.argtypes = [vp, C.POINTER(C.c_int64)]
         L.lc_timer_start.argtypes = [vp]
@@ -147,6 +148,14 @@ def scene(scene_id, seed=0):
     if n <= 0:
         raise LcError(n, f"scene {scene_id} is not in the wall-free catalogue")
     return pos[:n].copy(), goal[:n].copy(), float(md.value), int(rng.value)
+
+
+def dd_strips(pos, world, ghost_band):
+    """lc_dd_strips: the x cuts lc_dd_create picks by default (local counts — owned + ghosts — equalised).  Host code."""
+    pos = np.ascontiguousarray(pos, np.float32)
+    xb = np.zeros(world + 1, np.float32)
+    _ck(lib().lc_dd_strips(pos.shape[0], _p(pos), 2, world, C.c_float(ghost_band), _p(xb)))
+    return xb
 
 
 def scene_full(scene_id, seed=0):

@@ -308,29 +308,10 @@ static int create_impl(const lc_desc* d, const lc_domain_desc* dom, lc_sim** out
         xb[0] = -3.0e38f; xb[world] = 3.0e38f;
         if (dom->x_bounds) {
             for (int r = 1; r < world; ++r) xb[r] = dom->x_bounds[r];
-        } else {
-            // Balanced strips (same on every rank: a function of the global table only).  What a rank's kernels work on is its
-            // LOCAL set — the agents it owns plus the ghosts of its one (edge strips) or two (interior strips) bands — and the
-            // ranks run in lock step through the neighbour waits, so it is the local counts that are equalised: start from the
-            // n/world quantiles of the initial x coordinates, then shift every cut by half the difference of the loads either
-            // side of it, a few sweeps.
+        } else {  // balanced strips (host.cpp lc_dd_strips: same on every rank, a function of the global table only)
             std::vector<float> xs(n_ids);
             for (int i = 0; i < n_ids; ++i) xs[i] = d->pos[2 * i];
-            std::sort(xs.begin(), xs.end());
-            std::vector<long long> cut(world + 1);   // cut[r] = agents left of strip r
-            for (int r = 0; r <= world; ++r) cut[r] = (long long)r * n_ids / world;
-            auto cut_x = [&](long long k) { return 0.5f * (xs[k - 1] + xs[k]); };
-            auto load = [&](int r) {   // agents in the ghost-extended strip r
-                const float lo = r == 0 ? -3.0e38f : cut_x(cut[r]) - halo, hi = r == world - 1 ? 3.0e38f : cut_x(cut[r + 1]) + halo;
-                return (long long)(std::lower_bound(xs.begin(), xs.end(), hi) - std::lower_bound(xs.begin(), xs.end(), lo));
-            };
-            for (int sweep = 0; sweep < 12; ++sweep)
-                for (int r = 1; r < world; ++r) {
-                    const long long shift = (load(r - 1) - load(r)) / 2;   // > 0: the left strip is heavier, the cut moves left
-                    const long long k = cut[r] - shift;
-                    cut[r] = std::min(std::max(k, cut[r - 1] + 1), cut[r + 1] - 1);
-                }
-            for (int r = 1; r < world; ++r) xb[r] = cut_x(std::min<long long>(std::max<long long>(cut[r], 1), n_ids - 1));
+            if (lc_dd_strips(n_ids, xs.data(), 1, world, halo, xb.data()) != LC_OK) return LC_ERR_ARG;
         }
         for (int r = 1; r + 1 < world; ++r)
             if (!(xb[r + 1] - xb[r] >= 1.05f * halo))

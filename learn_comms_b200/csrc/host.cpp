@@ -389,3 +389,31 @@ int32_t lc_write_result(const char* path, float avg_velocity, float group_time) 
 }
 
 }  // extern "C"
+
+// lc_dd_create's default strips.  What a rank's kernels work on is its LOCAL set — the agents it owns plus the ghosts of its
+// one (edge strips) or two (interior strips) bands — and the ranks run in lock step through the neighbour waits, so it is
+// the local counts that are equalised: start from the n/world quantiles of the x coordinates, then shift every cut by half
+// the difference of the loads either side of it, a few sweeps.  Host code, same result on every rank.
+int lc_set_error(int code, const char* msg);  // capi.cu: text returned by lc_last_error()
+extern "C" int32_t lc_dd_strips(int32_t n, const float* x, int32_t stride, int32_t world, float ghost_band, float* x_bounds) {
+    if (!x || !x_bounds || stride < 1 || world < 1 || n < 2 * world || !(ghost_band >= 0.f))
+        return lc_set_error(LC_ERR_ARG, "lc_dd_strips: need x, x_bounds, stride >= 1, world >= 1, n >= 2 world, ghost_band >= 0");
+    std::vector<float> xs((size_t)n);
+    for (int i = 0; i < n; ++i) xs[i] = x[(size_t)i * stride];
+    std::sort(xs.begin(), xs.end());
+    std::vector<long long> cut((size_t)world + 1);   // cut[r] = agents left of strip r
+    for (int r = 0; r <= world; ++r) cut[r] = (long long)r * n / world;
+    auto cut_x = [&](long long k) { return 0.5f * (xs[k - 1] + xs[k]); };
+    auto load = [&](int r) {   // agents in the ghost-extended strip r
+        const float lo = r == 0 ? -3.0e38f : cut_x(cut[r]) - ghost_band, hi = r == world - 1 ? 3.0e38f : cut_x(cut[r + 1]) + ghost_band;
+        return (long long)(std::lower_bound(xs.begin(), xs.end(), hi) - std::lower_bound(xs.begin(), xs.end(), lo));
+    };
+    for (int sweep = 0; sweep < 12; ++sweep)
+        for (int r = 1; r < world; ++r) {
+            const long long shift = (load(r - 1) - load(r)) / 2;   // > 0: the left strip is heavier, the cut moves left
+            cut[r] = std::min(std::max(cut[r] - shift, cut[r - 1] + 1), cut[r + 1] - 1);
+        }
+    x_bounds[0] = -3.0e38f; x_bounds[world] = 3.0e38f;
+    for (int r = 1; r < world; ++r) x_bounds[r] = cut_x(std::min<long long>(std::max<long long>(cut[r], 1), n - 1));
+    return LC_OK;
+}

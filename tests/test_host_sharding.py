@@ -100,3 +100,36 @@ def test_domain_score_merge_is_pure_host_logic():
     assert np.isnan(lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 1, 0.25), (key(99, 0.75), 0, 0.25)])["avg_velocity"])
     assert np.isinf(lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 0, 0.25), (key(99, np.inf), 1, 0.25)])["avg_velocity"])
     assert np.isnan(lcb.DomainSim.merge_scores(r0, [(key(10, 0.5), 0, np.nan), (key(99, 0.75), 0, np.nan)])["avg_velocity"])
+
+
+def test_dd_strips_equalise_the_local_counts():
+    """lc_dd_strips (host code; lc_dd_create's default cuts): the LOCAL counts — own strip plus ghost bands — are what the
+    ranks' kernels work on, so those are equalised, not the owned counts: interior strips own fewer agents than edge strips."""
+    import learn_comms_b200 as lcb
+    rs = np.random.RandomState(11)
+    n, band = 200_000, 11.9
+    pos = np.stack([rs.uniform(-1000, 1000, n), rs.uniform(-1000, 1000, n)], 1).astype(np.float32)
+    xs = np.sort(pos[:, 0])
+    for world in (2, 4, 8):
+        xb = lcb.dd_strips(pos, world, band)
+        assert xb[0] < -1e38 and xb[world] > 1e38 and (np.diff(xb[1:world]) > 0).all()
+        lo = np.where(np.arange(world) == 0, -np.inf, xb[:world] - band)
+        hi = np.where(np.arange(world) == world - 1, np.inf, xb[1:] + band)
+        local = np.array([np.searchsorted(xs, h) - np.searchsorted(xs, l) for l, h in zip(lo, hi)])
+        owned = np.array([np.searchsorted(xs, xb[r + 1]) - np.searchsorted(xs, xb[r]) for r in range(world)])
+        assert owned.sum() == n
+        assert local.max() - local.min() <= 0.002 * local.mean(), (world, local)
+        if world > 2:   # the quantile cuts would leave the interior strips a ghost band heavier
+            assert owned[0] > owned[1] and owned[-1] > owned[-2]
+            q = np.array([np.searchsorted(xs, np.inf if r == world - 1 else xs[(r + 1) * n // world] + band) -
+                          np.searchsorted(xs, -np.inf if r == 0 else xs[r * n // world] - band) for r in range(world)])
+            assert q.max() - q.min() > 10 * (local.max() - local.min())
+    # a lopsided crowd: three quarters of the agents in the left tenth
+    pos2 = pos.copy()
+    pos2[: 3 * n // 4, 0] = rs.uniform(-1000, -800, 3 * n // 4)
+    xb = lcb.dd_strips(pos2, 4, band)
+    xs2 = np.sort(pos2[:, 0])
+    local = [np.searchsorted(xs2, (np.inf if r == 3 else xb[r + 1] + band)) - np.searchsorted(xs2, (-np.inf if r == 0 else xb[r] - band)) for r in range(4)]
+    assert max(local) - min(local) <= 0.01 * np.mean(local), local
+    with pytest.raises(lcb.LcError):
+        lcb.dd_strips(pos[:5], 4, band)   # fewer than two agents per strip
