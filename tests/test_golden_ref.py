@@ -234,3 +234,37 @@ def test_live_reference_wall_geometry_matches_canon():
     spec.loader.exec_module(mod)
     rec = mod.inputs(seed=2024, k=20000)
     _assert_wall_words_equal(_oracle.wall_geometry(rec), _oref.run_geom(rec))
+
+
+@pytest.mark.skipif(not _oref.available(), reason="oracle/_ref/oref not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("scene", list(range(19)))
+def test_live_whole_scene_catalogue_matches_the_reference(scene):
+    """Every scene id of demo.cpp:141-511 through the reference's own demo::init (O-ref, one frame) against the catalogue
+    of the product (lc_scene_full, host.cpp) and of the oracle (canon_scene_full): start positions, goals, wall rectangles
+    in creation order, and the order the reference's tables iterate in (lc_table_order)."""
+    import learn_comms_b200 as lcb
+    for seed in ((0, 3) if scene == 12 else (0,)):   # scene 12 draws its layout from the seed
+        ref = _oref.run(scene, seed=seed, max_frames=1, dump_every=1)
+        for tag, (pos, goal, md, rng, walls) in (("product", lcb.scene_full(scene, seed)), ("oracle", _oracle.scene_full(scene, seed))):
+            assert len(pos) == ref["n"] and len(walls) == ref["n_walls"], (tag, scene)
+            assert np.array_equal(pos, ref["pos0"]) and np.array_equal(goal, ref["goal"]), (tag, scene)
+            assert np.array_equal(np.asarray(walls, np.float32).reshape(-1, 4), ref["walls"]), (tag, scene)
+        order, wall_order = lcb.table_order(ref["n"], ref["n_walls"])
+        assert np.array_equal(order, ref["order"]), scene
+        if ref["n_walls"]:
+            assert np.array_equal(wall_order, ref["wall_order"]), scene
+
+
+def test_whole_scene_catalogue_matches_the_reference_fixture():
+    """The same against the committed dump of the reference's demo::init for all 19 scene ids (tools/make_golden_catalogue.py):
+    runs wherever the library builds, O-ref or not."""
+    import learn_comms_b200 as lcb
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "catalogue_oref.npz"))
+    assert len(g["cases"]) == 20
+    for scene, seed in g["cases"]:
+        k = f"s{scene}_{seed}"
+        for tag, (pos, goal, md, rng, walls) in (("product", lcb.scene_full(int(scene), int(seed))), ("oracle", _oracle.scene_full(int(scene), int(seed)))):
+            assert np.array_equal(pos, g[k + "_pos"]) and np.array_equal(goal, g[k + "_goal"]), (tag, k)
+            assert np.array_equal(np.asarray(walls, np.float32).reshape(-1, 4), g[k + "_walls"]), (tag, k)
+        order, wall_order = lcb.table_order(len(g[k + "_pos"]), len(g[k + "_walls"]))
+        assert np.array_equal(order, g[k + "_order"]) and np.array_equal(wall_order[:len(g[k + "_walls"])], g[k + "_wall_order"]), k
