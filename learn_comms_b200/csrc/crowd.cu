@@ -1725,7 +1725,10 @@ __device__ __forceinline__ void dd_push_body(const Params* __restrict__ P, const
 // S3b: collision push-out (physics.cpp:58-69 + BVH.cpp:106-120), Jacobi: every agent tests the others at their
 // integrated, not yet pushed positions; hits are applied in table (id) order.  Then physics.cpp:72-76.
 template <bool DD, bool WALLS>
-__global__ void __launch_bounds__(128) k_collide(const Params* __restrict__ P, Buffers b) {
+#ifndef LC_COLLIDE_BLOCKS
+#define LC_COLLIDE_BLOCKS 10
+#endif
+__global__ void __launch_bounds__(128, LC_COLLIDE_BLOCKS) k_collide(const Params* __restrict__ P, Buffers b) {
     pdl_enter();
     Ctl* ctl = b.ctl;
     if (ctl->halt) return;
