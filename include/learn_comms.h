@@ -165,7 +165,7 @@ int32_t lc_step_profiled(lc_sim* sim, int32_t nframes, float* ms_per_kernel);
  * round trip).  All ranks must be stepped by the same number of frames.  Results are bit-identical to lc_create's. */
 typedef struct lc_domain_desc {
     int32_t rank, world;        /* 2 <= world <= 8 */
-    const float* x_bounds;      /* [world + 1] strip boundaries (entries 1..world-1 are used); NULL = balanced quantiles of pos.x */
+    const float* x_bounds;      /* [world + 1] strip boundaries (entries 1..world-1 are used); NULL = lc_dd_strips (local counts equalised) */
     int32_t capacity;           /* local slot capacity (owned + ghost agents); 0 = 1.5 n/world + 2 halo_capacity */
     int32_t halo_capacity;      /* records one neighbour may send per frame; 0 = max(65536, n/world/2) */
     const float* vel;           /* optional [n][2] initial vel and vel_forehalf (developed-flow benchmarks); NULL = at rest */
